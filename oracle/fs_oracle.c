@@ -1,0 +1,639 @@
+/* oracle/fs_oracle.c -- TEST INFRASTRUCTURE ONLY (checker, never product; see fs_oracle.h).
+ *
+ * Plain-C, scalar, single-threaded restatement of the stencil operators on the reference's
+ * timestep path.  Each function cites the reference lines it follows.  Arithmetic is written
+ * in the same operation order as the reference; the library is built with
+ * -ffp-contract=off, so it is the un-fused (no FMA) evaluation of those expressions.
+ *
+ * Parity pin: tests/test_oracle_vs_ref.py checks every function here against the UNMODIFIED
+ * reference compiled into oracle/_ref/libfsref.so, and tests/golden/ holds outputs of that
+ * library for the GPU box, where /root/reference does not exist.
+ */
+#include "fs_oracle.h"
+
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define NX (fs->nx)
+#define NY (fs->ny)
+/* accessors in the reference's storage (src/Container.hpp:105-111) */
+#define IU(i, j) ((j) + 1 + ((i) + 1) * (NY + 2))  /* U-like: (NX+3) x (NY+2) */
+#define IV(i, j) ((j) + 1 + ((i) + 1) * (NY + 3))  /* V-like: (NX+2) x (NY+3) */
+#define IC(i, j) ((j) + 1 + ((i) + 1) * (NY + 2))  /* cell:   (NX+2) x (NY+2) */
+/* Layout::F cell index (i fastest), src/Container.hpp:109 */
+#define IF(i, j) ((i) + 1 + ((j) + 1) * (NX + 2))
+
+static inline double dmin(double a, double b) { return a < b ? a : b; }
+static inline double dmax(double a, double b) { return a > b ? a : b; }
+static inline double sqr(double a) { return a * a; }
+
+/* src/FS.hpp:100-128 (note: no absolute value on the convective terms, as in the reference) */
+double fso_adjust_dt(const fso_fs* fs, double cfl_max, double dt_max) {
+  double cx = 0.0, cy = 0.0, vx = 0.0, vy = 0.0, st = 0.0;
+  if (fs->sigma > 0.0) {
+    st = 1.0 / sqrt(((fs->rho_gas + fs->rho_liquid) * pow(fs->dx * fs->dy, 3.0 / 2.0)) /
+                    (4.0 * M_PI * fs->sigma));
+  }
+  for (int64_t i = 0; i < NX; ++i) {
+    for (int64_t j = 0; j < NY; ++j) {
+      cx = dmax(cx, (fs->U[IU(i, j)] + fs->U[IU(i + 1, j)]) / 2 / fs->dx);
+      cy = dmax(cy, (fs->V[IV(i, j)] + fs->V[IV(i, j + 1)]) / 2 / fs->dy);
+      const double rho = (fs->rho_u[IU(i, j)] + fs->rho_u[IU(i + 1, j)] + fs->rho_v[IV(i, j)] +
+                          fs->rho_v[IV(i, j + 1)]) /
+                         4.0;
+      vx = dmax(vx, 4.0 * fs->visc[IC(i, j)] / (sqr(fs->dx) * rho));
+      vy = dmax(vy, 4.0 * fs->visc[IC(i, j)] / (sqr(fs->dy) * rho));
+    }
+  }
+  const double m = dmax(dmax(dmax(cx, cy), dmax(vx, vy)), st);
+  return dmin(cfl_max / m, dt_max);
+}
+
+/* src/FS.hpp:76-97 */
+void fso_save_old_state(fso_fs* fs) {
+  const size_t nu = (size_t)((NX + 3) * (NY + 2)), nv = (size_t)((NX + 2) * (NY + 3));
+  memcpy(fs->rho_u_old, fs->rho_u, nu * sizeof(double));
+  memcpy(fs->rho_v_old, fs->rho_v, nv * sizeof(double));
+  memcpy(fs->U_old, fs->U, nu * sizeof(double));
+  memcpy(fs->V_old, fs->V, nv * sizeof(double));
+}
+
+/* src/Operators.hpp:44-49: all entries incl. ghosts */
+void fso_calc_mid_time(double* cur, const double* old, int64_t n) {
+  for (int64_t k = 0; k < n; ++k) cur[k] = 0.5 * (cur[k] + old[k]);
+}
+
+/* src/FS.hpp:132-150 */
+static inline void hybrid_interp(double eps, double rm, double rp, double vm, double vp, double tm,
+                                 double tp, double* rho, double* vel) {
+  const int upwind = fabs(rp - rm) > eps;
+  if (!upwind) {
+    *rho = (rp + rm) / 2.0;
+    *vel = (vp + vm) / 2.0;
+  } else if (tp + tm >= 0.0) {
+    *rho = rm;
+    *vel = vm;
+  } else {
+    *rho = rp;
+    *vel = vp;
+  }
+}
+
+/* the four flux lambdas of src/FS.hpp:180-254 */
+static double flux_FXU(const fso_fs* fs, double eps, int64_t i, int64_t j) {
+  double rh, uh;
+  hybrid_interp(eps, fs->rho_u_old[IU(i, j)], fs->rho_u_old[IU(i + 1, j)], fs->U[IU(i, j)],
+                fs->U[IU(i + 1, j)], fs->U[IU(i, j)], fs->U[IU(i + 1, j)], &rh, &uh);
+  const double Ui   = (fs->U[IU(i + 1, j)] + fs->U[IU(i, j)]) / 2;
+  const double dUdx = (fs->U[IU(i + 1, j)] - fs->U[IU(i, j)]) / fs->dx;
+  return -rh * uh * Ui + 2.0 * fs->visc[IC(i, j)] * dUdx - fs->p[IC(i, j)];
+}
+static double flux_FYU(const fso_fs* fs, double eps, int64_t i, int64_t j) {
+  double rh, uh;
+  hybrid_interp(eps, fs->rho_u_old[IU(i, j - 1)], fs->rho_u_old[IU(i, j)], fs->U[IU(i, j - 1)],
+                fs->U[IU(i, j)], fs->V[IV(i - 1, j)], fs->V[IV(i, j)], &rh, &uh);
+  const double Vi = (fs->V[IV(i - 1, j)] + fs->V[IV(i, j)]) / 2;
+  const double vc = (fs->visc[IC(i, j)] + fs->visc[IC(i - 1, j)] + fs->visc[IC(i, j - 1)] +
+                     fs->visc[IC(i - 1, j - 1)]) /
+                    4.0;
+  const double dUdy = (fs->U[IU(i, j)] - fs->U[IU(i, j - 1)]) / fs->dy;
+  const double dVdx = (fs->V[IV(i, j)] - fs->V[IV(i - 1, j)]) / fs->dx;
+  return -rh * uh * Vi + vc * (dUdy + dVdx);
+}
+static double flux_FXV(const fso_fs* fs, double eps, int64_t i, int64_t j) {
+  double rh, vh;
+  hybrid_interp(eps, fs->rho_v_old[IV(i - 1, j)], fs->rho_v_old[IV(i, j)], fs->V[IV(i - 1, j)],
+                fs->V[IV(i, j)], fs->U[IU(i, j - 1)], fs->U[IU(i, j)], &rh, &vh);
+  const double Ui = (fs->U[IU(i, j)] + fs->U[IU(i, j - 1)]) / 2;
+  const double vc = (fs->visc[IC(i, j)] + fs->visc[IC(i - 1, j)] + fs->visc[IC(i, j - 1)] +
+                     fs->visc[IC(i - 1, j - 1)]) /
+                    4.0;
+  const double dUdy = (fs->U[IU(i, j)] - fs->U[IU(i, j - 1)]) / fs->dy;
+  const double dVdx = (fs->V[IV(i, j)] - fs->V[IV(i - 1, j)]) / fs->dx;
+  return -rh * Ui * vh + vc * (dUdy + dVdx);
+}
+static double flux_FYV(const fso_fs* fs, double eps, int64_t i, int64_t j) {
+  double rh, vh;
+  hybrid_interp(eps, fs->rho_v_old[IV(i, j)], fs->rho_v_old[IV(i, j + 1)], fs->V[IV(i, j)],
+                fs->V[IV(i, j + 1)], fs->V[IV(i, j)], fs->V[IV(i, j + 1)], &rh, &vh);
+  const double Vi   = (fs->V[IV(i, j)] + fs->V[IV(i, j + 1)]) / 2;
+  const double dVdy = (fs->V[IV(i, j + 1)] - fs->V[IV(i, j)]) / fs->dy;
+  return -rh * vh * Vi + 2.0 * fs->visc[IC(i, j)] * dVdy - fs->p[IC(i, j)];
+}
+
+/* src/FS.hpp:158-315, default build: flux scratch fields, then their divergence */
+void fso_calc_dmomdt(const fso_fs* fs, double* dmomU, double* dmomV) {
+  const double eps = 1e-3 * dmin(fs->rho_gas, fs->rho_liquid); /* FS.hpp:153-155 */
+  const size_t nu = (size_t)((NX + 3) * (NY + 2)), nv = (size_t)((NX + 2) * (NY + 3));
+  /* FXU, FYV: Field2D<NX,NY,1>; FYU, FXV: Field2D<NX+1,NY+1,0> (FS.hpp:163-169) */
+  double* FXU = malloc(sizeof(double) * (size_t)((NX + 2) * (NY + 2)));
+  double* FYV = malloc(sizeof(double) * (size_t)((NX + 2) * (NY + 2)));
+  double* FYU = malloc(sizeof(double) * (size_t)((NX + 1) * (NY + 1)));
+  double* FXV = malloc(sizeof(double) * (size_t)((NX + 1) * (NY + 1)));
+#define ICR(i, j) ((j) + (i) * (NY + 1))
+  memset(dmomU, 0, nu * sizeof(double));
+  memset(dmomV, 0, nv * sizeof(double));
+  for (int64_t i = -1; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j) FXU[IC(i, j)] = flux_FXU(fs, eps, i, j);
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j) FYU[ICR(i, j)] = flux_FYU(fs, eps, i, j);
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j)
+      dmomU[IU(i, j)] = (FXU[IC(i, j)] - FXU[IC(i - 1, j)]) / fs->dx +
+                        (FYU[ICR(i, j + 1)] - FYU[ICR(i, j)]) / fs->dy + fs->p_jump_u[IU(i, j)];
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j) FXV[ICR(i, j)] = flux_FXV(fs, eps, i, j);
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = -1; j < NY + 1; ++j) FYV[IC(i, j)] = flux_FYV(fs, eps, i, j);
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j)
+      dmomV[IV(i, j)] = (FXV[ICR(i + 1, j)] - FXV[ICR(i, j)]) / fs->dx +
+                        (FYV[IC(i, j)] - FYV[IC(i, j - 1)]) / fs->dy + fs->p_jump_v[IV(i, j)];
+#undef ICR
+  free(FXU);
+  free(FYV);
+  free(FYU);
+  free(FXV);
+}
+
+/* src/FS.hpp:423-436 */
+void fso_update_velocity(fso_fs* fs, const double* dmomU, const double* dmomV, double dt) {
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j)
+      fs->U[IU(i, j)] = (fs->rho_u_old[IU(i, j)] * fs->U_old[IU(i, j)] + dt * dmomU[IU(i, j)]) /
+                        fs->rho_u[IU(i, j)];
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j)
+      fs->V[IV(i, j)] = (fs->rho_v_old[IV(i, j)] * fs->V_old[IV(i, j)] + dt * dmomV[IV(i, j)]) /
+                        fs->rho_v[IV(i, j)];
+}
+
+/* ---- boundary conditions: src/BoundaryConditions.hpp:14-224 --------------------------------
+ * Sides are applied in the order left, right, bottom, top (BoundaryConditions.hpp:220-223), each
+ * over the full ghost-inclusive range of the 1-D coordinate it iterates (for_each_a). */
+static void bc_left(fso_fs* fs, const fso_bconds* bc) {
+  const int s = FSO_LEFT;
+  double *U = fs->U, *V = fs->V;
+  switch (bc->kind[s]) {
+    case FSO_BC_DIRICHLET: /* :19-33 */
+      for (int64_t j = -1; j < NY + 1; ++j) {
+        const double ub = bc->u_prof[s] ? bc->u_prof[s][j + 1] : bc->u_val[s];
+        U[IU(-1, j)] = ub;
+        U[IU(0, j)]  = ub;
+      }
+      for (int64_t j = -1; j < NY + 2; ++j) {
+        const double vb = bc->v_prof[s] ? bc->v_prof[s][j + 1] : bc->v_val[s];
+        V[IV(-1, j)] = 2.0 * vb - V[IV(0, j)];
+      }
+      break;
+    case FSO_BC_NEUMANN: /* :93-102 */
+      for (int64_t j = -1; j < NY + 1; ++j)
+        U[IU(-1, j)] = bc->clipped[s] ? dmin(U[IU(0, j)], 0.0) : U[IU(0, j)];
+      for (int64_t j = -1; j < NY + 2; ++j) V[IV(-1, j)] = V[IV(0, j)];
+      break;
+    case FSO_BC_PERIODIC: /* :143-147 */
+      for (int64_t j = -1; j < NY + 1; ++j) U[IU(-1, j)] = U[IU(NX - 1, j)];
+      for (int64_t j = -1; j < NY + 2; ++j) V[IV(-1, j)] = V[IV(NX - 1, j)];
+      break;
+    case FSO_BC_SYMMETRY: /* :170-177 */
+      for (int64_t j = -1; j < NY + 1; ++j) {
+        U[IU(-1, j)] = -U[IU(1, j)];
+        U[IU(0, j)]  = 0.0;
+      }
+      for (int64_t j = -1; j < NY + 2; ++j) V[IV(-1, j)] = V[IV(0, j)];
+      break;
+  }
+}
+static void bc_right(fso_fs* fs, const fso_bconds* bc) {
+  const int s = FSO_RIGHT;
+  double *U = fs->U, *V = fs->V;
+  switch (bc->kind[s]) {
+    case FSO_BC_DIRICHLET: /* :36-51 */
+      for (int64_t j = -1; j < NY + 1; ++j) {
+        const double ub = bc->u_prof[s] ? bc->u_prof[s][j + 1] : bc->u_val[s];
+        U[IU(NX, j)]     = ub;
+        U[IU(NX + 1, j)] = ub;
+      }
+      for (int64_t j = -1; j < NY + 2; ++j) {
+        const double vb = bc->v_prof[s] ? bc->v_prof[s][j + 1] : bc->v_val[s];
+        V[IV(NX, j)] = 2.0 * vb - V[IV(NX - 1, j)];
+      }
+      break;
+    case FSO_BC_NEUMANN: /* :105-114 */
+      for (int64_t j = -1; j < NY + 1; ++j)
+        U[IU(NX + 1, j)] = bc->clipped[s] ? dmax(U[IU(NX, j)], 0.0) : U[IU(NX, j)];
+      for (int64_t j = -1; j < NY + 2; ++j) V[IV(NX, j)] = V[IV(NX - 1, j)];
+      break;
+    case FSO_BC_PERIODIC: /* :150-153 */
+      for (int64_t j = -1; j < NY + 1; ++j) U[IU(NX + 1, j)] = U[IU(1, j)];
+      for (int64_t j = -1; j < NY + 2; ++j) V[IV(NX, j)] = V[IV(0, j)];
+      break;
+    case FSO_BC_SYMMETRY: /* :180-186 */
+      for (int64_t j = -1; j < NY + 1; ++j) {
+        U[IU(NX + 1, j)] = -U[IU(NX - 1, j)];
+        U[IU(NX, j)]     = 0.0;
+      }
+      for (int64_t j = -1; j < NY + 2; ++j) V[IV(NX, j)] = V[IV(NX - 1, j)];
+      break;
+  }
+}
+static void bc_bottom(fso_fs* fs, const fso_bconds* bc) {
+  const int s = FSO_BOTTOM;
+  double *U = fs->U, *V = fs->V;
+  switch (bc->kind[s]) {
+    case FSO_BC_DIRICHLET: /* :54-69 */
+      for (int64_t i = -1; i < NX + 2; ++i) {
+        const double ub = bc->u_prof[s] ? bc->u_prof[s][i + 1] : bc->u_val[s];
+        U[IU(i, -1)] = 2.0 * ub - U[IU(i, 0)];
+      }
+      for (int64_t i = -1; i < NX + 1; ++i) {
+        const double vb = bc->v_prof[s] ? bc->v_prof[s][i + 1] : bc->v_val[s];
+        V[IV(i, -1)] = vb;
+        V[IV(i, 0)]  = vb;
+      }
+      break;
+    case FSO_BC_NEUMANN: /* :117-125 */
+      for (int64_t i = -1; i < NX + 2; ++i) U[IU(i, -1)] = U[IU(i, 0)];
+      for (int64_t i = -1; i < NX + 1; ++i)
+        V[IV(i, -1)] = bc->clipped[s] ? dmin(V[IV(i, 0)], 0.0) : V[IV(i, 0)];
+      break;
+    case FSO_BC_PERIODIC: /* :156-159 */
+      for (int64_t i = -1; i < NX + 2; ++i) U[IU(i, -1)] = U[IU(i, NY - 1)];
+      for (int64_t i = -1; i < NX + 1; ++i) V[IV(i, -1)] = V[IV(i, NY - 1)];
+      break;
+    case FSO_BC_SYMMETRY: /* :189-195 */
+      for (int64_t i = -1; i < NX + 2; ++i) U[IU(i, -1)] = U[IU(i, 0)];
+      for (int64_t i = -1; i < NX + 1; ++i) {
+        V[IV(i, -1)] = -V[IV(i, 1)];
+        V[IV(i, 0)]  = 0.0;
+      }
+      break;
+  }
+}
+static void bc_top(fso_fs* fs, const fso_bconds* bc) {
+  const int s = FSO_TOP;
+  double *U = fs->U, *V = fs->V;
+  switch (bc->kind[s]) {
+    case FSO_BC_DIRICHLET: /* :72-87 */
+      for (int64_t i = -1; i < NX + 2; ++i) {
+        const double ub = bc->u_prof[s] ? bc->u_prof[s][i + 1] : bc->u_val[s];
+        U[IU(i, NY)] = 2.0 * ub - U[IU(i, NY - 1)];
+      }
+      for (int64_t i = -1; i < NX + 1; ++i) {
+        const double vb = bc->v_prof[s] ? bc->v_prof[s][i + 1] : bc->v_val[s];
+        V[IV(i, NY)]     = vb;
+        V[IV(i, NY + 1)] = vb;
+      }
+      break;
+    case FSO_BC_NEUMANN: /* :128-137 */
+      for (int64_t i = -1; i < NX + 2; ++i) U[IU(i, NY)] = U[IU(i, NY - 1)];
+      for (int64_t i = -1; i < NX + 1; ++i)
+        V[IV(i, NY + 1)] = bc->clipped[s] ? dmax(V[IV(i, NY)], 0.0) : V[IV(i, NY)];
+      break;
+    case FSO_BC_PERIODIC: /* :162-165 */
+      for (int64_t i = -1; i < NX + 2; ++i) U[IU(i, NY)] = U[IU(i, 0)];
+      for (int64_t i = -1; i < NX + 1; ++i) V[IV(i, NY + 1)] = V[IV(i, 1)];
+      break;
+    case FSO_BC_SYMMETRY: /* :198-205 */
+      for (int64_t i = -1; i < NX + 2; ++i) U[IU(i, NY)] = U[IU(i, NY - 1)];
+      for (int64_t i = -1; i < NX + 1; ++i) {
+        V[IV(i, NY + 1)] = -V[IV(i, NY - 1)];
+        V[IV(i, NY)]     = 0.0;
+      }
+      break;
+  }
+}
+void fso_apply_velocity_bconds(fso_fs* fs, const fso_bconds* bc) {
+  bc_left(fs, bc);
+  bc_right(fs, bc);
+  bc_bottom(fs, bc);
+  bc_top(fs, bc);
+}
+
+/* test/LaminarChannel.cpp:55-66 (sums over j = -1..NY in order) and :201-205 */
+double fso_outflow_fix(fso_fs* fs) {
+  double inflow = 0, outflow = 0;
+  for (int64_t j = -1; j < NY + 1; ++j) {
+    inflow += fs->rho_u[IU(-1, j)] * fs->U[IU(-1, j)];
+    outflow += fs->rho_u[IU(NX + 1, j)] * fs->U[IU(NX + 1, j)];
+  }
+  const double mass_error = outflow - inflow;
+  for (int64_t j = -1; j < NY + 1; ++j)
+    fs->U[IU(NX + 1, j)] -= mass_error / (fs->rho_u[IU(NX + 1, j)] * (double)(NY + 2));
+  return mass_error;
+}
+
+/* src/Operators.hpp:32-41: all cells incl. ghosts */
+void fso_calc_divergence(const fso_fs* fs, double* div) {
+  for (int64_t i = -1; i < NX + 1; ++i)
+    for (int64_t j = -1; j < NY + 1; ++j)
+      div[IC(i, j)] = (fs->U[IU(i + 1, j)] - fs->U[IU(i, j)]) / fs->dx +
+                      (fs->V[IV(i, j + 1)] - fs->V[IV(i, j)]) / fs->dy;
+}
+
+/* src/LinearSystem.hpp:32-122.  op[IF(i,j)*5 + {C,W,E,S,N}], Layout::F. */
+void fso_fill_pressure_operator(const fso_fs* fs, int psd, double* op) {
+  const double vol = fs->dx * fs->dy;
+  const double* ru = fs->rho_u;
+  const double* rv = fs->rho_v;
+  for (int64_t i = -1; i < NX + 1; ++i) {
+    for (int64_t j = -1; j < NY + 1; ++j) {
+      double* s = op + 5 * IF(i, j);
+      s[0] = s[1] = s[2] = s[3] = s[4] = 0.0;
+      if (i == -1) { /* :41-45 */
+        s[0] += -vol * -1.0 / (sqr(fs->dx) * ru[IU(i + 1, j)]);
+        s[1] += 0.0;
+        s[2] += -vol * 1.0 / (sqr(fs->dx) * ru[IU(i + 1, j)]);
+      } else if (i == NX) { /* :46-50 */
+        s[0] += -vol * -1.0 / (sqr(fs->dx) * ru[IU(i, j)]);
+        s[1] += -vol * 1.0 / (sqr(fs->dx) * ru[IU(i, j)]);
+        s[2] += 0.0;
+      } else { /* :51-57 */
+        s[0] += -vol * (-1.0 / (sqr(fs->dx) * ru[IU(i, j)]) + -1.0 / (sqr(fs->dx) * ru[IU(i + 1, j)]));
+        s[1] += -vol * 1.0 / (sqr(fs->dx) * ru[IU(i, j)]);
+        s[2] += -vol * 1.0 / (sqr(fs->dx) * ru[IU(i + 1, j)]);
+      }
+      if (j == -1) { /* :60-64 */
+        s[0] += -vol * -1.0 / (sqr(fs->dy) * rv[IV(i, j + 1)]);
+        s[3] += 0.0;
+        s[4] += -vol * 1.0 / (sqr(fs->dy) * rv[IV(i, j + 1)]);
+      } else if (j == NY) { /* :65-69 */
+        s[0] += -vol * -1.0 / (sqr(fs->dy) * rv[IV(i, j)]);
+        s[3] += -vol * 1.0 / (sqr(fs->dy) * rv[IV(i, j)]);
+        s[4] += 0.0;
+      } else { /* :70-76 */
+        s[0] += -vol * (-1.0 / (sqr(fs->dy) * rv[IV(i, j)]) + -1.0 / (sqr(fs->dy) * rv[IV(i, j + 1)]));
+        s[3] += -vol * 1.0 / (sqr(fs->dy) * rv[IV(i, j)]);
+        s[4] += -vol * 1.0 / (sqr(fs->dy) * rv[IV(i, j + 1)]);
+      }
+    }
+  }
+  /* identity row on one side, :79-121 */
+#define IDROW(i, j)                  \
+  do {                               \
+    double* s = op + 5 * IF(i, j);   \
+    s[0] = 1.0;                      \
+    s[1] = s[2] = s[3] = s[4] = 0.0; \
+  } while (0)
+  if (psd == FSO_PSD_LEFT)
+    for (int64_t j = -1; j < NY + 1; ++j) IDROW(-1, j);
+  if (psd == FSO_PSD_RIGHT)
+    for (int64_t j = -1; j < NY + 1; ++j) IDROW(NX, j);
+  if (psd == FSO_PSD_BOTTOM)
+    for (int64_t i = -1; i < NX + 1; ++i) IDROW(i, -1);
+  if (psd == FSO_PSD_TOP)
+    for (int64_t i = -1; i < NX + 1; ++i) IDROW(i, NY);
+#undef IDROW
+}
+
+/* src/LinearSystem.hpp:125-155.  rhs in Layout::F; the mean is std::reduce over the array in
+ * storage order (serial left fold), :147-149. */
+void fso_fill_pressure_rhs(const fso_fs* fs, const double* div, double dt, int psd, double* rhs) {
+  const double vol = fs->dx * fs->dy;
+  for (int64_t i = -1; i < NX + 1; ++i)
+    for (int64_t j = -1; j < NY + 1; ++j) rhs[IF(i, j)] = -vol * div[IC(i, j)] / dt;
+  if (psd == FSO_PSD_LEFT)
+    for (int64_t j = -1; j < NY + 1; ++j) rhs[IF(-1, j)] = 0.0;
+  else if (psd == FSO_PSD_RIGHT)
+    for (int64_t j = -1; j < NY + 1; ++j) rhs[IF(NX, j)] = 0.0;
+  else if (psd == FSO_PSD_BOTTOM)
+    for (int64_t i = -1; i < NX + 1; ++i) rhs[IF(i, -1)] = 0.0;
+  else if (psd == FSO_PSD_TOP)
+    for (int64_t i = -1; i < NX + 1; ++i) rhs[IF(i, NY)] = 0.0;
+  else {
+    const int64_t n = (NX + 2) * (NY + 2);
+    double sum = 0.0;
+    for (int64_t k = 0; k < n; ++k) sum += rhs[k];
+    const double mean = sum / (double)n;
+    for (int64_t k = 0; k < n; ++k) rhs[k] -= mean;
+  }
+}
+
+/* src/Operators.hpp:78-82 with integrate<true> :52-62 (row-major serial sum, then * dx * dy) */
+void fso_shift_pressure_to_zero(const fso_fs* fs, double* dp) {
+  const int64_t n = (NX + 2) * (NY + 2);
+  double integral = 0.0;
+  for (int64_t k = 0; k < n; ++k) integral += dp[k];
+  const double c = integral * fs->dx * fs->dy;
+  for (int64_t k = 0; k < n; ++k) dp[k] -= c;
+}
+
+/* p += dp on all cells; U,V corrected on interior faces with the variable-density form
+ * test/LaminarChannel.cpp:222-233 (== scaling/LidDrivenFlow.cpp:153-160 for constant rho) */
+void fso_correct(fso_fs* fs, const double* dp, double dt) {
+  const int64_t n = (NX + 2) * (NY + 2);
+  for (int64_t k = 0; k < n; ++k) fs->p[k] += dp[k];
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j)
+      fs->U[IU(i, j)] -= (dp[IC(i, j)] - dp[IC(i - 1, j)]) / fs->dx * dt / fs->rho_u[IU(i, j)];
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j)
+      fs->V[IV(i, j)] -= (dp[IC(i, j)] - dp[IC(i, j - 1)]) / fs->dy * dt / fs->rho_v[IV(i, j)];
+}
+
+/* src/Utility.hpp:80-88 (over the whole array incl. ghosts) */
+double fso_abs_max(const double* a, int64_t n) {
+  double m = 0.0;
+  for (int64_t k = 0; k < n; ++k) m = dmax(m, fabs(a[k]));
+  return m;
+}
+
+/* src/BoundaryConditions.hpp:227-252 for an (m+2) x (n+2) field */
+void fso_apply_neumann_bconds(double* f, int64_t m, int64_t n) {
+#define F(i, j) f[(j) + 1 + ((i) + 1) * (n + 2)]
+  for (int64_t j = -1; j < n + 1; ++j) {
+    F(-1, j) = F(0, j);
+    F(m, j)  = F(m - 1, j);
+  }
+  for (int64_t i = -1; i < m + 1; ++i) {
+    F(i, -1) = F(i, 0);
+    F(i, n)  = F(i, n - 1);
+  }
+#undef F
+}
+
+/* src/FS.hpp:569-589 */
+void fso_calc_rho_visc_const(fso_fs* fs) {
+  const int64_t nu = (NX + 3) * (NY + 2), nv = (NX + 2) * (NY + 3), nc = (NX + 2) * (NY + 2);
+  for (int64_t k = 0; k < nu; ++k) fs->rho_u[k] = fs->rho_u_old[k] = fs->rho_gas;
+  for (int64_t k = 0; k < nv; ++k) fs->rho_v[k] = fs->rho_v_old[k] = fs->rho_gas;
+  for (int64_t k = 0; k < nc; ++k) fs->visc[k] = fs->visc_gas;
+}
+
+/* src/FS.hpp:592-650 (harmonic viscosity; VF_LOW/VF_HIGH from src/IR.hpp:16-17) */
+void fso_calc_rho_visc_vof(fso_fs* fs, const double* vf) {
+  const double VF_LOW = 1e-8, VF_HIGH = 1.0 - 1e-8;
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j) {
+      const double rm = vf[IC(i - 1, j)] * fs->rho_liquid + (1.0 - vf[IC(i - 1, j)]) * fs->rho_gas;
+      const double rp = vf[IC(i, j)] * fs->rho_liquid + (1.0 - vf[IC(i, j)]) * fs->rho_gas;
+      fs->rho_u[IU(i, j)] = (rm + rp) / 2.0;
+    }
+  fso_apply_neumann_bconds(fs->rho_u, NX + 1, NY);
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j) {
+      const double rm = vf[IC(i, j - 1)] * fs->rho_liquid + (1.0 - vf[IC(i, j - 1)]) * fs->rho_gas;
+      const double rp = vf[IC(i, j)] * fs->rho_liquid + (1.0 - vf[IC(i, j)]) * fs->rho_gas;
+      fs->rho_v[IV(i, j)] = (rm + rp) / 2.0;
+    }
+  fso_apply_neumann_bconds(fs->rho_v, NX, NY + 1);
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY; ++j) {
+      const double f = vf[IC(i, j)];
+      if (f < VF_LOW) fs->visc[IC(i, j)] = fs->visc_gas;
+      else if (f > VF_HIGH) fs->visc[IC(i, j)] = fs->visc_liquid;
+      else
+        fs->visc[IC(i, j)] =
+            (fs->visc_liquid * fs->visc_gas) / (fs->visc_liquid * (1.0 - f) + fs->visc_gas * f);
+    }
+  fso_apply_neumann_bconds(fs->visc, NX, NY);
+}
+
+/* src/FS.hpp:439-466 */
+void fso_calc_pressure_jump(fso_fs* fs, const double* vf, const double* curv, const double* ilen) {
+  memset(fs->p_jump_u, 0, sizeof(double) * (size_t)((NX + 3) * (NY + 2)));
+  memset(fs->p_jump_v, 0, sizeof(double) * (size_t)((NX + 2) * (NY + 3)));
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j) {
+      const double ml = ilen[IC(i - 1, j)], pl = ilen[IC(i, j)];
+      const double c =
+          (pl + ml) > 0.0 ? (curv[IC(i, j)] * pl + curv[IC(i - 1, j)] * ml) / (pl + ml) : 0.0;
+      fs->p_jump_u[IU(i, j)] = fs->sigma * c * (vf[IC(i, j)] - vf[IC(i - 1, j)]) / fs->dx;
+    }
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j) {
+      const double ml = ilen[IC(i, j - 1)], pl = ilen[IC(i, j)];
+      const double c =
+          (pl + ml) > 0.0 ? (curv[IC(i, j)] * pl + curv[IC(i, j - 1)] * ml) / (pl + ml) : 0.0;
+      fs->p_jump_v[IV(i, j)] = fs->sigma * c * (vf[IC(i, j)] - vf[IC(i, j - 1)]) / fs->dy;
+    }
+}
+
+/* src/Operators.hpp:10-19: all cells incl. ghosts */
+void fso_interpolate_UV(const fso_fs* fs, double* Ui, double* Vi) {
+  for (int64_t i = -1; i < NX + 1; ++i)
+    for (int64_t j = -1; j < NY + 1; ++j) {
+      Ui[IC(i, j)] = (fs->U[IU(i, j)] + fs->U[IU(i + 1, j)]) / 2;
+      Vi[IC(i, j)] = (fs->V[IV(i, j)] + fs->V[IV(i, j + 1)]) / 2;
+    }
+}
+
+/* src/FS.hpp:653-676 */
+void fso_conserved(const fso_fs* fs, double* mass, double* mom_x, double* mom_y) {
+  double m = 0, mx = 0, my = 0;
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY; ++j) {
+      m += (fs->rho_u[IU(i, j)] + fs->rho_u[IU(i + 1, j)] + fs->rho_v[IV(i, j)] +
+            fs->rho_v[IV(i, j + 1)]) /
+           4.0 * fs->dx * fs->dy;
+      mx += (fs->rho_u[IU(i, j)] * fs->U[IU(i, j)] + fs->rho_u[IU(i + 1, j)] * fs->U[IU(i + 1, j)]) /
+            2.0 * fs->dx * fs->dy;
+      my += (fs->rho_v[IV(i, j)] * fs->V[IV(i, j)] + fs->rho_v[IV(i, j + 1)] * fs->V[IV(i, j + 1)]) /
+            2.0 * fs->dx * fs->dy;
+    }
+  *mass = m;
+  *mom_x = mx;
+  *mom_y = my;
+}
+
+/* src/FS.hpp:318-406: mass fluxes with the same hybrid density selection (velocity slots 0) */
+static inline double rho_hybrid(double eps, double rm, double rp, double tm, double tp) {
+  double r, v;
+  hybrid_interp(eps, rm, rp, 0.0, 0.0, tm, tp, &r, &v);
+  return r;
+}
+void fso_calc_drhodt(const fso_fs* fs, double* drho_u, double* drho_v) {
+  const double eps = 1e-3 * dmin(fs->rho_gas, fs->rho_liquid);
+  const size_t nu = (size_t)((NX + 3) * (NY + 2)), nv = (size_t)((NX + 2) * (NY + 3));
+  double* FXU = malloc(sizeof(double) * (size_t)((NX + 2) * (NY + 2)));
+  double* FYV = malloc(sizeof(double) * (size_t)((NX + 2) * (NY + 2)));
+  double* FYU = malloc(sizeof(double) * (size_t)((NX + 1) * (NY + 1)));
+  double* FXV = malloc(sizeof(double) * (size_t)((NX + 1) * (NY + 1)));
+#define ICR(i, j) ((j) + (i) * (NY + 1))
+  memset(drho_u, 0, nu * sizeof(double));
+  memset(drho_v, 0, nv * sizeof(double));
+  const double *U = fs->U, *V = fs->V, *ru = fs->rho_u_old, *rv = fs->rho_v_old;
+  for (int64_t i = -1; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j) { /* :340-351 */
+      const double r = rho_hybrid(eps, ru[IU(i, j)], ru[IU(i + 1, j)], U[IU(i, j)], U[IU(i + 1, j)]);
+      FXU[IC(i, j)] = -r * ((U[IU(i, j)] + U[IU(i + 1, j)]) / 2.0);
+    }
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j) { /* :355-366 */
+      const double r = rho_hybrid(eps, ru[IU(i, j - 1)], ru[IU(i, j)], V[IV(i - 1, j)], V[IV(i, j)]);
+      FYU[ICR(i, j)] = -r * ((V[IV(i - 1, j)] + V[IV(i, j)]) / 2);
+    }
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j)
+      drho_u[IU(i, j)] = (FXU[IC(i, j)] - FXU[IC(i - 1, j)]) / fs->dx +
+                         (FYU[ICR(i, j + 1)] - FYU[ICR(i, j)]) / fs->dy;
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j) { /* :377-388 */
+      const double r = rho_hybrid(eps, rv[IV(i - 1, j)], rv[IV(i, j)], U[IU(i, j - 1)], U[IU(i, j)]);
+      FXV[ICR(i, j)] = -r * ((U[IU(i, j - 1)] + U[IU(i, j)]) / 2.0);
+    }
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = -1; j < NY + 1; ++j) { /* :392-403 */
+      const double r = rho_hybrid(eps, rv[IV(i, j)], rv[IV(i, j + 1)], V[IV(i, j)], V[IV(i, j + 1)]);
+      FYV[IC(i, j)] = -r * ((V[IV(i, j)] + V[IV(i, j + 1)]) / 2.0);
+    }
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j)
+      drho_v[IV(i, j)] = (FXV[ICR(i + 1, j)] - FXV[ICR(i, j)]) / fs->dx +
+                         (FYV[IC(i, j)] - FYV[IC(i, j - 1)]) / fs->dy;
+#undef ICR
+  free(FXU);
+  free(FYV);
+  free(FYU);
+  free(FXV);
+}
+
+/* src/FS.hpp:409-420 */
+void fso_update_density(fso_fs* fs, const double* drho_u, const double* drho_v, double dt) {
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j)
+      fs->rho_u[IU(i, j)] = fs->rho_u_old[IU(i, j)] + dt * drho_u[IU(i, j)];
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j)
+      fs->rho_v[IV(i, j)] = fs->rho_v_old[IV(i, j)] + dt * drho_v[IV(i, j)];
+}
+
+/* One timestep's sub-iteration loop, scaling/LidDrivenFlow.cpp:127-161
+ * (+ test/LaminarChannel.cpp:201-205 outflow fix, + operator rebuild of two-phase drivers). */
+int fso_step(fso_fs* fs, const fso_bconds* bc, fso_solver* s, const fso_step_opts* o, double dt,
+             double* res) {
+  const int64_t nu = (NX + 3) * (NY + 2), nv = (NX + 2) * (NY + 3), nc = (NX + 2) * (NY + 2);
+  double* dmomU = malloc(sizeof(double) * (size_t)nu);
+  double* dmomV = malloc(sizeof(double) * (size_t)nv);
+  double* div   = malloc(sizeof(double) * (size_t)nc);
+  double* rhs   = malloc(sizeof(double) * (size_t)nc);
+  double* dp    = malloc(sizeof(double) * (size_t)nc);
+  double* op    = o->rebuild_operator_each_subiter ? malloc(sizeof(double) * 5 * (size_t)nc) : NULL;
+  int iters = 0;
+  fso_save_old_state(fs);
+  for (int sub = 0; sub < o->num_subiter; ++sub) {
+    fso_calc_mid_time(fs->U, fs->U_old, nu);
+    fso_calc_mid_time(fs->V, fs->V_old, nv);
+    fso_calc_dmomdt(fs, dmomU, dmomV);
+    fso_update_velocity(fs, dmomU, dmomV, dt);
+    fso_apply_velocity_bconds(fs, bc);
+    if (o->outflow_fix) fso_outflow_fix(fs);
+    fso_calc_divergence(fs, div);
+    if (op) {
+      fso_fill_pressure_operator(fs, o->psd, op);
+      fso_solver_set_operator(s, op);
+    }
+    fso_fill_pressure_rhs(fs, div, dt, o->psd, rhs);
+    iters += fso_solver_solve(s, rhs, dp, res);
+    fso_shift_pressure_to_zero(fs, dp);
+    fso_correct(fs, dp, dt);
+  }
+  free(dmomU);
+  free(dmomV);
+  free(div);
+  free(rhs);
+  free(dp);
+  free(op);
+  return iters;
+}

@@ -1,0 +1,296 @@
+// oracle/ref_harness.cpp -- TEST INFRASTRUCTURE ONLY.
+//
+// extern "C" wrapper around the UNMODIFIED reference (headers under /root/reference/src and the
+// vendored HYPRE 3.0.0), compiled by oracle/Makefile into oracle/_ref/libfsref.so.  No reference
+// source is copied: this file only #includes the reference headers where they lie and calls their
+// public functions.  The reference fixes grid sizes at compile time (template parameters), so the
+// sizes in ref_harness_sizes.inc are instantiated and dispatched on at run time.
+//
+// Used by: tests/ (to pin oracle/fs_oracle.c and to generate tests/golden/), bench.py's
+// cpu_baseline leg and `bench.py --impl reference`.  Never by the product path.
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+
+#include <omp.h>
+
+#include "FS.hpp"
+#include "LinearSolver_StructHypre.hpp"
+#include "Operators.hpp"
+#include "Utility.hpp"
+
+#include "fs_oracle.h"
+
+namespace {
+
+using Float = double;
+
+struct SessionBase {
+  virtual ~SessionBase()                                                       = default;
+  virtual void load(const fso_fs* in)                                          = 0;
+  virtual void store(fso_fs* out) const                                        = 0;
+  virtual void set_bconds(const fso_bconds* bc)                                = 0;
+  virtual double adjust_dt(double cfl, double dt_max)                          = 0;
+  virtual void save_old_state()                                                = 0;
+  virtual void calc_mid_time()                                                 = 0;
+  virtual void calc_dmomdt(double* dU, double* dV)                             = 0;
+  virtual void update_velocity(const double* dU, const double* dV, double dt)  = 0;
+  virtual void apply_bconds()                                                  = 0;
+  virtual void calc_divergence(double* div)                                    = 0;
+  virtual void fill_operator(int psd, double* op)                              = 0;
+  virtual void fill_rhs(const double* div, double dt, int psd, double* rhs)    = 0;
+  virtual void shift_pressure(double* dp)                                      = 0;
+  virtual void calc_drhodt(double* dru, double* drv)                           = 0;
+  virtual void rho_visc_vof(const double* vf)                                  = 0;
+  virtual void solver_create(double tol, int max_iter, int psd)                = 0;
+  virtual void solver_set_operator()                                           = 0;
+  virtual int solver_solve(const double* div, double dt, double* dp, double* res) = 0;
+  virtual int step(const fso_step_opts* o, double dt, double* res, double* phase_secs) = 0;
+  virtual void diagnostics(double* umax, double* vmax, double* divmax)         = 0;
+};
+
+template <Index NX, Index NY>
+struct Session final : SessionBase {
+  static constexpr Index G = 1;
+  FS<Float, NX, NY, G> fs{};
+  Field2D<Float, NX + 1, NY, G> dU{};
+  Field2D<Float, NX, NY + 1, G> dV{};
+  Field2D<Float, NX, NY, G> div{};
+  Field2D<Float, NX, NY, G> dp{};
+  FlowBConds<Float> bconds{Neumann{}, Neumann{}, Neumann{}, Neumann{}};
+  std::unique_ptr<LinearSolver_StructHypre<Float, NX, NY, G>> ps{};
+  int psd_ = 0;
+
+  template <typename F>
+  static void cp_in(F& f, const double* src) {
+    if (src) std::memcpy(f.get_data(), src, sizeof(double) * static_cast<size_t>(f.size()));
+  }
+  template <typename F>
+  static void cp_out(const F& f, double* dst) {
+    if (dst) std::memcpy(dst, f.get_data(), sizeof(double) * static_cast<size_t>(f.size()));
+  }
+
+  void load(const fso_fs* in) override {
+    fs.visc_gas = in->visc_gas; fs.visc_liquid = in->visc_liquid;
+    fs.rho_gas = in->rho_gas; fs.rho_liquid = in->rho_liquid; fs.sigma = in->sigma;
+    // init_grid (src/FS.hpp:55-73) on [0, nx*dx] x [0, ny*dy]
+    init_grid(0.0, in->dx * static_cast<Float>(NX), NX, 0.0, in->dy * static_cast<Float>(NY), NY, fs);
+    fs.dx = in->dx; fs.dy = in->dy;
+    cp_in(fs.visc, in->visc); cp_in(fs.p, in->p);
+    cp_in(fs.p_jump_u_stag, in->p_jump_u); cp_in(fs.p_jump_v_stag, in->p_jump_v);
+    cp_in(fs.old.rho_u_stag, in->rho_u_old); cp_in(fs.old.rho_v_stag, in->rho_v_old);
+    cp_in(fs.old.U, in->U_old); cp_in(fs.old.V, in->V_old);
+    cp_in(fs.curr.rho_u_stag, in->rho_u); cp_in(fs.curr.rho_v_stag, in->rho_v);
+    cp_in(fs.curr.U, in->U); cp_in(fs.curr.V, in->V);
+  }
+  void store(fso_fs* out) const override {
+    cp_out(fs.visc, out->visc); cp_out(fs.p, out->p);
+    cp_out(fs.p_jump_u_stag, out->p_jump_u); cp_out(fs.p_jump_v_stag, out->p_jump_v);
+    cp_out(fs.old.rho_u_stag, out->rho_u_old); cp_out(fs.old.rho_v_stag, out->rho_v_old);
+    cp_out(fs.old.U, out->U_old); cp_out(fs.old.V, out->V_old);
+    cp_out(fs.curr.rho_u_stag, out->rho_u); cp_out(fs.curr.rho_v_stag, out->rho_v);
+    cp_out(fs.curr.U, out->U); cp_out(fs.curr.V, out->V);
+  }
+  static BCond_t<Float> make_bc(const fso_bconds* bc, int s) {
+    switch (bc->kind[s]) {
+      case FSO_BC_DIRICHLET: return Dirichlet<Float>{.U = bc->u_val[s], .V = bc->v_val[s]};
+      case FSO_BC_NEUMANN:   return Neumann{.clipped = bc->clipped[s] != 0};
+      case FSO_BC_PERIODIC:  return Periodic{};
+      default:               return Symmetry{};
+    }
+  }
+  void set_bconds(const fso_bconds* bc) override {
+    bconds = FlowBConds<Float>{make_bc(bc, 0), make_bc(bc, 1), make_bc(bc, 2), make_bc(bc, 3)};
+  }
+  double adjust_dt(double cfl, double dt_max) override { return ::adjust_dt(fs, cfl, dt_max); }
+  void save_old_state() override { ::save_old_state(fs.curr, fs.old); }
+  void calc_mid_time() override {
+    ::calc_mid_time(fs.curr.U, fs.old.U);
+    ::calc_mid_time(fs.curr.V, fs.old.V);
+  }
+  void calc_dmomdt(double* oU, double* oV) override {
+    ::calc_dmomdt(fs, dU, dV);
+    cp_out(dU, oU); cp_out(dV, oV);
+  }
+  void update_velocity(const double* iU, const double* iV, double dt) override {
+    cp_in(dU, iU); cp_in(dV, iV);
+    ::update_velocity(dU, dV, dt, fs);
+  }
+  void apply_bconds() override { ::apply_velocity_bconds(fs, bconds, 0.0); }
+  void calc_divergence(double* o) override {
+    ::calc_divergence(fs.curr.U, fs.curr.V, fs.dx, fs.dy, div);
+    cp_out(div, o);
+  }
+  void fill_operator(int psd, double* op) override {
+    auto ls = std::make_unique<LinearSystem<Float, NX, NY, G, Layout::F>>();
+    ls->fill_pressure_operator(fs, static_cast<PSDirichlet>(psd));
+    std::memcpy(op, ls->op.get_data()->data(), sizeof(double) * 5 * static_cast<size_t>(ls->op.size()));
+  }
+  void fill_rhs(const double* idiv, double dt, int psd, double* rhs) override {
+    auto ls = std::make_unique<LinearSystem<Float, NX, NY, G, Layout::F>>();
+    cp_in(div, idiv);
+    ls->fill_pressure_rhs(fs, div, dt, static_cast<PSDirichlet>(psd));
+    std::memcpy(rhs, ls->rhs.get_data(), sizeof(double) * static_cast<size_t>(ls->rhs.size()));
+  }
+  void shift_pressure(double* io) override {
+    cp_in(dp, io);
+    ::shift_pressure_to_zero(fs.dx, fs.dy, dp);
+    cp_out(dp, io);
+  }
+  void calc_drhodt(double* oU, double* oV) override {
+    ::calc_drhodt(fs, dU, dV);
+    cp_out(dU, oU); cp_out(dV, oV);
+  }
+  void rho_visc_vof(const double* vf) override {
+    auto f = std::make_unique<Field2D<Float, NX, NY, G>>();
+    cp_in(*f, vf);
+    ::calc_rho(*f, fs);
+    ::calc_visc(*f, fs);
+  }
+  void solver_create(double tol, int max_iter, int psd) override {
+    psd_ = psd;
+    ps.reset();
+    ps = std::make_unique<LinearSolver_StructHypre<Float, NX, NY, G>>(
+        tol, max_iter, HypreSolver::PCG, HyprePrecond::PFMG, static_cast<PSDirichlet>(psd));
+  }
+  void solver_set_operator() override { ps->set_pressure_operator(fs); }
+  int solver_solve(const double* idiv, double dt, double* odp, double* res) override {
+    cp_in(div, idiv);
+    Index it = 0;
+    Float r  = 0;
+    ps->set_pressure_rhs(fs, div, dt);
+    ps->solve(dp, &r, &it);
+    cp_out(dp, odp);
+    if (res) *res = r;
+    return static_cast<int>(it);
+  }
+  // The sub-iteration loop of scaling/LidDrivenFlow.cpp:124-161 with the variable-density
+  // correction of test/LaminarChannel.cpp:222-233 and its outflow fix (:201-205).
+  // phase_secs (optional, 4 entries): momentum(mid-time+dmomdt+update+bc), div+rhs, solve, correct.
+  int step(const fso_step_opts* o, double dt, double* res, double* phase) override {
+    using clk = std::chrono::steady_clock;
+    auto secs = [](clk::time_point a, clk::time_point b) {
+      return std::chrono::duration<double>(b - a).count();
+    };
+    ::save_old_state(fs.curr, fs.old);
+    int iters = 0;
+    Float r   = 0;
+    for (int sub = 0; sub < o->num_subiter; ++sub) {
+      auto t0 = clk::now();
+      ::calc_mid_time(fs.curr.U, fs.old.U);
+      ::calc_mid_time(fs.curr.V, fs.old.V);
+      ::calc_dmomdt(fs, dU, dV);
+      for_each_i<Exec::Parallel>(fs.curr.U, [&](Index i, Index j) {
+        fs.curr.U(i, j) =
+            (fs.old.rho_u_stag(i, j) * fs.old.U(i, j) + dt * dU(i, j)) / fs.curr.rho_u_stag(i, j);
+      });
+      for_each_i<Exec::Parallel>(fs.curr.V, [&](Index i, Index j) {
+        fs.curr.V(i, j) =
+            (fs.old.rho_v_stag(i, j) * fs.old.V(i, j) + dt * dV(i, j)) / fs.curr.rho_v_stag(i, j);
+      });
+      ::apply_velocity_bconds(fs, bconds, 0.0);
+      if (o->outflow_fix) {
+        Float inflow = 0, outflow = 0;
+        for_each_a(fs.ym, [&](Index j) {
+          inflow  += fs.curr.rho_u_stag(-G, j) * fs.curr.U(-G, j);
+          outflow += fs.curr.rho_u_stag(NX + G, j) * fs.curr.U(NX + G, j);
+        });
+        const Float mass_error = outflow - inflow;
+        for_each_a<Exec::Parallel>(fs.ym, [&](Index j) {
+          fs.curr.U(NX + G, j) -=
+              mass_error / (fs.curr.rho_u_stag(NX + G, j) * static_cast<Float>(NY + 2 * G));
+        });
+      }
+      auto t1 = clk::now();
+      ::calc_divergence(fs.curr.U, fs.curr.V, fs.dx, fs.dy, div);
+      if (o->rebuild_operator_each_subiter) ps->set_pressure_operator(fs);
+      ps->set_pressure_rhs(fs, div, dt);
+      auto t2 = clk::now();
+      Index it = 0;
+      ps->solve(dp, &r, &it);
+      iters += static_cast<int>(it);
+      auto t3 = clk::now();
+      ::shift_pressure_to_zero(fs.dx, fs.dy, dp);
+      for_each_a<Exec::Parallel>(fs.p, [&](Index i, Index j) { fs.p(i, j) += dp(i, j); });
+      for_each_i<Exec::Parallel>(fs.curr.U, [&](Index i, Index j) {
+        fs.curr.U(i, j) -= (dp(i, j) - dp(i - 1, j)) / fs.dx * dt / fs.curr.rho_u_stag(i, j);
+      });
+      for_each_i<Exec::Parallel>(fs.curr.V, [&](Index i, Index j) {
+        fs.curr.V(i, j) -= (dp(i, j) - dp(i, j - 1)) / fs.dy * dt / fs.curr.rho_v_stag(i, j);
+      });
+      auto t4 = clk::now();
+      if (phase) {
+        phase[0] += secs(t0, t1); phase[1] += secs(t1, t2);
+        phase[2] += secs(t2, t3); phase[3] += secs(t3, t4);
+      }
+    }
+    if (res) *res = r;
+    return iters;
+  }
+  void diagnostics(double* umax, double* vmax, double* divmax) override {
+    ::calc_divergence(fs.curr.U, fs.curr.V, fs.dx, fs.dy, div);
+    *umax = abs_max(fs.curr.U); *vmax = abs_max(fs.curr.V); *divmax = abs_max(div);
+  }
+};
+
+SessionBase* make_session(int64_t nx, int64_t ny) {
+#define X(A, B) \
+  if (nx == (A) && ny == (B)) return new Session<(A), (B)>();
+#include "ref_harness_sizes.inc"
+#undef X
+  return nullptr;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fsref_supported(int64_t nx, int64_t ny) {
+#define X(A, B) \
+  if (nx == (A) && ny == (B)) return 1;
+#include "ref_harness_sizes.inc"
+#undef X
+  return 0;
+}
+void fsref_set_threads(int n) { omp_set_num_threads(n); }
+int fsref_max_threads(void) { return omp_get_max_threads(); }
+
+void* fsref_create(int64_t nx, int64_t ny) { return make_session(nx, ny); }
+void fsref_destroy(void* s) { delete static_cast<SessionBase*>(s); }
+#define S static_cast<SessionBase*>(s)
+void fsref_load(void* s, const fso_fs* in) { S->load(in); }
+void fsref_store(void* s, fso_fs* out) { S->store(out); }
+void fsref_set_bconds(void* s, const fso_bconds* bc) { S->set_bconds(bc); }
+double fsref_adjust_dt(void* s, double cfl, double dt_max) { return S->adjust_dt(cfl, dt_max); }
+void fsref_save_old_state(void* s) { S->save_old_state(); }
+void fsref_calc_mid_time(void* s) { S->calc_mid_time(); }
+void fsref_calc_dmomdt(void* s, double* dU, double* dV) { S->calc_dmomdt(dU, dV); }
+void fsref_update_velocity(void* s, const double* dU, const double* dV, double dt) {
+  S->update_velocity(dU, dV, dt);
+}
+void fsref_apply_velocity_bconds(void* s) { S->apply_bconds(); }
+void fsref_calc_divergence(void* s, double* div) { S->calc_divergence(div); }
+void fsref_fill_pressure_operator(void* s, int psd, double* op) { S->fill_operator(psd, op); }
+void fsref_fill_pressure_rhs(void* s, const double* div, double dt, int psd, double* rhs) {
+  S->fill_rhs(div, dt, psd, rhs);
+}
+void fsref_shift_pressure_to_zero(void* s, double* dp) { S->shift_pressure(dp); }
+void fsref_calc_drhodt(void* s, double* dru, double* drv) { S->calc_drhodt(dru, drv); }
+void fsref_calc_rho_visc_vof(void* s, const double* vf) { S->rho_visc_vof(vf); }
+void fsref_solver_create(void* s, double tol, int max_iter, int psd) {
+  S->solver_create(tol, max_iter, psd);
+}
+void fsref_solver_set_operator(void* s) { S->solver_set_operator(); }
+int fsref_solver_solve(void* s, const double* div, double dt, double* dp, double* res) {
+  return S->solver_solve(div, dt, dp, res);
+}
+int fsref_step(void* s, const fso_step_opts* o, double dt, double* res, double* phase_secs) {
+  return S->step(o, dt, res, phase_secs);
+}
+void fsref_diagnostics(void* s, double* umax, double* vmax, double* divmax) {
+  S->diagnostics(umax, vmax, divmax);
+}
+#undef S
+}

@@ -1,0 +1,402 @@
+"""ctypes bindings for the CHECKERS (test infrastructure, never product):
+
+* ``oracle/liboracle.so``     -- plain-C restatement of the reference path (oracle/fs_oracle.c,
+                                 oracle/pfmg_oracle.c)
+* ``oracle/_ref/libfsref.so`` -- the UNMODIFIED reference (headers + vendored HYPRE) behind
+                                 oracle/ref_harness.cpp; present where oracle/Makefile built it.
+
+All arrays are numpy float64 in the reference's storage (src/Container.hpp:105-111): ghost
+inclusive, j fastest.  U-like (NX+3, NY+2), V-like (NX+2, NY+3), cell (NX+2, NY+2).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass, field
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libfsref.so")
+
+DIRICHLET, NEUMANN, PERIODIC, SYMMETRY = 0, 1, 2, 3
+LEFT, RIGHT, BOTTOM, TOP = 0, 1, 2, 3
+PSD_NONE, PSD_LEFT, PSD_RIGHT, PSD_BOTTOM, PSD_TOP = 0, 1, 2, 3, 4
+
+DP = C.POINTER(C.c_double)
+
+
+class CFs(C.Structure):
+    _fields_ = [("nx", C.c_int64), ("ny", C.c_int64), ("dx", C.c_double), ("dy", C.c_double),
+                ("rho_gas", C.c_double), ("rho_liquid", C.c_double), ("visc_gas", C.c_double),
+                ("visc_liquid", C.c_double), ("sigma", C.c_double)] + [
+        (n, DP) for n in ("visc", "p", "p_jump_u", "p_jump_v", "rho_u_old", "rho_v_old", "U_old",
+                          "V_old", "rho_u", "rho_v", "U", "V")]
+
+
+class CBconds(C.Structure):
+    _fields_ = [("kind", C.c_int * 4), ("u_val", C.c_double * 4), ("v_val", C.c_double * 4),
+                ("u_prof", DP * 4), ("v_prof", DP * 4), ("clipped", C.c_int * 4)]
+
+
+class CSolverOpts(C.Structure):
+    _fields_ = [("tol", C.c_double), ("max_iter", C.c_int), ("max_levels", C.c_int),
+                ("relax_type", C.c_int), ("skip_relax", C.c_int)]
+
+
+class CStepOpts(C.Structure):
+    _fields_ = [("num_subiter", C.c_int), ("outflow_fix", C.c_int), ("psd", C.c_int),
+                ("rebuild_operator_each_subiter", C.c_int)]
+
+
+FIELDS_U = ("p_jump_u", "rho_u_old", "U_old", "rho_u", "U")
+FIELDS_V = ("p_jump_v", "rho_v_old", "V_old", "rho_v", "V")
+FIELDS_C = ("visc", "p")
+ALL_FIELDS = FIELDS_C + FIELDS_U + FIELDS_V
+
+
+def shape_of(name: str, nx: int, ny: int):
+    if name in FIELDS_U or name in ("dmomU",):
+        return (nx + 3, ny + 2)
+    if name in FIELDS_V or name in ("dmomV",):
+        return (nx + 2, ny + 3)
+    return (nx + 2, ny + 2)
+
+
+@dataclass
+class State:
+    """Host copy of the reference's ``FS`` (src/FS.hpp:28-52) as numpy arrays."""
+    nx: int
+    ny: int
+    dx: float
+    dy: float
+    rho_gas: float = 1.0
+    rho_liquid: float = 1.0
+    visc_gas: float = 1e-3
+    visc_liquid: float = 1e-3
+    sigma: float = 0.0
+    a: dict = field(default_factory=dict)
+
+    def __post_init__(self):
+        for n in ALL_FIELDS:
+            if n not in self.a:
+                self.a[n] = np.zeros(shape_of(n, self.nx, self.ny))
+            else:
+                self.a[n] = np.ascontiguousarray(self.a[n], dtype=np.float64)
+                assert self.a[n].shape == shape_of(n, self.nx, self.ny), n
+
+    def copy(self) -> "State":
+        return State(self.nx, self.ny, self.dx, self.dy, self.rho_gas, self.rho_liquid, self.visc_gas,
+                     self.visc_liquid, self.sigma, {k: v.copy() for k, v in self.a.items()})
+
+    def cstruct(self) -> CFs:
+        s = CFs(self.nx, self.ny, self.dx, self.dy, self.rho_gas, self.rho_liquid, self.visc_gas,
+                self.visc_liquid, self.sigma)
+        for n in ALL_FIELDS:
+            setattr(s, n, self.a[n].ctypes.data_as(DP))
+        return s
+
+    def __getattr__(self, n):
+        a = self.__dict__.get("a", {})
+        if n in a:
+            return a[n]
+        raise AttributeError(n)
+
+
+@dataclass
+class BConds:
+    """Mirror of ``FlowBConds`` (src/BoundaryConditions.hpp:207-212); order left,right,bottom,top."""
+    kind: tuple = (NEUMANN,) * 4
+    u_val: tuple = (0.0,) * 4
+    v_val: tuple = (0.0,) * 4
+    clipped: tuple = (0,) * 4
+    u_prof: tuple = (None,) * 4
+    v_prof: tuple = (None,) * 4
+
+    def cstruct(self) -> CBconds:
+        b = CBconds()
+        self._keep = []
+        for s in range(4):
+            b.kind[s] = self.kind[s]
+            b.u_val[s] = self.u_val[s]
+            b.v_val[s] = self.v_val[s]
+            b.clipped[s] = self.clipped[s]
+            for nm, prof in (("u_prof", self.u_prof[s]), ("v_prof", self.v_prof[s])):
+                if prof is not None:
+                    arr = np.ascontiguousarray(prof, dtype=np.float64)
+                    self._keep.append(arr)
+                    getattr(b, nm)[s] = arr.ctypes.data_as(DP)
+        return b
+
+
+def _ptr(a):
+    return a.ctypes.data_as(DP)
+
+
+class Oracle:
+    """oracle/liboracle.so"""
+
+    def __init__(self, path: str = ORACLE_SO):
+        self.lib = L = C.CDLL(path)
+        L.fso_adjust_dt.restype = C.c_double
+        L.fso_adjust_dt.argtypes = [C.POINTER(CFs), C.c_double, C.c_double]
+        L.fso_outflow_fix.restype = C.c_double
+        L.fso_abs_max.restype = C.c_double
+        L.fso_abs_max.argtypes = [DP, C.c_int64]
+        L.fso_calc_mid_time.argtypes = [DP, DP, C.c_int64]
+        L.fso_update_velocity.argtypes = [C.POINTER(CFs), DP, DP, C.c_double]
+        L.fso_update_density.argtypes = [C.POINTER(CFs), DP, DP, C.c_double]
+        L.fso_fill_pressure_operator.argtypes = [C.POINTER(CFs), C.c_int, DP]
+        L.fso_fill_pressure_rhs.argtypes = [C.POINTER(CFs), DP, C.c_double, C.c_int, DP]
+        L.fso_correct.argtypes = [C.POINTER(CFs), DP, C.c_double]
+        L.fso_apply_neumann_bconds.argtypes = [DP, C.c_int64, C.c_int64]
+        L.fso_solver_create.restype = C.c_void_p
+        L.fso_solver_create.argtypes = [C.c_int64, C.c_int64, C.POINTER(CSolverOpts)]
+        L.fso_solver_destroy.argtypes = [C.c_void_p]
+        L.fso_solver_set_operator.argtypes = [C.c_void_p, DP]
+        L.fso_solver_solve.restype = C.c_int
+        L.fso_solver_solve.argtypes = [C.c_void_p, DP, DP, DP]
+        L.fso_solver_num_levels.argtypes = [C.c_void_p]
+        L.fso_step.restype = C.c_int
+        L.fso_step.argtypes = [C.POINTER(CFs), C.POINTER(CBconds), C.c_void_p, C.POINTER(CStepOpts),
+                               C.c_double, DP]
+
+    # each method mutates / returns numpy arrays; `st` is a State
+    def adjust_dt(self, st, cfl, dt_max):
+        return self.lib.fso_adjust_dt(C.byref(st.cstruct()), cfl, dt_max)
+
+    def save_old_state(self, st):
+        self.lib.fso_save_old_state(C.byref(st.cstruct()))
+
+    def calc_mid_time(self, st):
+        self.lib.fso_calc_mid_time(_ptr(st.U), _ptr(st.U_old), st.U.size)
+        self.lib.fso_calc_mid_time(_ptr(st.V), _ptr(st.V_old), st.V.size)
+
+    def calc_dmomdt(self, st):
+        dU = np.zeros(shape_of("dmomU", st.nx, st.ny))
+        dV = np.zeros(shape_of("dmomV", st.nx, st.ny))
+        self.lib.fso_calc_dmomdt(C.byref(st.cstruct()), _ptr(dU), _ptr(dV))
+        return dU, dV
+
+    def calc_drhodt(self, st):
+        dU = np.zeros(shape_of("dmomU", st.nx, st.ny))
+        dV = np.zeros(shape_of("dmomV", st.nx, st.ny))
+        self.lib.fso_calc_drhodt(C.byref(st.cstruct()), _ptr(dU), _ptr(dV))
+        return dU, dV
+
+    def update_velocity(self, st, dU, dV, dt):
+        self.lib.fso_update_velocity(C.byref(st.cstruct()), _ptr(dU), _ptr(dV), dt)
+
+    def apply_velocity_bconds(self, st, bc):
+        self.lib.fso_apply_velocity_bconds(C.byref(st.cstruct()), C.byref(bc.cstruct()))
+
+    def outflow_fix(self, st):
+        return self.lib.fso_outflow_fix(C.byref(st.cstruct()))
+
+    def calc_divergence(self, st):
+        div = np.zeros((st.nx + 2, st.ny + 2))
+        self.lib.fso_calc_divergence(C.byref(st.cstruct()), _ptr(div))
+        return div
+
+    def fill_pressure_operator(self, st, psd=PSD_NONE):
+        op = np.zeros((st.ny + 2, st.nx + 2, 5))  # Layout::F: [j][i][5]
+        self.lib.fso_fill_pressure_operator(C.byref(st.cstruct()), psd, _ptr(op))
+        return op
+
+    def fill_pressure_rhs(self, st, div, dt, psd=PSD_NONE):
+        rhs = np.zeros((st.ny + 2, st.nx + 2))  # Layout::F
+        self.lib.fso_fill_pressure_rhs(C.byref(st.cstruct()), _ptr(div), dt, psd, _ptr(rhs))
+        return rhs
+
+    def shift_pressure_to_zero(self, st, dp):
+        self.lib.fso_shift_pressure_to_zero(C.byref(st.cstruct()), _ptr(dp))
+
+    def correct(self, st, dp, dt):
+        self.lib.fso_correct(C.byref(st.cstruct()), _ptr(dp), dt)
+
+    def abs_max(self, a):
+        return self.lib.fso_abs_max(_ptr(a), a.size)
+
+    def calc_rho_visc_const(self, st):
+        self.lib.fso_calc_rho_visc_const(C.byref(st.cstruct()))
+
+    def calc_rho_visc_vof(self, st, vf):
+        self.lib.fso_calc_rho_visc_vof(C.byref(st.cstruct()), _ptr(vf))
+
+    def apply_neumann_bconds(self, f):
+        self.lib.fso_apply_neumann_bconds(_ptr(f), f.shape[0] - 2, f.shape[1] - 2)
+
+    def solver(self, nx, ny, tol=1e-6, max_iter=50, max_levels=16, relax_type=1, skip_relax=1):
+        return OracleSolver(self, nx, ny, CSolverOpts(tol, max_iter, max_levels, relax_type, skip_relax))
+
+    def step(self, st, bc, solver, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0):
+        res = C.c_double(0)
+        o = CStepOpts(num_subiter, outflow_fix, psd, rebuild)
+        it = self.lib.fso_step(C.byref(st.cstruct()), C.byref(bc.cstruct()), solver.h, C.byref(o), dt,
+                               C.byref(res))
+        return it, res.value
+
+
+class OracleSolver:
+    def __init__(self, o: Oracle, nx, ny, opts: CSolverOpts):
+        self.o, self.nx, self.ny = o, nx, ny
+        self.h = C.c_void_p(o.lib.fso_solver_create(nx, ny, C.byref(opts)))
+
+    def set_operator(self, op):
+        op = np.ascontiguousarray(op)
+        self.o.lib.fso_solver_set_operator(self.h, _ptr(op))
+
+    def solve(self, rhs):
+        sol = np.zeros((self.nx + 2, self.ny + 2))
+        res = C.c_double(0)
+        rhs = np.ascontiguousarray(rhs)
+        it = self.o.lib.fso_solver_solve(self.h, _ptr(rhs), _ptr(sol), C.byref(res))
+        return sol, res.value, it
+
+    @property
+    def num_levels(self):
+        return self.o.lib.fso_solver_num_levels(self.h)
+
+    def __del__(self):
+        try:
+            self.o.lib.fso_solver_destroy(self.h)
+        except Exception:
+            pass
+
+
+def have_ref() -> bool:
+    return os.path.exists(REF_SO)
+
+
+class Ref:
+    """oracle/_ref/libfsref.so: one session = one reference ``FS`` + solver of a fixed size."""
+
+    _lib = None
+
+    @classmethod
+    def lib(cls):
+        if cls._lib is None:
+            L = C.CDLL(REF_SO)
+            L.fsref_create.restype = C.c_void_p
+            L.fsref_create.argtypes = [C.c_int64, C.c_int64]
+            L.fsref_supported.argtypes = [C.c_int64, C.c_int64]
+            for n in ("destroy", "save_old_state", "calc_mid_time", "apply_velocity_bconds",
+                      "solver_set_operator"):
+                getattr(L, "fsref_" + n).argtypes = [C.c_void_p]
+            L.fsref_load.argtypes = [C.c_void_p, C.POINTER(CFs)]
+            L.fsref_store.argtypes = [C.c_void_p, C.POINTER(CFs)]
+            L.fsref_set_bconds.argtypes = [C.c_void_p, C.POINTER(CBconds)]
+            L.fsref_adjust_dt.restype = C.c_double
+            L.fsref_adjust_dt.argtypes = [C.c_void_p, C.c_double, C.c_double]
+            L.fsref_calc_dmomdt.argtypes = [C.c_void_p, DP, DP]
+            L.fsref_calc_drhodt.argtypes = [C.c_void_p, DP, DP]
+            L.fsref_update_velocity.argtypes = [C.c_void_p, DP, DP, C.c_double]
+            L.fsref_calc_divergence.argtypes = [C.c_void_p, DP]
+            L.fsref_fill_pressure_operator.argtypes = [C.c_void_p, C.c_int, DP]
+            L.fsref_fill_pressure_rhs.argtypes = [C.c_void_p, DP, C.c_double, C.c_int, DP]
+            L.fsref_shift_pressure_to_zero.argtypes = [C.c_void_p, DP]
+            L.fsref_calc_rho_visc_vof.argtypes = [C.c_void_p, DP]
+            L.fsref_solver_create.argtypes = [C.c_void_p, C.c_double, C.c_int, C.c_int]
+            L.fsref_solver_solve.restype = C.c_int
+            L.fsref_solver_solve.argtypes = [C.c_void_p, DP, C.c_double, DP, DP]
+            L.fsref_step.restype = C.c_int
+            L.fsref_step.argtypes = [C.c_void_p, C.POINTER(CStepOpts), C.c_double, DP, DP]
+            L.fsref_diagnostics.argtypes = [C.c_void_p, DP, DP, DP]
+            L.fsref_set_threads.argtypes = [C.c_int]
+            cls._lib = L
+        return cls._lib
+
+    def __init__(self, nx, ny):
+        L = self.lib()
+        if not L.fsref_supported(nx, ny):
+            raise ValueError(f"reference harness has no instantiation for {nx}x{ny}")
+        self.nx, self.ny = nx, ny
+        self.h = C.c_void_p(L.fsref_create(nx, ny))
+
+    def __del__(self):
+        try:
+            self.lib().fsref_destroy(self.h)
+        except Exception:
+            pass
+
+    def load(self, st):
+        self.lib().fsref_load(self.h, C.byref(st.cstruct()))
+
+    def store(self, st):
+        self.lib().fsref_store(self.h, C.byref(st.cstruct()))
+
+    def set_bconds(self, bc):
+        self.lib().fsref_set_bconds(self.h, C.byref(bc.cstruct()))
+
+    def adjust_dt(self, cfl, dt_max):
+        return self.lib().fsref_adjust_dt(self.h, cfl, dt_max)
+
+    def save_old_state(self):
+        self.lib().fsref_save_old_state(self.h)
+
+    def calc_mid_time(self):
+        self.lib().fsref_calc_mid_time(self.h)
+
+    def calc_dmomdt(self):
+        dU = np.zeros(shape_of("dmomU", self.nx, self.ny))
+        dV = np.zeros(shape_of("dmomV", self.nx, self.ny))
+        self.lib().fsref_calc_dmomdt(self.h, _ptr(dU), _ptr(dV))
+        return dU, dV
+
+    def calc_drhodt(self):
+        dU = np.zeros(shape_of("dmomU", self.nx, self.ny))
+        dV = np.zeros(shape_of("dmomV", self.nx, self.ny))
+        self.lib().fsref_calc_drhodt(self.h, _ptr(dU), _ptr(dV))
+        return dU, dV
+
+    def update_velocity(self, dU, dV, dt):
+        self.lib().fsref_update_velocity(self.h, _ptr(dU), _ptr(dV), dt)
+
+    def apply_velocity_bconds(self):
+        self.lib().fsref_apply_velocity_bconds(self.h)
+
+    def calc_divergence(self):
+        div = np.zeros((self.nx + 2, self.ny + 2))
+        self.lib().fsref_calc_divergence(self.h, _ptr(div))
+        return div
+
+    def fill_pressure_operator(self, psd=PSD_NONE):
+        op = np.zeros((self.ny + 2, self.nx + 2, 5))
+        self.lib().fsref_fill_pressure_operator(self.h, psd, _ptr(op))
+        return op
+
+    def fill_pressure_rhs(self, div, dt, psd=PSD_NONE):
+        rhs = np.zeros((self.ny + 2, self.nx + 2))
+        self.lib().fsref_fill_pressure_rhs(self.h, _ptr(div), dt, psd, _ptr(rhs))
+        return rhs
+
+    def shift_pressure_to_zero(self, dp):
+        self.lib().fsref_shift_pressure_to_zero(self.h, _ptr(dp))
+
+    def calc_rho_visc_vof(self, vf):
+        self.lib().fsref_calc_rho_visc_vof(self.h, _ptr(vf))
+
+    def solver_create(self, tol=1e-6, max_iter=50, psd=PSD_NONE):
+        self.lib().fsref_solver_create(self.h, tol, max_iter, psd)
+
+    def solver_set_operator(self):
+        self.lib().fsref_solver_set_operator(self.h)
+
+    def solver_solve(self, div, dt):
+        dp = np.zeros((self.nx + 2, self.ny + 2))
+        res = C.c_double(0)
+        it = self.lib().fsref_solver_solve(self.h, _ptr(div), dt, _ptr(dp), C.byref(res))
+        return dp, res.value, it
+
+    def step(self, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0, phases=None):
+        res = C.c_double(0)
+        o = CStepOpts(num_subiter, outflow_fix, psd, rebuild)
+        ph = _ptr(phases) if phases is not None else None
+        it = self.lib().fsref_step(self.h, C.byref(o), dt, C.byref(res), ph)
+        return it, res.value
+
+    def diagnostics(self):
+        a, b, c = C.c_double(0), C.c_double(0), C.c_double(0)
+        self.lib().fsref_diagnostics(self.h, C.byref(a), C.byref(b), C.byref(c))
+        return a.value, b.value, c.value
