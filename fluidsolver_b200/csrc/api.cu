@@ -1,0 +1,358 @@
+// fluidsolver_b200/csrc/api.cu -- the C ABI of include/fsgpu.h.
+#include "solver.h"
+
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <new>
+
+int64_t g_launches = 0;
+static thread_local char g_err[512] = "";
+
+void fs_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+#define FS_CHECK_CTX(c)                           \
+  do {                                            \
+    if (!(c)) {                                   \
+      fs_set_error("%s: null context", __func__); \
+      return 1;                                   \
+    }                                             \
+    FS_CUDA(cudaSetDevice((c)->device));          \
+  } while (0)
+#define FS_CHECK_FIELD(f)                                  \
+  do {                                                     \
+    if ((f) < 0 || (f) >= FSGPU_NUM_FIELDS) {              \
+      fs_set_error("%s: bad field id %d", __func__, (f));  \
+      return 1;                                            \
+    }                                                      \
+  } while (0)
+
+extern "C" {
+
+const char* fsgpu_last_error(void) { return g_err; }
+int64_t fsgpu_launch_count(void) { return g_launches; }
+
+int fsgpu_device_count(int* n) {
+  FS_CUDA(cudaGetDeviceCount(n));
+  return 0;
+}
+
+int fsgpu_create(int64_t nx, int64_t ny, double dx, double dy, int device, fsgpu_ctx** out) {
+  if (!out || nx < 2 || ny < 2 || !(dx > 0) || !(dy > 0)) {
+    fs_set_error("fsgpu_create: bad arguments (nx=%lld ny=%lld)", (long long)nx, (long long)ny);
+    return 1;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    fs_set_error("fsgpu_create: no CUDA device (this library has no CPU fallback)");
+    return 1;
+  }
+  FS_CUDA(cudaSetDevice(device));
+  fsgpu_ctx* c = new (std::nothrow) fsgpu_ctx();
+  if (!c) { fs_set_error("out of host memory"); return 1; }
+  c->device = device;
+  c->g.nx = nx; c->g.ny = ny; c->g.dx = dx; c->g.dy = dy;
+  c->g.pitch = (ny + 3 + FS_CO + 2 + 15) / 16 * 16;
+  c->g.rows  = nx + 3 + 2 * FS_RO;
+  const size_t n = (size_t)c->g.count();
+  const int nf = FSGPU_NUM_FIELDS + 2;
+  FS_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  FS_CUDA(cudaMalloc(&c->slab, n * nf * sizeof(double)));
+  FS_CUDA(cudaMemsetAsync(c->slab, 0, n * nf * sizeof(double), c->stream));
+  for (int f = 0; f < FSGPU_NUM_FIELDS; ++f) c->f[f] = c->slab + n * f;
+  c->U_alt = c->slab + n * FSGPU_NUM_FIELDS;
+  c->V_alt = c->slab + n * (FSGPU_NUM_FIELDS + 1);
+  FS_CUDA(cudaMalloc(&c->ticket, sizeof(unsigned int)));
+  FS_CUDA(cudaMemsetAsync(c->ticket, 0, sizeof(unsigned int), c->stream));
+  FS_CUDA(cudaMalloc(&c->red_out, 16 * sizeof(double)));
+  FS_CUDA(cudaMemsetAsync(c->red_out, 0, 16 * sizeof(double), c->stream));
+  FS_CUDA(cudaMallocHost(&c->h_red, 16 * sizeof(double)));
+  FS_CUDA(cudaStreamSynchronize(c->stream));
+  *out = c;
+  return 0;
+}
+
+int fsgpu_destroy(fsgpu_ctx* c) {
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (int s = 0; s < 4; ++s) {
+    if (c->bc[s].u_prof) cudaFree(c->bc[s].u_prof);
+    if (c->bc[s].v_prof) cudaFree(c->bc[s].v_prof);
+  }
+  cudaFree(c->slab);
+  cudaFree(c->part);
+  cudaFree(c->ticket);
+  cudaFree(c->red_out);
+  cudaFreeHost(c->h_red);
+  cudaStreamDestroy(c->stream);
+  delete c;
+  return 0;
+}
+
+int fsgpu_set_props(fsgpu_ctx* c, double rho_gas, double rho_liquid, double visc_gas,
+                    double visc_liquid, double sigma) {
+  FS_CHECK_CTX(c);
+  c->rho_gas = rho_gas; c->rho_liquid = rho_liquid;
+  c->visc_gas = visc_gas; c->visc_liquid = visc_liquid; c->sigma = sigma;
+  return 0;
+}
+
+int fsgpu_upload(fsgpu_ctx* c, int field, const double* host) {
+  FS_CHECK_CTX(c);
+  FS_CHECK_FIELD(field);
+  int64_t m, n;
+  field_extent(c->g, field, &m, &n);
+  FS_CUDA(cudaMemcpy2DAsync(c->f[field] + c->g.idx(0, 0), c->g.pitch * sizeof(double), host,
+                            n * sizeof(double), n * sizeof(double), m, cudaMemcpyHostToDevice,
+                            c->stream));
+  // pageable host memory: the copy may still be staged when the call returns
+  FS_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int fsgpu_download(fsgpu_ctx* c, int field, double* host) {
+  FS_CHECK_CTX(c);
+  FS_CHECK_FIELD(field);
+  int64_t m, n;
+  field_extent(c->g, field, &m, &n);
+  FS_CUDA(cudaMemcpy2DAsync(host, n * sizeof(double), c->f[field] + c->g.idx(0, 0),
+                            c->g.pitch * sizeof(double), n * sizeof(double), m,
+                            cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int fsgpu_fill(fsgpu_ctx* c, int field, double value) {
+  FS_CHECK_CTX(c);
+  FS_CHECK_FIELD(field);
+  return fs_launch_fill(c, field, value);
+}
+
+int fsgpu_sync(fsgpu_ctx* c) {
+  FS_CHECK_CTX(c);
+  FS_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int fsgpu_device_field(fsgpu_ctx* c, int field, double** ptr, int64_t* pitch, int64_t* row0,
+                       int64_t* col0) {
+  FS_CHECK_CTX(c);
+  FS_CHECK_FIELD(field);
+  if (ptr) *ptr = c->f[field];
+  if (pitch) *pitch = c->g.pitch;
+  if (row0) *row0 = FS_RO;
+  if (col0) *col0 = FS_CO;
+  return 0;
+}
+
+int fsgpu_stream(fsgpu_ctx* c, void** cuda_stream) {
+  FS_CHECK_CTX(c);
+  *cuda_stream = (void*)c->stream;
+  return 0;
+}
+
+int fsgpu_set_bconds(fsgpu_ctx* c, int side, int kind, double u_val, double v_val,
+                     const double* u_prof, const double* v_prof, int clipped) {
+  FS_CHECK_CTX(c);
+  if (side < 0 || side > 3 || kind < 0 || kind > 3) {
+    fs_set_error("fsgpu_set_bconds: bad side/kind %d/%d", side, kind);
+    return 1;
+  }
+  BCondSide& b = c->bc[side];
+  b.kind = kind; b.u = u_val; b.v = v_val; b.clipped = clipped;
+  const bool lr = side == FSGPU_LEFT || side == FSGPU_RIGHT;
+  const size_t nu = (size_t)(lr ? c->g.ny + 2 : c->g.nx + 3);
+  const size_t nv = (size_t)(lr ? c->g.ny + 3 : c->g.nx + 2);
+  FS_CUDA(cudaStreamSynchronize(c->stream));
+  if (b.u_prof) { cudaFree(b.u_prof); b.u_prof = nullptr; }
+  if (b.v_prof) { cudaFree(b.v_prof); b.v_prof = nullptr; }
+  if (u_prof) {
+    FS_CUDA(cudaMalloc(&b.u_prof, nu * sizeof(double)));
+    FS_CUDA(cudaMemcpy(b.u_prof, u_prof, nu * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  if (v_prof) {
+    FS_CUDA(cudaMalloc(&b.v_prof, nv * sizeof(double)));
+    FS_CUDA(cudaMemcpy(b.v_prof, v_prof, nv * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  return 0;
+}
+
+static int read_red(fsgpu_ctx* c, int off, int n) {
+  FS_CUDA(cudaMemcpyAsync(c->h_red + off, c->red_out + off, n * sizeof(double),
+                          cudaMemcpyDeviceToHost, c->stream));
+  FS_CUDA(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int fsgpu_adjust_dt(fsgpu_ctx* c, double cfl_max, double dt_max, double* dt) {
+  FS_CHECK_CTX(c);
+  if (fs_launch_cfl(c)) return 1;
+  if (read_red(c, 0, 4)) return 1;
+  double st = 0.0;
+  if (c->sigma > 0.0) {  // FS.hpp:108-114
+    st = 1.0 / sqrt(((c->rho_gas + c->rho_liquid) * pow(c->g.dx * c->g.dy, 3.0 / 2.0)) /
+                    (4.0 * M_PI * c->sigma));
+  }
+  double m = st;
+  for (int q = 0; q < 4; ++q) m = fmax(m, c->h_red[q]);
+  *dt = fmin(cfl_max / m, dt_max);
+  return 0;
+}
+
+static int copy_field(fsgpu_ctx* c, int dst, int src) {
+  FS_CUDA(cudaMemcpyAsync(c->f[dst], c->f[src], (size_t)c->g.count() * sizeof(double),
+                          cudaMemcpyDeviceToDevice, c->stream));
+  return 0;
+}
+int fsgpu_save_old_velocity(fsgpu_ctx* c) {
+  FS_CHECK_CTX(c);
+  return copy_field(c, FSGPU_U_OLD, FSGPU_U) || copy_field(c, FSGPU_V_OLD, FSGPU_V);
+}
+int fsgpu_save_old_density(fsgpu_ctx* c) {
+  FS_CHECK_CTX(c);
+  return copy_field(c, FSGPU_RHO_U_OLD, FSGPU_RHO_U) || copy_field(c, FSGPU_RHO_V_OLD, FSGPU_RHO_V);
+}
+int fsgpu_save_old_state(fsgpu_ctx* c) {
+  return fsgpu_save_old_density(c) || fsgpu_save_old_velocity(c);
+}
+
+int fsgpu_calc_mid_time(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_mid_time(c); }
+int fsgpu_calc_dmomdt(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_dmomdt(c); }
+int fsgpu_update_velocity(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_update_velocity(c, dt); }
+int fsgpu_momentum_update(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_momentum_update(c, dt); }
+int fsgpu_apply_velocity_bconds(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_bconds(c); }
+int fsgpu_calc_divergence(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_divergence(c); }
+int fsgpu_shift_pressure_to_zero(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_shift_pressure(c); }
+int fsgpu_correct_velocity(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_correct(c, dt, false); }
+
+int fsgpu_outflow_fix(fsgpu_ctx* c, double* mass_error) {
+  FS_CHECK_CTX(c);
+  if (fs_launch_outflow_fix(c, c->red_out + 2)) return 1;
+  if (mass_error) {
+    if (read_red(c, 2, 1)) return 1;
+    *mass_error = c->h_red[2];
+  }
+  return 0;
+}
+
+int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out) {
+  FS_CHECK_CTX(c);
+  FS_CHECK_FIELD(field);
+  if (fs_launch_absmax(c, field)) return 1;
+  if (read_red(c, 0, 1)) return 1;
+  *out = c->h_red[0];
+  return 0;
+}
+
+int fsgpu_calc_rho_visc_const(fsgpu_ctx* c) {
+  FS_CHECK_CTX(c);
+  // calc_rho(fs) fills curr and old densities, calc_visc(fs) the viscosity (FS.hpp:569-589)
+  return fs_launch_fill(c, FSGPU_RHO_U, c->rho_gas) || fs_launch_fill(c, FSGPU_RHO_V, c->rho_gas) ||
+         fs_launch_fill(c, FSGPU_RHO_U_OLD, c->rho_gas) || fs_launch_fill(c, FSGPU_RHO_V_OLD, c->rho_gas) ||
+         fs_launch_fill(c, FSGPU_VISC, c->visc_gas);
+}
+int fsgpu_calc_rho_visc_vof(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_rho_visc_vof(c); }
+int fsgpu_apply_neumann_bconds(fsgpu_ctx* c, int field) {
+  FS_CHECK_CTX(c);
+  FS_CHECK_FIELD(field);
+  int64_t m, n;
+  field_extent(c->g, field, &m, &n);
+  return fs_launch_neumann(c, c->f[field], m - 2, n - 2);
+}
+
+// ---- solver -----------------------------------------------------------------------------------
+int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out) {
+  FS_CHECK_CTX(c);
+  if (!o || !out) { fs_set_error("fsgpu_ps_create: null argument"); return 1; }
+  if (o->relax != 0 && o->relax != FSGPU_RELAX_JACOBI) {
+    fs_set_error("fsgpu_ps_create: smoother %d not available in this build", o->relax);
+    return 1;
+  }
+  fsgpu_ps* s = new (std::nothrow) fsgpu_ps();
+  if (!s) { fs_set_error("out of host memory"); return 1; }
+  s->c = c;
+  s->o = *o;
+  if (s->o.relax == 0) s->o.relax = FSGPU_RELAX_JACOBI;
+  FS_CUDA(cudaMalloc(&s->scal, sizeof(PcgScal)));
+  FS_CUDA(cudaMemset(s->scal, 0, sizeof(PcgScal)));
+  FS_CUDA(cudaMallocHost(&s->h_scal, 4 * sizeof(PcgScal)));
+  for (int i = 0; i < 4; ++i) FS_CUDA(cudaEventCreateWithFlags(&s->ev[i], cudaEventDisableTiming));
+  *out = s;
+  return 0;
+}
+
+int fsgpu_ps_destroy(fsgpu_ps* s) {
+  if (!s) return 0;
+  cudaSetDevice(s->c->device);
+  cudaStreamSynchronize(s->c->stream);
+  cudaFree(s->slab);
+  cudaFree(s->scal);
+  cudaFreeHost(s->h_scal);
+  for (int i = 0; i < 4; ++i) cudaEventDestroy(s->ev[i]);
+  delete s;
+  return 0;
+}
+
+int fsgpu_ps_set_operator(fsgpu_ps* s) {
+  if (!s) { fs_set_error("null solver"); return 1; }
+  FS_CHECK_CTX(s->c);
+  return ps_setup(s);
+}
+
+int fsgpu_ps_set_rhs(fsgpu_ps* s, double dt) {
+  if (!s) { fs_set_error("null solver"); return 1; }
+  FS_CHECK_CTX(s->c);
+  return fs_launch_rhs(s->c, dt, s->o.psd, false);
+}
+
+int fsgpu_ps_solve(fsgpu_ps* s, double* residual, int* iters) {
+  if (!s) { fs_set_error("null solver"); return 1; }
+  FS_CHECK_CTX(s->c);
+  if (!s->is_setup) { fs_set_error("fsgpu_ps_solve: set_pressure_operator has not been called"); return 1; }
+  return ps_solve(s, residual, iters);
+}
+
+int fsgpu_ps_num_levels(fsgpu_ps* s, int* n) {
+  if (!s) { fs_set_error("null solver"); return 1; }
+  *n = s->nl;
+  return 0;
+}
+
+// ---- fused sub-iteration / step, scaling/LidDrivenFlow.cpp:121-163 ----------------------------
+int fsgpu_substep(fsgpu_ctx* c, fsgpu_ps* s, double dt, int flags, double* residual, int* iters) {
+  FS_CHECK_CTX(c);
+  if (!s || s->c != c) { fs_set_error("fsgpu_substep: solver does not belong to this context"); return 1; }
+  if (fs_launch_momentum_update(c, dt)) return 1;  // mid-time + dmomdt + update
+  if (fs_launch_bconds(c)) return 1;
+  if ((flags & FSGPU_STEP_OUTFLOW_FIX) && fs_launch_outflow_fix(c, c->red_out + 2)) return 1;
+  if ((flags & FSGPU_STEP_REBUILD_OPERATOR) || !s->is_setup) {
+    if (ps_setup(s)) return 1;
+  }
+  if (fs_launch_rhs(c, dt, s->o.psd, true)) return 1;  // divergence + rhs (+ mean removal)
+  if (ps_solve(s, residual, iters)) return 1;
+  if (fs_launch_correct(c, dt, true)) return 1;        // shift + p += dp + velocity correction
+  return 0;
+}
+
+int fsgpu_step(fsgpu_ctx* c, fsgpu_ps* s, double dt, int num_subiter, int flags, double* residual,
+               int* iters) {
+  if (fsgpu_save_old_state(c)) return 1;
+  int total = 0;
+  for (int k = 0; k < num_subiter; ++k) {
+    int it = 0;
+    if (fsgpu_substep(c, s, dt, flags, residual, &it)) return 1;
+    total += it;
+  }
+  if (iters) *iters = total;
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,181 @@
+// fluidsolver_b200/csrc/bconds.cu -- velocity boundary conditions on the ghost ring.
+//
+// Replaces apply_velocity_bconds (src/BoundaryConditions.hpp:215-224) with its four kinds
+// Dirichlet (:14-90), Neumann (:93-139), Periodic (:142-167), Symmetry (:170-206), the scalar
+// apply_neumann_bconds (:227-252) and the channel drivers' outflow fix
+// (test/LaminarChannel.cpp:55-66,201-205).
+//
+// The reference applies left, right, bottom, top in that order; bottom/top run over the ghost
+// inclusive i-range and read the values left/right have just written at i = -1 / NX(+1), so the
+// work is two launches: k_bc_lr (left + right, which never touch each other's rows) and then
+// k_bc_bt (bottom + top).
+#include "ctx.h"
+
+namespace {
+
+struct BcArgs {
+  int kind[4];
+  double u[4], v[4];
+  int clipped[4];
+  const double* up[4];
+  const double* vp[4];
+  double *U, *V;
+};
+
+// left (s = 0) and right (s = 1): thread b = j + 1 in [0, NY + 2]
+__global__ void k_bc_lr(const BcArgs a, const Geom g) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s     = blockIdx.y;  // 0 left, 1 right
+  if (b > g.ny + 2) return;
+  const int64_t P = g.pitch;
+  const bool in_u = b <= g.ny + 1;  // U rows have NY+2 entries, V rows NY+3
+  // U: ghost row ag, boundary face row af, first interior-side row a1; V: ghost row vg, inner vi
+  const int64_t ag = s == 0 ? 0 : g.nx + 2, af = s == 0 ? 1 : g.nx + 1, a1 = s == 0 ? 2 : g.nx;
+  const int64_t vg = s == 0 ? 0 : g.nx + 1, vi = s == 0 ? 1 : g.nx;
+  double* U = a.U;
+  double* V = a.V;
+  switch (a.kind[s]) {
+    case FSGPU_BC_DIRICHLET: {
+      if (in_u) {
+        const double ub = a.up[s] ? a.up[s][b] : a.u[s];
+        U[g.idx(ag, b)] = ub;
+        U[g.idx(af, b)] = ub;
+      }
+      const double vb = a.vp[s] ? a.vp[s][b] : a.v[s];
+      V[g.idx(vg, b)] = 2.0 * vb - V[g.idx(vi, b)];
+    } break;
+    case FSGPU_BC_NEUMANN: {
+      if (in_u) {
+        double x = U[g.idx(af, b)];
+        if (a.clipped[s]) x = s == 0 ? fmin(x, 0.0) : fmax(x, 0.0);
+        U[g.idx(ag, b)] = x;
+      }
+      V[g.idx(vg, b)] = V[g.idx(vi, b)];
+    } break;
+    case FSGPU_BC_PERIODIC: {
+      // left: U(-1,j) = U(NX-1,j), V(-1,j) = V(NX-1,j); right: U(NX+1,j) = U(1,j), V(NX,j) = V(0,j)
+      if (in_u) U[g.idx(ag, b)] = U[g.idx(s == 0 ? g.nx : 2, b)];
+      V[g.idx(vg, b)] = V[g.idx(s == 0 ? g.nx : 1, b)];
+    } break;
+    default: {  // symmetry
+      if (in_u) {
+        U[g.idx(ag, b)] = -U[g.idx(a1, b)];
+        U[g.idx(af, b)] = 0.0;
+      }
+      V[g.idx(vg, b)] = V[g.idx(vi, b)];
+    } break;
+  }
+  (void)P;
+}
+
+// bottom (s = 2) and top (s = 3): thread a = i + 1 in [0, NX + 2]
+__global__ void k_bc_bt(const BcArgs a, const Geom g) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int s     = 2 + blockIdx.y;
+  if (r > g.nx + 2) return;
+  const bool in_v = r <= g.nx + 1;  // V has NX+2 rows, U NX+3
+  const int64_t ug = s == 2 ? 0 : g.ny + 1, ui = s == 2 ? 1 : g.ny;                      // U cols
+  const int64_t bg = s == 2 ? 0 : g.ny + 2, bf = s == 2 ? 1 : g.ny + 1, b1 = s == 2 ? 2 : g.ny;  // V cols
+  double* U = a.U;
+  double* V = a.V;
+  switch (a.kind[s]) {
+    case FSGPU_BC_DIRICHLET: {
+      const double ub = a.up[s] ? a.up[s][r] : a.u[s];
+      U[g.idx(r, ug)] = 2.0 * ub - U[g.idx(r, ui)];
+      if (in_v) {
+        const double vb = a.vp[s] ? a.vp[s][r] : a.v[s];
+        V[g.idx(r, bg)] = vb;
+        V[g.idx(r, bf)] = vb;
+      }
+    } break;
+    case FSGPU_BC_NEUMANN: {
+      U[g.idx(r, ug)] = U[g.idx(r, ui)];
+      if (in_v) {
+        double x = V[g.idx(r, bf)];
+        if (a.clipped[s]) x = s == 2 ? fmin(x, 0.0) : fmax(x, 0.0);
+        V[g.idx(r, bg)] = x;
+      }
+    } break;
+    case FSGPU_BC_PERIODIC: {
+      // bottom: U(i,-1) = U(i,NY-1), V(i,-1) = V(i,NY-1); top: U(i,NY) = U(i,0), V(i,NY+1) = V(i,1)
+      U[g.idx(r, ug)] = U[g.idx(r, s == 2 ? g.ny : 1)];
+      if (in_v) V[g.idx(r, bg)] = V[g.idx(r, s == 2 ? g.ny : 2)];
+    } break;
+    default: {  // symmetry
+      U[g.idx(r, ug)] = U[g.idx(r, ui)];
+      if (in_v) {
+        V[g.idx(r, bg)] = -V[g.idx(r, b1)];
+        V[g.idx(r, bf)] = 0.0;
+      }
+    } break;
+  }
+}
+
+// test/LaminarChannel.cpp:55-66 (sums over j = -1..NY) and :201-205; one block
+__global__ void k_outflow_fix(double* __restrict__ U, const double* __restrict__ ru, const Geom g,
+                              double* mass_error_out) {
+  __shared__ double sm[32];
+  __shared__ double merr;
+  double in = 0.0, out = 0.0;
+  for (int64_t b = threadIdx.x; b <= g.ny + 1; b += blockDim.x) {
+    in += ru[g.idx(0, b)] * U[g.idx(0, b)];
+    out += ru[g.idx(g.nx + 2, b)] * U[g.idx(g.nx + 2, b)];
+  }
+  in  = block_reduce<ReduceSum>(in, sm);
+  out = block_reduce<ReduceSum>(out, sm);
+  if (threadIdx.x == 0) {
+    merr = out - in;
+    if (mass_error_out) *mass_error_out = merr;
+  }
+  __syncthreads();
+  const double me = merr;
+  for (int64_t b = threadIdx.x; b <= g.ny + 1; b += blockDim.x) {
+    const int64_t k = g.idx(g.nx + 2, b);
+    U[k] -= me / (ru[k] * (double)(g.ny + 2));
+  }
+}
+
+// BoundaryConditions.hpp:227-252 on an (m+2) x (n+2) field: left/right first, then bottom/top
+__global__ void k_neumann_lr(double* f, int64_t m, int64_t n, const Geom g) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > n + 1) return;
+  f[g.idx(0, b)]     = f[g.idx(1, b)];
+  f[g.idx(m + 1, b)] = f[g.idx(m, b)];
+}
+__global__ void k_neumann_bt(double* f, int64_t m, int64_t n, const Geom g) {
+  const int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a > m + 1) return;
+  f[g.idx(a, 0)]     = f[g.idx(a, 1)];
+  f[g.idx(a, n + 1)] = f[g.idx(a, n)];
+}
+
+}  // namespace
+
+int fs_launch_bconds(fsgpu_ctx* c) {
+  BcArgs a;
+  for (int s = 0; s < 4; ++s) {
+    a.kind[s] = c->bc[s].kind; a.u[s] = c->bc[s].u; a.v[s] = c->bc[s].v;
+    a.clipped[s] = c->bc[s].clipped; a.up[s] = c->bc[s].u_prof; a.vp[s] = c->bc[s].v_prof;
+  }
+  a.U = c->f[FSGPU_U];
+  a.V = c->f[FSGPU_V];
+  k_bc_lr<<<dim3((unsigned)cdiv(c->g.ny + 3, 128), 2), 128, 0, c->stream>>>(a, c->g);
+  FS_LAUNCHED();
+  k_bc_bt<<<dim3((unsigned)cdiv(c->g.nx + 3, 128), 2), 128, 0, c->stream>>>(a, c->g);
+  FS_LAUNCHED();
+  return 0;
+}
+
+int fs_launch_outflow_fix(fsgpu_ctx* c, double* d_mass_error) {
+  k_outflow_fix<<<1, 1024, 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_RHO_U], c->g, d_mass_error);
+  FS_LAUNCHED();
+  return 0;
+}
+
+int fs_launch_neumann(fsgpu_ctx* c, double* f, int64_t m, int64_t n) {
+  k_neumann_lr<<<(unsigned)cdiv(n + 2, 128), 128, 0, c->stream>>>(f, m, n, c->g);
+  FS_LAUNCHED();
+  k_neumann_bt<<<(unsigned)cdiv(m + 2, 128), 128, 0, c->stream>>>(f, m, n, c->g);
+  FS_LAUNCHED();
+  return 0;
+}

@@ -1,0 +1,125 @@
+// fluidsolver_b200/csrc/common.cuh -- shared definitions of libfsgpu.so (sm_100a only).
+//
+// Device data layout (DESIGN.md "Data layout in HBM").  Every level-0 array -- flow fields and
+// solver vectors alike -- is one padded 2-D array of doubles with the SAME geometry, so a kernel
+// addresses U, V, rho, p, rhs, delta_p ... with one linear index:
+//
+//     element (a, b), a = i + 1 >= 0, b = j + 1 >= 0   (ghost-inclusive, zero based; i, j are the
+//     reference's indices, src/Container.hpp:105-111)  lives at  (a + FS_RO) * pitch + (b + FS_CO)
+//
+// FS_RO = 2 zero rows above/below and FS_CO = 4 / >= 2 zero columns left/right stay zero for the
+// lifetime of the context: stencils may read one or two points past the edge without a branch
+// (coefficients there are zero), and b = 0 sits on a 32-byte boundary for vector access.
+// `pitch` is a multiple of 16 doubles (128 B lines).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define FS_RO 2
+#define FS_CO 4
+
+struct Geom {
+  int64_t nx, ny;   // interior cells
+  int64_t pitch;    // doubles per row
+  int64_t rows;     // allocated rows = nx + 3 + 2 * FS_RO
+  double dx, dy;
+  __host__ __device__ inline int64_t idx(int64_t a, int64_t b) const {
+    return (a + FS_RO) * pitch + (b + FS_CO);
+  }
+  __host__ __device__ inline int64_t count() const { return rows * pitch; }
+};
+
+// ---- deterministic grid-wide reductions -----------------------------------------------------
+// Each block reduces with warp shuffles + one shared-memory stage and stores its partial at
+// part[blockIdx]; the LAST block to finish (threadfence + atomic ticket) folds all partials in a
+// fixed order, so results do not depend on block scheduling.
+struct ReduceSum {
+  __device__ static inline double op(double a, double b) { return a + b; }
+  __device__ static inline double id() { return 0.0; }
+};
+struct ReduceMax {
+  __device__ static inline double op(double a, double b) { return a > b ? a : b; }
+  __device__ static inline double id() { return -1.0e308; }
+};
+
+template <class R>
+__device__ inline double warp_reduce(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = R::op(v, __shfl_down_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// all threads of the block must call; result valid in thread 0
+template <class R>
+__device__ inline double block_reduce(double v, double* sm /* >= 32 doubles */) {
+  const int tid  = threadIdx.x + threadIdx.y * blockDim.x;
+  const int nthr = blockDim.x * blockDim.y;
+  const int lane = tid & 31, w = tid >> 5;
+  v = warp_reduce<R>(v);
+  __syncthreads();
+  if (lane == 0) sm[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    v = (lane < (nthr + 31) / 32) ? sm[lane] : R::id();
+    v = warp_reduce<R>(v);
+  }
+  return v;
+}
+
+// NV values per thread reduced at once.  Returns true in ALL threads of the last block, with the
+// grid totals in out[0..NV) (valid in thread 0 of that block).  part must hold NV * nblocks doubles.
+template <class R, int NV>
+__device__ inline bool grid_reduce(const double (&v)[NV], double* part, unsigned int* ticket,
+                                   double (&out)[NV]) {
+  __shared__ double sm[32];
+  __shared__ bool last;
+  const int tid     = threadIdx.x + threadIdx.y * blockDim.x;
+  const int nthr    = blockDim.x * blockDim.y;
+  const unsigned nb = gridDim.x * gridDim.y;
+  const unsigned bid = blockIdx.x + blockIdx.y * gridDim.x;
+#pragma unroll
+  for (int q = 0; q < NV; ++q) {
+    const double r = block_reduce<R>(v[q], sm);
+    if (tid == 0) part[(size_t)q * nb + bid] = r;
+  }
+  __threadfence();
+  if (tid == 0) {
+    const unsigned t = atomicInc(ticket, nb - 1);  // wraps to 0 after the last block
+    last = (t == nb - 1);
+  }
+  __syncthreads();
+  if (!last) return false;
+  __threadfence();
+#pragma unroll
+  for (int q = 0; q < NV; ++q) {
+    double a = R::id();
+    for (unsigned k = tid; k < nb; k += nthr) a = R::op(a, __ldcg(&part[(size_t)q * nb + k]));
+    a = block_reduce<R>(a, sm);
+    out[q] = a;
+  }
+  return true;
+}
+
+// ---- error handling / launch accounting (api.cu) ---------------------------------------------
+void fs_set_error(const char* fmt, ...);
+extern int64_t g_launches;
+#define FS_CUDA(x)                                                                       \
+  do {                                                                                   \
+    cudaError_t e_ = (x);                                                                \
+    if (e_ != cudaSuccess) {                                                             \
+      fs_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #x, cudaGetErrorString(e_));   \
+      return 1;                                                                          \
+    }                                                                                    \
+  } while (0)
+#define FS_LAUNCHED()                                                                    \
+  do {                                                                                   \
+    ++g_launches;                                                                        \
+    cudaError_t e_ = cudaPeekAtLastError();                                              \
+    if (e_ != cudaSuccess) {                                                             \
+      fs_set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
+      return 1;                                                                          \
+    }                                                                                    \
+  } while (0)
+
+static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }

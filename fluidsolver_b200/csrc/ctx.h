@@ -1,0 +1,64 @@
+// fluidsolver_b200/csrc/ctx.h -- host-side context of libfsgpu.so (internal).
+#pragma once
+
+#include "../../include/fsgpu.h"
+#include "common.cuh"
+
+struct BCondSide {
+  int kind    = FSGPU_BC_NEUMANN;
+  double u    = 0.0, v = 0.0;
+  int clipped = 0;
+  double* u_prof = nullptr;  // device, optional
+  double* v_prof = nullptr;
+};
+
+struct fsgpu_ctx {
+  Geom g{};
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  double rho_gas = 1, rho_liquid = 1, visc_gas = 1e-3, visc_liquid = 1e-3, sigma = 0;
+  double* slab = nullptr;              // one allocation for all fields
+  double* f[FSGPU_NUM_FIELDS] = {};    // field base pointers (padded layout)
+  double *U_alt = nullptr, *V_alt = nullptr;  // ping-pong targets of the fused momentum update
+  BCondSide bc[4];
+  // reduction scratch
+  double* part = nullptr;       // block partials
+  size_t part_cap = 0;          // doubles
+  unsigned int* ticket = nullptr;
+  double* red_out = nullptr;    // device result slots (8 doubles)
+  double* h_red = nullptr;      // pinned mirror
+};
+
+// field classes: extents of the ghost-inclusive reference array
+static inline void field_extent(const Geom& g, int field, int64_t* m, int64_t* n) {
+  switch (field) {
+    case FSGPU_P_JUMP_U: case FSGPU_RHO_U_OLD: case FSGPU_U_OLD: case FSGPU_RHO_U: case FSGPU_U:
+    case FSGPU_DMOM_U:
+      *m = g.nx + 3; *n = g.ny + 2; break;
+    case FSGPU_P_JUMP_V: case FSGPU_RHO_V_OLD: case FSGPU_V_OLD: case FSGPU_RHO_V: case FSGPU_V:
+    case FSGPU_DMOM_V:
+      *m = g.nx + 2; *n = g.ny + 3; break;
+    default:
+      *m = g.nx + 2; *n = g.ny + 2; break;
+  }
+}
+
+// ---- stencil.cu -------------------------------------------------------------------------------
+int fs_launch_mid_time(fsgpu_ctx* c);
+int fs_launch_dmomdt(fsgpu_ctx* c);
+int fs_launch_update_velocity(fsgpu_ctx* c, double dt);
+int fs_launch_momentum_update(fsgpu_ctx* c, double dt);
+int fs_launch_bconds(fsgpu_ctx* c);
+int fs_launch_outflow_fix(fsgpu_ctx* c, double* d_mass_error);
+int fs_launch_divergence(fsgpu_ctx* c);
+// rhs = -vol*div/dt (+ Dirichlet row zeroing); if psd == NONE the mean over all cells is
+// subtracted (two passes).  div_from_uv: compute div on the fly from U,V and store it too.
+int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv);
+int fs_launch_shift_pressure(fsgpu_ctx* c);
+int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift);
+int fs_launch_cfl(fsgpu_ctx* c);               // 4 maxima -> red_out[0..3]
+int fs_launch_absmax(fsgpu_ctx* c, int field);  // -> red_out[0]
+int fs_launch_fill(fsgpu_ctx* c, int field, double v);
+int fs_launch_rho_visc_vof(fsgpu_ctx* c);
+int fs_launch_neumann(fsgpu_ctx* c, double* f, int64_t m, int64_t n);
+int fs_ensure_part(fsgpu_ctx* c, size_t doubles);

@@ -1,0 +1,306 @@
+// fluidsolver_b200/csrc/project.cu -- divergence / rhs / projection / reductions.
+//
+//   k_divergence   calc_divergence               src/Operators.hpp:32-41 (all cells incl. ghosts)
+//   k_rhs          fill_pressure_rhs             src/LinearSystem.hpp:125-155
+//   k_sum          integrate<true>               src/Operators.hpp:52-62
+//   k_correct      shift_pressure_to_zero + p += dp + velocity correction
+//                                                src/Operators.hpp:78-82, scaling/LidDrivenFlow.cpp:153-160,
+//                                                test/LaminarChannel.cpp:222-233
+//   k_cfl          adjust_dt                     src/FS.hpp:100-128
+//   k_absmax       abs_max                       src/Utility.hpp:80-88
+//   k_rho_visc_vof calc_rho(vf,fs)/calc_visc(vf,fs)  src/FS.hpp:592-650
+#include "ctx.h"
+
+#include <math.h>
+
+#include <algorithm>
+
+namespace {
+
+constexpr int BX = 64, BY = 4;
+
+__device__ __forceinline__ double div_at(const double* __restrict__ U, const double* __restrict__ V,
+                                         int64_t k, int64_t P, double dx, double dy) {
+  return (__ldg(U + k + P) - __ldg(U + k)) / dx + (__ldg(V + k + 1) - __ldg(V + k)) / dy;
+}
+
+__global__ void __launch_bounds__(BX* BY)
+k_divergence(const double* __restrict__ U, const double* __restrict__ V, double* __restrict__ div,
+             const Geom g) {
+  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (a > g.nx + 1 || b > g.ny + 1) return;
+  const int64_t k = g.idx(a, b);
+  div[k] = div_at(U, V, k, g.pitch, g.dx, g.dy);
+}
+
+// rhs = -vol * div / dt on all cells; zero on the Dirichlet side; block partial sums of rhs.
+// FROM_UV: div is computed from U, V here (and stored) instead of being read.
+template <bool FROM_UV>
+__global__ void __launch_bounds__(BX* BY)
+k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __restrict__ div,
+      double* __restrict__ rhs, const Geom g, double dt, int psd, double* part,
+      unsigned int* ticket, double* out) {
+  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
+  double v[1] = {0.0};
+  if (a <= g.nx + 1 && b <= g.ny + 1) {
+    const int64_t k = g.idx(a, b);
+    double d;
+    if (FROM_UV) {
+      d      = div_at(U, V, k, g.pitch, g.dx, g.dy);
+      div[k] = d;
+    } else {
+      d = div[k];
+    }
+    const double vol = g.dx * g.dy;
+    double r         = -vol * d / dt;
+    if ((psd == FSGPU_PSD_LEFT && a == 0) || (psd == FSGPU_PSD_RIGHT && a == g.nx + 1) ||
+        (psd == FSGPU_PSD_BOTTOM && b == 0) || (psd == FSGPU_PSD_TOP && b == g.ny + 1))
+      r = 0.0;
+    rhs[k] = r;
+    v[0]   = r;
+  }
+  double tot[1];
+  if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
+    if (threadIdx.x == 0 && threadIdx.y == 0) out[0] = tot[0];
+  }
+}
+
+// f -= (*sum) * scale on all cells
+__global__ void __launch_bounds__(BX* BY)
+k_sub_scaled(double* __restrict__ f, const double* __restrict__ sum, double scale, const Geom g) {
+  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (a > g.nx + 1 || b > g.ny + 1) return;
+  f[g.idx(a, b)] -= __ldg(sum) * scale;
+}
+
+__global__ void __launch_bounds__(BX* BY)
+k_sum(const double* __restrict__ f, const Geom g, double* part, unsigned int* ticket, double* out) {
+  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
+  double v[1] = {0.0};
+  if (a <= g.nx + 1 && b <= g.ny + 1) v[0] = f[g.idx(a, b)];
+  double tot[1];
+  if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
+    if (threadIdx.x == 0 && threadIdx.y == 0) out[0] = tot[0];
+  }
+}
+
+// SHIFT: dp is used as (dp - c), c = (*sum) * dx * dy (shift_pressure_to_zero), and stored so.
+template <bool SHIFT>
+__global__ void __launch_bounds__(BX* BY)
+k_correct(double* __restrict__ dp, double* __restrict__ p, double* __restrict__ U,
+          double* __restrict__ V, const double* __restrict__ ru, const double* __restrict__ rv,
+          const double* __restrict__ sum, const Geom g, double dt) {
+  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (a > g.nx + 1 || b > g.ny + 1) return;
+  const int64_t k = g.idx(a, b), P = g.pitch;
+  const double c  = SHIFT ? __ldg(sum) * g.dx * g.dy : 0.0;
+  // neighbours are read un-shifted from global memory and shifted locally: no ordering hazard
+  // with the in-place store below because every thread only stores its own dp[k].
+  const double d0 = dp[k] - c;
+  // U(i,j) for i in [0,NX], j in [0,NY): a in [1,NX+1], b in [1,NY]
+  if (a >= 1 && b >= 1 && b <= g.ny) {
+    const double dm = __ldcg(dp + k - P) - c;
+    U[k] -= (d0 - dm) / g.dx * dt / __ldg(ru + k);
+  }
+  // V(i,j) for i in [0,NX), j in [0,NY]: a in [1,NX], b in [1,NY+1]
+  if (a >= 1 && a <= g.nx && b >= 1) {
+    const double dm = __ldcg(dp + k - 1) - c;
+    V[k] -= (d0 - dm) / g.dy * dt / __ldg(rv + k);
+  }
+  p[k] += d0;
+  (void)d0;
+}
+
+// in-place shift as its own pass (public fsgpu_shift_pressure_to_zero)
+// -> k_sub_scaled with scale dx*dy.
+
+__global__ void __launch_bounds__(BX* BY)
+k_cfl(const double* __restrict__ U, const double* __restrict__ V, const double* __restrict__ ru,
+      const double* __restrict__ rv, const double* __restrict__ mu, const Geom g, double* part,
+      unsigned int* ticket, double* out) {
+  const int64_t j = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t i = (int64_t)blockIdx.y * BY + threadIdx.y;
+  double v[4] = {0.0, 0.0, 0.0, 0.0};  // the reference's maxima start at 0 (FS.hpp:102-106)
+  if (i < g.nx && j < g.ny) {
+    const int64_t k = g.idx(i + 1, j + 1), P = g.pitch;
+    v[0] = (U[k] + U[k + P]) / 2 / g.dx;
+    v[1] = (V[k] + V[k + 1]) / 2 / g.dy;
+    const double rho = (ru[k] + ru[k + P] + rv[k] + rv[k + 1]) / 4.0;
+    v[2] = 4.0 * mu[k] / (g.dx * g.dx * rho);
+    v[3] = 4.0 * mu[k] / (g.dy * g.dy * rho);
+  }
+  double tot[4];
+  if (grid_reduce<ReduceMax, 4>(v, part, ticket, tot)) {
+    if (threadIdx.x == 0 && threadIdx.y == 0)
+      for (int q = 0; q < 4; ++q) out[q] = fmax(tot[q], 0.0);
+  }
+}
+
+__global__ void k_absmax(const double* __restrict__ f, int64_t n, double* part,
+                         unsigned int* ticket, double* out) {
+  double v[1] = {0.0};
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n;
+       k += (int64_t)gridDim.x * blockDim.x)
+    v[0] = fmax(v[0], fabs(f[k]));
+  double tot[1];
+  if (grid_reduce<ReduceMax, 1>(v, part, ticket, tot)) {
+    if (threadIdx.x == 0) out[0] = fmax(tot[0], 0.0);
+  }
+}
+
+// fill the (m+2) x (n+2) ghost-inclusive extent of a field
+__global__ void k_fill(double* __restrict__ f, int64_t m2, int64_t n2, double v, const Geom g) {
+  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (a >= m2 || b >= n2) return;
+  f[g.idx(a, b)] = v;
+}
+
+// FS.hpp:592-650: face densities are the mean of the two adjacent cell densities, viscosity is
+// the harmonic mix with the VF_LOW / VF_HIGH clamps of src/IR.hpp:16-17; interior only, the
+// caller applies apply_neumann_bconds to each.
+__global__ void __launch_bounds__(BX* BY)
+k_rho_visc_vof(const double* __restrict__ vf, double* __restrict__ ru, double* __restrict__ rv,
+               double* __restrict__ mu, const Geom g, double rg, double rl, double mg, double ml) {
+  const int64_t j = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t i = (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (i > g.nx || j > g.ny) return;
+  const int64_t k = g.idx(i + 1, j + 1), P = g.pitch;
+  const double f0 = vf[k];
+  const double r0 = f0 * rl + (1.0 - f0) * rg;
+  if (j < g.ny) {
+    const double fm = vf[k - P];
+    ru[k]           = ((fm * rl + (1.0 - fm) * rg) + r0) / 2.0;
+  }
+  if (i < g.nx) {
+    const double fm = vf[k - 1];
+    rv[k]           = ((fm * rl + (1.0 - fm) * rg) + r0) / 2.0;
+  }
+  if (i < g.nx && j < g.ny) {
+    const double VF_LOW = 1e-8, VF_HIGH = 1.0 - 1e-8;
+    double m;
+    if (f0 < VF_LOW) m = mg;
+    else if (f0 > VF_HIGH) m = ml;
+    else m = (ml * mg) / (ml * (1.0 - f0) + mg * f0);
+    mu[k] = m;
+  }
+}
+
+}  // namespace
+
+int fs_ensure_part(fsgpu_ctx* c, size_t doubles) {
+  if (doubles <= c->part_cap) return 0;
+  if (c->part) cudaFree(c->part);
+  c->part = nullptr;
+  FS_CUDA(cudaMalloc(&c->part, doubles * sizeof(double)));
+  c->part_cap = doubles;
+  return 0;
+}
+
+static dim3 cell_grid(const Geom& g) {
+  return dim3((unsigned)cdiv(g.ny + 2, BX), (unsigned)cdiv(g.nx + 2, BY));
+}
+static dim3 ext_grid(int64_t m2, int64_t n2) {
+  return dim3((unsigned)cdiv(n2, BX), (unsigned)cdiv(m2, BY));
+}
+
+int fs_launch_divergence(fsgpu_ctx* c) {
+  k_divergence<<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V],
+                                                                c->f[FSGPU_DIV], c->g);
+  FS_LAUNCHED();
+  return 0;
+}
+
+int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
+  const dim3 gr = cell_grid(c->g);
+  if (fs_ensure_part(c, (size_t)gr.x * gr.y * 4)) return 1;
+  if (div_from_uv)
+    k_rhs<true><<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
+                                                    c->f[FSGPU_RHS], c->g, dt, psd, c->part,
+                                                    c->ticket, c->red_out);
+  else
+    k_rhs<false><<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
+                                                     c->f[FSGPU_RHS], c->g, dt, psd, c->part,
+                                                     c->ticket, c->red_out);
+  FS_LAUNCHED();
+  if (psd == FSGPU_PSD_NONE) {  // subtract the arithmetic mean over all (NX+2)(NY+2) entries
+    const double inv_n = 1.0 / (double)((c->g.nx + 2) * (c->g.ny + 2));
+    k_sub_scaled<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_RHS], c->red_out, inv_n, c->g);
+    FS_LAUNCHED();
+  }
+  return 0;
+}
+
+static int launch_sum_dp(fsgpu_ctx* c) {
+  const dim3 gr = cell_grid(c->g);
+  if (fs_ensure_part(c, (size_t)gr.x * gr.y * 4)) return 1;
+  k_sum<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_DELTA_P], c->g, c->part, c->ticket,
+                                            c->red_out + 1);
+  FS_LAUNCHED();
+  return 0;
+}
+
+int fs_launch_shift_pressure(fsgpu_ctx* c) {
+  if (launch_sum_dp(c)) return 1;
+  k_sub_scaled<<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_DELTA_P], c->red_out + 1,
+                                                                c->g.dx * c->g.dy, c->g);
+  FS_LAUNCHED();
+  return 0;
+}
+
+int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift) {
+  if (fuse_shift) {
+    // a shifted dp is needed by every thread's neighbours too, so the shift cannot be stored
+    // in place inside the same pass: shift first (in place), then correct.
+    if (fs_launch_shift_pressure(c)) return 1;
+  }
+  k_correct<false><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
+      c->f[FSGPU_DELTA_P], c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
+      c->f[FSGPU_RHO_V], c->red_out + 1, c->g, dt);
+  FS_LAUNCHED();
+  return 0;
+}
+
+int fs_launch_cfl(fsgpu_ctx* c) {
+  const dim3 gr((unsigned)cdiv(c->g.ny, BX), (unsigned)cdiv(c->g.nx, BY));
+  if (fs_ensure_part(c, (size_t)gr.x * gr.y * 4)) return 1;
+  k_cfl<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
+                                            c->f[FSGPU_RHO_V], c->f[FSGPU_VISC], c->g, c->part,
+                                            c->ticket, c->red_out);
+  FS_LAUNCHED();
+  return 0;
+}
+
+int fs_launch_absmax(fsgpu_ctx* c, int field) {
+  const int64_t n    = c->g.count();
+  const unsigned nbl = (unsigned)std::min<int64_t>(cdiv(n, 256), 148 * 8);
+  if (fs_ensure_part(c, (size_t)nbl * 4)) return 1;
+  k_absmax<<<nbl, 256, 0, c->stream>>>(c->f[field], n, c->part, c->ticket, c->red_out);
+  FS_LAUNCHED();
+  return 0;
+}
+
+int fs_launch_fill(fsgpu_ctx* c, int field, double v) {
+  int64_t m, n;
+  field_extent(c->g, field, &m, &n);
+  k_fill<<<ext_grid(m, n), dim3(BX, BY), 0, c->stream>>>(c->f[field], m, n, v, c->g);
+  FS_LAUNCHED();
+  return 0;
+}
+
+int fs_launch_rho_visc_vof(fsgpu_ctx* c) {
+  k_rho_visc_vof<<<dim3((unsigned)cdiv(c->g.ny + 1, BX), (unsigned)cdiv(c->g.nx + 1, BY)),
+                   dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_VF], c->f[FSGPU_RHO_U], c->f[FSGPU_RHO_V],
+                                                 c->f[FSGPU_VISC], c->g, c->rho_gas, c->rho_liquid,
+                                                 c->visc_gas, c->visc_liquid);
+  FS_LAUNCHED();
+  if (fs_launch_neumann(c, c->f[FSGPU_RHO_U], c->g.nx + 1, c->g.ny)) return 1;
+  if (fs_launch_neumann(c, c->f[FSGPU_RHO_V], c->g.nx, c->g.ny + 1)) return 1;
+  if (fs_launch_neumann(c, c->f[FSGPU_VISC], c->g.nx, c->g.ny)) return 1;
+  return 0;
+}

@@ -1,0 +1,189 @@
+// fluidsolver_b200/csrc/solver_pcg.cu -- preconditioned conjugate gradients on the device.
+//
+// hypre_PCGSolve (Submodules/hypre/src/krylov/pcg.c:328-1027) with the settings of
+// src/LinearSolver_StructHypre.hpp:332-338 (two_norm 0, rel_change 0, a_tol 0, zero guess):
+//   p = C b; bi = <p, b>;  r = b;  gamma = bi
+//   loop: s = A p; alpha = gamma / <s,p>; x += alpha p; r -= alpha s; s = C r; gamma' = <r,s>;
+//         stop if gamma'/bi < tol^2; beta = gamma'/gamma; p = s + beta p
+// (HYPRE evaluates C r a second time before the loop; with x0 = 0 that equals C b bit for bit,
+// so it is computed once here.)
+//
+// All recurrence scalars live in device memory (PcgScal); dot products are deterministic
+// two-stage reductions whose last block updates the scalars, so an iteration needs no host
+// round trip.  The host runs FS_LAG iterations ahead and reads the `done` flag through pinned
+// memory; kernels of iterations enqueued past convergence return immediately.
+#include "solver.h"
+
+#include <math.h>
+
+#define FS_LAG 1
+
+namespace {
+
+constexpr int BX = 64, BY = 4;
+
+// s = A p and <s, p>;  last block: alpha = gamma / <s,p> with HYPRE's breakdown exits
+__global__ void __launch_bounds__(BX* BY)
+k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict__ s, PcgScal* scal,
+             double* part, unsigned int* ticket) {
+  if (scal->done) return;
+  const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
+  double v[1] = {0.0};
+  if (li < L.n0 && lj < L.n1) {
+    const int64_t k = L.idx(li, lj), P = L.pitch;
+    const double pk = __ldg(p + k);
+    double a = __ldg(L.d + k) * pk;
+    a += __ldg(L.cx + k) * __ldg(p + k - P);
+    a += __ldg(L.cx + k + P) * __ldg(p + k + P);
+    a += __ldg(L.cy + k) * __ldg(p + k - 1);
+    a += __ldg(L.cy + k + 1) * __ldg(p + k + 1);
+    s[k] = a;
+    v[0] = a * pk;
+  }
+  double tot[1];
+  if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+      scal->iter += 1;
+      scal->sdotp = tot[0];
+      if (tot[0] == 0.0) {  // pcg.c:760-775
+        if (scal->iter == 1) scal->iprod = scal->gamma;
+        scal->done = PCG_BREAKDOWN;
+      } else {
+        const double alpha = scal->gamma / tot[0];
+        scal->alpha = alpha;
+        if (alpha <= 0.0) {  // pcg.c:777-790
+          if (scal->iter == 1) scal->iprod = scal->gamma;
+          scal->done = PCG_BREAKDOWN;
+        }
+      }
+    }
+  }
+}
+
+// x += alpha p; r -= alpha s
+__global__ void __launch_bounds__(BX* BY)
+k_xr_update(const LevelDev L, double* __restrict__ x, double* __restrict__ r,
+            const double* __restrict__ p, const double* __restrict__ s, const PcgScal* scal) {
+  if (scal->done) return;
+  const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (li >= L.n0 || lj >= L.n1) return;
+  const int64_t k = L.idx(li, lj);
+  const double alpha = scal->alpha;
+  x[k] += alpha * p[k];
+  r[k] -= alpha * s[k];
+}
+
+// gamma' = <r, z>.  INIT: this is bi = <C b, b>; otherwise the convergence test + beta.
+template <bool INIT>
+__global__ void __launch_bounds__(BX* BY)
+k_dot_rz(const LevelDev L, const double* __restrict__ r, const double* __restrict__ z, PcgScal* scal,
+         double* part, unsigned int* ticket) {
+  if (scal->done) return;
+  const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
+  double v[1] = {0.0};
+  if (li < L.n0 && lj < L.n1) {
+    const int64_t k = L.idx(li, lj);
+    v[0] = r[k] * z[k];
+  }
+  double tot[1];
+  if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+      const double g = tot[0];
+      if (INIT) {
+        scal->bi    = g;
+        scal->gamma = g;
+        scal->iprod = 0.0;
+        scal->beta  = 0.0;
+        if (!(g > 0.0)) scal->done = PCG_ZERO_RHS;  // pcg.c:473-488
+      } else {
+        scal->iprod = g;
+        if (g / scal->bi < scal->eps) scal->done = PCG_CONVERGED;  // pcg.c:816
+        else if (g <= 0.0) scal->done = PCG_BREAKDOWN;
+        else {
+          scal->beta  = g / scal->gamma;
+          scal->gamma = g;
+        }
+      }
+    }
+  }
+}
+
+// p = z + beta p   (FIRST: p = z)
+template <bool FIRST>
+__global__ void __launch_bounds__(BX* BY)
+k_p_update(const LevelDev L, double* __restrict__ p, const double* __restrict__ z,
+           const PcgScal* scal) {
+  if (scal->done) return;
+  const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (li >= L.n0 || lj >= L.n1) return;
+  const int64_t k = L.idx(li, lj);
+  if (FIRST) p[k] = z[k];
+  else p[k] = z[k] + scal->beta * p[k];
+}
+
+__global__ void k_scal_init(PcgScal* scal, double eps) {
+  scal->gamma = scal->sdotp = scal->alpha = scal->beta = scal->bi = scal->iprod = 0.0;
+  scal->eps   = eps;
+  scal->iter  = 0;
+  scal->done  = PCG_RUNNING;
+  scal->first = 1;
+}
+
+}  // namespace
+
+int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
+  fsgpu_ctx* c    = s->c;
+  cudaStream_t st = c->stream;
+  const LevelDev& L0 = s->L[0].v;
+  const dim3 gr((unsigned)cdiv(L0.n1, BX), (unsigned)cdiv(L0.n0, BY)), bl(BX, BY);
+  if (fs_ensure_part(c, (size_t)gr.x * gr.y * 4)) return 1;
+  double* x = c->f[FSGPU_DELTA_P];
+  double* r = c->f[FSGPU_RHS];  // r = b - A 0 = b: the rhs buffer becomes the residual
+  k_scal_init<<<1, 1, 0, st>>>(s->scal, s->o.tol * s->o.tol);
+  FS_LAUNCHED();
+  FS_CUDA(cudaMemsetAsync(x, 0, (size_t)c->g.count() * sizeof(double), st));
+  if (ps_vcycle(s, r, s->z)) return 1;
+  k_dot_rz<true><<<gr, bl, 0, st>>>(L0, r, s->z, s->scal, c->part, c->ticket);
+  FS_LAUNCHED();
+  k_p_update<true><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);
+  FS_LAUNCHED();
+  const int nslot = FS_LAG + 1;
+  int launched = 0;
+  bool stop = false;
+  for (int it = 1; it <= s->o.max_iter && !stop; ++it) {
+    k_matvec_dot<<<gr, bl, 0, st>>>(L0, s->p, s->s, s->scal, c->part, c->ticket);
+    FS_LAUNCHED();
+    k_xr_update<<<gr, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal);
+    FS_LAUNCHED();
+    if (ps_vcycle(s, r, s->z)) return 1;
+    k_dot_rz<false><<<gr, bl, 0, st>>>(L0, r, s->z, s->scal, c->part, c->ticket);
+    FS_LAUNCHED();
+    k_p_update<false><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);
+    FS_LAUNCHED();
+    const int slot = it % nslot;
+    FS_CUDA(cudaMemcpyAsync(&s->h_scal[slot], s->scal, sizeof(PcgScal), cudaMemcpyDeviceToHost, st));
+    FS_CUDA(cudaEventRecord(s->ev[slot], st));
+    launched = it;
+    if (it > FS_LAG) {  // look at the state FS_LAG iterations back while this one runs
+      const int ps = (it - FS_LAG) % nslot;
+      FS_CUDA(cudaEventSynchronize(s->ev[ps]));
+      if (s->h_scal[ps].done) stop = true;
+    }
+  }
+  (void)launched;
+  FS_CUDA(cudaMemcpyAsync(&s->h_scal[0], s->scal, sizeof(PcgScal), cudaMemcpyDeviceToHost, st));
+  FS_CUDA(cudaStreamSynchronize(st));
+  const PcgScal& h = s->h_scal[0];
+  if (h.done == PCG_ZERO_RHS) {
+    if (residual) *residual = 0.0;
+    if (iters) *iters = 0;
+    return 0;
+  }
+  if (residual) *residual = sqrt(h.iprod / h.bi);  // pcg.c:1016
+  if (iters) *iters = h.iter;
+  return 0;
+}

@@ -1,0 +1,300 @@
+"""ctypes binding of libfsgpu.so: the reference's call surface (src/FS.hpp, src/Operators.hpp,
+src/BoundaryConditions.hpp, src/LinearSolver_StructHypre.hpp) over the C ABI of include/fsgpu.h.
+
+Method names and argument meaning follow the reference functions they stand for; host arrays are
+numpy float64 in the reference's storage (ghost inclusive, j fastest).  The product path never
+touches oracle/ and has no CPU fallback: if libfsgpu.so is missing or no CUDA device is present
+the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libfsgpu.so")
+
+FIELDS = ("VISC", "P", "P_JUMP_U", "P_JUMP_V", "RHO_U_OLD", "RHO_V_OLD", "U_OLD", "V_OLD", "RHO_U",
+          "RHO_V", "U", "V", "DMOM_U", "DMOM_V", "DIV", "DELTA_P", "VF", "RHS")
+FIELD_ID = {n: i for i, n in enumerate(FIELDS)}
+U_LIKE = {"P_JUMP_U", "RHO_U_OLD", "U_OLD", "RHO_U", "U", "DMOM_U"}
+V_LIKE = {"P_JUMP_V", "RHO_V_OLD", "V_OLD", "RHO_V", "V", "DMOM_V"}
+
+DIRICHLET, NEUMANN, PERIODIC, SYMMETRY = 0, 1, 2, 3
+LEFT, RIGHT, BOTTOM, TOP = 0, 1, 2, 3
+PSD_NONE, PSD_LEFT, PSD_RIGHT, PSD_BOTTOM, PSD_TOP = 0, 1, 2, 3, 4
+RELAX_JACOBI, RELAX_RBGS = 1, 2
+STEP_OUTFLOW_FIX, STEP_REBUILD_OPERATOR = 1, 2
+
+DP = C.POINTER(C.c_double)
+
+# every symbol include/fsgpu.h declares (tests check the library exports all of them)
+SYMBOLS = (
+    "fsgpu_last_error", "fsgpu_launch_count", "fsgpu_device_count", "fsgpu_create", "fsgpu_destroy",
+    "fsgpu_set_props", "fsgpu_upload", "fsgpu_download", "fsgpu_fill", "fsgpu_sync",
+    "fsgpu_device_field", "fsgpu_stream", "fsgpu_set_bconds", "fsgpu_adjust_dt",
+    "fsgpu_save_old_state", "fsgpu_save_old_velocity", "fsgpu_save_old_density",
+    "fsgpu_calc_mid_time", "fsgpu_calc_dmomdt", "fsgpu_update_velocity", "fsgpu_momentum_update",
+    "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_calc_divergence",
+    "fsgpu_shift_pressure_to_zero", "fsgpu_correct_velocity", "fsgpu_abs_max",
+    "fsgpu_calc_rho_visc_const", "fsgpu_calc_rho_visc_vof", "fsgpu_apply_neumann_bconds",
+    "fsgpu_ps_create", "fsgpu_ps_destroy", "fsgpu_ps_set_operator", "fsgpu_ps_set_rhs",
+    "fsgpu_ps_solve", "fsgpu_ps_num_levels", "fsgpu_substep", "fsgpu_step",
+)
+
+
+class PsOpts(C.Structure):
+    _fields_ = [("tol", C.c_double), ("max_iter", C.c_int), ("psd", C.c_int), ("relax", C.c_int),
+                ("max_levels", C.c_int), ("skip_relax", C.c_int)]
+
+
+class FsgpuError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """dlopen libfsgpu.so (built by fluidsolver_b200.build); raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FsgpuError(f"{LIB_PATH} not built: run `python -m fluidsolver_b200.build` "
+                         "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, i64, dbl, i32 = C.c_void_p, C.c_int64, C.c_double, C.c_int
+    L.fsgpu_last_error.restype = C.c_char_p
+    L.fsgpu_launch_count.restype = i64
+    L.fsgpu_device_count.argtypes = [C.POINTER(i32)]
+    L.fsgpu_create.argtypes = [i64, i64, dbl, dbl, i32, C.POINTER(vp)]
+    L.fsgpu_set_props.argtypes = [vp, dbl, dbl, dbl, dbl, dbl]
+    L.fsgpu_upload.argtypes = [vp, i32, DP]
+    L.fsgpu_download.argtypes = [vp, i32, DP]
+    L.fsgpu_fill.argtypes = [vp, i32, dbl]
+    L.fsgpu_device_field.argtypes = [vp, i32, C.POINTER(DP), C.POINTER(i64), C.POINTER(i64),
+                                     C.POINTER(i64)]
+    L.fsgpu_stream.argtypes = [vp, C.POINTER(vp)]
+    L.fsgpu_set_bconds.argtypes = [vp, i32, i32, dbl, dbl, DP, DP, i32]
+    L.fsgpu_adjust_dt.argtypes = [vp, dbl, dbl, DP]
+    for n in ("destroy", "sync", "save_old_state", "save_old_velocity", "save_old_density",
+              "calc_mid_time", "calc_dmomdt", "apply_velocity_bconds", "calc_divergence",
+              "shift_pressure_to_zero", "calc_rho_visc_const", "calc_rho_visc_vof"):
+        getattr(L, "fsgpu_" + n).argtypes = [vp]
+    for n in ("update_velocity", "momentum_update", "correct_velocity"):
+        getattr(L, "fsgpu_" + n).argtypes = [vp, dbl]
+    L.fsgpu_outflow_fix.argtypes = [vp, DP]
+    L.fsgpu_abs_max.argtypes = [vp, i32, DP]
+    L.fsgpu_apply_neumann_bconds.argtypes = [vp, i32]
+    L.fsgpu_ps_create.argtypes = [vp, C.POINTER(PsOpts), C.POINTER(vp)]
+    L.fsgpu_ps_destroy.argtypes = [vp]
+    L.fsgpu_ps_set_operator.argtypes = [vp]
+    L.fsgpu_ps_set_rhs.argtypes = [vp, dbl]
+    L.fsgpu_ps_solve.argtypes = [vp, DP, C.POINTER(i32)]
+    L.fsgpu_ps_num_levels.argtypes = [vp, C.POINTER(i32)]
+    L.fsgpu_substep.argtypes = [vp, vp, dbl, i32, DP, C.POINTER(i32)]
+    L.fsgpu_step.argtypes = [vp, vp, dbl, i32, i32, DP, C.POINTER(i32)]
+    _lib = L
+    return L
+
+
+def _chk(rc):
+    if rc != 0:
+        raise FsgpuError(load().fsgpu_last_error().decode())
+
+
+def launch_count() -> int:
+    return int(load().fsgpu_launch_count())
+
+
+def device_count() -> int:
+    n = C.c_int(0)
+    _chk(load().fsgpu_device_count(C.byref(n)))
+    return n.value
+
+
+def field_shape(name: str, nx: int, ny: int):
+    if name in U_LIKE:
+        return (nx + 3, ny + 2)
+    if name in V_LIKE:
+        return (nx + 2, ny + 3)
+    return (nx + 2, ny + 2)
+
+
+class FS:
+    """The reference's ``FS<Float,NX,NY,1>`` (src/FS.hpp:28-52) resident on one B200."""
+
+    def __init__(self, nx, ny, dx, dy, rho_gas=1.0, rho_liquid=1.0, visc_gas=1e-3, visc_liquid=1e-3,
+                 sigma=0.0, device=0):
+        self.L = load()
+        self.nx, self.ny, self.dx, self.dy = int(nx), int(ny), float(dx), float(dy)
+        self.h = C.c_void_p()
+        _chk(self.L.fsgpu_create(self.nx, self.ny, self.dx, self.dy, device, C.byref(self.h)))
+        self.set_props(rho_gas, rho_liquid, visc_gas, visc_liquid, sigma)
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.L.fsgpu_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_props(self, rho_gas, rho_liquid, visc_gas, visc_liquid, sigma=0.0):
+        self.rho_gas, self.rho_liquid = rho_gas, rho_liquid
+        self.visc_gas, self.visc_liquid, self.sigma = visc_gas, visc_liquid, sigma
+        _chk(self.L.fsgpu_set_props(self.h, rho_gas, rho_liquid, visc_gas, visc_liquid, sigma))
+
+    # ---- Field2D::get_data() ------------------------------------------------------------------
+    def upload(self, name, arr):
+        a = np.ascontiguousarray(arr, dtype=np.float64)
+        assert a.shape == field_shape(name, self.nx, self.ny), (name, a.shape)
+        _chk(self.L.fsgpu_upload(self.h, FIELD_ID[name], a.ctypes.data_as(DP)))
+
+    def download(self, name, out=None):
+        a = out if out is not None else np.empty(field_shape(name, self.nx, self.ny))
+        _chk(self.L.fsgpu_download(self.h, FIELD_ID[name], a.ctypes.data_as(DP)))
+        return a
+
+    def fill(self, name, value):
+        _chk(self.L.fsgpu_fill(self.h, FIELD_ID[name], value))
+
+    def sync(self):
+        _chk(self.L.fsgpu_sync(self.h))
+
+    def stream(self) -> int:
+        s = C.c_void_p()
+        _chk(self.L.fsgpu_stream(self.h, C.byref(s)))
+        return s.value or 0
+
+    def device_field(self, name):
+        p, pitch, r0, c0 = DP(), C.c_int64(), C.c_int64(), C.c_int64()
+        _chk(self.L.fsgpu_device_field(self.h, FIELD_ID[name], C.byref(p), C.byref(pitch),
+                                       C.byref(r0), C.byref(c0)))
+        return C.cast(p, C.c_void_p).value, pitch.value, r0.value, c0.value
+
+    # ---- FlowBConds ---------------------------------------------------------------------------
+    def set_bconds(self, side, kind, u=0.0, v=0.0, u_prof=None, v_prof=None, clipped=False):
+        up = vp = None
+        if u_prof is not None:
+            u_prof = np.ascontiguousarray(u_prof, dtype=np.float64)
+            up = u_prof.ctypes.data_as(DP)
+        if v_prof is not None:
+            v_prof = np.ascontiguousarray(v_prof, dtype=np.float64)
+            vp = v_prof.ctypes.data_as(DP)
+        _chk(self.L.fsgpu_set_bconds(self.h, side, kind, u, v, up, vp, int(clipped)))
+
+    # ---- the reference's free functions -------------------------------------------------------
+    def adjust_dt(self, cfl_max, dt_max):
+        dt = C.c_double()
+        _chk(self.L.fsgpu_adjust_dt(self.h, cfl_max, dt_max, C.byref(dt)))
+        return dt.value
+
+    def save_old_state(self):
+        _chk(self.L.fsgpu_save_old_state(self.h))
+
+    def save_old_velocity(self):
+        _chk(self.L.fsgpu_save_old_velocity(self.h))
+
+    def save_old_density(self):
+        _chk(self.L.fsgpu_save_old_density(self.h))
+
+    def calc_mid_time(self):
+        _chk(self.L.fsgpu_calc_mid_time(self.h))
+
+    def calc_dmomdt(self):
+        _chk(self.L.fsgpu_calc_dmomdt(self.h))
+
+    def update_velocity(self, dt):
+        _chk(self.L.fsgpu_update_velocity(self.h, dt))
+
+    def momentum_update(self, dt):
+        _chk(self.L.fsgpu_momentum_update(self.h, dt))
+
+    def apply_velocity_bconds(self):
+        _chk(self.L.fsgpu_apply_velocity_bconds(self.h))
+
+    def outflow_fix(self, want_error=True):
+        e = C.c_double()
+        _chk(self.L.fsgpu_outflow_fix(self.h, C.byref(e) if want_error else None))
+        return e.value
+
+    def calc_divergence(self):
+        _chk(self.L.fsgpu_calc_divergence(self.h))
+
+    def shift_pressure_to_zero(self):
+        _chk(self.L.fsgpu_shift_pressure_to_zero(self.h))
+
+    def correct_velocity(self, dt):
+        _chk(self.L.fsgpu_correct_velocity(self.h, dt))
+
+    def abs_max(self, name):
+        o = C.c_double()
+        _chk(self.L.fsgpu_abs_max(self.h, FIELD_ID[name], C.byref(o)))
+        return o.value
+
+    def calc_rho_visc_const(self):
+        _chk(self.L.fsgpu_calc_rho_visc_const(self.h))
+
+    def calc_rho_visc_vof(self):
+        _chk(self.L.fsgpu_calc_rho_visc_vof(self.h))
+
+    def apply_neumann_bconds(self, name):
+        _chk(self.L.fsgpu_apply_neumann_bconds(self.h, FIELD_ID[name]))
+
+    # ---- fused path ---------------------------------------------------------------------------
+    def substep(self, ps, dt, flags=0):
+        res, it = C.c_double(), C.c_int()
+        _chk(self.L.fsgpu_substep(self.h, ps.h, dt, flags, C.byref(res), C.byref(it)))
+        return res.value, it.value
+
+    def step(self, ps, dt, num_subiter, flags=0):
+        res, it = C.c_double(), C.c_int()
+        _chk(self.L.fsgpu_step(self.h, ps.h, dt, num_subiter, flags, C.byref(res), C.byref(it)))
+        return res.value, it.value
+
+
+class LinearSolver:
+    """``LinearSolver_StructHypre<Float,NX,NY,1>`` (src/LinearSolver_StructHypre.hpp:28-192)."""
+
+    def __init__(self, fs: FS, tol=1e-6, max_iter=50, psd=PSD_NONE, relax=0, max_levels=0,
+                 skip_relax=-1):
+        self.fs, self.L = fs, fs.L
+        self.h = C.c_void_p()
+        o = PsOpts(tol, max_iter, psd, relax, max_levels, skip_relax)
+        _chk(self.L.fsgpu_ps_create(fs.h, C.byref(o), C.byref(self.h)))
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.L.fsgpu_ps_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_pressure_operator(self):
+        _chk(self.L.fsgpu_ps_set_operator(self.h))
+
+    def set_pressure_rhs(self, dt):
+        _chk(self.L.fsgpu_ps_set_rhs(self.h, dt))
+
+    def solve(self):
+        """-> (residual, num_iter); the solution is field DELTA_P"""
+        res, it = C.c_double(), C.c_int()
+        _chk(self.L.fsgpu_ps_solve(self.h, C.byref(res), C.byref(it)))
+        return res.value, it.value
+
+    @property
+    def num_levels(self):
+        n = C.c_int()
+        _chk(self.L.fsgpu_ps_num_levels(self.h, C.byref(n)))
+        return n.value

@@ -1,0 +1,180 @@
+/* include/fsgpu.h -- C ABI of libfsgpu.so, the B200 (sm_100a) implementation of the per-timestep
+ * stepping path of gidonbauer/FluidSolver.
+ *
+ * The reference has no FFI layer: its "API" is C++ function templates over an `FS` object
+ * (src/FS.hpp, src/Operators.hpp, src/BoundaryConditions.hpp, src/LinearSolver_StructHypre.hpp).
+ * Every entry point below replaces exactly one of those calls and cites it; the header-only C++
+ * shim under include/shim/ re-creates the reference's template signatures on top of this ABI, so
+ * a reference driver (test/TaylorGreenVortex.cpp, scaling/LidDrivenFlow.cpp, ...) switches by
+ * changing its include path.
+ *
+ * Conventions
+ *  - plain C, pointers and sizes only; every function returns 0 on success, non-zero on error
+ *    (fsgpu_last_error() gives the message).  There is NO CPU fallback: without a CUDA device
+ *    fsgpu_create fails.
+ *  - host arrays are in the reference's storage (src/Container.hpp:105-111, Layout::C, NGHOST=1):
+ *    ghost inclusive, j fastest.  U-like fields (NX+3)x(NY+2), V-like (NX+2)x(NY+3), cell fields
+ *    (NX+2)x(NY+2).  The device keeps its own padded layout (DESIGN.md "Data layout").
+ *  - one host thread per context (as the reference: single caller thread, parallelism inside).
+ *    All device work of a context is ordered on one CUDA stream; calls that return a scalar
+ *    synchronise, the others are asynchronous.
+ */
+#ifndef FSGPU_H_
+#define FSGPU_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fsgpu_ctx fsgpu_ctx;
+typedef struct fsgpu_ps fsgpu_ps;
+
+/* ---- field ids: the members of the reference's `FS` / `State` (src/FS.hpp:15-52) plus the
+ * scratch fields the drivers own (scaling/LidDrivenFlow.cpp:63-70) ------------------------------ */
+enum {
+  FSGPU_VISC = 0,      /* fs.visc            cell   */
+  FSGPU_P,             /* fs.p               cell   */
+  FSGPU_P_JUMP_U,      /* fs.p_jump_u_stag   U-like */
+  FSGPU_P_JUMP_V,      /* fs.p_jump_v_stag   V-like */
+  FSGPU_RHO_U_OLD,     /* fs.old.rho_u_stag  U-like */
+  FSGPU_RHO_V_OLD,     /* fs.old.rho_v_stag  V-like */
+  FSGPU_U_OLD,         /* fs.old.U           U-like */
+  FSGPU_V_OLD,         /* fs.old.V           V-like */
+  FSGPU_RHO_U,         /* fs.curr.rho_u_stag U-like */
+  FSGPU_RHO_V,         /* fs.curr.rho_v_stag V-like */
+  FSGPU_U,             /* fs.curr.U          U-like */
+  FSGPU_V,             /* fs.curr.V          V-like */
+  FSGPU_DMOM_U,        /* drhoUdt            U-like */
+  FSGPU_DMOM_V,        /* drhoVdt            V-like */
+  FSGPU_DIV,           /* div                cell   */
+  FSGPU_DELTA_P,       /* delta_p            cell   */
+  FSGPU_VF,            /* volume fraction    cell   */
+  FSGPU_RHS,           /* pressure rhs, (NX+2)x(NY+2) in Layout::C (the reference keeps it in
+                          Layout::F, src/LinearSystem.hpp:18-24; transpose to compare) */
+  FSGPU_NUM_FIELDS
+};
+
+/* src/BoundaryConditions.hpp:14-200 */
+enum { FSGPU_BC_DIRICHLET = 0, FSGPU_BC_NEUMANN = 1, FSGPU_BC_PERIODIC = 2, FSGPU_BC_SYMMETRY = 3 };
+/* order of application in apply_velocity_bconds, src/BoundaryConditions.hpp:220-223 */
+enum { FSGPU_LEFT = 0, FSGPU_RIGHT = 1, FSGPU_BOTTOM = 2, FSGPU_TOP = 3 };
+/* PSDirichlet, src/LinearSystem.hpp:10 */
+enum { FSGPU_PSD_NONE = 0, FSGPU_PSD_LEFT = 1, FSGPU_PSD_RIGHT = 2, FSGPU_PSD_BOTTOM = 3, FSGPU_PSD_TOP = 4 };
+/* smoother of the multigrid preconditioner */
+enum {
+  FSGPU_RELAX_JACOBI = 1, /* weighted Jacobi: what the reference gets from HYPRE's defaults
+                             (Submodules/hypre/src/struct_ls/pfmg.c:32) */
+  FSGPU_RELAX_RBGS = 2    /* symmetric red/black Gauss-Seidel (struct_ls/red_black_gs.c) */
+};
+
+const char* fsgpu_last_error(void);
+/* number of CUDA kernels launched by this library since load (bench.py's gpu_launches) */
+int64_t fsgpu_launch_count(void);
+int fsgpu_device_count(int* n);
+
+/* ---- context = the reference's `FS<Float,NX,NY,1>` object (src/FS.hpp:28-52) on one device ---- */
+/* replaces: `FS<Float,NX,NY,NGHOST> fs{...}; init_grid(...)` (src/FS.hpp:55-73) */
+int fsgpu_create(int64_t nx, int64_t ny, double dx, double dy, int device, fsgpu_ctx** out);
+int fsgpu_destroy(fsgpu_ctx* c);
+/* fs.rho_gas, fs.rho_liquid, fs.visc_gas, fs.visc_liquid, fs.sigma (src/FS.hpp:29-33) */
+int fsgpu_set_props(fsgpu_ctx* c, double rho_gas, double rho_liquid, double visc_gas,
+                    double visc_liquid, double sigma);
+/* Field2D::get_data() access (src/Container.hpp:150-155): whole field incl. ghosts */
+int fsgpu_upload(fsgpu_ctx* c, int field, const double* host);
+int fsgpu_download(fsgpu_ctx* c, int field, double* host);
+int fsgpu_fill(fsgpu_ctx* c, int field, double value); /* fill(), src/Container.hpp:172-180 */
+int fsgpu_sync(fsgpu_ctx* c);
+/* raw device pointer + layout of a field, for zero-copy interop (torch tensors, other kernels):
+ * element (i, j) of the reference lives at ptr[(i + 1 + row0) * pitch + (j + 1 + col0)] */
+int fsgpu_device_field(fsgpu_ctx* c, int field, double** ptr, int64_t* pitch, int64_t* row0,
+                       int64_t* col0);
+int fsgpu_stream(fsgpu_ctx* c, void** cuda_stream);
+
+/* FlowBConds (src/BoundaryConditions.hpp:207-212): one call per side.  u_prof / v_prof are the
+ * function-pointer Dirichlet variant (src/BoundaryConditions.hpp:15-17) evaluated by the caller
+ * at the ghost-inclusive coordinates of that side (NULL = constant u_val / v_val):
+ * left/right: u_prof NY+2 values (j=-1..NY), v_prof NY+3 (j=-1..NY+1);
+ * bottom/top: u_prof NX+3 values (i=-1..NX+1), v_prof NX+2 (i=-1..NX). */
+int fsgpu_set_bconds(fsgpu_ctx* c, int side, int kind, double u_val, double v_val,
+                     const double* u_prof, const double* v_prof, int clipped);
+
+/* adjust_dt, src/FS.hpp:100-128 */
+int fsgpu_adjust_dt(fsgpu_ctx* c, double cfl_max, double dt_max, double* dt);
+/* save_old_state / save_old_velocity / save_old_density, src/FS.hpp:76-97 */
+int fsgpu_save_old_state(fsgpu_ctx* c);
+int fsgpu_save_old_velocity(fsgpu_ctx* c);
+int fsgpu_save_old_density(fsgpu_ctx* c);
+/* calc_mid_time(curr.U, old.U); calc_mid_time(curr.V, old.V), src/Operators.hpp:44-49 */
+int fsgpu_calc_mid_time(fsgpu_ctx* c);
+/* calc_dmomdt(fs, drhoUdt, drhoVdt), src/FS.hpp:158-315 -> FSGPU_DMOM_U / FSGPU_DMOM_V */
+int fsgpu_calc_dmomdt(fsgpu_ctx* c);
+/* update_velocity(drhoUdt, drhoVdt, dt, fs), src/FS.hpp:423-436 */
+int fsgpu_update_velocity(fsgpu_ctx* c, double dt);
+/* the three calls above in one kernel (the pattern of bench/update-velo-fuse.cpp:57-164):
+ * mid-time average, fluxes and velocity update in one pass over the fields */
+int fsgpu_momentum_update(fsgpu_ctx* c, double dt);
+/* apply_velocity_bconds(fs, bconds, t), src/BoundaryConditions.hpp:215-224 */
+int fsgpu_apply_velocity_bconds(fsgpu_ctx* c);
+/* driver-level outflow correction of the channel cases, test/LaminarChannel.cpp:55-66,201-205;
+ * mass_error (may be NULL) receives outflow - inflow before the fix */
+int fsgpu_outflow_fix(fsgpu_ctx* c, double* mass_error);
+/* calc_divergence(curr.U, curr.V, dx, dy, div), src/Operators.hpp:32-41 -> FSGPU_DIV */
+int fsgpu_calc_divergence(fsgpu_ctx* c);
+/* shift_pressure_to_zero(dx, dy, delta_p), src/Operators.hpp:78-82 (on FSGPU_DELTA_P) */
+int fsgpu_shift_pressure_to_zero(fsgpu_ctx* c);
+/* the driver-inlined projection, scaling/LidDrivenFlow.cpp:153-160 and, for variable density,
+ * test/LaminarChannel.cpp:222-233: p += delta_p; U,V -= grad(delta_p)*dt/rho on interior faces */
+int fsgpu_correct_velocity(fsgpu_ctx* c, double dt);
+/* abs_max(field), src/Utility.hpp:80-88 */
+int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out);
+/* calc_rho(fs)/calc_visc(fs), src/FS.hpp:569-589 and calc_rho(vf,fs)/calc_visc(vf,fs),
+ * src/FS.hpp:592-650 (uses FSGPU_VF) */
+int fsgpu_calc_rho_visc_const(fsgpu_ctx* c);
+int fsgpu_calc_rho_visc_vof(fsgpu_ctx* c);
+/* apply_neumann_bconds(field), src/BoundaryConditions.hpp:227-252 */
+int fsgpu_apply_neumann_bconds(fsgpu_ctx* c, int field);
+
+/* ---- pressure solver = `LinearSolver_StructHypre<Float,NX,NY,1>` -------------------------------
+ * constructor (src/LinearSolver_StructHypre.hpp:43-62): tol, max_iter, PSDirichlet.  The solver
+ * is always PCG preconditioned by one PFMG-style V-cycle (the reference's default
+ * HypreSolver::PCG + HyprePrecond::PFMG, :31-32). */
+typedef struct {
+  double tol;
+  int max_iter;
+  int psd;        /* FSGPU_PSD_* */
+  int relax;      /* FSGPU_RELAX_*; 0 = default (Jacobi, the reference's configuration) */
+  int max_levels; /* 0 = default 16 = PS_PFMG_MAX_LEVELS (src/LinearSolver_StructHypre.hpp:221) */
+  int skip_relax; /* -1 = default (1, HYPRE's pfmg.c:38); 0/1 */
+} fsgpu_ps_opts;
+int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out);
+int fsgpu_ps_destroy(fsgpu_ps* s);
+/* set_pressure_operator(fs), src/LinearSolver_StructHypre.hpp:91-106 (+ LinearSystem.hpp:32-122
+ * and the PFMG setup of Submodules/hypre/src/struct_ls/pfmg_setup.c) */
+int fsgpu_ps_set_operator(fsgpu_ps* s);
+/* set_pressure_rhs(fs, div, dt), src/LinearSolver_StructHypre.hpp:109-116 (+ LinearSystem.hpp:125-155);
+ * reads FSGPU_DIV, writes FSGPU_RHS */
+int fsgpu_ps_set_rhs(fsgpu_ps* s, double dt);
+/* solve(delta_p, &residual, &num_iter), src/LinearSolver_StructHypre.hpp:119-192 -> FSGPU_DELTA_P.
+ * Non-convergence is not an error (the reference only warns, :177-183): returns 0 with
+ * *iters == max_iter and *residual >= tol. */
+int fsgpu_ps_solve(fsgpu_ps* s, double* residual, int* iters);
+int fsgpu_ps_num_levels(fsgpu_ps* s, int* n);
+
+/* ---- fused fast path used by our own drivers: one projection sub-iteration
+ * (scaling/LidDrivenFlow.cpp:127-161) and one whole timestep (:121-163) ----------------------- */
+enum {
+  FSGPU_STEP_OUTFLOW_FIX = 1,       /* test/LaminarChannel.cpp:201-205 */
+  FSGPU_STEP_REBUILD_OPERATOR = 2   /* set_pressure_operator every sub-iteration (two-phase
+                                       drivers, test/StationaryDrop.cpp:357) */
+};
+int fsgpu_substep(fsgpu_ctx* c, fsgpu_ps* s, double dt, int flags, double* residual, int* iters);
+/* save_old_state + num_subiter sub-iterations; *iters = total PCG iterations of the step */
+int fsgpu_step(fsgpu_ctx* c, fsgpu_ps* s, double dt, int num_subiter, int flags, double* residual,
+               int* iters);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FSGPU_H_ */

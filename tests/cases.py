@@ -1,0 +1,104 @@
+"""Seeded input states for the parity tests, shaped after BASELINE.json's configs
+ at sizes the CPU oracle finishes in seconds."""
+from __future__ import annotations
+
+import numpy as np
+
+from oracle_lib import (ALL_FIELDS, BConds, DIRICHLET, NEUMANN, PERIODIC, SYMMETRY, State)
+
+
+def random_state(nx, ny, seed=0, rho_ratio=1000.0, lx=1.0, ly=1.0):
+    """Every field random; densities jump between gas and liquid so both branches of
+    hybrid_interp (src/FS.hpp:132-150) are taken."""
+    rng = np.random.default_rng(seed)
+    st = State(nx, ny, lx / nx, ly / ny, rho_gas=1.0, rho_liquid=rho_ratio, visc_gas=1e-3,
+               visc_liquid=1e-2)
+    for n in ALL_FIELDS:
+        st.a[n][:] = rng.uniform(-1, 1, st.a[n].shape)
+    for n in ("rho_u", "rho_v", "rho_u_old", "rho_v_old"):
+        blob = rng.uniform(size=st.a[n].shape) < 0.5
+        st.a[n][:] = np.where(blob, 1.0, rho_ratio) * (1 + 1e-4 * rng.uniform(size=st.a[n].shape))
+    st.a["visc"][:] = np.abs(st.a["visc"]) * 1e-2 + 1e-3
+    return st
+
+
+def ellipse_vf(nx, ny, dx, dy, sharp=1.5):
+    """Smoothed indicator of the ellipse (2(x-1/2))^2 + (y-1/2)^2 <= 0.25^2
+    (test/StationaryDrop.cpp:46-52), ghost inclusive."""
+    x = (np.arange(-1, nx + 1) + 0.5) * dx
+    y = (np.arange(-1, ny + 1) + 0.5) * dy
+    X, Y = np.meshgrid(x, y, indexing="ij")
+    d = np.sqrt((2 * (X - 0.5)) ** 2 + (Y - 0.5) ** 2) - 0.25
+    return np.clip(0.5 - d / (sharp * dx), 0.0, 1.0)
+
+
+def cavity_bc():
+    """scaling/LidDrivenFlow.cpp:33-41: no-slip walls, lid U = 1 on top."""
+    return BConds(kind=(DIRICHLET,) * 4, u_val=(0.0, 0.0, 0.0, 1.0), v_val=(0.0,) * 4)
+
+
+def channel_bc():
+    """test/LaminarChannel.cpp:42-50: inlet U = 1, Neumann outlet, no-slip walls."""
+    return BConds(kind=(DIRICHLET, NEUMANN, DIRICHLET, DIRICHLET), u_val=(1.0, 0.0, 0.0, 0.0),
+                  v_val=(0.0,) * 4)
+
+
+def periodic_bc():
+    return BConds(kind=(PERIODIC,) * 4)
+
+
+def cavity_state(oracle, nx, ny, drop=False, lx=1.0, ly=1.0, rho=1.0, mu=1e-3, seed=None):
+    st = State(nx, ny, lx / nx, ly / ny, rho_gas=rho, rho_liquid=1000.0 if drop else rho,
+               visc_gas=mu, visc_liquid=mu)
+    if drop:
+        vf = ellipse_vf(nx, ny, st.dx, st.dy)
+        oracle.apply_neumann_bconds(vf)
+        oracle.calc_rho_visc_vof(st, vf)
+        st.vf = vf
+    else:
+        oracle.calc_rho_visc_const(st)
+    st.a["rho_u_old"][:] = st.a["rho_u"]
+    st.a["rho_v_old"][:] = st.a["rho_v"]
+    if seed is not None:
+        rng = np.random.default_rng(seed)
+        st.a["U"][:] = 0.1 * rng.uniform(-1, 1, st.a["U"].shape)
+        st.a["V"][:] = 0.1 * rng.uniform(-1, 1, st.a["V"].shape)
+    return st
+
+
+def tgv_state(oracle, n=128):
+    """test/TaylorGreenVortex.cpp:21-48,109-113 (note: the test fills V over U's index range)."""
+    L = 2 * np.pi
+    st = State(n, n, L / n, L / n, rho_gas=0.9, rho_liquid=0.9, visc_gas=0.1, visc_liquid=0.1)
+    oracle.calc_rho_visc_const(st)
+    x = np.arange(-1, n + 2) * st.dx          # face coordinates
+    xm = (np.arange(-1, n + 1) + 0.5) * st.dx  # centre coordinates
+    st.a["U"][:] = np.sin(x)[:, None] * np.cos(xm)[None, :]
+    V = np.zeros((n + 2, n + 3))
+    # V(i, j) = -cos(xm(i)) sin(y(j)) for (i, j) in U's interior range [0, N] x [0, N)
+    Vfull = -np.cos(xm)[:, None] * np.sin(x)[None, :]
+    V[1:n + 2, 1:n + 1] = Vfull[1:n + 2, 1:n + 1]
+    st.a["V"][:] = V
+    return st
+
+
+def to_gpu(F, st, bc=None, device=0):
+    """oracle_lib.State -> fluidsolver_b200.FS (upload every field)."""
+    fs = F.FS(st.nx, st.ny, st.dx, st.dy, st.rho_gas, st.rho_liquid, st.visc_gas, st.visc_liquid,
+              st.sigma, device=device)
+    for n in ALL_FIELDS:
+        fs.upload(n.upper(), st.a[n])
+    if bc is not None:
+        for s in range(4):
+            fs.set_bconds(s, bc.kind[s], bc.u_val[s], bc.v_val[s], bc.u_prof[s], bc.v_prof[s],
+                          bc.clipped[s])
+    return fs
+
+
+def rel_inf(a, b):
+    """||a - b||_inf / ||b||_inf (norm-relative, SURVEY.md section 7 'FMA contraction')"""
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
+
+
+def rel_l2(a, b):
+    return float(np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300))
