@@ -7,8 +7,32 @@
 #include <string.h>
 
 #include <new>
+#include <vector>
 
 int64_t g_launches = 0;
+unsigned int g_prof_mask = 0;
+
+namespace {
+struct ProfRec { int cls; cudaEvent_t a, b; };
+std::vector<ProfRec> g_prof_recs;
+std::vector<cudaEvent_t> g_prof_pool;
+cudaEvent_t g_prof_open[PROF_NCLASS];
+cudaEvent_t prof_event() {
+  cudaEvent_t e;
+  if (!g_prof_pool.empty()) { e = g_prof_pool.back(); g_prof_pool.pop_back(); }
+  else cudaEventCreate(&e);
+  return e;
+}
+}  // namespace
+void fs_prof_begin(int cls, cudaStream_t st) {
+  g_prof_open[cls] = prof_event();
+  cudaEventRecord(g_prof_open[cls], st);
+}
+void fs_prof_end(int cls, cudaStream_t st) {
+  cudaEvent_t e = prof_event();
+  cudaEventRecord(e, st);
+  g_prof_recs.push_back({cls, g_prof_open[cls], e});
+}
 static thread_local char g_err[512] = "";
 
 void fs_set_error(const char* fmt, ...) {
@@ -38,6 +62,25 @@ extern "C" {
 
 const char* fsgpu_last_error(void) { return g_err; }
 int64_t fsgpu_launch_count(void) { return g_launches; }
+
+int fsgpu_prof_enable(unsigned int class_mask) {
+  g_prof_mask = class_mask;
+  return 0;
+}
+// sums the recorded intervals per class (synchronises the device) and clears the records
+int fsgpu_prof_read(double* ms_total, int64_t* count, int nclass) {
+  FS_CUDA(cudaDeviceSynchronize());
+  for (int q = 0; q < nclass; ++q) { ms_total[q] = 0.0; count[q] = 0; }
+  for (const ProfRec& r : g_prof_recs) {
+    float ms = 0.f;
+    FS_CUDA(cudaEventElapsedTime(&ms, r.a, r.b));
+    if (r.cls < nclass) { ms_total[r.cls] += ms; count[r.cls] += 1; }
+    g_prof_pool.push_back(r.a);
+    g_prof_pool.push_back(r.b);
+  }
+  g_prof_recs.clear();
+  return 0;
+}
 
 int fsgpu_device_count(int* n) {
   FS_CUDA(cudaGetDeviceCount(n));
@@ -330,15 +373,27 @@ int fsgpu_ps_num_levels(fsgpu_ps* s, int* n) {
 int fsgpu_substep(fsgpu_ctx* c, fsgpu_ps* s, double dt, int flags, double* residual, int* iters) {
   FS_CHECK_CTX(c);
   if (!s || s->c != c) { fs_set_error("fsgpu_substep: solver does not belong to this context"); return 1; }
-  if (fs_launch_momentum_update(c, dt)) return 1;  // mid-time + dmomdt + update
-  if (fs_launch_bconds(c)) return 1;
+  {
+    ProfScope ps_(PROF_MOMENTUM, c->stream);
+    if (fs_launch_momentum_update(c, dt)) return 1;  // mid-time + dmomdt + update
+  }
+  {
+    ProfScope ps_(PROF_BC, c->stream);
+    if (fs_launch_bconds(c)) return 1;
+  }
   if ((flags & FSGPU_STEP_OUTFLOW_FIX) && fs_launch_outflow_fix(c, c->red_out + 2)) return 1;
   if ((flags & FSGPU_STEP_REBUILD_OPERATOR) || !s->is_setup) {
     if (ps_setup(s)) return 1;
   }
-  if (fs_launch_rhs(c, dt, s->o.psd, true)) return 1;  // divergence + rhs (+ mean removal)
+  {
+    ProfScope ps_(PROF_RHS, c->stream);
+    if (fs_launch_rhs(c, dt, s->o.psd, true)) return 1;  // divergence + rhs (+ mean removal)
+  }
   if (ps_solve(s, residual, iters)) return 1;
-  if (fs_launch_correct(c, dt, true)) return 1;        // shift + p += dp + velocity correction
+  {
+    ProfScope ps_(PROF_CORRECT, c->stream);
+    if (fs_launch_correct(c, dt, true)) return 1;  // shift + p += dp + velocity correction
+  }
   return 0;
 }
 

@@ -123,3 +123,25 @@ extern int64_t g_launches;
   } while (0)
 
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// ---- optional per-kernel-class timing with CUDA events on the launching stream (api.cu) -------
+// bench.py enables ONE class at a time (fsgpu_prof_enable) to get the average launch duration of
+// the dominant kernel inside the timed region; disabled (the default) it costs one branch.
+enum {
+  PROF_MOMENTUM = 0, PROF_BC, PROF_RHS, PROF_CORRECT, PROF_MATVEC, PROF_XR, PROF_DOT, PROF_PUPD,
+  PROF_DOWN0, PROF_UP0, PROF_DOWN, PROF_UP, PROF_COARSE, PROF_SETUP, PROF_OTHER, PROF_NCLASS
+};
+extern unsigned int g_prof_mask;
+void fs_prof_begin(int cls, cudaStream_t st);
+void fs_prof_end(int cls, cudaStream_t st);
+struct ProfScope {
+  int cls;
+  cudaStream_t st;
+  bool on;
+  ProfScope(int c, cudaStream_t s) : cls(c), st(s), on((g_prof_mask >> c) & 1u) {
+    if (on) fs_prof_begin(cls, st);
+  }
+  ~ProfScope() {
+    if (on) fs_prof_end(cls, st);
+  }
+};

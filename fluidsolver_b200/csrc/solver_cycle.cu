@@ -236,14 +236,19 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z) {
   // down: level l rhs -> level l+1 rhs
   for (int l = 0; l <= nl - 2; ++l) {
     const double* fb = l == 0 ? r : L[l].v.b;
+    ProfScope ps_(l == 0 ? PROF_DOWN0 : PROF_DOWN, st);
     DISPATCH(k_down, L[l].cdir, L[l].active, lvl_grid(L[l + 1].v), L[l].v, fb, L[l + 1].v,
              L[l + 1].v.b, L[l].weight, s->scal);
   }
-  if (coarse_solve(s, nl - 1, L[nl - 1].v.b, L[nl - 1].v.x)) return 1;
+  {
+    ProfScope ps_(PROF_COARSE, st);
+    if (coarse_solve(s, nl - 1, L[nl - 1].v.b, L[nl - 1].v.x)) return 1;
+  }
   // up: level l+1 x -> level l x
   for (int l = nl - 2; l >= 0; --l) {
     const double* fb = l == 0 ? r : L[l].v.b;
     double* fx       = l == 0 ? z : L[l].v.x;
+    ProfScope ps_(l == 0 ? PROF_UP0 : PROF_UP, st);
     DISPATCH(k_up, L[l].cdir, L[l].active, lvl_grid(L[l].v), L[l].v, fb, fx, L[l + 1].v,
              L[l + 1].v.x, L[l].weight, s->scal);
   }

@@ -155,15 +155,27 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   int launched = 0;
   bool stop = false;
   for (int it = 1; it <= s->o.max_iter && !stop; ++it) {
-    k_matvec_dot<<<gr, bl, 0, st>>>(L0, s->p, s->s, s->scal, c->part, c->ticket);
-    FS_LAUNCHED();
-    k_xr_update<<<gr, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal);
-    FS_LAUNCHED();
+    {
+      ProfScope ps_(PROF_MATVEC, st);
+      k_matvec_dot<<<gr, bl, 0, st>>>(L0, s->p, s->s, s->scal, c->part, c->ticket);
+      FS_LAUNCHED();
+    }
+    {
+      ProfScope ps_(PROF_XR, st);
+      k_xr_update<<<gr, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal);
+      FS_LAUNCHED();
+    }
     if (ps_vcycle(s, r, s->z)) return 1;
-    k_dot_rz<false><<<gr, bl, 0, st>>>(L0, r, s->z, s->scal, c->part, c->ticket);
-    FS_LAUNCHED();
-    k_p_update<false><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);
-    FS_LAUNCHED();
+    {
+      ProfScope ps_(PROF_DOT, st);
+      k_dot_rz<false><<<gr, bl, 0, st>>>(L0, r, s->z, s->scal, c->part, c->ticket);
+      FS_LAUNCHED();
+    }
+    {
+      ProfScope ps_(PROF_PUPD, st);
+      k_p_update<false><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);
+      FS_LAUNCHED();
+    }
     const int slot = it % nslot;
     FS_CUDA(cudaMemcpyAsync(&s->h_scal[slot], s->scal, sizeof(PcgScal), cudaMemcpyDeviceToHost, st));
     FS_CUDA(cudaEventRecord(s->ev[slot], st));

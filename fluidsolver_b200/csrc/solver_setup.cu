@@ -263,6 +263,7 @@ static dim3 lvl_grid(const LevelDev& v) {
 int ps_setup(fsgpu_ps* s) {
   fsgpu_ctx* c = s->c;
   const Geom& g = c->g;
+  ProfScope ps_(PROF_SETUP, c->stream);
   // sizes of level 0 are fixed; the first setup needs level-0 arrays before the schedule is
   // known, so allocate for a provisional single level, then re-run once the schedule exists.
   if (!s->levels_allocated) {

@@ -32,7 +32,8 @@ DP = C.POINTER(C.c_double)
 
 # every symbol include/fsgpu.h declares (tests check the library exports all of them)
 SYMBOLS = (
-    "fsgpu_last_error", "fsgpu_launch_count", "fsgpu_device_count", "fsgpu_create", "fsgpu_destroy",
+    "fsgpu_last_error", "fsgpu_launch_count", "fsgpu_device_count", "fsgpu_prof_enable",
+    "fsgpu_prof_read", "fsgpu_create", "fsgpu_destroy",
     "fsgpu_set_props", "fsgpu_upload", "fsgpu_download", "fsgpu_fill", "fsgpu_sync",
     "fsgpu_device_field", "fsgpu_stream", "fsgpu_set_bconds", "fsgpu_adjust_dt",
     "fsgpu_save_old_state", "fsgpu_save_old_velocity", "fsgpu_save_old_density",
@@ -108,6 +109,31 @@ def _chk(rc):
 
 def launch_count() -> int:
     return int(load().fsgpu_launch_count())
+
+
+PROF_CLASSES = ("momentum", "bconds", "div_rhs", "shift_correct", "matvec_dot", "xr_update", "dot_rz",
+                "p_update", "vcycle_down_l0", "vcycle_up_l0", "vcycle_down_coarse", "vcycle_up_coarse",
+                "coarsest_solve", "operator_setup", "other")
+
+
+def prof_enable(classes=()):
+    """enable device timing for the named kernel classes (empty = off)"""
+    mask = 0
+    for c in classes:
+        mask |= 1 << PROF_CLASSES.index(c)
+    L = load()
+    L.fsgpu_prof_enable.argtypes = [C.c_uint]
+    _chk(L.fsgpu_prof_enable(mask))
+
+
+def prof_read():
+    """-> {class: (total_ms, count)} for classes with records; clears the records"""
+    L = load()
+    n = len(PROF_CLASSES)
+    ms, cnt = (C.c_double * n)(), (C.c_int64 * n)()
+    L.fsgpu_prof_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int]
+    _chk(L.fsgpu_prof_read(ms, cnt, n))
+    return {PROF_CLASSES[i]: (ms[i], cnt[i]) for i in range(n) if cnt[i]}
 
 
 def device_count() -> int:

@@ -73,6 +73,13 @@ const char* fsgpu_last_error(void);
 /* number of CUDA kernels launched by this library since load (bench.py's gpu_launches) */
 int64_t fsgpu_launch_count(void);
 int fsgpu_device_count(int* n);
+/* per-kernel-class device timing (CUDA events on the context's stream) for bench.py's roofline:
+ * bit k of class_mask enables class k: 0 momentum, 1 bconds, 2 div+rhs, 3 shift+correct,
+ * 4 matvec+dot, 5 x/r update, 6 <r,z>, 7 p update, 8 V-cycle down level 0, 9 V-cycle up level 0,
+ * 10 down levels>=1, 11 up levels>=1, 12 coarsest solve, 13 operator setup.  fsgpu_prof_read
+ * synchronises, returns total milliseconds and launch-group counts per class, and clears. */
+int fsgpu_prof_enable(unsigned int class_mask);
+int fsgpu_prof_read(double* ms_total, int64_t* count, int nclass);
 
 /* ---- context = the reference's `FS<Float,NX,NY,1>` object (src/FS.hpp:28-52) on one device ---- */
 /* replaces: `FS<Float,NX,NY,NGHOST> fs{...}; init_grid(...)` (src/FS.hpp:55-73) */

@@ -102,3 +102,12 @@ def rel_inf(a, b):
 
 def rel_l2(a, b):
     return float(np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300))
+
+
+def vel_err(U, V, Uref, Vref):
+    """relative L2 error of the velocity FIELD (U, V) -- north_star's "velocity ... fields after N
+    steps within 1e-10 relative L2"; one norm over both components, so a component that is
+    ~1e-4 of the other (V in a channel) is not judged against its own tiny norm."""
+    num = np.linalg.norm((U - Uref).ravel()) ** 2 + np.linalg.norm((V - Vref).ravel()) ** 2
+    den = np.linalg.norm(Uref.ravel()) ** 2 + np.linalg.norm(Vref.ravel()) ** 2
+    return float(np.sqrt(num / max(den, 1e-300)))
