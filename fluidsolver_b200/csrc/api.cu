@@ -7,6 +7,7 @@
 #include <string.h>
 
 #include <new>
+#include <set>
 #include <vector>
 
 int64_t g_launches = 0;
@@ -122,10 +123,17 @@ int fsgpu_create(int64_t nx, int64_t ny, double dx, double dy, int device, fsgpu
   return 0;
 }
 
+static std::set<fsgpu_ps*> g_live_solvers;  // so that destroy order (solver / context) is free
+static int ps_destroy_impl(fsgpu_ps* s);
+
 int fsgpu_destroy(fsgpu_ctx* c) {
   if (!c) return 0;
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  std::vector<fsgpu_ps*> mine;
+  for (fsgpu_ps* s : g_live_solvers)
+    if (s->c == c) mine.push_back(s);
+  for (fsgpu_ps* s : mine) ps_destroy_impl(s);
   for (int s = 0; s < 4; ++s) {
     if (c->bc[s].u_prof) cudaFree(c->bc[s].u_prof);
     if (c->bc[s].v_prof) cudaFree(c->bc[s].v_prof);
@@ -328,12 +336,19 @@ int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out) {
   FS_CUDA(cudaMemset(s->scal, 0, sizeof(PcgScal)));
   FS_CUDA(cudaMallocHost(&s->h_scal, 4 * sizeof(PcgScal)));
   for (int i = 0; i < 4; ++i) FS_CUDA(cudaEventCreateWithFlags(&s->ev[i], cudaEventDisableTiming));
+  g_live_solvers.insert(s);
   *out = s;
   return 0;
 }
 
 int fsgpu_ps_destroy(fsgpu_ps* s) {
-  if (!s) return 0;
+  // a solver already torn down with its context (fsgpu_destroy) is a no-op here
+  if (!s || !g_live_solvers.count(s)) return 0;
+  return ps_destroy_impl(s);
+}
+
+static int ps_destroy_impl(fsgpu_ps* s) {
+  g_live_solvers.erase(s);
   cudaSetDevice(s->c->device);
   cudaStreamSynchronize(s->c->stream);
   cudaFree(s->slab);

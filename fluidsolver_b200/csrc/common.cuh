@@ -101,6 +101,33 @@ __device__ inline bool grid_reduce(const double (&v)[NV], double* part, unsigned
   return true;
 }
 
+// ---- persistent tile loop for kernels that end in a grid-wide reduction ------------------------
+// A (64 x 4)-thread block walks 16-row x 64-column tiles with a grid stride, so the grid is a few
+// CTAs per SM (persist_blocks) instead of one CTA per 256 points: the reduction then costs
+// ~1e3 partials + tickets instead of ~3e5 serialised atomics on one address (measured: 0.8 ms per
+// reduction at 8192^2 before this change).
+template <class F>
+__device__ __forceinline__ void for_each_point(int64_t n0, int64_t n1, F&& f) {
+  const int64_t tiles_j = (n1 + 63) / 64, nt = tiles_j * ((n0 + 15) / 16);
+  for (int64_t t = blockIdx.x; t < nt; t += gridDim.x) {
+    const int64_t ti = t / tiles_j, tj = t - ti * tiles_j;
+    const int64_t lj = tj * 64 + threadIdx.x;
+    if (lj < n1) {
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        const int64_t li = ti * 16 + threadIdx.y + 4 * m;
+        if (li < n0) f(li, lj);
+      }
+    }
+  }
+}
+#define FS_NUM_SMS 148
+static inline unsigned persist_blocks(int64_t n0, int64_t n1, int per_sm = 8) {
+  const int64_t nt = ((n1 + 63) / 64) * ((n0 + 15) / 16);
+  const int64_t cap = (int64_t)FS_NUM_SMS * per_sm;
+  return (unsigned)(nt < cap ? (nt > 0 ? nt : 1) : cap);
+}
+
 // ---- error handling / launch accounting (api.cu) ---------------------------------------------
 void fs_set_error(const char* fmt, ...);
 extern int64_t g_launches;

@@ -41,10 +41,8 @@ __global__ void __launch_bounds__(BX* BY)
 k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __restrict__ div,
       double* __restrict__ rhs, const Geom g, double dt, int psd, double* part,
       unsigned int* ticket, double* out) {
-  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
   double v[1] = {0.0};
-  if (a <= g.nx + 1 && b <= g.ny + 1) {
+  for_each_point(g.nx + 2, g.ny + 2, [&](int64_t a, int64_t b) {
     const int64_t k = g.idx(a, b);
     double d;
     if (FROM_UV) {
@@ -59,8 +57,8 @@ k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __rest
         (psd == FSGPU_PSD_BOTTOM && b == 0) || (psd == FSGPU_PSD_TOP && b == g.ny + 1))
       r = 0.0;
     rhs[k] = r;
-    v[0]   = r;
-  }
+    v[0] += r;
+  });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
     if (threadIdx.x == 0 && threadIdx.y == 0) out[0] = tot[0];
@@ -78,10 +76,8 @@ k_sub_scaled(double* __restrict__ f, const double* __restrict__ sum, double scal
 
 __global__ void __launch_bounds__(BX* BY)
 k_sum(const double* __restrict__ f, const Geom g, double* part, unsigned int* ticket, double* out) {
-  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
   double v[1] = {0.0};
-  if (a <= g.nx + 1 && b <= g.ny + 1) v[0] = f[g.idx(a, b)];
+  for_each_point(g.nx + 2, g.ny + 2, [&](int64_t a, int64_t b) { v[0] += f[g.idx(a, b)]; });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
     if (threadIdx.x == 0 && threadIdx.y == 0) out[0] = tot[0];
@@ -123,17 +119,15 @@ __global__ void __launch_bounds__(BX* BY)
 k_cfl(const double* __restrict__ U, const double* __restrict__ V, const double* __restrict__ ru,
       const double* __restrict__ rv, const double* __restrict__ mu, const Geom g, double* part,
       unsigned int* ticket, double* out) {
-  const int64_t j = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t i = (int64_t)blockIdx.y * BY + threadIdx.y;
   double v[4] = {0.0, 0.0, 0.0, 0.0};  // the reference's maxima start at 0 (FS.hpp:102-106)
-  if (i < g.nx && j < g.ny) {
+  for_each_point(g.nx, g.ny, [&](int64_t i, int64_t j) {
     const int64_t k = g.idx(i + 1, j + 1), P = g.pitch;
-    v[0] = (U[k] + U[k + P]) / 2 / g.dx;
-    v[1] = (V[k] + V[k + 1]) / 2 / g.dy;
+    v[0] = fmax(v[0], (U[k] + U[k + P]) / 2 / g.dx);
+    v[1] = fmax(v[1], (V[k] + V[k + 1]) / 2 / g.dy);
     const double rho = (ru[k] + ru[k + P] + rv[k] + rv[k + 1]) / 4.0;
-    v[2] = 4.0 * mu[k] / (g.dx * g.dx * rho);
-    v[3] = 4.0 * mu[k] / (g.dy * g.dy * rho);
-  }
+    v[2] = fmax(v[2], 4.0 * mu[k] / (g.dx * g.dx * rho));
+    v[3] = fmax(v[3], 4.0 * mu[k] / (g.dy * g.dy * rho));
+  });
   double tot[4];
   if (grid_reduce<ReduceMax, 4>(v, part, ticket, tot)) {
     if (threadIdx.x == 0 && threadIdx.y == 0)
@@ -218,13 +212,14 @@ int fs_launch_divergence(fsgpu_ctx* c) {
 
 int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
   const dim3 gr = cell_grid(c->g);
-  if (fs_ensure_part(c, (size_t)gr.x * gr.y * 4)) return 1;
+  const unsigned pg = persist_blocks(c->g.nx + 2, c->g.ny + 2);
+  if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
   if (div_from_uv)
-    k_rhs<true><<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
+    k_rhs<true><<<pg, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
                                                     c->f[FSGPU_RHS], c->g, dt, psd, c->part,
                                                     c->ticket, c->red_out);
   else
-    k_rhs<false><<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
+    k_rhs<false><<<pg, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
                                                      c->f[FSGPU_RHS], c->g, dt, psd, c->part,
                                                      c->ticket, c->red_out);
   FS_LAUNCHED();
@@ -237,8 +232,8 @@ int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
 }
 
 static int launch_sum_dp(fsgpu_ctx* c) {
-  const dim3 gr = cell_grid(c->g);
-  if (fs_ensure_part(c, (size_t)gr.x * gr.y * 4)) return 1;
+  const unsigned gr = persist_blocks(c->g.nx + 2, c->g.ny + 2);
+  if (fs_ensure_part(c, (size_t)gr * 4)) return 1;
   k_sum<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_DELTA_P], c->g, c->part, c->ticket,
                                             c->red_out + 1);
   FS_LAUNCHED();
@@ -267,8 +262,8 @@ int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift) {
 }
 
 int fs_launch_cfl(fsgpu_ctx* c) {
-  const dim3 gr((unsigned)cdiv(c->g.ny, BX), (unsigned)cdiv(c->g.nx, BY));
-  if (fs_ensure_part(c, (size_t)gr.x * gr.y * 4)) return 1;
+  const unsigned gr = persist_blocks(c->g.nx, c->g.ny);
+  if (fs_ensure_part(c, (size_t)gr * 4)) return 1;
   k_cfl<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
                                             c->f[FSGPU_RHO_V], c->f[FSGPU_VISC], c->g, c->part,
                                             c->ticket, c->red_out);

@@ -45,6 +45,30 @@ struct PcgScal {
 // done codes
 enum { PCG_RUNNING = 0, PCG_CONVERGED = 1, PCG_BREAKDOWN = 2, PCG_ZERO_RHS = 3 };
 
+#ifdef __CUDACC__
+// the scalar part of "gamma' = <r, C r>" (executed by one thread of the last reduction block).
+// INIT: bi = <C b, b> before the loop (pcg.c:430-488); otherwise the convergence test of
+// pcg.c:816 and beta = gamma'/gamma.
+template <bool INIT>
+__device__ __forceinline__ void pcg_after_rz(PcgScal* scal, double g) {
+  if (INIT) {
+    scal->bi    = g;
+    scal->gamma = g;
+    scal->iprod = 0.0;
+    scal->beta  = 0.0;
+    if (!(g > 0.0)) scal->done = PCG_ZERO_RHS;  // pcg.c:473-488
+  } else {
+    scal->iprod = g;
+    if (g / scal->bi < scal->eps) scal->done = PCG_CONVERGED;  // pcg.c:816
+    else if (g <= 0.0) scal->done = PCG_BREAKDOWN;
+    else {
+      scal->beta  = g / scal->gamma;
+      scal->gamma = g;
+    }
+  }
+}
+#endif
+
 struct fsgpu_ps {
   fsgpu_ctx* c = nullptr;
   fsgpu_ps_opts o{};
@@ -65,7 +89,9 @@ struct fsgpu_ps {
 
 // solver_setup.cu
 int ps_setup(fsgpu_ps* s);
-// solver_cycle.cu: z = C r, one V-cycle from a zero guess (r, z in level-0 layout)
-int ps_vcycle(fsgpu_ps* s, const double* r, double* z);
+// solver_cycle.cu: z = C r, one V-cycle from a zero guess (r, z in level-0 layout).
+// dot_mode 0: nothing more; 1: also gamma' = <r, z> with the convergence test and beta;
+// 2: also bi = <r, z> (first V-cycle).  The dot product rides on the last kernel of the cycle.
+int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode);
 // solver_pcg.cu
 int ps_solve(fsgpu_ps* s, double* residual, int* iters);

@@ -65,12 +65,13 @@ k_down(const LevelDev f, const double* __restrict__ fb, const LevelDev c, double
 }
 
 // value at fine point (li, lj) after [zero-guess relaxation] + interpolation of the coarse x
+// (bq = rhs at the point, only used when ACTIVE)
 template <int CDIR, bool ACTIVE>
-__device__ __forceinline__ double x_interp(const LevelDev& f, const double* __restrict__ fb,
-                                           const LevelDev& c, const double* __restrict__ cx_,
-                                           int64_t li, int64_t lj, int64_t q, double w) {
+__device__ __forceinline__ double x_interp(const LevelDev& f, double bq, const LevelDev& c,
+                                           const double* __restrict__ cx_, int64_t li, int64_t lj,
+                                           int64_t q, double w) {
   const Coef<CDIR> C{f.cx, f.cy, f.pitch};
-  double x = ACTIVE ? w * __ldg(fb + q) * __ldg(f.dinv + q) : 0.0;
+  double x = ACTIVE ? w * bq * __ldg(f.dinv + q) : 0.0;
   const int64_t pos = (CDIR == 0 ? li : lj) - c.foff;  // even <=> C-point
   const int64_t csd = CDIR == 0 ? c.pitch : 1;
   if ((pos & 1) == 0) {
@@ -87,27 +88,116 @@ __device__ __forceinline__ double x_interp(const LevelDev& f, const double* __re
   return x;
 }
 
-template <int CDIR, bool ACTIVE>
+// inactive level: interpolation only (no relaxation on this level)
+template <int CDIR>
 __global__ void __launch_bounds__(BX* BY)
-k_up(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
-     const double* __restrict__ cxv, double w, const PcgScal* scal) {
+k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
+            const double* __restrict__ cxv, const PcgScal* scal) {
   if (scal->done) return;
   const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
   const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
   if (li >= f.n0 || lj >= f.n1) return;
-  const int64_t k = f.idx(li, lj), P = f.pitch;
-  const double x0 = x_interp<CDIR, ACTIVE>(f, fb, c, cxv, li, lj, k, w);
-  if (!ACTIVE) {
-    fx[k] = x0;
-    return;
+  const int64_t k = f.idx(li, lj);
+  fx[k] = x_interp<CDIR, false>(f, 0.0, c, cxv, li, lj, k, 0.0);
+}
+
+// active level: x0 = w b / d + P x_c is formed ONCE per point in a shared-memory tile
+// (32 rows x 64 columns + a one-point ring), then x = x0 + w (b - A x0) / d reads its four
+// neighbours from the tile.  A CTA walks tiles with a grid stride (persistent), so the optional
+// dot product <b, x> (= <r, z> of PCG on level 0) ends in ~600 partials.
+// DOT: 0 none, 1 PCG iteration (convergence test + beta), 2 first V-cycle (bi).
+constexpr int UT_I = 32, UT_J = 64, UT_Y = 4, UT_SW = UT_J + 2, UT_PER = UT_I / UT_Y;
+
+template <int CDIR, int DOT>
+__global__ void __launch_bounds__(UT_J* UT_Y, 3)
+k_up_tiled(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
+           const double* __restrict__ cxv, double w, PcgScal* scal, double* part,
+           unsigned int* ticket) {
+  if (scal->done) return;
+  __shared__ double sx[(UT_I + 2) * UT_SW];
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * UT_J + tx;
+  const int64_t tiles_j = (f.n1 + UT_J - 1) / UT_J, nt = tiles_j * ((f.n0 + UT_I - 1) / UT_I);
+  const int64_t P = f.pitch;
+  double acc[1] = {0.0};
+  for (int64_t t = blockIdx.x; t < nt; t += gridDim.x) {
+    const int64_t ti = t / tiles_j, tj = t - ti * tiles_j;
+    const int64_t i0 = ti * UT_I, j0 = tj * UT_J;
+    const int64_t lj = j0 + tx;
+    double bv[UT_PER], x0v[UT_PER];
+    // phase 1a: this thread's own points
+#pragma unroll
+    for (int m = 0; m < UT_PER; ++m) {
+      const int r = ty + UT_Y * m;
+      const int64_t li = i0 + r;
+      double b = 0.0, x0 = 0.0;
+      if (li < f.n0 && lj < f.n1) {
+        const int64_t k = f.idx(li, lj);
+        b  = __ldg(fb + k);
+        x0 = x_interp<CDIR, true>(f, b, c, cxv, li, lj, k, w);
+      }
+      bv[m] = b;
+      x0v[m] = x0;
+      sx[(r + 1) * UT_SW + tx + 1] = x0;
+    }
+    // phase 1b: the ring (2 rows of UT_SW + 2 columns of UT_I = 196 points), one per thread
+    if (tid < 2 * UT_SW + 2 * UT_I) {
+      int r, cc;
+      if (tid < UT_SW) { r = -1; cc = tid - 1; }
+      else if (tid < 2 * UT_SW) { r = UT_I; cc = tid - UT_SW - 1; }
+      else if (tid < 2 * UT_SW + UT_I) { r = tid - 2 * UT_SW; cc = -1; }
+      else { r = tid - 2 * UT_SW - UT_I; cc = UT_J; }
+      const int64_t li = i0 + r, l2 = j0 + cc;
+      double x0 = 0.0;
+      if (li >= 0 && li < f.n0 && l2 >= 0 && l2 < f.n1) {
+        const int64_t k = f.idx(li, l2);
+        x0 = x_interp<CDIR, true>(f, __ldg(fb + k), c, cxv, li, l2, k, w);
+      }
+      sx[(r + 1) * UT_SW + cc + 1] = x0;
+    }
+    __syncthreads();
+    // phase 2: post-relaxation
+#pragma unroll
+    for (int m = 0; m < UT_PER; ++m) {
+      const int r = ty + UT_Y * m;
+      const int64_t li = i0 + r;
+      if (li < f.n0 && lj < f.n1) {
+        const int64_t k = f.idx(li, lj);
+        const int sm = (r + 1) * UT_SW + tx + 1;
+        double v = __ldg(f.d + k) * x0v[m];
+        v += __ldg(f.cx + k) * sx[sm - UT_SW];
+        v += __ldg(f.cx + k + P) * sx[sm + UT_SW];
+        v += __ldg(f.cy + k) * sx[sm - 1];
+        v += __ldg(f.cy + k + 1) * sx[sm + 1];
+        const double xo = x0v[m] + w * (bv[m] - v) * __ldg(f.dinv + k);
+        fx[k] = xo;
+        if (DOT) acc[0] += bv[m] * xo;
+      }
+    }
+    __syncthreads();  // the tile is overwritten by the next iteration
   }
-  double v = __ldg(f.d + k) * x0;
-  // neighbours outside the grid have a zero coupling; skip them so no index leaves the arrays
-  if (li > 0) v += __ldg(f.cx + k) * x_interp<CDIR, ACTIVE>(f, fb, c, cxv, li - 1, lj, k - P, w);
-  if (li < f.n0 - 1) v += __ldg(f.cx + k + P) * x_interp<CDIR, ACTIVE>(f, fb, c, cxv, li + 1, lj, k + P, w);
-  if (lj > 0) v += __ldg(f.cy + k) * x_interp<CDIR, ACTIVE>(f, fb, c, cxv, li, lj - 1, k - 1, w);
-  if (lj < f.n1 - 1) v += __ldg(f.cy + k + 1) * x_interp<CDIR, ACTIVE>(f, fb, c, cxv, li, lj + 1, k + 1, w);
-  fx[k] = x0 + w * (__ldg(fb + k) - v) * __ldg(f.dinv + k);
+  if (DOT) {
+    double tot[1];
+    if (grid_reduce<ReduceSum, 1>(acc, part, ticket, tot)) {
+      if (tid == 0) pcg_after_rz<DOT == 2>(scal, tot[0]);
+    }
+  }
+}
+
+// <r, z> as its own pass (only for one-level hierarchies, where no k_up runs)
+template <bool INIT>
+__global__ void __launch_bounds__(BX* BY)
+k_dot_rz(const LevelDev L, const double* __restrict__ r, const double* __restrict__ z, PcgScal* scal,
+         double* part, unsigned int* ticket) {
+  if (scal->done) return;
+  double v[1] = {0.0};
+  for_each_point(L.n0, L.n1, [&](int64_t li, int64_t lj) {
+    const int64_t k = L.idx(li, lj);
+    v[0] += r[k] * z[k];
+  });
+  double tot[1];
+  if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
+    if (threadIdx.x == 0 && threadIdx.y == 0) pcg_after_rz<INIT>(scal, tot[0]);
+  }
 }
 
 // ---- coarsest level: `sweeps` Jacobi sweeps with weight 1 from a zero guess
@@ -222,15 +312,47 @@ static int coarse_solve(fsgpu_ps* s, int l, const double* b, double* x) {
   return 0;
 }
 
-int ps_vcycle(fsgpu_ps* s, const double* r, double* z) {
+static unsigned up_blocks(const LevelDev& v) {
+  const int64_t nt = cdiv(v.n1, UT_J) * cdiv(v.n0, UT_I);
+  const int64_t cap = (int64_t)FS_NUM_SMS * 3;
+  return (unsigned)(nt < cap ? nt : cap);
+}
+
+template <int CDIR>
+static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_mode) {
+  cudaStream_t st = s->c->stream;
+  Level* L        = s->L;
+  fsgpu_ctx* c    = s->c;
+  if (!L[l].active) {
+    k_up_interp<CDIR><<<lvl_grid(L[l].v), dim3(BX, BY), 0, st>>>(L[l].v, fx, L[l + 1].v, L[l + 1].v.x, s->scal);
+    FS_LAUNCHED();
+    return 0;
+  }
+  const unsigned nb = up_blocks(L[l].v);
+  const dim3 bl(UT_J, UT_Y);
+#define UP_ARGS L[l].v, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, s->scal, c->part, c->ticket
+  if (dot_mode == 1) k_up_tiled<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
+  else if (dot_mode == 2) k_up_tiled<CDIR, 2><<<nb, bl, 0, st>>>(UP_ARGS);
+  else k_up_tiled<CDIR, 0><<<nb, bl, 0, st>>>(UP_ARGS);
+#undef UP_ARGS
+  FS_LAUNCHED();
+  return 0;
+}
+
+int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
   cudaStream_t st = s->c->stream;
   Level* L        = s->L;
   const int nl    = s->nl;
+  if (fs_ensure_part(s->c, (size_t)FS_NUM_SMS * 8 * 4)) return 1;
   if (nl == 1) {  // relax from zero, relax again (pfmg_solve.c with a single level)
     k_jacobi<true><<<lvl_grid(L[0].v), dim3(BX, BY), 0, st>>>(L[0].v, r, nullptr, s->ctmp, L[0].weight, 1, s->scal);
     FS_LAUNCHED();
     k_jacobi<false><<<lvl_grid(L[0].v), dim3(BX, BY), 0, st>>>(L[0].v, r, s->ctmp, z, L[0].weight, 1, s->scal);
     FS_LAUNCHED();
+    const unsigned pg = persist_blocks(L[0].v.n0, L[0].v.n1);
+    if (dot_mode == 1) k_dot_rz<false><<<pg, dim3(BX, BY), 0, st>>>(L[0].v, r, z, s->scal, s->c->part, s->c->ticket);
+    if (dot_mode == 2) k_dot_rz<true><<<pg, dim3(BX, BY), 0, st>>>(L[0].v, r, z, s->scal, s->c->part, s->c->ticket);
+    if (dot_mode) FS_LAUNCHED();
     return 0;
   }
   // down: level l rhs -> level l+1 rhs
@@ -244,13 +366,14 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z) {
     ProfScope ps_(PROF_COARSE, st);
     if (coarse_solve(s, nl - 1, L[nl - 1].v.b, L[nl - 1].v.x)) return 1;
   }
-  // up: level l+1 x -> level l x
+  // up: level l+1 x -> level l x; the level-0 kernel also carries PCG's <r, z>
   for (int l = nl - 2; l >= 0; --l) {
     const double* fb = l == 0 ? r : L[l].v.b;
     double* fx       = l == 0 ? z : L[l].v.x;
     ProfScope ps_(l == 0 ? PROF_UP0 : PROF_UP, st);
-    DISPATCH(k_up, L[l].cdir, L[l].active, lvl_grid(L[l].v), L[l].v, fb, fx, L[l + 1].v,
-             L[l + 1].v.x, L[l].weight, s->scal);
+    const int dm = l == 0 ? dot_mode : 0;
+    if (L[l].cdir == 0) { if (launch_up<0>(s, l, fb, fx, dm)) return 1; }
+    else { if (launch_up<1>(s, l, fb, fx, dm)) return 1; }
   }
   return 0;
 }

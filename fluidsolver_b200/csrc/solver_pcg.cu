@@ -27,11 +27,10 @@ __global__ void __launch_bounds__(BX* BY)
 k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict__ s, PcgScal* scal,
              double* part, unsigned int* ticket) {
   if (scal->done) return;
-  const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
   double v[1] = {0.0};
-  if (li < L.n0 && lj < L.n1) {
-    const int64_t k = L.idx(li, lj), P = L.pitch;
+  const int64_t P = L.pitch;
+  for_each_point(L.n0, L.n1, [&](int64_t li, int64_t lj) {
+    const int64_t k = L.idx(li, lj);
     const double pk = __ldg(p + k);
     double a = __ldg(L.d + k) * pk;
     a += __ldg(L.cx + k) * __ldg(p + k - P);
@@ -39,8 +38,8 @@ k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict_
     a += __ldg(L.cy + k) * __ldg(p + k - 1);
     a += __ldg(L.cy + k + 1) * __ldg(p + k + 1);
     s[k] = a;
-    v[0] = a * pk;
-  }
+    v[0] += a * pk;
+  });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
     if (threadIdx.x == 0 && threadIdx.y == 0) {
@@ -81,32 +80,15 @@ __global__ void __launch_bounds__(BX* BY)
 k_dot_rz(const LevelDev L, const double* __restrict__ r, const double* __restrict__ z, PcgScal* scal,
          double* part, unsigned int* ticket) {
   if (scal->done) return;
-  const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
   double v[1] = {0.0};
-  if (li < L.n0 && lj < L.n1) {
+  for_each_point(L.n0, L.n1, [&](int64_t li, int64_t lj) {
     const int64_t k = L.idx(li, lj);
-    v[0] = r[k] * z[k];
-  }
+    v[0] += r[k] * z[k];
+  });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
     if (threadIdx.x == 0 && threadIdx.y == 0) {
-      const double g = tot[0];
-      if (INIT) {
-        scal->bi    = g;
-        scal->gamma = g;
-        scal->iprod = 0.0;
-        scal->beta  = 0.0;
-        if (!(g > 0.0)) scal->done = PCG_ZERO_RHS;  // pcg.c:473-488
-      } else {
-        scal->iprod = g;
-        if (g / scal->bi < scal->eps) scal->done = PCG_CONVERGED;  // pcg.c:816
-        else if (g <= 0.0) scal->done = PCG_BREAKDOWN;
-        else {
-          scal->beta  = g / scal->gamma;
-          scal->gamma = g;
-        }
-      }
+      pcg_after_rz<INIT>(scal, tot[0]);
     }
   }
 }
@@ -140,15 +122,14 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   cudaStream_t st = c->stream;
   const LevelDev& L0 = s->L[0].v;
   const dim3 gr((unsigned)cdiv(L0.n1, BX), (unsigned)cdiv(L0.n0, BY)), bl(BX, BY);
-  if (fs_ensure_part(c, (size_t)gr.x * gr.y * 4)) return 1;
+  const unsigned pg = persist_blocks(L0.n0, L0.n1);
+  if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
   double* x = c->f[FSGPU_DELTA_P];
   double* r = c->f[FSGPU_RHS];  // r = b - A 0 = b: the rhs buffer becomes the residual
   k_scal_init<<<1, 1, 0, st>>>(s->scal, s->o.tol * s->o.tol);
   FS_LAUNCHED();
   FS_CUDA(cudaMemsetAsync(x, 0, (size_t)c->g.count() * sizeof(double), st));
-  if (ps_vcycle(s, r, s->z)) return 1;
-  k_dot_rz<true><<<gr, bl, 0, st>>>(L0, r, s->z, s->scal, c->part, c->ticket);
-  FS_LAUNCHED();
+  if (ps_vcycle(s, r, s->z, 2)) return 1;  // z = C b and bi = <z, b>
   k_p_update<true><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);
   FS_LAUNCHED();
   const int nslot = FS_LAG + 1;
@@ -157,7 +138,7 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   for (int it = 1; it <= s->o.max_iter && !stop; ++it) {
     {
       ProfScope ps_(PROF_MATVEC, st);
-      k_matvec_dot<<<gr, bl, 0, st>>>(L0, s->p, s->s, s->scal, c->part, c->ticket);
+      k_matvec_dot<<<pg, bl, 0, st>>>(L0, s->p, s->s, s->scal, c->part, c->ticket);
       FS_LAUNCHED();
     }
     {
@@ -165,12 +146,7 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
       k_xr_update<<<gr, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal);
       FS_LAUNCHED();
     }
-    if (ps_vcycle(s, r, s->z)) return 1;
-    {
-      ProfScope ps_(PROF_DOT, st);
-      k_dot_rz<false><<<gr, bl, 0, st>>>(L0, r, s->z, s->scal, c->part, c->ticket);
-      FS_LAUNCHED();
-    }
+    if (ps_vcycle(s, r, s->z, 1)) return 1;  // z = C r and gamma' = <r, z>
     {
       ProfScope ps_(PROF_PUPD, st);
       k_p_update<false><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);

@@ -18,10 +18,8 @@ constexpr int BX = 64, BY = 4;
 __global__ void __launch_bounds__(BX* BY)
 k_build_l0(const double* __restrict__ ru, const double* __restrict__ rv, LevelDev L, const Geom g,
            int psd, double* part, unsigned int* ticket, double* out) {
-  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
   double v[4] = {0.0, 0.0, 0.0, 0.0};
-  if (a <= g.nx + 1 && b <= g.ny + 1) {
+  for_each_point(g.nx + 2, g.ny + 2, [&](int64_t a, int64_t b) {
     const int64_t k = g.idx(a, b), P = g.pitch;
     const double vol = g.dx * g.dy, dx2 = g.dx * g.dx, dy2 = g.dy * g.dy;
     double W = 0.0, E = 0.0, S = 0.0, N = 0.0, dxp, dyp;
@@ -74,8 +72,8 @@ k_build_l0(const double* __restrict__ ru, const double* __restrict__ rv, LevelDe
     // pfmg_coarsen.c:374-503 (cxyz / sqcxyz of pfmg_cxyz_vc.c): sign from the diagonal
     const double sign = d < 0.0 ? 1.0 : -1.0;
     const double w0 = sign * (W + E), w1 = sign * (S + N);
-    v[0] = w0; v[1] = w0 * w0; v[2] = w1; v[3] = w1 * w1;
-  }
+    v[0] += w0; v[1] += w0 * w0; v[2] += w1; v[3] += w1 * w1;
+  });
   double tot[4];
   if (grid_reduce<ReduceSum, 4>(v, part, ticket, tot)) {
     if (threadIdx.x == 0 && threadIdx.y == 0)
@@ -273,8 +271,8 @@ int ps_setup(fsgpu_ps* s) {
     // the schedule instead: here only level 0.
     if (alloc_levels(s)) return 1;
   }
-  const dim3 gr((unsigned)cdiv(g.ny + 2, BX), (unsigned)cdiv(g.nx + 2, BY));
-  if (fs_ensure_part(c, (size_t)gr.x * gr.y * 4)) return 1;
+  const unsigned gr = persist_blocks(g.nx + 2, g.ny + 2);
+  if (fs_ensure_part(c, (size_t)gr * 4)) return 1;
   k_build_l0<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_RHO_U], c->f[FSGPU_RHO_V], s->L[0].v, g,
                                                  s->o.psd, c->part, c->ticket, c->red_out + 4);
   FS_LAUNCHED();

@@ -10,6 +10,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import weakref
 
 import numpy as np
 
@@ -158,11 +159,17 @@ class FS:
         self.L = load()
         self.nx, self.ny, self.dx, self.dy = int(nx), int(ny), float(dx), float(dy)
         self.h = C.c_void_p()
+        self._solvers = []  # weak refs: solvers hold device state of this context
         _chk(self.L.fsgpu_create(self.nx, self.ny, self.dx, self.dy, device, C.byref(self.h)))
         self.set_props(rho_gas, rho_liquid, visc_gas, visc_liquid, sigma)
 
     def close(self):
         if getattr(self, "h", None) and self.h.value:
+            for w in self._solvers:  # a solver must go before its context (any GC order)
+                ps = w()
+                if ps is not None:
+                    ps.close()
+            self._solvers = []
             self.L.fsgpu_destroy(self.h)
             self.h = C.c_void_p()
 
@@ -295,6 +302,7 @@ class LinearSolver:
         self.h = C.c_void_p()
         o = PsOpts(tol, max_iter, psd, relax, max_levels, skip_relax)
         _chk(self.L.fsgpu_ps_create(fs.h, C.byref(o), C.byref(self.h)))
+        fs._solvers.append(weakref.ref(self))
 
     def close(self):
         if getattr(self, "h", None) and self.h.value:
