@@ -26,6 +26,11 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# CPU-baseline protocol: all host cores, threads pinned.  Must be in the
+# environment before any OpenMP runtime is loaded (without binding, 8 spinning threads on this
+# container's 8 vCPUs ran the reference 4x slower).
+os.environ.setdefault("OMP_PROC_BIND", "close")
+os.environ.setdefault("OMP_PLACES", "cores")
 
 NSUB, TOL, MAX_ITER, CFL, DT_MAX = 5, 1e-6, 50, 0.9, 0.1
 CPU_SAMPLE_N = 2048  # grid of the bounded CPU sample (reference instantiation in ref_harness_sizes.inc)
@@ -130,3 +135,166 @@ def cpu_leg(steps, warmup, n=CPU_SAMPLE_N):
             "sample": f"lid-driven cavity {n}^2, {steps} timesteps x {NSUB} sub-iterations after {warmup} warm-up, "
                       f"{its / max(steps * NSUB, 1):.1f} PCG its/solve, OpenMP threads = {cores}",
             "ms_per_step": el / steps * 1e3}
+
+
+# ---- algorithmic bytes per cell of each kernel class (DESIGN.md "Kernels and rooflines") -------
+# doubles moved once per launch by the algorithm as implemented (8 B each), per fine-level cell
+ALGO_BYTES = {
+    "matvec_dot": 40.0,        # read p, d, cx, cy; write s
+    "xr_update": 48.0,         # read x, p, r, s; write x, r
+    "p_update": 24.0,          # read z, p; write p
+    "vcycle_down_l0": 40.0,    # read r, dinv, cx, cy, pc(F rows: 0.5); write b_coarse (0.5)
+    "vcycle_up_l0": 56.0,      # read r, dinv, d, cx, cy, pc (0.5), x_coarse (0.5); write z
+    "momentum": 112.0,         # 12 fields read, U and V written
+    "div_rhs": 48.0,           # read U, V; write div, rhs; second pass rhs -= mean (read + write)
+    "shift_correct": 104.0,    # sum dp (1), dp -= c (2), read dp, p, U, V, rho_u, rho_v; write p, U, V (10)
+}
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    n_gpus = a.gpus
+    if a.impl == "reference":
+        if rank != 0:
+            return 0
+        cb = cpu_leg(max(a.steps, 1), min(a.warmup, 1))
+        line = {"impl": "reference", "metric": "timestep MCell-updates/s (FP64, incl. Poisson solve)",
+                "value": cb["value"], "unit": "MCell-updates/s", "n_gpus": n_gpus, "steps": a.steps,
+                "warmup": min(a.warmup, 1), "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"lid-driven cavity (scaling/LidDrivenFlow.cpp constants), bounded sample "
+                                       f"{CPU_SAMPLE_N}^2 of the 8192^2 workload, NUM_SUBITER {NSUB}, PCG+PFMG tol {TOL}"},
+                "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": cb["value"], "unit": "MCell-updates/s", "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line), flush=True)
+        return 0
+
+    import numpy as np
+    import torch
+    import fluidsolver_b200 as F
+
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    n = a.n or 8192
+    if world > 1:
+        raise SystemExit("multi-GPU slab decomposition is not wired into bench.py yet (see DESIGN.md)")
+
+    fs = F.FS(n, n, 1.0 / n, 1.0 / n, 1.0, 1.0, 1e-3, 1e-3, device=local)
+    fs.calc_rho_visc_const()
+    for s, u in enumerate((0.0, 0.0, 0.0, 1.0)):
+        fs.set_bconds(s, F.DIRICHLET, u, 0.0)
+    fs.apply_velocity_bconds()
+    ps = F.LinearSolver(fs, tol=TOL, max_iter=MAX_ITER, max_levels=max(a.max_levels, 0))
+    ps.set_pressure_operator()
+    stream = torch.cuda.ExternalStream(fs.stream(), device=torch.device("cuda", local))
+
+    def one_step():
+        dt = fs.adjust_dt(CFL, DT_MAX)
+        return fs.step(ps, dt, NSUB)
+
+    for _ in range(a.warmup):
+        one_step()
+    prof_cls = a.prof or "vcycle_up_l0"
+    F.prof_enable((prof_cls,))
+    F.prof_read()
+    clocks = ClockSampler(local)
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    fs.sync()
+    torch.cuda.synchronize()
+    l0 = F.launch_count()
+    e0.record(stream)
+    its = 0
+    for _ in range(a.steps):
+        _, it = one_step()
+        its += it
+    e1.record(stream)
+    fs.sync()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    launches = F.launch_count() - l0
+    clk = clocks.stop()
+    prof = F.prof_read()
+    F.prof_enable(())
+    value = n * n * a.steps / (ms * 1e-3) / 1e6
+    k_bar = its / (a.steps * NSUB)
+
+    # roofline of the dominant kernel, timed live with CUDA events on the launching stream
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    cells = (n + 2) * (n + 2)
+    kms, kcnt = prof.get(prof_cls, (0.0, 0))
+    achieved = ALGO_BYTES[prof_cls] * cells / (kms / max(kcnt, 1) * 1e-3) / 1e9 if kcnt else None
+    roofline = {"bound": "hbm", "kernel": prof_cls, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak if achieved else None, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
+                "algorithmic_bytes_per_launch": ALGO_BYTES[prof_cls] * cells,
+                "avg_launch_us": kms / max(kcnt, 1) * 1e3, "launches_timed": kcnt,
+                "share_of_step": kms / ms if ms else None}
+    # whole-step roofline: SURVEY.md section 8d  B_step(k) = NSUB (232 + 160 + 264 k) + 120 bytes per cell
+    b_step = NSUB * (232 + 160 + 264 * k_bar) + 120
+    step_gbs = b_step * n * n * a.steps / (ms * 1e-3) / 1e9
+    roofline["step_algorithmic_GBs"] = step_gbs
+    roofline["step_frac"] = step_gbs / peak
+
+    # e2e: the same step through the C ABI with HOST buffers (pinned), copies inside the timed region
+    e2e = None
+    if not a.no_e2e:
+        names = ("U", "V", "P")
+        host = {}
+        for nm in names:
+            t = torch.empty(F.field_shape(nm, n, n), dtype=torch.float64, pin_memory=True)
+            host[nm] = t.numpy()
+            fs.download(nm, host[nm])
+        ke = max(1, min(a.steps, 3))
+        nbytes = sum(h.nbytes for h in host.values())
+        fs.sync()
+        t0 = time.perf_counter()
+        for _ in range(ke):
+            for nm in names:
+                fs.upload(nm, host[nm])
+            one_step()
+            for nm in names:
+                fs.download(nm, host[nm])
+        fs.sync()
+        el = time.perf_counter() - t0
+        e2e = {"value": n * n * ke / el / 1e6, "unit": "MCell-updates/s", "h2d_bytes_per_step": nbytes,
+               "d2h_bytes_per_step": nbytes, "steps": ke, "ms_per_step": el / ke * 1e3,
+               "api": "fsgpu_upload(U,V,P) -> fsgpu_adjust_dt -> fsgpu_step -> fsgpu_download(U,V,P), pinned host buffers"}
+    umax = fs.abs_max("U")
+    ps.close()
+    fs.close()
+
+    cpu = None
+    if rank == 0 and n_gpus == 1 and not a.no_cpu:
+        cpu = cpu_leg(2, 1)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+
+    line = {"metric": "timestep MCell-updates/s (FP64, incl. Poisson solve)", "value": value,
+            "unit": "MCell-updates/s", "n_gpus": n_gpus, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"lid-driven cavity {n}^2 (scaling/LidDrivenFlow.cpp:16-42), NUM_SUBITER {NSUB}, "
+                                   f"PCG tol {TOL} max_iter {MAX_ITER}, CFL {CFL}",
+                       "pcg_iters_per_solve": k_bar, "mg_levels": None, "l2": "inputs larger than L2 "
+                       f"(each field {cells * 8 / 1e6:.0f} MB vs 126 MB L2)", "max_abs_U": umax},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

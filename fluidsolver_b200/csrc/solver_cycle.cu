@@ -64,6 +64,121 @@ k_down(const LevelDev f, const double* __restrict__ fb, const LevelDev c, double
   cb[c.idx(ci, cj)] = v;
 }
 
+// ---- marching restriction kernels (same strip / chunk scheme as k_up_march below) -------------
+// k_down_march0: coarsening along i.  Per fine row the warp forms X = w b / d, then the residual
+// R of the row above from three rows of X held in registers (left/right by shuffle), and on every
+// second row the coarse rhs  b_c = R + pp(row-1) R(row-1) + pm(row+1) R(row+1).
+template <bool ACTIVE>
+__global__ void __launch_bounds__(128, 8)
+k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
+              double* __restrict__ cb, double w, int mrc, const PcgScal* scal) {
+  if (scal->done) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n1 = (int)f.n1, n0c = (int)c.n0, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  const int strips = (n1 + 119) / 120;
+  const int total  = strips * ((n0c + mrc - 1) / mrc);
+  for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    const int ch = t / strips, sp = t - ch * strips;
+    int lj = sp * 120 + warp * 30 - 1 + lane;
+    const bool store_lane = lane >= 1 && lane <= 30 && lj < n1;
+    if (lj > n1) lj = n1;
+    const int c0 = ch * mrc, c1 = min(c0 + mrc, n0c);
+    const int f0 = 2 * c0 + foff, fL = 2 * (c1 - 1) + foff;
+    double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx2 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0, Ra = 0.0, Rb = 0.0;
+    int li = f0 - 2;
+    int o  = (li + FS_RO) * P + lj + FS_CO;
+#pragma unroll 2
+    for (; li <= fL + 2; ++li, o += P) {
+      const double b0 = __ldg(fb + o), cx0 = __ldg(f.cx + o);
+      double X0 = 0.0, cy0 = 0.0, cy0p = 0.0;
+      if (ACTIVE) {
+        X0   = w * b0 * __ldg(f.dinv + o);
+        cy0  = __ldg(f.cy + o);
+        cy0p = __ldg(f.cy + o + 1);
+      }
+      // residual of row li - 1
+      double Rn;
+      if (ACTIVE) {
+        const double xl = __shfl_up_sync(0xffffffffu, X1, 1), xr = __shfl_down_sync(0xffffffffu, X1, 1);
+        double v = w * b1;
+        v += cx1 * X2;
+        v += cx0 * X0;
+        v += cy1 * xl;
+        v += cy1p * xr;
+        Rn = b1 - v;
+      } else {
+        Rn = b1;
+      }
+      // coarse point on row li - 2 (a C row when li - f0 is even)
+      if (li >= f0 + 2 && ((li - f0) & 1) == 0) {
+        const double pcm = __ldg(f.pc + o - 3 * P), pcp = __ldg(f.pc + o - P);
+        double v = Rb;
+        v += (-cx2 * pcm) * Ra;
+        v += (-cx1 * pcp) * Rn;
+        if (store_lane) cb[(((li - 2 - foff) >> 1) + FS_RO) * Pc + lj + FS_CO] = v;
+      }
+      X2 = X1; X1 = X0; b1 = b0; cx2 = cx1; cx1 = cx0; cy1 = cy0; cy1p = cy0p; Ra = Rb; Rb = Rn;
+    }
+  }
+}
+
+// k_down_march1: coarsening along j.  Lanes 1..30 hold a valid residual (X of the neighbours by
+// shuffle), lanes 2..29 that sit on a C column emit  b_c = R + pp(j-1) R(j-1) + pm(j+1) R(j+1).
+template <bool ACTIVE>
+__global__ void __launch_bounds__(128, 8)
+k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
+              double* __restrict__ cb, double w, int mr, const PcgScal* scal) {
+  if (scal->done) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n0 = (int)f.n0, n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  const int strips = (n1 + 111) / 112;
+  const int total  = strips * ((n0 + mr - 1) / mr);
+  for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    const int ch = t / strips, sp = t - ch * strips;
+    int lj = sp * 112 + warp * 28 - 2 + lane;
+    const int pos = lj - foff;
+    const bool store_lane = lane >= 2 && lane <= 29 && lj < n1 && (pos & 1) == 0;
+    const int oc_col = (pos >> 1) + FS_CO;
+    if (lj > n1) lj = n1;
+    const int r0 = ch * mr, r1 = min(r0 + mr, n0);
+    double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0;
+    int li = r0 - 1;
+    int o  = (li + FS_RO) * P + lj + FS_CO;
+#pragma unroll 2
+    for (; li <= r1; ++li, o += P) {
+      const double b0 = __ldg(fb + o);
+      const double cy0 = __ldg(f.cy + o), cy0p = __ldg(f.cy + o + 1);
+      double X0 = 0.0, cx0 = 0.0;
+      if (ACTIVE) {
+        X0  = w * b0 * __ldg(f.dinv + o);
+        cx0 = __ldg(f.cx + o);
+      }
+      if (li > r0) {  // row li - 1
+        double Rn;
+        if (ACTIVE) {
+          const double xl = __shfl_up_sync(0xffffffffu, X1, 1), xr = __shfl_down_sync(0xffffffffu, X1, 1);
+          double v = w * b1;
+          v += cx1 * X2;
+          v += cx0 * X0;
+          v += cy1 * xl;
+          v += cy1p * xr;
+          Rn = b1 - v;
+        } else {
+          Rn = b1;
+        }
+        const double pcv = __ldg(f.pc + o - P);
+        const double pcl = __shfl_up_sync(0xffffffffu, pcv, 1), pcr = __shfl_down_sync(0xffffffffu, pcv, 1);
+        const double Rl = __shfl_up_sync(0xffffffffu, Rn, 1), Rr = __shfl_down_sync(0xffffffffu, Rn, 1);
+        double v = Rn;
+        v += (-cy1 * pcl) * Rl;
+        v += (-cy1p * pcr) * Rr;
+        if (store_lane) cb[(li - 1 + FS_RO) * Pc + oc_col] = v;
+      }
+      X2 = X1; X1 = X0; b1 = b0; cx1 = cx0; cy1 = cy0; cy1p = cy0p;
+    }
+  }
+}
+
 // value at fine point (li, lj) after [zero-guess relaxation] + interpolation of the coarse x
 // (bq = rhs at the point, only used when ACTIVE)
 template <int CDIR, bool ACTIVE>
@@ -101,84 +216,86 @@ k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
   fx[k] = x_interp<CDIR, false>(f, 0.0, c, cxv, li, lj, k, 0.0);
 }
 
-// active level: x0 = w b / d + P x_c is formed ONCE per point in a shared-memory tile
-// (32 rows x 64 columns + a one-point ring), then x = x0 + w (b - A x0) / d reads its four
-// neighbours from the tile.  A CTA walks tiles with a grid stride (persistent), so the optional
-// dot product <b, x> (= <r, z> of PCG on level 0) ends in ~600 partials.
+// active level, "marching" formulation.  A warp owns a strip of 32 consecutive columns (30 of
+// them produce output, lanes 0 and 31 are the left/right halo) and walks down MR rows.  Per row
+// it forms  x0 = w b / d + P x_c  ONCE per point, keeps x0 of three consecutive rows in
+// registers, takes the left/right neighbours by warp shuffle, and emits
+// x = x0 + w (b - A x0) / d  for the row above.  No shared memory, no block barrier, 32-bit
+// offsets advanced by one pitch per row; every array is read once (plus the 2/32 column and
+// 2/MR row overlap).  CTAs loop over (strip, chunk) tasks, so the optional dot product <b, x>
+// (= <r, z> of PCG on level 0) ends in ~1e3 partials.
 // DOT: 0 none, 1 PCG iteration (convergence test + beta), 2 first V-cycle (bi).
-constexpr int UT_I = 32, UT_J = 64, UT_Y = 4, UT_SW = UT_J + 2, UT_PER = UT_I / UT_Y;
+constexpr int MOUT = 30, MWARPS = 4;
 
 template <int CDIR, int DOT>
-__global__ void __launch_bounds__(UT_J* UT_Y, 3)
-k_up_tiled(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
-           const double* __restrict__ cxv, double w, PcgScal* scal, double* part,
+__global__ void __launch_bounds__(32 * MWARPS, 8)
+k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
+           const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part,
            unsigned int* ticket) {
   if (scal->done) return;
-  __shared__ double sx[(UT_I + 2) * UT_SW];
-  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * UT_J + tx;
-  const int64_t tiles_j = (f.n1 + UT_J - 1) / UT_J, nt = tiles_j * ((f.n0 + UT_I - 1) / UT_I);
-  const int64_t P = f.pitch;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n0 = (int)f.n0, n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  const int strips = (n1 + MOUT * MWARPS - 1) / (MOUT * MWARPS);
+  const int total  = strips * ((n0 + mr - 1) / mr);
   double acc[1] = {0.0};
-  for (int64_t t = blockIdx.x; t < nt; t += gridDim.x) {
-    const int64_t ti = t / tiles_j, tj = t - ti * tiles_j;
-    const int64_t i0 = ti * UT_I, j0 = tj * UT_J;
-    const int64_t lj = j0 + tx;
-    double bv[UT_PER], x0v[UT_PER];
-    // phase 1a: this thread's own points
-#pragma unroll
-    for (int m = 0; m < UT_PER; ++m) {
-      const int r = ty + UT_Y * m;
-      const int64_t li = i0 + r;
-      double b = 0.0, x0 = 0.0;
-      if (li < f.n0 && lj < f.n1) {
-        const int64_t k = f.idx(li, lj);
-        b  = __ldg(fb + k);
-        x0 = x_interp<CDIR, true>(f, b, c, cxv, li, lj, k, w);
+  for (int t = blockIdx.x; t < total; t += gridDim.x) {
+    const int ch = t / strips, sp = t - ch * strips;
+    int lj = sp * (MOUT * MWARPS) + warp * MOUT - 1 + lane;  // lane 0 sits one column left
+    const bool store_lane = lane >= 1 && lane <= MOUT && lj < n1;
+    if (lj > n1) lj = n1;  // the zero pad column right of the grid
+    const int r0 = ch * mr, r1 = min(r0 + mr, n0);
+    double x0p = 0.0, x0c = 0.0, bc = 0.0, dic = 0.0, cyc = 0.0, cy1c = 0.0, cxc = 0.0;
+    int li = r0 - 1;
+    int o  = (li + FS_RO) * P + lj + FS_CO;
+    double cxn = __ldg(f.cx + o);
+#pragma unroll 2
+    for (; li <= r1; ++li, o += P) {
+      const double cxnn = __ldg(f.cx + o + P);
+      const double bn = __ldg(fb + o), din = __ldg(f.dinv + o);
+      const double cyn = __ldg(f.cy + o), cy1n = __ldg(f.cy + o + 1);
+      double xi;
+      if (CDIR == 0) {
+        const int pos = li - foff, par = pos & 1;
+        const int oc  = (((pos - par) >> 1) + FS_RO) * Pc + lj + FS_CO;
+        const double xm = __ldg(xc + oc);
+        if (par == 0) {  // C row (warp uniform)
+          xi = xm;
+        } else {
+          const double pcv = __ldg(f.pc + o), xp = __ldg(xc + oc + Pc);
+          double v = (-cxn * pcv) * xm;
+          v += (-cxnn * pcv) * xp;
+          xi = v;
+        }
+      } else {
+        const int pos = lj - foff, par = pos & 1;
+        const int oc  = (li + FS_RO) * Pc + ((pos - par) >> 1) + FS_CO;
+        const double xm = __ldg(xc + oc), xp = __ldg(xc + oc + 1), pcv = __ldg(f.pc + o);
+        double v = (-cyn * pcv) * xm;
+        v += (-cy1n * pcv) * xp;
+        xi = par ? v : xm;
       }
-      bv[m] = b;
-      x0v[m] = x0;
-      sx[(r + 1) * UT_SW + tx + 1] = x0;
-    }
-    // phase 1b: the ring (2 rows of UT_SW + 2 columns of UT_I = 196 points), one per thread
-    if (tid < 2 * UT_SW + 2 * UT_I) {
-      int r, cc;
-      if (tid < UT_SW) { r = -1; cc = tid - 1; }
-      else if (tid < 2 * UT_SW) { r = UT_I; cc = tid - UT_SW - 1; }
-      else if (tid < 2 * UT_SW + UT_I) { r = tid - 2 * UT_SW; cc = -1; }
-      else { r = tid - 2 * UT_SW - UT_I; cc = UT_J; }
-      const int64_t li = i0 + r, l2 = j0 + cc;
-      double x0 = 0.0;
-      if (li >= 0 && li < f.n0 && l2 >= 0 && l2 < f.n1) {
-        const int64_t k = f.idx(li, l2);
-        x0 = x_interp<CDIR, true>(f, __ldg(fb + k), c, cxv, li, l2, k, w);
+      const double x0n = w * bn * din + xi;
+      if (li > r0) {  // emit row li - 1
+        const double dd = __ldg(f.d + o - P);
+        const double xl = __shfl_up_sync(0xffffffffu, x0c, 1), xr = __shfl_down_sync(0xffffffffu, x0c, 1);
+        double v = dd * x0c;
+        v += cxc * x0p;
+        v += cxn * x0n;
+        v += cyc * xl;
+        v += cy1c * xr;
+        const double xo = x0c + w * (bc - v) * dic;
+        if (store_lane) {
+          fx[o - P] = xo;
+          if (DOT) acc[0] += bc * xo;
+        }
       }
-      sx[(r + 1) * UT_SW + cc + 1] = x0;
+      x0p = x0c; x0c = x0n; bc = bn; dic = din; cyc = cyn; cy1c = cy1n; cxc = cxn; cxn = cxnn;
     }
-    __syncthreads();
-    // phase 2: post-relaxation
-#pragma unroll
-    for (int m = 0; m < UT_PER; ++m) {
-      const int r = ty + UT_Y * m;
-      const int64_t li = i0 + r;
-      if (li < f.n0 && lj < f.n1) {
-        const int64_t k = f.idx(li, lj);
-        const int sm = (r + 1) * UT_SW + tx + 1;
-        double v = __ldg(f.d + k) * x0v[m];
-        v += __ldg(f.cx + k) * sx[sm - UT_SW];
-        v += __ldg(f.cx + k + P) * sx[sm + UT_SW];
-        v += __ldg(f.cy + k) * sx[sm - 1];
-        v += __ldg(f.cy + k + 1) * sx[sm + 1];
-        const double xo = x0v[m] + w * (bv[m] - v) * __ldg(f.dinv + k);
-        fx[k] = xo;
-        if (DOT) acc[0] += bv[m] * xo;
-      }
-    }
-    __syncthreads();  // the tile is overwritten by the next iteration
   }
   if (DOT) {
     double tot[1];
     if (grid_reduce<ReduceSum, 1>(acc, part, ticket, tot)) {
-      if (tid == 0) pcg_after_rz<DOT == 2>(scal, tot[0]);
+      if (threadIdx.x == 0) pcg_after_rz<DOT == 2>(scal, tot[0]);
     }
   }
 }
@@ -312,10 +429,38 @@ static int coarse_solve(fsgpu_ps* s, int l, const double* b, double* x) {
   return 0;
 }
 
-static unsigned up_blocks(const LevelDev& v) {
-  const int64_t nt = cdiv(v.n1, UT_J) * cdiv(v.n0, UT_I);
-  const int64_t cap = (int64_t)FS_NUM_SMS * 3;
-  return (unsigned)(nt < cap ? nt : cap);
+// rows per marching task: 64 when that still gives every SM several tasks, else smaller chunks
+// (more halo-row overlap, but small levels are latency bound, not bandwidth bound)
+static int pick_rows(int64_t rows, int64_t strips) {
+  int mr = 64;
+  while (mr > 4 && strips * cdiv(rows, mr) < (int64_t)FS_NUM_SMS * 16) mr >>= 1;
+  return mr;
+}
+static unsigned march_blocks(int64_t rows, int64_t strips, int mr) {
+  const int64_t total = strips * cdiv(rows, mr);
+  const int64_t cap = (int64_t)FS_NUM_SMS * 8;
+  return (unsigned)(total < cap ? (total > 0 ? total : 1) : cap);
+}
+
+static int launch_down(fsgpu_ps* s, int l, const double* fb) {
+  cudaStream_t st = s->c->stream;
+  Level* L        = s->L;
+  const LevelDev &f = L[l].v, &c = L[l + 1].v;
+  if (L[l].cdir == 0) {
+    const int64_t strips = cdiv(f.n1, 120);
+    const int mrc = pick_rows(c.n0, strips);
+    const unsigned nb = march_blocks(c.n0, strips, mrc);
+    if (L[l].active) k_down_march0<true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal);
+    else k_down_march0<false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal);
+  } else {
+    const int64_t strips = cdiv(f.n1, 112);
+    const int mr = pick_rows(f.n0, strips);
+    const unsigned nb = march_blocks(f.n0, strips, mr);
+    if (L[l].active) k_down_march1<true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal);
+    else k_down_march1<false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal);
+  }
+  FS_LAUNCHED();
+  return 0;
 }
 
 template <int CDIR>
@@ -328,12 +473,14 @@ static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_m
     FS_LAUNCHED();
     return 0;
   }
-  const unsigned nb = up_blocks(L[l].v);
-  const dim3 bl(UT_J, UT_Y);
-#define UP_ARGS L[l].v, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, s->scal, c->part, c->ticket
-  if (dot_mode == 1) k_up_tiled<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
-  else if (dot_mode == 2) k_up_tiled<CDIR, 2><<<nb, bl, 0, st>>>(UP_ARGS);
-  else k_up_tiled<CDIR, 0><<<nb, bl, 0, st>>>(UP_ARGS);
+  const int64_t strips = cdiv(L[l].v.n1, MOUT * MWARPS);
+  const int mr      = pick_rows(L[l].v.n0, strips);
+  const unsigned nb = march_blocks(L[l].v.n0, strips, mr);
+  const int bl = 32 * MWARPS;
+#define UP_ARGS L[l].v, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket
+  if (dot_mode == 1) k_up_march<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
+  else if (dot_mode == 2) k_up_march<CDIR, 2><<<nb, bl, 0, st>>>(UP_ARGS);
+  else k_up_march<CDIR, 0><<<nb, bl, 0, st>>>(UP_ARGS);
 #undef UP_ARGS
   FS_LAUNCHED();
   return 0;
@@ -359,8 +506,7 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
   for (int l = 0; l <= nl - 2; ++l) {
     const double* fb = l == 0 ? r : L[l].v.b;
     ProfScope ps_(l == 0 ? PROF_DOWN0 : PROF_DOWN, st);
-    DISPATCH(k_down, L[l].cdir, L[l].active, lvl_grid(L[l + 1].v), L[l].v, fb, L[l + 1].v,
-             L[l + 1].v.b, L[l].weight, s->scal);
+    if (launch_down(s, l, fb)) return 1;
   }
   {
     ProfScope ps_(PROF_COARSE, st);
