@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
 #include <new>
 #include <set>
 #include <vector>
@@ -88,11 +89,30 @@ int fsgpu_device_count(int* n) {
   return 0;
 }
 
-int fsgpu_create(int64_t nx, int64_t ny, double dx, double dy, int device, fsgpu_ctx** out) {
+int fsgpu_slab_range(int64_t nx, int rank, int nranks, int64_t* a_lo, int64_t* a_hi) {
+  if (nranks < 1 || rank < 0 || rank >= nranks || nx < 2) {
+    fs_set_error("fsgpu_slab_range: bad arguments (rank %d of %d)", rank, nranks);
+    return 1;
+  }
+  const int64_t n = nx + 2;
+  if (n / nranks < 2 * FS_RO) {
+    fs_set_error("fsgpu_slab_range: %lld rows over %d ranks leaves fewer than %d rows per slab",
+                 (long long)n, nranks, 2 * FS_RO);
+    return 1;
+  }
+  if (a_lo) *a_lo = n * rank / nranks;
+  if (a_hi) *a_hi = n * (rank + 1) / nranks;
+  return 0;
+}
+
+int fsgpu_create_slab(int64_t nx, int64_t ny, double dx, double dy, int device, int rank, int nranks,
+                      const void* id128, int transport, fsgpu_ctx** out) {
   if (!out || nx < 2 || ny < 2 || !(dx > 0) || !(dy > 0)) {
     fs_set_error("fsgpu_create: bad arguments (nx=%lld ny=%lld)", (long long)nx, (long long)ny);
     return 1;
   }
+  int64_t a_lo, a_hi;
+  if (fsgpu_slab_range(nx, rank, nranks, &a_lo, &a_hi)) return 1;
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
     fs_set_error("fsgpu_create: no CUDA device (this library has no CPU fallback)");
@@ -103,27 +123,37 @@ int fsgpu_create(int64_t nx, int64_t ny, double dx, double dy, int device, fsgpu
   if (!c) { fs_set_error("out of host memory"); return 1; }
   c->device = device;
   c->g.nx = nx; c->g.ny = ny; c->g.dx = dx; c->g.dy = dy;
+  c->g.a_lo = a_lo; c->g.a_hi = a_hi;
   c->g.pitch = (ny + 3 + FS_CO + 2 + 15) / 16 * 16;
-  c->g.rows  = nx + 3 + 2 * FS_RO;
+  c->g.rows  = (a_hi - a_lo) + 1 + 2 * FS_RO;
   const size_t n = (size_t)c->g.count();
   const int nf = FSGPU_NUM_FIELDS + 2;
   FS_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   FS_CUDA(cudaMalloc(&c->slab, n * nf * sizeof(double)));
   FS_CUDA(cudaMemsetAsync(c->slab, 0, n * nf * sizeof(double), c->stream));
-  for (int f = 0; f < FSGPU_NUM_FIELDS; ++f) c->f[f] = c->slab + n * f;
-  c->U_alt = c->slab + n * FSGPU_NUM_FIELDS;
-  c->V_alt = c->slab + n * (FSGPU_NUM_FIELDS + 1);
+  for (int f = 0; f < FSGPU_NUM_FIELDS; ++f) c->f[f] = c->slab + n * f - c->g.voff();
+  c->U_alt = c->slab + n * FSGPU_NUM_FIELDS - c->g.voff();
+  c->V_alt = c->slab + n * (FSGPU_NUM_FIELDS + 1) - c->g.voff();
   FS_CUDA(cudaMalloc(&c->ticket, sizeof(unsigned int)));
   FS_CUDA(cudaMemsetAsync(c->ticket, 0, sizeof(unsigned int), c->stream));
   FS_CUDA(cudaMalloc(&c->red_out, 16 * sizeof(double)));
   FS_CUDA(cudaMemsetAsync(c->red_out, 0, 16 * sizeof(double), c->stream));
   FS_CUDA(cudaMallocHost(&c->h_red, 16 * sizeof(double)));
   FS_CUDA(cudaStreamSynchronize(c->stream));
+  if (comm_create(c, rank, nranks, id128, transport)) {
+    fsgpu_destroy(c);
+    return 1;
+  }
   *out = c;
   return 0;
 }
 
+int fsgpu_create(int64_t nx, int64_t ny, double dx, double dy, int device, fsgpu_ctx** out) {
+  return fsgpu_create_slab(nx, ny, dx, dy, device, 0, 1, nullptr, FSGPU_TRANSPORT_NCCL, out);
+}
+
 static std::set<fsgpu_ps*> g_live_solvers;  // so that destroy order (solver / context) is free
+static std::mutex g_live_mu;                // contexts may be driven by different host threads
 static int ps_destroy_impl(fsgpu_ps* s);
 
 int fsgpu_destroy(fsgpu_ctx* c) {
@@ -131,9 +161,13 @@ int fsgpu_destroy(fsgpu_ctx* c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   std::vector<fsgpu_ps*> mine;
-  for (fsgpu_ps* s : g_live_solvers)
-    if (s->c == c) mine.push_back(s);
+  {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    for (fsgpu_ps* s : g_live_solvers)
+      if (s->c == c) mine.push_back(s);
+  }
   for (fsgpu_ps* s : mine) ps_destroy_impl(s);
+  comm_destroy(c);
   for (int s = 0; s < 4; ++s) {
     if (c->bc[s].u_prof) cudaFree(c->bc[s].u_prof);
     if (c->bc[s].v_prof) cudaFree(c->bc[s].v_prof);
@@ -161,9 +195,12 @@ int fsgpu_upload(fsgpu_ctx* c, int field, const double* host) {
   FS_CHECK_FIELD(field);
   int64_t m, n;
   field_extent(c->g, field, &m, &n);
-  FS_CUDA(cudaMemcpy2DAsync(c->f[field] + c->g.idx(0, 0), c->g.pitch * sizeof(double), host,
-                            n * sizeof(double), n * sizeof(double), m, cudaMemcpyHostToDevice,
-                            c->stream));
+  // this rank's rows and its halo rows, straight from the global array
+  const int64_t r0 = c->g.a_lo - FS_RO > 0 ? c->g.a_lo - FS_RO : 0;
+  const int64_t r1 = c->g.a_hi + FS_RO < m ? c->g.a_hi + FS_RO : m;
+  FS_CUDA(cudaMemcpy2DAsync(c->f[field] + c->g.idx(r0, 0), c->g.pitch * sizeof(double),
+                            host + r0 * n, n * sizeof(double), n * sizeof(double), r1 - r0,
+                            cudaMemcpyHostToDevice, c->stream));
   // pageable host memory: the copy may still be staged when the call returns
   FS_CUDA(cudaStreamSynchronize(c->stream));
   return 0;
@@ -174,8 +211,10 @@ int fsgpu_download(fsgpu_ctx* c, int field, double* host) {
   FS_CHECK_FIELD(field);
   int64_t m, n;
   field_extent(c->g, field, &m, &n);
-  FS_CUDA(cudaMemcpy2DAsync(host, n * sizeof(double), c->f[field] + c->g.idx(0, 0),
-                            c->g.pitch * sizeof(double), n * sizeof(double), m,
+  // the rows this rank owns (a U-like field's extra row belongs to the last rank)
+  const int64_t r0 = c->g.a_lo, r1 = c->g.last() ? m : c->g.a_hi;
+  FS_CUDA(cudaMemcpy2DAsync(host + r0 * n, n * sizeof(double), c->f[field] + c->g.idx(r0, 0),
+                            c->g.pitch * sizeof(double), n * sizeof(double), r1 - r0,
                             cudaMemcpyDeviceToHost, c->stream));
   FS_CUDA(cudaStreamSynchronize(c->stream));
   return 0;
@@ -259,8 +298,8 @@ int fsgpu_adjust_dt(fsgpu_ctx* c, double cfl_max, double dt_max, double* dt) {
 }
 
 static int copy_field(fsgpu_ctx* c, int dst, int src) {
-  FS_CUDA(cudaMemcpyAsync(c->f[dst], c->f[src], (size_t)c->g.count() * sizeof(double),
-                          cudaMemcpyDeviceToDevice, c->stream));
+  FS_CUDA(cudaMemcpyAsync(alloc_base(c->g, c->f[dst]), alloc_base(c->g, c->f[src]),
+                          (size_t)c->g.count() * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
   return 0;
 }
 int fsgpu_save_old_velocity(fsgpu_ctx* c) {
@@ -316,7 +355,8 @@ int fsgpu_apply_neumann_bconds(fsgpu_ctx* c, int field) {
   FS_CHECK_FIELD(field);
   int64_t m, n;
   field_extent(c->g, field, &m, &n);
-  return fs_launch_neumann(c, c->f[field], m - 2, n - 2);
+  if (fs_launch_neumann(c, c->f[field], m - 2, n - 2)) return 1;
+  return fs_exchange_fields(c, &field, 1, FS_RO);
 }
 
 // ---- solver -----------------------------------------------------------------------------------
@@ -336,19 +376,28 @@ int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out) {
   FS_CUDA(cudaMemset(s->scal, 0, sizeof(PcgScal)));
   FS_CUDA(cudaMallocHost(&s->h_scal, 4 * sizeof(PcgScal)));
   for (int i = 0; i < 4; ++i) FS_CUDA(cudaEventCreateWithFlags(&s->ev[i], cudaEventDisableTiming));
-  g_live_solvers.insert(s);
+  {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    g_live_solvers.insert(s);
+  }
   *out = s;
   return 0;
 }
 
 int fsgpu_ps_destroy(fsgpu_ps* s) {
   // a solver already torn down with its context (fsgpu_destroy) is a no-op here
-  if (!s || !g_live_solvers.count(s)) return 0;
+  {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    if (!s || !g_live_solvers.count(s)) return 0;
+  }
   return ps_destroy_impl(s);
 }
 
 static int ps_destroy_impl(fsgpu_ps* s) {
-  g_live_solvers.erase(s);
+  {
+    std::lock_guard<std::mutex> lk(g_live_mu);
+    if (!g_live_solvers.erase(s)) return 0;
+  }
   cudaSetDevice(s->c->device);
   cudaStreamSynchronize(s->c->stream);
   cudaFree(s->slab);
@@ -381,6 +430,12 @@ int fsgpu_ps_solve(fsgpu_ps* s, double* residual, int* iters) {
 int fsgpu_ps_num_levels(fsgpu_ps* s, int* n) {
   if (!s) { fs_set_error("null solver"); return 1; }
   *n = s->nl;
+  return 0;
+}
+
+int fsgpu_ps_num_distributed_levels(fsgpu_ps* s, int* n) {
+  if (!s) { fs_set_error("null solver"); return 1; }
+  *n = s->ld;
   return 0;
 }
 

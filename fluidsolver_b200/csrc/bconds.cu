@@ -27,6 +27,10 @@ __global__ void k_bc_lr(const BcArgs a, const Geom g) {
   const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int s     = blockIdx.y;  // 0 left, 1 right
   if (b > g.ny + 2) return;
+  // the left rows live on the first slab, the right rows on the last one.  x-periodic sides of a
+  // decomposed grid are filled by the wrap-around exchange in fs_launch_bconds instead.
+  if (s == 0 ? !g.first() : !g.last()) return;
+  if (a.kind[s] == FSGPU_BC_PERIODIC && !(g.first() && g.last())) return;
   const int64_t P = g.pitch;
   const bool in_u = b <= g.ny + 1;  // U rows have NY+2 entries, V rows NY+3
   // U: ghost row ag, boundary face row af, first interior-side row a1; V: ghost row vg, inner vi
@@ -70,9 +74,9 @@ __global__ void k_bc_lr(const BcArgs a, const Geom g) {
 
 // bottom (s = 2) and top (s = 3): thread a = i + 1 in [0, NX + 2]
 __global__ void k_bc_bt(const BcArgs a, const Geom g) {
-  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t r = g.a_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int s     = 2 + blockIdx.y;
-  if (r > g.nx + 2) return;
+  if (r >= g.u_hi()) return;
   const bool in_v = r <= g.nx + 1;  // V has NX+2 rows, U NX+3
   const int64_t ug = s == 2 ? 0 : g.ny + 1, ui = s == 2 ? 1 : g.ny;                      // U cols
   const int64_t bg = s == 2 ? 0 : g.ny + 2, bf = s == 2 ? 1 : g.ny + 1, b1 = s == 2 ? 2 : g.ny;  // V cols
@@ -111,24 +115,29 @@ __global__ void k_bc_bt(const BcArgs a, const Geom g) {
   }
 }
 
-// test/LaminarChannel.cpp:55-66 (sums over j = -1..NY) and :201-205; one block
-__global__ void k_outflow_fix(double* __restrict__ U, const double* __restrict__ ru, const Geom g,
-                              double* mass_error_out) {
+// test/LaminarChannel.cpp:55-66 (sums over j = -1..NY) and :201-205.  Two one-block kernels so
+// that a decomposed grid can combine the inlet sum (first slab) and the outlet sum (last slab)
+// in between: io[0] = inflow, io[1] = outflow.
+__global__ void k_outflow_sums(const double* __restrict__ U, const double* __restrict__ ru, const Geom g,
+                               double* io) {
   __shared__ double sm[32];
-  __shared__ double merr;
   double in = 0.0, out = 0.0;
   for (int64_t b = threadIdx.x; b <= g.ny + 1; b += blockDim.x) {
-    in += ru[g.idx(0, b)] * U[g.idx(0, b)];
-    out += ru[g.idx(g.nx + 2, b)] * U[g.idx(g.nx + 2, b)];
+    if (g.first()) in += ru[g.idx(0, b)] * U[g.idx(0, b)];
+    if (g.last()) out += ru[g.idx(g.nx + 2, b)] * U[g.idx(g.nx + 2, b)];
   }
   in  = block_reduce<ReduceSum>(in, sm);
   out = block_reduce<ReduceSum>(out, sm);
   if (threadIdx.x == 0) {
-    merr = out - in;
-    if (mass_error_out) *mass_error_out = merr;
+    io[0] = in;
+    io[1] = out;
   }
-  __syncthreads();
-  const double me = merr;
+}
+__global__ void k_outflow_apply(double* __restrict__ U, const double* __restrict__ ru, const Geom g,
+                                const double* io, double* mass_error_out) {
+  const double me = io[1] - io[0];
+  if (threadIdx.x == 0 && mass_error_out) *mass_error_out = me;
+  if (!g.last()) return;
   for (int64_t b = threadIdx.x; b <= g.ny + 1; b += blockDim.x) {
     const int64_t k = g.idx(g.nx + 2, b);
     U[k] -= me / (ru[k] * (double)(g.ny + 2));
@@ -139,12 +148,12 @@ __global__ void k_outflow_fix(double* __restrict__ U, const double* __restrict__
 __global__ void k_neumann_lr(double* f, int64_t m, int64_t n, const Geom g) {
   const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b > n + 1) return;
-  f[g.idx(0, b)]     = f[g.idx(1, b)];
-  f[g.idx(m + 1, b)] = f[g.idx(m, b)];
+  if (g.first()) f[g.idx(0, b)] = f[g.idx(1, b)];
+  if (g.last()) f[g.idx(m + 1, b)] = f[g.idx(m, b)];
 }
 __global__ void k_neumann_bt(double* f, int64_t m, int64_t n, const Geom g) {
-  const int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (a > m + 1) return;
+  const int64_t a = g.a_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (a > m + 1 || a >= g.u_hi()) return;
   f[g.idx(a, 0)]     = f[g.idx(a, 1)];
   f[g.idx(a, n + 1)] = f[g.idx(a, n)];
 }
@@ -161,13 +170,40 @@ int fs_launch_bconds(fsgpu_ctx* c) {
   a.V = c->f[FSGPU_V];
   k_bc_lr<<<dim3((unsigned)cdiv(c->g.ny + 3, 128), 2), 128, 0, c->stream>>>(a, c->g);
   FS_LAUNCHED();
-  k_bc_bt<<<dim3((unsigned)cdiv(c->g.nx + 3, 128), 2), 128, 0, c->stream>>>(a, c->g);
+  const Geom& g = c->g;
+  if (c->nranks > 1 && (c->bc[FSGPU_LEFT].kind == FSGPU_BC_PERIODIC || c->bc[FSGPU_RIGHT].kind == FSGPU_BC_PERIODIC)) {
+    // x-periodic wrap-around between the first and the last slab (BoundaryConditions.hpp:142-167):
+    // left ghosts U(-1,.) = U(NX-1,.), V(-1,.) = V(NX-1,.); right ghosts U(NX+1,.) = U(1,.), V(NX,.) = V(0,.)
+    if (c->bc[FSGPU_LEFT].kind != c->bc[FSGPU_RIGHT].kind) {
+      fs_set_error("periodic left/right sides must come as a pair");
+      return 1;
+    }
+    const double* snd[2];
+    double* rcv[2];
+    int peer = -1;
+    if (g.first()) {
+      peer = c->nranks - 1;
+      snd[0] = a.U + g.idx(2, 0) - FS_CO;  rcv[0] = a.U + g.idx(0, 0) - FS_CO;
+      snd[1] = a.V + g.idx(1, 0) - FS_CO;  rcv[1] = a.V + g.idx(0, 0) - FS_CO;
+    } else if (g.last()) {
+      peer = 0;
+      snd[0] = a.U + g.idx(g.nx, 0) - FS_CO;  rcv[0] = a.U + g.idx(g.nx + 2, 0) - FS_CO;
+      snd[1] = a.V + g.idx(g.nx, 0) - FS_CO;  rcv[1] = a.V + g.idx(g.nx + 1, 0) - FS_CO;
+    }
+    if (comm_sendrecv(c, peer, snd, rcv, 2, g.pitch)) return 1;
+  }
+  k_bc_bt<<<dim3((unsigned)cdiv(g.u_hi() - g.a_lo, 128), 2), 128, 0, c->stream>>>(a, g);
   FS_LAUNCHED();
-  return 0;
+  const int fl[2] = {FSGPU_U, FSGPU_V};
+  return fs_exchange_fields(c, fl, 2, 1);
 }
 
 int fs_launch_outflow_fix(fsgpu_ctx* c, double* d_mass_error) {
-  k_outflow_fix<<<1, 1024, 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_RHO_U], c->g, d_mass_error);
+  double* io = c->red_out + 8;
+  k_outflow_sums<<<1, 1024, 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_RHO_U], c->g, io);
+  FS_LAUNCHED();
+  if (comm_allreduce(c, io, 2, COMM_SUM)) return 1;  // inflow lives on the first slab, outflow on the last
+  k_outflow_apply<<<1, 1024, 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_RHO_U], c->g, io, d_mass_error);
   FS_LAUNCHED();
   return 0;
 }
@@ -175,7 +211,7 @@ int fs_launch_outflow_fix(fsgpu_ctx* c, double* d_mass_error) {
 int fs_launch_neumann(fsgpu_ctx* c, double* f, int64_t m, int64_t n) {
   k_neumann_lr<<<(unsigned)cdiv(n + 2, 128), 128, 0, c->stream>>>(f, m, n, c->g);
   FS_LAUNCHED();
-  k_neumann_bt<<<(unsigned)cdiv(m + 2, 128), 128, 0, c->stream>>>(f, m, n, c->g);
+  k_neumann_bt<<<(unsigned)cdiv(c->g.u_hi() - c->g.a_lo, 128), 128, 0, c->stream>>>(f, m, n, c->g);
   FS_LAUNCHED();
   return 0;
 }

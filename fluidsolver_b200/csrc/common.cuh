@@ -19,15 +19,31 @@
 #define FS_RO 2
 #define FS_CO 4
 
+//
+// Slab decomposition.  A context owns the ghost-inclusive rows
+// a in [a_lo, a_hi) of the GLOBAL grid (one rank: [0, nx + 2)); U-like fields have one more row
+// (a = nx + 2), owned by the last rank.  Kernels keep addressing rows by their GLOBAL index: the
+// field pointers handed to them are "virtual" bases (allocation base - a_lo * pitch), so
+// idx(a, b) lands inside the local allocation for a in [a_lo - FS_RO, a_hi + 1 + FS_RO).  The
+// FS_RO rows above/below the owned range are zero pads at a physical boundary and halo rows
+// (copies of the neighbour rank's rows) at an interior slab boundary; either way a stencil reads
+// them without a branch.
 struct Geom {
-  int64_t nx, ny;   // interior cells
-  int64_t pitch;    // doubles per row
-  int64_t rows;     // allocated rows = nx + 3 + 2 * FS_RO
+  int64_t nx, ny;      // interior cells of the GLOBAL grid
+  int64_t pitch;       // doubles per row
+  int64_t rows;        // allocated rows = (a_hi - a_lo) + 1 + 2 * FS_RO
+  int64_t a_lo, a_hi;  // owned ghost-inclusive cell rows [a_lo, a_hi)
   double dx, dy;
   __host__ __device__ inline int64_t idx(int64_t a, int64_t b) const {
     return (a + FS_RO) * pitch + (b + FS_CO);
   }
   __host__ __device__ inline int64_t count() const { return rows * pitch; }
+  // offset of the virtual base relative to the allocation base (subtract it from the latter)
+  __host__ __device__ inline int64_t voff() const { return a_lo * pitch; }
+  __host__ __device__ inline bool first() const { return a_lo == 0; }
+  __host__ __device__ inline bool last() const { return a_hi == nx + 2; }
+  // owned rows of a U-like field end one later on the last rank
+  __host__ __device__ inline int64_t u_hi() const { return a_hi + (last() ? 1 : 0); }
 };
 
 // ---- deterministic grid-wide reductions -----------------------------------------------------
@@ -106,8 +122,10 @@ __device__ inline bool grid_reduce(const double (&v)[NV], double* part, unsigned
 // CTAs per SM (persist_blocks) instead of one CTA per 256 points: the reduction then costs
 // ~1e3 partials + tickets instead of ~3e5 serialised atomics on one address (measured: 0.8 ms per
 // reduction at 8192^2 before this change).
+// rows [r0, r1) x columns [0, n1)
 template <class F>
-__device__ __forceinline__ void for_each_point(int64_t n0, int64_t n1, F&& f) {
+__device__ __forceinline__ void for_each_point(int64_t r0, int64_t r1, int64_t n1, F&& f) {
+  const int64_t n0 = r1 - r0;
   const int64_t tiles_j = (n1 + 63) / 64, nt = tiles_j * ((n0 + 15) / 16);
   for (int64_t t = blockIdx.x; t < nt; t += gridDim.x) {
     const int64_t ti = t / tiles_j, tj = t - ti * tiles_j;
@@ -115,8 +133,8 @@ __device__ __forceinline__ void for_each_point(int64_t n0, int64_t n1, F&& f) {
     if (lj < n1) {
 #pragma unroll
       for (int m = 0; m < 4; ++m) {
-        const int64_t li = ti * 16 + threadIdx.y + 4 * m;
-        if (li < n0) f(li, lj);
+        const int64_t li = r0 + ti * 16 + threadIdx.y + 4 * m;
+        if (li < r1) f(li, lj);
       }
     }
   }

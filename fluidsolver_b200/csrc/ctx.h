@@ -12,13 +12,17 @@ struct BCondSide {
   double* v_prof = nullptr;
 };
 
+struct Comm;  // comm.cu: NCCL (one process per GPU) or the in-process test transport
+
 struct fsgpu_ctx {
   Geom g{};
   int device = 0;
+  int rank = 0, nranks = 1;   // slab decomposition along i
+  Comm* comm = nullptr;       // null for a single rank
   cudaStream_t stream = nullptr;
   double rho_gas = 1, rho_liquid = 1, visc_gas = 1e-3, visc_liquid = 1e-3, sigma = 0;
   double* slab = nullptr;              // one allocation for all fields
-  double* f[FSGPU_NUM_FIELDS] = {};    // field base pointers (padded layout)
+  double* f[FSGPU_NUM_FIELDS] = {};    // VIRTUAL field base pointers (allocation base - g.voff())
   double *U_alt = nullptr, *V_alt = nullptr;  // ping-pong targets of the fused momentum update
   BCondSide bc[4];
   // reduction scratch
@@ -42,6 +46,23 @@ static inline void field_extent(const Geom& g, int field, int64_t* m, int64_t* n
       *m = g.nx + 2; *n = g.ny + 2; break;
   }
 }
+
+// allocation base of an array whose virtual base is v (for whole-array memset / memcpy)
+static inline double* alloc_base(const Geom& g, double* v) { return v + g.voff(); }
+
+// ---- comm.cu: halo exchange and reductions between the slabs ------------------------------------
+// All of these are no-ops for a single rank.  With NCCL everything is enqueued on c->stream.
+enum { COMM_SUM = 0, COMM_MAX = 1 };
+int comm_create(fsgpu_ctx* c, int rank, int nranks, const void* id128, int transport);
+void comm_destroy(fsgpu_ctx* c);
+// arrays given by VIRTUAL base pointers sharing `pitch`; this rank owns rows [i0, i1) (global
+// indices).  Fills the h rows above and below from the neighbour ranks' owned rows.
+int comm_halo(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i0, int64_t i1, int h);
+int comm_allreduce(fsgpu_ctx* c, double* dev, int64_t n, int op);
+// n doubles to / from one peer rank (the x-periodic wrap-around); peer < 0: not a participant
+int comm_sendrecv(fsgpu_ctx* c, int peer, const double* const* send, double* const* recv, int narr, int64_t n);
+// halo rows of flow fields (ids), h rows each
+int fs_exchange_fields(fsgpu_ctx* c, const int* fields, int n, int h);
 
 // ---- stencil.cu -------------------------------------------------------------------------------
 int fs_launch_mid_time(fsgpu_ctx* c);

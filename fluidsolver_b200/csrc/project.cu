@@ -28,8 +28,8 @@ __global__ void __launch_bounds__(BX* BY)
 k_divergence(const double* __restrict__ U, const double* __restrict__ V, double* __restrict__ div,
              const Geom g) {
   const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (a > g.nx + 1 || b > g.ny + 1) return;
+  const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (a >= g.a_hi || b > g.ny + 1) return;
   const int64_t k = g.idx(a, b);
   div[k] = div_at(U, V, k, g.pitch, g.dx, g.dy);
 }
@@ -42,7 +42,7 @@ k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __rest
       double* __restrict__ rhs, const Geom g, double dt, int psd, double* part,
       unsigned int* ticket, double* out) {
   double v[1] = {0.0};
-  for_each_point(g.nx + 2, g.ny + 2, [&](int64_t a, int64_t b) {
+  for_each_point(g.a_lo, g.a_hi, g.ny + 2, [&](int64_t a, int64_t b) {
     const int64_t k = g.idx(a, b);
     double d;
     if (FROM_UV) {
@@ -69,15 +69,15 @@ k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __rest
 __global__ void __launch_bounds__(BX* BY)
 k_sub_scaled(double* __restrict__ f, const double* __restrict__ sum, double scale, const Geom g) {
   const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (a > g.nx + 1 || b > g.ny + 1) return;
+  const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (a >= g.a_hi || b > g.ny + 1) return;
   f[g.idx(a, b)] -= __ldg(sum) * scale;
 }
 
 __global__ void __launch_bounds__(BX* BY)
 k_sum(const double* __restrict__ f, const Geom g, double* part, unsigned int* ticket, double* out) {
   double v[1] = {0.0};
-  for_each_point(g.nx + 2, g.ny + 2, [&](int64_t a, int64_t b) { v[0] += f[g.idx(a, b)]; });
+  for_each_point(g.a_lo, g.a_hi, g.ny + 2, [&](int64_t a, int64_t b) { v[0] += f[g.idx(a, b)]; });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
     if (threadIdx.x == 0 && threadIdx.y == 0) out[0] = tot[0];
@@ -91,8 +91,8 @@ k_correct(double* __restrict__ dp, double* __restrict__ p, double* __restrict__ 
           double* __restrict__ V, const double* __restrict__ ru, const double* __restrict__ rv,
           const double* __restrict__ sum, const Geom g, double dt) {
   const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (a > g.nx + 1 || b > g.ny + 1) return;
+  const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (a >= g.a_hi || b > g.ny + 1) return;
   const int64_t k = g.idx(a, b), P = g.pitch;
   const double c  = SHIFT ? __ldg(sum) * g.dx * g.dy : 0.0;
   // neighbours are read un-shifted from global memory and shifted locally: no ordering hazard
@@ -120,8 +120,9 @@ k_cfl(const double* __restrict__ U, const double* __restrict__ V, const double* 
       const double* __restrict__ rv, const double* __restrict__ mu, const Geom g, double* part,
       unsigned int* ticket, double* out) {
   double v[4] = {0.0, 0.0, 0.0, 0.0};  // the reference's maxima start at 0 (FS.hpp:102-106)
-  for_each_point(g.nx, g.ny, [&](int64_t i, int64_t j) {
-    const int64_t k = g.idx(i + 1, j + 1), P = g.pitch;
+  const int64_t r0 = g.a_lo > 1 ? g.a_lo : 1, r1 = g.a_hi < g.nx + 1 ? g.a_hi : g.nx + 1;
+  for_each_point(r0, r1, g.ny, [&](int64_t a, int64_t j) {  // a = i + 1 over the owned interior rows
+    const int64_t k = g.idx(a, j + 1), P = g.pitch;
     v[0] = fmax(v[0], (U[k] + U[k + P]) / 2 / g.dx);
     v[1] = fmax(v[1], (V[k] + V[k + 1]) / 2 / g.dy);
     const double rho = (ru[k] + ru[k + P] + rv[k] + rv[k + 1]) / 4.0;
@@ -148,10 +149,11 @@ __global__ void k_absmax(const double* __restrict__ f, int64_t n, double* part,
 }
 
 // fill the (m+2) x (n+2) ghost-inclusive extent of a field
-__global__ void k_fill(double* __restrict__ f, int64_t m2, int64_t n2, double v, const Geom g) {
+// (rows [r0, r1): the owned rows and the halo rows inside the field's extent)
+__global__ void k_fill(double* __restrict__ f, int64_t r0, int64_t r1, int64_t n2, double v, const Geom g) {
   const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t a = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (a >= m2 || b >= n2) return;
+  const int64_t a = r0 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (a >= r1 || b >= n2) return;
   f[g.idx(a, b)] = v;
 }
 
@@ -162,8 +164,8 @@ __global__ void __launch_bounds__(BX* BY)
 k_rho_visc_vof(const double* __restrict__ vf, double* __restrict__ ru, double* __restrict__ rv,
                double* __restrict__ mu, const Geom g, double rg, double rl, double mg, double ml) {
   const int64_t j = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t i = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (i > g.nx || j > g.ny) return;
+  const int64_t i = (g.a_lo > 1 ? g.a_lo : 1) - 1 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (i > g.nx || i + 1 >= g.a_hi || j > g.ny) return;
   const int64_t k = g.idx(i + 1, j + 1), P = g.pitch;
   const double f0 = vf[k];
   const double r0 = f0 * rl + (1.0 - f0) * rg;
@@ -196,8 +198,8 @@ int fs_ensure_part(fsgpu_ctx* c, size_t doubles) {
   return 0;
 }
 
-static dim3 cell_grid(const Geom& g) {
-  return dim3((unsigned)cdiv(g.ny + 2, BX), (unsigned)cdiv(g.nx + 2, BY));
+static dim3 cell_grid(const Geom& g) {  // the owned cell rows
+  return dim3((unsigned)cdiv(g.ny + 2, BX), (unsigned)cdiv(g.a_hi - g.a_lo, BY));
 }
 static dim3 ext_grid(int64_t m2, int64_t n2) {
   return dim3((unsigned)cdiv(n2, BX), (unsigned)cdiv(m2, BY));
@@ -212,7 +214,7 @@ int fs_launch_divergence(fsgpu_ctx* c) {
 
 int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
   const dim3 gr = cell_grid(c->g);
-  const unsigned pg = persist_blocks(c->g.nx + 2, c->g.ny + 2);
+  const unsigned pg = persist_blocks(c->g.a_hi - c->g.a_lo, c->g.ny + 2);
   if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
   if (div_from_uv)
     k_rhs<true><<<pg, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
@@ -224,6 +226,7 @@ int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
                                                      c->ticket, c->red_out);
   FS_LAUNCHED();
   if (psd == FSGPU_PSD_NONE) {  // subtract the arithmetic mean over all (NX+2)(NY+2) entries
+    if (comm_allreduce(c, c->red_out, 1, COMM_SUM)) return 1;
     const double inv_n = 1.0 / (double)((c->g.nx + 2) * (c->g.ny + 2));
     k_sub_scaled<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_RHS], c->red_out, inv_n, c->g);
     FS_LAUNCHED();
@@ -232,12 +235,12 @@ int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
 }
 
 static int launch_sum_dp(fsgpu_ctx* c) {
-  const unsigned gr = persist_blocks(c->g.nx + 2, c->g.ny + 2);
+  const unsigned gr = persist_blocks(c->g.a_hi - c->g.a_lo, c->g.ny + 2);
   if (fs_ensure_part(c, (size_t)gr * 4)) return 1;
   k_sum<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_DELTA_P], c->g, c->part, c->ticket,
                                             c->red_out + 1);
   FS_LAUNCHED();
-  return 0;
+  return comm_allreduce(c, c->red_out + 1, 1, COMM_SUM);
 }
 
 int fs_launch_shift_pressure(fsgpu_ctx* c) {
@@ -254,42 +257,50 @@ int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift) {
     // in place inside the same pass: shift first (in place), then correct.
     if (fs_launch_shift_pressure(c)) return 1;
   }
+  {  // the correction of face a reads delta_p of row a - 1
+    const int fl[1] = {FSGPU_DELTA_P};
+    if (fs_exchange_fields(c, fl, 1, 1)) return 1;
+  }
   k_correct<false><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
       c->f[FSGPU_DELTA_P], c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
       c->f[FSGPU_RHO_V], c->red_out + 1, c->g, dt);
   FS_LAUNCHED();
-  return 0;
+  const int fl[3] = {FSGPU_U, FSGPU_V, FSGPU_P};
+  return fs_exchange_fields(c, fl, 3, 1);
 }
 
 int fs_launch_cfl(fsgpu_ctx* c) {
-  const unsigned gr = persist_blocks(c->g.nx, c->g.ny);
+  const unsigned gr = persist_blocks(c->g.a_hi - c->g.a_lo, c->g.ny);
   if (fs_ensure_part(c, (size_t)gr * 4)) return 1;
   k_cfl<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
                                             c->f[FSGPU_RHO_V], c->f[FSGPU_VISC], c->g, c->part,
                                             c->ticket, c->red_out);
   FS_LAUNCHED();
-  return 0;
+  return comm_allreduce(c, c->red_out, 4, COMM_MAX);
 }
 
 int fs_launch_absmax(fsgpu_ctx* c, int field) {
   const int64_t n    = c->g.count();
   const unsigned nbl = (unsigned)std::min<int64_t>(cdiv(n, 256), 148 * 8);
   if (fs_ensure_part(c, (size_t)nbl * 4)) return 1;
-  k_absmax<<<nbl, 256, 0, c->stream>>>(c->f[field], n, c->part, c->ticket, c->red_out);
+  // whole local allocation: pads are zero and halo rows are copies, neither changes the maximum
+  k_absmax<<<nbl, 256, 0, c->stream>>>(alloc_base(c->g, c->f[field]), n, c->part, c->ticket, c->red_out);
   FS_LAUNCHED();
-  return 0;
+  return comm_allreduce(c, c->red_out, 1, COMM_MAX);
 }
 
 int fs_launch_fill(fsgpu_ctx* c, int field, double v) {
   int64_t m, n;
   field_extent(c->g, field, &m, &n);
-  k_fill<<<ext_grid(m, n), dim3(BX, BY), 0, c->stream>>>(c->f[field], m, n, v, c->g);
+  const int64_t r0 = c->g.a_lo - FS_RO > 0 ? c->g.a_lo - FS_RO : 0;
+  const int64_t r1 = c->g.a_hi + FS_RO < m ? c->g.a_hi + FS_RO : m;
+  k_fill<<<ext_grid(r1 - r0, n), dim3(BX, BY), 0, c->stream>>>(c->f[field], r0, r1, n, v, c->g);
   FS_LAUNCHED();
   return 0;
 }
 
 int fs_launch_rho_visc_vof(fsgpu_ctx* c) {
-  k_rho_visc_vof<<<dim3((unsigned)cdiv(c->g.ny + 1, BX), (unsigned)cdiv(c->g.nx + 1, BY)),
+  k_rho_visc_vof<<<dim3((unsigned)cdiv(c->g.ny + 1, BX), (unsigned)cdiv(c->g.a_hi - c->g.a_lo, BY)),
                    dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_VF], c->f[FSGPU_RHO_U], c->f[FSGPU_RHO_V],
                                                  c->f[FSGPU_VISC], c->g, c->rho_gas, c->rho_liquid,
                                                  c->visc_gas, c->visc_liquid);
@@ -297,5 +308,6 @@ int fs_launch_rho_visc_vof(fsgpu_ctx* c) {
   if (fs_launch_neumann(c, c->f[FSGPU_RHO_U], c->g.nx + 1, c->g.ny)) return 1;
   if (fs_launch_neumann(c, c->f[FSGPU_RHO_V], c->g.nx, c->g.ny + 1)) return 1;
   if (fs_launch_neumann(c, c->f[FSGPU_VISC], c->g.nx, c->g.ny)) return 1;
-  return 0;
+  const int fl[3] = {FSGPU_RHO_U, FSGPU_RHO_V, FSGPU_VISC};
+  return fs_exchange_fields(c, fl, 3, FS_RO);
 }

@@ -17,8 +17,13 @@
 
 #define FS_MAX_LEVELS 40
 
+// Slab decomposition: rows are addressed by their GLOBAL level index li; the array pointers are
+// virtual bases (allocation base - first stored row * pitch) exactly like the flow fields
+// (common.cuh), and kernels sweep the rows [i0, i1) this rank owns ([0, n0) for one rank and on
+// the replicated coarse levels).
 struct LevelDev {
-  int64_t n0, n1;     // points along i (d = 0) and j (d = 1)
+  int64_t n0, n1;     // points along i (d = 0) and j (d = 1) of the GLOBAL level grid
+  int64_t i0, i1;     // rows swept by a kernel launched on this level
   int64_t pitch;      // doubles per row
   int64_t foff;       // fine index along cdir of THIS level's point 0 in its parent (0 or 1)
   double *d, *dinv, *cx, *cy, *pc;
@@ -32,6 +37,9 @@ struct Level {
   LevelDev v{};
   int64_t lo[2] = {0, 0};  // global index of point (0, 0) (the fine box starts at -1)
   int64_t rows   = 0;      // allocated rows
+  int64_t own0 = 0, own1 = 0;  // rows [own0, own1) belong to this rank under the slab partition
+  bool replicated = false;     // level >= ld: every rank holds (and solves) the whole level
+  int64_t voff() const { return replicated ? 0 : own0 * v.pitch; }
   int cdir       = -1;     // direction coarsened to reach the next level; -1 on the coarsest
   int active     = 1;      // relax on this level
   double weight  = 1.0;    // Jacobi weight
@@ -41,6 +49,10 @@ struct Level {
 struct PcgScal {
   double gamma, sdotp, alpha, beta, bi, iprod, eps;
   int iter, done, first, coarse_zero_diag;
+  // slab decomposition: nranks > 1 makes the reduction kernels park their LOCAL sum in red[]
+  // instead of finishing the recurrence; after the all-reduce k_pcg_after_* finishes it.
+  int nranks;
+  double red[4];
 };
 // done codes
 enum { PCG_RUNNING = 0, PCG_CONVERGED = 1, PCG_BREAKDOWN = 2, PCG_ZERO_RHS = 3 };
@@ -67,12 +79,39 @@ __device__ __forceinline__ void pcg_after_rz(PcgScal* scal, double g) {
     }
   }
 }
+// the scalar part of "<s, p>" (k_matvec_dot): alpha = gamma / <s,p> with HYPRE's breakdown exits
+__device__ __forceinline__ void pcg_after_sp(PcgScal* scal, double sp) {
+  scal->iter += 1;
+  scal->sdotp = sp;
+  if (sp == 0.0) {  // pcg.c:760-775
+    if (scal->iter == 1) scal->iprod = scal->gamma;
+    scal->done = PCG_BREAKDOWN;
+  } else {
+    const double alpha = scal->gamma / sp;
+    scal->alpha = alpha;
+    if (alpha <= 0.0) {  // pcg.c:777-790
+      if (scal->iter == 1) scal->iprod = scal->gamma;
+      scal->done = PCG_BREAKDOWN;
+    }
+  }
+}
+// called by the last block of a reduction kernel with this rank's sum
+template <bool INIT>
+__device__ __forceinline__ void pcg_local_rz(PcgScal* scal, double g) {
+  if (scal->nranks > 1) scal->red[0] = g;
+  else pcg_after_rz<INIT>(scal, g);
+}
+__device__ __forceinline__ void pcg_local_sp(PcgScal* scal, double sp) {
+  if (scal->nranks > 1) scal->red[0] = sp;
+  else pcg_after_sp(scal, sp);
+}
 #endif
 
 struct fsgpu_ps {
   fsgpu_ctx* c = nullptr;
   fsgpu_ps_opts o{};
   int nl = 0;
+  int ld = 0;  // levels [0, ld) are distributed over the ranks, [ld, nl) replicated (ld == nl: 1 rank)
   Level L[FS_MAX_LEVELS];
   int coarse_sweeps = 0;
   double* slab = nullptr;  // every level's arrays + PCG vectors
@@ -94,4 +133,9 @@ int ps_setup(fsgpu_ps* s);
 // 2: also bi = <r, z> (first V-cycle).  The dot product rides on the last kernel of the cycle.
 int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode);
 // solver_pcg.cu
+// slab decomposition: all-reduce the parked local sum and finish the recurrence (no-ops for 1 rank)
+int ps_finish_rz(fsgpu_ps* s, bool init);
+int ps_finish_sp(fsgpu_ps* s);
+// halo rows of level-l arrays given by virtual base pointers
+int ps_halo(fsgpu_ps* s, int l, double* const* ptrs, int n, int h);
 int ps_solve(fsgpu_ps* s, double* residual, int* iters);

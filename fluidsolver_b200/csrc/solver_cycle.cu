@@ -28,42 +28,6 @@ struct Coef {
   __device__ __forceinline__ double ap(int64_t q) const { return CDIR == 0 ? __ldg(cx + q + P) : __ldg(cy + q + 1); }
 };
 
-// residual after the zero-guess Jacobi sweep at fine point q (b is the level's rhs)
-template <bool ACTIVE>
-__device__ __forceinline__ double resid0(const LevelDev& f, const double* __restrict__ b, int64_t q,
-                                         double w) {
-  const double bq = __ldg(b + q);
-  if (!ACTIVE) return bq;
-  const int64_t P = f.pitch;
-  auto X = [&](int64_t r) { return w * __ldg(b + r) * __ldg(f.dinv + r); };
-  double v = w * bq;  // d * x(q)
-  v += __ldg(f.cx + q) * X(q - P);
-  v += __ldg(f.cx + q + P) * X(q + P);
-  v += __ldg(f.cy + q) * X(q - 1);
-  v += __ldg(f.cy + q + 1) * X(q + 1);
-  return bq - v;
-}
-
-template <int CDIR, bool ACTIVE>
-__global__ void __launch_bounds__(BX* BY)
-k_down(const LevelDev f, const double* __restrict__ fb, const LevelDev c, double* __restrict__ cb,
-       double w, const PcgScal* scal) {
-  if (scal->done) return;
-  const int64_t cj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t ci = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (ci >= c.n0 || cj >= c.n1) return;
-  const int64_t fi = CDIR == 0 ? 2 * ci + c.foff : ci;
-  const int64_t fj = CDIR == 1 ? 2 * cj + c.foff : cj;
-  const int64_t k = f.idx(fi, fj), sd = CDIR == 0 ? f.pitch : 1;
-  const Coef<CDIR> C{f.cx, f.cy, f.pitch};
-  const double pp_m = -C.ap(k - sd) * __ldg(f.pc + k - sd);  // F-point below, weight to this C-point
-  const double pm_p = -C.am(k + sd) * __ldg(f.pc + k + sd);  // F-point above, weight to this C-point
-  double v = resid0<ACTIVE>(f, fb, k, w);
-  v += pp_m * resid0<ACTIVE>(f, fb, k - sd, w);
-  v += pm_p * resid0<ACTIVE>(f, fb, k + sd, w);
-  cb[c.idx(ci, cj)] = v;
-}
-
 // ---- marching restriction kernels (same strip / chunk scheme as k_up_march below) -------------
 // k_down_march0: coarsening along i.  Per fine row the warp forms X = w b / d, then the residual
 // R of the row above from three rows of X held in registers (left/right by shuffle), and on every
@@ -74,15 +38,16 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
               double* __restrict__ cb, double w, int mrc, const PcgScal* scal) {
   if (scal->done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int n1 = (int)f.n1, n0c = (int)c.n0, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  const int n1 = (int)f.n1, c_lo = (int)c.i0, c_hi = (int)c.i1, P = (int)f.pitch, Pc = (int)c.pitch,
+            foff = (int)c.foff;
   const int strips = (n1 + 119) / 120;
-  const int total  = strips * ((n0c + mrc - 1) / mrc);
+  const int total  = strips * ((c_hi - c_lo + mrc - 1) / mrc);
   for (int t = blockIdx.x; t < total; t += gridDim.x) {
     const int ch = t / strips, sp = t - ch * strips;
     int lj = sp * 120 + warp * 30 - 1 + lane;
     const bool store_lane = lane >= 1 && lane <= 30 && lj < n1;
     if (lj > n1) lj = n1;
-    const int c0 = ch * mrc, c1 = min(c0 + mrc, n0c);
+    const int c0 = c_lo + ch * mrc, c1 = min(c0 + mrc, c_hi);
     const int f0 = 2 * c0 + foff, fL = 2 * (c1 - 1) + foff;
     double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx2 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0, Ra = 0.0, Rb = 0.0;
     int li = f0 - 2;
@@ -130,9 +95,10 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
               double* __restrict__ cb, double w, int mr, const PcgScal* scal) {
   if (scal->done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int n0 = (int)f.n0, n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  const int f_lo = (int)f.i0, f_hi = (int)f.i1, n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch,
+            foff = (int)c.foff;
   const int strips = (n1 + 111) / 112;
-  const int total  = strips * ((n0 + mr - 1) / mr);
+  const int total  = strips * ((f_hi - f_lo + mr - 1) / mr);
   for (int t = blockIdx.x; t < total; t += gridDim.x) {
     const int ch = t / strips, sp = t - ch * strips;
     int lj = sp * 112 + warp * 28 - 2 + lane;
@@ -140,7 +106,7 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
     const bool store_lane = lane >= 2 && lane <= 29 && lj < n1 && (pos & 1) == 0;
     const int oc_col = (pos >> 1) + FS_CO;
     if (lj > n1) lj = n1;
-    const int r0 = ch * mr, r1 = min(r0 + mr, n0);
+    const int r0 = f_lo + ch * mr, r1 = min(r0 + mr, f_hi);
     double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0;
     int li = r0 - 1;
     int o  = (li + FS_RO) * P + lj + FS_CO;
@@ -210,8 +176,8 @@ k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
             const double* __restrict__ cxv, const PcgScal* scal) {
   if (scal->done) return;
   const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (li >= f.n0 || lj >= f.n1) return;
+  const int64_t li = f.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (li >= f.i1 || lj >= f.n1) return;
   const int64_t k = f.idx(li, lj);
   fx[k] = x_interp<CDIR, false>(f, 0.0, c, cxv, li, lj, k, 0.0);
 }
@@ -234,16 +200,17 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
            unsigned int* ticket) {
   if (scal->done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int n0 = (int)f.n0, n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  const int f_lo = (int)f.i0, f_hi = (int)f.i1, n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch,
+            foff = (int)c.foff;
   const int strips = (n1 + MOUT * MWARPS - 1) / (MOUT * MWARPS);
-  const int total  = strips * ((n0 + mr - 1) / mr);
+  const int total  = strips * ((f_hi - f_lo + mr - 1) / mr);
   double acc[1] = {0.0};
   for (int t = blockIdx.x; t < total; t += gridDim.x) {
     const int ch = t / strips, sp = t - ch * strips;
     int lj = sp * (MOUT * MWARPS) + warp * MOUT - 1 + lane;  // lane 0 sits one column left
     const bool store_lane = lane >= 1 && lane <= MOUT && lj < n1;
     if (lj > n1) lj = n1;  // the zero pad column right of the grid
-    const int r0 = ch * mr, r1 = min(r0 + mr, n0);
+    const int r0 = f_lo + ch * mr, r1 = min(r0 + mr, f_hi);
     double x0p = 0.0, x0c = 0.0, bc = 0.0, dic = 0.0, cyc = 0.0, cy1c = 0.0, cxc = 0.0;
     int li = r0 - 1;
     int o  = (li + FS_RO) * P + lj + FS_CO;
@@ -295,7 +262,7 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
   if (DOT) {
     double tot[1];
     if (grid_reduce<ReduceSum, 1>(acc, part, ticket, tot)) {
-      if (threadIdx.x == 0) pcg_after_rz<DOT == 2>(scal, tot[0]);
+      if (threadIdx.x == 0) pcg_local_rz<DOT == 2>(scal, tot[0]);
     }
   }
 }
@@ -307,13 +274,13 @@ k_dot_rz(const LevelDev L, const double* __restrict__ r, const double* __restric
          double* part, unsigned int* ticket) {
   if (scal->done) return;
   double v[1] = {0.0};
-  for_each_point(L.n0, L.n1, [&](int64_t li, int64_t lj) {
+  for_each_point(L.i0, L.i1, L.n1, [&](int64_t li, int64_t lj) {
     const int64_t k = L.idx(li, lj);
     v[0] += r[k] * z[k];
   });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
-    if (threadIdx.x == 0 && threadIdx.y == 0) pcg_after_rz<INIT>(scal, tot[0]);
+    if (threadIdx.x == 0 && threadIdx.y == 0) pcg_local_rz<INIT>(scal, tot[0]);
   }
 }
 
@@ -366,8 +333,8 @@ k_jacobi(const LevelDev L, const double* __restrict__ b, const double* __restric
          double* __restrict__ xo, double w, int on, const PcgScal* scal) {
   if (scal->done) return;
   const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (li >= L.n0 || lj >= L.n1) return;
+  const int64_t li = L.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (li >= L.i1 || lj >= L.n1) return;
   const int64_t k = L.idx(li, lj), P = L.pitch;
   if (!on || scal->coarse_zero_diag * (on == 2)) {
     xo[k] = 0.0;
@@ -385,32 +352,17 @@ k_jacobi(const LevelDev L, const double* __restrict__ b, const double* __restric
   xo[k] = xi[k] + w * (b[k] - v) * L.dinv[k];
 }
 
-dim3 lvl_grid(const LevelDev& v) { return dim3((unsigned)cdiv(v.n1, BX), (unsigned)cdiv(v.n0, BY)); }
+dim3 lvl_grid(const LevelDev& v) { return dim3((unsigned)cdiv(v.n1, BX), (unsigned)cdiv(v.i1 - v.i0, BY)); }
 
 }  // namespace
-
-#define DISPATCH(KER, cdir, act, grid, ...)                                                    \
-  do {                                                                                         \
-    if ((cdir) == 0) {                                                                         \
-      if (act) KER<0, true><<<grid, dim3(BX, BY), 0, st>>>(__VA_ARGS__);                       \
-      else KER<0, false><<<grid, dim3(BX, BY), 0, st>>>(__VA_ARGS__);                          \
-    } else {                                                                                   \
-      if (act) KER<1, true><<<grid, dim3(BX, BY), 0, st>>>(__VA_ARGS__);                       \
-      else KER<1, false><<<grid, dim3(BX, BY), 0, st>>>(__VA_ARGS__);                          \
-    }                                                                                          \
-    FS_LAUNCHED();                                                                             \
-  } while (0)
 
 static int coarse_solve(fsgpu_ps* s, int l, const double* b, double* x) {
   cudaStream_t st = s->c->stream;
   const Level& L  = s->L[l];
   const size_t smem = (size_t)(2 * (L.v.n0 + 2) * (L.v.n1 + 2)) * sizeof(double);
   if (smem <= 200 * 1024) {
-    static bool attr_set = false;
-    if (!attr_set) {
-      FS_CUDA(cudaFuncSetAttribute(k_coarse_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      attr_set = true;
-    }
+    // per device, and cheap: set on every call (several contexts / devices may share the process)
+    FS_CUDA(cudaFuncSetAttribute(k_coarse_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     k_coarse_smem<<<1, 1024, smem, st>>>(L.v, b, x, s->coarse_sweeps, L.active, s->scal);
     FS_LAUNCHED();
     return 0;
@@ -445,17 +397,22 @@ static unsigned march_blocks(int64_t rows, int64_t strips, int mr) {
 static int launch_down(fsgpu_ps* s, int l, const double* fb) {
   cudaStream_t st = s->c->stream;
   Level* L        = s->L;
-  const LevelDev &f = L[l].v, &c = L[l + 1].v;
+  const LevelDev& f = L[l].v;
+  LevelDev c = L[l + 1].v;
+  if (!L[l].replicated) {  // a distributed level writes the coarse rows this rank owns
+    c.i0 = L[l + 1].own0;
+    c.i1 = L[l + 1].own1;
+  }
   if (L[l].cdir == 0) {
     const int64_t strips = cdiv(f.n1, 120);
-    const int mrc = pick_rows(c.n0, strips);
-    const unsigned nb = march_blocks(c.n0, strips, mrc);
+    const int mrc = pick_rows(c.i1 - c.i0, strips);
+    const unsigned nb = march_blocks(c.i1 - c.i0, strips, mrc);
     if (L[l].active) k_down_march0<true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal);
     else k_down_march0<false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal);
   } else {
     const int64_t strips = cdiv(f.n1, 112);
-    const int mr = pick_rows(f.n0, strips);
-    const unsigned nb = march_blocks(f.n0, strips, mr);
+    const int mr = pick_rows(f.i1 - f.i0, strips);
+    const unsigned nb = march_blocks(f.i1 - f.i0, strips, mr);
     if (L[l].active) k_down_march1<true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal);
     else k_down_march1<false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal);
   }
@@ -474,8 +431,8 @@ static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_m
     return 0;
   }
   const int64_t strips = cdiv(L[l].v.n1, MOUT * MWARPS);
-  const int mr      = pick_rows(L[l].v.n0, strips);
-  const unsigned nb = march_blocks(L[l].v.n0, strips, mr);
+  const int mr      = pick_rows(L[l].v.i1 - L[l].v.i0, strips);
+  const unsigned nb = march_blocks(L[l].v.i1 - L[l].v.i0, strips, mr);
   const int bl = 32 * MWARPS;
 #define UP_ARGS L[l].v, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket
   if (dot_mode == 1) k_up_march<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
@@ -491,28 +448,43 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
   Level* L        = s->L;
   const int nl    = s->nl;
   if (fs_ensure_part(s->c, (size_t)FS_NUM_SMS * 8 * 4)) return 1;
+  const bool dist = s->c->nranks > 1;
   if (nl == 1) {  // relax from zero, relax again (pfmg_solve.c with a single level)
     k_jacobi<true><<<lvl_grid(L[0].v), dim3(BX, BY), 0, st>>>(L[0].v, r, nullptr, s->ctmp, L[0].weight, 1, s->scal);
     FS_LAUNCHED();
+    if (ps_halo(s, 0, &s->ctmp, 1, 1)) return 1;
     k_jacobi<false><<<lvl_grid(L[0].v), dim3(BX, BY), 0, st>>>(L[0].v, r, s->ctmp, z, L[0].weight, 1, s->scal);
     FS_LAUNCHED();
-    const unsigned pg = persist_blocks(L[0].v.n0, L[0].v.n1);
+    const unsigned pg = persist_blocks(L[0].v.i1 - L[0].v.i0, L[0].v.n1);
     if (dot_mode == 1) k_dot_rz<false><<<pg, dim3(BX, BY), 0, st>>>(L[0].v, r, z, s->scal, s->c->part, s->c->ticket);
     if (dot_mode == 2) k_dot_rz<true><<<pg, dim3(BX, BY), 0, st>>>(L[0].v, r, z, s->scal, s->c->part, s->c->ticket);
     if (dot_mode) FS_LAUNCHED();
+    if (dot_mode && ps_finish_rz(s, dot_mode == 2)) return 1;
     return 0;
   }
-  // down: level l rhs -> level l+1 rhs
+  // down: level l rhs -> level l+1 rhs.  Slab decomposition: a distributed coarse level gets
+  // FS_RO halo rows of its rhs from the neighbours; the first replicated level is gathered
+  // (every rank writes its rows into a zeroed full array, then a sum all-reduce).
   for (int l = 0; l <= nl - 2; ++l) {
     const double* fb = l == 0 ? r : L[l].v.b;
     ProfScope ps_(l == 0 ? PROF_DOWN0 : PROF_DOWN, st);
+    const bool gather = dist && l + 1 == s->ld;
+    const size_t cn = (size_t)(L[l + 1].v.n0 * L[l + 1].v.pitch);
+    double* crow0 = L[l + 1].v.b + FS_RO * L[l + 1].v.pitch;  // row 0 of the replicated level
+    if (gather) FS_CUDA(cudaMemsetAsync(crow0, 0, cn * sizeof(double), st));
     if (launch_down(s, l, fb)) return 1;
+    if (gather) {
+      if (comm_allreduce(s->c, crow0, (int64_t)cn, COMM_SUM)) return 1;
+    } else if (dist && l + 1 < s->ld) {
+      if (ps_halo(s, l + 1, &L[l + 1].v.b, 1, FS_RO)) return 1;
+    }
   }
   {
     ProfScope ps_(PROF_COARSE, st);
     if (coarse_solve(s, nl - 1, L[nl - 1].v.b, L[nl - 1].v.x)) return 1;
   }
-  // up: level l+1 x -> level l x; the level-0 kernel also carries PCG's <r, z>
+  // up: level l+1 x -> level l x; the level-0 kernel also carries PCG's <r, z>.  A distributed
+  // level's x needs one halo row before the next finer level interpolates from it.
   for (int l = nl - 2; l >= 0; --l) {
     const double* fb = l == 0 ? r : L[l].v.b;
     double* fx       = l == 0 ? z : L[l].v.x;
@@ -520,6 +492,8 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
     const int dm = l == 0 ? dot_mode : 0;
     if (L[l].cdir == 0) { if (launch_up<0>(s, l, fb, fx, dm)) return 1; }
     else { if (launch_up<1>(s, l, fb, fx, dm)) return 1; }
+    if (dist && l >= 1 && l < s->ld && ps_halo(s, l, &fx, 1, 1)) return 1;
   }
+  if (dot_mode && ps_finish_rz(s, dot_mode == 2)) return 1;
   return 0;
 }

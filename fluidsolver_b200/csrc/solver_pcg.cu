@@ -29,7 +29,7 @@ k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict_
   if (scal->done) return;
   double v[1] = {0.0};
   const int64_t P = L.pitch;
-  for_each_point(L.n0, L.n1, [&](int64_t li, int64_t lj) {
+  for_each_point(L.i0, L.i1, L.n1, [&](int64_t li, int64_t lj) {
     const int64_t k = L.idx(li, lj);
     const double pk = __ldg(p + k);
     double a = __ldg(L.d + k) * pk;
@@ -42,21 +42,7 @@ k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict_
   });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
-    if (threadIdx.x == 0 && threadIdx.y == 0) {
-      scal->iter += 1;
-      scal->sdotp = tot[0];
-      if (tot[0] == 0.0) {  // pcg.c:760-775
-        if (scal->iter == 1) scal->iprod = scal->gamma;
-        scal->done = PCG_BREAKDOWN;
-      } else {
-        const double alpha = scal->gamma / tot[0];
-        scal->alpha = alpha;
-        if (alpha <= 0.0) {  // pcg.c:777-790
-          if (scal->iter == 1) scal->iprod = scal->gamma;
-          scal->done = PCG_BREAKDOWN;
-        }
-      }
-    }
+    if (threadIdx.x == 0 && threadIdx.y == 0) pcg_local_sp(scal, tot[0]);
   }
 }
 
@@ -66,8 +52,8 @@ k_xr_update(const LevelDev L, double* __restrict__ x, double* __restrict__ r,
             const double* __restrict__ p, const double* __restrict__ s, const PcgScal* scal) {
   if (scal->done) return;
   const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (li >= L.n0 || lj >= L.n1) return;
+  const int64_t li = L.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (li >= L.i1 || lj >= L.n1) return;
   const int64_t k = L.idx(li, lj);
   const double alpha = scal->alpha;
   x[k] += alpha * p[k];
@@ -81,15 +67,13 @@ k_dot_rz(const LevelDev L, const double* __restrict__ r, const double* __restric
          double* part, unsigned int* ticket) {
   if (scal->done) return;
   double v[1] = {0.0};
-  for_each_point(L.n0, L.n1, [&](int64_t li, int64_t lj) {
+  for_each_point(L.i0, L.i1, L.n1, [&](int64_t li, int64_t lj) {
     const int64_t k = L.idx(li, lj);
     v[0] += r[k] * z[k];
   });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
-    if (threadIdx.x == 0 && threadIdx.y == 0) {
-      pcg_after_rz<INIT>(scal, tot[0]);
-    }
+    if (threadIdx.x == 0 && threadIdx.y == 0) pcg_local_rz<INIT>(scal, tot[0]);
   }
 }
 
@@ -100,14 +84,24 @@ k_p_update(const LevelDev L, double* __restrict__ p, const double* __restrict__ 
            const PcgScal* scal) {
   if (scal->done) return;
   const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (li >= L.n0 || lj >= L.n1) return;
+  const int64_t li = L.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (li >= L.i1 || lj >= L.n1) return;
   const int64_t k = L.idx(li, lj);
   if (FIRST) p[k] = z[k];
   else p[k] = z[k] + scal->beta * p[k];
 }
 
-__global__ void k_scal_init(PcgScal* scal, double eps) {
+// (the reduction kernels return at once after convergence and leave red[] stale: skip then too)
+__global__ void k_after_sp(PcgScal* scal) {
+  if (!scal->done) pcg_after_sp(scal, scal->red[0]);
+}
+template <bool INIT>
+__global__ void k_after_rz(PcgScal* scal) {
+  if (!scal->done) pcg_after_rz<INIT>(scal, scal->red[0]);
+}
+
+__global__ void k_scal_init(PcgScal* scal, double eps, int nranks) {
+  scal->nranks = nranks;
   scal->gamma = scal->sdotp = scal->alpha = scal->beta = scal->bi = scal->iprod = 0.0;
   scal->eps   = eps;
   scal->iter  = 0;
@@ -117,21 +111,46 @@ __global__ void k_scal_init(PcgScal* scal, double eps) {
 
 }  // namespace
 
+int ps_finish_sp(fsgpu_ps* s) {
+  if (s->c->nranks <= 1) return 0;
+  if (comm_allreduce(s->c, s->scal->red, 1, COMM_SUM)) return 1;
+  k_after_sp<<<1, 1, 0, s->c->stream>>>(s->scal);
+  FS_LAUNCHED();
+  return 0;
+}
+int ps_finish_rz(fsgpu_ps* s, bool init) {
+  if (s->c->nranks <= 1) return 0;
+  if (comm_allreduce(s->c, s->scal->red, 1, COMM_SUM)) return 1;
+  if (init) k_after_rz<true><<<1, 1, 0, s->c->stream>>>(s->scal);
+  else k_after_rz<false><<<1, 1, 0, s->c->stream>>>(s->scal);
+  FS_LAUNCHED();
+  return 0;
+}
+int ps_halo(fsgpu_ps* s, int l, double* const* ptrs, int n, int h) {
+  if (s->c->nranks <= 1) return 0;
+  const Level& L = s->L[l];
+  return comm_halo(s->c, ptrs, n, L.v.pitch, L.own0, L.own1, h);
+}
+
 int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   fsgpu_ctx* c    = s->c;
   cudaStream_t st = c->stream;
   const LevelDev& L0 = s->L[0].v;
-  const dim3 gr((unsigned)cdiv(L0.n1, BX), (unsigned)cdiv(L0.n0, BY)), bl(BX, BY);
-  const unsigned pg = persist_blocks(L0.n0, L0.n1);
+  const dim3 gr((unsigned)cdiv(L0.n1, BX), (unsigned)cdiv(L0.i1 - L0.i0, BY)), bl(BX, BY);
+  const unsigned pg = persist_blocks(L0.i1 - L0.i0, L0.n1);
   if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
   double* x = c->f[FSGPU_DELTA_P];
   double* r = c->f[FSGPU_RHS];  // r = b - A 0 = b: the rhs buffer becomes the residual
-  k_scal_init<<<1, 1, 0, st>>>(s->scal, s->o.tol * s->o.tol);
+  k_scal_init<<<1, 1, 0, st>>>(s->scal, s->o.tol * s->o.tol, c->nranks);
   FS_LAUNCHED();
-  FS_CUDA(cudaMemsetAsync(x, 0, (size_t)c->g.count() * sizeof(double), st));
+  FS_CUDA(cudaMemsetAsync(alloc_base(c->g, x), 0, (size_t)c->g.count() * sizeof(double), st));
+  // slab decomposition, per iteration: r needs FS_RO halo rows before the V-cycle (restriction
+  // reaches two rows out), p one halo row before the matvec
+  if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
   if (ps_vcycle(s, r, s->z, 2)) return 1;  // z = C b and bi = <z, b>
   k_p_update<true><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);
   FS_LAUNCHED();
+  if (ps_halo(s, 0, &s->p, 1, 1)) return 1;
   const int nslot = FS_LAG + 1;
   int launched = 0;
   bool stop = false;
@@ -140,17 +159,20 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
       ProfScope ps_(PROF_MATVEC, st);
       k_matvec_dot<<<pg, bl, 0, st>>>(L0, s->p, s->s, s->scal, c->part, c->ticket);
       FS_LAUNCHED();
+      if (ps_finish_sp(s)) return 1;
     }
     {
       ProfScope ps_(PROF_XR, st);
       k_xr_update<<<gr, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal);
       FS_LAUNCHED();
+      if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
     }
     if (ps_vcycle(s, r, s->z, 1)) return 1;  // z = C r and gamma' = <r, z>
     {
       ProfScope ps_(PROF_PUPD, st);
       k_p_update<false><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);
       FS_LAUNCHED();
+      if (ps_halo(s, 0, &s->p, 1, 1)) return 1;
     }
     const int slot = it % nslot;
     FS_CUDA(cudaMemcpyAsync(&s->h_scal[slot], s->scal, sizeof(PcgScal), cudaMemcpyDeviceToHost, st));

@@ -9,7 +9,10 @@
 #include "solver.h"
 
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
+
+#include <vector>
 
 namespace {
 
@@ -19,7 +22,7 @@ __global__ void __launch_bounds__(BX* BY)
 k_build_l0(const double* __restrict__ ru, const double* __restrict__ rv, LevelDev L, const Geom g,
            int psd, double* part, unsigned int* ticket, double* out) {
   double v[4] = {0.0, 0.0, 0.0, 0.0};
-  for_each_point(g.nx + 2, g.ny + 2, [&](int64_t a, int64_t b) {
+  for_each_point(g.a_lo, g.a_hi, g.ny + 2, [&](int64_t a, int64_t b) {
     const int64_t k = g.idx(a, b), P = g.pitch;
     const double vol = g.dx * g.dy, dx2 = g.dx * g.dx, dy2 = g.dy * g.dy;
     double W = 0.0, E = 0.0, S = 0.0, N = 0.0, dxp, dyp;
@@ -95,8 +98,8 @@ struct Coef {  // accessors "along cdir" (a_m, a_p) and "transverse" (t_m, t_p) 
 template <int CDIR>
 __global__ void __launch_bounds__(BX* BY) k_interp(LevelDev f) {
   const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (li >= f.n0 || lj >= f.n1) return;
+  const int64_t li = f.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (li >= f.i1 || lj >= f.n1) return;
   const int64_t k = f.idx(li, lj);
   const Coef<CDIR> C{f.cx, f.cy, f.pitch};
   const double center = f.d[k] + C.tm(k) + C.tp(k);
@@ -105,10 +108,10 @@ __global__ void __launch_bounds__(BX* BY) k_interp(LevelDev f) {
 
 // coarse operator, pfmg_setup_rap5.c:339-379 (thread per coarse point)
 template <int CDIR>
-__global__ void __launch_bounds__(BX* BY) k_rap(LevelDev f, LevelDev c, int is_coarsest, PcgScal* scal) {
+__global__ void __launch_bounds__(BX* BY) k_rap(LevelDev f, LevelDev c) {
   const int64_t cj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t ci = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (ci >= c.n0 || cj >= c.n1) return;
+  const int64_t ci = c.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (ci >= c.i1 || cj >= c.n1) return;
   const int64_t fi = CDIR == 0 ? 2 * ci + c.foff : ci;
   const int64_t fj = CDIR == 1 ? 2 * cj + c.foff : cj;
   const int64_t k = f.idx(fi, fj), kc = c.idx(ci, cj);
@@ -129,8 +132,15 @@ __global__ void __launch_bounds__(BX* BY) k_rap(LevelDev f, LevelDev c, int is_c
   (CDIR == 0 ? c.cy : c.cx)[kc] = west;
   c.d[kc]    = dc;
   c.dinv[kc] = dc != 0.0 ? 1.0 / dc : 0.0;
-  // zero diagonal on the coarsest grid => no relaxation there, pfmg_setup.c:349-357
-  if (is_coarsest && dc == 0.0) scal->coarse_zero_diag = 1;
+}
+
+// zero diagonal on the coarsest grid => no relaxation there, pfmg_setup.c:349-357 (its own pass
+// so that it sees the whole gathered level when the hierarchy is decomposed)
+__global__ void __launch_bounds__(BX* BY) k_zero_diag(LevelDev c, PcgScal* scal) {
+  const int64_t cj = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t ci = c.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (ci >= c.i1 || cj >= c.n1) return;
+  if (c.d[c.idx(ci, cj)] == 0.0) scal->coarse_zero_diag = 1;
 }
 
 int64_t ceil_div2(int64_t a) { return a >= 0 ? (a + 1) / 2 : -((-a) / 2); }
@@ -215,6 +225,51 @@ static void schedule(fsgpu_ps* s, const double sums[4]) {
   s->coarse_sweeps = 4 * s->nl < cmaxsize ? 4 * s->nl : (int)cmaxsize;  // pfmg_setup.c:400-412
 }
 
+// Slab decomposition of the hierarchy.  Every level's rows are split by
+// following the fine partition down: a coarse row belongs to the rank that owns the fine row it
+// sits on.  Levels stay distributed while every rank keeps >= 2 FS_RO rows and the level has
+// more than `repl_points` points; from level `ld` on the (small) levels are gathered and every
+// rank runs the rest of the V-cycle redundantly on the whole level -- no exchanges there, and
+// no rank is ever left with fewer rows than a halo is wide.
+static int partition(fsgpu_ps* s) {
+  const int R = s->c->nranks, me = s->c->rank;
+  Level* L = s->L;
+  if (R <= 1) {
+    for (int l = 0; l < s->nl; ++l) {
+      L[l].own0 = 0; L[l].own1 = L[l].v.n0; L[l].replicated = false;
+      L[l].v.i0 = 0; L[l].v.i1 = L[l].v.n0;
+    }
+    s->ld = s->nl;
+    return 0;
+  }
+  int64_t repl_points = 1 << 16;
+  if (const char* e = getenv("FSGPU_REPL_POINTS")) repl_points = atoll(e);
+  std::vector<int64_t> lo(R), hi(R);
+  for (int r = 0; r < R; ++r)
+    if (fsgpu_slab_range(s->c->g.nx, r, R, &lo[r], &hi[r])) return 1;
+  int ld = -1;
+  for (int l = 0; l < s->nl; ++l) {
+    int64_t min_rows = hi[0] - lo[0];
+    for (int r = 1; r < R; ++r) min_rows = hi[r] - lo[r] < min_rows ? hi[r] - lo[r] : min_rows;
+    const bool keep = min_rows >= 2 * FS_RO && L[l].v.n0 * L[l].v.n1 > repl_points;
+    if (ld < 0 && l >= 1 && !keep) ld = l;
+    L[l].own0 = lo[me]; L[l].own1 = hi[me];
+    if (l + 1 < s->nl && L[l].cdir == 0) {
+      const int64_t foff = L[l + 1].v.foff;
+      for (int r = 0; r < R; ++r) { lo[r] = ceil_div2(lo[r] - foff); hi[r] = ceil_div2(hi[r] - foff); }
+    }
+  }
+  if (ld < 0) ld = s->nl;
+  if (s->nl >= 2 && ld > s->nl - 1) ld = s->nl - 1;  // the coarsest level is always replicated
+  s->ld = ld;
+  for (int l = 0; l < s->nl; ++l) {
+    L[l].replicated = l >= ld;
+    L[l].v.i0 = L[l].replicated ? 0 : L[l].own0;
+    L[l].v.i1 = L[l].replicated ? L[l].v.n0 : L[l].own1;
+  }
+  return 0;
+}
+
 // (re)allocate the level arrays for the current schedule; returns 0 on success
 static int alloc_levels(fsgpu_ps* s) {
   const Geom& g = s->c->g;
@@ -226,7 +281,7 @@ static int alloc_levels(fsgpu_ps* s) {
   total += n_l0 * (5 + 3);  // d, dinv, cx, cy, pc + p, s, z
   for (int l = 1; l < s->nl; ++l) {
     L[l].v.pitch = round_up(L[l].v.n1 + FS_CO + 2, 16);
-    L[l].rows    = L[l].v.n0 + 2 * FS_RO;
+    L[l].rows    = (L[l].v.i1 - L[l].v.i0) + 2 * FS_RO;  // owned (or all) rows + pads / halos
     total += (size_t)(L[l].rows * L[l].v.pitch) * 7;  // + x, b
   }
   const Level& c = L[s->nl - 1];
@@ -240,42 +295,54 @@ static int alloc_levels(fsgpu_ps* s) {
   }
   FS_CUDA(cudaMemsetAsync(s->slab, 0, s->slab_doubles * sizeof(double), s->c->stream));
   double* q = s->slab;
-  auto take = [&](size_t n) { double* r = q; q += n; return r; };
+  int cur = 0;  // arrays are handed out as VIRTUAL bases of level `cur`
+  auto take = [&](size_t n) { double* r = q - L[cur].voff(); q += n; return r; };
   L[0].v.d = take(n_l0); L[0].v.dinv = take(n_l0); L[0].v.cx = take(n_l0); L[0].v.cy = take(n_l0);
   L[0].v.pc = take(n_l0);
   s->p = take(n_l0); s->s = take(n_l0); s->z = take(n_l0);
   L[0].v.x = nullptr; L[0].v.b = nullptr;  // bound per V-cycle call
   for (int l = 1; l < s->nl; ++l) {
     const size_t n = (size_t)(L[l].rows * L[l].v.pitch);
+    cur = l;
     L[l].v.d = take(n); L[l].v.dinv = take(n); L[l].v.cx = take(n); L[l].v.cy = take(n);
     L[l].v.pc = take(n); L[l].v.x = take(n); L[l].v.b = take(n);
   }
+  cur = s->nl - 1;
   s->ctmp = take((size_t)(c.rows * c.v.pitch));
   return 0;
 }
 
 static dim3 lvl_grid(const LevelDev& v) {
-  return dim3((unsigned)cdiv(v.n1, BX), (unsigned)cdiv(v.n0, BY));
+  return dim3((unsigned)cdiv(v.n1, BX), (unsigned)cdiv(v.i1 - v.i0, BY));
+}
+
+// exchange FS_RO halo rows of a distributed level's operator arrays
+static int halo_coeffs(fsgpu_ps* s, int l) {
+  LevelDev& v = s->L[l].v;
+  double* ptrs[4] = {v.d, v.dinv, v.cx, v.cy};
+  return ps_halo(s, l, ptrs, 4, FS_RO);
 }
 
 int ps_setup(fsgpu_ps* s) {
   fsgpu_ctx* c = s->c;
   const Geom& g = c->g;
+  const bool dist = c->nranks > 1;
   ProfScope ps_(PROF_SETUP, c->stream);
   // sizes of level 0 are fixed; the first setup needs level-0 arrays before the schedule is
   // known, so allocate for a provisional single level, then re-run once the schedule exists.
   if (!s->levels_allocated) {
     s->nl = 1;
     s->L[0].v.n0 = g.nx + 2; s->L[0].v.n1 = g.ny + 2;
-    // worst case of the hierarchy below level 0 is < 1.2x level 0 in points; allocate after
-    // the schedule instead: here only level 0.
+    s->L[0].cdir = -1;
+    if (partition(s)) return 1;
     if (alloc_levels(s)) return 1;
   }
-  const unsigned gr = persist_blocks(g.nx + 2, g.ny + 2);
+  const unsigned gr = persist_blocks(g.a_hi - g.a_lo, g.ny + 2);
   if (fs_ensure_part(c, (size_t)gr * 4)) return 1;
   k_build_l0<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_RHO_U], c->f[FSGPU_RHO_V], s->L[0].v, g,
                                                  s->o.psd, c->part, c->ticket, c->red_out + 4);
   FS_LAUNCHED();
+  if (comm_allreduce(c, c->red_out + 4, 4, COMM_SUM)) return 1;
   FS_CUDA(cudaMemcpyAsync(c->h_red + 4, c->red_out + 4, 4 * sizeof(double), cudaMemcpyDeviceToHost,
                           c->stream));
   FS_CUDA(cudaStreamSynchronize(c->stream));
@@ -284,6 +351,7 @@ int ps_setup(fsgpu_ps* s) {
   int old_cdir[FS_MAX_LEVELS];
   for (int l = 0; l < old_nl; ++l) old_cdir[l] = s->L[l].cdir;
   schedule(s, c->h_red + 4);
+  if (partition(s)) return 1;
   bool same = (old_nl == s->nl);
   for (int l = 0; same && l < s->nl; ++l) same = (old_cdir[l] == s->L[l].cdir);
   if (!same) {
@@ -294,21 +362,38 @@ int ps_setup(fsgpu_ps* s) {
                                                    g, s->o.psd, c->part, c->ticket, c->red_out + 4);
     FS_LAUNCHED();
   }
+  if (halo_coeffs(s, 0)) return 1;
   FS_CUDA(cudaMemsetAsync(&s->scal->coarse_zero_diag, 0, sizeof(int), c->stream));
   for (int l = 0; l + 1 < s->nl; ++l) {
-    const LevelDev &f = s->L[l].v, &cc = s->L[l + 1].v;
-    const int last = (l + 2 == s->nl);
-    if (s->L[l].cdir == 0) {
-      k_interp<0><<<lvl_grid(f), dim3(BX, BY), 0, c->stream>>>(f);
-      FS_LAUNCHED();
-      k_rap<0><<<lvl_grid(cc), dim3(BX, BY), 0, c->stream>>>(f, cc, last, s->scal);
-      FS_LAUNCHED();
-    } else {
-      k_interp<1><<<lvl_grid(f), dim3(BX, BY), 0, c->stream>>>(f);
-      FS_LAUNCHED();
-      k_rap<1><<<lvl_grid(cc), dim3(BX, BY), 0, c->stream>>>(f, cc, last, s->scal);
-      FS_LAUNCHED();
+    const LevelDev& f = s->L[l].v;
+    LevelDev cc = s->L[l + 1].v;
+    const bool gather = dist && l + 1 == s->ld;  // first replicated level: built in slabs, then summed
+    if (!s->L[l].replicated) { cc.i0 = s->L[l + 1].own0; cc.i1 = s->L[l + 1].own1; }
+    if (s->L[l].cdir == 0) k_interp<0><<<lvl_grid(f), dim3(BX, BY), 0, c->stream>>>(f);
+    else k_interp<1><<<lvl_grid(f), dim3(BX, BY), 0, c->stream>>>(f);
+    FS_LAUNCHED();
+    if (!s->L[l].replicated) {
+      double* pc = f.pc;
+      if (ps_halo(s, l, &pc, 1, FS_RO)) return 1;
     }
+    const size_t cn = (size_t)(cc.n0 * cc.pitch);
+    double* arrs[4] = {cc.d, cc.dinv, cc.cx, cc.cy};
+    if (gather)
+      for (double* a : arrs) FS_CUDA(cudaMemsetAsync(a + FS_RO * cc.pitch, 0, cn * sizeof(double), c->stream));
+    if (s->L[l].cdir == 0) k_rap<0><<<lvl_grid(cc), dim3(BX, BY), 0, c->stream>>>(f, cc);
+    else k_rap<1><<<lvl_grid(cc), dim3(BX, BY), 0, c->stream>>>(f, cc);
+    FS_LAUNCHED();
+    if (gather) {
+      for (double* a : arrs)
+        if (comm_allreduce(c, a + FS_RO * cc.pitch, (int64_t)cn, COMM_SUM)) return 1;
+    } else if (dist && l + 1 < s->ld) {
+      if (halo_coeffs(s, l + 1)) return 1;
+    }
+  }
+  if (s->nl >= 2) {
+    const LevelDev& cl = s->L[s->nl - 1].v;
+    k_zero_diag<<<lvl_grid(cl), dim3(BX, BY), 0, c->stream>>>(cl, s->scal);
+    FS_LAUNCHED();
   }
   s->is_setup = true;
   return 0;

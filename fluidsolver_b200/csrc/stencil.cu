@@ -96,8 +96,9 @@ template <int MODE>
 __global__ void __launch_bounds__(BX* BY)
 k_momentum(const MomArgs a, const Geom g) {
   const int64_t j = (int64_t)blockIdx.x * BX + threadIdx.x;  // 0..NY
-  const int64_t i = (int64_t)blockIdx.y * BY + threadIdx.y;  // 0..NX
-  if (i > g.nx || j > g.ny) return;
+  // 0..NX, restricted to the face rows a = i + 1 this slab owns
+  const int64_t i = (g.a_lo > 1 ? g.a_lo : 1) - 1 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (i > g.nx || i + 1 >= g.a_hi || j > g.ny) return;
   const int64_t P = g.pitch, k = g.idx(i + 1, j + 1);
   constexpr bool MID = (MODE == 1);
   const Vel<MID> U{a.U, a.Uo}, V{a.V, a.Vo};
@@ -136,8 +137,8 @@ __global__ void k_update_velocity(const MomArgs a, const double* __restrict__ dU
                                   const double* __restrict__ dV, double* __restrict__ U,
                                   double* __restrict__ V, const Geom g) {
   const int64_t j = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t i = (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (i > g.nx || j > g.ny) return;
+  const int64_t i = (g.a_lo > 1 ? g.a_lo : 1) - 1 + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (i > g.nx || i + 1 >= g.a_hi || j > g.ny) return;
   const int64_t k = g.idx(i + 1, j + 1);
   if (j < g.ny) U[k] = (a.ruo[k] * a.Uo[k] + a.dt * dU[k]) / a.ru[k];
   if (i < g.nx) V[k] = (a.rvo[k] * a.Vo[k] + a.dt * dV[k]) / a.rv[k];
@@ -158,13 +159,17 @@ static MomArgs mom_args(fsgpu_ctx* c, double dt) {
   return a;
 }
 static dim3 face_grid(const Geom& g) {
-  return dim3((unsigned)cdiv(g.ny + 1, BX), (unsigned)cdiv(g.nx + 1, BY));
+  return dim3((unsigned)cdiv(g.ny + 1, BX), (unsigned)cdiv(g.a_hi - g.a_lo, BY));
 }
 
 int fs_launch_mid_time(fsgpu_ctx* c) {
   const int64_t n = c->g.count();
+  // whole local allocation (the reference averages every entry incl. ghosts; halo rows are
+  // averaged redundantly, which keeps them equal to the neighbour's rows)
+  const Geom& g = c->g;
   k_mid_time<<<(unsigned)std::min<int64_t>(cdiv(n, 256), 148 * 16), 256, 0, c->stream>>>(
-      c->f[FSGPU_U], c->f[FSGPU_U_OLD], c->f[FSGPU_V], c->f[FSGPU_V_OLD], n);
+      alloc_base(g, c->f[FSGPU_U]), alloc_base(g, c->f[FSGPU_U_OLD]), alloc_base(g, c->f[FSGPU_V]),
+      alloc_base(g, c->f[FSGPU_V_OLD]), n);
   FS_LAUNCHED();
   return 0;
 }

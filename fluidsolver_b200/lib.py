@@ -44,7 +44,10 @@ SYMBOLS = (
     "fsgpu_calc_rho_visc_const", "fsgpu_calc_rho_visc_vof", "fsgpu_apply_neumann_bconds",
     "fsgpu_ps_create", "fsgpu_ps_destroy", "fsgpu_ps_set_operator", "fsgpu_ps_set_rhs",
     "fsgpu_ps_solve", "fsgpu_ps_num_levels", "fsgpu_substep", "fsgpu_step",
+    "fsgpu_comm_id", "fsgpu_create_slab", "fsgpu_slab_range", "fsgpu_ps_num_distributed_levels",
 )
+TRANSPORT_NCCL, TRANSPORT_LOCAL = 0, 1
+COMM_ID_BYTES = 128
 
 
 class PsOpts(C.Structure):
@@ -73,6 +76,10 @@ def load():
     L.fsgpu_launch_count.restype = i64
     L.fsgpu_device_count.argtypes = [C.POINTER(i32)]
     L.fsgpu_create.argtypes = [i64, i64, dbl, dbl, i32, C.POINTER(vp)]
+    L.fsgpu_comm_id.argtypes = [C.c_char_p]
+    L.fsgpu_create_slab.argtypes = [i64, i64, dbl, dbl, i32, i32, i32, C.c_char_p, i32, C.POINTER(vp)]
+    L.fsgpu_slab_range.argtypes = [i64, i32, i32, C.POINTER(i64), C.POINTER(i64)]
+    L.fsgpu_ps_num_distributed_levels.argtypes = [vp, C.POINTER(i32)]
     L.fsgpu_set_props.argtypes = [vp, dbl, dbl, dbl, dbl, dbl]
     L.fsgpu_upload.argtypes = [vp, i32, DP]
     L.fsgpu_download.argtypes = [vp, i32, DP]
@@ -143,6 +150,20 @@ def device_count() -> int:
     return n.value
 
 
+def comm_id() -> bytes:
+    """ncclGetUniqueId (rank 0 calls it and broadcasts the 128 bytes to the other ranks)"""
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    _chk(load().fsgpu_comm_id(buf))
+    return buf.raw
+
+
+def slab_range(nx: int, rank: int, nranks: int):
+    """ghost-inclusive cell rows [a_lo, a_hi) of `rank` (host-only partition rule)"""
+    lo, hi = C.c_int64(), C.c_int64()
+    _chk(load().fsgpu_slab_range(nx, rank, nranks, C.byref(lo), C.byref(hi)))
+    return lo.value, hi.value
+
+
 def field_shape(name: str, nx: int, ny: int):
     if name in U_LIKE:
         return (nx + 3, ny + 2)
@@ -152,15 +173,23 @@ def field_shape(name: str, nx: int, ny: int):
 
 
 class FS:
-    """The reference's ``FS<Float,NX,NY,1>`` (src/FS.hpp:28-52) resident on one B200."""
+    """The reference's ``FS<Float,NX,NY,1>`` (src/FS.hpp:28-52) resident on one B200, or -- with
+    rank / nranks / comm_id -- one slab of it (include/fsgpu.h "slab decomposition"): every method
+    is then collective and host arrays stay GLOBAL arrays."""
 
     def __init__(self, nx, ny, dx, dy, rho_gas=1.0, rho_liquid=1.0, visc_gas=1e-3, visc_liquid=1e-3,
-                 sigma=0.0, device=0):
+                 sigma=0.0, device=0, rank=0, nranks=1, comm_id=None, transport=TRANSPORT_NCCL):
         self.L = load()
         self.nx, self.ny, self.dx, self.dy = int(nx), int(ny), float(dx), float(dy)
         self.h = C.c_void_p()
         self._solvers = []  # weak refs: solvers hold device state of this context
-        _chk(self.L.fsgpu_create(self.nx, self.ny, self.dx, self.dy, device, C.byref(self.h)))
+        self.rank, self.nranks = int(rank), int(nranks)
+        if self.nranks > 1:
+            assert comm_id is not None and len(comm_id) == COMM_ID_BYTES
+            _chk(self.L.fsgpu_create_slab(self.nx, self.ny, self.dx, self.dy, device, self.rank,
+                                          self.nranks, comm_id, transport, C.byref(self.h)))
+        else:
+            _chk(self.L.fsgpu_create(self.nx, self.ny, self.dx, self.dy, device, C.byref(self.h)))
         self.set_props(rho_gas, rho_liquid, visc_gas, visc_liquid, sigma)
 
     def close(self):
@@ -326,6 +355,12 @@ class LinearSolver:
         res, it = C.c_double(), C.c_int()
         _chk(self.L.fsgpu_ps_solve(self.h, C.byref(res), C.byref(it)))
         return res.value, it.value
+
+    @property
+    def num_distributed_levels(self):
+        n = C.c_int()
+        _chk(self.L.fsgpu_ps_num_distributed_levels(self.h, C.byref(n)))
+        return n.value
 
     @property
     def num_levels(self):

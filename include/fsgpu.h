@@ -85,6 +85,27 @@ int fsgpu_prof_read(double* ms_total, int64_t* count, int nclass);
 /* replaces: `FS<Float,NX,NY,NGHOST> fs{...}; init_grid(...)` (src/FS.hpp:55-73) */
 int fsgpu_create(int64_t nx, int64_t ny, double dx, double dy, int device, fsgpu_ctx** out);
 int fsgpu_destroy(fsgpu_ctx* c);
+
+/* ---- slab decomposition over the GPUs of one box (the reference itself is
+ * single-node OpenMP, so there is no reference call behind these) -------------------------------
+ * The global (NX+2) x (NY+2) ghost-inclusive grid is cut into `nranks` slabs of whole i-rows;
+ * rank r owns the rows a = i + 1 in [a_lo, a_hi) returned by fsgpu_slab_range (U-like fields: the
+ * last rank also owns the extra row a = NX + 2).  Every other call of this header keeps its
+ * meaning and is COLLECTIVE: all ranks call it in the same order with the same arguments; scalars
+ * returned (dt, residual, iterations, maxima) are identical on every rank.  Host arrays passed to
+ * fsgpu_upload / fsgpu_download stay GLOBAL arrays in the reference layout: upload reads this
+ * rank's rows (+ halo rows) from it, download writes this rank's rows into it.
+ * Transports: NCCL = one process per GPU, `id` from fsgpu_comm_id on rank 0 and broadcast by the
+ * launcher (torch.distributed, MPI, a file ...); LOCAL = all ranks are contexts of ONE process,
+ * each driven by its own host thread, `id` any 128-byte key shared by the group (test transport,
+ * lets the decomposed path run on a single GPU). */
+enum { FSGPU_TRANSPORT_NCCL = 0, FSGPU_TRANSPORT_LOCAL = 1 };
+#define FSGPU_COMM_ID_BYTES 128
+int fsgpu_comm_id(void* id128); /* ncclGetUniqueId */
+int fsgpu_create_slab(int64_t nx, int64_t ny, double dx, double dy, int device, int rank, int nranks,
+                      const void* id128, int transport, fsgpu_ctx** out);
+/* host-only partition rule (no device needed): rows [*a_lo, *a_hi) of rank `rank` */
+int fsgpu_slab_range(int64_t nx, int rank, int nranks, int64_t* a_lo, int64_t* a_hi);
 /* fs.rho_gas, fs.rho_liquid, fs.visc_gas, fs.visc_liquid, fs.sigma (src/FS.hpp:29-33) */
 int fsgpu_set_props(fsgpu_ctx* c, double rho_gas, double rho_liquid, double visc_gas,
                     double visc_liquid, double sigma);
@@ -168,6 +189,10 @@ int fsgpu_ps_set_rhs(fsgpu_ps* s, double dt);
  * *iters == max_iter and *residual >= tol. */
 int fsgpu_ps_solve(fsgpu_ps* s, double* residual, int* iters);
 int fsgpu_ps_num_levels(fsgpu_ps* s, int* n);
+/* slab decomposition: number of leading multigrid levels that are distributed over the ranks; the
+ * remaining (coarse) levels are gathered and solved redundantly on every rank.  Equal to the number
+ * of levels for a single rank. */
+int fsgpu_ps_num_distributed_levels(fsgpu_ps* s, int* n);
 
 /* ---- fused fast path used by our own drivers: one projection sub-iteration
  * (scaling/LidDrivenFlow.cpp:127-161) and one whole timestep (:121-163) ----------------------- */
