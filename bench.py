@@ -33,7 +33,7 @@ os.environ.setdefault("OMP_PROC_BIND", "close")
 os.environ.setdefault("OMP_PLACES", "cores")
 
 NSUB, TOL, MAX_ITER, CFL, DT_MAX = 5, 1e-6, 50, 0.9, 0.1
-CPU_SAMPLE_N = 2048  # grid of the bounded CPU sample (reference instantiation in ref_harness_sizes.inc)
+CPU_SAMPLE_N = int(os.environ.get("FSBENCH_CPU_N", "2048"))  # grid of the bounded CPU sample (reference instantiation in ref_harness_sizes.inc)
 
 
 def parse():
@@ -178,17 +178,24 @@ def main():
     import torch
     import fluidsolver_b200 as F
 
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    dist = None
+    comm_id = None
     if world > 1:
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
-    n = a.n or 8192
-    if world > 1:
-        raise SystemExit("multi-GPU slab decomposition is not wired into bench.py yet (see DESIGN.md)")
+        # the library's own NCCL communicator: rank 0 draws the id, torch.distributed carries it
+        box = [F.comm_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        comm_id = box[0]
+    # N = 1: BASELINE configs[2] (8192^2, the configuration the metric is quoted on);
+    # N > 1: configs[4], the 16384^2 strong-scaling case, slab-decomposed over the N GPUs
+    n = a.n or (8192 if world == 1 else 16384)
 
-    fs = F.FS(n, n, 1.0 / n, 1.0 / n, 1.0, 1.0, 1e-3, 1e-3, device=local)
+    fs = F.FS(n, n, 1.0 / n, 1.0 / n, 1.0, 1.0, 1e-3, 1e-3, device=local, rank=rank, nranks=world,
+              comm_id=comm_id)
     fs.calc_rho_visc_const()
     for s, u in enumerate((0.0, 0.0, 0.0, 1.0)):
         fs.set_bconds(s, F.DIRICHLET, u, 0.0)
@@ -211,6 +218,8 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     fs.sync()
     torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
     l0 = F.launch_count()
     e0.record(stream)
     its = 0
@@ -220,7 +229,13 @@ def main():
     e1.record(stream)
     fs.sync()
     torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
     ms = e0.elapsed_time(e1)
+    if dist:  # device time, MAX over ranks
+        t = torch.tensor([ms], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
     launches = F.launch_count() - l0
     clk = clocks.stop()
     prof = F.prof_read()
@@ -235,7 +250,8 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    cells = (n + 2) * (n + 2)
+    a_lo, a_hi = F.slab_range(n, rank, world)
+    cells = (a_hi - a_lo) * (n + 2)  # level-0 unknowns this rank's kernels sweep per launch
     kms, kcnt = prof.get(prof_cls, (0.0, 0))
     achieved = ALGO_BYTES[prof_cls] * cells / (kms / max(kcnt, 1) * 1e-3) / 1e9 if kcnt else None
     roofline = {"bound": "hbm", "kernel": prof_cls, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -248,35 +264,53 @@ def main():
     b_step = NSUB * (232 + 160 + 264 * k_bar) + 120
     step_gbs = b_step * n * n * a.steps / (ms * 1e-3) / 1e9
     roofline["step_algorithmic_GBs"] = step_gbs
-    roofline["step_frac"] = step_gbs / peak
+    roofline["step_frac"] = step_gbs / (peak * world)  # N GPUs: N x the single-GPU peak
 
     # e2e: the same step through the C ABI with HOST buffers (pinned), copies inside the timed region
     e2e = None
     if not a.no_e2e:
         names = ("U", "V", "P")
-        host = {}
-        for nm in names:
-            t = torch.empty(F.field_shape(nm, n, n), dtype=torch.float64, pin_memory=True)
-            host[nm] = t.numpy()
-            fs.download(nm, host[nm])
+        host, r0s = {}, {}
+        for nm in names:  # each rank pins only its own rows (+ halo rows) of the global arrays
+            r0, r1 = fs.local_rows(nm)
+            t = torch.empty((r1 - r0, F.field_shape(nm, n, n)[1]), dtype=torch.float64, pin_memory=True)
+            host[nm], r0s[nm] = t.numpy(), r0
+            fs.download_rows(nm, host[nm], r0)
         ke = max(1, min(a.steps, 3))
         nbytes = sum(h.nbytes for h in host.values())
         fs.sync()
+        if dist:
+            dist.barrier()
         t0 = time.perf_counter()
         for _ in range(ke):
             for nm in names:
-                fs.upload(nm, host[nm])
+                fs.upload_rows(nm, host[nm], r0s[nm])
             one_step()
             for nm in names:
-                fs.download(nm, host[nm])
+                fs.download_rows(nm, host[nm], r0s[nm])
         fs.sync()
+        if dist:
+            dist.barrier()
         el = time.perf_counter() - t0
+        if dist:
+            t = torch.tensor([el, float(nbytes)], dtype=torch.float64, device=f"cuda:{local}")
+            tm = t.clone()
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            el, nbytes = float(tm[0].item()), int(t[1].item())
         e2e = {"value": n * n * ke / el / 1e6, "unit": "MCell-updates/s", "h2d_bytes_per_step": nbytes,
                "d2h_bytes_per_step": nbytes, "steps": ke, "ms_per_step": el / ke * 1e3,
-               "api": "fsgpu_upload(U,V,P) -> fsgpu_adjust_dt -> fsgpu_step -> fsgpu_download(U,V,P), pinned host buffers"}
+               "api": "fsgpu_upload(U,V,P) -> fsgpu_adjust_dt -> fsgpu_step -> fsgpu_download(U,V,P), pinned host "
+                      "buffers" + (" (each rank its own slab rows; bytes summed over ranks)" if dist else "")}
     umax = fs.abs_max("U")
+    levels = (ps.num_levels, ps.num_distributed_levels)
     ps.close()
     fs.close()
+    if dist:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return 0
 
     cpu = None
     if rank == 0 and n_gpus == 1 and not a.no_cpu:
@@ -289,9 +323,12 @@ def main():
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"lid-driven cavity {n}^2 (scaling/LidDrivenFlow.cpp:16-42), NUM_SUBITER {NSUB}, "
                                    f"PCG tol {TOL} max_iter {MAX_ITER}, CFL {CFL}",
-                       "pcg_iters_per_solve": k_bar, "mg_levels": None, "l2": "inputs larger than L2 "
+                       "pcg_iters_per_solve": k_bar, "mg_levels": levels[0],
+                       "decomposition": None if world == 1 else
+                       f"{world} slabs of i-rows, NCCL halo exchange + all-reduce, multigrid levels "
+                       f"0..{levels[1] - 1} distributed, {levels[1]}..{levels[0] - 1} replicated", "l2": "inputs larger than L2 "
                        f"(each field {cells * 8 / 1e6:.0f} MB vs 126 MB L2)", "max_abs_U": umax},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clk}
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches * world, "clocks": clk}
     print(json.dumps(line), flush=True)
     return 0
 

@@ -105,6 +105,13 @@ int fsgpu_slab_range(int64_t nx, int rank, int nranks, int64_t* a_lo, int64_t* a
   return 0;
 }
 
+int fsgpu_slab_coarse_range(int64_t lo, int64_t hi, int64_t foff, int64_t* c_lo, int64_t* c_hi) {
+  auto ceil_div2 = [](int64_t a) { return a >= 0 ? (a + 1) / 2 : -((-a) / 2); };
+  if (c_lo) *c_lo = ceil_div2(lo - foff);
+  if (c_hi) *c_hi = ceil_div2(hi - foff);
+  return 0;
+}
+
 int fsgpu_create_slab(int64_t nx, int64_t ny, double dx, double dy, int device, int rank, int nranks,
                       const void* id128, int transport, fsgpu_ctx** out) {
   if (!out || nx < 2 || ny < 2 || !(dx > 0) || !(dy > 0)) {

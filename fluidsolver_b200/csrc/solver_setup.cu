@@ -256,7 +256,7 @@ static int partition(fsgpu_ps* s) {
     L[l].own0 = lo[me]; L[l].own1 = hi[me];
     if (l + 1 < s->nl && L[l].cdir == 0) {
       const int64_t foff = L[l + 1].v.foff;
-      for (int r = 0; r < R; ++r) { lo[r] = ceil_div2(lo[r] - foff); hi[r] = ceil_div2(hi[r] - foff); }
+      for (int r = 0; r < R; ++r) fsgpu_slab_coarse_range(lo[r], hi[r], foff, &lo[r], &hi[r]);
     }
   }
   if (ld < 0) ld = s->nl;

@@ -44,7 +44,8 @@ SYMBOLS = (
     "fsgpu_calc_rho_visc_const", "fsgpu_calc_rho_visc_vof", "fsgpu_apply_neumann_bconds",
     "fsgpu_ps_create", "fsgpu_ps_destroy", "fsgpu_ps_set_operator", "fsgpu_ps_set_rhs",
     "fsgpu_ps_solve", "fsgpu_ps_num_levels", "fsgpu_substep", "fsgpu_step",
-    "fsgpu_comm_id", "fsgpu_create_slab", "fsgpu_slab_range", "fsgpu_ps_num_distributed_levels",
+    "fsgpu_comm_id", "fsgpu_create_slab", "fsgpu_slab_range", "fsgpu_slab_coarse_range",
+    "fsgpu_ps_num_distributed_levels",
 )
 TRANSPORT_NCCL, TRANSPORT_LOCAL = 0, 1
 COMM_ID_BYTES = 128
@@ -79,6 +80,7 @@ def load():
     L.fsgpu_comm_id.argtypes = [C.c_char_p]
     L.fsgpu_create_slab.argtypes = [i64, i64, dbl, dbl, i32, i32, i32, C.c_char_p, i32, C.POINTER(vp)]
     L.fsgpu_slab_range.argtypes = [i64, i32, i32, C.POINTER(i64), C.POINTER(i64)]
+    L.fsgpu_slab_coarse_range.argtypes = [i64, i64, i64, C.POINTER(i64), C.POINTER(i64)]
     L.fsgpu_ps_num_distributed_levels.argtypes = [vp, C.POINTER(i32)]
     L.fsgpu_set_props.argtypes = [vp, dbl, dbl, dbl, dbl, dbl]
     L.fsgpu_upload.argtypes = [vp, i32, DP]
@@ -164,6 +166,20 @@ def slab_range(nx: int, rank: int, nranks: int):
     return lo.value, hi.value
 
 
+def slab_coarse_range(lo: int, hi: int, foff: int):
+    a, b = C.c_int64(), C.c_int64()
+    _chk(load().fsgpu_slab_coarse_range(lo, hi, foff, C.byref(a), C.byref(b)))
+    return a.value, b.value
+
+
+def slab_rows(name: str, nx: int, ny: int, rank: int, nranks: int):
+    """-> (r0, r1): rows of the GLOBAL host array of field `name` that fsgpu_upload reads on `rank`
+    (its owned rows + the halo rows that exist); fsgpu_download writes the owned sub-range"""
+    m = field_shape(name, nx, ny)[0]
+    lo, hi = slab_range(nx, rank, nranks)
+    return max(lo - 2, 0), min(hi + 2, m)
+
+
 def field_shape(name: str, nx: int, ny: int):
     if name in U_LIKE:
         return (nx + 3, ny + 2)
@@ -223,6 +239,24 @@ class FS:
         a = out if out is not None else np.empty(field_shape(name, self.nx, self.ny))
         _chk(self.L.fsgpu_download(self.h, FIELD_ID[name], a.ctypes.data_as(DP)))
         return a
+
+    # slab decomposition: host buffers that hold only this rank's rows of the global array
+    def local_rows(self, name):
+        """-> (r0, r1): the rows of the global array fsgpu_upload reads on this rank (owned rows
+        + halo rows); fsgpu_download writes a sub-range of them"""
+        return slab_rows(name, self.nx, self.ny, self.rank, self.nranks)
+
+    def _shifted(self, name, rows, r0):
+        n = field_shape(name, self.nx, self.ny)[1]
+        assert rows.dtype == np.float64 and rows.flags.c_contiguous and rows.shape[1] == n
+        assert (r0, r0 + rows.shape[0]) == self.local_rows(name)
+        return C.cast(C.c_void_p(rows.ctypes.data - r0 * n * 8), DP)  # base of the virtual global array
+
+    def upload_rows(self, name, rows, r0):
+        _chk(self.L.fsgpu_upload(self.h, FIELD_ID[name], self._shifted(name, rows, r0)))
+
+    def download_rows(self, name, rows, r0):
+        _chk(self.L.fsgpu_download(self.h, FIELD_ID[name], self._shifted(name, rows, r0)))
 
     def fill(self, name, value):
         _chk(self.L.fsgpu_fill(self.h, FIELD_ID[name], value))

@@ -106,6 +106,10 @@ int fsgpu_create_slab(int64_t nx, int64_t ny, double dx, double dy, int device, 
                       const void* id128, int transport, fsgpu_ctx** out);
 /* host-only partition rule (no device needed): rows [*a_lo, *a_hi) of rank `rank` */
 int fsgpu_slab_range(int64_t nx, int rank, int nranks, int64_t* a_lo, int64_t* a_hi);
+/* host-only: the rows [*c_lo, *c_hi) of the next coarser multigrid level that belong to the owner of
+ * the fine rows [lo, hi) when the level is coarsened along i with coarse point c sitting on fine row
+ * 2 c + foff (a coarse row goes with the fine row it sits on; coarsening along j keeps the rows) */
+int fsgpu_slab_coarse_range(int64_t lo, int64_t hi, int64_t foff, int64_t* c_lo, int64_t* c_hi);
 /* fs.rho_gas, fs.rho_liquid, fs.visc_gas, fs.visc_liquid, fs.sigma (src/FS.hpp:29-33) */
 int fsgpu_set_props(fsgpu_ctx* c, double rho_gas, double rho_liquid, double visc_gas,
                     double visc_liquid, double sigma);
