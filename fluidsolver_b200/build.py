@@ -17,6 +17,7 @@ OBJ = os.path.join(HERE, "csrc", "build")
 LIB = os.path.join(HERE, "libfsgpu.so")
 SOURCES = ["stencil.cu", "bconds.cu", "project.cu", "solver_setup.cu", "solver_cycle.cu",
            "solver_pcg.cu", "comm.cu", "api.cu"]
+NO_FMA = {"solver_setup.cu"}
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
@@ -36,7 +37,11 @@ def _compile(src: str, force: bool) -> str:
     deps.append(os.path.join(HERE, "..", "include", "fsgpu.h"))
     if not force and _newer(obj, deps):
         return obj
-    cmd = [NVCC] + FLAGS + ["-c", os.path.join(CSRC, src), "-o", obj]
+    # the multigrid setup is compiled without FMA contraction: the coarse operators then carry
+    # the same roundings as HYPRE's (built without -march, i.e. no FMA), in particular the EXACT
+    # zero of the singular 1x1 coarsest operator that pfmg_setup.c:349-357 tests for
+    extra = ["-fmad=false"] if src in NO_FMA else []
+    cmd = [NVCC] + FLAGS + extra + ["-c", os.path.join(CSRC, src), "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     with open(obj.replace(".o", ".ptxas.log"), "w") as f:
         f.write(r.stdout + r.stderr)

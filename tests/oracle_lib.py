@@ -269,15 +269,25 @@ def have_ref() -> bool:
     return os.path.exists(REF_SO)
 
 
+def ref_variant(max_levels):
+    """the reference rebuilt with -DPS_PFMG_MAX_LEVELS=<n> (its own knob,
+    src/LinearSolver_StructHypre.hpp:221-229): oracle/_ref/libfsref_ml<n>.so, or None"""
+    so = os.path.join(ROOT, "oracle", "_ref", f"libfsref_ml{max_levels}.so")
+    if not os.path.exists(so):
+        return None
+    return type(f"RefML{max_levels}", (Ref,), {"_lib": None, "SO": so})
+
+
 class Ref:
     """oracle/_ref/libfsref.so: one session = one reference ``FS`` + solver of a fixed size."""
 
     _lib = None
+    SO = REF_SO
 
     @classmethod
     def lib(cls):
         if cls._lib is None:
-            L = C.CDLL(REF_SO)
+            L = C.CDLL(cls.SO)
             L.fsref_create.restype = C.c_void_p
             L.fsref_create.argtypes = [C.c_int64, C.c_int64]
             L.fsref_supported.argtypes = [C.c_int64, C.c_int64]

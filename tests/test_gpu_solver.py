@@ -33,6 +33,11 @@ CASES = [
     ("channel256x64", dict(nx=256, ny=64, lx=100.0, ly=1.0, rho=0.5), False),
     ("drop128", dict(nx=128, ny=128, drop=True), True),
     ("tiny6x5", dict(nx=6, ny=5), False),
+    # hierarchies that reach a 1x1 coarsest grid inside 16 levels: singular coarsest operator,
+    # zero diagonal => no relaxation there (pfmg_setup.c:349-357)
+    ("cavity64", dict(nx=64, ny=64), False),
+    ("cavity48", dict(nx=48, ny=48), False),
+    ("cavity80x40", dict(nx=80, ny=40), False),
 ]
 
 
@@ -60,6 +65,29 @@ def test_solve_matches_oracle(F, oracle, name, kw, drop, tol):
         assert res_g == pytest.approx(res_o, rel=1e-3)
     a, b = dp - dp.mean(), sol - sol.mean()
     assert rel_l2(a, b) <= TOL_FIELD
+    ps.close()
+    fs.close()
+
+
+@pytest.mark.parametrize("max_levels", [2, 3, 4, 7, 10])
+def test_truncated_hierarchy(F, oracle, max_levels):
+    """PS_PFMG_MAX_LEVELS truncation (src/LinearSolver_StructHypre.hpp:221-229; 16 in production,
+    which cuts the hierarchy from 2048^2 upwards): coarsest level forced active with
+    min(4 levels, size) weight-1 sweeps.  The oracle's truncated cycle is pinned against the
+    reference rebuilt with -DPS_PFMG_MAX_LEVELS (tests/test_oracle.py)."""
+    st = cavity_state(oracle, seed=2, nx=96, ny=72)
+    fs, op, rhs = _setup(oracle, F, st, cavity_bc(), 1e-2)
+    so = oracle.solver(st.nx, st.ny, tol=1e-10, max_iter=300, max_levels=max_levels)
+    so.set_operator(op)
+    sol, res_o, it_o = so.solve(rhs)
+    ps = F.LinearSolver(fs, tol=1e-10, max_iter=300, max_levels=max_levels)
+    ps.set_pressure_operator()
+    assert ps.num_levels == so.num_levels == max_levels
+    ps.set_pressure_rhs(1e-2)
+    res_g, it_g = ps.solve()
+    dp = fs.download("DELTA_P")
+    assert it_g == it_o and res_g == pytest.approx(res_o, rel=1e-3), (it_g, it_o, res_g, res_o)
+    assert rel_l2(dp - dp.mean(), sol - sol.mean()) <= TOL_FIELD
     ps.close()
     fs.close()
 
