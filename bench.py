@@ -42,7 +42,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=0, help="grid size override (default 8192; 16384 for N > 1)")
+    ap.add_argument("--grid", dest="n", type=int, default=0, help="grid size override (default 8192; 16384 for N > 1)")
     ap.add_argument("--max-levels", type=int, default=-1, help="multigrid depth (-1: library default)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")

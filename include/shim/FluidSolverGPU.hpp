@@ -1,0 +1,381 @@
+// include/shim/FluidSolverGPU.hpp -- header-only C++ host layer that re-creates the call surface of
+// gidonbauer/FluidSolver's per-timestep path on top of the C ABI of include/fsgpu.h.
+//
+// A reference driver (scaling/LidDrivenFlow.cpp, test/TaylorGreenVortex.cpp, test/LaminarChannel.cpp)
+// includes FS.hpp / Operators.hpp / BoundaryConditions.hpp / LinearSolver_StructHypre.hpp and calls
+// free function templates on an `FS` object.  This header declares the same names with the same
+// argument meaning; behind them every operation is a CUDA kernel of libfsgpu.so (no CPU fallback).
+// INTEGRATION.md lists, call by call, what a driver changes.
+//
+// Differences a driver author must know (they follow from the state living in HBM):
+//  * Field2D::operator()(i, j) reads / writes a HOST mirror.  After initialising fields with host
+//    loops call fs.to_device(); before inspecting results call fs.to_host() (or field.download()).
+//  * the loops the reference drivers inline (velocity update, pressure correction) are the calls
+//    update_velocity(dU, dV, dt, fs) (exists in the reference: src/FS.hpp:423-436) and
+//    correct_velocity(fs, delta_p, dt) (scaling/LidDrivenFlow.cpp:153-160).
+//  * scratch fields (div, drhoUdt, drhoVdt, delta_p) are bound to the context's device fields the
+//    first time they are passed to a call in that role.
+#ifndef FSGPU_SHIM_FLUIDSOLVERGPU_HPP_
+#define FSGPU_SHIM_FLUIDSOLVERGPU_HPP_
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <variant>
+#include <vector>
+
+#include "../fsgpu.h"
+
+using Index = std::int64_t;  // src/Container.hpp
+
+namespace fsgpu_shim {
+// the reference's error convention: Igor::Panic -> message + exit(1) (Igor/Logging.hpp:50-62)
+inline void check(int rc, const char* what) {
+  if (rc != 0) {
+    std::fprintf(stderr, "[fsgpu] %s failed: %s\n", what, fsgpu_last_error());
+    std::exit(1);
+  }
+}
+}  // namespace fsgpu_shim
+#define FSGPU_CHECK(call) ::fsgpu_shim::check((call), #call)
+
+// ---- Field2D / Field1D (src/Container.hpp:25-169) -------------------------------------------------
+template <typename Float, Index N, Index NGHOST>
+class Field1D {
+  std::vector<Float> m_data = std::vector<Float>(static_cast<size_t>(N + 2 * NGHOST), Float{});
+ public:
+  Float& operator()(Index i) { return m_data[static_cast<size_t>(i + NGHOST)]; }
+  const Float& operator()(Index i) const { return m_data[static_cast<size_t>(i + NGHOST)]; }
+  Float* get_data() { return m_data.data(); }
+  const Float* get_data() const { return m_data.data(); }
+  static constexpr Index extent(Index) { return N; }
+  static constexpr Index size() { return N + 2 * NGHOST; }
+};
+
+template <typename Float, Index M, Index N, Index NGHOST>
+class Field2D {
+  static_assert(sizeof(Float) == sizeof(double), "libfsgpu.so computes in FP64");
+  std::vector<Float> m_data = std::vector<Float>(static_cast<size_t>((M + 2 * NGHOST) * (N + 2 * NGHOST)), Float{});
+  fsgpu_ctx* m_ctx = nullptr;
+  int m_field      = -1;
+ public:
+  Field2D() = default;
+  Field2D(const Field2D&)            = delete;  // as the reference: non-copyable, non-movable
+  Field2D& operator=(const Field2D&) = delete;
+  // host mirror, Layout::C with j fastest (src/Container.hpp:105-111)
+  Float& operator()(Index i, Index j) {
+    return m_data[static_cast<size_t>((j + NGHOST) + (i + NGHOST) * (N + 2 * NGHOST))];
+  }
+  const Float& operator()(Index i, Index j) const {
+    return m_data[static_cast<size_t>((j + NGHOST) + (i + NGHOST) * (N + 2 * NGHOST))];
+  }
+  Float* get_data() { return m_data.data(); }
+  const Float* get_data() const { return m_data.data(); }
+  static constexpr Index extent(Index d) { return d == 0 ? M : N; }
+  static constexpr Index size() { return (M + 2 * NGHOST) * (N + 2 * NGHOST); }
+  // device binding
+  void bind(fsgpu_ctx* ctx, int field) { m_ctx = ctx; m_field = field; }
+  bool bound() const { return m_ctx != nullptr; }
+  fsgpu_ctx* context() const { return m_ctx; }
+  int field_id() const { return m_field; }
+  void upload() const { if (m_ctx) FSGPU_CHECK(fsgpu_upload(m_ctx, m_field, m_data.data())); }
+  void download() { if (m_ctx) FSGPU_CHECK(fsgpu_download(m_ctx, m_field, m_data.data())); }
+};
+
+namespace fsgpu_shim {
+template <class F>
+fsgpu_ctx* ctx_of(const F& f) {
+  if (!f.bound()) check(1, "field is not bound to a device context (call init_grid(..., fs) first)");
+  return f.context();
+}
+}  // namespace fsgpu_shim
+
+// fill(field, value), src/Container.hpp:172-180: host mirror and device
+template <typename Float, Index M, Index N, Index NGHOST>
+void fill(Field2D<Float, M, N, NGHOST>& f, Float v) {
+  for (Index k = 0; k < f.size(); ++k) f.get_data()[k] = v;
+  f.upload();
+}
+
+// ---- State / FS (src/FS.hpp:15-52) ------------------------------------------------------------------
+template <typename Float, Index NX, Index NY, Index NGHOST>
+struct State {
+  Field2D<Float, NX + 1, NY, NGHOST> rho_u_stag{};
+  Field2D<Float, NX, NY + 1, NGHOST> rho_v_stag{};
+  Field2D<Float, NX + 1, NY, NGHOST> U{};
+  Field2D<Float, NX, NY + 1, NGHOST> V{};
+};
+
+template <typename Float, Index NX, Index NY, Index NGHOST>
+struct FS {
+  static_assert(NGHOST == 1, "the stepping path uses exactly one ghost cell (BoundaryConditions.hpp:219)");
+  Float visc_gas{};
+  Float visc_liquid{};
+  Float rho_gas{};
+  Float rho_liquid{};
+
+  Field1D<Float, NX + 1, NGHOST> x{};
+  Field1D<Float, NX, NGHOST> xm{};
+  Float dx{};
+  Field1D<Float, NY + 1, NGHOST> y{};
+  Field1D<Float, NY, NGHOST> ym{};
+  Float dy{};
+
+  Field2D<Float, NX, NY, NGHOST> visc{};
+  Field2D<Float, NX, NY, NGHOST> p{};
+  Float sigma{};
+  Field2D<Float, NX + 1, NY, NGHOST> p_jump_u_stag{};
+  Field2D<Float, NX, NY + 1, NGHOST> p_jump_v_stag{};
+
+  State<Float, NX, NY, NGHOST> old{};
+  State<Float, NX, NY, NGHOST> curr{};
+
+  // ---- device side (not in the reference) ----
+  fsgpu_ctx* ctx = nullptr;
+  int device     = 0;
+  ~FS() { if (ctx) fsgpu_destroy(ctx); }
+
+  // created by init_grid (dx, dy are known then)
+  void create_context() {
+    if (ctx) return;
+    FSGPU_CHECK(fsgpu_create(NX, NY, dx, dy, device, &ctx));
+    FSGPU_CHECK(fsgpu_set_props(ctx, rho_gas, rho_liquid, visc_gas, visc_liquid, sigma));
+    visc.bind(ctx, FSGPU_VISC); p.bind(ctx, FSGPU_P);
+    p_jump_u_stag.bind(ctx, FSGPU_P_JUMP_U); p_jump_v_stag.bind(ctx, FSGPU_P_JUMP_V);
+    old.rho_u_stag.bind(ctx, FSGPU_RHO_U_OLD); old.rho_v_stag.bind(ctx, FSGPU_RHO_V_OLD);
+    old.U.bind(ctx, FSGPU_U_OLD); old.V.bind(ctx, FSGPU_V_OLD);
+    curr.rho_u_stag.bind(ctx, FSGPU_RHO_U); curr.rho_v_stag.bind(ctx, FSGPU_RHO_V);
+    curr.U.bind(ctx, FSGPU_U); curr.V.bind(ctx, FSGPU_V);
+  }
+  // host mirrors -> HBM (after host-side initialisation) and back (before inspection / output)
+  void to_device() {
+    FSGPU_CHECK(fsgpu_set_props(ctx, rho_gas, rho_liquid, visc_gas, visc_liquid, sigma));
+    visc.upload(); p.upload(); p_jump_u_stag.upload(); p_jump_v_stag.upload();
+    old.rho_u_stag.upload(); old.rho_v_stag.upload(); old.U.upload(); old.V.upload();
+    curr.rho_u_stag.upload(); curr.rho_v_stag.upload(); curr.U.upload(); curr.V.upload();
+  }
+  void to_host() {
+    visc.download(); p.download();
+    old.rho_u_stag.download(); old.rho_v_stag.download(); old.U.download(); old.V.download();
+    curr.rho_u_stag.download(); curr.rho_v_stag.download(); curr.U.download(); curr.V.download();
+  }
+};
+
+// init_grid, src/FS.hpp:55-73 (+ creation of the device context)
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void init_grid(Float x_min, Float x_max, Index nx, Float y_min, Float y_max, Index ny,
+               FS<Float, NX, NY, NGHOST>& fs) {
+  fs.dx = (x_max - x_min) / static_cast<Float>(nx);
+  fs.dy = (y_max - y_min) / static_cast<Float>(ny);
+  for (Index i = -NGHOST; i < NX + 1 + NGHOST; ++i) fs.x(i) = x_min + static_cast<Float>(i) * fs.dx;
+  for (Index j = -NGHOST; j < NY + 1 + NGHOST; ++j) fs.y(j) = y_min + static_cast<Float>(j) * fs.dy;
+  for (Index i = -NGHOST; i < NX + NGHOST; ++i) fs.xm(i) = (fs.x(i) + fs.x(i + 1)) / 2;
+  for (Index j = -NGHOST; j < NY + NGHOST; ++j) fs.ym(j) = (fs.y(j) + fs.y(j + 1)) / 2;
+  fs.create_context();
+}
+
+// calc_rho(fs) / calc_visc(fs), src/FS.hpp:569-589 (constant properties, on the device)
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_rho(FS<Float, NX, NY, NGHOST>& fs) {
+  for (auto* f : {&fs.curr.rho_u_stag, &fs.old.rho_u_stag}) fill(*f, fs.rho_gas);
+  for (auto* f : {&fs.curr.rho_v_stag, &fs.old.rho_v_stag}) fill(*f, fs.rho_gas);
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_visc(FS<Float, NX, NY, NGHOST>& fs) { fill(fs.visc, fs.visc_gas); }
+
+// ---- boundary conditions (src/BoundaryConditions.hpp:14-224) --------------------------------------
+template <typename Float>
+struct Dirichlet {
+  std::variant<Float, Float (*)(Float, Float)> U{}, V{};
+};
+struct Neumann { bool clipped = false; };
+struct Periodic {};
+struct Symmetry {};
+template <typename Float>
+using BCond_t = std::variant<Dirichlet<Float>, Neumann, Periodic, Symmetry>;
+template <typename Float>
+struct FlowBConds { BCond_t<Float> left, right, bottom, top; };
+
+namespace fsgpu_shim {
+template <typename Float, Index NX, Index NY>
+void set_side(FS<Float, NX, NY, 1>& fs, int side, const BCond_t<Float>& bc, Float t) {
+  if (const auto* d = std::get_if<Dirichlet<Float>>(&bc)) {
+    // function-pointer profiles are evaluated on the host at the ghost-inclusive coordinates the
+    // reference uses (left/right: U at ym(j), V at y(j); bottom/top: U at x(i), V at xm(i))
+    const bool lr = side == FSGPU_LEFT || side == FSGPU_RIGHT;
+    std::vector<double> up, vp;
+    double uval = 0.0, vval = 0.0;
+    if (std::holds_alternative<Float>(d->U)) uval = std::get<0>(d->U);
+    else {
+      auto f = std::get<1>(d->U);
+      if (lr) for (Index j = -1; j <= NY; ++j) up.push_back(f(fs.ym(j), t));
+      else for (Index i = -1; i <= NX + 1; ++i) up.push_back(f(fs.x(i), t));
+    }
+    if (std::holds_alternative<Float>(d->V)) vval = std::get<0>(d->V);
+    else {
+      auto f = std::get<1>(d->V);
+      if (lr) for (Index j = -1; j <= NY + 1; ++j) vp.push_back(f(fs.y(j), t));
+      else for (Index i = -1; i <= NX; ++i) vp.push_back(f(fs.xm(i), t));
+    }
+    FSGPU_CHECK(fsgpu_set_bconds(fs.ctx, side, FSGPU_BC_DIRICHLET, uval, vval, up.empty() ? nullptr : up.data(),
+                                 vp.empty() ? nullptr : vp.data(), 0));
+  } else if (const auto* n = std::get_if<Neumann>(&bc)) {
+    FSGPU_CHECK(fsgpu_set_bconds(fs.ctx, side, FSGPU_BC_NEUMANN, 0, 0, nullptr, nullptr, n->clipped ? 1 : 0));
+  } else if (std::holds_alternative<Periodic>(bc)) {
+    FSGPU_CHECK(fsgpu_set_bconds(fs.ctx, side, FSGPU_BC_PERIODIC, 0, 0, nullptr, nullptr, 0));
+  } else {
+    FSGPU_CHECK(fsgpu_set_bconds(fs.ctx, side, FSGPU_BC_SYMMETRY, 0, 0, nullptr, nullptr, 0));
+  }
+}
+template <typename Float>
+bool time_dependent(const FlowBConds<Float>& b) {
+  for (const BCond_t<Float>* s : {&b.left, &b.right, &b.bottom, &b.top})
+    if (const auto* d = std::get_if<Dirichlet<Float>>(s))
+      if (!std::holds_alternative<Float>(d->U) || !std::holds_alternative<Float>(d->V)) return true;
+  return false;
+}
+}  // namespace fsgpu_shim
+
+// apply_velocity_bconds(fs, bconds, t), src/BoundaryConditions.hpp:215-224.  The side table is sent
+// to the device on the first call and again whenever a function-pointer profile may depend on t.
+template <typename Float, Index NX, Index NY>
+void apply_velocity_bconds(FS<Float, NX, NY, 1>& fs, const FlowBConds<Float>& bconds, Float t = -1.0) {
+  static const void* sent_for = nullptr;
+  static double sent_t        = 0.0;
+  if (sent_for != &fs || (fsgpu_shim::time_dependent(bconds) && sent_t != t)) {
+    fsgpu_shim::set_side(fs, FSGPU_LEFT, bconds.left, t);
+    fsgpu_shim::set_side(fs, FSGPU_RIGHT, bconds.right, t);
+    fsgpu_shim::set_side(fs, FSGPU_BOTTOM, bconds.bottom, t);
+    fsgpu_shim::set_side(fs, FSGPU_TOP, bconds.top, t);
+    sent_for = &fs;
+    sent_t   = t;
+  }
+  FSGPU_CHECK(fsgpu_apply_velocity_bconds(fs.ctx));
+}
+
+// ---- the stepping path (src/FS.hpp, src/Operators.hpp, src/Utility.hpp) ------------------------------
+// adjust_dt, src/FS.hpp:100-128
+template <typename Float, Index NX, Index NY, Index NGHOST>
+Float adjust_dt(const FS<Float, NX, NY, NGHOST>& fs, Float cfl_max, Float dt_max) {
+  double dt = 0.0;
+  FSGPU_CHECK(fsgpu_adjust_dt(fs.ctx, cfl_max, dt_max, &dt));
+  return dt;
+}
+// save_old_state / save_old_velocity / save_old_density, src/FS.hpp:76-97
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void save_old_state(const State<Float, NX, NY, NGHOST>& curr, State<Float, NX, NY, NGHOST>& old) {
+  (void)old;
+  FSGPU_CHECK(fsgpu_save_old_state(fsgpu_shim::ctx_of(curr.U)));
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void save_old_velocity(const State<Float, NX, NY, NGHOST>& curr, State<Float, NX, NY, NGHOST>&) {
+  FSGPU_CHECK(fsgpu_save_old_velocity(fsgpu_shim::ctx_of(curr.U)));
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void save_old_density(const State<Float, NX, NY, NGHOST>& curr, State<Float, NX, NY, NGHOST>&) {
+  FSGPU_CHECK(fsgpu_save_old_density(fsgpu_shim::ctx_of(curr.U)));
+}
+// calc_mid_time(current, old), src/Operators.hpp:44-49.  The drivers call it once for U and once for
+// V (scaling/LidDrivenFlow.cpp:128-129); the device pass averages both, so it runs on the U call.
+template <typename Float, Index M, Index N, Index NGHOST>
+void calc_mid_time(Field2D<Float, M, N, NGHOST>& current, const Field2D<Float, M, N, NGHOST>& old) {
+  (void)old;
+  if (current.field_id() == FSGPU_U) FSGPU_CHECK(fsgpu_calc_mid_time(fsgpu_shim::ctx_of(current)));
+  else if (current.field_id() != FSGPU_V) fsgpu_shim::check(1, "calc_mid_time on a field that is not curr.U / curr.V");
+}
+// calc_dmomdt(fs, dmomUdt, dmomVdt), src/FS.hpp:158-315
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_dmomdt(const FS<Float, NX, NY, NGHOST>& fs, Field2D<Float, NX + 1, NY, NGHOST>& dmomUdt,
+                 Field2D<Float, NX, NY + 1, NGHOST>& dmomVdt) {
+  dmomUdt.bind(fs.ctx, FSGPU_DMOM_U);
+  dmomVdt.bind(fs.ctx, FSGPU_DMOM_V);
+  FSGPU_CHECK(fsgpu_calc_dmomdt(fs.ctx));
+}
+// update_velocity(dmomUdt, dmomVdt, dt, fs), src/FS.hpp:423-436
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void update_velocity(const Field2D<Float, NX + 1, NY, NGHOST>&, const Field2D<Float, NX, NY + 1, NGHOST>&,
+                     Float dt, FS<Float, NX, NY, NGHOST>& fs) {
+  FSGPU_CHECK(fsgpu_update_velocity(fs.ctx, dt));
+}
+// calc_divergence(U, V, dx, dy, div), src/Operators.hpp:32-41
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_divergence(const Field2D<Float, NX + 1, NY, NGHOST>& U, const Field2D<Float, NX, NY + 1, NGHOST>& V,
+                     Float, Float, Field2D<Float, NX, NY, NGHOST>& div) {
+  if (U.field_id() != FSGPU_U || V.field_id() != FSGPU_V) fsgpu_shim::check(1, "calc_divergence expects fs.curr.U, fs.curr.V");
+  div.bind(fsgpu_shim::ctx_of(U), FSGPU_DIV);
+  FSGPU_CHECK(fsgpu_calc_divergence(fsgpu_shim::ctx_of(U)));
+}
+// shift_pressure_to_zero(dx, dy, delta_p), src/Operators.hpp:78-82
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void shift_pressure_to_zero(Float, Float, Field2D<Float, NX, NY, NGHOST>& dp) {
+  FSGPU_CHECK(fsgpu_shift_pressure_to_zero(fsgpu_shim::ctx_of(dp)));
+}
+// the projection every driver inlines: p += delta_p; U, V -= grad(delta_p) dt / rho
+// (scaling/LidDrivenFlow.cpp:153-160; variable density: test/LaminarChannel.cpp:222-233)
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void correct_velocity(FS<Float, NX, NY, NGHOST>& fs, const Field2D<Float, NX, NY, NGHOST>&, Float dt) {
+  FSGPU_CHECK(fsgpu_correct_velocity(fs.ctx, dt));
+}
+// abs_max(field), src/Utility.hpp:80-88
+template <typename Float, Index M, Index N, Index NGHOST>
+Float abs_max(const Field2D<Float, M, N, NGHOST>& f) {
+  double v = 0.0;
+  FSGPU_CHECK(fsgpu_abs_max(fsgpu_shim::ctx_of(f), f.field_id(), &v));
+  return v;
+}
+
+// ---- LinearSolver_StructHypre (src/LinearSolver_StructHypre.hpp:28-192) ----------------------------
+enum class HypreSolver { GMRES, PCG, BiCGSTAB };   // only PCG + PFMG (the reference's defaults) exist here
+enum class HyprePrecond { SMG, PFMG, NONE };
+enum class PSDirichlet { NONE, LEFT, RIGHT, BOTTOM, TOP };  // src/LinearSystem.hpp:10
+
+template <typename Float, Index NX, Index NY, Index NGHOST>
+class LinearSolver_StructHypre {
+  fsgpu_ps* m_ps   = nullptr;
+  fsgpu_ctx* m_ctx = nullptr;
+  fsgpu_ps_opts m_opts{};
+  void create(fsgpu_ctx* ctx) {
+    if (!m_ps) FSGPU_CHECK(fsgpu_ps_create(ctx, &m_opts, &m_ps));
+    m_ctx = ctx;
+  }
+ public:
+  LinearSolver_StructHypre(Float tol, int max_iter, HypreSolver solver = HypreSolver::PCG,
+                           HyprePrecond precond = HyprePrecond::PFMG, PSDirichlet psd = PSDirichlet::NONE) {
+    if (solver != HypreSolver::PCG || precond != HyprePrecond::PFMG)
+      fsgpu_shim::check(1, "LinearSolver_StructHypre: only PCG + PFMG is implemented on the GPU");
+    m_opts.tol = tol; m_opts.max_iter = max_iter; m_opts.psd = static_cast<int>(psd);
+    m_opts.relax = 0; m_opts.max_levels = 0; m_opts.skip_relax = -1;
+  }
+  LinearSolver_StructHypre(const LinearSolver_StructHypre&)            = delete;
+  LinearSolver_StructHypre& operator=(const LinearSolver_StructHypre&) = delete;
+  ~LinearSolver_StructHypre() { if (m_ps) fsgpu_ps_destroy(m_ps); }
+
+  void set_pressure_operator(const FS<Float, NX, NY, NGHOST>& fs) {   // :91-106
+    create(fs.ctx);
+    FSGPU_CHECK(fsgpu_ps_set_operator(m_ps));
+  }
+  void set_pressure_rhs(const FS<Float, NX, NY, NGHOST>& fs, const Field2D<Float, NX, NY, NGHOST>& div,
+                        Float dt) {                                     // :109-116
+    if (div.field_id() != FSGPU_DIV) fsgpu_shim::check(1, "set_pressure_rhs expects the field calc_divergence wrote");
+    create(fs.ctx);
+    FSGPU_CHECK(fsgpu_ps_set_rhs(m_ps, dt));
+  }
+  // :119-192.  Non-convergence only warns, as in the reference (:177-183)
+  bool solve(Field2D<Float, NX, NY, NGHOST>& sol, Float* residual = nullptr, Index* num_iter = nullptr) {
+    double res = 0.0;
+    int it     = 0;
+    if (!m_ps) fsgpu_shim::check(1, "solve before set_pressure_operator");
+    FSGPU_CHECK(fsgpu_ps_solve(m_ps, &res, &it));
+    sol.bind(m_ctx, FSGPU_DELTA_P);
+    if (residual) *residual = res;
+    if (num_iter) *num_iter = it;
+#ifndef FS_SILENCE_CONV_WARN
+    if (it >= m_opts.max_iter && res >= m_opts.tol)
+      std::fprintf(stderr, "[WARN] pressure solve did not converge: residual %.6e after %d iterations\n", res, it);
+#endif
+    return true;
+  }
+  fsgpu_ps* handle() { return m_ps; }
+};
+
+#endif  // FSGPU_SHIM_FLUIDSOLVERGPU_HPP_
