@@ -143,8 +143,8 @@ ALGO_BYTES = {
     "matvec_dot": 40.0,        # read p, d, cx, cy; write s
     "xr_update": 48.0,         # read x, p, r, s; write x, r
     "p_update": 24.0,          # read z, p; write p
-    "vcycle_down_l0": 40.0,    # read r, dinv, cx, cy, pc(F rows: 0.5); write b_coarse (0.5)
-    "vcycle_up_l0": 56.0,      # read r, dinv, d, cx, cy, pc (0.5), x_coarse (0.5); write z
+    "vcycle_down_l0": 36.0,    # read r, d, cx, cy; write b_coarse (0.5)   (dinv, pc recomputed in registers)
+    "vcycle_up_l0": 44.0,      # read r, d, cx, cy, x_coarse (0.5); write z (dinv, pc recomputed in registers)
     "momentum": 112.0,         # 12 fields read, U and V written
     "div_rhs": 48.0,           # read U, V; write div, rhs; second pass rhs -= mean (read + write)
     "shift_correct": 104.0,    # sum dp (1), dp -= c (2), read dp, p, U, V, rho_u, rho_v; write p, U, V (10)

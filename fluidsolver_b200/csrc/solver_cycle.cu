@@ -16,9 +16,21 @@
 
 #include <utility>
 
+// resident CTAs per SM the marching kernels are compiled for (register cap = 65536 / (128 * MINB))
+#ifndef FS_MARCH_MINB
+#define FS_MARCH_MINB 8
+#endif
+
 namespace {
 
 constexpr int BX = 64, BY = 4;
+
+// 1 / v with the convention of the stored dinv / pc arrays (0 where v == 0: pads, halo-less walls,
+// a singular coarsest point).  The active-level kernels recompute dinv = 1/d and the interpolation
+// denominator pc = 1/(d + t_m + t_p) from d, cx, cy instead of loading them: two FP64 divisions
+// per point buy 16 B/point less HBM traffic, and the values are bit-identical to the stored ones
+// (same operands, same association as k_interp / k_rap, correctly rounded division).
+__device__ __forceinline__ double rcp0(double v) { return v != 0.0 ? 1.0 / v : 0.0; }
 
 template <int CDIR>
 struct Coef {
@@ -33,7 +45,7 @@ struct Coef {
 // R of the row above from three rows of X held in registers (left/right by shuffle), and on every
 // second row the coarse rhs  b_c = R + pp(row-1) R(row-1) + pm(row+1) R(row+1).
 template <bool ACTIVE>
-__global__ void __launch_bounds__(128, 8)
+__global__ void __launch_bounds__(128, FS_MARCH_MINB)
 k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
               double* __restrict__ cb, double w, int mrc, const PcgScal* scal) {
   if (scal->done) return;
@@ -50,16 +62,19 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
     const int c0 = c_lo + ch * mrc, c1 = min(c0 + mrc, c_hi);
     const int f0 = 2 * c0 + foff, fL = 2 * (c1 - 1) + foff;
     double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx2 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0, Ra = 0.0, Rb = 0.0;
+    double pc1 = 0.0, pc2 = 0.0, pc3 = 0.0;  // ACTIVE: pc of rows li - 1, li - 2, li - 3
     int li = f0 - 2;
     int o  = (li + FS_RO) * P + lj + FS_CO;
 #pragma unroll 2
     for (; li <= fL + 2; ++li, o += P) {
       const double b0 = __ldg(fb + o), cx0 = __ldg(f.cx + o);
-      double X0 = 0.0, cy0 = 0.0, cy0p = 0.0;
+      double X0 = 0.0, cy0 = 0.0, cy0p = 0.0, pc0 = 0.0;
       if (ACTIVE) {
-        X0   = w * b0 * __ldg(f.dinv + o);
+        const double d0 = __ldg(f.d + o);
         cy0  = __ldg(f.cy + o);
         cy0p = __ldg(f.cy + o + 1);
+        X0   = w * b0 * rcp0(d0);
+        pc0  = rcp0(d0 + cy0 + cy0p);
       }
       // residual of row li - 1
       double Rn;
@@ -76,13 +91,15 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
       }
       // coarse point on row li - 2 (a C row when li - f0 is even)
       if (li >= f0 + 2 && ((li - f0) & 1) == 0) {
-        const double pcm = __ldg(f.pc + o - 3 * P), pcp = __ldg(f.pc + o - P);
+        const double pcm = ACTIVE ? pc3 : __ldg(f.pc + o - 3 * P);
+        const double pcp = ACTIVE ? pc1 : __ldg(f.pc + o - P);
         double v = Rb;
         v += (-cx2 * pcm) * Ra;
         v += (-cx1 * pcp) * Rn;
         if (store_lane) cb[(((li - 2 - foff) >> 1) + FS_RO) * Pc + lj + FS_CO] = v;
       }
       X2 = X1; X1 = X0; b1 = b0; cx2 = cx1; cx1 = cx0; cy1 = cy0; cy1p = cy0p; Ra = Rb; Rb = Rn;
+      pc3 = pc2; pc2 = pc1; pc1 = pc0;
     }
   }
 }
@@ -90,7 +107,7 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
 // k_down_march1: coarsening along j.  Lanes 1..30 hold a valid residual (X of the neighbours by
 // shuffle), lanes 2..29 that sit on a C column emit  b_c = R + pp(j-1) R(j-1) + pm(j+1) R(j+1).
 template <bool ACTIVE>
-__global__ void __launch_bounds__(128, 8)
+__global__ void __launch_bounds__(128, FS_MARCH_MINB)
 k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
               double* __restrict__ cb, double w, int mr, const PcgScal* scal) {
   if (scal->done) return;
@@ -107,16 +124,17 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
     const int oc_col = (pos >> 1) + FS_CO;
     if (lj > n1) lj = n1;
     const int r0 = f_lo + ch * mr, r1 = min(r0 + mr, f_hi);
-    double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0;
+    double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0, d1 = 0.0;
     int li = r0 - 1;
     int o  = (li + FS_RO) * P + lj + FS_CO;
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
       const double b0 = __ldg(fb + o);
       const double cy0 = __ldg(f.cy + o), cy0p = __ldg(f.cy + o + 1);
-      double X0 = 0.0, cx0 = 0.0;
+      double X0 = 0.0, cx0 = 0.0, d0 = 0.0;
       if (ACTIVE) {
-        X0  = w * b0 * __ldg(f.dinv + o);
+        d0  = __ldg(f.d + o);
+        X0  = w * b0 * rcp0(d0);
         cx0 = __ldg(f.cx + o);
       }
       if (li > r0) {  // row li - 1
@@ -132,7 +150,7 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
         } else {
           Rn = b1;
         }
-        const double pcv = __ldg(f.pc + o - P);
+        const double pcv = ACTIVE ? rcp0(d1 + cx1 + cx0) : __ldg(f.pc + o - P);
         const double pcl = __shfl_up_sync(0xffffffffu, pcv, 1), pcr = __shfl_down_sync(0xffffffffu, pcv, 1);
         const double Rl = __shfl_up_sync(0xffffffffu, Rn, 1), Rr = __shfl_down_sync(0xffffffffu, Rn, 1);
         double v = Rn;
@@ -140,7 +158,7 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
         v += (-cy1p * pcr) * Rr;
         if (store_lane) cb[(li - 1 + FS_RO) * Pc + oc_col] = v;
       }
-      X2 = X1; X1 = X0; b1 = b0; cx1 = cx0; cy1 = cy0; cy1p = cy0p;
+      X2 = X1; X1 = X0; b1 = b0; cx1 = cx0; cy1 = cy0; cy1p = cy0p; d1 = d0;
     }
   }
 }
@@ -194,7 +212,7 @@ k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
 constexpr int MOUT = 30, MWARPS = 4;
 
 template <int CDIR, int DOT>
-__global__ void __launch_bounds__(32 * MWARPS, 8)
+__global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB)
 k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
            const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part,
            unsigned int* ticket) {
@@ -211,14 +229,14 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
     const bool store_lane = lane >= 1 && lane <= MOUT && lj < n1;
     if (lj > n1) lj = n1;  // the zero pad column right of the grid
     const int r0 = f_lo + ch * mr, r1 = min(r0 + mr, f_hi);
-    double x0p = 0.0, x0c = 0.0, bc = 0.0, dic = 0.0, cyc = 0.0, cy1c = 0.0, cxc = 0.0;
+    double x0p = 0.0, x0c = 0.0, bc = 0.0, dic = 0.0, dc = 0.0, cyc = 0.0, cy1c = 0.0, cxc = 0.0;
     int li = r0 - 1;
     int o  = (li + FS_RO) * P + lj + FS_CO;
     double cxn = __ldg(f.cx + o);
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
       const double cxnn = __ldg(f.cx + o + P);
-      const double bn = __ldg(fb + o), din = __ldg(f.dinv + o);
+      const double bn = __ldg(fb + o), dn = __ldg(f.d + o), din = rcp0(dn);
       const double cyn = __ldg(f.cy + o), cy1n = __ldg(f.cy + o + 1);
       double xi;
       if (CDIR == 0) {
@@ -228,7 +246,7 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
         if (par == 0) {  // C row (warp uniform)
           xi = xm;
         } else {
-          const double pcv = __ldg(f.pc + o), xp = __ldg(xc + oc + Pc);
+          const double pcv = rcp0(dn + cyn + cy1n), xp = __ldg(xc + oc + Pc);
           double v = (-cxn * pcv) * xm;
           v += (-cxnn * pcv) * xp;
           xi = v;
@@ -236,14 +254,14 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
       } else {
         const int pos = lj - foff, par = pos & 1;
         const int oc  = (li + FS_RO) * Pc + ((pos - par) >> 1) + FS_CO;
-        const double xm = __ldg(xc + oc), xp = __ldg(xc + oc + 1), pcv = __ldg(f.pc + o);
+        const double xm = __ldg(xc + oc), xp = __ldg(xc + oc + 1), pcv = rcp0(dn + cxn + cxnn);
         double v = (-cyn * pcv) * xm;
         v += (-cy1n * pcv) * xp;
         xi = par ? v : xm;
       }
       const double x0n = w * bn * din + xi;
       if (li > r0) {  // emit row li - 1
-        const double dd = __ldg(f.d + o - P);
+        const double dd = dc;
         const double xl = __shfl_up_sync(0xffffffffu, x0c, 1), xr = __shfl_down_sync(0xffffffffu, x0c, 1);
         double v = dd * x0c;
         v += cxc * x0p;
@@ -256,7 +274,7 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
           if (DOT) acc[0] += bc * xo;
         }
       }
-      x0p = x0c; x0c = x0n; bc = bn; dic = din; cyc = cyn; cy1c = cy1n; cxc = cxn; cxn = cxnn;
+      x0p = x0c; x0c = x0n; bc = bn; dic = din; dc = dn; cyc = cyn; cy1c = cy1n; cxc = cxn; cxn = cxnn;
     }
   }
   if (DOT) {
@@ -287,6 +305,9 @@ k_dot_rz(const LevelDev L, const double* __restrict__ r, const double* __restric
 // ---- coarsest level: `sweeps` Jacobi sweeps with weight 1 from a zero guess
 // (pfmg_setup.c:400-412 sets the sweep count, pfmg_relax.c / jacobi.c the iteration).
 // One CTA; x ping-pongs between two shared-memory tiles with a one-point zero ring.
+// STAGE: the five coefficient arrays and b are staged in shared memory as well (7 tiles), so a
+// sweep touches no global memory at all; otherwise they are re-read through L1/L2 every sweep.
+template <bool STAGE>
 __global__ void __launch_bounds__(1024)
 k_coarse_smem(const LevelDev L, const double* __restrict__ b, double* __restrict__ x, int sweeps,
               int active, const PcgScal* scal) {
@@ -295,25 +316,39 @@ k_coarse_smem(const LevelDev L, const double* __restrict__ b, double* __restrict
   const int64_t n0 = L.n0, n1 = L.n1, w1 = n1 + 2, tot = (n0 + 2) * w1, n = n0 * n1;
   double* xa = sm;
   double* xb = sm + tot;
+  double *sd = sm + 2 * tot, *sdi = sm + 3 * tot, *scx = sm + 4 * tot, *scy = sm + 5 * tot, *sb = sm + 6 * tot;
   const bool on = active && !scal->coarse_zero_diag;
-  for (int64_t t = threadIdx.x; t < 2 * tot; t += blockDim.x) sm[t] = 0.0;
+  for (int64_t t = threadIdx.x; t < (STAGE ? 7 : 2) * tot; t += blockDim.x) sm[t] = 0.0;
   __syncthreads();
   if (on) {
     for (int64_t t = threadIdx.x; t < n; t += blockDim.x) {
-      const int64_t li = t / n1, lj = t - li * n1, k = L.idx(li, lj);
-      xa[(li + 1) * w1 + lj + 1] = b[k] * L.dinv[k];
+      const int64_t li = t / n1, lj = t - li * n1, k = L.idx(li, lj), m = (li + 1) * w1 + lj + 1;
+      xa[m] = b[k] * L.dinv[k];
+      if (STAGE) {  // couplings past the edge stay 0, as the pads of the global arrays
+        sd[m] = L.d[k]; sdi[m] = L.dinv[k]; scx[m] = L.cx[k]; scy[m] = L.cy[k]; sb[m] = b[k];
+      }
     }
     __syncthreads();
     for (int it = 1; it < sweeps; ++it) {
       for (int64_t t = threadIdx.x; t < n; t += blockDim.x) {
-        const int64_t li = t / n1, lj = t - li * n1, k = L.idx(li, lj), P = L.pitch;
+        const int64_t li = t / n1, lj = t - li * n1;
         const int64_t m = (li + 1) * w1 + lj + 1;
-        double v = L.d[k] * xa[m];
-        v += L.cx[k] * xa[m - w1];
-        v += L.cx[k + P] * xa[m + w1];
-        v += L.cy[k] * xa[m - 1];
-        v += L.cy[k + 1] * xa[m + 1];
-        xb[m] = xa[m] + (b[k] - v) * L.dinv[k];
+        if (STAGE) {
+          double v = sd[m] * xa[m];
+          v += scx[m] * xa[m - w1];
+          v += scx[m + w1] * xa[m + w1];
+          v += scy[m] * xa[m - 1];
+          v += scy[m + 1] * xa[m + 1];
+          xb[m] = xa[m] + (sb[m] - v) * sdi[m];
+        } else {
+          const int64_t k = L.idx(li, lj), P = L.pitch;
+          double v = L.d[k] * xa[m];
+          v += L.cx[k] * xa[m - w1];
+          v += L.cx[k + P] * xa[m + w1];
+          v += L.cy[k] * xa[m - 1];
+          v += L.cy[k + 1] * xa[m + 1];
+          xb[m] = xa[m] + (b[k] - v) * L.dinv[k];
+        }
       }
       __syncthreads();
       double* t2 = xa; xa = xb; xb = t2;
@@ -359,11 +394,17 @@ dim3 lvl_grid(const LevelDev& v) { return dim3((unsigned)cdiv(v.n1, BX), (unsign
 static int coarse_solve(fsgpu_ps* s, int l, const double* b, double* x) {
   cudaStream_t st = s->c->stream;
   const Level& L  = s->L[l];
-  const size_t smem = (size_t)(2 * (L.v.n0 + 2) * (L.v.n1 + 2)) * sizeof(double);
-  if (smem <= 200 * 1024) {
+  const size_t tile = (size_t)((L.v.n0 + 2) * (L.v.n1 + 2)) * sizeof(double);
+  const size_t cap  = 200 * 1024;
+  if (2 * tile <= cap) {
     // per device, and cheap: set on every call (several contexts / devices may share the process)
-    FS_CUDA(cudaFuncSetAttribute(k_coarse_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    k_coarse_smem<<<1, 1024, smem, st>>>(L.v, b, x, s->coarse_sweeps, L.active, s->scal);
+    if (7 * tile <= cap) {
+      FS_CUDA(cudaFuncSetAttribute(k_coarse_smem<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap));
+      k_coarse_smem<true><<<1, 1024, 7 * tile, st>>>(L.v, b, x, s->coarse_sweeps, L.active, s->scal);
+    } else {
+      FS_CUDA(cudaFuncSetAttribute(k_coarse_smem<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap));
+      k_coarse_smem<false><<<1, 1024, 2 * tile, st>>>(L.v, b, x, s->coarse_sweeps, L.active, s->scal);
+    }
     FS_LAUNCHED();
     return 0;
   }
@@ -386,6 +427,9 @@ static int coarse_solve(fsgpu_ps* s, int l, const double* b, double* x) {
 static int pick_rows(int64_t rows, int64_t strips) {
   int mr = 64;
   while (mr > 4 && strips * cdiv(rows, mr) < (int64_t)FS_NUM_SMS * 16) mr >>= 1;
+  // tiny levels are pure latency: a task's rows are a serial chain of dependent loads, so hand
+  // every warp as few rows as possible while the whole level still fits one wave of CTAs
+  while (mr > 1 && strips * cdiv(rows, mr) < (int64_t)FS_NUM_SMS * 2) mr >>= 1;
   return mr;
 }
 static unsigned march_blocks(int64_t rows, int64_t strips, int mr) {

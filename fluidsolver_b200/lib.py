@@ -15,7 +15,8 @@ import weakref
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libfsgpu.so")
+# FSGPU_LIB: load another build of the same library (kernel-variant A/B runs); default in-tree
+LIB_PATH = os.environ.get("FSGPU_LIB") or os.path.join(HERE, "libfsgpu.so")
 
 FIELDS = ("VISC", "P", "P_JUMP_U", "P_JUMP_V", "RHO_U_OLD", "RHO_V_OLD", "U_OLD", "V_OLD", "RHO_U",
           "RHO_V", "U", "V", "DMOM_U", "DMOM_V", "DIV", "DELTA_P", "VF", "RHS")

@@ -28,3 +28,6 @@ if [ -f /tmp/${TAG}_full.ncu-rep ]; then
   [ "$SZ" -lt 45000000 ] && cp /tmp/${TAG}_full.ncu-rep gpurun_out/
 fi
 ls -la gpurun_out
+# strong-scaling baseline: the 16384^2 workload on ONE GPU
+timeout 600 python bench.py --grid 16384 --steps 3 --warmup 2 --no-cpu > gpurun_out/${TAG}_bench16384.json 2> gpurun_out/${TAG}_bench16384.err; echo "bench16384 exit $?"
+cat gpurun_out/${TAG}_bench16384.json
