@@ -20,6 +20,14 @@
 #ifndef FS_MARCH_MINB
 #define FS_MARCH_MINB 8
 #endif
+// k_up_march operand policy: 0 load dinv and pc; 1 recompute both (two divisions per point);
+// 2 load dinv, recompute pc (half a division per point on an i-coarsened level)
+#ifndef FS_UP_MODE
+#define FS_UP_MODE 1
+#endif
+#ifndef FS_UP_PREFETCH
+#define FS_UP_PREFETCH 0
+#endif
 
 namespace {
 
@@ -233,31 +241,83 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
     int li = r0 - 1;
     int o  = (li + FS_RO) * P + lj + FS_CO;
     double cxn = __ldg(f.cx + o);
+    // operands of one row, loaded one row AHEAD of their use (software pipelining: the loads of
+    // row li + 1 are in flight while row li is computed, independent of what the compiler hoists)
+    struct Row { double b, d, di, cy, cy1, cxnn, xm, xp, pc; };
+    auto load_row = [&](int li_, int o_) {
+      Row q;
+      q.cxnn = __ldg(f.cx + o_ + P);
+      q.b    = __ldg(fb + o_);
+      q.cy   = __ldg(f.cy + o_);
+      q.cy1  = __ldg(f.cy + o_ + 1);
+#if FS_UP_MODE == 1
+      q.d = __ldg(f.d + o_);  q.di = 0.0;  q.pc = 0.0;
+#elif FS_UP_MODE == 2
+      q.d = __ldg(f.d + o_);  q.di = __ldg(f.dinv + o_);  q.pc = 0.0;
+#else
+      q.d = __ldg(f.d + o_);  q.di = __ldg(f.dinv + o_);  q.pc = 0.0;
+#endif
+      if (CDIR == 0) {
+        const int pos = li_ - foff, par = pos & 1;
+        const int oc  = (((pos - par) >> 1) + FS_RO) * Pc + lj + FS_CO;
+        q.xm = __ldg(xc + oc);
+        q.xp = par ? __ldg(xc + oc + Pc) : 0.0;
+#if FS_UP_MODE == 0
+        if (par) q.pc = __ldg(f.pc + o_);
+#endif
+      } else {
+        const int pos = lj - foff, par = pos & 1;
+        const int oc  = (li_ + FS_RO) * Pc + ((pos - par) >> 1) + FS_CO;
+        q.xm = __ldg(xc + oc);
+        q.xp = __ldg(xc + oc + 1);
+#if FS_UP_MODE == 0
+        q.pc = __ldg(f.pc + o_);
+#endif
+      }
+      return q;
+    };
+#if FS_UP_PREFETCH
+    Row nx = load_row(li, o);
+#endif
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
-      const double cxnn = __ldg(f.cx + o + P);
-      const double bn = __ldg(fb + o), dn = __ldg(f.d + o), din = rcp0(dn);
-      const double cyn = __ldg(f.cy + o), cy1n = __ldg(f.cy + o + 1);
+#if FS_UP_PREFETCH
+      const Row q = nx;
+      if (li < r1) nx = load_row(li + 1, o + P);
+#else
+      const Row q = load_row(li, o);
+#endif
+      const double cxnn = q.cxnn, bn = q.b, dn = q.d, cyn = q.cy, cy1n = q.cy1;
+#if FS_UP_MODE == 1
+      const double din = rcp0(dn);
+#else
+      const double din = q.di;
+#endif
       double xi;
       if (CDIR == 0) {
-        const int pos = li - foff, par = pos & 1;
-        const int oc  = (((pos - par) >> 1) + FS_RO) * Pc + lj + FS_CO;
-        const double xm = __ldg(xc + oc);
+        const int par = (li - foff) & 1;
         if (par == 0) {  // C row (warp uniform)
-          xi = xm;
+          xi = q.xm;
         } else {
-          const double pcv = rcp0(dn + cyn + cy1n), xp = __ldg(xc + oc + Pc);
-          double v = (-cxn * pcv) * xm;
-          v += (-cxnn * pcv) * xp;
+#if FS_UP_MODE == 0
+          const double pcv = q.pc;
+#else
+          const double pcv = rcp0(dn + cyn + cy1n);
+#endif
+          double v = (-cxn * pcv) * q.xm;
+          v += (-cxnn * pcv) * q.xp;
           xi = v;
         }
       } else {
-        const int pos = lj - foff, par = pos & 1;
-        const int oc  = (li + FS_RO) * Pc + ((pos - par) >> 1) + FS_CO;
-        const double xm = __ldg(xc + oc), xp = __ldg(xc + oc + 1), pcv = rcp0(dn + cxn + cxnn);
-        double v = (-cyn * pcv) * xm;
-        v += (-cy1n * pcv) * xp;
-        xi = par ? v : xm;
+        const int par = (lj - foff) & 1;
+#if FS_UP_MODE == 0
+        const double pcv = q.pc;
+#else
+        const double pcv = rcp0(dn + cxn + cxnn);
+#endif
+        double v = (-cyn * pcv) * q.xm;
+        v += (-cy1n * pcv) * q.xp;
+        xi = par ? v : q.xm;
       }
       const double x0n = w * bn * din + xi;
       if (li > r0) {  // emit row li - 1
