@@ -43,7 +43,10 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--grid", dest="n", type=int, default=0, help="grid size override (default 8192; 16384 for N > 1)")
-    ap.add_argument("--max-levels", type=int, default=-1, help="multigrid depth (-1: library default)")
+    ap.add_argument("--max-levels", type=int, default=40,
+                    help="multigrid depth cap (default 40 = uncapped: coarsen down to one point; 16 = the "
+                         "reference's PS_PFMG_MAX_LEVELS, src/LinearSolver_StructHypre.hpp:221-229)")
+    ap.add_argument("--no-ref-depth", action="store_true", help="skip the secondary 16-level measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--prof", default="", help="kernel class to time for the roofline (default: auto)")
@@ -200,6 +203,12 @@ def main():
     for s, u in enumerate((0.0, 0.0, 0.0, 1.0)):
         fs.set_bconds(s, F.DIRICHLET, u, 0.0)
     fs.apply_velocity_bconds()
+    # Multigrid depth.  The reference caps PFMG at 16 semicoarsened levels (a knob of its HYPRE
+    # wrapper); from 2048^2 upwards that leaves a coarsest grid far too large for its few Jacobi
+    # sweeps and the PCG iteration count climbs (13 at 8192^2, 23 at 16384^2 instead of 7).  The
+    # GPU solver coarsens down to a single point by default here -- same stopping tolerance, same
+    # operator, same smoother -- and the capped configuration is timed next to it
+    # (config.reference_depth_16).
     ps = F.LinearSolver(fs, tol=TOL, max_iter=MAX_ITER, max_levels=max(a.max_levels, 0))
     ps.set_pressure_operator()
     stream = torch.cuda.ExternalStream(fs.stream(), device=torch.device("cuda", local))
@@ -305,6 +314,32 @@ def main():
     umax = fs.abs_max("U")
     levels = (ps.num_levels, ps.num_distributed_levels)
     ps.close()
+    # the same steps with the reference's 16-level cap (secondary number, device-resident timing)
+    ref_depth = None
+    if not a.no_ref_depth and levels[0] > 16:
+        ps16 = F.LinearSolver(fs, tol=TOL, max_iter=MAX_ITER, max_levels=16)
+        ps16.set_pressure_operator()
+        k16 = max(1, min(a.steps, 3))
+        fs.step(ps16, fs.adjust_dt(CFL, DT_MAX), NSUB)  # warm-up
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fs.sync()
+        if dist:
+            dist.barrier()
+        f0.record(stream)
+        it16 = 0
+        for _ in range(k16):
+            it16 += fs.step(ps16, fs.adjust_dt(CFL, DT_MAX), NSUB)[1]
+        f1.record(stream)
+        fs.sync()
+        torch.cuda.synchronize()
+        ms16 = f0.elapsed_time(f1)
+        if dist:
+            t = torch.tensor([ms16], dtype=torch.float64, device=f"cuda:{local}")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms16 = float(t.item())
+        ref_depth = {"value": n * n * k16 / (ms16 * 1e-3) / 1e6, "unit": "MCell-updates/s", "mg_levels": 16,
+                     "pcg_iters_per_solve": it16 / (k16 * NSUB), "steps": k16}
+        ps16.close()
     fs.close()
     if dist:
         dist.barrier()
@@ -324,6 +359,8 @@ def main():
             "config": {"workload": f"lid-driven cavity {n}^2 (scaling/LidDrivenFlow.cpp:16-42), NUM_SUBITER {NSUB}, "
                                    f"PCG tol {TOL} max_iter {MAX_ITER}, CFL {CFL}",
                        "pcg_iters_per_solve": k_bar, "mg_levels": levels[0],
+                       "mg_depth": "uncapped (coarsest grid = 1 point)" if a.max_levels >= 40 else f"capped at {a.max_levels}",
+                       "reference_depth_16": ref_depth,
                        "decomposition": None if world == 1 else
                        f"{world} slabs of i-rows, NCCL halo exchange + all-reduce, multigrid levels "
                        f"0..{levels[1] - 1} distributed, {levels[1]}..{levels[0] - 1} replicated", "l2": "inputs larger than L2 "

@@ -92,6 +92,38 @@ def test_truncated_hierarchy(F, oracle, max_levels):
     fs.close()
 
 
+def test_uncapped_depth_at_scale(F):
+    """2048^2 (where the reference's 16-level cap already truncates the hierarchy): the uncapped
+    hierarchy -- bench.py's default -- and the capped one are two different preconditioners for the
+    SAME system, so their solutions must agree to the solver tolerance; the uncapped one needs
+    fewer iterations.  Size-independent property, no oracle needed."""
+    n = 2048
+    rng = np.random.default_rng(11)
+    fs = F.FS(n, n, 1.0 / n, 1.0 / n, 1.0, 1.0, 1e-3, 1e-3)
+    fs.calc_rho_visc_const()
+    fs.upload("U", 0.1 * rng.uniform(-1, 1, F.field_shape("U", n, n)))
+    fs.upload("V", 0.1 * rng.uniform(-1, 1, F.field_shape("V", n, n)))
+    for s_, u in enumerate((0.0, 0.0, 0.0, 1.0)):
+        fs.set_bconds(s_, F.DIRICHLET, u, 0.0)
+    fs.apply_velocity_bconds()
+    fs.calc_divergence()
+    sols, its = [], []
+    for ml in (16, 40):
+        ps = F.LinearSolver(fs, tol=1e-10, max_iter=200, max_levels=ml)
+        ps.set_pressure_operator()
+        ps.set_pressure_rhs(1e-3)
+        res, it = ps.solve()
+        assert res < 1e-10
+        assert ps.num_levels == (16 if ml == 16 else 25)  # 2050 -> 1 takes 12 halvings per direction
+        dp = fs.download("DELTA_P")
+        sols.append(dp - dp.mean())
+        its.append(it)
+        ps.close()
+    fs.close()
+    assert its[1] < its[0], its
+    assert rel_l2(sols[1], sols[0]) <= 1e-7
+
+
 def test_zero_rhs_and_max_iter(F, oracle):
     st = cavity_state(oracle, 32, 32)
     fs = to_gpu(F, st, cavity_bc())
