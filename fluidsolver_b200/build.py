@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "csrc", "build")
 LIB = os.path.join(HERE, "libfsgpu.so")
-SOURCES = ["stencil.cu", "bconds.cu", "project.cu", "solver_setup.cu", "solver_cycle.cu",
+SOURCES = ["stencil.cu", "bconds.cu", "project.cu", "twophase.cu", "solver_setup.cu", "solver_cycle.cu",
            "solver_pcg.cu", "comm.cu", "api.cu"]
 NO_FMA = {"solver_setup.cu"}
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

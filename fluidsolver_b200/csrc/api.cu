@@ -58,6 +58,7 @@ void fs_set_error(const char* fmt, ...) {
       fs_set_error("%s: bad field id %d", __func__, (f));  \
       return 1;                                            \
     }                                                      \
+    if (fs_ensure_field(c, (f))) return 1;                 \
   } while (0)
 
 extern "C" {
@@ -134,13 +135,13 @@ int fsgpu_create_slab(int64_t nx, int64_t ny, double dx, double dy, int device, 
   c->g.pitch = (ny + 3 + FS_CO + 2 + 15) / 16 * 16;
   c->g.rows  = (a_hi - a_lo) + 1 + 2 * FS_RO;
   const size_t n = (size_t)c->g.count();
-  const int nf = FSGPU_NUM_FIELDS + 2;
+  const int nf = FSGPU_NUM_CORE_FIELDS + 2;
   FS_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   FS_CUDA(cudaMalloc(&c->slab, n * nf * sizeof(double)));
   FS_CUDA(cudaMemsetAsync(c->slab, 0, n * nf * sizeof(double), c->stream));
-  for (int f = 0; f < FSGPU_NUM_FIELDS; ++f) c->f[f] = c->slab + n * f - c->g.voff();
-  c->U_alt = c->slab + n * FSGPU_NUM_FIELDS - c->g.voff();
-  c->V_alt = c->slab + n * (FSGPU_NUM_FIELDS + 1) - c->g.voff();
+  for (int f = 0; f < FSGPU_NUM_CORE_FIELDS; ++f) c->f[f] = c->slab + n * f - c->g.voff();
+  c->U_alt = c->slab + n * FSGPU_NUM_CORE_FIELDS - c->g.voff();
+  c->V_alt = c->slab + n * (FSGPU_NUM_CORE_FIELDS + 1) - c->g.voff();
   FS_CUDA(cudaMalloc(&c->ticket, sizeof(unsigned int)));
   FS_CUDA(cudaMemsetAsync(c->ticket, 0, sizeof(unsigned int), c->stream));
   FS_CUDA(cudaMalloc(&c->red_out, 16 * sizeof(double)));
@@ -180,6 +181,8 @@ int fsgpu_destroy(fsgpu_ctx* c) {
     if (c->bc[s].v_prof) cudaFree(c->bc[s].v_prof);
   }
   cudaFree(c->slab);
+  for (int f = 0; f < FSGPU_NUM_FIELDS; ++f)
+    if (c->ext_alloc[f]) cudaFree(c->ext_alloc[f]);
   cudaFree(c->part);
   cudaFree(c->ticket);
   cudaFree(c->red_out);
@@ -366,6 +369,40 @@ int fsgpu_apply_neumann_bconds(fsgpu_ctx* c, int field) {
   return fs_exchange_fields(c, &field, 1, FS_RO);
 }
 
+// ---- rows either side of the single-phase path (twophase.cu) ------------------------------------
+int fsgpu_calc_drhodt(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_drhodt(c); }
+int fsgpu_update_density(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_update_density(c, dt); }
+int fsgpu_density_step(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_density_step(c, dt, false); }
+int fsgpu_calc_pressure_jump(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_pressure_jump(c); }
+int fsgpu_capillary_divergence(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_capillary_divergence(c, dt); }
+int fsgpu_correct_velocity_ib_implicit_euler(fsgpu_ctx* c, double dt) {
+  FS_CHECK_CTX(c);
+  return fs_launch_ib_implicit_euler(c, dt);
+}
+int fsgpu_update_velocity_ib_semi_analytical(fsgpu_ctx* c, double dt) {
+  FS_CHECK_CTX(c);
+  return fs_launch_ib_semi_analytical(c, dt);
+}
+int fsgpu_interpolate_cell_centres(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_interpolate(c); }
+int fsgpu_calc_conserved_quantities(fsgpu_ctx* c, double* mass, double* momentum_x, double* momentum_y) {
+  FS_CHECK_CTX(c);
+  if (fs_launch_conserved(c)) return 1;
+  if (read_red(c, 4, 3)) return 1;
+  if (mass) *mass = c->h_red[4];
+  if (momentum_x) *momentum_x = c->h_red[5];
+  if (momentum_y) *momentum_y = c->h_red[6];
+  return 0;
+}
+int fsgpu_monitor(fsgpu_ctx* c, double* u_max, double* v_max, double* div_max) {
+  FS_CHECK_CTX(c);
+  if (fs_launch_monitor(c)) return 1;
+  if (read_red(c, 4, 3)) return 1;
+  if (u_max) *u_max = c->h_red[4];
+  if (v_max) *v_max = c->h_red[5];
+  if (div_max) *div_max = c->h_red[6];
+  return 0;
+}
+
 // ---- solver -----------------------------------------------------------------------------------
 int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out) {
   FS_CHECK_CTX(c);
@@ -450,6 +487,7 @@ int fsgpu_ps_num_distributed_levels(fsgpu_ps* s, int* n) {
 int fsgpu_substep(fsgpu_ctx* c, fsgpu_ps* s, double dt, int flags, double* residual, int* iters) {
   FS_CHECK_CTX(c);
   if (!s || s->c != c) { fs_set_error("fsgpu_substep: solver does not belong to this context"); return 1; }
+  if ((flags & FSGPU_STEP_DENSITY) && fs_launch_density_step(c, dt, true)) return 1;
   {
     ProfScope ps_(PROF_MOMENTUM, c->stream);
     if (fs_launch_momentum_update(c, dt)) return 1;  // mid-time + dmomdt + update
@@ -462,9 +500,12 @@ int fsgpu_substep(fsgpu_ctx* c, fsgpu_ps* s, double dt, int flags, double* resid
   if ((flags & FSGPU_STEP_REBUILD_OPERATOR) || !s->is_setup) {
     if (ps_setup(s)) return 1;
   }
+  if (flags & FSGPU_STEP_CAPILLARY) {  // the divergence is corrected before it becomes the rhs
+    if (fs_launch_divergence(c) || fs_launch_capillary_divergence(c, dt)) return 1;
+  }
   {
-    ProfScope ps_(PROF_RHS, c->stream);
-    if (fs_launch_rhs(c, dt, s->o.psd, true)) return 1;  // divergence + rhs (+ mean removal)
+    ProfScope ps_(PROF_RHS, c->stream);  // divergence + rhs (+ mean removal)
+    if (fs_launch_rhs(c, dt, s->o.psd, !(flags & FSGPU_STEP_CAPILLARY))) return 1;
   }
   if (ps_solve(s, residual, iters)) return 1;
   {

@@ -23,6 +23,7 @@ struct fsgpu_ctx {
   double rho_gas = 1, rho_liquid = 1, visc_gas = 1e-3, visc_liquid = 1e-3, sigma = 0;
   double* slab = nullptr;              // one allocation for all fields
   double* f[FSGPU_NUM_FIELDS] = {};    // VIRTUAL field base pointers (allocation base - g.voff())
+  double* ext_alloc[FSGPU_NUM_FIELDS] = {};  // extension fields: own allocations, made on first use
   double *U_alt = nullptr, *V_alt = nullptr;  // ping-pong targets of the fused momentum update
   BCondSide bc[4];
   // reduction scratch
@@ -37,10 +38,10 @@ struct fsgpu_ctx {
 static inline void field_extent(const Geom& g, int field, int64_t* m, int64_t* n) {
   switch (field) {
     case FSGPU_P_JUMP_U: case FSGPU_RHO_U_OLD: case FSGPU_U_OLD: case FSGPU_RHO_U: case FSGPU_U:
-    case FSGPU_DMOM_U:
+    case FSGPU_DMOM_U: case FSGPU_DRHO_U: case FSGPU_PJ_OLD_U: case FSGPU_IB_CORR_U:
       *m = g.nx + 3; *n = g.ny + 2; break;
     case FSGPU_P_JUMP_V: case FSGPU_RHO_V_OLD: case FSGPU_V_OLD: case FSGPU_RHO_V: case FSGPU_V:
-    case FSGPU_DMOM_V:
+    case FSGPU_DMOM_V: case FSGPU_DRHO_V: case FSGPU_PJ_OLD_V: case FSGPU_IB_CORR_V:
       *m = g.nx + 2; *n = g.ny + 3; break;
     default:
       *m = g.nx + 2; *n = g.ny + 2; break;
@@ -83,3 +84,16 @@ int fs_launch_fill(fsgpu_ctx* c, int field, double v);
 int fs_launch_rho_visc_vof(fsgpu_ctx* c);
 int fs_launch_neumann(fsgpu_ctx* c, double* f, int64_t m, int64_t n);
 int fs_ensure_part(fsgpu_ctx* c, size_t doubles);
+
+// ---- twophase.cu ------------------------------------------------------------
+int fs_ensure_field(fsgpu_ctx* c, int field);  // allocate an extension field on first use
+int fs_launch_drhodt(fsgpu_ctx* c);
+int fs_launch_update_density(fsgpu_ctx* c, double dt);
+int fs_launch_density_step(fsgpu_ctx* c, double dt, bool mid);
+int fs_launch_pressure_jump(fsgpu_ctx* c);
+int fs_launch_capillary_divergence(fsgpu_ctx* c, double dt);
+int fs_launch_ib_implicit_euler(fsgpu_ctx* c, double dt);
+int fs_launch_ib_semi_analytical(fsgpu_ctx* c, double dt);
+int fs_launch_interpolate(fsgpu_ctx* c);
+int fs_launch_conserved(fsgpu_ctx* c);  // -> red_out[4..6]
+int fs_launch_monitor(fsgpu_ctx* c);    // -> red_out[4..6]

@@ -19,16 +19,19 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FSGPU_LIB") or os.path.join(HERE, "libfsgpu.so")
 
 FIELDS = ("VISC", "P", "P_JUMP_U", "P_JUMP_V", "RHO_U_OLD", "RHO_V_OLD", "U_OLD", "V_OLD", "RHO_U",
-          "RHO_V", "U", "V", "DMOM_U", "DMOM_V", "DIV", "DELTA_P", "VF", "RHS")
+          "RHO_V", "U", "V", "DMOM_U", "DMOM_V", "DIV", "DELTA_P", "VF", "RHS",
+          # extension fields, device memory allocated on first use
+          "DRHO_U", "DRHO_V", "CURV", "INTERFACE_LENGTH", "PJ_OLD_U", "PJ_OLD_V", "UI", "VI", "RHOI",
+          "IB_CORR_U", "IB_CORR_V")
 FIELD_ID = {n: i for i, n in enumerate(FIELDS)}
-U_LIKE = {"P_JUMP_U", "RHO_U_OLD", "U_OLD", "RHO_U", "U", "DMOM_U"}
-V_LIKE = {"P_JUMP_V", "RHO_V_OLD", "V_OLD", "RHO_V", "V", "DMOM_V"}
+U_LIKE = {"P_JUMP_U", "RHO_U_OLD", "U_OLD", "RHO_U", "U", "DMOM_U", "DRHO_U", "PJ_OLD_U", "IB_CORR_U"}
+V_LIKE = {"P_JUMP_V", "RHO_V_OLD", "V_OLD", "RHO_V", "V", "DMOM_V", "DRHO_V", "PJ_OLD_V", "IB_CORR_V"}
 
 DIRICHLET, NEUMANN, PERIODIC, SYMMETRY = 0, 1, 2, 3
 LEFT, RIGHT, BOTTOM, TOP = 0, 1, 2, 3
 PSD_NONE, PSD_LEFT, PSD_RIGHT, PSD_BOTTOM, PSD_TOP = 0, 1, 2, 3, 4
 RELAX_JACOBI, RELAX_RBGS = 1, 2
-STEP_OUTFLOW_FIX, STEP_REBUILD_OPERATOR = 1, 2
+STEP_OUTFLOW_FIX, STEP_REBUILD_OPERATOR, STEP_DENSITY, STEP_CAPILLARY = 1, 2, 4, 8
 
 DP = C.POINTER(C.c_double)
 
@@ -47,6 +50,10 @@ SYMBOLS = (
     "fsgpu_ps_solve", "fsgpu_ps_num_levels", "fsgpu_substep", "fsgpu_step",
     "fsgpu_comm_id", "fsgpu_create_slab", "fsgpu_slab_range", "fsgpu_slab_coarse_range",
     "fsgpu_ps_num_distributed_levels",
+    "fsgpu_calc_drhodt", "fsgpu_update_density", "fsgpu_density_step", "fsgpu_calc_pressure_jump",
+    "fsgpu_capillary_divergence", "fsgpu_correct_velocity_ib_implicit_euler",
+    "fsgpu_update_velocity_ib_semi_analytical", "fsgpu_interpolate_cell_centres",
+    "fsgpu_calc_conserved_quantities", "fsgpu_monitor",
 )
 TRANSPORT_NCCL, TRANSPORT_LOCAL = 0, 1
 COMM_ID_BYTES = 128
@@ -94,10 +101,15 @@ def load():
     L.fsgpu_adjust_dt.argtypes = [vp, dbl, dbl, DP]
     for n in ("destroy", "sync", "save_old_state", "save_old_velocity", "save_old_density",
               "calc_mid_time", "calc_dmomdt", "apply_velocity_bconds", "calc_divergence",
-              "shift_pressure_to_zero", "calc_rho_visc_const", "calc_rho_visc_vof"):
+              "shift_pressure_to_zero", "calc_rho_visc_const", "calc_rho_visc_vof", "calc_drhodt",
+              "calc_pressure_jump", "interpolate_cell_centres"):
         getattr(L, "fsgpu_" + n).argtypes = [vp]
-    for n in ("update_velocity", "momentum_update", "correct_velocity"):
+    for n in ("update_velocity", "momentum_update", "correct_velocity", "update_density", "density_step",
+              "capillary_divergence", "correct_velocity_ib_implicit_euler",
+              "update_velocity_ib_semi_analytical"):
         getattr(L, "fsgpu_" + n).argtypes = [vp, dbl]
+    L.fsgpu_calc_conserved_quantities.argtypes = [vp, DP, DP, DP]
+    L.fsgpu_monitor.argtypes = [vp, DP, DP, DP]
     L.fsgpu_outflow_fix.argtypes = [vp, DP]
     L.fsgpu_abs_max.argtypes = [vp, i32, DP]
     L.fsgpu_apply_neumann_bconds.argtypes = [vp, i32]
@@ -344,6 +356,42 @@ class FS:
 
     def apply_neumann_bconds(self, name):
         _chk(self.L.fsgpu_apply_neumann_bconds(self.h, FIELD_ID[name]))
+
+    # ---- rows either side of the single-phase path ---------------------------------
+    def calc_drhodt(self):
+        _chk(self.L.fsgpu_calc_drhodt(self.h))
+
+    def update_density(self, dt):
+        _chk(self.L.fsgpu_update_density(self.h, dt))
+
+    def density_step(self, dt):
+        _chk(self.L.fsgpu_density_step(self.h, dt))
+
+    def calc_pressure_jump(self):
+        _chk(self.L.fsgpu_calc_pressure_jump(self.h))
+
+    def capillary_divergence(self, dt):
+        _chk(self.L.fsgpu_capillary_divergence(self.h, dt))
+
+    def correct_velocity_ib_implicit_euler(self, dt):
+        _chk(self.L.fsgpu_correct_velocity_ib_implicit_euler(self.h, dt))
+
+    def update_velocity_ib_semi_analytical(self, dt):
+        _chk(self.L.fsgpu_update_velocity_ib_semi_analytical(self.h, dt))
+
+    def interpolate_cell_centres(self):
+        _chk(self.L.fsgpu_interpolate_cell_centres(self.h))
+
+    def calc_conserved_quantities(self):
+        m, mx, my = C.c_double(), C.c_double(), C.c_double()
+        _chk(self.L.fsgpu_calc_conserved_quantities(self.h, C.byref(m), C.byref(mx), C.byref(my)))
+        return m.value, mx.value, my.value
+
+    def monitor(self):
+        """-> (max|U|, max|V|, max|div|); div is stored in field DIV"""
+        a, b, d = C.c_double(), C.c_double(), C.c_double()
+        _chk(self.L.fsgpu_monitor(self.h, C.byref(a), C.byref(b), C.byref(d)))
+        return a.value, b.value, d.value
 
     # ---- fused path ---------------------------------------------------------------------------
     def substep(self, ps, dt, flags=0):

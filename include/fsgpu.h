@@ -53,8 +53,21 @@ enum {
   FSGPU_VF,            /* volume fraction    cell   */
   FSGPU_RHS,           /* pressure rhs, (NX+2)x(NY+2) in Layout::C (the reference keeps it in
                           Layout::F, src/LinearSystem.hpp:18-24; transpose to compare) */
+  /* ---- extension fields: device memory is allocated on first use ---- */
+  FSGPU_DRHO_U,        /* drho_u_stagdt      U-like  test/StationaryDrop.cpp:107 */
+  FSGPU_DRHO_V,        /* drho_v_stagdt      V-like */
+  FSGPU_CURV,          /* vof.curv           cell    src/VOF.hpp (input of calc_pressure_jump) */
+  FSGPU_INTERFACE_LENGTH, /* vof.interface_length cell */
+  FSGPU_PJ_OLD_U,      /* previous p_jump_u_stag (the drivers' delta_pj_u_stag scratch) U-like */
+  FSGPU_PJ_OLD_V,      /* previous p_jump_v_stag V-like */
+  FSGPU_UI,            /* Ui   cell-centred U     cell   src/Operators.hpp:10-13 */
+  FSGPU_VI,            /* Vi   cell-centred V     cell   src/Operators.hpp:16-19 */
+  FSGPU_RHOI,          /* rhoi cell-centred rho   cell   src/Operators.hpp:22-29 */
+  FSGPU_IB_CORR_U,     /* ib_corr_u_stag     U-like  src/IB.hpp:62-107 (input) */
+  FSGPU_IB_CORR_V,     /* ib_corr_v_stag     V-like */
   FSGPU_NUM_FIELDS
 };
+#define FSGPU_NUM_CORE_FIELDS (FSGPU_RHS + 1)
 
 /* src/BoundaryConditions.hpp:14-200 */
 enum { FSGPU_BC_DIRICHLET = 0, FSGPU_BC_NEUMANN = 1, FSGPU_BC_PERIODIC = 2, FSGPU_BC_SYMMETRY = 3 };
@@ -168,6 +181,35 @@ int fsgpu_calc_rho_visc_vof(fsgpu_ctx* c);
 /* apply_neumann_bconds(field), src/BoundaryConditions.hpp:227-252 */
 int fsgpu_apply_neumann_bconds(fsgpu_ctx* c, int field);
 
+/* ---- rows either side of the single-phase path ---------------------------------- */
+/* calc_drhodt(fs, drho_u_stagdt, drho_v_stagdt), src/FS.hpp:318-406 -> FSGPU_DRHO_U / FSGPU_DRHO_V */
+int fsgpu_calc_drhodt(fsgpu_ctx* c);
+/* update_density(drho_u_stagdt, drho_v_stagdt, dt, fs), src/FS.hpp:409-420 */
+int fsgpu_update_density(fsgpu_ctx* c, double dt);
+/* the density block of the two-phase drivers in one pass (test/StationaryDrop.cpp:274-293):
+ * calc_drhodt + update_density + apply_neumann_bconds(curr.rho_u_stag / rho_v_stag) */
+int fsgpu_density_step(fsgpu_ctx* c, double dt);
+/* calc_pressure_jump(vf, curv, interface_length, fs), src/FS.hpp:439-466; reads FSGPU_VF,
+ * FSGPU_CURV, FSGPU_INTERFACE_LENGTH and fs.sigma, writes FSGPU_P_JUMP_U / _V (ghosts 0) */
+int fsgpu_calc_pressure_jump(fsgpu_ctx* c);
+/* the capillary block of the two-phase drivers (test/StationaryDrop.cpp:331-353): keep the old
+ * jump (FSGPU_PJ_OLD_*), calc_pressure_jump, apply_neumann_bconds on both jumps, and
+ * div += dt * div((pj - pj_old) / rho) on all cells of FSGPU_DIV */
+int fsgpu_capillary_divergence(fsgpu_ctx* c, double dt);
+/* correct_velocity_ib_implicit_euler(ib_corr_u, ib_corr_v, dt, fs), src/IB.hpp:110-126 */
+int fsgpu_correct_velocity_ib_implicit_euler(fsgpu_ctx* c, double dt);
+/* update_velocity_ib_semi_analytical(drhoUdt, drhoVdt, dt, ib_corr_u, ib_corr_v, fs),
+ * src/IB.hpp:129-186; reads FSGPU_DMOM_U / _V and FSGPU_IB_CORR_U / _V */
+int fsgpu_update_velocity_ib_semi_analytical(fsgpu_ctx* c, double dt);
+/* interpolate_U, interpolate_V, interpolate_UV_staggered_field(rho_u, rho_v), src/Operators.hpp:10-29
+ * -> FSGPU_UI, FSGPU_VI, FSGPU_RHOI (all cells incl. ghosts), one pass */
+int fsgpu_interpolate_cell_centres(fsgpu_ctx* c);
+/* calc_conserved_quantities(fs, mass, momentum_x, momentum_y), src/FS.hpp:653-676 */
+int fsgpu_calc_conserved_quantities(fsgpu_ctx* c, double* mass, double* momentum_x, double* momentum_y);
+/* the monitor row of every driver (scaling/LidDrivenFlow.cpp:166-170) in one pass:
+ * calc_divergence -> FSGPU_DIV, then abs_max(curr.U), abs_max(curr.V), abs_max(div) */
+int fsgpu_monitor(fsgpu_ctx* c, double* u_max, double* v_max, double* div_max);
+
 /* ---- pressure solver = `LinearSolver_StructHypre<Float,NX,NY,1>` -------------------------------
  * constructor (src/LinearSolver_StructHypre.hpp:43-62): tol, max_iter, PSDirichlet.  The solver
  * is always PCG preconditioned by one PFMG-style V-cycle (the reference's default
@@ -202,8 +244,13 @@ int fsgpu_ps_num_distributed_levels(fsgpu_ps* s, int* n);
  * (scaling/LidDrivenFlow.cpp:127-161) and one whole timestep (:121-163) ----------------------- */
 enum {
   FSGPU_STEP_OUTFLOW_FIX = 1,       /* test/LaminarChannel.cpp:201-205 */
-  FSGPU_STEP_REBUILD_OPERATOR = 2   /* set_pressure_operator every sub-iteration (two-phase
+  FSGPU_STEP_REBUILD_OPERATOR = 2,  /* set_pressure_operator every sub-iteration (two-phase
                                        drivers, test/StationaryDrop.cpp:357) */
+  FSGPU_STEP_DENSITY = 4,           /* consistent mass transport before the momentum update
+                                       (test/StationaryDrop.cpp:274-293) */
+  FSGPU_STEP_CAPILLARY = 8          /* capillary block after the divergence
+                                       (test/StationaryDrop.cpp:331-353); FSGPU_VF, FSGPU_CURV and
+                                       FSGPU_INTERFACE_LENGTH are inputs, frozen during the step */
 };
 int fsgpu_substep(fsgpu_ctx* c, fsgpu_ps* s, double dt, int flags, double* residual, int* iters);
 /* save_old_state + num_subiter sub-iterations; *iters = total PCG iterations of the step */

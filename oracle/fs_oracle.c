@@ -599,6 +599,72 @@ void fso_update_density(fso_fs* fs, const double* drho_u, const double* drho_v, 
       fs->rho_v[IV(i, j)] = fs->rho_v_old[IV(i, j)] + dt * drho_v[IV(i, j)];
 }
 
+/* src/IB.hpp:110-126 */
+void fso_correct_velocity_ib_implicit_euler(fso_fs* fs, const double* ib_u, const double* ib_v, double dt) {
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j) {
+      const double visc = (fs->visc[IC(i, j)] + fs->visc[IC(i - 1, j)]) / 2.0;
+      const double rho  = fs->rho_u[IU(i, j)];
+      fs->U[IU(i, j)] /= 1.0 + dt * visc / rho * ib_u[IU(i, j)];
+    }
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j) {
+      const double visc = (fs->visc[IC(i, j)] + fs->visc[IC(i, j - 1)]) / 2.0;
+      const double rho  = fs->rho_v[IV(i, j)];
+      fs->V[IV(i, j)] /= 1.0 + dt * visc / rho * ib_v[IV(i, j)];
+    }
+}
+
+/* src/IB.hpp:129-186: U = (B rho_old U_old + dt F) / (A rho), B = l dt / (exp(l dt) - 1), A = l dt + B */
+static inline double ib_semi(double lambda, double dt, double ro, double uo, double f, double r) {
+  if (isinf(lambda)) return 0.0;
+  const double B = fabs(lambda) < 1e-6 ? 1.0 : (lambda * dt) / (exp(lambda * dt) - 1.0);
+  const double A = lambda * dt + B;
+  return (B * ro * uo + dt * f) / (A * r);
+}
+void fso_update_velocity_ib_semi_analytical(fso_fs* fs, const double* dmomU, const double* dmomV,
+                                            double dt, const double* ib_u, const double* ib_v) {
+  for (int64_t i = 0; i < NX + 1; ++i)
+    for (int64_t j = 0; j < NY; ++j) {
+      const double visc = (fs->visc[IC(i, j)] + fs->visc[IC(i - 1, j)]) / 2.0;
+      const double rho  = fs->rho_u[IU(i, j)];
+      fs->U[IU(i, j)] = ib_semi(visc / rho * ib_u[IU(i, j)], dt, fs->rho_u_old[IU(i, j)],
+                                fs->U_old[IU(i, j)], dmomU[IU(i, j)], rho);
+    }
+  for (int64_t i = 0; i < NX; ++i)
+    for (int64_t j = 0; j < NY + 1; ++j) {
+      const double visc = (fs->visc[IC(i, j)] + fs->visc[IC(i, j - 1)]) / 2.0;
+      const double rho  = fs->rho_v[IV(i, j)];
+      fs->V[IV(i, j)] = ib_semi(visc / rho * ib_v[IV(i, j)], dt, fs->rho_v_old[IV(i, j)],
+                                fs->V_old[IV(i, j)], dmomV[IV(i, j)], rho);
+    }
+}
+
+/* test/StationaryDrop.cpp:331-353 */
+void fso_capillary_divergence(fso_fs* fs, const double* vf, const double* curv, const double* ilen,
+                              double dt, double* div) {
+  const size_t nu = (size_t)((NX + 3) * (NY + 2)), nv = (size_t)((NX + 2) * (NY + 3));
+  double* du = malloc(sizeof(double) * nu);
+  double* dv = malloc(sizeof(double) * nv);
+  memcpy(du, fs->p_jump_u, sizeof(double) * nu); /* :332-333 copy(fs.p_jump_*, delta_pj_*) */
+  memcpy(dv, fs->p_jump_v, sizeof(double) * nv);
+  fso_calc_pressure_jump(fs, vf, curv, ilen);
+  fso_apply_neumann_bconds(fs->p_jump_u, NX + 1, NY);
+  fso_apply_neumann_bconds(fs->p_jump_v, NX, NY + 1);
+  for (size_t k = 0; k < nu; ++k) du[k] = fs->p_jump_u[k] - du[k];
+  for (size_t k = 0; k < nv; ++k) dv[k] = fs->p_jump_v[k] - dv[k];
+  for (int64_t i = -1; i < NX + 1; ++i)
+    for (int64_t j = -1; j < NY + 1; ++j)
+      div[IC(i, j)] += dt * ((du[IU(i + 1, j)] / fs->rho_u[IU(i + 1, j)] -
+                              du[IU(i, j)] / fs->rho_u[IU(i, j)]) /
+                                 fs->dx +
+                             (dv[IV(i, j + 1)] / fs->rho_v[IV(i, j + 1)] -
+                              dv[IV(i, j)] / fs->rho_v[IV(i, j)]) /
+                                 fs->dy);
+  free(du);
+  free(dv);
+}
+
 /* One timestep's sub-iteration loop, scaling/LidDrivenFlow.cpp:127-161
  * (+ test/LaminarChannel.cpp:201-205 outflow fix, + operator rebuild of two-phase drivers). */
 int fso_step(fso_fs* fs, const fso_bconds* bc, fso_solver* s, const fso_step_opts* o, double dt,
@@ -615,11 +681,18 @@ int fso_step(fso_fs* fs, const fso_bconds* bc, fso_solver* s, const fso_step_opt
   for (int sub = 0; sub < o->num_subiter; ++sub) {
     fso_calc_mid_time(fs->U, fs->U_old, nu);
     fso_calc_mid_time(fs->V, fs->V_old, nv);
+    if (o->density_update) { /* test/StationaryDrop.cpp:274-293; dmomU/V double as drho scratch */
+      fso_calc_drhodt(fs, dmomU, dmomV);
+      fso_update_density(fs, dmomU, dmomV, dt);
+      fso_apply_neumann_bconds(fs->rho_u, NX + 1, NY);
+      fso_apply_neumann_bconds(fs->rho_v, NX, NY + 1);
+    }
     fso_calc_dmomdt(fs, dmomU, dmomV);
     fso_update_velocity(fs, dmomU, dmomV, dt);
     fso_apply_velocity_bconds(fs, bc);
     if (o->outflow_fix) fso_outflow_fix(fs);
     fso_calc_divergence(fs, div);
+    if (o->capillary) fso_capillary_divergence(fs, o->vf, o->curv, o->ilen, dt, div);
     if (op) {
       fso_fill_pressure_operator(fs, o->psd, op);
       fso_solver_set_operator(s, op);

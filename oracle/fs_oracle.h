@@ -86,6 +86,15 @@ void fso_update_density(fso_fs* fs, const double* drho_u, const double* drho_v, 
 /* src/Operators.hpp:10-19, src/FS.hpp:653-676 */
 void fso_interpolate_UV(const fso_fs* fs, double* Ui, double* Vi);
 void fso_conserved(const fso_fs* fs, double* mass, double* mom_x, double* mom_y);
+/* src/IB.hpp:110-126 and :129-186 (immersed-boundary variants of the velocity update) */
+void fso_correct_velocity_ib_implicit_euler(fso_fs* fs, const double* ib_u, const double* ib_v, double dt);
+void fso_update_velocity_ib_semi_analytical(fso_fs* fs, const double* dmomU, const double* dmomV,
+                                            double dt, const double* ib_u, const double* ib_v);
+/* the capillary block of the two-phase drivers, test/StationaryDrop.cpp:331-353: keeps the old
+ * pressure jump, recomputes it (calc_pressure_jump + apply_neumann_bconds), and adds
+ * dt * div(delta_pj / rho) to div on all cells */
+void fso_capillary_divergence(fso_fs* fs, const double* vf, const double* curv, const double* ilen,
+                              double dt, double* div);
 
 /* ---- pressure solver: restatement of HYPRE 3.0.0 Struct PCG + PFMG as configured by
  * src/LinearSolver_StructHypre.hpp:196-290 (see oracle/pfmg_oracle.c) ------------------------ */
@@ -111,6 +120,9 @@ typedef struct {
   int outflow_fix;   /* test/LaminarChannel.cpp:201-205 */
   int psd;
   int rebuild_operator_each_subiter; /* two-phase drivers, test/StationaryDrop.cpp:357 */
+  int density_update; /* consistent mass transport, test/StationaryDrop.cpp:274-293 */
+  int capillary;      /* pressure-jump block, test/StationaryDrop.cpp:331-353 (needs vf, curv, ilen) */
+  const double *vf, *curv, *ilen; /* cell fields (NX+2)x(NY+2); frozen during the step */
 } fso_step_opts;
 /* returns total PCG iterations of the step; *res = last residual */
 int fso_step(fso_fs* fs, const fso_bconds* bc, fso_solver* s, const fso_step_opts* o, double dt,

@@ -17,6 +17,7 @@
 #include <omp.h>
 
 #include "FS.hpp"
+#include "IB.hpp"
 #include "LinearSolver_StructHypre.hpp"
 #include "Operators.hpp"
 #include "Utility.hpp"
@@ -49,6 +50,13 @@ struct SessionBase {
   virtual int solver_solve(const double* div, double dt, double* dp, double* res) = 0;
   virtual int step(const fso_step_opts* o, double dt, double* res, double* phase_secs) = 0;
   virtual void diagnostics(double* umax, double* vmax, double* divmax)         = 0;
+  virtual void update_density(const double* dru, const double* drv, double dt) = 0;
+  virtual void pressure_jump(const double* vf, const double* curv, const double* ilen) = 0;
+  virtual void interpolate_uv(double* ui, double* vi)                          = 0;
+  virtual void conserved(double* mass, double* mx, double* my)                 = 0;
+  virtual void ib_implicit_euler(const double* ibu, const double* ibv, double dt) = 0;
+  virtual void ib_semi_analytical(const double* dU, const double* dV, double dt, const double* ibu,
+                                  const double* ibv)                           = 0;
 };
 
 template <Index NX, Index NY>
@@ -149,6 +157,48 @@ struct Session final : SessionBase {
     ::calc_rho(*f, fs);
     ::calc_visc(*f, fs);
   }
+  void update_density(const double* iU, const double* iV, double dt) override {
+    cp_in(dU, iU); cp_in(dV, iV);
+    ::update_density(dU, dV, dt, fs);
+  }
+  // cell-field scratch for the two-phase inputs (vf, curv, interface_length)
+  std::unique_ptr<Field2D<Float, NX, NY, G>> c_vf{}, c_curv{}, c_ilen{};
+  void load_cells(const double* vf, const double* curv, const double* ilen) {
+    if (!c_vf) {
+      c_vf   = std::make_unique<Field2D<Float, NX, NY, G>>();
+      c_curv = std::make_unique<Field2D<Float, NX, NY, G>>();
+      c_ilen = std::make_unique<Field2D<Float, NX, NY, G>>();
+    }
+    cp_in(*c_vf, vf); cp_in(*c_curv, curv); cp_in(*c_ilen, ilen);
+  }
+  void pressure_jump(const double* vf, const double* curv, const double* ilen) override {
+    load_cells(vf, curv, ilen);
+    ::calc_pressure_jump(*c_vf, *c_curv, *c_ilen, fs);
+  }
+  void interpolate_uv(double* ui, double* vi) override {
+    auto a = std::make_unique<Field2D<Float, NX, NY, G>>();
+    ::interpolate_U(fs.curr.U, *a);
+    cp_out(*a, ui);
+    ::interpolate_V(fs.curr.V, *a);
+    cp_out(*a, vi);
+  }
+  void conserved(double* mass, double* mx, double* my) override {
+    ::calc_conserved_quantities(fs, *mass, *mx, *my);
+  }
+  void ib_implicit_euler(const double* ibu, const double* ibv, double dt) override {
+    auto a = std::make_unique<Field2D<Float, NX + 1, NY, G>>();
+    auto b = std::make_unique<Field2D<Float, NX, NY + 1, G>>();
+    cp_in(*a, ibu); cp_in(*b, ibv);
+    ::correct_velocity_ib_implicit_euler(*a, *b, dt, fs);
+  }
+  void ib_semi_analytical(const double* iU, const double* iV, double dt, const double* ibu,
+                          const double* ibv) override {
+    auto a = std::make_unique<Field2D<Float, NX + 1, NY, G>>();
+    auto b = std::make_unique<Field2D<Float, NX, NY + 1, G>>();
+    cp_in(*a, ibu); cp_in(*b, ibv);
+    cp_in(dU, iU); cp_in(dV, iV);
+    ::update_velocity_ib_semi_analytical(dU, dV, dt, *a, *b, fs);
+  }
   void solver_create(double tol, int max_iter, int psd) override {
     psd_ = psd;
     ps.reset();
@@ -181,6 +231,12 @@ struct Session final : SessionBase {
       auto t0 = clk::now();
       ::calc_mid_time(fs.curr.U, fs.old.U);
       ::calc_mid_time(fs.curr.V, fs.old.V);
+      if (o->density_update) {  // the calls of test/StationaryDrop.cpp:274-293
+        ::calc_drhodt(fs, dU, dV);
+        ::update_density(dU, dV, dt, fs);
+        ::apply_neumann_bconds(fs.curr.rho_u_stag);
+        ::apply_neumann_bconds(fs.curr.rho_v_stag);
+      }
       ::calc_dmomdt(fs, dU, dV);
       for_each_i<Exec::Parallel>(fs.curr.U, [&](Index i, Index j) {
         fs.curr.U(i, j) =
@@ -205,6 +261,24 @@ struct Session final : SessionBase {
       }
       auto t1 = clk::now();
       ::calc_divergence(fs.curr.U, fs.curr.V, fs.dx, fs.dy, div);
+      if (o->capillary) {  // the calls of test/StationaryDrop.cpp:331-353 (curvature is an input)
+        load_cells(o->vf, o->curv, o->ilen);
+        copy(fs.p_jump_u_stag, dU);
+        copy(fs.p_jump_v_stag, dV);
+        ::calc_pressure_jump(*c_vf, *c_curv, *c_ilen, fs);
+        ::apply_neumann_bconds(fs.p_jump_u_stag);
+        ::apply_neumann_bconds(fs.p_jump_v_stag);
+        for_each_a<Exec::Parallel>(dU, [&](Index i, Index j) { dU(i, j) = fs.p_jump_u_stag(i, j) - dU(i, j); });
+        for_each_a<Exec::Parallel>(dV, [&](Index i, Index j) { dV(i, j) = fs.p_jump_v_stag(i, j) - dV(i, j); });
+        for_each_a<Exec::Parallel>(div, [&](Index i, Index j) {
+          div(i, j) += dt * ((dU(i + 1, j) / fs.curr.rho_u_stag(i + 1, j) -
+                              dU(i, j) / fs.curr.rho_u_stag(i, j)) /
+                                 fs.dx +
+                             (dV(i, j + 1) / fs.curr.rho_v_stag(i, j + 1) -
+                              dV(i, j) / fs.curr.rho_v_stag(i, j)) /
+                                 fs.dy);
+        });
+      }
       if (o->rebuild_operator_each_subiter) ps->set_pressure_operator(fs);
       ps->set_pressure_rhs(fs, div, dt);
       auto t2 = clk::now();
@@ -291,6 +365,21 @@ int fsref_step(void* s, const fso_step_opts* o, double dt, double* res, double* 
 }
 void fsref_diagnostics(void* s, double* umax, double* vmax, double* divmax) {
   S->diagnostics(umax, vmax, divmax);
+}
+void fsref_update_density(void* s, const double* dru, const double* drv, double dt) {
+  S->update_density(dru, drv, dt);
+}
+void fsref_calc_pressure_jump(void* s, const double* vf, const double* curv, const double* ilen) {
+  S->pressure_jump(vf, curv, ilen);
+}
+void fsref_interpolate_uv(void* s, double* ui, double* vi) { S->interpolate_uv(ui, vi); }
+void fsref_conserved(void* s, double* mass, double* mx, double* my) { S->conserved(mass, mx, my); }
+void fsref_ib_implicit_euler(void* s, const double* ibu, const double* ibv, double dt) {
+  S->ib_implicit_euler(ibu, ibv, dt);
+}
+void fsref_ib_semi_analytical(void* s, const double* dU, const double* dV, double dt,
+                              const double* ibu, const double* ibv) {
+  S->ib_semi_analytical(dU, dV, dt, ibu, ibv);
 }
 #undef S
 }

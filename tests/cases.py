@@ -82,6 +82,38 @@ def tgv_state(oracle, n=128):
     return st
 
 
+def twophase_inputs(st, seed=0, random_vf=False):
+    """vf, curv, interface_length (cell fields) for calc_pressure_jump (src/FS.hpp:439-466): curvature
+    scattered around 1/R = 4 and a positive interface length in mixed cells only (plus, for the
+    random variant, isolated zero-length cells next to non-zero ones so both branches of the
+    length-weighted average are taken)."""
+    rng = np.random.default_rng(seed)
+    shape = (st.nx + 2, st.ny + 2)
+    if random_vf:
+        vf = rng.uniform(0, 1, shape)
+        ilen = np.where(rng.uniform(size=shape) < 0.5, 0.0, rng.uniform(0.1, 1.0, shape) * st.dx)
+    else:
+        vf = getattr(st, "vf", None)
+        if vf is None:
+            vf = ellipse_vf(st.nx, st.ny, st.dx, st.dy)
+        ilen = np.where((vf > 1e-8) & (vf < 1 - 1e-8), rng.uniform(0.5, 1.4, shape) * st.dx, 0.0)
+    curv = 4.0 * (1 + 0.05 * rng.uniform(-1, 1, shape))
+    return np.ascontiguousarray(vf), curv, ilen
+
+
+def ib_inputs(st, seed=0):
+    """ib_corr_u_stag / ib_corr_v_stag (src/IB.hpp:62-107 computes lambda = (d - dist)/(dist d^2) near
+    the wall): zero in the free flow, ~1/d^2 near the wall, inf inside the solid"""
+    rng = np.random.default_rng(seed)
+    out = []
+    for n, d in (("U", st.dx), ("V", st.dy)):
+        sh = st.a[n].shape
+        r = rng.uniform(size=sh)
+        lam = rng.uniform(0.1, 3.0, sh) / (d * d)
+        out.append(np.where(r < 0.5, 0.0, np.where(r < 0.9, lam, np.inf)))
+    return out
+
+
 def to_gpu(F, st, bc=None, device=0):
     """oracle_lib.State -> fluidsolver_b200.FS (upload every field)."""
     fs = F.FS(st.nx, st.ny, st.dx, st.dy, st.rho_gas, st.rho_liquid, st.visc_gas, st.visc_liquid,

@@ -1,0 +1,86 @@
+"""Golden vectors for the rows either side of the single-phase path, from the
+UNMODIFIED reference (oracle/_ref/libfsref.so):   python tests/golden/make_golden_8f.py
+
+ops8f_<case>.npz : update_density, calc_pressure_jump, interpolate_U/V, calc_conserved_quantities,
+                   correct_velocity_ib_implicit_euler, update_velocity_ib_semi_analytical
+run_twophase128.npz : two timesteps of the two-phase sub-iteration (density update + capillary block
+                   + operator rebuild, test/StationaryDrop.cpp:270-384) on the frozen-VOF drop
+Inputs are the seeded states of tests/cases.py, re-created by the tests.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+
+from cases import cavity_bc, cavity_state, ib_inputs, random_state, twophase_inputs  # noqa: E402
+from oracle_lib import Oracle, Ref  # noqa: E402
+
+o = Oracle()  # input construction only
+
+
+def ops8f(name, st, random_vf, dt=1e-2):
+    r = Ref(st.nx, st.ny)
+    out = {}
+    s2 = st.copy()
+    r.load(st)
+    dru, drv = r.calc_drhodt()
+    r.update_density(dru, drv, dt)
+    r.store(s2)
+    out["rho_u"], out["rho_v"] = s2.rho_u.copy(), s2.rho_v.copy()
+    r.load(st)
+    vf, curv, ilen = twophase_inputs(st, seed=7, random_vf=random_vf)
+    r.calc_pressure_jump(vf, curv, ilen)
+    r.store(s2)
+    out["pj_u"], out["pj_v"] = s2.p_jump_u.copy(), s2.p_jump_v.copy()
+    r.load(st)
+    out["Ui"], out["Vi"] = r.interpolate_UV()
+    out["conserved"] = np.array(r.conserved())
+    ibu, ibv = ib_inputs(st, seed=11)
+    r.ib_implicit_euler(ibu, ibv, dt)
+    r.store(s2)
+    out["ibe_U"], out["ibe_V"] = s2.U.copy(), s2.V.copy()
+    r.load(st)
+    dU, dV = r.calc_dmomdt()
+    r.ib_semi_analytical(dU, dV, dt, ibu, ibv)
+    r.store(s2)
+    out["ibs_U"], out["ibs_V"] = s2.U.copy(), s2.V.copy()
+    np.savez_compressed(os.path.join(HERE, f"ops8f_{name}.npz"), **out)
+    print("ops8f", name, {k: v.shape for k, v in out.items()})
+
+
+def twophase_state(n=128):
+    st = cavity_state(o, n, n, drop=True, seed=1)
+    st.sigma = 0.05
+    return st
+
+
+def run_twophase(name, nsub=3, nsteps=2):
+    st, bc = twophase_state(), cavity_bc()
+    cap = twophase_inputs(st, seed=7)
+    o.apply_velocity_bconds(st, bc)
+    r = Ref(st.nx, st.ny)
+    r.load(st)
+    r.set_bconds(bc)
+    r.solver_create(1e-13, 500)
+    r.solver_set_operator()
+    dts, its = [], []
+    for _ in range(nsteps):
+        dt = r.adjust_dt(0.9, 0.1)
+        it, res = r.step(dt, nsub, rebuild=1, density=1, capillary=cap)
+        dts.append(dt)
+        its.append(it)
+    s2 = st.copy()
+    r.store(s2)
+    out = {"dts": np.array(dts), "its": np.array(its), "U": s2.U, "V": s2.V, "p": s2.a["p"],
+           "rho_u": s2.rho_u, "rho_v": s2.rho_v, "pj_u": s2.p_jump_u, "pj_v": s2.p_jump_v}
+    np.savez_compressed(os.path.join(HERE, f"run_{name}.npz"), **out)
+    print("run", name, "its", its, "dt", dts, "max|U|", np.abs(s2.U).max())
+
+
+if __name__ == "__main__":
+    ops8f("random48x20", random_state(48, 20, seed=48020), True)
+    ops8f("drop64", cavity_state(o, 64, 64, drop=True, seed=3), False)
+    run_twophase("twophase128")

@@ -47,7 +47,16 @@ class CSolverOpts(C.Structure):
 
 class CStepOpts(C.Structure):
     _fields_ = [("num_subiter", C.c_int), ("outflow_fix", C.c_int), ("psd", C.c_int),
-                ("rebuild_operator_each_subiter", C.c_int)]
+                ("rebuild_operator_each_subiter", C.c_int), ("density_update", C.c_int),
+                ("capillary", C.c_int), ("vf", DP), ("curv", DP), ("ilen", DP)]
+
+
+def _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary):
+    o = CStepOpts(num_subiter, outflow_fix, psd, rebuild, int(density), int(capillary is not None))
+    if capillary is not None:
+        o._keep = [np.ascontiguousarray(a, dtype=np.float64) for a in capillary]
+        o.vf, o.curv, o.ilen = (a.ctypes.data_as(DP) for a in o._keep)
+    return o
 
 
 FIELDS_U = ("p_jump_u", "rho_u_old", "U_old", "rho_u", "U")
@@ -151,6 +160,12 @@ class Oracle:
         L.fso_fill_pressure_rhs.argtypes = [C.POINTER(CFs), DP, C.c_double, C.c_int, DP]
         L.fso_correct.argtypes = [C.POINTER(CFs), DP, C.c_double]
         L.fso_apply_neumann_bconds.argtypes = [DP, C.c_int64, C.c_int64]
+        L.fso_calc_pressure_jump.argtypes = [C.POINTER(CFs), DP, DP, DP]
+        L.fso_interpolate_UV.argtypes = [C.POINTER(CFs), DP, DP]
+        L.fso_conserved.argtypes = [C.POINTER(CFs), DP, DP, DP]
+        L.fso_correct_velocity_ib_implicit_euler.argtypes = [C.POINTER(CFs), DP, DP, C.c_double]
+        L.fso_update_velocity_ib_semi_analytical.argtypes = [C.POINTER(CFs), DP, DP, C.c_double, DP, DP]
+        L.fso_capillary_divergence.argtypes = [C.POINTER(CFs), DP, DP, DP, C.c_double, DP]
         L.fso_solver_create.restype = C.c_void_p
         L.fso_solver_create.argtypes = [C.c_int64, C.c_int64, C.POINTER(CSolverOpts)]
         L.fso_solver_destroy.argtypes = [C.c_void_p]
@@ -187,6 +202,32 @@ class Oracle:
 
     def update_velocity(self, st, dU, dV, dt):
         self.lib.fso_update_velocity(C.byref(st.cstruct()), _ptr(dU), _ptr(dV), dt)
+
+    def update_density(self, st, dru, drv, dt):
+        self.lib.fso_update_density(C.byref(st.cstruct()), _ptr(dru), _ptr(drv), dt)
+
+    def calc_pressure_jump(self, st, vf, curv, ilen):
+        self.lib.fso_calc_pressure_jump(C.byref(st.cstruct()), _ptr(vf), _ptr(curv), _ptr(ilen))
+
+    def capillary_divergence(self, st, vf, curv, ilen, dt, div):
+        self.lib.fso_capillary_divergence(C.byref(st.cstruct()), _ptr(vf), _ptr(curv), _ptr(ilen), dt, _ptr(div))
+
+    def interpolate_UV(self, st):
+        ui, vi = np.zeros((st.nx + 2, st.ny + 2)), np.zeros((st.nx + 2, st.ny + 2))
+        self.lib.fso_interpolate_UV(C.byref(st.cstruct()), _ptr(ui), _ptr(vi))
+        return ui, vi
+
+    def conserved(self, st):
+        a, b, c = C.c_double(0), C.c_double(0), C.c_double(0)
+        self.lib.fso_conserved(C.byref(st.cstruct()), C.byref(a), C.byref(b), C.byref(c))
+        return a.value, b.value, c.value
+
+    def ib_implicit_euler(self, st, ibu, ibv, dt):
+        self.lib.fso_correct_velocity_ib_implicit_euler(C.byref(st.cstruct()), _ptr(ibu), _ptr(ibv), dt)
+
+    def ib_semi_analytical(self, st, dU, dV, dt, ibu, ibv):
+        self.lib.fso_update_velocity_ib_semi_analytical(C.byref(st.cstruct()), _ptr(dU), _ptr(dV), dt,
+                                                        _ptr(ibu), _ptr(ibv))
 
     def apply_velocity_bconds(self, st, bc):
         self.lib.fso_apply_velocity_bconds(C.byref(st.cstruct()), C.byref(bc.cstruct()))
@@ -230,9 +271,11 @@ class Oracle:
     def solver(self, nx, ny, tol=1e-6, max_iter=50, max_levels=16, relax_type=1, skip_relax=1):
         return OracleSolver(self, nx, ny, CSolverOpts(tol, max_iter, max_levels, relax_type, skip_relax))
 
-    def step(self, st, bc, solver, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0):
+    def step(self, st, bc, solver, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0, density=0,
+             capillary=None):
+        """capillary = (vf, curv, interface_length) cell arrays, or None"""
         res = C.c_double(0)
-        o = CStepOpts(num_subiter, outflow_fix, psd, rebuild)
+        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary)
         it = self.lib.fso_step(C.byref(st.cstruct()), C.byref(bc.cstruct()), solver.h, C.byref(o), dt,
                                C.byref(res))
         return it, res.value
@@ -313,6 +356,12 @@ class Ref:
             L.fsref_step.restype = C.c_int
             L.fsref_step.argtypes = [C.c_void_p, C.POINTER(CStepOpts), C.c_double, DP, DP]
             L.fsref_diagnostics.argtypes = [C.c_void_p, DP, DP, DP]
+            L.fsref_update_density.argtypes = [C.c_void_p, DP, DP, C.c_double]
+            L.fsref_calc_pressure_jump.argtypes = [C.c_void_p, DP, DP, DP]
+            L.fsref_interpolate_uv.argtypes = [C.c_void_p, DP, DP]
+            L.fsref_conserved.argtypes = [C.c_void_p, DP, DP, DP]
+            L.fsref_ib_implicit_euler.argtypes = [C.c_void_p, DP, DP, C.c_double]
+            L.fsref_ib_semi_analytical.argtypes = [C.c_void_p, DP, DP, C.c_double, DP, DP]
             L.fsref_set_threads.argtypes = [C.c_int]
             cls._lib = L
         return cls._lib
@@ -399,9 +448,32 @@ class Ref:
         it = self.lib().fsref_solver_solve(self.h, _ptr(div), dt, _ptr(dp), C.byref(res))
         return dp, res.value, it
 
-    def step(self, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0, phases=None):
+    def update_density(self, dru, drv, dt):
+        self.lib().fsref_update_density(self.h, _ptr(dru), _ptr(drv), dt)
+
+    def calc_pressure_jump(self, vf, curv, ilen):
+        self.lib().fsref_calc_pressure_jump(self.h, _ptr(vf), _ptr(curv), _ptr(ilen))
+
+    def interpolate_UV(self):
+        ui, vi = np.zeros((self.nx + 2, self.ny + 2)), np.zeros((self.nx + 2, self.ny + 2))
+        self.lib().fsref_interpolate_uv(self.h, _ptr(ui), _ptr(vi))
+        return ui, vi
+
+    def conserved(self):
+        a, b, c = C.c_double(0), C.c_double(0), C.c_double(0)
+        self.lib().fsref_conserved(self.h, C.byref(a), C.byref(b), C.byref(c))
+        return a.value, b.value, c.value
+
+    def ib_implicit_euler(self, ibu, ibv, dt):
+        self.lib().fsref_ib_implicit_euler(self.h, _ptr(ibu), _ptr(ibv), dt)
+
+    def ib_semi_analytical(self, dU, dV, dt, ibu, ibv):
+        self.lib().fsref_ib_semi_analytical(self.h, _ptr(dU), _ptr(dV), dt, _ptr(ibu), _ptr(ibv))
+
+    def step(self, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0, phases=None, density=0,
+             capillary=None):
         res = C.c_double(0)
-        o = CStepOpts(num_subiter, outflow_fix, psd, rebuild)
+        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary)
         ph = _ptr(phases) if phases is not None else None
         it = self.lib().fsref_step(self.h, C.byref(o), dt, C.byref(res), ph)
         return it, res.value
