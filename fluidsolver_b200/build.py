@@ -63,21 +63,24 @@ def build(force: bool = False) -> str:
     return LIB
 
 
-def build_examples() -> str:
-    """the C++ host layer (include/shim) + example driver, plain g++ against libfsgpu.so"""
+def build_examples() -> list:
+    """the C++ host layer (include/shim) + example drivers, plain g++ against libfsgpu.so"""
     root = os.path.dirname(HERE)
-    src = os.path.join(root, "examples", "lid_driven_cavity.cpp")
-    out = os.path.join(root, "examples", "lid_driven_cavity")
-    deps = [src, LIB, os.path.join(root, "include", "fsgpu.h"),
-            os.path.join(root, "include", "shim", "FluidSolverGPU.hpp")]
-    if _newer(out, deps):
-        return out
-    cmd = [os.environ.get("CXX", "/usr/bin/g++"), "-std=c++20", "-O2", "-Wall", "-I" + os.path.join(root, "include"),
-           src, "-L" + HERE, "-lfsgpu", "-Wl,-rpath,$ORIGIN/../fluidsolver_b200", "-o", out]
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if r.returncode != 0:
-        raise RuntimeError(f"g++ failed for the shim example:\n{r.stdout}\n{r.stderr}")
-    return out
+    outs = []
+    for name in ("lid_driven_cavity", "two_phase_drop"):
+        src = os.path.join(root, "examples", name + ".cpp")
+        out = os.path.join(root, "examples", name)
+        deps = [src, LIB, os.path.join(root, "include", "fsgpu.h"),
+                os.path.join(root, "include", "shim", "FluidSolverGPU.hpp")]
+        outs.append(out)
+        if _newer(out, deps):
+            continue
+        cmd = [os.environ.get("CXX", "/usr/bin/g++"), "-std=c++20", "-O2", "-Wall", "-I" + os.path.join(root, "include"),
+               src, "-L" + HERE, "-lfsgpu", "-Wl,-rpath,$ORIGIN/../fluidsolver_b200", "-o", out]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"g++ failed for the shim example {name}:\n{r.stdout}\n{r.stderr}")
+    return outs
 
 
 if __name__ == "__main__":

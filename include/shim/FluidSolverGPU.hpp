@@ -183,6 +183,20 @@ void calc_rho(FS<Float, NX, NY, NGHOST>& fs) {
 template <typename Float, Index NX, Index NY, Index NGHOST>
 void calc_visc(FS<Float, NX, NY, NGHOST>& fs) { fill(fs.visc, fs.visc_gas); }
 
+// calc_rho(vf, fs) / calc_visc(vf, fs), src/FS.hpp:592-650: one device pass computes the face
+// densities and the viscosity (incl. their Neumann ghosts); it runs on the calc_rho call
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_rho(Field2D<Float, NX, NY, NGHOST>& vf, FS<Float, NX, NY, NGHOST>& fs) {
+  vf.bind(fs.ctx, FSGPU_VF);
+  vf.upload();
+  FSGPU_CHECK(fsgpu_set_props(fs.ctx, fs.rho_gas, fs.rho_liquid, fs.visc_gas, fs.visc_liquid, fs.sigma));
+  FSGPU_CHECK(fsgpu_calc_rho_visc_vof(fs.ctx));
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_visc(const Field2D<Float, NX, NY, NGHOST>& vf, FS<Float, NX, NY, NGHOST>&) {
+  if (vf.field_id() != FSGPU_VF) fsgpu_shim::check(1, "calc_visc(vf, fs) must follow calc_rho(vf, fs)");
+}
+
 // ---- boundary conditions (src/BoundaryConditions.hpp:14-224) --------------------------------------
 template <typename Float>
 struct Dirichlet {
@@ -322,6 +336,91 @@ Float abs_max(const Field2D<Float, M, N, NGHOST>& f) {
   double v = 0.0;
   FSGPU_CHECK(fsgpu_abs_max(fsgpu_shim::ctx_of(f), f.field_id(), &v));
   return v;
+}
+
+// ---- rows either side of the single-phase path -------------------------------------
+// calc_drhodt(fs, drho_u_stagdt, drho_v_stagdt), src/FS.hpp:318-406
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_drhodt(const FS<Float, NX, NY, NGHOST>& fs, Field2D<Float, NX + 1, NY, NGHOST>& drho_u_stagdt,
+                 Field2D<Float, NX, NY + 1, NGHOST>& drho_v_stagdt) {
+  drho_u_stagdt.bind(fs.ctx, FSGPU_DRHO_U);
+  drho_v_stagdt.bind(fs.ctx, FSGPU_DRHO_V);
+  FSGPU_CHECK(fsgpu_calc_drhodt(fs.ctx));
+}
+// update_density(drho_u_stagdt, drho_v_stagdt, dt, fs), src/FS.hpp:409-420
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void update_density(const Field2D<Float, NX + 1, NY, NGHOST>&, const Field2D<Float, NX, NY + 1, NGHOST>&,
+                    Float dt, FS<Float, NX, NY, NGHOST>& fs) {
+  FSGPU_CHECK(fsgpu_update_density(fs.ctx, dt));
+}
+// apply_neumann_bconds(field), src/BoundaryConditions.hpp:227-252
+template <typename Float, Index M, Index N, Index NGHOST>
+void apply_neumann_bconds(Field2D<Float, M, N, NGHOST>& f) {
+  FSGPU_CHECK(fsgpu_apply_neumann_bconds(fsgpu_shim::ctx_of(f), f.field_id()));
+}
+// calc_pressure_jump(vf, curv, interface_length, fs), src/FS.hpp:439-466.  The three cell fields
+// come from the VOF module (out of scope here): bind_cell_input uploads a host-filled field.
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void bind_cell_input(FS<Float, NX, NY, NGHOST>& fs, Field2D<Float, NX, NY, NGHOST>& f, int field) {
+  f.bind(fs.ctx, field);
+  f.upload();
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_pressure_jump(Field2D<Float, NX, NY, NGHOST>& vf, Field2D<Float, NX, NY, NGHOST>& curv,
+                        Field2D<Float, NX, NY, NGHOST>& interface_length, FS<Float, NX, NY, NGHOST>& fs) {
+  if (!vf.bound()) bind_cell_input(fs, vf, FSGPU_VF);
+  if (!curv.bound()) bind_cell_input(fs, curv, FSGPU_CURV);
+  if (!interface_length.bound()) bind_cell_input(fs, interface_length, FSGPU_INTERFACE_LENGTH);
+  FSGPU_CHECK(fsgpu_calc_pressure_jump(fs.ctx));
+}
+// the capillary block the two-phase drivers inline (test/StationaryDrop.cpp:331-353)
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void add_capillary_divergence(FS<Float, NX, NY, NGHOST>& fs, Field2D<Float, NX, NY, NGHOST>& div, Float dt) {
+  if (div.field_id() != FSGPU_DIV) fsgpu_shim::check(1, "add_capillary_divergence expects the field calc_divergence wrote");
+  FSGPU_CHECK(fsgpu_capillary_divergence(fs.ctx, dt));
+}
+// correct_velocity_ib_implicit_euler / update_velocity_ib_semi_analytical, src/IB.hpp:110-186
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void correct_velocity_ib_implicit_euler(Field2D<Float, NX + 1, NY, NGHOST>& ib_corr_u_stag,
+                                        Field2D<Float, NX, NY + 1, NGHOST>& ib_corr_v_stag, Float dt,
+                                        FS<Float, NX, NY, NGHOST>& fs) {
+  if (!ib_corr_u_stag.bound()) { ib_corr_u_stag.bind(fs.ctx, FSGPU_IB_CORR_U); ib_corr_u_stag.upload(); }
+  if (!ib_corr_v_stag.bound()) { ib_corr_v_stag.bind(fs.ctx, FSGPU_IB_CORR_V); ib_corr_v_stag.upload(); }
+  FSGPU_CHECK(fsgpu_correct_velocity_ib_implicit_euler(fs.ctx, dt));
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void update_velocity_ib_semi_analytical(const Field2D<Float, NX + 1, NY, NGHOST>&,
+                                        const Field2D<Float, NX, NY + 1, NGHOST>&, Float dt,
+                                        Field2D<Float, NX + 1, NY, NGHOST>& ib_corr_u_stag,
+                                        Field2D<Float, NX, NY + 1, NGHOST>& ib_corr_v_stag,
+                                        FS<Float, NX, NY, NGHOST>& fs) {
+  if (!ib_corr_u_stag.bound()) { ib_corr_u_stag.bind(fs.ctx, FSGPU_IB_CORR_U); ib_corr_u_stag.upload(); }
+  if (!ib_corr_v_stag.bound()) { ib_corr_v_stag.bind(fs.ctx, FSGPU_IB_CORR_V); ib_corr_v_stag.upload(); }
+  FSGPU_CHECK(fsgpu_update_velocity_ib_semi_analytical(fs.ctx, dt));
+}
+// interpolate_U / interpolate_V / interpolate_UV_staggered_field, src/Operators.hpp:10-29: one device
+// pass fills all three cell-centred fields; it runs on the interpolate_U call
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void interpolate_U(const Field2D<Float, NX + 1, NY, NGHOST>& U, Field2D<Float, NX, NY, NGHOST>& Ui) {
+  Ui.bind(fsgpu_shim::ctx_of(U), FSGPU_UI);
+  FSGPU_CHECK(fsgpu_interpolate_cell_centres(fsgpu_shim::ctx_of(U)));
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void interpolate_V(const Field2D<Float, NX, NY + 1, NGHOST>& V, Field2D<Float, NX, NY, NGHOST>& Vi) {
+  Vi.bind(fsgpu_shim::ctx_of(V), FSGPU_VI);
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void interpolate_UV_staggered_field(const Field2D<Float, NX + 1, NY, NGHOST>& u_stag,
+                                    const Field2D<Float, NX, NY + 1, NGHOST>&,
+                                    Field2D<Float, NX, NY, NGHOST>& interp) {
+  if (u_stag.field_id() != FSGPU_RHO_U) fsgpu_shim::check(1, "interpolate_UV_staggered_field expects curr.rho_u_stag / rho_v_stag");
+  interp.bind(fsgpu_shim::ctx_of(u_stag), FSGPU_RHOI);
+}
+// calc_conserved_quantities(fs, mass, momentum_x, momentum_y), src/FS.hpp:653-676
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_conserved_quantities(const FS<Float, NX, NY, NGHOST>& fs, Float& mass, Float& momentum_x,
+                               Float& momentum_y) {
+  FSGPU_CHECK(fsgpu_calc_conserved_quantities(fs.ctx, &mass, &momentum_x, &momentum_y));
 }
 
 // ---- LinearSolver_StructHypre (src/LinearSolver_StructHypre.hpp:28-192) ----------------------------
