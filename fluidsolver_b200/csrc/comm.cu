@@ -113,6 +113,9 @@ struct LocalGroup {
       return 0;
     }
     const bool ok = cv.wait_for(lk, std::chrono::seconds(120), [&] { return generation != gen || broken; });
+    // a barrier that completed is a success even if a faster rank has left the group since
+    // (fsgpu_destroy marks the group broken): only an incomplete generation is a failure
+    if (generation != gen) return 0;
     if (!ok || broken) {
       broken = true;
       cv.notify_all();
