@@ -13,9 +13,10 @@
 
 int64_t g_launches = 0;
 unsigned int g_prof_mask = 0;
+int g_prof_tag = 0;
 
 namespace {
-struct ProfRec { int cls; cudaEvent_t a, b; };
+struct ProfRec { int cls; cudaEvent_t a, b; int tag; };
 std::vector<ProfRec> g_prof_recs;
 std::vector<cudaEvent_t> g_prof_pool;
 cudaEvent_t g_prof_open[PROF_NCLASS];
@@ -33,7 +34,25 @@ void fs_prof_begin(int cls, cudaStream_t st) {
 void fs_prof_end(int cls, cudaStream_t st) {
   cudaEvent_t e = prof_event();
   cudaEventRecord(e, st);
-  g_prof_recs.push_back({cls, g_prof_open[cls], e});
+  g_prof_recs.push_back({cls, g_prof_open[cls], e, g_prof_tag});
+}
+// PCG launches one iteration past convergence (its kernels return at their first instruction);
+// the solver tags records with the iteration they belong to and, once it knows how many
+// iterations were real, drops the records of the empty ones so that averages are over launches
+// that did work.
+size_t fs_prof_mark(void) { return g_prof_recs.size(); }
+void fs_prof_drop_after(size_t from, int last_real_tag, int cls_empty_at_last) {
+  size_t w = from;
+  for (size_t k = from; k < g_prof_recs.size(); ++k) {
+    if (g_prof_recs[k].tag > last_real_tag ||
+        (g_prof_recs[k].tag == last_real_tag && g_prof_recs[k].cls == cls_empty_at_last)) {
+      g_prof_pool.push_back(g_prof_recs[k].a);
+      g_prof_pool.push_back(g_prof_recs[k].b);
+    } else {
+      g_prof_recs[w++] = g_prof_recs[k];
+    }
+  }
+  g_prof_recs.resize(w);
 }
 static thread_local char g_err[512] = "";
 

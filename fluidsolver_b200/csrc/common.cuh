@@ -177,6 +177,10 @@ enum {
   PROF_DOWN0, PROF_UP0, PROF_DOWN, PROF_UP, PROF_COARSE, PROF_SETUP, PROF_OTHER, PROF_NCLASS
 };
 extern unsigned int g_prof_mask;
+extern int g_prof_tag;  // stamped on every record (PCG: the iteration number)
+size_t fs_prof_mark(void);
+// drop records [from, end) with tag > last_real_tag, and those of class cls_empty_at_last with tag == last_real_tag
+void fs_prof_drop_after(size_t from, int last_real_tag, int cls_empty_at_last);
 void fs_prof_begin(int cls, cudaStream_t st);
 void fs_prof_end(int cls, cudaStream_t st);
 struct ProfScope {

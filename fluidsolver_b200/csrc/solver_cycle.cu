@@ -14,6 +14,9 @@
 // Pads of every array are zero, so stencils read past the grid edge without branches.
 #include "solver.h"
 
+#include <stdlib.h>
+
+#include <algorithm>
 #include <utility>
 
 // resident CTAs per SM the marching kernels are compiled for (register cap = 65536 / (128 * MINB))
@@ -447,6 +450,149 @@ k_jacobi(const LevelDev L, const double* __restrict__ b, const double* __restric
   xo[k] = xi[k] + w * (b[k] - v) * L.dinv[k];
 }
 
+// ---- the tail of the hierarchy in ONE kernel ------------------------------------------------------
+// From the first level whose padded grid fits a 48 KB shared-memory tile (<= FS_TAIL_TILE points)
+// down to the coarsest, a V-cycle leg is a handful of points per thread: as separate launches
+// those ~2 x 15 levels cost 5-10 us each (launch + drain), 6 % of a timestep at 8192^2.  Here one
+// CTA walks them all -- restriction down, the coarsest sweeps, interpolation + post-relaxation up --
+// with a block barrier between levels.  b and x of the tail levels stay in their global arrays
+// (L1/L2 resident; plain loads, never ld.global.nc, because this kernel writes them); the
+// pre-relaxed iterate x0 of the level being post-relaxed lives in shared memory.  Same formulas
+// and association as k_down_march* / k_up_march / k_coarse_smem.
+#define FS_TAIL_MAX 24
+#define FS_TAIL_TILE 6144
+struct TailArgs {
+  int n;       // number of tail levels; v[0] is the first tail level, v[n - 1] the coarsest
+  int sweeps;  // coarsest-level Jacobi sweeps
+  LevelDev v[FS_TAIL_MAX];
+  int cdir[FS_TAIL_MAX], active[FS_TAIL_MAX];
+  double w[FS_TAIL_MAX];
+};
+
+// residual of the zero-guess pre-relaxation at q: b - A (w b / d)   (inactive level: b)
+__device__ __forceinline__ double tail_resid(const LevelDev& f, const double* b, bool active, double w,
+                                             int64_t q) {
+  const double bq = b[q];
+  if (!active) return bq;
+  const int64_t P = f.pitch;
+  double v = w * bq;
+  v += __ldg(f.cx + q) * (w * b[q - P] * __ldg(f.dinv + q - P));
+  v += __ldg(f.cx + q + P) * (w * b[q + P] * __ldg(f.dinv + q + P));
+  v += __ldg(f.cy + q) * (w * b[q - 1] * __ldg(f.dinv + q - 1));
+  v += __ldg(f.cy + q + 1) * (w * b[q + 1] * __ldg(f.dinv + q + 1));
+  return bq - v;
+}
+
+__global__ void __launch_bounds__(1024)
+k_tail_vcycle(const TailArgs a, const PcgScal* scal) {
+  if (scal->done) return;
+  extern __shared__ double sm[];
+  const int tid = threadIdx.x, nth = blockDim.x;
+  // ---- down: b of level k -> b of level k + 1
+  for (int k = 0; k + 1 < a.n; ++k) {
+    const LevelDev& f = a.v[k];
+    const LevelDev& c = a.v[k + 1];
+    const int64_t P = f.pitch, nc = c.n0 * c.n1;
+    const bool act = a.active[k] != 0;
+    const double w = a.w[k];
+    const int cd = a.cdir[k];
+    for (int64_t t = tid; t < nc; t += nth) {
+      const int64_t ci = t / c.n1, cj = t - ci * c.n1;
+      const int64_t li = cd == 0 ? 2 * ci + c.foff : ci, lj = cd == 0 ? cj : 2 * cj + c.foff;
+      const int64_t q = f.idx(li, lj), st = cd == 0 ? P : 1;
+      const double am = cd == 0 ? __ldg(f.cx + q) : __ldg(f.cy + q);
+      const double ap = cd == 0 ? __ldg(f.cx + q + P) : __ldg(f.cy + q + 1);
+      double v = tail_resid(f, f.b, act, w, q);
+      v += (-am * __ldg(f.pc + q - st)) * tail_resid(f, f.b, act, w, q - st);
+      v += (-ap * __ldg(f.pc + q + st)) * tail_resid(f, f.b, act, w, q + st);
+      c.b[c.idx(ci, cj)] = v;
+    }
+    __syncthreads();
+  }
+  // ---- coarsest level: `sweeps` Jacobi sweeps (weight 1) from a zero guess, as k_coarse_smem
+  {
+    const LevelDev& L = a.v[a.n - 1];
+    const int64_t n0 = L.n0, n1 = L.n1, w1 = n1 + 2, tot = (n0 + 2) * w1, n = n0 * n1, P = L.pitch;
+    double* xa = sm;
+    double* xb = sm + tot;
+    const bool on = a.active[a.n - 1] && !scal->coarse_zero_diag;
+    for (int64_t t = tid; t < 2 * tot; t += nth) sm[t] = 0.0;
+    __syncthreads();
+    if (on) {
+      for (int64_t t = tid; t < n; t += nth) {
+        const int64_t li = t / n1, lj = t - li * n1, q = L.idx(li, lj);
+        xa[(li + 1) * w1 + lj + 1] = L.b[q] * __ldg(L.dinv + q);
+      }
+      __syncthreads();
+      for (int it = 1; it < a.sweeps; ++it) {
+        for (int64_t t = tid; t < n; t += nth) {
+          const int64_t li = t / n1, lj = t - li * n1, q = L.idx(li, lj), m = (li + 1) * w1 + lj + 1;
+          double v = __ldg(L.d + q) * xa[m];
+          v += __ldg(L.cx + q) * xa[m - w1];
+          v += __ldg(L.cx + q + P) * xa[m + w1];
+          v += __ldg(L.cy + q) * xa[m - 1];
+          v += __ldg(L.cy + q + 1) * xa[m + 1];
+          xb[m] = xa[m] + (L.b[q] - v) * __ldg(L.dinv + q);
+        }
+        __syncthreads();
+        double* t2 = xa; xa = xb; xb = t2;
+      }
+    }
+    for (int64_t t = tid; t < n; t += nth) {
+      const int64_t li = t / n1, lj = t - li * n1;
+      L.x[L.idx(li, lj)] = xa[(li + 1) * w1 + lj + 1];
+    }
+    __syncthreads();
+  }
+  // ---- up: x of level k + 1 -> x of level k (interpolation + post-relaxation)
+  for (int k = a.n - 2; k >= 0; --k) {
+    const LevelDev& f = a.v[k];
+    const LevelDev& c = a.v[k + 1];
+    const int64_t P = f.pitch, n1 = f.n1, w1 = n1 + 2, tot = (f.n0 + 2) * w1, n = f.n0 * n1;
+    const bool act = a.active[k] != 0;
+    const double w = a.w[k];
+    const int cd = a.cdir[k];
+    if (act) {
+      for (int64_t t = tid; t < tot; t += nth) sm[t] = 0.0;
+      __syncthreads();
+    }
+    for (int64_t t = tid; t < n; t += nth) {
+      const int64_t li = t / n1, lj = t - li * n1, q = f.idx(li, lj);
+      double x = act ? w * f.b[q] * __ldg(f.dinv + q) : 0.0;
+      const int64_t pos = (cd == 0 ? li : lj) - c.foff;  // even <=> C-point
+      if ((pos & 1) == 0) {
+        const int64_t cp = pos >> 1;
+        x += c.x[cd == 0 ? c.idx(cp, lj) : c.idx(li, cp)];
+      } else {
+        const int64_t cm = (pos - 1) >> 1;
+        const int64_t kc = cd == 0 ? c.idx(cm, lj) : c.idx(li, cm);
+        const double pc  = __ldg(f.pc + q);
+        const double am = cd == 0 ? __ldg(f.cx + q) : __ldg(f.cy + q);
+        const double ap = cd == 0 ? __ldg(f.cx + q + P) : __ldg(f.cy + q + 1);
+        double v = (-am * pc) * c.x[kc];
+        v += (-ap * pc) * c.x[kc + (cd == 0 ? c.pitch : 1)];
+        x += v;
+      }
+      if (act) sm[(li + 1) * w1 + lj + 1] = x;
+      else f.x[q] = x;
+    }
+    __syncthreads();
+    if (act) {
+      for (int64_t t = tid; t < n; t += nth) {
+        const int64_t li = t / n1, lj = t - li * n1, q = f.idx(li, lj), m = (li + 1) * w1 + lj + 1;
+        const double x0 = sm[m];
+        double v = __ldg(f.d + q) * x0;
+        v += __ldg(f.cx + q) * sm[m - w1];
+        v += __ldg(f.cx + q + P) * sm[m + w1];
+        v += __ldg(f.cy + q) * sm[m - 1];
+        v += __ldg(f.cy + q + 1) * sm[m + 1];
+        f.x[q] = x0 + w * (f.b[q] - v) * __ldg(f.dinv + q);
+      }
+      __syncthreads();
+    }
+  }
+}
+
 dim3 lvl_grid(const LevelDev& v) { return dim3((unsigned)cdiv(v.n1, BX), (unsigned)cdiv(v.i1 - v.i0, BY)); }
 
 }  // namespace
@@ -547,6 +693,41 @@ static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_m
   return 0;
 }
 
+// first level of the one-kernel tail (k_tail_vcycle), or nl if the hierarchy has none: at least two
+// levels, every one of them whole on this rank (single rank, or replicated levels) and small
+// enough for the shared-memory tile.  FSGPU_NO_TAIL=1 keeps the per-level launches (A/B runs).
+static int tail_start(const fsgpu_ps* s) {
+  static const bool off = getenv("FSGPU_NO_TAIL") != nullptr;
+  if (off) return s->nl;
+  int lt = s->nl;
+  for (int l = s->nl - 1; l >= 1; --l) {
+    const LevelDev& v = s->L[l].v;
+    if ((v.n0 + 2) * (v.n1 + 2) > FS_TAIL_TILE || v.i0 != 0 || v.i1 != v.n0) break;
+    if (s->c->nranks > 1 && l < s->ld) break;
+    lt = l;
+  }
+  if (s->nl - lt < 2 || s->nl - lt > FS_TAIL_MAX) return s->nl;
+  return lt;
+}
+static int launch_tail(fsgpu_ps* s, int lt) {
+  TailArgs a;
+  a.n = s->nl - lt;
+  a.sweeps = s->coarse_sweeps;
+  size_t tile = 0;
+  for (int k = 0; k < a.n; ++k) {
+    const Level& L = s->L[lt + k];
+    a.v[k] = L.v; a.cdir[k] = L.cdir; a.active[k] = L.active; a.w[k] = L.weight;
+    if (k + 1 < a.n) tile = std::max(tile, (size_t)((L.v.n0 + 2) * (L.v.n1 + 2)));
+  }
+  const LevelDev& C = s->L[s->nl - 1].v;
+  const size_t smem = std::max(tile, (size_t)(2 * (C.n0 + 2) * (C.n1 + 2))) * sizeof(double);
+  if (smem > 48 * 1024)
+    FS_CUDA(cudaFuncSetAttribute(k_tail_vcycle, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_tail_vcycle<<<1, 1024, smem, s->c->stream>>>(a, s->scal);
+  FS_LAUNCHED();
+  return 0;
+}
+
 int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
   cudaStream_t st = s->c->stream;
   Level* L        = s->L;
@@ -569,7 +750,9 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
   // down: level l rhs -> level l+1 rhs.  Slab decomposition: a distributed coarse level gets
   // FS_RO halo rows of its rhs from the neighbours; the first replicated level is gathered
   // (every rank writes its rows into a zeroed full array, then a sum all-reduce).
-  for (int l = 0; l <= nl - 2; ++l) {
+  const int lt = tail_start(s);  // levels [lt, nl) run inside k_tail_vcycle (lt == nl: none)
+  const int lbot = lt < nl ? lt : nl - 1;
+  for (int l = 0; l <= lbot - 1; ++l) {
     const double* fb = l == 0 ? r : L[l].v.b;
     ProfScope ps_(l == 0 ? PROF_DOWN0 : PROF_DOWN, st);
     const bool gather = dist && l + 1 == s->ld;
@@ -585,11 +768,12 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
   }
   {
     ProfScope ps_(PROF_COARSE, st);
-    if (coarse_solve(s, nl - 1, L[nl - 1].v.b, L[nl - 1].v.x)) return 1;
+    if (lt < nl) { if (launch_tail(s, lt)) return 1; }
+    else if (coarse_solve(s, nl - 1, L[nl - 1].v.b, L[nl - 1].v.x)) return 1;
   }
   // up: level l+1 x -> level l x; the level-0 kernel also carries PCG's <r, z>.  A distributed
   // level's x needs one halo row before the next finer level interpolates from it.
-  for (int l = nl - 2; l >= 0; --l) {
+  for (int l = lbot - 1; l >= 0; --l) {
     const double* fb = l == 0 ? r : L[l].v.b;
     double* fx       = l == 0 ? z : L[l].v.x;
     ProfScope ps_(l == 0 ? PROF_UP0 : PROF_UP, st);

@@ -141,6 +141,8 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
   double* x = c->f[FSGPU_DELTA_P];
   double* r = c->f[FSGPU_RHS];  // r = b - A 0 = b: the rhs buffer becomes the residual
+  const size_t prof0 = fs_prof_mark();
+  g_prof_tag = 0;
   k_scal_init<<<1, 1, 0, st>>>(s->scal, s->o.tol * s->o.tol, c->nranks);
   FS_LAUNCHED();
   FS_CUDA(cudaMemsetAsync(alloc_base(c->g, x), 0, (size_t)c->g.count() * sizeof(double), st));
@@ -155,6 +157,7 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   int launched = 0;
   bool stop = false;
   for (int it = 1; it <= s->o.max_iter && !stop; ++it) {
+    g_prof_tag = it;
     {
       ProfScope ps_(PROF_MATVEC, st);
       k_matvec_dot<<<pg, bl, 0, st>>>(L0, s->p, s->s, s->scal, c->part, c->ticket);
@@ -188,6 +191,9 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   FS_CUDA(cudaMemcpyAsync(&s->h_scal[0], s->scal, sizeof(PcgScal), cudaMemcpyDeviceToHost, st));
   FS_CUDA(cudaStreamSynchronize(st));
   const PcgScal& h = s->h_scal[0];
+  g_prof_tag = 0;
+  // (the p update of the iteration that met the convergence test is empty as well)
+  if (g_prof_mask) fs_prof_drop_after(prof0, h.done == PCG_ZERO_RHS ? 0 : h.iter, h.done ? PROF_PUPD : -1);
   if (h.done == PCG_ZERO_RHS) {
     if (residual) *residual = 0.0;
     if (iters) *iters = 0;

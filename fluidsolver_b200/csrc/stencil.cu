@@ -42,6 +42,7 @@ struct MomArgs {
   const double *mu, *p, *pju, *pjv;
   double *outU, *outV;              // dmom (MODE 0) or new velocity (MODE 1/2)
   double dx, dy, dt, eps;
+  double rdx, rdy;  // 1/dx, 1/dy: the fused pass multiplies (<= 1 ulp per quotient, tolerance 1e-12)
 };
 
 // MID: velocities are averaged with the old ones on the fly (calc_mid_time fused in).
@@ -61,7 +62,7 @@ __device__ __forceinline__ double flux_FXU(const MomArgs& a, const Vel<MID>& U, 
   double rh, uh;
   hybrid_interp(a.eps, __ldg(a.ruo + k), __ldg(a.ruo + k + P), um, up, um, up, rh, uh);
   const double Ui   = (up + um) / 2;
-  const double dUdx = (up - um) / a.dx;
+  const double dUdx = MID ? (up - um) * a.rdx : (up - um) / a.dx;
   return -rh * uh * Ui + 2.0 * __ldg(a.mu + k) * dUdx - __ldg(a.p + k);
 }
 template <bool MID>
@@ -70,7 +71,7 @@ __device__ __forceinline__ double flux_FYV(const MomArgs& a, const Vel<MID>& V, 
   double rh, vh;
   hybrid_interp(a.eps, __ldg(a.rvo + k), __ldg(a.rvo + k + 1), vm, vp, vm, vp, rh, vh);
   const double Vi   = (vm + vp) / 2;
-  const double dVdy = (vp - vm) / a.dy;
+  const double dVdy = MID ? (vp - vm) * a.rdy : (vp - vm) / a.dy;
   return -rh * vh * Vi + 2.0 * __ldg(a.mu + k) * dVdy - __ldg(a.p + k);
 }
 // corner fluxes FYU(i,j) and FXV(i,j) share the corner viscosity and the shear rate
@@ -81,8 +82,8 @@ __device__ __forceinline__ void flux_corner(const MomArgs& a, const Vel<MID>& U,
   const double v0 = V(k - P), v1 = V(k);   // V(i-1,j), V(i,j)
   const double vc = (__ldg(a.mu + k) + __ldg(a.mu + k - P) + __ldg(a.mu + k - 1) +
                      __ldg(a.mu + k - P - 1)) / 4.0;
-  const double dUdy = (u1 - u0) / a.dy;
-  const double dVdx = (v1 - v0) / a.dx;
+  const double dUdy = MID ? (u1 - u0) * a.rdy : (u1 - u0) / a.dy;
+  const double dVdx = MID ? (v1 - v0) * a.rdx : (v1 - v0) / a.dx;
   const double sh   = vc * (dUdy + dVdx);
   double rh, h;
   hybrid_interp(a.eps, __ldg(a.ruo + k - 1), __ldg(a.ruo + k), u0, u1, v0, v1, rh, h);
@@ -108,7 +109,8 @@ k_momentum(const MomArgs a, const Geom g) {
     double fyu01, t;                        // corner (i, j+1)
     flux_corner<MID>(a, U, V, k + 1, P, fyu01, t);
     const double fxu0 = flux_FXU<MID>(a, U, k, P), fxum = flux_FXU<MID>(a, U, k - P, P);
-    const double dm = (fxu0 - fxum) / a.dx + (fyu01 - fyu00) / a.dy + __ldg(a.pju + k);
+    const double dm = (MID ? (fxu0 - fxum) * a.rdx + (fyu01 - fyu00) * a.rdy
+                           : (fxu0 - fxum) / a.dx + (fyu01 - fyu00) / a.dy) + __ldg(a.pju + k);
     if (MODE == 0) a.outU[k] = dm;
     else a.outU[k] = (__ldg(a.ruo + k) * __ldg(a.Uo + k) + a.dt * dm) / __ldg(a.ru + k);
   }
@@ -116,7 +118,8 @@ k_momentum(const MomArgs a, const Geom g) {
     double fxv10, t;                        // corner (i+1, j)
     flux_corner<MID>(a, U, V, k + P, P, t, fxv10);
     const double fyv0 = flux_FYV<MID>(a, V, k, P), fyvm = flux_FYV<MID>(a, V, k - 1, P);
-    const double dm = (fxv10 - fxv00) / a.dx + (fyv0 - fyvm) / a.dy + __ldg(a.pjv + k);
+    const double dm = (MID ? (fxv10 - fxv00) * a.rdx + (fyv0 - fyvm) * a.rdy
+                           : (fxv10 - fxv00) / a.dx + (fyv0 - fyvm) / a.dy) + __ldg(a.pjv + k);
     if (MODE == 0) a.outV[k] = dm;
     else a.outV[k] = (__ldg(a.rvo + k) * __ldg(a.Vo + k) + a.dt * dm) / __ldg(a.rv + k);
   }
@@ -155,6 +158,7 @@ static MomArgs mom_args(fsgpu_ctx* c, double dt) {
   a.pju = c->f[FSGPU_P_JUMP_U]; a.pjv = c->f[FSGPU_P_JUMP_V];
   a.outU = c->f[FSGPU_DMOM_U]; a.outV = c->f[FSGPU_DMOM_V];
   a.dx = c->g.dx; a.dy = c->g.dy; a.dt = dt;
+  a.rdx = 1.0 / c->g.dx; a.rdy = 1.0 / c->g.dy;
   a.eps = 1e-3 * fmin(c->rho_gas, c->rho_liquid);  // calc_rho_eps, FS.hpp:153-155
   return a;
 }
