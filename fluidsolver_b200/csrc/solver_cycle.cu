@@ -198,17 +198,17 @@ __device__ __forceinline__ double x_interp(const LevelDev& f, double bq, const L
   return x;
 }
 
-// inactive level: interpolation only (no relaxation on this level)
+// inactive level: interpolation only (no relaxation on this level); persistent tile loop, so the
+// copies enqueued past PCG convergence cost a few us instead of an empty 1e5-CTA grid
 template <int CDIR>
 __global__ void __launch_bounds__(BX* BY)
 k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
             const double* __restrict__ cxv, const PcgScal* scal) {
   if (scal->done) return;
-  const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = f.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (li >= f.i1 || lj >= f.n1) return;
-  const int64_t k = f.idx(li, lj);
-  fx[k] = x_interp<CDIR, false>(f, 0.0, c, cxv, li, lj, k, 0.0);
+  for_each_point(f.i0, f.i1, f.n1, [&](int64_t li, int64_t lj) {
+    const int64_t k = f.idx(li, lj);
+    fx[k] = x_interp<CDIR, false>(f, 0.0, c, cxv, li, lj, k, 0.0);
+  });
 }
 
 // active level, "marching" formulation.  A warp owns a strip of 32 consecutive columns (30 of
@@ -676,7 +676,7 @@ static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_m
   Level* L        = s->L;
   fsgpu_ctx* c    = s->c;
   if (!L[l].active) {
-    k_up_interp<CDIR><<<lvl_grid(L[l].v), dim3(BX, BY), 0, st>>>(L[l].v, fx, L[l + 1].v, L[l + 1].v.x, s->scal);
+    k_up_interp<CDIR><<<persist_blocks(L[l].v.i1 - L[l].v.i0, L[l].v.n1), dim3(BX, BY), 0, st>>>(L[l].v, fx, L[l + 1].v, L[l + 1].v.x, s->scal);
     FS_LAUNCHED();
     return 0;
   }

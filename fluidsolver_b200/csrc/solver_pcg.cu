@@ -46,18 +46,18 @@ k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict_
   }
 }
 
-// x += alpha p; r -= alpha s
+// x += alpha p; r -= alpha s.  Persistent grid (as the reduction kernels): the copy of this kernel
+// that is enqueued past convergence then costs ~3 us instead of the 140 us a 264k-CTA empty grid takes.
 __global__ void __launch_bounds__(BX* BY)
 k_xr_update(const LevelDev L, double* __restrict__ x, double* __restrict__ r,
             const double* __restrict__ p, const double* __restrict__ s, const PcgScal* scal) {
   if (scal->done) return;
-  const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = L.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (li >= L.i1 || lj >= L.n1) return;
-  const int64_t k = L.idx(li, lj);
   const double alpha = scal->alpha;
-  x[k] += alpha * p[k];
-  r[k] -= alpha * s[k];
+  for_each_point(L.i0, L.i1, L.n1, [&](int64_t li, int64_t lj) {
+    const int64_t k = L.idx(li, lj);
+    x[k] += alpha * p[k];
+    r[k] -= alpha * s[k];
+  });
 }
 
 // gamma' = <r, z>.  INIT: this is bi = <C b, b>; otherwise the convergence test + beta.
@@ -77,18 +77,18 @@ k_dot_rz(const LevelDev L, const double* __restrict__ r, const double* __restric
   }
 }
 
-// p = z + beta p   (FIRST: p = z)
+// p = z + beta p   (FIRST: p = z); persistent grid for the same reason
 template <bool FIRST>
 __global__ void __launch_bounds__(BX* BY)
 k_p_update(const LevelDev L, double* __restrict__ p, const double* __restrict__ z,
            const PcgScal* scal) {
   if (scal->done) return;
-  const int64_t lj = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t li = L.i0 + (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (li >= L.i1 || lj >= L.n1) return;
-  const int64_t k = L.idx(li, lj);
-  if (FIRST) p[k] = z[k];
-  else p[k] = z[k] + scal->beta * p[k];
+  const double beta = FIRST ? 0.0 : scal->beta;
+  for_each_point(L.i0, L.i1, L.n1, [&](int64_t li, int64_t lj) {
+    const int64_t k = L.idx(li, lj);
+    if (FIRST) p[k] = z[k];
+    else p[k] = z[k] + beta * p[k];
+  });
 }
 
 // (the reduction kernels return at once after convergence and leave red[] stale: skip then too)
@@ -136,7 +136,7 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   fsgpu_ctx* c    = s->c;
   cudaStream_t st = c->stream;
   const LevelDev& L0 = s->L[0].v;
-  const dim3 gr((unsigned)cdiv(L0.n1, BX), (unsigned)cdiv(L0.i1 - L0.i0, BY)), bl(BX, BY);
+  const dim3 bl(BX, BY);
   const unsigned pg = persist_blocks(L0.i1 - L0.i0, L0.n1);
   if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
   double* x = c->f[FSGPU_DELTA_P];
@@ -150,7 +150,7 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   // reaches two rows out), p one halo row before the matvec
   if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
   if (ps_vcycle(s, r, s->z, 2)) return 1;  // z = C b and bi = <z, b>
-  k_p_update<true><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);
+  k_p_update<true><<<pg, bl, 0, st>>>(L0, s->p, s->z, s->scal);
   FS_LAUNCHED();
   if (ps_halo(s, 0, &s->p, 1, 1)) return 1;
   const int nslot = FS_LAG + 1;
@@ -166,14 +166,14 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
     }
     {
       ProfScope ps_(PROF_XR, st);
-      k_xr_update<<<gr, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal);
+      k_xr_update<<<pg, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal);
       FS_LAUNCHED();
       if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
     }
     if (ps_vcycle(s, r, s->z, 1)) return 1;  // z = C r and gamma' = <r, z>
     {
       ProfScope ps_(PROF_PUPD, st);
-      k_p_update<false><<<gr, bl, 0, st>>>(L0, s->p, s->z, s->scal);
+      k_p_update<false><<<pg, bl, 0, st>>>(L0, s->p, s->z, s->scal);
       FS_LAUNCHED();
       if (ps_halo(s, 0, &s->p, 1, 1)) return 1;
     }
