@@ -263,11 +263,23 @@ def main():
     cells = (a_hi - a_lo) * (n + 2)  # level-0 unknowns this rank's kernels sweep per launch
     kms, kcnt = prof.get(prof_cls, (0.0, 0))
     achieved = ALGO_BYTES[prof_cls] * cells / (kms / max(kcnt, 1) * 1e-3) / 1e9 if kcnt else None
+    # DRAM bytes per launch of that kernel from the committed ncu --set full capture (same grid only)
+    traffic = None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if tr["grid"] == n and world == 1 and prof_cls in tr["dram_bytes_per_launch"]:
+            e = tr["dram_bytes_per_launch"][prof_cls]
+            traffic = e["read"] + e["write"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "kernel": prof_cls, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak if achieved else None, "traffic": None,
+                "frac": achieved / peak if achieved else None, "traffic": traffic,
+                "traffic_source": "profiles/ncu_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full)" if traffic else None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                 "algorithmic_bytes_per_launch": ALGO_BYTES[prof_cls] * cells,
                 "avg_launch_us": kms / max(kcnt, 1) * 1e3, "launches_timed": kcnt,
+                "launches_note": "launches that did work: the copies PCG enqueues one iteration past convergence "
+                                 "(they return at their first instruction) are excluded from the average",
                 "share_of_step": kms / ms if ms else None}
     # whole-step roofline: SURVEY.md section 8d  B_step(k) = NSUB (232 + 160 + 264 k) + 120 bytes per cell
     b_step = NSUB * (232 + 160 + 264 * k_bar) + 120
