@@ -7,7 +7,7 @@ for N in "$@"; do
   for RP in ${REPLS:-default}; do
     [ "$RP" = default ] && unset FSGPU_REPL_POINTS || export FSGPU_REPL_POINTS=$RP
     out=gpurun_out/${TAG}_n${N}_${RP}
-    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 \
+    timeout ${RUN_TIMEOUT:-600} python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 \
       --master-port 29541 bench.py --gpus $N --steps 4 --warmup 3 ${BENCH_ARGS:-} > $out.json 2> $out.err
     echo "N=$N repl=$RP exit $?"
     python - <<PY
