@@ -258,7 +258,7 @@ int fsgpu_fill(fsgpu_ctx* c, int field, double value) {
 int fsgpu_sync(fsgpu_ctx* c) {
   FS_CHECK_CTX(c);
   FS_CUDA(cudaStreamSynchronize(c->stream));
-  return 0;
+  return comm_failed(c);
 }
 
 int fsgpu_device_field(fsgpu_ctx* c, int field, double** ptr, int64_t* pitch, int64_t* row0,
@@ -308,7 +308,7 @@ static int read_red(fsgpu_ctx* c, int off, int n) {
   FS_CUDA(cudaMemcpyAsync(c->h_red + off, c->red_out + off, n * sizeof(double),
                           cudaMemcpyDeviceToHost, c->stream));
   FS_CUDA(cudaStreamSynchronize(c->stream));
-  return 0;
+  return comm_failed(c);
 }
 
 int fsgpu_adjust_dt(fsgpu_ctx* c, double cfl_max, double dt_max, double* dt) {

@@ -18,6 +18,8 @@
 #include "ctx.h"
 
 #include <dlfcn.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <nccl.h>
 #include <string.h>
 
@@ -38,6 +40,8 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int)                       = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t)                                                 = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                            cudaStream_t)                                                 = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t,
                             cudaStream_t)                                                 = nullptr;
   ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t)      = nullptr;
@@ -69,6 +73,7 @@ int nccl_load() {
   SYM(CommInitRank, "ncclCommInitRank");
   SYM(CommDestroy, "ncclCommDestroy");
   SYM(AllReduce, "ncclAllReduce");
+  SYM(AllGather, "ncclAllGather");
   SYM(Send, "ncclSend");
   SYM(Recv, "ncclRecv");
   SYM(GroupStart, "ncclGroupStart");
@@ -99,6 +104,7 @@ struct LocalGroup {
   std::vector<fsgpu_ctx*> ctx;
   std::vector<std::vector<const double*>> pub;  // pointers published by each rank for the current op
   std::vector<std::vector<double>> host;        // reduction staging
+  std::vector<char*> box;                       // FSGPU_HALO=p2p: every rank's mailbox
   int members = 0;
 
   // generation barrier with a timeout, so a failed rank cannot hang the others for ever
@@ -124,6 +130,100 @@ struct LocalGroup {
     return 0;
   }
 };
+// ---- direct halo exchange through peer-mapped mailboxes (FSGPU_HALO=p2p) ---------------------------
+// Every rank owns one device allocation, its MAILBOX, that its two neighbours map (cudaIpc between
+// processes, plain pointers inside one process):
+//   byte 0   : flag[0]  last epoch whose rows from rank - 1 are complete       (own 128-byte line)
+//   byte 128 : flag[1]  ... from rank + 1
+//   byte 192 : arrive counter of the local exchange kernel
+//   byte 256 : 4 slots of `cap` doubles: (side 0 | side 1) x (epoch parity 0 | 1)
+// One exchange = ONE kernel per rank on the context's stream: (A) store my boundary rows straight
+// into the neighbours' slots over NVLink, fence, the last CTA to arrive raises the neighbours' flags
+// to the epoch number; (B) wait for my own flags to reach the epoch, copy my slots into my halo rows.
+// No host round trip, no NCCL launch.  Two slots per side are enough: a rank can only start epoch
+// e + 2 after finishing e + 1, which needed the neighbour's flag e + 1, which the neighbour raises
+// after its epoch-e kernel (including the unpacking of slot e & 1) has completed in stream order.
+// The waits are bounded (a peer that never arrives sets *err instead of hanging the GPU).
+struct HaloP2PArgs {
+  double* ptr[4];
+  int n, h;
+  int64_t pitch, i0, i1;
+  char *mine, *up, *dn;  // mailbox bases: mine, rank - 1's, rank + 1's (null at the ends of the chain)
+  size_t cap;            // doubles per slot
+  unsigned long long e;  // epoch, counts exchanges from 1
+  int* err;
+};
+__device__ __forceinline__ double* p2p_slot(char* base, int side, int par, size_t cap) {
+  return reinterpret_cast<double*>(base + 256) + (size_t)(side * 2 + par) * cap;
+}
+__device__ __forceinline__ volatile unsigned long long* p2p_flag(char* base, int side) {
+  return reinterpret_cast<volatile unsigned long long*>(base + 128 * side);
+}
+constexpr int P2P_CTAS = 8, P2P_THREADS = 512;
+
+__global__ void __launch_bounds__(P2P_THREADS)
+k_halo_p2p(const HaloP2PArgs a) {
+  if (*(volatile int*)a.err) return;  // an earlier exchange timed out: fail fast, the host reports it
+  const size_t cnt2 = (size_t)a.h * (size_t)a.pitch / 2;  // double2 per array and direction
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
+  const int par = (int)(a.e & 1ull);
+  // (A) my first h rows go to the lower halo of rank - 1 (its side 1), my last h rows to the upper
+  // halo of rank + 1 (its side 0)
+  for (int k = 0; k < a.n; ++k) {
+    if (a.up) {
+      const double2* src = reinterpret_cast<const double2*>(a.ptr[k] + (a.i0 + FS_RO) * a.pitch);
+      double2* dst = reinterpret_cast<double2*>(p2p_slot(a.up, 1, par, a.cap)) + (size_t)k * cnt2;
+      for (size_t t = tid; t < cnt2; t += nth) dst[t] = src[t];
+    }
+    if (a.dn) {
+      const double2* src = reinterpret_cast<const double2*>(a.ptr[k] + (a.i1 - a.h + FS_RO) * a.pitch);
+      double2* dst = reinterpret_cast<double2*>(p2p_slot(a.dn, 0, par, a.cap)) + (size_t)k * cnt2;
+      for (size_t t = tid; t < cnt2; t += nth) dst[t] = src[t];
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int* arrive = reinterpret_cast<unsigned int*>(a.mine + 192);
+    if (atomicAdd(arrive, 1u) == gridDim.x - 1) {  // every CTA's rows are out
+      *arrive = 0;
+      __threadfence_system();
+      if (a.up) *p2p_flag(a.up, 1) = a.e;
+      if (a.dn) *p2p_flag(a.dn, 0) = a.e;
+    }
+    // (B) wait for the neighbours' rows of this epoch
+    const long long t0 = clock64();
+    bool ok = true;
+    while (ok && ((a.up && *p2p_flag(a.mine, 0) < a.e) || (a.dn && *p2p_flag(a.mine, 1) < a.e))) {
+      if (clock64() - t0 > 4000000000ll) ok = false;  // ~2 s
+    }
+    if (!ok) *a.err = 1;
+    __threadfence_system();
+  }
+  __syncthreads();
+  for (int k = 0; k < a.n; ++k) {
+    if (a.up) {
+      const double2* src = reinterpret_cast<const double2*>(p2p_slot(a.mine, 0, par, a.cap)) + (size_t)k * cnt2;
+      double2* dst = reinterpret_cast<double2*>(a.ptr[k] + (a.i0 - a.h + FS_RO) * a.pitch);
+      for (size_t t = tid; t < cnt2; t += nth) dst[t] = __ldcg(src + t);
+    }
+    if (a.dn) {
+      const double2* src = reinterpret_cast<const double2*>(p2p_slot(a.mine, 1, par, a.cap)) + (size_t)k * cnt2;
+      double2* dst = reinterpret_cast<double2*>(a.ptr[k] + (a.i1 + FS_RO) * a.pitch);
+      for (size_t t = tid; t < cnt2; t += nth) dst[t] = __ldcg(src + t);
+    }
+  }
+}
+
+struct P2PBox {
+  bool on = false;
+  char* base = nullptr;               // my mailbox
+  size_t cap = 0;                     // doubles per slot
+  unsigned long long epoch = 0;
+  char* nb[2] = {nullptr, nullptr};   // rank - 1's and rank + 1's mailbox, mapped here
+  bool ipc[2] = {false, false};       // mapped with cudaIpcOpenMemHandle (to be closed)
+  int *h_err = nullptr, *d_err = nullptr;  // mapped pinned flag the kernel raises on a timeout
+};
 std::map<std::string, std::shared_ptr<LocalGroup>> g_groups;
 std::mutex g_groups_mu;
 
@@ -134,6 +234,7 @@ struct Comm {
   ncclComm_t nccl = nullptr;
   std::shared_ptr<LocalGroup> grp;
   std::string key;
+  P2PBox p2p;
 };
 
 #define LOCAL_BARRIER(cm)                                                    \
@@ -143,6 +244,78 @@ struct Comm {
       return 1;                                                              \
     }                                                                        \
   } while (0)
+
+// Mailbox setup; collective.  Returns 0 also when the direct path cannot be used (it then stays
+// off on EVERY rank: the decision is all-reduced) -- the NCCL / staged exchange keeps working.
+static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
+  P2PBox& b = cm->p2p;
+  const char* env = getenv("FSGPU_HALO");
+  if (!env || strcmp(env, "p2p") != 0) return 0;
+  b.cap = (size_t)((8 * c->g.pitch + 15) / 16 * 16);  // the widest exchange: 4 arrays x FS_RO rows
+  const size_t bytes = 256 + 4 * b.cap * sizeof(double);
+  int ok = 1;
+  if (cudaMalloc(&b.base, bytes) != cudaSuccess) { b.base = nullptr; ok = 0; }
+  if (ok && cudaMemsetAsync(b.base, 0, bytes, c->stream) != cudaSuccess) ok = 0;
+  if (ok && cudaHostAlloc(&b.h_err, sizeof(int), cudaHostAllocMapped) != cudaSuccess) { b.h_err = nullptr; ok = 0; }
+  if (ok) {
+    *b.h_err = 0;
+    if (cudaHostGetDevicePointer(&b.d_err, b.h_err, 0) != cudaSuccess) ok = 0;
+  }
+  const int peer[2] = {c->rank - 1, c->rank + 1 < c->nranks ? c->rank + 1 : -1};
+  if (cm->transport == FSGPU_TRANSPORT_NCCL) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof(mine));
+    if (ok && cudaIpcGetMemHandle(&mine, b.base) != cudaSuccess) ok = 0;
+    char* d_all = nullptr;  // every rank takes part in the collectives below, whatever its `ok`
+    FS_CUDA(cudaMalloc(&d_all, 64 * (size_t)c->nranks + sizeof(int)));
+    FS_CUDA(cudaMemcpyAsync(d_all + 64 * c->rank, &mine, 64, cudaMemcpyHostToDevice, c->stream));
+    FS_NCCL(g_nccl.AllGather(d_all + 64 * c->rank, d_all, 64, ncclChar, cm->nccl, c->stream));
+    std::vector<cudaIpcMemHandle_t> all((size_t)c->nranks);
+    FS_CUDA(cudaMemcpyAsync(all.data(), d_all, 64 * (size_t)c->nranks, cudaMemcpyDeviceToHost, c->stream));
+    FS_CUDA(cudaStreamSynchronize(c->stream));
+    for (int sd = 0; sd < 2 && ok; ++sd) {
+      if (peer[sd] < 0) continue;
+      void* q = nullptr;
+      if (cudaIpcOpenMemHandle(&q, all[(size_t)peer[sd]], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = 0;
+      else { b.nb[sd] = (char*)q; b.ipc[sd] = true; }
+    }
+    cudaGetLastError();  // a failed attempt must not poison later launch checks
+    int* d_ok = reinterpret_cast<int*>(d_all + 64 * (size_t)c->nranks);
+    FS_CUDA(cudaMemcpyAsync(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    FS_NCCL(g_nccl.AllReduce(d_ok, d_ok, 1, ncclInt, ncclMin, cm->nccl, c->stream));
+    FS_CUDA(cudaMemcpyAsync(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    FS_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(d_all);
+  } else {
+    LocalGroup& g = *cm->grp;
+    {
+      std::lock_guard<std::mutex> lk(g.mu);
+      if (g.box.size() != (size_t)c->nranks) g.box.assign((size_t)c->nranks, nullptr);
+      g.box[(size_t)c->rank] = ok ? b.base : nullptr;
+    }
+    FS_CUDA(cudaStreamSynchronize(c->stream));
+    LOCAL_BARRIER(cm);
+    for (int r = 0; r < c->nranks; ++r)
+      if (!g.box[(size_t)r]) ok = 0;  // same verdict on every rank
+    for (int sd = 0; sd < 2; ++sd)
+      if (peer[sd] >= 0) b.nb[sd] = g.box[(size_t)peer[sd]];
+    LOCAL_BARRIER(cm);
+  }
+  b.on = ok != 0;
+  if (!b.on && c->rank == 0)
+    fprintf(stderr, "[fsgpu] FSGPU_HALO=p2p: peer mailboxes unavailable, halo exchange stays on the default transport\n");
+  return 0;
+}
+
+static void p2p_teardown(Comm* cm) {
+  P2PBox& b = cm->p2p;
+  for (int sd = 0; sd < 2; ++sd)
+    if (b.ipc[sd] && b.nb[sd]) cudaIpcCloseMemHandle(b.nb[sd]);
+  if (b.base) cudaFree(b.base);
+  if (b.h_err) cudaFreeHost(b.h_err);
+  b = P2PBox();
+}
 
 int comm_create(fsgpu_ctx* c, int rank, int nranks, const void* id128, int transport) {
   c->rank = rank;
@@ -187,12 +360,26 @@ int comm_create(fsgpu_ctx* c, int rank, int nranks, const void* id128, int trans
     return 1;
   }
   c->comm = cm;
+  if (p2p_setup(c, cm)) {
+    comm_destroy(c);
+    return 1;
+  }
   return 0;
+}
+
+// non-zero once a direct halo exchange has timed out waiting for a neighbour
+int comm_failed(fsgpu_ctx* c) {
+  Comm* cm = c->comm;
+  if (!cm || !cm->p2p.on || !*(volatile int*)cm->p2p.h_err) return 0;
+  fs_set_error("direct halo exchange: rank %d timed out waiting for a neighbour's rows", c->rank);
+  return 1;
 }
 
 void comm_destroy(fsgpu_ctx* c) {
   Comm* cm = c->comm;
   if (!cm) return;
+  cudaStreamSynchronize(c->stream);
+  p2p_teardown(cm);
   if (cm->transport == FSGPU_TRANSPORT_NCCL) {
     if (cm->nccl) g_nccl.CommDestroy(cm->nccl);
   } else {
@@ -219,6 +406,20 @@ int comm_halo(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i
   const size_t cnt = (size_t)h * (size_t)pitch;
   auto row = [&](double* p, int64_t i) { return p + (i + FS_RO) * pitch; };
   const bool up = c->rank > 0, dn = c->rank + 1 < c->nranks;
+  if (cm->p2p.on && n <= 4 && (size_t)n * cnt <= cm->p2p.cap) {  // same decision on every rank
+    HaloP2PArgs a;
+    for (int k = 0; k < 4; ++k) a.ptr[k] = k < n ? ptrs[k] : nullptr;
+    a.n = n; a.h = h; a.pitch = pitch; a.i0 = i0; a.i1 = i1;
+    a.mine = cm->p2p.base;
+    a.up = up ? cm->p2p.nb[0] : nullptr;
+    a.dn = dn ? cm->p2p.nb[1] : nullptr;
+    a.cap = cm->p2p.cap;
+    a.e = ++cm->p2p.epoch;
+    a.err = cm->p2p.d_err;
+    k_halo_p2p<<<P2P_CTAS, P2P_THREADS, 0, c->stream>>>(a);
+    FS_LAUNCHED();
+    return 0;
+  }
   if (cm->transport == FSGPU_TRANSPORT_NCCL) {
     FS_NCCL(g_nccl.GroupStart());
     for (int k = 0; k < n; ++k) {

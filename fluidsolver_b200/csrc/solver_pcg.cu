@@ -192,6 +192,7 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   FS_CUDA(cudaStreamSynchronize(st));
   const PcgScal& h = s->h_scal[0];
   g_prof_tag = 0;
+  if (comm_failed(c)) return 1;
   // (the p update of the iteration that met the convergence test is empty as well)
   if (g_prof_mask) fs_prof_drop_after(prof0, h.done == PCG_ZERO_RHS ? 0 : h.iter, h.done ? PROF_PUPD : -1);
   if (h.done == PCG_ZERO_RHS) {

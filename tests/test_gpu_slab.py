@@ -189,3 +189,30 @@ def test_slab_timesteps(F, oracle, name, kind, n, nsub, flags, R):
     floor = kind in ("tgv", "channel")
     assert ev <= (1e-7 if floor else 1e-10)
     assert ep <= (1e-5 if floor else 1e-8)
+
+
+@pytest.mark.skipif(os.environ.get("FSGPU_TEST_P2P") != "1",
+                    reason="direct (mailbox) halo exchange is opt-in until it has run on a GPU box: FSGPU_TEST_P2P=1")
+@pytest.mark.parametrize("R", [2, 3])
+def test_slab_timesteps_p2p_halo(F, oracle, R, monkeypatch):
+    """FSGPU_HALO=p2p: halo rows travel through peer-mapped mailboxes (one kernel per exchange) instead
+    of the staged copies; results must equal the default transport bit for bit"""
+    st, bc = cavity_state(oracle, 96, 96), cavity_bc()
+    oracle.apply_velocity_bconds(st, bc)
+
+    def body(fs, r):
+        ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
+        ps.set_pressure_operator()
+        hist = []
+        for _ in range(2):
+            dt = fs.adjust_dt(0.9, 0.1)
+            hist.append((dt, fs.step(ps, dt, 5)[1]))
+        ps.close()
+        return hist
+
+    b, rb = run_ranks(F, st, bc, R, body, fields=("U", "V", "P"))
+    monkeypatch.setenv("FSGPU_HALO", "p2p")
+    a, ra = run_ranks(F, st, bc, R, body, fields=("U", "V", "P"))
+    assert ra == rb
+    for n in ("U", "V", "P"):
+        assert np.array_equal(a[n], b[n]), n
