@@ -1,7 +1,7 @@
 """Per-operation cost of the slab transport, for diagnosing multi-GPU scaling (run under torchrun):
 
   NCCL_DEBUG=INFO python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-      --master-port 29555 scripts/comm_probe.py [grid] 2> nccl.log      (grep 'via P2P\|via SHM\|NET/' nccl.log)
+      --master-port 29555 scripts/comm_probe.py [grid] 2> nccl.log      (grep -E 'via P2P|via SHM|NET/' nccl.log)
   FSGPU_HALO=p2p ... the same with the mailbox halo exchange
 
 Prints, on rank 0: us per halo exchange (2 rows of one field, stream-ordered, no host sync in the loop),
