@@ -9,6 +9,8 @@
 //                          no host synchronisation.  libnccl.so.2 is dlopen'ed on first use (in a
 //                          torch process this resolves to the copy torch already loaded), so the
 //                          library has no link-time dependency on NCCL.
+//                          FSGPU_HALO=p2p (opt-in): halo rows and scalar reductions bypass NCCL and
+//                          go through peer-mapped mailboxes, one kernel per exchange (see below).
 //   FSGPU_TRANSPORT_LOCAL  all ranks are contexts of ONE process, each driven by its own host
 //                          thread (any mix of devices, typically all on one GPU).  Copies are
 //                          cudaMemcpyAsync between the contexts, ordered by host barriers.  It is
@@ -215,13 +217,70 @@ k_halo_p2p(const HaloP2PArgs a) {
   }
 }
 
+// Scalar all-reduce (n <= P2P_RED_MAX doubles) through the same mailboxes: every rank stores its
+// values into slot [parity][its rank] of EVERY rank's reduce area and raises that rank's flag for it;
+// then it waits for all flags of this epoch and folds the slots in rank order -- the same order on
+// every rank, so the result is bitwise identical everywhere (what the PCG control flow relies on).
+// Area layout at mailbox offset red_off: flag[P2P_MAX_RANKS] (u64), then
+// values[2][P2P_MAX_RANKS][P2P_RED_MAX].
+constexpr int P2P_MAX_RANKS = 16, P2P_RED_MAX = 16;
+struct RedP2PArgs {
+  char* peer[P2P_MAX_RANKS];
+  double* dev;
+  int n, rank, nranks, op;
+  size_t red_off;
+  unsigned long long e;
+  int* err;
+};
+__device__ __forceinline__ volatile unsigned long long* red_flag(char* base, size_t off, int src) {
+  return reinterpret_cast<volatile unsigned long long*>(base + off) + src;
+}
+__device__ __forceinline__ double* red_vals(char* base, size_t off, int par, int src) {
+  return reinterpret_cast<double*>(base + off + P2P_MAX_RANKS * sizeof(unsigned long long)) +
+         ((size_t)par * P2P_MAX_RANKS + src) * P2P_RED_MAX;
+}
+__global__ void __launch_bounds__(P2P_MAX_RANKS * P2P_RED_MAX)
+k_allreduce_p2p(const RedP2PArgs a) {
+  if (*(volatile int*)a.err) return;
+  const int t = threadIdx.x, par = (int)(a.e & 1ull);
+  char* mine = a.peer[a.rank];
+  if (t < a.nranks * a.n) {
+    const int pr = t / a.n, q = t - pr * a.n;
+    red_vals(a.peer[pr], a.red_off, par, a.rank)[q] = a.dev[q];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (t < a.nranks) {
+    __threadfence_system();
+    *red_flag(a.peer[t], a.red_off, a.rank) = a.e;
+    const long long t0 = clock64();
+    bool ok = true;
+    while (ok && *red_flag(mine, a.red_off, t) < a.e)
+      if (clock64() - t0 > 4000000000ll) ok = false;  // ~2 s
+    if (!ok) *a.err = 1;
+    __threadfence_system();
+  }
+  __syncthreads();
+  if (t < a.n) {
+    double acc = __ldcg(red_vals(mine, a.red_off, par, 0) + t);
+    for (int r = 1; r < a.nranks; ++r) {
+      const double v = __ldcg(red_vals(mine, a.red_off, par, r) + t);
+      acc = a.op == COMM_MAX ? (acc > v ? acc : v) : acc + v;
+    }
+    a.dev[t] = acc;
+  }
+}
+
 struct P2PBox {
   bool on = false;
   char* base = nullptr;               // my mailbox
   size_t cap = 0;                     // doubles per slot
   unsigned long long epoch = 0;
   char* nb[2] = {nullptr, nullptr};   // rank - 1's and rank + 1's mailbox, mapped here
-  bool ipc[2] = {false, false};       // mapped with cudaIpcOpenMemHandle (to be closed)
+  std::vector<char*> peer;            // every rank's mailbox (peer[rank] == base)
+  std::vector<char> ipc;              // mapped with cudaIpcOpenMemHandle (to be closed)
+  size_t red_off = 0;                 // byte offset of the scalar all-reduce area
+  unsigned long long red_epoch = 0;
   int *h_err = nullptr, *d_err = nullptr;  // mapped pinned flag the kernel raises on a timeout
 };
 std::map<std::string, std::shared_ptr<LocalGroup>> g_groups;
@@ -252,8 +311,12 @@ static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
   const char* env = getenv("FSGPU_HALO");
   if (!env || strcmp(env, "p2p") != 0) return 0;
   b.cap = (size_t)((8 * c->g.pitch + 15) / 16 * 16);  // the widest exchange: 4 arrays x FS_RO rows
-  const size_t bytes = 256 + 4 * b.cap * sizeof(double);
-  int ok = 1;
+  b.red_off = 256 + 4 * b.cap * sizeof(double);
+  const size_t bytes = b.red_off + P2P_MAX_RANKS * sizeof(unsigned long long) +
+                       2 * (size_t)P2P_MAX_RANKS * P2P_RED_MAX * sizeof(double);
+  int ok = c->nranks <= P2P_MAX_RANKS ? 1 : 0;
+  b.peer.assign((size_t)c->nranks, nullptr);
+  b.ipc.assign((size_t)c->nranks, 0);
   if (cudaMalloc(&b.base, bytes) != cudaSuccess) { b.base = nullptr; ok = 0; }
   if (ok && cudaMemsetAsync(b.base, 0, bytes, c->stream) != cudaSuccess) ok = 0;
   if (ok && cudaHostAlloc(&b.h_err, sizeof(int), cudaHostAllocMapped) != cudaSuccess) { b.h_err = nullptr; ok = 0; }
@@ -274,12 +337,14 @@ static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
     std::vector<cudaIpcMemHandle_t> all((size_t)c->nranks);
     FS_CUDA(cudaMemcpyAsync(all.data(), d_all, 64 * (size_t)c->nranks, cudaMemcpyDeviceToHost, c->stream));
     FS_CUDA(cudaStreamSynchronize(c->stream));
-    for (int sd = 0; sd < 2 && ok; ++sd) {
-      if (peer[sd] < 0) continue;
+    for (int r = 0; r < c->nranks && ok; ++r) {  // every rank: the scalar all-reduce is all-to-all
+      if (r == c->rank) { b.peer[(size_t)r] = b.base; continue; }
       void* q = nullptr;
-      if (cudaIpcOpenMemHandle(&q, all[(size_t)peer[sd]], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = 0;
-      else { b.nb[sd] = (char*)q; b.ipc[sd] = true; }
+      if (cudaIpcOpenMemHandle(&q, all[(size_t)r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = 0;
+      else { b.peer[(size_t)r] = (char*)q; b.ipc[(size_t)r] = 1; }
     }
+    for (int sd = 0; sd < 2; ++sd)
+      if (peer[sd] >= 0) b.nb[sd] = b.peer[(size_t)peer[sd]];
     cudaGetLastError();  // a failed attempt must not poison later launch checks
     int* d_ok = reinterpret_cast<int*>(d_all + 64 * (size_t)c->nranks);
     FS_CUDA(cudaMemcpyAsync(d_ok, &ok, sizeof(int), cudaMemcpyHostToDevice, c->stream));
@@ -298,6 +363,7 @@ static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
     LOCAL_BARRIER(cm);
     for (int r = 0; r < c->nranks; ++r)
       if (!g.box[(size_t)r]) ok = 0;  // same verdict on every rank
+    for (int r = 0; r < c->nranks; ++r) b.peer[(size_t)r] = g.box[(size_t)r];
     for (int sd = 0; sd < 2; ++sd)
       if (peer[sd] >= 0) b.nb[sd] = g.box[(size_t)peer[sd]];
     LOCAL_BARRIER(cm);
@@ -310,8 +376,8 @@ static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
 
 static void p2p_teardown(Comm* cm) {
   P2PBox& b = cm->p2p;
-  for (int sd = 0; sd < 2; ++sd)
-    if (b.ipc[sd] && b.nb[sd]) cudaIpcCloseMemHandle(b.nb[sd]);
+  for (size_t r = 0; r < b.peer.size(); ++r)
+    if (b.ipc[r] && b.peer[r]) cudaIpcCloseMemHandle(b.peer[r]);
   if (b.base) cudaFree(b.base);
   if (b.h_err) cudaFreeHost(b.h_err);
   b = P2PBox();
@@ -460,6 +526,17 @@ int comm_halo(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i
 int comm_allreduce(fsgpu_ctx* c, double* dev, int64_t n, int op) {
   Comm* cm = c->comm;
   if (!cm || c->nranks <= 1 || n <= 0) return 0;
+  if (cm->p2p.on && n <= P2P_RED_MAX) {  // scalars: one kernel, rank-ordered fold
+    RedP2PArgs a;
+    for (int r = 0; r < P2P_MAX_RANKS; ++r) a.peer[r] = r < c->nranks ? cm->p2p.peer[(size_t)r] : nullptr;
+    a.dev = dev; a.n = (int)n; a.rank = c->rank; a.nranks = c->nranks; a.op = op;
+    a.red_off = cm->p2p.red_off;
+    a.e = ++cm->p2p.red_epoch;
+    a.err = cm->p2p.d_err;
+    k_allreduce_p2p<<<1, P2P_MAX_RANKS * P2P_RED_MAX, 0, c->stream>>>(a);
+    FS_LAUNCHED();
+    return 0;
+  }
   if (cm->transport == FSGPU_TRANSPORT_NCCL) {
     FS_NCCL(g_nccl.AllReduce(dev, dev, (size_t)n, ncclDouble, op == COMM_MAX ? ncclMax : ncclSum,
                              cm->nccl, c->stream));
