@@ -43,6 +43,34 @@ def channel_bc():
                   v_val=(0.0,) * 4)
 
 
+def couette_bc():
+    """test/Couette.cpp:45-50: Neumann left / right, no-slip bottom, lid U = 1 on top."""
+    return BConds(kind=(NEUMANN, NEUMANN, DIRICHLET, DIRICHLET), u_val=(0.0, 0.0, 0.0, 1.0), v_val=(0.0,) * 4)
+
+
+def couette_state(oracle, seed=None):
+    """test/Couette.cpp:21-41: 210 x 21 cells on 10 x 1, rho = 0.9, mu = 0.1, zero initial flow
+    (seed: a small random velocity instead, so that the pressure solves have work to do)"""
+    nx, ny = 210, 21
+    st = State(nx, ny, 10.0 / nx, 1.0 / ny, rho_gas=0.9, rho_liquid=0.9, visc_gas=0.1, visc_liquid=0.1)
+    oracle.calc_rho_visc_const(st)
+    if seed is not None:
+        rng = np.random.default_rng(seed)
+        st.a["U"][:] = 0.1 * rng.uniform(-1, 1, st.a["U"].shape)
+        st.a["V"][:] = 0.1 * rng.uniform(-1, 1, st.a["V"].shape)
+    return st
+
+
+def couette_l1_errors(U, nx, ny):
+    """test/Couette.cpp:226-240: trapezoid L1 error of U against U_top y at x = NX/4, NX/2, 3NX/4"""
+    ym = (np.arange(-1, ny + 1) + 0.5) / ny
+    out = []
+    for i in (nx // 4, nx // 2, 3 * nx // 4):
+        d = np.abs(U[i + 1, :] - ym)
+        out.append(float(np.sum((ym[1:] - ym[:-1]) * 0.5 * (d[1:] + d[:-1]))))
+    return out
+
+
 def periodic_bc():
     return BConds(kind=(PERIODIC,) * 4)
 

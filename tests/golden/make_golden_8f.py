@@ -15,7 +15,8 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
 
-from cases import cavity_bc, cavity_state, ib_inputs, random_state, twophase_inputs  # noqa: E402
+from cases import (cavity_bc, cavity_state, couette_bc, couette_state, ib_inputs, random_state,  # noqa: E402
+                   twophase_inputs)
 from oracle_lib import Oracle, Ref  # noqa: E402
 
 o = Oracle()  # input construction only
@@ -80,7 +81,34 @@ def run_twophase(name, nsub=3, nsteps=2):
     print("run", name, "its", its, "dt", dts, "max|U|", np.abs(s2.U).max())
 
 
+def run_couette(name, nsub=2, nsteps=3):
+    """test/Couette.cpp boundary conditions (Neumann left/right) on a seeded velocity field: three
+    timesteps at tight tolerance"""
+    st, bc = couette_state(o, seed=5), couette_bc()
+    o.apply_velocity_bconds(st, bc)
+    r = Ref(st.nx, st.ny)
+    r.load(st)
+    r.set_bconds(bc)
+    r.solver_create(1e-13, 500)
+    r.solver_set_operator()
+    dts, its = [], []
+    for _ in range(nsteps):
+        dt = r.adjust_dt(0.9, 0.1)
+        it, res = r.step(dt, nsub)
+        dts.append(dt)
+        its.append(it)
+    s2 = st.copy()
+    r.store(s2)
+    np.savez_compressed(os.path.join(HERE, f"run_{name}.npz"), dts=np.array(dts), its=np.array(its), U=s2.U,
+                        V=s2.V, p=s2.a["p"])
+    print("run", name, "its", its, "dt", dts)
+
+
 if __name__ == "__main__":
+    if "couette" in sys.argv:
+        run_couette("couette210x21")
+        sys.exit(0)
     ops8f("random48x20", random_state(48, 20, seed=48020), True)
     ops8f("drop64", cavity_state(o, 64, 64, drop=True, seed=3), False)
     run_twophase("twophase128")
+    run_couette("couette210x21")
