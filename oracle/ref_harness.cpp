@@ -11,7 +11,9 @@
 #include <chrono>
 #include <cstdint>
 #include <cstdio>
+#include <cmath>
 #include <cstring>
+#include <vector>
 #include <memory>
 
 #include <omp.h>
@@ -27,6 +29,28 @@
 namespace {
 
 using Float = double;
+
+// The reference's Dirichlet condition takes plain function pointers `Float (*)(Float coord, Float t)`
+// (src/BoundaryConditions.hpp:15-17).  The harness receives per-point tables (fso_bconds::u_prof /
+// v_prof, evaluated by the caller at the ghost-inclusive coordinates of the side), so each
+// (side, component) gets one static function that looks its table up by coordinate.
+struct ProfTable {
+  const double* v = nullptr;
+  double c0 = 0.0, h = 1.0;  // coordinate of entry 0 and spacing
+  long n = 0;
+};
+ProfTable g_prof[4][2];
+template <int SIDE, int COMP>
+Float prof_fn(Float coord, Float /*t*/) {
+  const ProfTable& p = g_prof[SIDE][COMP];
+  long k = std::lround((coord - p.c0) / p.h);
+  if (k < 0) k = 0;
+  if (k >= p.n) k = p.n - 1;
+  return p.v[k];
+}
+using ProfFn = Float (*)(Float, Float);
+constexpr ProfFn PROF_FNS[4][2] = {{&prof_fn<0, 0>, &prof_fn<0, 1>}, {&prof_fn<1, 0>, &prof_fn<1, 1>},
+                                   {&prof_fn<2, 0>, &prof_fn<2, 1>}, {&prof_fn<3, 0>, &prof_fn<3, 1>}};
 
 struct SessionBase {
   virtual ~SessionBase()                                                       = default;
@@ -101,9 +125,32 @@ struct Session final : SessionBase {
     cp_out(fs.curr.rho_u_stag, out->rho_u); cp_out(fs.curr.rho_v_stag, out->rho_v);
     cp_out(fs.curr.U, out->U); cp_out(fs.curr.V, out->V);
   }
-  static BCond_t<Float> make_bc(const fso_bconds* bc, int s) {
+  // copies of the caller's profile tables (left/right: U at ym(j), V at y(j); bottom/top: U at x(i),
+  // V at xm(i); all ghost inclusive) and the (side, component) slots they are published in
+  std::vector<double> prof_[4][2];
+  void publish_profiles() {
+    for (int s = 0; s < 4; ++s)
+      for (int q = 0; q < 2; ++q) {
+        const bool lr = s < 2;
+        const double h = lr ? fs.dy : fs.dx;
+        // U on left/right and V on bottom/top live at cell centres of the side, the others at faces
+        const bool centred = lr ? (q == 0) : (q == 1);
+        g_prof[s][q] = ProfTable{prof_[s][q].empty() ? nullptr : prof_[s][q].data(),
+                                 centred ? -0.5 * h : -h, h, static_cast<long>(prof_[s][q].size())};
+      }
+  }
+  BCond_t<Float> make_bc(const fso_bconds* bc, int s) {
+    const bool lr = s < 2;
+    const size_t nu = static_cast<size_t>(lr ? NY + 2 : NX + 3), nv = static_cast<size_t>(lr ? NY + 3 : NX + 2);
+    prof_[s][0].clear();
+    prof_[s][1].clear();
+    if (bc->kind[s] == FSO_BC_DIRICHLET) {
+      Dirichlet<Float> d{.U = bc->u_val[s], .V = bc->v_val[s]};
+      if (bc->u_prof[s]) { prof_[s][0].assign(bc->u_prof[s], bc->u_prof[s] + nu); d.U = PROF_FNS[s][0]; }
+      if (bc->v_prof[s]) { prof_[s][1].assign(bc->v_prof[s], bc->v_prof[s] + nv); d.V = PROF_FNS[s][1]; }
+      return d;
+    }
     switch (bc->kind[s]) {
-      case FSO_BC_DIRICHLET: return Dirichlet<Float>{.U = bc->u_val[s], .V = bc->v_val[s]};
       case FSO_BC_NEUMANN:   return Neumann{.clipped = bc->clipped[s] != 0};
       case FSO_BC_PERIODIC:  return Periodic{};
       default:               return Symmetry{};
@@ -111,6 +158,7 @@ struct Session final : SessionBase {
   }
   void set_bconds(const fso_bconds* bc) override {
     bconds = FlowBConds<Float>{make_bc(bc, 0), make_bc(bc, 1), make_bc(bc, 2), make_bc(bc, 3)};
+    publish_profiles();
   }
   double adjust_dt(double cfl, double dt_max) override { return ::adjust_dt(fs, cfl, dt_max); }
   void save_old_state() override { ::save_old_state(fs.curr, fs.old); }
@@ -126,7 +174,10 @@ struct Session final : SessionBase {
     cp_in(dU, iU); cp_in(dV, iV);
     ::update_velocity(dU, dV, dt, fs);
   }
-  void apply_bconds() override { ::apply_velocity_bconds(fs, bconds, 0.0); }
+  void apply_bconds() override {
+    publish_profiles();
+    ::apply_velocity_bconds(fs, bconds, 0.0);
+  }
   void calc_divergence(double* o) override {
     ::calc_divergence(fs.curr.U, fs.curr.V, fs.dx, fs.dy, div);
     cp_out(div, o);
@@ -221,6 +272,7 @@ struct Session final : SessionBase {
   // phase_secs (optional, 4 entries): momentum(mid-time+dmomdt+update+bc), div+rhs, solve, correct.
   int step(const fso_step_opts* o, double dt, double* res, double* phase) override {
     using clk = std::chrono::steady_clock;
+    publish_profiles();
     auto secs = [](clk::time_point a, clk::time_point b) {
       return std::chrono::duration<double>(b - a).count();
     };

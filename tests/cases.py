@@ -71,6 +71,23 @@ def couette_l1_errors(U, nx, ny):
     return out
 
 
+def profile_bcs(nx, ny, seed=5):
+    """two FlowBConds with function-pointer Dirichlet sides (src/BoundaryConditions.hpp:15-17) given
+    as per-point tables: every side and component, and a mix with constants / Neumann"""
+    rng = np.random.default_rng(seed)
+    lr_u, lr_v, bt_u, bt_v = ny + 2, ny + 3, nx + 3, nx + 2
+    full = BConds(kind=(DIRICHLET,) * 4, u_val=(0.0,) * 4, v_val=(0.0,) * 4,
+                  u_prof=(rng.uniform(-1, 1, lr_u), rng.uniform(-1, 1, lr_u), rng.uniform(-1, 1, bt_u),
+                          rng.uniform(-1, 1, bt_u)),
+                  v_prof=(rng.uniform(-1, 1, lr_v), rng.uniform(-1, 1, lr_v), rng.uniform(-1, 1, bt_v),
+                          rng.uniform(-1, 1, bt_v)))
+    mixed = BConds(kind=(DIRICHLET, NEUMANN, DIRICHLET, DIRICHLET), u_val=(0.0, 0.0, 0.3, 1.0),
+                   v_val=(0.1, 0.0, 0.0, -0.2),
+                   u_prof=(rng.uniform(0, 1, lr_u), None, None, rng.uniform(0, 1, bt_u)),
+                   v_prof=(None, None, rng.uniform(-1, 1, bt_v), None))
+    return {"full": full, "mixed": mixed}
+
+
 def periodic_bc():
     return BConds(kind=(PERIODIC,) * 4)
 

@@ -15,8 +15,8 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
 
-from cases import (cavity_bc, cavity_state, couette_bc, couette_state, ib_inputs, random_state,  # noqa: E402
-                   twophase_inputs)
+from cases import (cavity_bc, cavity_state, couette_bc, couette_state, ib_inputs, profile_bcs,  # noqa: E402
+                   random_state, twophase_inputs)
 from oracle_lib import Oracle, Ref  # noqa: E402
 
 o = Oracle()  # input construction only
@@ -104,7 +104,26 @@ def run_couette(name, nsub=2, nsteps=3):
     print("run", name, "its", its, "dt", dts)
 
 
+def bc_profiles(name="bc_profiles48x20"):
+    """apply_velocity_bconds with function-pointer Dirichlet sides (src/BoundaryConditions.hpp:15-88)"""
+    st = random_state(48, 20, seed=3)
+    out = {}
+    for key, bc in profile_bcs(48, 20).items():
+        r = Ref(st.nx, st.ny)
+        r.load(st)
+        r.set_bconds(bc)
+        r.apply_velocity_bconds()
+        s2 = st.copy()
+        r.store(s2)
+        out[f"{key}_U"], out[f"{key}_V"] = s2.U, s2.V
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
+    print(name, list(out))
+
+
 if __name__ == "__main__":
+    if "profiles" in sys.argv:
+        bc_profiles()
+        sys.exit(0)
     if "couette" in sys.argv:
         run_couette("couette210x21")
         sys.exit(0)
@@ -112,3 +131,4 @@ if __name__ == "__main__":
     ops8f("drop64", cavity_state(o, 64, 64, drop=True, seed=3), False)
     run_twophase("twophase128")
     run_couette("couette210x21")
+    bc_profiles()

@@ -72,3 +72,17 @@ def test_couette_bconds_timesteps(F, oracle):
         assert ev <= 1e-6 and ep <= 1e-4
     ps.close()
     fs.close()
+
+
+def test_dirichlet_profiles_vs_reference_golden(F):
+    """function-pointer Dirichlet sides (src/BoundaryConditions.hpp:15-88; the inlet of
+    test/CustomDirichletChannel.cpp) against the committed output of the unmodified reference"""
+    from cases import profile_bcs, random_state
+    g = np.load(os.path.join(GOLD, "bc_profiles48x20.npz"))
+    st = random_state(48, 20, seed=3)
+    for key, bc in profile_bcs(48, 20).items():
+        fs = to_gpu(F, st, bc)
+        fs.apply_velocity_bconds()
+        assert np.array_equal(fs.download("U"), g[f"{key}_U"]), key
+        assert np.array_equal(fs.download("V"), g[f"{key}_V"]), key
+        fs.close()
