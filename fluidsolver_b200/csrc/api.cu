@@ -362,14 +362,16 @@ int fsgpu_outflow_fix(fsgpu_ctx* c, double* mass_error) {
   return 0;
 }
 
-int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out) {
+static int abs_max_impl(fsgpu_ctx* c, int field, bool include_ghost, double* out) {
   FS_CHECK_CTX(c);
   FS_CHECK_FIELD(field);
-  if (fs_launch_absmax(c, field)) return 1;
+  if (fs_launch_absmax(c, field, include_ghost)) return 1;
   if (read_red(c, 0, 1)) return 1;
   *out = c->h_red[0];
   return 0;
 }
+int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out) { return abs_max_impl(c, field, false, out); }
+int fsgpu_abs_max_all(fsgpu_ctx* c, int field, double* out) { return abs_max_impl(c, field, true, out); }
 
 int fsgpu_calc_rho_visc_const(fsgpu_ctx* c) {
   FS_CHECK_CTX(c);

@@ -80,7 +80,7 @@ int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv);
 int fs_launch_shift_pressure(fsgpu_ctx* c);
 int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift);
 int fs_launch_cfl(fsgpu_ctx* c);               // 4 maxima -> red_out[0..3]
-int fs_launch_absmax(fsgpu_ctx* c, int field);  // -> red_out[0]
+int fs_launch_absmax(fsgpu_ctx* c, int field, bool include_ghost);  // -> red_out[0]
 int fs_launch_fill(fsgpu_ctx* c, int field, double v);
 int fs_launch_rho_visc_vof(fsgpu_ctx* c);
 int fs_launch_neumann(fsgpu_ctx* c, double* f, int64_t m, int64_t n);

@@ -136,15 +136,15 @@ k_cfl(const double* __restrict__ U, const double* __restrict__ V, const double* 
   }
 }
 
-__global__ void k_absmax(const double* __restrict__ f, int64_t n, double* part,
-                         unsigned int* ticket, double* out) {
+// max |f| over rows [r0, r1) x columns [b0, b0 + nb) (ghost-inclusive indices)
+__global__ void __launch_bounds__(BX* BY)
+k_absmax(const double* __restrict__ f, int64_t r0, int64_t r1, int64_t b0, int64_t nb, const Geom g,
+         double* part, unsigned int* ticket, double* out) {
   double v[1] = {0.0};
-  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n;
-       k += (int64_t)gridDim.x * blockDim.x)
-    v[0] = fmax(v[0], fabs(f[k]));
+  for_each_point(r0, r1, nb, [&](int64_t a, int64_t j) { v[0] = fmax(v[0], fabs(f[g.idx(a, b0 + j)])); });
   double tot[1];
   if (grid_reduce<ReduceMax, 1>(v, part, ticket, tot)) {
-    if (threadIdx.x == 0) out[0] = fmax(tot[0], 0.0);
+    if (threadIdx.x == 0 && threadIdx.y == 0) out[0] = fmax(tot[0], 0.0);
   }
 }
 
@@ -279,12 +279,19 @@ int fs_launch_cfl(fsgpu_ctx* c) {
   return comm_allreduce(c, c->red_out, 4, COMM_MAX);
 }
 
-int fs_launch_absmax(fsgpu_ctx* c, int field) {
-  const int64_t n    = c->g.count();
-  const unsigned nbl = (unsigned)std::min<int64_t>(cdiv(n, 256), 148 * 8);
+// abs_max<INCLUDE_GHOST>(field), src/Utility.hpp:44-88: the reference's default reduces over the
+// INTERIOR of the field (for_each_i), abs_max<true> over the whole ghost-inclusive extent
+int fs_launch_absmax(fsgpu_ctx* c, int field, bool include_ghost) {
+  const Geom& g = c->g;
+  int64_t m2, n2;
+  field_extent(g, field, &m2, &n2);
+  const int64_t lo = include_ghost ? 0 : 1;
+  const int64_t own_hi = g.last() ? m2 : g.a_hi;  // a U-like field's extra row belongs to the last rank
+  const int64_t r0 = std::max<int64_t>(lo, g.a_lo), r1 = std::min<int64_t>(m2 - lo, own_hi);
+  const int64_t nb = n2 - 2 * lo;
+  const unsigned nbl = persist_blocks(r1 > r0 ? r1 - r0 : 0, nb);
   if (fs_ensure_part(c, (size_t)nbl * 4)) return 1;
-  // whole local allocation: pads are zero and halo rows are copies, neither changes the maximum
-  k_absmax<<<nbl, 256, 0, c->stream>>>(alloc_base(c->g, c->f[field]), n, c->part, c->ticket, c->red_out);
+  k_absmax<<<nbl, dim3(BX, BY), 0, c->stream>>>(c->f[field], r0, r1, lo, nb, g, c->part, c->ticket, c->red_out);
   FS_LAUNCHED();
   return comm_allreduce(c, c->red_out, 1, COMM_MAX);
 }

@@ -228,21 +228,22 @@ k_conserved(const double* __restrict__ U, const double* __restrict__ V, const do
 }
 
 // the monitor row of every driver (scaling/LidDrivenFlow.cpp:166-170): div = calc_divergence (stored,
-// all cells), then max|U|, max|V|, max|div| over each field's whole ghost-inclusive extent
+// all cells incl. ghosts), then abs_max(curr.U), abs_max(curr.V), abs_max(div) -- abs_max's default
+// reduces over the INTERIOR entries of each field (src/Utility.hpp:44-88):
+// U: a in [1, NX+1], b in [1, NY];  V: a in [1, NX], b in [1, NY+1];  div: a in [1, NX], b in [1, NY]
 __global__ void __launch_bounds__(BX* BY)
 k_monitor(const double* __restrict__ U, const double* __restrict__ V, double* __restrict__ div,
           const Geom g, double* part, unsigned int* ticket, double* out) {
   double v[3] = {0.0, 0.0, 0.0};
-  for_each_point(g.a_lo, g.u_hi(), g.ny + 3, [&](int64_t a, int64_t b) {
+  for_each_point(g.a_lo, g.a_hi, g.ny + 2, [&](int64_t a, int64_t b) {  // the owned cell rows
     const int64_t k = g.idx(a, b), P = g.pitch;
-    const double u = U[k], w = V[k];  // zero pads past either extent do not move a maximum of |.|
-    v[0] = fmax(v[0], fabs(u));
-    v[1] = fmax(v[1], fabs(w));
-    if (a <= g.nx + 1 && b <= g.ny + 1) {
-      const double d = (U[k + P] - u) / g.dx + (V[k + 1] - w) / g.dy;
-      div[k] = d;
-      v[2]   = fmax(v[2], fabs(d));
-    }
+    const double u = U[k], w = V[k];
+    const double d = (U[k + P] - u) / g.dx + (V[k + 1] - w) / g.dy;
+    div[k] = d;
+    const bool ia = a >= 1 && a <= g.nx, ib = b >= 1 && b <= g.ny;
+    if (a >= 1 && ib) v[0] = fmax(v[0], fabs(u));                 // rows 1 .. NX+1 (a_hi <= NX+2)
+    if (ia && b >= 1) v[1] = fmax(v[1], fabs(w));                 // columns 1 .. NY+1
+    if (ia && ib) v[2] = fmax(v[2], fabs(d));
   });
   double tot[3];
   if (grid_reduce<ReduceMax, 3>(v, part, ticket, tot)) {
@@ -396,7 +397,7 @@ int fs_launch_conserved(fsgpu_ctx* c) {  // -> red_out[4..6]
 }
 
 int fs_launch_monitor(fsgpu_ctx* c) {  // -> red_out[4..6]
-  const unsigned gr = persist_blocks(c->g.u_hi() - c->g.a_lo, c->g.ny + 3);
+  const unsigned gr = persist_blocks(c->g.a_hi - c->g.a_lo, c->g.ny + 2);
   if (fs_ensure_part(c, (size_t)gr * 4)) return 1;
   k_monitor<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV], c->g,
                                                 c->part, c->ticket, c->red_out + 4);

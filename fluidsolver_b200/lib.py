@@ -44,7 +44,7 @@ SYMBOLS = (
     "fsgpu_save_old_state", "fsgpu_save_old_velocity", "fsgpu_save_old_density",
     "fsgpu_calc_mid_time", "fsgpu_calc_dmomdt", "fsgpu_update_velocity", "fsgpu_momentum_update",
     "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_calc_divergence",
-    "fsgpu_shift_pressure_to_zero", "fsgpu_correct_velocity", "fsgpu_abs_max",
+    "fsgpu_shift_pressure_to_zero", "fsgpu_correct_velocity", "fsgpu_abs_max", "fsgpu_abs_max_all",
     "fsgpu_calc_rho_visc_const", "fsgpu_calc_rho_visc_vof", "fsgpu_apply_neumann_bconds",
     "fsgpu_ps_create", "fsgpu_ps_destroy", "fsgpu_ps_set_operator", "fsgpu_ps_set_rhs",
     "fsgpu_ps_solve", "fsgpu_ps_num_levels", "fsgpu_substep", "fsgpu_step",
@@ -112,6 +112,7 @@ def load():
     L.fsgpu_monitor.argtypes = [vp, DP, DP, DP]
     L.fsgpu_outflow_fix.argtypes = [vp, DP]
     L.fsgpu_abs_max.argtypes = [vp, i32, DP]
+    L.fsgpu_abs_max_all.argtypes = [vp, i32, DP]
     L.fsgpu_apply_neumann_bconds.argtypes = [vp, i32]
     L.fsgpu_ps_create.argtypes = [vp, C.POINTER(PsOpts), C.POINTER(vp)]
     L.fsgpu_ps_destroy.argtypes = [vp]
@@ -343,9 +344,11 @@ class FS:
     def correct_velocity(self, dt):
         _chk(self.L.fsgpu_correct_velocity(self.h, dt))
 
-    def abs_max(self, name):
+    def abs_max(self, name, include_ghost=False):
+        """abs_max<INCLUDE_GHOST = false>(field), src/Utility.hpp:44-88: interior entries unless include_ghost"""
         o = C.c_double()
-        _chk(self.L.fsgpu_abs_max(self.h, FIELD_ID[name], C.byref(o)))
+        fn = self.L.fsgpu_abs_max_all if include_ghost else self.L.fsgpu_abs_max
+        _chk(fn(self.h, FIELD_ID[name], C.byref(o)))
         return o.value
 
     def calc_rho_visc_const(self):
@@ -388,7 +391,8 @@ class FS:
         return m.value, mx.value, my.value
 
     def monitor(self):
-        """-> (max|U|, max|V|, max|div|); div is stored in field DIV"""
+        """-> (abs_max(U), abs_max(V), abs_max(div)) over the interior entries of each field, as the
+        drivers' monitor row; div (all cells) is stored in field DIV"""
         a, b, d = C.c_double(), C.c_double(), C.c_double()
         _chk(self.L.fsgpu_monitor(self.h, C.byref(a), C.byref(b), C.byref(d)))
         return a.value, b.value, d.value

@@ -172,8 +172,11 @@ int fsgpu_shift_pressure_to_zero(fsgpu_ctx* c);
 /* the driver-inlined projection, scaling/LidDrivenFlow.cpp:153-160 and, for variable density,
  * test/LaminarChannel.cpp:222-233: p += delta_p; U,V -= grad(delta_p)*dt/rho on interior faces */
 int fsgpu_correct_velocity(fsgpu_ctx* c, double dt);
-/* abs_max(field), src/Utility.hpp:80-88 */
+/* abs_max(field) = abs_max<INCLUDE_GHOST = false>, src/Utility.hpp:44-88: the maximum over the
+ * field's INTERIOR entries (what every driver's monitor row uses); fsgpu_abs_max_all is
+ * abs_max<true>(field), the whole ghost-inclusive extent */
 int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out);
+int fsgpu_abs_max_all(fsgpu_ctx* c, int field, double* out);
 /* calc_rho(fs)/calc_visc(fs), src/FS.hpp:569-589 and calc_rho(vf,fs)/calc_visc(vf,fs),
  * src/FS.hpp:592-650 (uses FSGPU_VF) */
 int fsgpu_calc_rho_visc_const(fsgpu_ctx* c);
@@ -207,7 +210,8 @@ int fsgpu_interpolate_cell_centres(fsgpu_ctx* c);
 /* calc_conserved_quantities(fs, mass, momentum_x, momentum_y), src/FS.hpp:653-676 */
 int fsgpu_calc_conserved_quantities(fsgpu_ctx* c, double* mass, double* momentum_x, double* momentum_y);
 /* the monitor row of every driver (scaling/LidDrivenFlow.cpp:166-170) in one pass:
- * calc_divergence -> FSGPU_DIV, then abs_max(curr.U), abs_max(curr.V), abs_max(div) */
+ * calc_divergence -> FSGPU_DIV (all cells), then abs_max(curr.U), abs_max(curr.V), abs_max(div)
+ * (interior entries of each field, as abs_max's default) */
 int fsgpu_monitor(fsgpu_ctx* c, double* u_max, double* v_max, double* div_max);
 
 /* ---- pressure solver = `LinearSolver_StructHypre<Float,NX,NY,1>` -------------------------------

@@ -330,11 +330,12 @@ template <typename Float, Index NX, Index NY, Index NGHOST>
 void correct_velocity(FS<Float, NX, NY, NGHOST>& fs, const Field2D<Float, NX, NY, NGHOST>&, Float dt) {
   FSGPU_CHECK(fsgpu_correct_velocity(fs.ctx, dt));
 }
-// abs_max(field), src/Utility.hpp:80-88
-template <typename Float, Index M, Index N, Index NGHOST>
+// abs_max<INCLUDE_GHOST = false>(field), src/Utility.hpp:44-88: interior entries unless INCLUDE_GHOST
+template <bool INCLUDE_GHOST = false, typename Float, Index M, Index N, Index NGHOST>
 Float abs_max(const Field2D<Float, M, N, NGHOST>& f) {
   double v = 0.0;
-  FSGPU_CHECK(fsgpu_abs_max(fsgpu_shim::ctx_of(f), f.field_id(), &v));
+  if (INCLUDE_GHOST) FSGPU_CHECK(fsgpu_abs_max_all(fsgpu_shim::ctx_of(f), f.field_id(), &v));
+  else FSGPU_CHECK(fsgpu_abs_max(fsgpu_shim::ctx_of(f), f.field_id(), &v));
   return v;
 }
 

@@ -433,10 +433,14 @@ void fso_correct(fso_fs* fs, const double* dp, double dt) {
 }
 
 /* src/Utility.hpp:80-88 (over the whole array incl. ghosts) */
-double fso_abs_max(const double* a, int64_t n) {
-  double m = 0.0;
-  for (int64_t k = 0; k < n; ++k) m = dmax(m, fabs(a[k]));
-  return m;
+/* src/Utility.hpp:44-88: abs_max<INCLUDE_GHOST = false>(field) of an (m+2) x (n+2) field reduces over the
+ * INTERIOR m x n entries (for_each_i) unless include_ghost (for_each_a) */
+double fso_abs_max(const double* a, int64_t m, int64_t n, int include_ghost) {
+  double r = 0.0;
+  const int64_t lo = include_ghost ? -1 : 0;
+  for (int64_t i = lo; i < m - lo; ++i)
+    for (int64_t j = lo; j < n - lo; ++j) r = dmax(r, fabs(a[(j + 1) + (i + 1) * (n + 2)]));
+  return r;
 }
 
 /* src/BoundaryConditions.hpp:227-252 for an (m+2) x (n+2) field */

@@ -72,8 +72,9 @@ void fso_fill_pressure_rhs(const fso_fs* fs, const double* div, double dt, int p
 void fso_shift_pressure_to_zero(const fso_fs* fs, double* dp);
 /* driver-inlined, scaling/LidDrivenFlow.cpp:153-160 / test/LaminarChannel.cpp:224-233 */
 void fso_correct(fso_fs* fs, const double* dp, double dt);
-/* src/Utility.hpp:80-88 */
-double fso_abs_max(const double* a, int64_t n);
+/* src/Utility.hpp:44-88: abs_max<INCLUDE_GHOST = false> of an (m+2) x (n+2) field: interior entries only
+ * unless include_ghost */
+double fso_abs_max(const double* a, int64_t m, int64_t n, int include_ghost);
 /* src/FS.hpp:569-650 with src/BoundaryConditions.hpp:227-252 */
 void fso_calc_rho_visc_const(fso_fs* fs);
 void fso_calc_rho_visc_vof(fso_fs* fs, const double* vf);

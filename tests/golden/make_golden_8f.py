@@ -120,7 +120,28 @@ def bc_profiles(name="bc_profiles48x20"):
     print(name, list(out))
 
 
+def misc(name="misc_random48x20"):
+    """calc_rho(vf, fs) / calc_visc(vf, fs) (src/FS.hpp:592-650), adjust_dt with surface tension
+    (src/FS.hpp:108-114) and the monitor maxima (src/Utility.hpp:80-88)"""
+    st = random_state(48, 20, seed=9)
+    st.sigma = 0.05
+    vf = twophase_inputs(st, seed=2, random_vf=True)[0]
+    o.apply_neumann_bconds(vf)
+    r = Ref(st.nx, st.ny)
+    r.load(st)
+    out = {"adjust_dt_sigma": np.array(r.adjust_dt(0.9, 1e9)), "diag": np.array(r.diagnostics())}
+    r.calc_rho_visc_vof(vf)
+    s2 = st.copy()
+    r.store(s2)
+    out["rho_u"], out["rho_v"], out["visc"] = s2.rho_u, s2.rho_v, s2.visc
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
+    print(name, out["adjust_dt_sigma"], out["diag"])
+
+
 if __name__ == "__main__":
+    if "misc" in sys.argv:
+        misc()
+        sys.exit(0)
     if "profiles" in sys.argv:
         bc_profiles()
         sys.exit(0)
@@ -132,3 +153,4 @@ if __name__ == "__main__":
     run_twophase("twophase128")
     run_couette("couette210x21")
     bc_profiles()
+    misc()

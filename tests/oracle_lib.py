@@ -152,7 +152,7 @@ class Oracle:
         L.fso_adjust_dt.argtypes = [C.POINTER(CFs), C.c_double, C.c_double]
         L.fso_outflow_fix.restype = C.c_double
         L.fso_abs_max.restype = C.c_double
-        L.fso_abs_max.argtypes = [DP, C.c_int64]
+        L.fso_abs_max.argtypes = [DP, C.c_int64, C.c_int64, C.c_int]
         L.fso_calc_mid_time.argtypes = [DP, DP, C.c_int64]
         L.fso_update_velocity.argtypes = [C.POINTER(CFs), DP, DP, C.c_double]
         L.fso_update_density.argtypes = [C.POINTER(CFs), DP, DP, C.c_double]
@@ -256,8 +256,10 @@ class Oracle:
     def correct(self, st, dp, dt):
         self.lib.fso_correct(C.byref(st.cstruct()), _ptr(dp), dt)
 
-    def abs_max(self, a):
-        return self.lib.fso_abs_max(_ptr(a), a.size)
+    def abs_max(self, a, include_ghost=False):
+        """abs_max<INCLUDE_GHOST = false>(field): interior entries unless include_ghost"""
+        a = np.ascontiguousarray(a)
+        return self.lib.fso_abs_max(_ptr(a), a.shape[0] - 2, a.shape[1] - 2, int(include_ghost))
 
     def calc_rho_visc_const(self, st):
         self.lib.fso_calc_rho_visc_const(C.byref(st.cstruct()))

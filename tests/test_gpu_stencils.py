@@ -152,8 +152,10 @@ def test_adjust_dt_absmax(F, oracle):
     fs = to_gpu(F, st)
     assert fs.adjust_dt(0.5, 1e9) == pytest.approx(oracle.adjust_dt(st, 0.5, 1e9), rel=1e-14)
     assert fs.adjust_dt(0.5, 1e-9) == 1e-9
-    for n in ("U", "V", "P"):
-        assert fs.abs_max(n) == oracle.abs_max(st.a[n.lower() if n == "P" else n])
+    for n in ("U", "V", "P"):   # abs_max<INCLUDE_GHOST = false> (interior) and abs_max<true>, src/Utility.hpp:44-88
+        a = st.a[n.lower() if n == "P" else n]
+        assert fs.abs_max(n) == oracle.abs_max(a) == np.abs(a[1:-1, 1:-1]).max()
+        assert fs.abs_max(n, include_ghost=True) == oracle.abs_max(a, include_ghost=True) == np.abs(a).max()
     fs.close()
 
 
