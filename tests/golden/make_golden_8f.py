@@ -130,6 +130,9 @@ def misc(name="misc_random48x20"):
     r = Ref(st.nx, st.ny)
     r.load(st)
     out = {"adjust_dt_sigma": np.array(r.adjust_dt(0.9, 1e9)), "diag": np.array(r.diagnostics())}
+    dp = np.random.default_rng(4).uniform(-1, 1, (st.nx + 2, st.ny + 2)) + 0.3
+    r.shift_pressure_to_zero(dp)  # src/Operators.hpp:52-62,78-82 (in place)
+    out["dp_shifted"] = dp
     r.calc_rho_visc_vof(vf)
     s2 = st.copy()
     r.store(s2)
