@@ -141,7 +141,32 @@ def misc(name="misc_random48x20"):
     print(name, out["adjust_dt_sigma"], out["diag"])
 
 
+def solve_psd(name="solve_psd128"):
+    """one PCG+PFMG solve per PSDirichlet side (src/LinearSystem.hpp:10,32-155; the two-phase drivers use
+    PSDirichlet::RIGHT with all-Neumann velocity BCs, test/StationaryDrop.cpp:67-72,223-224) on the
+    rho-ratio-1000 drop"""
+    from oracle_lib import BConds, NEUMANN
+    st = cavity_state(o, 128, 128, drop=True, seed=2)
+    bc = BConds(kind=(NEUMANN,) * 4)
+    o.apply_velocity_bconds(st, bc)
+    out = {}
+    for psd in (1, 2, 3, 4):
+        r = Ref(st.nx, st.ny)
+        r.load(st)
+        r.set_bconds(bc)
+        div = r.calc_divergence()
+        r.solver_create(1e-10, 300, psd)
+        r.solver_set_operator()
+        dp, res, it = r.solver_solve(div, 1e-2)
+        out[f"dp{psd}"], out[f"res{psd}"], out[f"it{psd}"] = dp, np.array(res), np.array(it)
+        print("psd", psd, "its", it, "res", res)
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
+
+
 if __name__ == "__main__":
+    if "psd" in sys.argv:
+        solve_psd()
+        sys.exit(0)
     if "misc" in sys.argv:
         misc()
         sys.exit(0)
@@ -157,3 +182,4 @@ if __name__ == "__main__":
     run_couette("couette210x21")
     bc_profiles()
     misc()
+    solve_psd()

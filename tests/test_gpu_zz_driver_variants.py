@@ -86,3 +86,29 @@ def test_dirichlet_profiles_vs_reference_golden(F):
         assert np.array_equal(fs.download("U"), g[f"{key}_U"]), key
         assert np.array_equal(fs.download("V"), g[f"{key}_V"]), key
         fs.close()
+
+
+@pytest.mark.parametrize("psd", [1, 2, 3, 4])
+def test_solve_with_dirichlet_side_vs_reference_golden(F, oracle, psd):
+    """PSDirichlet LEFT / RIGHT / BOTTOM / TOP (src/LinearSystem.hpp:10,32-155) on the rho-ratio-1000
+    drop with all-Neumann velocity BCs (test/StationaryDrop.cpp:67-72,223-224): same iteration count and
+    solution as HYPRE"""
+    from cases import cavity_state
+    from oracle_lib import BConds, NEUMANN
+    g = np.load(os.path.join(GOLD, "solve_psd128.npz"))
+    st = cavity_state(oracle, 128, 128, drop=True, seed=2)
+    bc = BConds(kind=(NEUMANN,) * 4)
+    oracle.apply_velocity_bconds(st, bc)
+    fs = to_gpu(F, st, bc)
+    ps = F.LinearSolver(fs, tol=1e-10, max_iter=300, psd=psd)
+    ps.set_pressure_operator()
+    fs.calc_divergence()
+    ps.set_pressure_rhs(1e-2)
+    res, it = ps.solve()
+    dp = fs.download("DELTA_P")
+    print(f"\n[PSDirichlet {psd}] its gpu {it} reference {int(g[f'it{psd}'])}, residual {res:.2e}, "
+          f"rel L2 {rel_l2(dp, g[f'dp{psd}']):.2e}")
+    assert res < 1e-10 and abs(it - int(g[f"it{psd}"])) <= 1
+    assert rel_l2(dp, g[f"dp{psd}"]) <= 1e-8
+    ps.close()
+    fs.close()
