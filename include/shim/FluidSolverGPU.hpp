@@ -90,6 +90,31 @@ fsgpu_ctx* ctx_of(const F& f) {
 }
 }  // namespace fsgpu_shim
 
+// ---- host loops of src/ForEach.hpp:23-136 (for_each, for_each_i, for_each_a) ----------------------
+// Drivers initialise fields and evaluate their test criteria with these; here they run serially on
+// the HOST mirrors (Exec is accepted and ignored), so such code compiles unchanged.  Follow
+// initialisation loops by fs.to_device() / field.upload(), precede evaluation loops by fs.to_host().
+enum class Exec : std::uint8_t { Serial, Parallel, ParallelDynamic, ParallelGPU };
+template <Index I_MIN, Index I_MAX, Exec EXEC = Exec::Serial, typename FUNC>
+void for_each(FUNC&& f) {
+  for (Index i = I_MIN; i < I_MAX; ++i) f(i);
+}
+template <Index I_MIN, Index I_MAX, Index J_MIN, Index J_MAX, Exec EXEC = Exec::Serial, typename FUNC>
+void for_each(FUNC&& f) {
+  for (Index i = I_MIN; i < I_MAX; ++i)
+    for (Index j = J_MIN; j < J_MAX; ++j) f(i, j);
+}
+template <Exec EXEC = Exec::Serial, typename Float, Index N, Index NGHOST, typename FUNC>
+void for_each_i(const Field1D<Float, N, NGHOST>&, FUNC&& f) { for_each<0, N, EXEC>(f); }
+template <Exec EXEC = Exec::Serial, typename Float, Index N, Index NGHOST, typename FUNC>
+void for_each_a(const Field1D<Float, N, NGHOST>&, FUNC&& f) { for_each<-NGHOST, N + NGHOST, EXEC>(f); }
+template <Exec EXEC = Exec::Serial, typename Float, Index M, Index N, Index NGHOST, typename FUNC>
+void for_each_i(const Field2D<Float, M, N, NGHOST>&, FUNC&& f) { for_each<0, M, 0, N, EXEC>(f); }
+template <Exec EXEC = Exec::Serial, typename Float, Index M, Index N, Index NGHOST, typename FUNC>
+void for_each_a(const Field2D<Float, M, N, NGHOST>&, FUNC&& f) {
+  for_each<-NGHOST, M + NGHOST, -NGHOST, N + NGHOST, EXEC>(f);
+}
+
 // fill(field, value), src/Container.hpp:172-180: host mirror and device
 template <typename Float, Index M, Index N, Index NGHOST>
 void fill(Field2D<Float, M, N, NGHOST>& f, Float v) {
@@ -255,13 +280,15 @@ bool time_dependent(const FlowBConds<Float>& b) {
 template <typename Float, Index NX, Index NY>
 void apply_velocity_bconds(FS<Float, NX, NY, 1>& fs, const FlowBConds<Float>& bconds, Float t = -1.0) {
   static const void* sent_for = nullptr;
+  static const void* sent_bc  = nullptr;
   static double sent_t        = 0.0;
-  if (sent_for != &fs || (fsgpu_shim::time_dependent(bconds) && sent_t != t)) {
+  if (sent_for != &fs || sent_bc != &bconds || (fsgpu_shim::time_dependent(bconds) && sent_t != t)) {
     fsgpu_shim::set_side(fs, FSGPU_LEFT, bconds.left, t);
     fsgpu_shim::set_side(fs, FSGPU_RIGHT, bconds.right, t);
     fsgpu_shim::set_side(fs, FSGPU_BOTTOM, bconds.bottom, t);
     fsgpu_shim::set_side(fs, FSGPU_TOP, bconds.top, t);
     sent_for = &fs;
+    sent_bc  = &bconds;
     sent_t   = t;
   }
   FSGPU_CHECK(fsgpu_apply_velocity_bconds(fs.ctx));
