@@ -39,20 +39,22 @@ k_divergence(const double* __restrict__ U, const double* __restrict__ V, double*
 template <bool FROM_UV>
 __global__ void __launch_bounds__(BX* BY)
 k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __restrict__ div,
-      double* __restrict__ rhs, const Geom g, double dt, int psd, double* part,
-      unsigned int* ticket, double* out) {
+      double* __restrict__ rhs, const Geom g, double dt, double rdx, double rdy, double mvol_dt, int psd,
+      double* part, unsigned int* ticket, double* out) {
   double v[1] = {0.0};
   for_each_point(g.a_lo, g.a_hi, g.ny + 2, [&](int64_t a, int64_t b) {
     const int64_t k = g.idx(a, b);
     double d;
-    if (FROM_UV) {
-      d      = div_at(U, V, k, g.pitch, g.dx, g.dy);
+    double r;
+    if (FROM_UV) {  // fused fast path: multiplies by 1/dx, 1/dy, -vol/dt (<= 1 ulp per quotient, tolerance 1e-12)
+      d      = (__ldg(U + k + g.pitch) - __ldg(U + k)) * rdx + (__ldg(V + k + 1) - __ldg(V + k)) * rdy;
       div[k] = d;
+      r      = mvol_dt * d;
     } else {
       d = div[k];
+      const double vol = g.dx * g.dy;
+      r                = -vol * d / dt;
     }
-    const double vol = g.dx * g.dy;
-    double r         = -vol * d / dt;
     if ((psd == FSGPU_PSD_LEFT && a == 0) || (psd == FSGPU_PSD_RIGHT && a == g.nx + 1) ||
         (psd == FSGPU_PSD_BOTTOM && b == 0) || (psd == FSGPU_PSD_TOP && b == g.ny + 1))
       r = 0.0;
@@ -89,7 +91,7 @@ template <bool SHIFT>
 __global__ void __launch_bounds__(BX* BY)
 k_correct(double* __restrict__ dp, double* __restrict__ p, double* __restrict__ U,
           double* __restrict__ V, const double* __restrict__ ru, const double* __restrict__ rv,
-          const double* __restrict__ sum, const Geom g, double dt) {
+          const double* __restrict__ sum, const Geom g, double dt_dx, double dt_dy) {
   const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
   const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
   if (a >= g.a_hi || b > g.ny + 1) return;
@@ -101,12 +103,12 @@ k_correct(double* __restrict__ dp, double* __restrict__ p, double* __restrict__ 
   // U(i,j) for i in [0,NX], j in [0,NY): a in [1,NX+1], b in [1,NY]
   if (a >= 1 && b >= 1 && b <= g.ny) {
     const double dm = __ldcg(dp + k - P) - c;
-    U[k] -= (d0 - dm) / g.dx * dt / __ldg(ru + k);
+    U[k] -= (d0 - dm) * dt_dx / __ldg(ru + k);  // (delta / dx * dt) / rho with dt/dx formed once (<= 1 ulp)
   }
   // V(i,j) for i in [0,NX), j in [0,NY]: a in [1,NX], b in [1,NY+1]
   if (a >= 1 && a <= g.nx && b >= 1) {
     const double dm = __ldcg(dp + k - 1) - c;
-    V[k] -= (d0 - dm) / g.dy * dt / __ldg(rv + k);
+    V[k] -= (d0 - dm) * dt_dy / __ldg(rv + k);
   }
   p[k] += d0;
   (void)d0;
@@ -218,11 +220,12 @@ int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
   if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
   if (div_from_uv)
     k_rhs<true><<<pg, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
-                                                    c->f[FSGPU_RHS], c->g, dt, psd, c->part,
-                                                    c->ticket, c->red_out);
+                                                    c->f[FSGPU_RHS], c->g, dt, 1.0 / c->g.dx, 1.0 / c->g.dy,
+                                                    -(c->g.dx * c->g.dy) / dt, psd, c->part, c->ticket,
+                                                    c->red_out);
   else
     k_rhs<false><<<pg, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
-                                                     c->f[FSGPU_RHS], c->g, dt, psd, c->part,
+                                                     c->f[FSGPU_RHS], c->g, dt, 0.0, 0.0, 0.0, psd, c->part,
                                                      c->ticket, c->red_out);
   FS_LAUNCHED();
   if (psd == FSGPU_PSD_NONE) {  // subtract the arithmetic mean over all (NX+2)(NY+2) entries
@@ -263,7 +266,7 @@ int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift) {
   }
   k_correct<false><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
       c->f[FSGPU_DELTA_P], c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
-      c->f[FSGPU_RHO_V], c->red_out + 1, c->g, dt);
+      c->f[FSGPU_RHO_V], c->red_out + 1, c->g, dt / c->g.dx, dt / c->g.dy);
   FS_LAUNCHED();
   const int fl[3] = {FSGPU_U, FSGPU_V, FSGPU_P};
   return fs_exchange_fields(c, fl, 3, 1);
