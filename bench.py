@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--no-ref-depth", action="store_true", help="skip the secondary 16-level measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--halo", default="", choices=["", "nccl", "p2p"],
+                    help="N > 1: p2p = halo rows and scalar reductions through peer-mapped mailboxes (sets FSGPU_HALO)")
     ap.add_argument("--prof", default="", help="kernel class to time for the roofline (default: auto)")
     return ap.parse_args()
 
@@ -193,6 +195,8 @@ def main():
         box = [F.comm_id() if rank == 0 else None]
         dist.broadcast_object_list(box, src=0)
         comm_id = box[0]
+    if a.halo:
+        os.environ["FSGPU_HALO"] = a.halo
     # N = 1: BASELINE configs[2] (8192^2, the configuration the metric is quoted on);
     # N > 1: configs[4], the 16384^2 strong-scaling case, slab-decomposed over the N GPUs
     n = a.n or (8192 if world == 1 else 16384)
@@ -324,6 +328,7 @@ def main():
                "api": "fsgpu_upload(U,V,P) -> fsgpu_adjust_dt -> fsgpu_step -> fsgpu_download(U,V,P), pinned host "
                       "buffers" + (" (each rank its own slab rows; bytes summed over ranks)" if dist else "")}
     umax = fs.abs_max("U")
+    direct = fs.halo_is_direct()
     levels = (ps.num_levels, ps.num_distributed_levels)
     ps.close()
     # the same steps with the reference's 16-level cap (secondary number, device-resident timing)
@@ -374,7 +379,9 @@ def main():
                        "mg_depth": "uncapped (coarsest grid = 1 point)" if a.max_levels >= 40 else f"capped at {a.max_levels}",
                        "reference_depth_16": ref_depth,
                        "decomposition": None if world == 1 else
-                       f"{world} slabs of i-rows, NCCL halo exchange + all-reduce, multigrid levels "
+                       f"{world} slabs of i-rows, " + ("mailbox (peer-mapped, one kernel per exchange) halo exchange + scalar "
+                                                     "all-reduce, NCCL for large reductions" if direct else
+                                                     "NCCL halo exchange + all-reduce") + ", multigrid levels "
                        f"0..{levels[1] - 1} distributed, {levels[1]}..{levels[0] - 1} replicated", "l2": "inputs larger than L2 "
                        f"(each field {cells * 8 / 1e6:.0f} MB vs 126 MB L2)", "max_abs_U": umax},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches * world, "clocks": clk}

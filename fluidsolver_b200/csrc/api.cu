@@ -211,6 +211,12 @@ int fsgpu_destroy(fsgpu_ctx* c) {
   return 0;
 }
 
+int fsgpu_halo_is_direct(fsgpu_ctx* c, int* on) {
+  FS_CHECK_CTX(c);
+  if (on) *on = comm_is_direct(c);
+  return 0;
+}
+
 int fsgpu_set_props(fsgpu_ctx* c, double rho_gas, double rho_liquid, double visc_gas,
                     double visc_liquid, double sigma) {
   FS_CHECK_CTX(c);

@@ -433,6 +433,9 @@ int comm_create(fsgpu_ctx* c, int rank, int nranks, const void* id128, int trans
   return 0;
 }
 
+// 1 when halo rows and scalar reductions go through the peer-mapped mailboxes (FSGPU_HALO=p2p took)
+int comm_is_direct(fsgpu_ctx* c) { return c->comm && c->comm->p2p.on ? 1 : 0; }
+
 // non-zero once a direct halo exchange has timed out waiting for a neighbour
 int comm_failed(fsgpu_ctx* c) {
   Comm* cm = c->comm;

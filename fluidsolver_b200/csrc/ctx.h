@@ -56,6 +56,7 @@ static inline double* alloc_base(const Geom& g, double* v) { return v + g.voff()
 enum { COMM_SUM = 0, COMM_MAX = 1 };
 int comm_create(fsgpu_ctx* c, int rank, int nranks, const void* id128, int transport);
 void comm_destroy(fsgpu_ctx* c);
+int comm_is_direct(fsgpu_ctx* c);
 int comm_failed(fsgpu_ctx* c);  // a direct (FSGPU_HALO=p2p) halo exchange timed out
 // arrays given by VIRTUAL base pointers sharing `pitch`; this rank owns rows [i0, i1) (global
 // indices).  Fills the h rows above and below from the neighbour ranks' owned rows.

@@ -49,7 +49,7 @@ SYMBOLS = (
     "fsgpu_ps_create", "fsgpu_ps_destroy", "fsgpu_ps_set_operator", "fsgpu_ps_set_rhs",
     "fsgpu_ps_solve", "fsgpu_ps_num_levels", "fsgpu_substep", "fsgpu_step",
     "fsgpu_comm_id", "fsgpu_create_slab", "fsgpu_slab_range", "fsgpu_slab_coarse_range",
-    "fsgpu_ps_num_distributed_levels",
+    "fsgpu_ps_num_distributed_levels", "fsgpu_halo_is_direct",
     "fsgpu_calc_drhodt", "fsgpu_update_density", "fsgpu_density_step", "fsgpu_calc_pressure_jump",
     "fsgpu_capillary_divergence", "fsgpu_correct_velocity_ib_implicit_euler",
     "fsgpu_update_velocity_ib_semi_analytical", "fsgpu_interpolate_cell_centres",
@@ -271,6 +271,13 @@ class FS:
 
     def download_rows(self, name, rows, r0):
         _chk(self.L.fsgpu_download(self.h, FIELD_ID[name], self._shifted(name, rows, r0)))
+
+    def halo_is_direct(self) -> bool:
+        """True if FSGPU_HALO=p2p took: halos / scalar reductions go through peer-mapped mailboxes"""
+        on = C.c_int(0)
+        self.L.fsgpu_halo_is_direct.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+        _chk(self.L.fsgpu_halo_is_direct(self.h, C.byref(on)))
+        return bool(on.value)
 
     def fill(self, name, value):
         _chk(self.L.fsgpu_fill(self.h, FIELD_ID[name], value))

@@ -117,6 +117,10 @@ enum { FSGPU_TRANSPORT_NCCL = 0, FSGPU_TRANSPORT_LOCAL = 1 };
 int fsgpu_comm_id(void* id128); /* ncclGetUniqueId */
 int fsgpu_create_slab(int64_t nx, int64_t ny, double dx, double dy, int device, int rank, int nranks,
                       const void* id128, int transport, fsgpu_ctx** out);
+/* Environment FSGPU_HALO=p2p (read by fsgpu_create_slab): halo rows and scalar all-reduces bypass NCCL
+ * and travel through peer-mapped mailboxes (cudaIpc between the processes), one kernel per exchange;
+ * falls back to the transport above on every rank if any rank cannot map a peer.  *on = 1 if active. */
+int fsgpu_halo_is_direct(fsgpu_ctx* c, int* on);
 /* host-only partition rule (no device needed): rows [*a_lo, *a_hi) of rank `rank` */
 int fsgpu_slab_range(int64_t nx, int rank, int nranks, int64_t* a_lo, int64_t* a_hi);
 /* host-only: the rows [*c_lo, *c_hi) of the next coarser multigrid level that belong to the owner of
