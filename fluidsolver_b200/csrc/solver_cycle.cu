@@ -31,10 +31,26 @@
 #ifndef FS_UP_PREFETCH
 #define FS_UP_PREFETCH 0
 #endif
+// marching kernels: rows ahead whose operands are pulled into L2 with prefetch.global.L2 (0 = off).
+// The kernels are latency bound (ncu: long-scoreboard stalls, DRAM 61 % busy, 30 warps/SM at 64
+// registers); an L2 prefetch adds memory-level parallelism without costing a register.  A/B variant
+// for scripts/build_variants.py (-DFS_PF_ROWS=4), not yet timed.
+#ifndef FS_PF_ROWS
+#define FS_PF_ROWS 0
+#endif
 
 namespace {
 
 constexpr int BX = 64, BY = 4;
+
+// one lane in eight touches the line (a warp row is 256 B = 2-3 lines of 128 B)
+__device__ __forceinline__ void pf_l2(const double* p, int lane) {
+#if FS_PF_ROWS > 0
+  if ((lane & 7) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+#else
+  (void)p; (void)lane;
+#endif
+}
 
 // 1 / v with the convention of the stored dinv / pc arrays (0 where v == 0: pads, halo-less walls,
 // a singular coarsest point).  The active-level kernels recompute dinv = 1/d and the interpolation
@@ -78,6 +94,13 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
     int o  = (li + FS_RO) * P + lj + FS_CO;
 #pragma unroll 2
     for (; li <= fL + 2; ++li, o += P) {
+#if FS_PF_ROWS > 0
+      if (li + FS_PF_ROWS <= fL + 2) {
+        const int op = o + FS_PF_ROWS * P;
+        pf_l2(fb + op, lane); pf_l2(f.cx + op, lane);
+        if (ACTIVE) { pf_l2(f.d + op, lane); pf_l2(f.cy + op, lane); }
+      }
+#endif
       const double b0 = __ldg(fb + o), cx0 = __ldg(f.cx + o);
       double X0 = 0.0, cy0 = 0.0, cy0p = 0.0, pc0 = 0.0;
       if (ACTIVE) {
@@ -140,6 +163,13 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
     int o  = (li + FS_RO) * P + lj + FS_CO;
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
+#if FS_PF_ROWS > 0
+      if (li + FS_PF_ROWS <= r1) {
+        const int op = o + FS_PF_ROWS * P;
+        pf_l2(fb + op, lane); pf_l2(f.cy + op, lane);
+        if (ACTIVE) { pf_l2(f.d + op, lane); pf_l2(f.cx + op, lane); }
+      }
+#endif
       const double b0 = __ldg(fb + o);
       const double cy0 = __ldg(f.cy + o), cy0p = __ldg(f.cy + o + 1);
       double X0 = 0.0, cx0 = 0.0, d0 = 0.0;
@@ -284,6 +314,12 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
 #endif
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
+#if FS_PF_ROWS > 0
+      if (li + FS_PF_ROWS <= r1) {  // cx is read one row further down than the others
+        const int op = o + FS_PF_ROWS * P;
+        pf_l2(fb + op, lane); pf_l2(f.d + op, lane); pf_l2(f.cy + op, lane); pf_l2(f.cx + op + P, lane);
+      }
+#endif
 #if FS_UP_PREFETCH
       const Row q = nx;
       if (li < r1) nx = load_row(li + 1, o + P);
