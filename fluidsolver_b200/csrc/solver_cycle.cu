@@ -250,10 +250,15 @@ k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
 // 2/MR row overlap).  CTAs loop over (strip, chunk) tasks, so the optional dot product <b, x>
 // (= <r, z> of PCG on level 0) ends in ~1e3 partials.
 // DOT: 0 none, 1 PCG iteration (convergence test + beta), 2 first V-cycle (bi).
-constexpr int MOUT = 30, MWARPS = 4;
+// FS_MWARPS: warps (= adjacent 30-column strips) per CTA of k_up_march; A/B variant (-DFS_MWARPS=8 keeps the
+// resident warps per SM: the CTA count per SM scales down with it)
+#ifndef FS_MWARPS
+#define FS_MWARPS 4
+#endif
+constexpr int MOUT = 30, MWARPS = FS_MWARPS;
 
 template <int CDIR, int DOT>
-__global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB)
+__global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB * 4 / MWARPS)
 k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
            const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part,
            unsigned int* ticket) {
