@@ -112,3 +112,29 @@ def test_solve_with_dirichlet_side_vs_reference_golden(F, oracle, psd):
     assert rel_l2(dp, g[f"dp{psd}"]) <= 1e-8
     ps.close()
     fs.close()
+
+
+def test_misc_vs_reference_golden(F, oracle):
+    """adjust_dt with the surface-tension limit (src/FS.hpp:108-114), the monitor maxima (interior entries,
+    src/Utility.hpp:44-88), shift_pressure_to_zero and calc_rho / calc_visc(vf, fs) against the committed
+    output of the unmodified reference (tests/golden/misc_random48x20.npz)"""
+    from cases import random_state, rel_inf, twophase_inputs
+    g = np.load(os.path.join(GOLD, "misc_random48x20.npz"))
+    st = random_state(48, 20, seed=9)
+    st.sigma = 0.05
+    vf = twophase_inputs(st, seed=2, random_vf=True)[0]
+    oracle.apply_neumann_bconds(vf)
+    fs = to_gpu(F, st)
+    assert fs.adjust_dt(0.9, 1e9) == pytest.approx(float(g["adjust_dt_sigma"]), rel=1e-13)
+    um, vm, dm = fs.monitor()
+    assert um == g["diag"][0] and vm == g["diag"][1] and dm == pytest.approx(g["diag"][2], rel=1e-12)
+    assert fs.abs_max("U") == g["diag"][0] and fs.abs_max("DIV") == pytest.approx(g["diag"][2], rel=1e-12)
+    dp = np.random.default_rng(4).uniform(-1, 1, (st.nx + 2, st.ny + 2)) + 0.3
+    fs.upload("DELTA_P", dp)
+    fs.shift_pressure_to_zero()
+    assert rel_inf(fs.download("DELTA_P"), g["dp_shifted"]) <= 1e-12
+    fs.upload("VF", vf)
+    fs.calc_rho_visc_vof()
+    for n, k in (("RHO_U", "rho_u"), ("RHO_V", "rho_v"), ("VISC", "visc")):
+        assert rel_inf(fs.download(n), g[k]) <= 1e-12, n
+    fs.close()
