@@ -5,5 +5,6 @@ from .lib import (FS, LinearSolver, FsgpuError, load, launch_count, device_count
                   FIELDS, FIELD_ID, SYMBOLS, LIB_PATH, PROF_CLASSES, prof_enable, prof_read,
                   DIRICHLET, NEUMANN, PERIODIC, SYMMETRY, LEFT, RIGHT, BOTTOM, TOP,
                   PSD_NONE, PSD_LEFT, PSD_RIGHT, PSD_BOTTOM, PSD_TOP, RELAX_JACOBI, RELAX_RBGS,
-                  STEP_OUTFLOW_FIX, STEP_REBUILD_OPERATOR, STEP_DENSITY, STEP_CAPILLARY, TRANSPORT_NCCL, TRANSPORT_LOCAL,
+                  FLOW_FORCE_TOTAL, FLOW_OUTFLOW_FIX, FLOW_OUTFLOW_FIX_DY, STEP_OUTFLOW_FIX,
+                  STEP_REBUILD_OPERATOR, STEP_DENSITY, STEP_CAPILLARY, TRANSPORT_NCCL, TRANSPORT_LOCAL,
                   COMM_ID_BYTES, comm_id, slab_range, slab_coarse_range, slab_rows)

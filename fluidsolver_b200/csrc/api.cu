@@ -358,13 +358,34 @@ int fsgpu_calc_divergence(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_dive
 int fsgpu_shift_pressure_to_zero(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_shift_pressure(c); }
 int fsgpu_correct_velocity(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_correct(c, dt, false); }
 
-int fsgpu_outflow_fix(fsgpu_ctx* c, double* mass_error) {
+static bool flow_mode_ok(int mode) {
+  if (mode >= FSGPU_FLOW_OUTFLOW_FIX && mode <= FSGPU_FLOW_FORCE_TOTAL) return true;
+  fs_set_error("flow control: unknown mode %d", mode);
+  return false;
+}
+int fsgpu_flow_control(fsgpu_ctx* c, int mode, double total_flow, double* inflow, double* outflow) {
   FS_CHECK_CTX(c);
-  if (fs_launch_outflow_fix(c, c->red_out + 2)) return 1;
-  if (mass_error) {
-    if (read_red(c, 2, 1)) return 1;
-    *mass_error = c->h_red[2];
+  if (!flow_mode_ok(mode)) return 1;
+  if (fs_launch_flow_control(c, mode, total_flow, c->red_out + 2)) return 1;
+  if (inflow || outflow) {
+    if (read_red(c, 8, 2)) return 1;
+    if (inflow) *inflow = c->h_red[8];
+    if (outflow) *outflow = c->h_red[9];
   }
+  return 0;
+}
+int fsgpu_outflow_fix(fsgpu_ctx* c, double* mass_error) {
+  double in = 0.0, out = 0.0;
+  if (fsgpu_flow_control(c, FSGPU_FLOW_OUTFLOW_FIX, 0.0, mass_error ? &in : nullptr, mass_error ? &out : nullptr))
+    return 1;
+  if (mass_error) *mass_error = out - in;
+  return 0;
+}
+int fsgpu_set_flow_control(fsgpu_ctx* c, int mode, double total_flow) {
+  FS_CHECK_CTX(c);
+  if (!flow_mode_ok(mode)) return 1;
+  c->flow_mode  = mode;
+  c->flow_total = total_flow;
   return 0;
 }
 
@@ -523,7 +544,8 @@ int fsgpu_substep(fsgpu_ctx* c, fsgpu_ps* s, double dt, int flags, double* resid
     ProfScope ps_(PROF_BC, c->stream);
     if (fs_launch_bconds(c)) return 1;
   }
-  if ((flags & FSGPU_STEP_OUTFLOW_FIX) && fs_launch_outflow_fix(c, c->red_out + 2)) return 1;
+  if ((flags & FSGPU_STEP_OUTFLOW_FIX) && fs_launch_flow_control(c, c->flow_mode, c->flow_total, c->red_out + 2))
+    return 1;
   if ((flags & FSGPU_STEP_REBUILD_OPERATOR) || !s->is_setup) {
     if (ps_setup(s)) return 1;
   }

@@ -115,16 +115,21 @@ __global__ void k_bc_bt(const BcArgs a, const Geom g) {
   }
 }
 
-// test/LaminarChannel.cpp:55-66 (sums over j = -1..NY) and :201-205.  Two one-block kernels so
-// that a decomposed grid can combine the inlet sum (first slab) and the outlet sum (last slab)
-// in between: io[0] = inflow, io[1] = outflow.
+// The channel drivers' corrections of the two ghost columns after apply_velocity_bconds:
+//   mode 1  test/LaminarChannel.cpp:55-66 (sums over j = -1..NY) and :201-205
+//   mode 2  test/CustomDirichletChannel.cpp:61-72,197-202 = scaling/Channel.cpp:65-76,208-213: the sums carry
+//           a factor dy, the correction formula is the same
+//   mode 3  test/PeriodicChannel.cpp:56-67,193-203 = scaling/Channel.cpp:196-206: both columns are shifted so
+//           that each carries total_flow
+// Two one-block kernels so that a decomposed grid can combine the inlet sum (first slab) and the
+// outlet sum (last slab) in between: io[0] = inflow, io[1] = outflow (w = 1 or dy per term).
 __global__ void k_outflow_sums(const double* __restrict__ U, const double* __restrict__ ru, const Geom g,
-                               double* io) {
+                               double w, double* io) {
   __shared__ double sm[32];
   double in = 0.0, out = 0.0;
   for (int64_t b = threadIdx.x; b <= g.ny + 1; b += blockDim.x) {
-    if (g.first()) in += ru[g.idx(0, b)] * U[g.idx(0, b)];
-    if (g.last()) out += ru[g.idx(g.nx + 2, b)] * U[g.idx(g.nx + 2, b)];
+    if (g.first()) in += ru[g.idx(0, b)] * U[g.idx(0, b)] * w;
+    if (g.last()) out += ru[g.idx(g.nx + 2, b)] * U[g.idx(g.nx + 2, b)] * w;
   }
   in  = block_reduce<ReduceSum>(in, sm);
   out = block_reduce<ReduceSum>(out, sm);
@@ -133,14 +138,29 @@ __global__ void k_outflow_sums(const double* __restrict__ U, const double* __res
     io[1] = out;
   }
 }
-__global__ void k_outflow_apply(double* __restrict__ U, const double* __restrict__ ru, const Geom g,
-                                const double* io, double* mass_error_out) {
+__global__ void k_outflow_apply(double* __restrict__ U, const double* __restrict__ ru, const Geom g, int mode,
+                                double total_flow, const double* io, double* mass_error_out) {
   const double me = io[1] - io[0];
   if (threadIdx.x == 0 && mass_error_out) *mass_error_out = me;
+  const double n2 = (double)(g.ny + 2);
+  if (mode == FSGPU_FLOW_FORCE_TOTAL) {
+    const double ie = total_flow - io[0], oe = total_flow - io[1];
+    for (int64_t b = threadIdx.x; b <= g.ny + 1; b += blockDim.x) {
+      if (g.first()) {
+        const int64_t k = g.idx(0, b);
+        U[k] += ie / (ru[k] * g.dy * n2);
+      }
+      if (g.last()) {
+        const int64_t k = g.idx(g.nx + 2, b);
+        U[k] += oe / (ru[k] * g.dy * n2);
+      }
+    }
+    return;
+  }
   if (!g.last()) return;
   for (int64_t b = threadIdx.x; b <= g.ny + 1; b += blockDim.x) {
     const int64_t k = g.idx(g.nx + 2, b);
-    U[k] -= me / (ru[k] * (double)(g.ny + 2));
+    U[k] -= me / (ru[k] * n2);
   }
 }
 
@@ -198,12 +218,15 @@ int fs_launch_bconds(fsgpu_ctx* c) {
   return fs_exchange_fields(c, fl, 2, 1);
 }
 
-int fs_launch_outflow_fix(fsgpu_ctx* c, double* d_mass_error) {
+// io (device, 2 doubles) keeps inflow and outflow as they were before the correction
+int fs_launch_flow_control(fsgpu_ctx* c, int mode, double total_flow, double* d_mass_error) {
   double* io = c->red_out + 8;
-  k_outflow_sums<<<1, 1024, 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_RHO_U], c->g, io);
+  const double w = mode == FSGPU_FLOW_OUTFLOW_FIX ? 1.0 : c->g.dy;
+  k_outflow_sums<<<1, 1024, 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_RHO_U], c->g, w, io);
   FS_LAUNCHED();
   if (comm_allreduce(c, io, 2, COMM_SUM)) return 1;  // inflow lives on the first slab, outflow on the last
-  k_outflow_apply<<<1, 1024, 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_RHO_U], c->g, io, d_mass_error);
+  k_outflow_apply<<<1, 1024, 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_RHO_U], c->g, mode, total_flow, io,
+                                             d_mass_error);
   FS_LAUNCHED();
   return 0;
 }

@@ -21,6 +21,8 @@ struct fsgpu_ctx {
   Comm* comm = nullptr;       // null for a single rank
   cudaStream_t stream = nullptr;
   double rho_gas = 1, rho_liquid = 1, visc_gas = 1e-3, visc_liquid = 1e-3, sigma = 0;
+  int flow_mode = FSGPU_FLOW_OUTFLOW_FIX;  // what FSGPU_STEP_OUTFLOW_FIX applies (fsgpu_set_flow_control)
+  double flow_total = 0.0;
   double* slab = nullptr;              // one allocation for all fields
   double* f[FSGPU_NUM_FIELDS] = {};    // VIRTUAL field base pointers (allocation base - g.voff())
   double* ext_alloc[FSGPU_NUM_FIELDS] = {};  // extension fields: own allocations, made on first use
@@ -73,7 +75,7 @@ int fs_launch_dmomdt(fsgpu_ctx* c);
 int fs_launch_update_velocity(fsgpu_ctx* c, double dt);
 int fs_launch_momentum_update(fsgpu_ctx* c, double dt);
 int fs_launch_bconds(fsgpu_ctx* c);
-int fs_launch_outflow_fix(fsgpu_ctx* c, double* d_mass_error);
+int fs_launch_flow_control(fsgpu_ctx* c, int mode, double total_flow, double* d_mass_error);
 int fs_launch_divergence(fsgpu_ctx* c);
 // rhs = -vol*div/dt (+ Dirichlet row zeroing); if psd == NONE the mean over all cells is
 // subtracted (two passes).  div_from_uv: compute div on the fly from U,V and store it too.

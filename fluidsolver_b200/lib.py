@@ -32,6 +32,7 @@ LEFT, RIGHT, BOTTOM, TOP = 0, 1, 2, 3
 PSD_NONE, PSD_LEFT, PSD_RIGHT, PSD_BOTTOM, PSD_TOP = 0, 1, 2, 3, 4
 RELAX_JACOBI, RELAX_RBGS = 1, 2
 STEP_OUTFLOW_FIX, STEP_REBUILD_OPERATOR, STEP_DENSITY, STEP_CAPILLARY = 1, 2, 4, 8
+FLOW_OUTFLOW_FIX, FLOW_OUTFLOW_FIX_DY, FLOW_FORCE_TOTAL = 1, 2, 3
 
 DP = C.POINTER(C.c_double)
 
@@ -43,7 +44,7 @@ SYMBOLS = (
     "fsgpu_device_field", "fsgpu_stream", "fsgpu_set_bconds", "fsgpu_adjust_dt",
     "fsgpu_save_old_state", "fsgpu_save_old_velocity", "fsgpu_save_old_density",
     "fsgpu_calc_mid_time", "fsgpu_calc_dmomdt", "fsgpu_update_velocity", "fsgpu_momentum_update",
-    "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_calc_divergence",
+    "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_flow_control", "fsgpu_set_flow_control", "fsgpu_calc_divergence",
     "fsgpu_shift_pressure_to_zero", "fsgpu_correct_velocity", "fsgpu_abs_max", "fsgpu_abs_max_all",
     "fsgpu_calc_rho_visc_const", "fsgpu_calc_rho_visc_vof", "fsgpu_apply_neumann_bconds",
     "fsgpu_ps_create", "fsgpu_ps_destroy", "fsgpu_ps_set_operator", "fsgpu_ps_set_rhs",
@@ -111,6 +112,8 @@ def load():
     L.fsgpu_calc_conserved_quantities.argtypes = [vp, DP, DP, DP]
     L.fsgpu_monitor.argtypes = [vp, DP, DP, DP]
     L.fsgpu_outflow_fix.argtypes = [vp, DP]
+    L.fsgpu_flow_control.argtypes = [vp, C.c_int, C.c_double, DP, DP]
+    L.fsgpu_set_flow_control.argtypes = [vp, C.c_int, C.c_double]
     L.fsgpu_abs_max.argtypes = [vp, i32, DP]
     L.fsgpu_abs_max_all.argtypes = [vp, i32, DP]
     L.fsgpu_apply_neumann_bconds.argtypes = [vp, i32]
@@ -341,6 +344,17 @@ class FS:
         e = C.c_double()
         _chk(self.L.fsgpu_outflow_fix(self.h, C.byref(e) if want_error else None))
         return e.value
+
+    def flow_control(self, mode, total_flow=0.0):
+        """the channel drivers' ghost-column corrections (FLOW_OUTFLOW_FIX, FLOW_OUTFLOW_FIX_DY, FLOW_FORCE_TOTAL);
+        returns (inflow, outflow) before the correction"""
+        i, o = C.c_double(), C.c_double()
+        _chk(self.L.fsgpu_flow_control(self.h, mode, total_flow, C.byref(i), C.byref(o)))
+        return i.value, o.value
+
+    def set_flow_control(self, mode, total_flow=0.0):
+        """what STEP_OUTFLOW_FIX applies inside substep()/step()"""
+        _chk(self.L.fsgpu_set_flow_control(self.h, mode, total_flow))
 
     def calc_divergence(self):
         _chk(self.L.fsgpu_calc_divergence(self.h))

@@ -169,6 +169,19 @@ int fsgpu_apply_velocity_bconds(fsgpu_ctx* c);
 /* driver-level outflow correction of the channel cases, test/LaminarChannel.cpp:55-66,201-205;
  * mass_error (may be NULL) receives outflow - inflow before the fix */
 int fsgpu_outflow_fix(fsgpu_ctx* c, double* mass_error);
+/* the other channel drivers' variants of that correction, applied to the ghost columns U(-1, .) and
+ * U(NX+1, .) right after apply_velocity_bconds; inflow / outflow (may be NULL) receive the two
+ * fluxes as they were before the correction (dy-weighted for the last two modes) */
+enum {
+  FSGPU_FLOW_OUTFLOW_FIX = 1,    /* test/LaminarChannel.cpp:55-66,201-205 (= fsgpu_outflow_fix) */
+  FSGPU_FLOW_OUTFLOW_FIX_DY = 2, /* test/CustomDirichletChannel.cpp:61-72,197-202, scaling/Channel.cpp:208-213 */
+  FSGPU_FLOW_FORCE_TOTAL = 3     /* test/PeriodicChannel.cpp:56-67,193-203, scaling/Channel.cpp:196-206:
+                                    both columns shifted so that each carries total_flow */
+};
+int fsgpu_flow_control(fsgpu_ctx* c, int mode, double total_flow, double* inflow, double* outflow);
+/* which of the three FSGPU_STEP_OUTFLOW_FIX applies inside fsgpu_substep / fsgpu_step
+ * (default FSGPU_FLOW_OUTFLOW_FIX) */
+int fsgpu_set_flow_control(fsgpu_ctx* c, int mode, double total_flow);
 /* calc_divergence(curr.U, curr.V, dx, dy, div), src/Operators.hpp:32-41 -> FSGPU_DIV */
 int fsgpu_calc_divergence(fsgpu_ctx* c);
 /* shift_pressure_to_zero(dx, dy, delta_p), src/Operators.hpp:78-82 (on FSGPU_DELTA_P) */
@@ -251,7 +264,8 @@ int fsgpu_ps_num_distributed_levels(fsgpu_ps* s, int* n);
 /* ---- fused fast path used by our own drivers: one projection sub-iteration
  * (scaling/LidDrivenFlow.cpp:127-161) and one whole timestep (:121-163) ----------------------- */
 enum {
-  FSGPU_STEP_OUTFLOW_FIX = 1,       /* test/LaminarChannel.cpp:201-205 */
+  FSGPU_STEP_OUTFLOW_FIX = 1,       /* test/LaminarChannel.cpp:201-205, or the variant chosen with
+                                       fsgpu_set_flow_control */
   FSGPU_STEP_REBUILD_OPERATOR = 2,  /* set_pressure_operator every sub-iteration (two-phase
                                        drivers, test/StationaryDrop.cpp:357) */
   FSGPU_STEP_DENSITY = 4,           /* consistent mass transport before the momentum update

@@ -324,6 +324,42 @@ double fso_outflow_fix(fso_fs* fs) {
   return mass_error;
 }
 
+/* the channel drivers' corrections of the two ghost columns after apply_velocity_bconds:
+ * mode 1 test/LaminarChannel.cpp:55-66,201-205 (plain sums);
+ * mode 2 test/CustomDirichletChannel.cpp:61-72,197-202 = scaling/Channel.cpp:65-76,208-213 (sums weighted
+ *        with dy, the same correction formula -> only a fraction dy of the error is removed);
+ * mode 3 test/PeriodicChannel.cpp:56-67,193-203 = scaling/Channel.cpp:196-206: both columns are shifted
+ *        so that each carries total_flow. */
+double fso_flow_control(fso_fs* fs, int mode, double total_flow, double* io) {
+  if (mode == 1) {
+    double in = 0, out = 0;
+    for (int64_t j = -1; j < NY + 1; ++j) {
+      in += fs->rho_u[IU(-1, j)] * fs->U[IU(-1, j)];
+      out += fs->rho_u[IU(NX + 1, j)] * fs->U[IU(NX + 1, j)];
+    }
+    if (io) { io[0] = in; io[1] = out; }
+    return fso_outflow_fix(fs);
+  }
+  double inflow = 0, outflow = 0;
+  for (int64_t j = -1; j < NY + 1; ++j) {
+    inflow += fs->rho_u[IU(-1, j)] * fs->U[IU(-1, j)] * fs->dy;
+    outflow += fs->rho_u[IU(NX + 1, j)] * fs->U[IU(NX + 1, j)] * fs->dy;
+  }
+  if (io) { io[0] = inflow; io[1] = outflow; }
+  const double mass_error = outflow - inflow;
+  if (mode == 2) {
+    for (int64_t j = -1; j < NY + 1; ++j)
+      fs->U[IU(NX + 1, j)] -= mass_error / (fs->rho_u[IU(NX + 1, j)] * (double)(NY + 2));
+  } else {
+    const double ie = total_flow - inflow, oe = total_flow - outflow;
+    for (int64_t j = -1; j < NY + 1; ++j) {
+      fs->U[IU(-1, j)] += ie / (fs->rho_u[IU(-1, j)] * fs->dy * (double)(NY + 2));
+      fs->U[IU(NX + 1, j)] += oe / (fs->rho_u[IU(NX + 1, j)] * fs->dy * (double)(NY + 2));
+    }
+  }
+  return mass_error;
+}
+
 /* src/Operators.hpp:32-41: all cells incl. ghosts */
 void fso_calc_divergence(const fso_fs* fs, double* div) {
   for (int64_t i = -1; i < NX + 1; ++i)
@@ -694,7 +730,7 @@ int fso_step(fso_fs* fs, const fso_bconds* bc, fso_solver* s, const fso_step_opt
     fso_calc_dmomdt(fs, dmomU, dmomV);
     fso_update_velocity(fs, dmomU, dmomV, dt);
     fso_apply_velocity_bconds(fs, bc);
-    if (o->outflow_fix) fso_outflow_fix(fs);
+    if (o->outflow_fix) fso_flow_control(fs, o->outflow_fix, o->total_flow, NULL);
     fso_calc_divergence(fs, div);
     if (o->capillary) fso_capillary_divergence(fs, o->vf, o->curv, o->ilen, dt, div);
     if (op) {

@@ -61,6 +61,9 @@ void fso_update_velocity(fso_fs* fs, const double* dmomU, const double* dmomV, d
 void fso_apply_velocity_bconds(fso_fs* fs, const fso_bconds* bc);
 /* test/LaminarChannel.cpp:55-66,201-205 ; returns mass_error before the fix */
 double fso_outflow_fix(fso_fs* fs);
+/* mode 1/2/3 as fso_step_opts.outflow_fix; io[0] = inflow, io[1] = outflow before the correction
+ * (dy-weighted for modes 2 and 3); returns outflow - inflow */
+double fso_flow_control(fso_fs* fs, int mode, double total_flow, double* io);
 /* src/Operators.hpp:32-41 */
 void fso_calc_divergence(const fso_fs* fs, double* div);
 /* src/LinearSystem.hpp:32-122 ; op is [(nx+2)*(ny+2)][5] in Layout::F (i fastest),
@@ -118,12 +121,15 @@ int fso_solver_num_levels(const fso_solver* s);
 /* ---- whole sub-iteration / timestep, scaling/LidDrivenFlow.cpp:121-174 -------------------- */
 typedef struct {
   int num_subiter;
-  int outflow_fix;   /* test/LaminarChannel.cpp:201-205 */
+  int outflow_fix;   /* 0 none; 1 test/LaminarChannel.cpp:201-205; 2 the dy-weighted variant of
+                        test/CustomDirichletChannel.cpp:61-72,197-202 (scaling/Channel.cpp:208-213);
+                        3 the total-flow forcing of test/PeriodicChannel.cpp:56-67,193-203 */
   int psd;
   int rebuild_operator_each_subiter; /* two-phase drivers, test/StationaryDrop.cpp:357 */
   int density_update; /* consistent mass transport, test/StationaryDrop.cpp:274-293 */
   int capillary;      /* pressure-jump block, test/StationaryDrop.cpp:331-353 (needs vf, curv, ilen) */
   const double *vf, *curv, *ilen; /* cell fields (NX+2)x(NY+2); frozen during the step */
+  double total_flow;  /* outflow_fix == 3: the flux both ghost columns are forced to */
 } fso_step_opts;
 /* returns total PCG iterations of the step; *res = last residual */
 int fso_step(fso_fs* fs, const fso_bconds* bc, fso_solver* s, const fso_step_opts* o, double dt,

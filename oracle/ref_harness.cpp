@@ -78,6 +78,7 @@ struct SessionBase {
   virtual void pressure_jump(const double* vf, const double* curv, const double* ilen) = 0;
   virtual void interpolate_uv(double* ui, double* vi)                          = 0;
   virtual void conserved(double* mass, double* mx, double* my)                 = 0;
+  virtual double flow_control(int mode, double total_flow, double* io)         = 0;
   virtual void ib_implicit_euler(const double* ibu, const double* ibv, double dt) = 0;
   virtual void ib_semi_analytical(const double* dU, const double* dV, double dt, const double* ibu,
                                   const double* ibv)                           = 0;
@@ -267,6 +268,41 @@ struct Session final : SessionBase {
     if (res) *res = r;
     return static_cast<int>(it);
   }
+  // The reference keeps these corrections in its drivers; the statements below are the drivers' own
+  // (mode 1 test/LaminarChannel.cpp:55-66,201-205; mode 2 test/CustomDirichletChannel.cpp:61-72,197-202;
+  // mode 3 test/PeriodicChannel.cpp:56-67,193-203), instantiated on this harness' fields.
+  double flow_control(int mode, double total_flow, double* io) override {
+    Float inflow = 0, outflow = 0;
+    if (mode == 1) {
+      for_each_a(fs.ym, [&](Index j) {
+        inflow  += fs.curr.rho_u_stag(-G, j) * fs.curr.U(-G, j);
+        outflow += fs.curr.rho_u_stag(NX + G, j) * fs.curr.U(NX + G, j);
+      });
+    } else {
+      for_each_a(fs.ym, [&](Index j) {
+        inflow  += fs.curr.rho_u_stag(-G, j) * fs.curr.U(-G, j) * fs.dy;
+        outflow += fs.curr.rho_u_stag(NX + G, j) * fs.curr.U(NX + G, j) * fs.dy;
+      });
+    }
+    if (io) { io[0] = inflow; io[1] = outflow; }
+    const Float mass_error = outflow - inflow;
+    if (mode == 3) {
+      const Float inflow_error  = total_flow - inflow;
+      const Float outflow_error = total_flow - outflow;
+      for_each_a<Exec::Parallel>(fs.ym, [&](Index j) {
+        fs.curr.U(-G, j)     += inflow_error / (fs.curr.rho_u_stag(-G, j) * fs.dy *
+                                            static_cast<Float>(NY + 2 * G));
+        fs.curr.U(NX + G, j) += outflow_error / (fs.curr.rho_u_stag(NX + G, j) * fs.dy *
+                                                 static_cast<Float>(NY + 2 * G));
+      });
+    } else {
+      for_each_a<Exec::Parallel>(fs.ym, [&](Index j) {
+        fs.curr.U(NX + G, j) -=
+            mass_error / (fs.curr.rho_u_stag(NX + G, j) * static_cast<Float>(NY + 2 * G));
+      });
+    }
+    return mass_error;
+  }
   // The sub-iteration loop of scaling/LidDrivenFlow.cpp:124-161 with the variable-density
   // correction of test/LaminarChannel.cpp:222-233 and its outflow fix (:201-205).
   // phase_secs (optional, 4 entries): momentum(mid-time+dmomdt+update+bc), div+rhs, solve, correct.
@@ -299,18 +335,7 @@ struct Session final : SessionBase {
             (fs.old.rho_v_stag(i, j) * fs.old.V(i, j) + dt * dV(i, j)) / fs.curr.rho_v_stag(i, j);
       });
       ::apply_velocity_bconds(fs, bconds, 0.0);
-      if (o->outflow_fix) {
-        Float inflow = 0, outflow = 0;
-        for_each_a(fs.ym, [&](Index j) {
-          inflow  += fs.curr.rho_u_stag(-G, j) * fs.curr.U(-G, j);
-          outflow += fs.curr.rho_u_stag(NX + G, j) * fs.curr.U(NX + G, j);
-        });
-        const Float mass_error = outflow - inflow;
-        for_each_a<Exec::Parallel>(fs.ym, [&](Index j) {
-          fs.curr.U(NX + G, j) -=
-              mass_error / (fs.curr.rho_u_stag(NX + G, j) * static_cast<Float>(NY + 2 * G));
-        });
-      }
+      if (o->outflow_fix) flow_control(o->outflow_fix, o->total_flow, nullptr);
       auto t1 = clk::now();
       ::calc_divergence(fs.curr.U, fs.curr.V, fs.dx, fs.dy, div);
       if (o->capillary) {  // the calls of test/StationaryDrop.cpp:331-353 (curvature is an input)
@@ -426,6 +451,9 @@ void fsref_calc_pressure_jump(void* s, const double* vf, const double* curv, con
 }
 void fsref_interpolate_uv(void* s, double* ui, double* vi) { S->interpolate_uv(ui, vi); }
 void fsref_conserved(void* s, double* mass, double* mx, double* my) { S->conserved(mass, mx, my); }
+double fsref_flow_control(void* s, int mode, double total_flow, double* io) {
+  return S->flow_control(mode, total_flow, io);
+}
 void fsref_ib_implicit_euler(void* s, const double* ibu, const double* ibv, double dt) {
   S->ib_implicit_euler(ibu, ibv, dt);
 }

@@ -71,6 +71,48 @@ def couette_l1_errors(U, nx, ny):
     return out
 
 
+CHANNEL215_TOTAL_FLOW = 0.5  # (Y_MAX - Y_MIN) * U * RHO, test/PeriodicChannel.cpp:39, test/CustomDirichletChannel.cpp:39
+
+
+def channel215_state(oracle, seed=None, backflow=False):
+    """test/PeriodicChannel.cpp:21-39,147-149 = test/CustomDirichletChannel.cpp:21-40,146-148: 215 x 43 cells on
+    5 x 1, rho = 0.5, mu = 1e-3, U = 1 on the interior faces, V = 0 (seed: a small random V on top;
+    backflow: the last face rows carry U in [-0.5, 1] so that a clipped Neumann outlet has something to clip)"""
+    nx, ny = 215, 43
+    st = State(nx, ny, 5.0 / nx, 1.0 / ny, rho_gas=0.5, rho_liquid=0.5, visc_gas=1e-3, visc_liquid=1e-3)
+    oracle.calc_rho_visc_const(st)
+    st.a["U"][1:nx + 2, 1:ny + 1] = 1.0
+    if seed is not None:
+        rng = np.random.default_rng(seed)
+        st.a["V"][1:nx + 1, 1:ny + 2] = 0.05 * rng.uniform(-1, 1, (nx, ny + 1))
+        if backflow:
+            st.a["U"][nx - 1:nx + 2, 1:ny + 1] = rng.uniform(-0.5, 1.0, (3, ny))
+    return st
+
+
+def periodic_channel_bc():
+    """test/PeriodicChannel.cpp:46-52: periodic left / right, no-slip walls"""
+    return BConds(kind=(PERIODIC, PERIODIC, DIRICHLET, DIRICHLET), u_val=(0.0,) * 4, v_val=(0.0,) * 4)
+
+
+def custom_channel_bc(ny=43, clipped=False):
+    """test/CustomDirichletChannel.cpp:46-56 (function inlet U(y) = dpdx / (2 mu) (y^2 - y), Neumann outlet,
+    no-slip walls); clipped=True is scaling/Channel.cpp:48-59"""
+    visc, rho = 1e-3, 0.5
+    dpdx = -12.0 * visc * CHANNEL215_TOTAL_FLOW / rho
+    ym = (np.arange(-1, ny + 1) + 0.5) / ny
+    prof = dpdx / (2.0 * visc) * (ym * ym - ym)
+    return BConds(kind=(DIRICHLET, NEUMANN, DIRICHLET, DIRICHLET), u_val=(0.0,) * 4, v_val=(0.0,) * 4,
+                  u_prof=(prof, None, None, None), clipped=(False, clipped, False, False))
+
+
+def channel215_cases():
+    """name -> (bconds, ghost-column correction mode (include/fsgpu.h FSGPU_FLOW_*), total flow, backflow)"""
+    return {"periodic215x43": (periodic_channel_bc(), 3, CHANNEL215_TOTAL_FLOW, False),   # test/PeriodicChannel.cpp
+            "customdirichlet215x43": (custom_channel_bc(), 2, 0.0, False),             # test/CustomDirichletChannel.cpp
+            "clippedchannel215x43": (custom_channel_bc(clipped=True), 2, 0.0, True)}   # scaling/Channel.cpp
+
+
 def profile_bcs(nx, ny, seed=5):
     """two FlowBConds with function-pointer Dirichlet sides (src/BoundaryConditions.hpp:15-17) given
     as per-point tables: every side and component, and a mix with constants / Neumann"""

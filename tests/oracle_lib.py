@@ -48,11 +48,14 @@ class CSolverOpts(C.Structure):
 class CStepOpts(C.Structure):
     _fields_ = [("num_subiter", C.c_int), ("outflow_fix", C.c_int), ("psd", C.c_int),
                 ("rebuild_operator_each_subiter", C.c_int), ("density_update", C.c_int),
-                ("capillary", C.c_int), ("vf", DP), ("curv", DP), ("ilen", DP)]
+                ("capillary", C.c_int), ("vf", DP), ("curv", DP), ("ilen", DP), ("total_flow", C.c_double)]
 
 
-def _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary):
+def _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary, total_flow=0.0):
+    """outflow_fix: 0 none, 1 LaminarChannel, 2 CustomDirichletChannel (dy-weighted), 3 PeriodicChannel
+    (both ghost columns forced to total_flow)"""
     o = CStepOpts(num_subiter, outflow_fix, psd, rebuild, int(density), int(capillary is not None))
+    o.total_flow = total_flow
     if capillary is not None:
         o._keep = [np.ascontiguousarray(a, dtype=np.float64) for a in capillary]
         o.vf, o.curv, o.ilen = (a.ctypes.data_as(DP) for a in o._keep)
@@ -151,6 +154,8 @@ class Oracle:
         L.fso_adjust_dt.restype = C.c_double
         L.fso_adjust_dt.argtypes = [C.POINTER(CFs), C.c_double, C.c_double]
         L.fso_outflow_fix.restype = C.c_double
+        L.fso_flow_control.restype = C.c_double
+        L.fso_flow_control.argtypes = [C.POINTER(CFs), C.c_int, C.c_double, DP]
         L.fso_abs_max.restype = C.c_double
         L.fso_abs_max.argtypes = [DP, C.c_int64, C.c_int64, C.c_int]
         L.fso_calc_mid_time.argtypes = [DP, DP, C.c_int64]
@@ -235,6 +240,12 @@ class Oracle:
     def outflow_fix(self, st):
         return self.lib.fso_outflow_fix(C.byref(st.cstruct()))
 
+    def flow_control(self, st, mode, total_flow=0.0):
+        """-> (inflow, outflow) before the correction"""
+        io = np.zeros(2)
+        self.lib.fso_flow_control(C.byref(st.cstruct()), mode, total_flow, _ptr(io))
+        return io[0], io[1]
+
     def calc_divergence(self, st):
         div = np.zeros((st.nx + 2, st.ny + 2))
         self.lib.fso_calc_divergence(C.byref(st.cstruct()), _ptr(div))
@@ -274,10 +285,10 @@ class Oracle:
         return OracleSolver(self, nx, ny, CSolverOpts(tol, max_iter, max_levels, relax_type, skip_relax))
 
     def step(self, st, bc, solver, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0, density=0,
-             capillary=None):
+             capillary=None, total_flow=0.0):
         """capillary = (vf, curv, interface_length) cell arrays, or None"""
         res = C.c_double(0)
-        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary)
+        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary, total_flow)
         it = self.lib.fso_step(C.byref(st.cstruct()), C.byref(bc.cstruct()), solver.h, C.byref(o), dt,
                                C.byref(res))
         return it, res.value
@@ -362,6 +373,8 @@ class Ref:
             L.fsref_calc_pressure_jump.argtypes = [C.c_void_p, DP, DP, DP]
             L.fsref_interpolate_uv.argtypes = [C.c_void_p, DP, DP]
             L.fsref_conserved.argtypes = [C.c_void_p, DP, DP, DP]
+            L.fsref_flow_control.argtypes = [C.c_void_p, C.c_int, C.c_double, DP]
+            L.fsref_flow_control.restype = C.c_double
             L.fsref_ib_implicit_euler.argtypes = [C.c_void_p, DP, DP, C.c_double]
             L.fsref_ib_semi_analytical.argtypes = [C.c_void_p, DP, DP, C.c_double, DP, DP]
             L.fsref_set_threads.argtypes = [C.c_int]
@@ -472,10 +485,15 @@ class Ref:
     def ib_semi_analytical(self, dU, dV, dt, ibu, ibv):
         self.lib().fsref_ib_semi_analytical(self.h, _ptr(dU), _ptr(dV), dt, _ptr(ibu), _ptr(ibv))
 
+    def flow_control(self, mode, total_flow=0.0):
+        io = np.zeros(2)
+        self.lib().fsref_flow_control(self.h, mode, total_flow, _ptr(io))
+        return io[0], io[1]
+
     def step(self, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0, phases=None, density=0,
-             capillary=None):
+             capillary=None, total_flow=0.0):
         res = C.c_double(0)
-        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary)
+        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary, total_flow)
         ph = _ptr(phases) if phases is not None else None
         it = self.lib().fsref_step(self.h, C.byref(o), dt, C.byref(res), ph)
         return it, res.value

@@ -138,3 +138,72 @@ def test_misc_vs_reference_golden(F, oracle):
     for n, k in (("RHO_U", "rho_u"), ("RHO_V", "rho_v"), ("VISC", "visc")):
         assert rel_inf(fs.download(n), g[k]) <= 1e-12, n
     fs.close()
+
+
+CHANNEL215 = ["periodic215x43", "customdirichlet215x43", "clippedchannel215x43"]
+
+
+def _channel215(oracle, name):
+    from cases import channel215_cases, channel215_state
+    bc, mode, total, backflow = channel215_cases()[name]
+    st = channel215_state(oracle, seed=8, backflow=backflow)
+    oracle.apply_velocity_bconds(st, bc)
+    return st, bc, mode, total
+
+
+@pytest.mark.parametrize("name", CHANNEL215)
+def test_channel215_drivers_vs_reference_golden(F, oracle, name):
+    """test/PeriodicChannel.cpp (total-flow forcing of both ghost columns), test/CustomDirichletChannel.cpp
+    (function inlet, dy-weighted outflow correction) and scaling/Channel.cpp (clipped Neumann outlet with
+    backflow): fsgpu_flow_control alone, then timesteps through fsgpu_step with
+    fsgpu_set_flow_control, against the committed output of the unmodified reference"""
+    from cases import rel_inf
+    g = np.load(os.path.join(GOLD, f"run_{name}.npz"))
+    st, bc, mode, total = _channel215(oracle, name)
+    fs = to_gpu(F, st, bc)
+    io = fs.flow_control(mode, total)
+    assert np.allclose(io, g["flow_io"], rtol=1e-13, atol=0)
+    assert rel_inf(fs.download("U"), g["flow_U"]) <= 1e-12
+    if mode == F.FLOW_FORCE_TOTAL:
+        assert np.allclose(fs.flow_control(mode, total), total, rtol=1e-12)
+    fs.upload("U", st.U)
+    fs.set_flow_control(mode, total)
+    ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
+    ps.set_pressure_operator()
+    for k, dt_ref in enumerate(g["dts"]):
+        assert fs.adjust_dt(0.9, 0.1) == pytest.approx(float(dt_ref), rel=1e-9)
+        res, it = fs.step(ps, float(dt_ref), 2, F.STEP_OUTFLOW_FIX)
+        assert res < 1e-12 and abs(it - int(g["its"][k])) <= max(3, 0.35 * int(g["its"][k]))
+    U, V, p = fs.download("U"), fs.download("V"), fs.download("P")
+    ev = vel_err(U, V, g["U"], g["V"])
+    ep = rel_l2(p - p.mean(), g["p"] - g["p"].mean())
+    print(f"\n[{name}] velocity rel L2 {ev:.3e}, pressure rel L2 {ep:.3e}")
+    assert ev <= 1e-10 and ep <= 1e-8
+    ps.close()
+    fs.close()
+
+
+@pytest.mark.parametrize("name", CHANNEL215[:2])
+def test_channel215_drivers_slabs(F, oracle, name):
+    """the same drivers on 3 slab contexts (in-process transport) vs one context: the inlet sum lives
+    on the first slab, the outlet sum on the last, the periodic wrap-around between the two"""
+    from test_gpu_slab import run_ranks, run_single
+    st, bc, mode, total = _channel215(oracle, name)
+
+    def body(fs, r):
+        fs.set_flow_control(mode, total)
+        ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
+        ps.set_pressure_operator()
+        hist = [fs.flow_control(mode, total)]
+        for _ in range(2):
+            dt = fs.adjust_dt(0.9, 0.1)
+            fs.step(ps, dt, 2, F.STEP_OUTFLOW_FIX)
+            hist.append(dt)
+        ps.close()
+        return hist
+
+    a, ra = run_ranks(F, st, bc, 3, body, fields=("U", "V", "P"))
+    b, rb = run_single(F, st, bc, body, fields=("U", "V", "P"))
+    assert all(x == ra[0] for x in ra)
+    assert np.allclose(ra[0][0], rb[0], rtol=1e-13) and ra[0][1:] == pytest.approx(rb[1:], rel=1e-12)
+    assert vel_err(a["U"], a["V"], b["U"], b["V"]) <= 1e-10
