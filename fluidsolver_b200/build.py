@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "csrc", "build")
 LIB = os.path.join(HERE, "libfsgpu.so")
 SOURCES = ["stencil.cu", "bconds.cu", "project.cu", "twophase.cu", "solver_setup.cu", "solver_cycle.cu",
-           "solver_pcg.cu", "comm.cu", "api.cu"]
+           "solver_pcg.cu", "comm.cu", "output.cu", "api.cu"]
 NO_FMA = {"solver_setup.cu"}
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

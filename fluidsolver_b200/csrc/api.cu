@@ -63,22 +63,6 @@ void fs_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-#define FS_CHECK_CTX(c)                           \
-  do {                                            \
-    if (!(c)) {                                   \
-      fs_set_error("%s: null context", __func__); \
-      return 1;                                   \
-    }                                             \
-    FS_CUDA(cudaSetDevice((c)->device));          \
-  } while (0)
-#define FS_CHECK_FIELD(f)                                  \
-  do {                                                     \
-    if ((f) < 0 || (f) >= FSGPU_NUM_FIELDS) {              \
-      fs_set_error("%s: bad field id %d", __func__, (f));  \
-      return 1;                                            \
-    }                                                      \
-    if (fs_ensure_field(c, (f))) return 1;                 \
-  } while (0)
 
 extern "C" {
 
@@ -204,6 +188,7 @@ int fsgpu_destroy(fsgpu_ctx* c) {
     if (c->ext_alloc[f]) cudaFree(c->ext_alloc[f]);
   cudaFree(c->part);
   cudaFree(c->ticket);
+  fs_output_release(c);
   cudaFree(c->red_out);
   cudaFreeHost(c->h_red);
   cudaStreamDestroy(c->stream);

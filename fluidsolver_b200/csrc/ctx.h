@@ -34,7 +34,26 @@ struct fsgpu_ctx {
   unsigned int* ticket = nullptr;
   double* red_out = nullptr;    // device result slots (8 doubles)
   double* h_red = nullptr;      // pinned mirror
+  struct OutStage* out = nullptr;  // output.cu: pinned / device staging of the file writers (made on first use)
 };
+
+// argument checks of the C-ABI entry points (api.cu, output.cu)
+#define FS_CHECK_CTX(c)                           \
+  do {                                            \
+    if (!(c)) {                                   \
+      fs_set_error("%s: null context", __func__); \
+      return 1;                                   \
+    }                                             \
+    FS_CUDA(cudaSetDevice((c)->device));          \
+  } while (0)
+#define FS_CHECK_FIELD(f)                                  \
+  do {                                                     \
+    if ((f) < 0 || (f) >= FSGPU_NUM_FIELDS) {              \
+      fs_set_error("%s: bad field id %d", __func__, (f));  \
+      return 1;                                            \
+    }                                                      \
+    if (fs_ensure_field(c, (f))) return 1;                 \
+  } while (0)
 
 // field classes: extents of the ghost-inclusive reference array
 static inline void field_extent(const Geom& g, int field, int64_t* m, int64_t* n) {
@@ -68,6 +87,9 @@ int comm_allreduce(fsgpu_ctx* c, double* dev, int64_t n, int op);
 int comm_sendrecv(fsgpu_ctx* c, int peer, const double* const* send, double* const* recv, int narr, int64_t n);
 // halo rows of flow fields (ids), h rows each
 int fs_exchange_fields(fsgpu_ctx* c, const int* fields, int n, int h);
+
+// ---- output.cu -------------------------------------------------------------------------------
+void fs_output_release(fsgpu_ctx* c);
 
 // ---- stencil.cu -------------------------------------------------------------------------------
 int fs_launch_mid_time(fsgpu_ctx* c);

@@ -44,7 +44,8 @@ SYMBOLS = (
     "fsgpu_device_field", "fsgpu_stream", "fsgpu_set_bconds", "fsgpu_adjust_dt",
     "fsgpu_save_old_state", "fsgpu_save_old_velocity", "fsgpu_save_old_density",
     "fsgpu_calc_mid_time", "fsgpu_calc_dmomdt", "fsgpu_update_velocity", "fsgpu_momentum_update",
-    "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_flow_control", "fsgpu_set_flow_control", "fsgpu_calc_divergence",
+    "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_flow_control", "fsgpu_set_flow_control",
+    "fsgpu_to_npy", "fsgpu_to_npy_state", "fsgpu_npy_write_host", "fsgpu_write_vtk", "fsgpu_calc_divergence",
     "fsgpu_shift_pressure_to_zero", "fsgpu_correct_velocity", "fsgpu_abs_max", "fsgpu_abs_max_all",
     "fsgpu_calc_rho_visc_const", "fsgpu_calc_rho_visc_vof", "fsgpu_apply_neumann_bconds",
     "fsgpu_ps_create", "fsgpu_ps_destroy", "fsgpu_ps_set_operator", "fsgpu_ps_set_rhs",
@@ -114,6 +115,11 @@ def load():
     L.fsgpu_outflow_fix.argtypes = [vp, DP]
     L.fsgpu_flow_control.argtypes = [vp, C.c_int, C.c_double, DP, DP]
     L.fsgpu_set_flow_control.argtypes = [vp, C.c_int, C.c_double]
+    L.fsgpu_to_npy.argtypes = [vp, i32, C.c_char_p]
+    L.fsgpu_to_npy_state.argtypes = [vp, C.c_char_p, DP, DP]
+    L.fsgpu_npy_write_host.argtypes = [C.c_char_p, DP, i64, i64]
+    L.fsgpu_write_vtk.argtypes = [vp, C.c_char_p, dbl, DP, DP, i32, C.POINTER(i32), C.POINTER(C.c_char_p), i32,
+                                  C.POINTER(i32), C.POINTER(C.c_char_p)]
     L.fsgpu_abs_max.argtypes = [vp, i32, DP]
     L.fsgpu_abs_max_all.argtypes = [vp, i32, DP]
     L.fsgpu_apply_neumann_bconds.argtypes = [vp, i32]
@@ -203,6 +209,14 @@ def field_shape(name: str, nx: int, ny: int):
     if name in V_LIKE:
         return (nx + 2, ny + 3)
     return (nx + 2, ny + 2)
+
+
+def npy_write_host(filename, arr):
+    """the host half of FS.to_npy (src/IO.hpp:25-95 + payload) on a 1-D or 2-D float64 array"""
+    a = np.ascontiguousarray(arr, dtype=np.float64)
+    assert a.ndim in (1, 2)
+    _chk(load().fsgpu_npy_write_host(os.fsencode(filename), a.ctypes.data_as(DP), a.shape[0],
+                                     a.shape[1] if a.ndim == 2 else 0))
 
 
 class FS:
@@ -419,6 +433,43 @@ class FS:
         return a.value, b.value, d.value
 
     # ---- fused path ---------------------------------------------------------------------------
+    # ---- file output from the device buffers (src/IO.hpp, src/VTKWriter.hpp) -----------------------
+    @staticmethod
+    def _coords(x, y):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        return x, y
+
+    def grid_coords(self, x_min=0.0, y_min=0.0):
+        """fs.x / fs.y of init_grid (src/FS.hpp:55-73) including their ghost entries"""
+        return (x_min + np.arange(-1, self.nx + 2, dtype=np.float64) * self.dx,
+                y_min + np.arange(-1, self.ny + 2, dtype=np.float64) * self.dy)
+
+    def to_npy(self, name, filename):
+        _chk(self.L.fsgpu_to_npy(self.h, FIELD_ID[name], os.fsencode(filename)))
+
+    def to_npy_state(self, directory, x=None, y=None):
+        """to_npy(directory, fs), src/IO.hpp:231-269 (x, y: fs.x / fs.y incl. ghosts, or None to skip them)"""
+        if x is None or y is None:
+            _chk(self.L.fsgpu_to_npy_state(self.h, os.fsencode(directory), None, None))
+            return
+        x, y = self._coords(x, y)
+        assert x.size == self.nx + 3 and y.size == self.ny + 3
+        _chk(self.L.fsgpu_to_npy_state(self.h, os.fsencode(directory), x.ctypes.data_as(DP), y.ctypes.data_as(DP)))
+
+    def write_vtk(self, filename, t, x, y, scalars=(), vectors=()):
+        """VTKWriter::write, src/VTKWriter.hpp:127-152. scalars: [(vtk name, field)], vectors: [(vtk name,
+        x field, y field)] with cell fields ("P", "DIV", "UI", "VI", ...)"""
+        x, y = self._coords(x, y)
+        assert x.size == self.nx + 3 and y.size == self.ny + 3
+        ns, nv = len(scalars), len(vectors)
+        sf = (C.c_int32 * max(ns, 1))(*[FIELD_ID[f] for _, f in scalars])
+        sn = (C.c_char_p * max(ns, 1))(*[n.encode() for n, _ in scalars])
+        vf = (C.c_int32 * max(2 * nv, 1))(*[FIELD_ID[f] for _, fx, fy in vectors for f in (fx, fy)])
+        vn = (C.c_char_p * max(nv, 1))(*[n.encode() for n, _, _ in vectors])
+        _chk(self.L.fsgpu_write_vtk(self.h, os.fsencode(filename), t, x.ctypes.data_as(DP), y.ctypes.data_as(DP),
+                                    ns, sf, sn, nv, vf, vn))
+
     def substep(self, ps, dt, flags=0):
         res, it = C.c_double(), C.c_int()
         _chk(self.L.fsgpu_substep(self.h, ps.h, dt, flags, C.byref(res), C.byref(it)))

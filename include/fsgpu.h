@@ -261,6 +261,29 @@ int fsgpu_ps_num_levels(fsgpu_ps* s, int* n);
  * of levels for a single rank. */
 int fsgpu_ps_num_distributed_levels(fsgpu_ps* s, int* n);
 
+/* ---- file output from the device buffers --------------------------
+ * Files are byte-identical to the reference's.  x and y are the reference's fs.x / fs.y arrays
+ * including their ghost entries (NX + 3 and NY + 3 doubles, fs.x.get_data()).  With slab contexts
+ * the calls are collective: every rank writes its own rows (npy) or columns (VTK) of the same
+ * file at their offsets, rank 0 adds headers and coordinates; the file is complete once every
+ * rank has returned. */
+/* to_npy(filename, Field2D), src/IO.hpp:204-228: .npy v1.0, '<f8', C order, shape incl. ghosts */
+int fsgpu_to_npy(fsgpu_ctx* c, int field, const char* filename);
+/* to_npy(directory, fs), src/IO.hpp:231-269: x, xm, y, ym (when x and y are given) and the twelve
+ * state fields under the reference's file names.  The directory is created if missing; unlike the
+ * reference (init_output_directory, src/IO.hpp:158-175) it is NOT emptied first. */
+int fsgpu_to_npy_state(fsgpu_ctx* c, const char* directory, const double* x, const double* y);
+/* the host half of the two calls above (src/IO.hpp:25-95 + payload), exported so that the byte
+ * format can be checked without a GPU; n = 0 writes a 1-D array of m entries */
+int fsgpu_npy_write_host(const char* filename, const double* data, int64_t m, int64_t n);
+/* VTKWriter::write, src/VTKWriter.hpp:39-152: legacy VTK, BINARY (big-endian), structured grid on
+ * the interior nodes, interior cell data in j-major order.  scalar_fields[n_scalars] and
+ * vector_fields[2 * n_vectors] (x then y component) are cell fields (FSGPU_P, FSGPU_DIV, FSGPU_UI,
+ * FSGPU_VI, FSGPU_VF ...); the transposition and byte swap run on the device. */
+int fsgpu_write_vtk(fsgpu_ctx* c, const char* filename, double t, const double* x, const double* y,
+                    int n_scalars, const int* scalar_fields, const char* const* scalar_names, int n_vectors,
+                    const int* vector_fields, const char* const* vector_names);
+
 /* ---- fused fast path used by our own drivers: one projection sub-iteration
  * (scaling/LidDrivenFlow.cpp:127-161) and one whole timestep (:121-163) ----------------------- */
 enum {

@@ -20,6 +20,7 @@
 
 #include "FS.hpp"
 #include "IB.hpp"
+#include "IO.hpp"
 #include "LinearSolver_StructHypre.hpp"
 #include "Operators.hpp"
 #include "Utility.hpp"
@@ -79,6 +80,8 @@ struct SessionBase {
   virtual void interpolate_uv(double* ui, double* vi)                          = 0;
   virtual void conserved(double* mass, double* mx, double* my)                 = 0;
   virtual double flow_control(int mode, double total_flow, double* io)         = 0;
+  virtual int to_npy(const char* dir)                                          = 0;
+  virtual int write_vtk(const char* dir, double t)                             = 0;
   virtual void ib_implicit_euler(const double* ibu, const double* ibv, double dt) = 0;
   virtual void ib_semi_analytical(const double* dU, const double* dV, double dt, const double* ibu,
                                   const double* ibv)                           = 0;
@@ -233,6 +236,22 @@ struct Session final : SessionBase {
     cp_out(*a, ui);
     ::interpolate_V(fs.curr.V, *a);
     cp_out(*a, vi);
+  }
+  // to_npy(directory, fs), src/IO.hpp:231-269 (removes and re-creates the directory)
+  int to_npy(const char* dir) override { return ::to_npy(std::string(dir), fs) ? 0 : 1; }
+  // the drivers' DataWriter (src/VTKWriter.hpp with FS_DISABLE_HDF, src/IO.hpp:13-16) set up as in
+  // test/PeriodicChannel.cpp:131-134: pressure, divergence, cell-centre velocity
+  int write_vtk(const char* dir, double t) override {
+    auto ui = std::make_unique<Field2D<Float, NX, NY, G>>();
+    auto vi = std::make_unique<Field2D<Float, NX, NY, G>>();
+    ::interpolate_U(fs.curr.U, *ui);
+    ::interpolate_V(fs.curr.V, *vi);
+    ::calc_divergence(fs.curr.U, fs.curr.V, fs.dx, fs.dy, div);
+    DataWriter<Float, NX, NY, G> w(dir, &fs.x, &fs.y);
+    w.add_scalar("pressure", &fs.p);
+    w.add_scalar("divergence", &div);
+    w.add_vector("velocity", ui.get(), vi.get());
+    return w.write(t) ? 0 : 1;
   }
   void conserved(double* mass, double* mx, double* my) override {
     ::calc_conserved_quantities(fs, *mass, *mx, *my);
@@ -451,6 +470,8 @@ void fsref_calc_pressure_jump(void* s, const double* vf, const double* curv, con
 }
 void fsref_interpolate_uv(void* s, double* ui, double* vi) { S->interpolate_uv(ui, vi); }
 void fsref_conserved(void* s, double* mass, double* mx, double* my) { S->conserved(mass, mx, my); }
+int fsref_to_npy(void* s, const char* dir) { return S->to_npy(dir); }
+int fsref_write_vtk(void* s, const char* dir, double t) { return S->write_vtk(dir, t); }
 double fsref_flow_control(void* s, int mode, double total_flow, double* io) {
   return S->flow_control(mode, total_flow, io);
 }

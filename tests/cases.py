@@ -230,3 +230,46 @@ def vel_err(U, V, Uref, Vref):
     num = np.linalg.norm((U - Uref).ravel()) ** 2 + np.linalg.norm((V - Vref).ravel()) ** 2
     den = np.linalg.norm(Uref.ravel()) ** 2 + np.linalg.norm(Vref.ravel()) ** 2
     return float(np.sqrt(num / max(den, 1e-300)))
+
+
+# ---- file formats of src/IO.hpp and src/VTKWriter.hpp, restated with numpy (checked against files
+# ---- written by the unmodified reference: tests/golden/io_random24x10.npz) ------------------------
+NPY_STATE_FILES = {"visc": "VISC", "p": "P", "p_jump_u_stag": "P_JUMP_U", "p_jump_v_stag": "P_JUMP_V",
+                   "rho_u_stag": "RHO_U", "rho_v_stag": "RHO_V", "U": "U", "V": "V", "rho_u_stag_old": "RHO_U_OLD",
+                   "rho_v_stag_old": "RHO_V_OLD", "U_old": "U_OLD", "V_old": "V_OLD"}
+
+
+def grid_coords(st, x_min=0.0, y_min=0.0):
+    """fs.x, fs.y of init_grid (src/FS.hpp:55-73) including ghost entries"""
+    return (x_min + np.arange(-1, st.nx + 2, dtype=np.float64) * st.dx,
+            y_min + np.arange(-1, st.ny + 2, dtype=np.float64) * st.dy)
+
+
+def npy_bytes(a):
+    """src/IO.hpp:25-95: version 1.0 header padded to a multiple of 64 bytes, then the C-order payload"""
+    a = np.ascontiguousarray(a, dtype="<f8")
+    h = "{'descr': '<f8', 'fortran_order': False, 'shape': (" + "".join(f"{n}, " for n in a.shape) + "), }"
+    while (6 + 2 + 2 + len(h) + 1) % 64:
+        h += " "
+    h += "\n"
+    return b"\x93NUMPY\x01\x00" + len(h).to_bytes(2, "little") + h.encode() + a.tobytes()
+
+
+def vtk_bytes(t, x, y, scalars, vectors):
+    """src/VTKWriter.hpp:39-152. x, y incl. ghosts; scalars [(name, cell array incl. ghosts)], vectors
+    [(name, ax, ay)]; interior cells, j outer / i inner, big-endian doubles"""
+    nx, ny = x.size - 3, y.size - 3
+    be = lambda a: np.ascontiguousarray(a, dtype=">f8").tobytes()  # noqa: E731
+    out = (f"# vtk DataFile Version 2.0\nState of FluidSolver at time t={t:g}\nBINARY\nDATASET STRUCTURED_GRID\n"
+           f"DIMENSIONS {nx + 1} {ny + 1} 1\nPOINTS {(nx + 1) * (ny + 1)} double\n").encode()
+    pts = np.zeros((ny + 1, nx + 1, 3))
+    pts[:, :, 0] = x[1:nx + 2][None, :]
+    pts[:, :, 1] = y[1:ny + 2][:, None]
+    out += be(pts) + f"\n\nCELL_DATA {nx * ny}\n".encode()
+    for name, a in scalars:
+        out += f"SCALARS {name} double 1\nLOOKUP_TABLE default\n".encode() + be(a[1:-1, 1:-1].T) + b"\n\n"
+    for name, ax, ay in vectors:
+        v = np.zeros((ny, nx, 3))
+        v[:, :, 0], v[:, :, 1] = ax[1:-1, 1:-1].T, ay[1:-1, 1:-1].T
+        out += f"VECTORS {name} double\n".encode() + be(v) + b"\n\n"
+    return out

@@ -182,6 +182,29 @@ def misc(name="misc_random48x20"):
     print(name, out["adjust_dt_sigma"], out["diag"])
 
 
+def io_files(name="io_random24x10"):
+    """the files the unmodified reference writes for a seeded state: to_npy(directory, fs) (src/IO.hpp:231-269)
+    and the drivers' VTK DataWriter with pressure, divergence and cell-centre velocity
+    (src/VTKWriter.hpp, test/PeriodicChannel.cpp:131-134); every file as a byte array"""
+    import tempfile
+    st = random_state(24, 10, seed=2410)
+    r = Ref(st.nx, st.ny)
+    r.load(st)
+    out = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        d = os.path.join(tmp, "npy")  # to_npy removes and re-creates its directory
+        r.to_npy(d)
+        for f in sorted(os.listdir(d)):
+            out["npy_" + f[:-4]] = np.fromfile(os.path.join(d, f), dtype=np.uint8)
+        v = os.path.join(tmp, "vtk")
+        os.makedirs(v)
+        r.write_vtk(v, 0.125)
+        (f,) = os.listdir(v)
+        out["vtk"] = np.fromfile(os.path.join(v, f), dtype=np.uint8)
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
+    print(name, {k: v.size for k, v in out.items()})
+
+
 def solve_psd(name="solve_psd128"):
     """one PCG+PFMG solve per PSDirichlet side (src/LinearSystem.hpp:10,32-155; the two-phase drivers use
     PSDirichlet::RIGHT with all-Neumann velocity BCs, test/StationaryDrop.cpp:67-72,223-224) on the
@@ -209,6 +232,9 @@ if __name__ == "__main__":
         for nm in CHANNEL215:
             run_channel215(nm)
         sys.exit(0)
+    if "io" in sys.argv:
+        io_files()
+        sys.exit(0)
     if "psd" in sys.argv:
         solve_psd()
         sys.exit(0)
@@ -230,3 +256,4 @@ if __name__ == "__main__":
     solve_psd()
     for nm in CHANNEL215:
         run_channel215(nm)
+    io_files()

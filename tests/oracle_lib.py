@@ -374,6 +374,8 @@ class Ref:
             L.fsref_interpolate_uv.argtypes = [C.c_void_p, DP, DP]
             L.fsref_conserved.argtypes = [C.c_void_p, DP, DP, DP]
             L.fsref_flow_control.argtypes = [C.c_void_p, C.c_int, C.c_double, DP]
+            L.fsref_to_npy.argtypes = [C.c_void_p, C.c_char_p]
+            L.fsref_write_vtk.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
             L.fsref_flow_control.restype = C.c_double
             L.fsref_ib_implicit_euler.argtypes = [C.c_void_p, DP, DP, C.c_double]
             L.fsref_ib_semi_analytical.argtypes = [C.c_void_p, DP, DP, C.c_double, DP, DP]
@@ -484,6 +486,14 @@ class Ref:
 
     def ib_semi_analytical(self, dU, dV, dt, ibu, ibv):
         self.lib().fsref_ib_semi_analytical(self.h, _ptr(dU), _ptr(dV), dt, _ptr(ibu), _ptr(ibv))
+
+    def to_npy(self, directory):
+        """to_npy(directory, fs), src/IO.hpp:231-269 -- REMOVES and re-creates `directory`"""
+        assert self.lib().fsref_to_npy(self.h, os.fsencode(directory)) == 0
+
+    def write_vtk(self, directory, t):
+        """the drivers' DataWriter (pressure, divergence, velocity) -> directory/state_NNNNNN.vtk"""
+        assert self.lib().fsref_write_vtk(self.h, os.fsencode(directory), t) == 0
 
     def flow_control(self, mode, total_flow=0.0):
         io = np.zeros(2)

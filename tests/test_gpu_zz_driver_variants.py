@@ -207,3 +207,90 @@ def test_channel215_drivers_slabs(F, oracle, name):
     assert all(x == ra[0] for x in ra)
     assert np.allclose(ra[0][0], rb[0], rtol=1e-13) and ra[0][1:] == pytest.approx(rb[1:], rel=1e-12)
     assert vel_err(a["U"], a["V"], b["U"], b["V"]) <= 1e-10
+
+
+# ---- file output from the device buffers ------------------------------
+def _io_case():
+    from cases import grid_coords, random_state
+    st = random_state(24, 10, seed=2410)
+    return (st,) + grid_coords(st)
+
+
+def _vtk_inputs(fs):
+    fs.calc_divergence()
+    fs.interpolate_cell_centres()
+    return [("pressure", "P"), ("divergence", "DIV")], [("velocity", "UI", "VI")]
+
+
+@pytest.mark.parametrize("chunk", [None, "1024"])
+def test_npy_and_vtk_files_vs_reference_files(F, tmp_path, monkeypatch, chunk):
+    """fsgpu_to_npy_state and fsgpu_write_vtk byte for byte against the files the unmodified reference
+    writes for the same state (tests/golden/io_random24x10.npz); chunk = 1024 bytes forces the
+    double-buffered staging through many chunks"""
+    if chunk:
+        monkeypatch.setenv("FSGPU_OUT_CHUNK_BYTES", chunk)
+    g = np.load(os.path.join(GOLD, "io_random24x10.npz"))
+    st, x, y = _io_case()
+    fs = to_gpu(F, st)
+    d = tmp_path / "npy"
+    fs.to_npy_state(str(d), x, y)
+    names = sorted(k[4:] for k in g.files if k.startswith("npy_"))
+    assert sorted(f[:-4] for f in os.listdir(d)) == names
+    for k in names:
+        assert (d / (k + ".npy")).read_bytes() == g["npy_" + k].tobytes(), k
+    sc, ve = _vtk_inputs(fs)
+    f = tmp_path / "state_000000.vtk"
+    f.write_bytes(b"\0" * 40000)  # an older, longer file
+    fs.write_vtk(str(f), 0.125, x, y, sc, ve)
+    assert f.read_bytes() == g["vtk"].tobytes()
+    fs.close()
+
+
+@pytest.mark.parametrize("nx,ny", [(130, 67), (64, 200)])
+def test_vtk_and_npy_other_sizes(F, oracle, tmp_path, monkeypatch, nx, ny):
+    """sizes that are no multiple of the transpose tile, against the numpy restatement of the two
+    formats (tests/cases.py, itself checked against the reference's files)"""
+    from cases import grid_coords, npy_bytes, random_state, twophase_inputs, vtk_bytes
+    monkeypatch.setenv("FSGPU_OUT_CHUNK_BYTES", "65536")
+    st = random_state(nx, ny, seed=nx + ny)
+    x, y = grid_coords(st, x_min=-0.25, y_min=1.5)
+    vf = twophase_inputs(st, seed=1, random_vf=True)[0]
+    fs = to_gpu(F, st)
+    fs.upload("VF", vf)
+    sc, ve = _vtk_inputs(fs)
+    f = tmp_path / "s.vtk"
+    fs.write_vtk(str(f), 1e-5, x, y, sc + [("vof", "VF")], ve)
+    div = oracle.calc_divergence(st)
+    ui, vi = oracle.interpolate_UV(st)
+    ref = vtk_bytes(1e-5, x, y, [("pressure", st.a["p"]), ("divergence", fs.download("DIV")), ("vof", vf)],
+                    [("velocity", fs.download("UI"), fs.download("VI"))])
+    assert f.read_bytes() == ref
+    assert np.abs(fs.download("DIV") - div).max() <= 1e-12 * np.abs(div).max()
+    assert np.abs(fs.download("UI") - ui).max() <= 1e-14 and np.abs(fs.download("VI") - vi).max() <= 1e-14
+    for name in ("U", "V", "P"):
+        fs.to_npy(name, str(tmp_path / (name + ".npy")))
+        assert (tmp_path / (name + ".npy")).read_bytes() == npy_bytes(st.a[name if name != "P" else "p"])
+    fs.close()
+
+
+def test_output_files_from_slabs(F, oracle, tmp_path):
+    """3 slab contexts write their rows (npy) / columns (VTK) of the same files: identical bytes"""
+    from test_gpu_slab import run_ranks, run_single
+    from cases import cavity_bc, grid_coords, random_state
+    st = random_state(50, 23, seed=7)
+    x, y = grid_coords(st)
+
+    def body(tag):
+        def run(fs, r):
+            sc, ve = _vtk_inputs(fs)
+            fs.to_npy_state(str(tmp_path / tag), x, y)
+            fs.write_vtk(str(tmp_path / (tag + ".vtk")), 2.0, x, y, sc, ve)
+        return run
+
+    run_ranks(F, st, cavity_bc(), 3, body("slabs"), fields=("U",))
+    run_single(F, st, cavity_bc(), body("one"), fields=("U",))
+    assert (tmp_path / "slabs.vtk").read_bytes() == (tmp_path / "one.vtk").read_bytes()
+    files = sorted(os.listdir(tmp_path / "one"))
+    assert len(files) == 16 and files == sorted(os.listdir(tmp_path / "slabs"))
+    for f in files:
+        assert (tmp_path / "slabs" / f).read_bytes() == (tmp_path / "one" / f).read_bytes(), f
