@@ -21,6 +21,8 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <array>
+#include <string>
 #include <variant>
 #include <vector>
 
@@ -450,6 +452,77 @@ void calc_conserved_quantities(const FS<Float, NX, NY, NGHOST>& fs, Float& mass,
                                Float& momentum_y) {
   FSGPU_CHECK(fsgpu_calc_conserved_quantities(fs.ctx, &mass, &momentum_x, &momentum_y));
 }
+
+// ---- output (src/IO.hpp:178-269, src/VTKWriter.hpp) -----------------------------------------------
+// The files are written from the device buffers and are byte-identical to the reference's.
+// to_npy(filename, Field1D / Field2D): a field bound to a device field is written from HBM, any other
+// from its host array.
+template <typename Float, Index N, Index NGHOST>
+[[nodiscard]] bool to_npy(const std::string& filename, const Field1D<Float, N, NGHOST>& v) {
+  return fsgpu_npy_write_host(filename.c_str(), v.get_data(), v.size(), 0) == 0;
+}
+template <typename Float, Index M, Index N, Index NGHOST>
+[[nodiscard]] bool to_npy(const std::string& filename, const Field2D<Float, M, N, NGHOST>& f) {
+  if (f.bound()) return fsgpu_to_npy(f.context(), f.field_id(), filename.c_str()) == 0;
+  return fsgpu_npy_write_host(filename.c_str(), f.get_data(), M + 2 * NGHOST, N + 2 * NGHOST) == 0;
+}
+// to_npy(directory, fs), src/IO.hpp:231-269 (the directory is created, not emptied first)
+template <typename Float, Index NX, Index NY, Index NGHOST>
+[[nodiscard]] bool to_npy(const std::string& directory, const FS<Float, NX, NY, NGHOST>& fs) {
+  return fsgpu_to_npy_state(fs.ctx, directory.c_str(), fs.x.get_data(), fs.y.get_data()) == 0;
+}
+
+// VTKWriter (src/VTKWriter.hpp:14-152), the drivers' DataWriter when HDF5 is off (src/IO.hpp:13-16).
+// Registered fields must be device-bound cell fields: fs.p, fs.visc, and the div / Ui / Vi / rhoi / vf /
+// curv scratch fields once they went through calc_divergence / interpolate_* / calc_rho(vf, fs) /
+// calc_pressure_jump.  The file counter is per writer (the reference's is per template instantiation).
+template <typename Float, Index NX, Index NY, Index NGHOST>
+class VTKWriter {
+  using Cell = Field2D<Float, NX, NY, NGHOST>;
+  std::string m_output_dir;
+  const Field1D<Float, NX + 1, NGHOST>* m_x;
+  const Field1D<Float, NY + 1, NGHOST>* m_y;
+  std::vector<std::string> m_scalar_names, m_vector_names;
+  std::vector<const Cell*> m_scalar_values;
+  std::vector<std::array<const Cell*, 2>> m_vector_values;
+  Index m_write_counter = 0;
+
+ public:
+  VTKWriter(std::string output_dir, const Field1D<Float, NX + 1, NGHOST>* x, const Field1D<Float, NY + 1, NGHOST>* y)
+      : m_output_dir(std::move(output_dir)), m_x(x), m_y(y) {}
+  VTKWriter(const VTKWriter&)            = delete;
+  VTKWriter& operator=(const VTKWriter&) = delete;
+  void add_scalar(std::string name, const Cell* value) {
+    m_scalar_names.emplace_back(std::move(name));
+    m_scalar_values.push_back(value);
+  }
+  void add_vector(std::string name, const Cell* x_value, const Cell* y_value) {
+    m_vector_names.emplace_back(std::move(name));
+    m_vector_values.push_back({x_value, y_value});
+  }
+  bool write(Float t = -1.0) {
+    char name[32];
+    std::snprintf(name, sizeof name, "/state_%06lld.vtk", static_cast<long long>(m_write_counter++));
+    fsgpu_ctx* ctx = nullptr;
+    std::vector<int> sf, vf;
+    std::vector<const char*> sn, vn;
+    auto use = [&](const Cell* f, std::vector<int>& ids) {
+      ctx = fsgpu_shim::ctx_of(*f);
+      ids.push_back(f->field_id());
+    };
+    for (size_t k = 0; k < m_scalar_values.size(); ++k) { use(m_scalar_values[k], sf); sn.push_back(m_scalar_names[k].c_str()); }
+    for (size_t k = 0; k < m_vector_values.size(); ++k) {
+      use(m_vector_values[k][0], vf); use(m_vector_values[k][1], vf);
+      vn.push_back(m_vector_names[k].c_str());
+    }
+    if (!ctx) fsgpu_shim::check(1, "VTKWriter::write: no field registered");
+    return fsgpu_write_vtk(ctx, (m_output_dir + name).c_str(), t, m_x->get_data(), m_y->get_data(),
+                           static_cast<int>(sf.size()), sf.data(), sn.data(), static_cast<int>(vn.size()),
+                           vf.data(), vn.data()) == 0;
+  }
+};
+template <typename Float, Index NX, Index NY, Index NGHOST>
+using DataWriter = VTKWriter<Float, NX, NY, NGHOST>;
 
 // ---- LinearSolver_StructHypre (src/LinearSolver_StructHypre.hpp:28-192) ----------------------------
 enum class HypreSolver { GMRES, PCG, BiCGSTAB };   // only PCG + PFMG (the reference's defaults) exist here

@@ -66,6 +66,13 @@ int main(int argc, char**) {
   Float mass = 0, mx = 0, my = 0;
   calc_conserved_quantities(fs, mass, mx, my);
   const Float m = abs_max(fs.curr.U) + abs_max<true>(div) + mass + mx + my;
+  DataWriter<Float, NX, NY, NGHOST> data_writer("/tmp/fsgpu_shim_check", &fs.x, &fs.y);
+  data_writer.add_scalar("pressure", &fs.p);
+  data_writer.add_scalar("divergence", &div);
+  data_writer.add_vector("velocity", &Ui, &Vi);
+  const bool wrote = to_npy("/tmp/fsgpu_shim_check", fs) && data_writer.write(0.0) &&
+                     to_npy("/tmp/fsgpu_shim_check/ym.npy", fs.ym) && to_npy("/tmp/fsgpu_shim_check/div.npy", div);
+  if (!wrote) return 2;
   fill(fs.p, 0.0);
   fs.to_host();
   return m == m ? 0 : 1;
