@@ -273,3 +273,45 @@ def vtk_bytes(t, x, y, scalars, vectors):
         v[:, :, 0], v[:, :, 1] = ax[1:-1, 1:-1].T, ay[1:-1, 1:-1].T
         out += f"VECTORS {name} double\n".encode() + be(v) + b"\n\n"
     return out
+
+
+# ---- the convergence study of scaling/Channel.cpp (non-periodic variant) -----------------------------
+def channel_study_case(oracle, n):
+    """scaling/Channel.cpp:19-59,81-83,152-154: NY = 2^n + 1, NX = 5 NY on 5 x 1, rho = 0.5, mu = 1e-3,
+    U = 1, function inlet + clipped Neumann outlet + no-slip walls; -> (state, bconds)"""
+    ny = (1 << n) + 1
+    nx = 5 * ny
+    st = State(nx, ny, 5.0 / nx, 1.0 / ny, rho_gas=0.5, rho_liquid=0.5, visc_gas=1e-3, visc_liquid=1e-3)
+    oracle.calc_rho_visc_const(st)
+    st.a["U"][1:nx + 2, 1:ny + 1] = 1.0
+    bc = custom_channel_bc(ny, clipped=True)
+    oracle.apply_velocity_bconds(st, bc)
+    return st, bc
+
+
+def channel_study_errors(p, U, V, nx, ny, dx, visc=1e-3):
+    """scaling/Channel.cpp:253-300 -> (pressure_error, dpdx_error, U_error, V_error)"""
+    P = p[1:, 1:]    # P[i, j] = p(i, j), i >= 0
+    pe = np.abs(P[:nx, :ny] - P[:nx, :1]).sum() / (nx * ny)
+    jm = ny // 2
+    ref_dpdx = (P[nx // 2 + 1, jm] - P[nx // 2, jm]) / dx
+    dpdx = (P[1:nx, jm] - P[0:nx - 1, jm]) / dx
+    de = np.abs(ref_dpdx - dpdx).sum() / (nx - 1)
+    i = nx // 2
+    ym = (np.arange(ny) + 0.5) / ny
+    g = (P[i, :ny] - p[i, 1:ny + 1]) / dx    # (p(i, j) - p(i - 1, j)) / dx
+    diff = np.abs(U[i + 1, 1:ny + 1] - g / (2 * visc) * (ym * ym - ym))
+    ue = float(np.sum((ym[1:] - ym[:-1]) * 0.5 * (diff[1:] + diff[:-1])))
+    ve = np.abs(V[1:nx + 1, 1:ny + 2]).sum() / (nx * (ny + 1))
+    return float(pe), float(de), ue, float(ve)
+
+
+def run_channel_study(adjust_dt, step, t_end=20.0):
+    """the time loop of scaling/Channel.cpp:169-172,235: adjust_dt() -> dt, step(dt); -> number of steps"""
+    t, n = 0.0, 0
+    while t < t_end:
+        dt = min(adjust_dt(), t_end - t)
+        step(dt)
+        t += dt
+        n += 1
+    return n

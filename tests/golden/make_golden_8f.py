@@ -15,7 +15,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
 
-from cases import (CHANNEL215_TOTAL_FLOW, cavity_bc, cavity_state, channel215_state, couette_bc,  # noqa: E402
+from cases import (CHANNEL215_TOTAL_FLOW, channel_study_case, channel_study_errors, run_channel_study, cavity_bc, cavity_state, channel215_state, couette_bc,  # noqa: E402
                    couette_state, custom_channel_bc, ib_inputs, periodic_channel_bc, profile_bcs, random_state,
                    twophase_inputs)
 from oracle_lib import Oracle, Ref  # noqa: E402
@@ -205,6 +205,30 @@ def io_files(name="io_random24x10"):
     print(name, {k: v.size for k, v in out.items()})
 
 
+def channel_study(name="channel_study", ns=(3, 4, 5)):
+    """scaling/Channel.cpp run by the unmodified reference at its own settings (tol 1e-6, 50 iterations,
+    NUM_SUBITER 2, CFL 0.9, T_END 20) for NY = 2^n + 1: the four error measures of :253-300"""
+    out = {"n": np.array(ns)}
+    rows = []
+    for n in ns:
+        st, bc = channel_study_case(o, n)
+        r = Ref(st.nx, st.ny)
+        r.load(st)
+        r.set_bconds(bc)
+        r.solver_create(1e-6, 50)
+        r.solver_set_operator()
+        steps = run_channel_study(lambda: r.adjust_dt(0.9, 0.1), lambda dt: r.step(dt, 2, outflow_fix=2))
+        s2 = st.copy()
+        r.store(s2)
+        e = channel_study_errors(s2.a["p"], s2.U, s2.V, st.nx, st.ny, st.dx)
+        rows.append(e + (steps,))
+        print("study n", n, st.nx, st.ny, "steps", steps, "errors", e)
+        if n == ns[0]:
+            out["U_n%d" % n], out["p_n%d" % n] = s2.U, s2.a["p"]
+    out["errors"] = np.array(rows)
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
+
+
 def solve_psd(name="solve_psd128"):
     """one PCG+PFMG solve per PSDirichlet side (src/LinearSystem.hpp:10,32-155; the two-phase drivers use
     PSDirichlet::RIGHT with all-Neumann velocity BCs, test/StationaryDrop.cpp:67-72,223-224) on the
@@ -232,6 +256,9 @@ if __name__ == "__main__":
         for nm in CHANNEL215:
             run_channel215(nm)
         sys.exit(0)
+    if "study" in sys.argv:
+        channel_study()
+        sys.exit(0)
     if "io" in sys.argv:
         io_files()
         sys.exit(0)
@@ -257,3 +284,4 @@ if __name__ == "__main__":
     for nm in CHANNEL215:
         run_channel215(nm)
     io_files()
+    channel_study()
