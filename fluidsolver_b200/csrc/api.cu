@@ -382,6 +382,40 @@ static int abs_max_impl(fsgpu_ctx* c, int field, bool include_ghost, double* out
   *out = c->h_red[0];
   return 0;
 }
+static int reduce_impl(fsgpu_ctx* c, int field, int include_ghost, int op, double* out) {
+  FS_CHECK_CTX(c);
+  FS_CHECK_FIELD(field);
+  if (!out) { fs_set_error("null result pointer"); return 1; }
+  if (fs_launch_reduce_field(c, field, include_ghost != 0, op)) return 1;
+  if (read_red(c, 0, 1)) return 1;
+  *out = c->h_red[0];
+  return 0;
+}
+int fsgpu_integrate(fsgpu_ctx* c, int field, int include_ghost, double* out) {
+  return reduce_impl(c, field, include_ghost, 1, out);
+}
+int fsgpu_l1_norm(fsgpu_ctx* c, int field, int include_ghost, double* out) {
+  return reduce_impl(c, field, include_ghost, 2, out);
+}
+int fsgpu_calc_grad_of_centered_points(fsgpu_ctx* c, int f, int dfdx, int dfdy) {
+  FS_CHECK_CTX(c);
+  const int ids[3] = {f, dfdx, dfdy};
+  for (int q = 0; q < 3; ++q) {
+    FS_CHECK_FIELD(ids[q]);
+    int64_t m, n;
+    field_extent(c->g, ids[q], &m, &n);
+    if (m != c->g.nx + 2 || n != c->g.ny + 2) {
+      fs_set_error("fsgpu_calc_grad_of_centered_points: field %d is not a cell field", ids[q]);
+      return 1;
+    }
+  }
+  if (f == dfdx || f == dfdy || dfdx == dfdy) {
+    fs_set_error("fsgpu_calc_grad_of_centered_points: the three fields must differ");
+    return 1;
+  }
+  if (c->g.nx < 2 || c->g.ny < 2) { fs_set_error("fsgpu_calc_grad_of_centered_points: grid too small"); return 1; }
+  return fs_launch_grad_centered(c, f, dfdx, dfdy);
+}
 int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out) { return abs_max_impl(c, field, false, out); }
 int fsgpu_abs_max_all(fsgpu_ctx* c, int field, double* out) { return abs_max_impl(c, field, true, out); }
 

@@ -106,6 +106,7 @@ int fs_launch_shift_pressure(fsgpu_ctx* c);
 int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift);
 int fs_launch_cfl(fsgpu_ctx* c);               // 4 maxima -> red_out[0..3]
 int fs_launch_absmax(fsgpu_ctx* c, int field, bool include_ghost);  // -> red_out[0]
+int fs_launch_reduce_field(fsgpu_ctx* c, int field, bool include_ghost, int op);  // 0 max|f|, 1 sum, 2 sum|f| (* dx dy)
 int fs_launch_fill(fsgpu_ctx* c, int field, double v);
 int fs_launch_rho_visc_vof(fsgpu_ctx* c);
 int fs_launch_neumann(fsgpu_ctx* c, double* f, int64_t m, int64_t n);
@@ -123,3 +124,4 @@ int fs_launch_ib_semi_analytical(fsgpu_ctx* c, double dt);
 int fs_launch_interpolate(fsgpu_ctx* c);
 int fs_launch_conserved(fsgpu_ctx* c);  // -> red_out[4..6]
 int fs_launch_monitor(fsgpu_ctx* c);    // -> red_out[4..6]
+int fs_launch_grad_centered(fsgpu_ctx* c, int f, int dfdx, int dfdy);

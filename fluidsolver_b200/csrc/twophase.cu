@@ -252,6 +252,27 @@ k_monitor(const double* __restrict__ U, const double* __restrict__ V, double* __
   }
 }
 
+// calc_grad_of_centered_points, src/Operators.hpp:164-201 (NGHOST = 1): on every cell incl. ghosts, per
+// direction the central difference where both neighbours exist and the second-order one-sided
+// difference on the outermost ring
+__global__ void __launch_bounds__(BX* BY)
+k_grad_centered(const double* __restrict__ f, double* __restrict__ gx, double* __restrict__ gy, const Geom g) {
+  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
+  const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
+  if (a >= g.a_hi || b > g.ny + 1) return;
+  const int64_t k = g.idx(a, b), P = g.pitch;
+  const double f0 = f[k], tdx = 2.0 * g.dx, tdy = 2.0 * g.dy;
+  double x, y;
+  if (a == 0) x = (-3.0 * f0 + 4.0 * f[k + P] - f[k + 2 * P]) / tdx;
+  else if (a == g.nx + 1) x = (3.0 * f0 - 4.0 * f[k - P] + f[k - 2 * P]) / tdx;
+  else x = (f[k + P] - f[k - P]) / tdx;
+  if (b == 0) y = (-3.0 * f0 + 4.0 * f[k + 1] - f[k + 2]) / tdy;
+  else if (b == g.ny + 1) y = (3.0 * f0 - 4.0 * f[k - 1] + f[k - 2]) / tdy;
+  else y = (f[k + 1] - f[k - 1]) / tdy;
+  gx[k] = x;
+  gy[k] = y;
+}
+
 }  // namespace
 
 static dim3 face_grid(const Geom& g) {
@@ -394,6 +415,14 @@ int fs_launch_conserved(fsgpu_ctx* c) {  // -> red_out[4..6]
                                                   c->red_out + 4);
   FS_LAUNCHED();
   return comm_allreduce(c, c->red_out + 4, 3, COMM_SUM);
+}
+
+int fs_launch_grad_centered(fsgpu_ctx* c, int f, int dfdx, int dfdy) {
+  if (fs_exchange_fields(c, &f, 1, FS_RO)) return 1;  // neighbours a +- 1 (a +- 2 on the first / last row)
+  k_grad_centered<<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(c->f[f], c->f[dfdx], c->f[dfdy], c->g);
+  FS_LAUNCHED();
+  const int fl[2] = {dfdx, dfdy};
+  return fs_exchange_fields(c, fl, 2, FS_RO);
 }
 
 int fs_launch_monitor(fsgpu_ctx* c) {  // -> red_out[4..6]

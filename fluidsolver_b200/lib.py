@@ -22,7 +22,7 @@ FIELDS = ("VISC", "P", "P_JUMP_U", "P_JUMP_V", "RHO_U_OLD", "RHO_V_OLD", "U_OLD"
           "RHO_V", "U", "V", "DMOM_U", "DMOM_V", "DIV", "DELTA_P", "VF", "RHS",
           # extension fields, device memory allocated on first use
           "DRHO_U", "DRHO_V", "CURV", "INTERFACE_LENGTH", "PJ_OLD_U", "PJ_OLD_V", "UI", "VI", "RHOI",
-          "IB_CORR_U", "IB_CORR_V")
+          "IB_CORR_U", "IB_CORR_V", "GRAD_X", "GRAD_Y", "GRAD_XX", "GRAD_YY")
 FIELD_ID = {n: i for i, n in enumerate(FIELDS)}
 U_LIKE = {"P_JUMP_U", "RHO_U_OLD", "U_OLD", "RHO_U", "U", "DMOM_U", "DRHO_U", "PJ_OLD_U", "IB_CORR_U"}
 V_LIKE = {"P_JUMP_V", "RHO_V_OLD", "V_OLD", "RHO_V", "V", "DMOM_V", "DRHO_V", "PJ_OLD_V", "IB_CORR_V"}
@@ -45,6 +45,7 @@ SYMBOLS = (
     "fsgpu_save_old_state", "fsgpu_save_old_velocity", "fsgpu_save_old_density",
     "fsgpu_calc_mid_time", "fsgpu_calc_dmomdt", "fsgpu_update_velocity", "fsgpu_momentum_update",
     "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_flow_control", "fsgpu_set_flow_control",
+    "fsgpu_integrate", "fsgpu_l1_norm", "fsgpu_calc_grad_of_centered_points",
     "fsgpu_to_npy", "fsgpu_to_npy_state", "fsgpu_npy_write_host", "fsgpu_write_vtk", "fsgpu_calc_divergence",
     "fsgpu_shift_pressure_to_zero", "fsgpu_correct_velocity", "fsgpu_abs_max", "fsgpu_abs_max_all",
     "fsgpu_calc_rho_visc_const", "fsgpu_calc_rho_visc_vof", "fsgpu_apply_neumann_bconds",
@@ -121,6 +122,9 @@ def load():
     L.fsgpu_write_vtk.argtypes = [vp, C.c_char_p, dbl, DP, DP, i32, C.POINTER(i32), C.POINTER(C.c_char_p), i32,
                                   C.POINTER(i32), C.POINTER(C.c_char_p)]
     L.fsgpu_abs_max.argtypes = [vp, i32, DP]
+    L.fsgpu_integrate.argtypes = [vp, i32, i32, DP]
+    L.fsgpu_l1_norm.argtypes = [vp, i32, i32, DP]
+    L.fsgpu_calc_grad_of_centered_points.argtypes = [vp, i32, i32, i32]
     L.fsgpu_abs_max_all.argtypes = [vp, i32, DP]
     L.fsgpu_apply_neumann_bconds.argtypes = [vp, i32]
     L.fsgpu_ps_create.argtypes = [vp, C.POINTER(PsOpts), C.POINTER(vp)]
@@ -385,6 +389,22 @@ class FS:
         fn = self.L.fsgpu_abs_max_all if include_ghost else self.L.fsgpu_abs_max
         _chk(fn(self.h, FIELD_ID[name], C.byref(o)))
         return o.value
+
+    def integrate(self, name, include_ghost=False):
+        """integrate<INCLUDE_GHOST>(dx, dy, field), src/Operators.hpp:51-62"""
+        o = C.c_double()
+        _chk(self.L.fsgpu_integrate(self.h, FIELD_ID[name], int(include_ghost), C.byref(o)))
+        return o.value
+
+    def l1_norm(self, name, include_ghost=False):
+        """L1_norm<INCLUDE_GHOST>(dx, dy, field), src/Operators.hpp:65-76"""
+        o = C.c_double()
+        _chk(self.L.fsgpu_l1_norm(self.h, FIELD_ID[name], int(include_ghost), C.byref(o)))
+        return o.value
+
+    def calc_grad_of_centered_points(self, f, dfdx="GRAD_X", dfdy="GRAD_Y"):
+        """src/Operators.hpp:164-201 on cell fields"""
+        _chk(self.L.fsgpu_calc_grad_of_centered_points(self.h, FIELD_ID[f], FIELD_ID[dfdx], FIELD_ID[dfdy]))
 
     def calc_rho_visc_const(self):
         _chk(self.L.fsgpu_calc_rho_visc_const(self.h))

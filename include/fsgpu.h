@@ -65,6 +65,10 @@ enum {
   FSGPU_RHOI,          /* rhoi cell-centred rho   cell   src/Operators.hpp:22-29 */
   FSGPU_IB_CORR_U,     /* ib_corr_u_stag     U-like  src/IB.hpp:62-107 (input) */
   FSGPU_IB_CORR_V,     /* ib_corr_v_stag     V-like */
+  FSGPU_GRAD_X,        /* dfdx, dfdy of calc_grad_of_centered_points and two spare cell fields for its */
+  FSGPU_GRAD_Y,        /* second derivatives (src/Curvature.hpp:337-339)   cell */
+  FSGPU_GRAD_XX,
+  FSGPU_GRAD_YY,
   FSGPU_NUM_FIELDS
 };
 #define FSGPU_NUM_CORE_FIELDS (FSGPU_RHS + 1)
@@ -194,6 +198,13 @@ int fsgpu_correct_velocity(fsgpu_ctx* c, double dt);
  * abs_max<true>(field), the whole ghost-inclusive extent */
 int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out);
 int fsgpu_abs_max_all(fsgpu_ctx* c, int field, double* out);
+/* integrate<INCLUDE_GHOST>(dx, dy, field) and L1_norm<INCLUDE_GHOST>(dx, dy, field), src/Operators.hpp:51-76:
+ * (sum of the entries, or of their magnitudes) * dx * dy over the interior or the whole extent */
+int fsgpu_integrate(fsgpu_ctx* c, int field, int include_ghost, double* out);
+int fsgpu_l1_norm(fsgpu_ctx* c, int field, int include_ghost, double* out);
+/* calc_grad_of_centered_points(f, dx, dy, dfdx, dfdy), src/Operators.hpp:164-201: three distinct cell
+ * fields (e.g. FSGPU_VF -> FSGPU_GRAD_X, FSGPU_GRAD_Y); every cell incl. ghosts is written */
+int fsgpu_calc_grad_of_centered_points(fsgpu_ctx* c, int f, int dfdx, int dfdy);
 /* calc_rho(fs)/calc_visc(fs), src/FS.hpp:569-589 and calc_rho(vf,fs)/calc_visc(vf,fs),
  * src/FS.hpp:592-650 (uses FSGPU_VF) */
 int fsgpu_calc_rho_visc_const(fsgpu_ctx* c);

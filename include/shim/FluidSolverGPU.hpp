@@ -453,6 +453,29 @@ void calc_conserved_quantities(const FS<Float, NX, NY, NGHOST>& fs, Float& mass,
   FSGPU_CHECK(fsgpu_calc_conserved_quantities(fs.ctx, &mass, &momentum_x, &momentum_y));
 }
 
+// integrate / L1_norm (src/Operators.hpp:51-76) and calc_grad_of_centered_points (:164-201) on device-bound
+// fields; the gradient's outputs are bound to FSGPU_GRAD_X / FSGPU_GRAD_Y unless already bound elsewhere
+template <bool INCLUDE_GHOST = false, typename Float, Index M, Index N, Index NGHOST>
+Float integrate(Float, Float, const Field2D<Float, M, N, NGHOST>& field) {
+  double out = 0.0;
+  FSGPU_CHECK(fsgpu_integrate(fsgpu_shim::ctx_of(field), field.field_id(), INCLUDE_GHOST ? 1 : 0, &out));
+  return out;
+}
+template <bool INCLUDE_GHOST = false, typename Float, Index M, Index N, Index NGHOST>
+Float L1_norm(Float, Float, const Field2D<Float, M, N, NGHOST>& field) {
+  double out = 0.0;
+  FSGPU_CHECK(fsgpu_l1_norm(fsgpu_shim::ctx_of(field), field.field_id(), INCLUDE_GHOST ? 1 : 0, &out));
+  return out;
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void calc_grad_of_centered_points(const Field2D<Float, NX, NY, NGHOST>& f, Float, Float,
+                                  Field2D<Float, NX, NY, NGHOST>& dfdx, Field2D<Float, NX, NY, NGHOST>& dfdy) {
+  fsgpu_ctx* ctx = fsgpu_shim::ctx_of(f);
+  if (!dfdx.bound()) dfdx.bind(ctx, f.field_id() == FSGPU_GRAD_X ? FSGPU_GRAD_XX : FSGPU_GRAD_X);
+  if (!dfdy.bound()) dfdy.bind(ctx, f.field_id() == FSGPU_GRAD_Y ? FSGPU_GRAD_YY : FSGPU_GRAD_Y);
+  FSGPU_CHECK(fsgpu_calc_grad_of_centered_points(ctx, f.field_id(), dfdx.field_id(), dfdy.field_id()));
+}
+
 // ---- output (src/IO.hpp:178-269, src/VTKWriter.hpp) -----------------------------------------------
 // The files are written from the device buffers and are byte-identical to the reference's.
 // to_npy(filename, Field1D / Field2D): a field bound to a device field is written from HBM, any other

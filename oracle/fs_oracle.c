@@ -479,6 +479,51 @@ double fso_abs_max(const double* a, int64_t m, int64_t n, int include_ghost) {
   return r;
 }
 
+/* integrate<INCLUDE_GHOST> / L1_norm<INCLUDE_GHOST>, src/Operators.hpp:51-76, of an (m+2) x (n+2) field:
+ * serial sum in row-major order, then * dx * dy */
+double fso_integrate(const double* a, int64_t m, int64_t n, double dx, double dy, int include_ghost, int l1) {
+  double r = 0.0;
+  const int64_t lo = include_ghost ? -1 : 0;
+  for (int64_t i = lo; i < m - lo; ++i)
+    for (int64_t j = lo; j < n - lo; ++j) {
+      const double v = a[(j + 1) + (i + 1) * (n + 2)];
+      r += l1 ? fabs(v) : v;
+    }
+  return r * dx * dy;
+}
+
+/* calc_grad_of_centered_points, src/Operators.hpp:164-201, NGHOST = 1: central differences where both
+ * neighbours exist, second-order one-sided differences on the outermost (ghost) ring */
+void fso_grad_centered(const double* f, int64_t m, int64_t n, double dx, double dy, double* dfdx, double* dfdy) {
+#define F(i, j) f[(j) + 1 + ((i) + 1) * (n + 2)]
+#define GX(i, j) dfdx[(j) + 1 + ((i) + 1) * (n + 2)]
+#define GY(i, j) dfdy[(j) + 1 + ((i) + 1) * (n + 2)]
+  for (int64_t i = 0; i < m; ++i)
+    for (int64_t j = 0; j < n; ++j) {
+      GX(i, j) = (F(i + 1, j) - F(i - 1, j)) / (2.0 * dx);
+      GY(i, j) = (F(i, j + 1) - F(i, j - 1)) / (2.0 * dy);
+    }
+  for (int64_t i = -1; i < m + 1; ++i) {
+    if (i > -1 && i < m) {
+      GX(i, -1) = (F(i + 1, -1) - F(i - 1, -1)) / (2.0 * dx);
+      GX(i, n)  = (F(i + 1, n) - F(i - 1, n)) / (2.0 * dx);
+    }
+    GY(i, -1) = (-3.0 * F(i, -1) + 4.0 * F(i, 0) - F(i, 1)) / (2.0 * dy);
+    GY(i, n)  = (3.0 * F(i, n) - 4.0 * F(i, n - 1) + F(i, n - 2)) / (2.0 * dy);
+  }
+  for (int64_t j = -1; j < n + 1; ++j) {
+    GX(-1, j) = (-3.0 * F(-1, j) + 4.0 * F(0, j) - F(1, j)) / (2.0 * dx);
+    GX(m, j)  = (3.0 * F(m, j) - 4.0 * F(m - 1, j) + F(m - 2, j)) / (2.0 * dx);
+    if (j > -1 && j < n) {
+      GY(-1, j) = (F(-1, j + 1) - F(-1, j - 1)) / (2.0 * dy);
+      GY(m, j)  = (F(m, j + 1) - F(m, j - 1)) / (2.0 * dy);
+    }
+  }
+#undef F
+#undef GX
+#undef GY
+}
+
 /* src/BoundaryConditions.hpp:227-252 for an (m+2) x (n+2) field */
 void fso_apply_neumann_bconds(double* f, int64_t m, int64_t n) {
 #define F(i, j) f[(j) + 1 + ((i) + 1) * (n + 2)]

@@ -78,6 +78,9 @@ void fso_correct(fso_fs* fs, const double* dp, double dt);
 /* src/Utility.hpp:44-88: abs_max<INCLUDE_GHOST = false> of an (m+2) x (n+2) field: interior entries only
  * unless include_ghost */
 double fso_abs_max(const double* a, int64_t m, int64_t n, int include_ghost);
+/* integrate / L1_norm, src/Operators.hpp:51-76; calc_grad_of_centered_points, :164-201 */
+double fso_integrate(const double* a, int64_t m, int64_t n, double dx, double dy, int include_ghost, int l1);
+void fso_grad_centered(const double* f, int64_t m, int64_t n, double dx, double dy, double* dfdx, double* dfdy);
 /* src/FS.hpp:569-650 with src/BoundaryConditions.hpp:227-252 */
 void fso_calc_rho_visc_const(fso_fs* fs);
 void fso_calc_rho_visc_vof(fso_fs* fs, const double* vf);

@@ -81,6 +81,8 @@ struct SessionBase {
   virtual void conserved(double* mass, double* mx, double* my)                 = 0;
   virtual double flow_control(int mode, double total_flow, double* io)         = 0;
   virtual int to_npy(const char* dir)                                          = 0;
+  virtual double integrate_cell(const double* f, int include_ghost, int l1)    = 0;
+  virtual void grad_centered(const double* f, double* dfdx, double* dfdy)      = 0;
   virtual int write_vtk(const char* dir, double t)                             = 0;
   virtual void ib_implicit_euler(const double* ibu, const double* ibv, double dt) = 0;
   virtual void ib_semi_analytical(const double* dU, const double* dV, double dt, const double* ibu,
@@ -399,6 +401,20 @@ struct Session final : SessionBase {
     if (res) *res = r;
     return iters;
   }
+  // integrate / L1_norm (src/Operators.hpp:51-76) and calc_grad_of_centered_points (:164-201) on a cell field
+  double integrate_cell(const double* f, int include_ghost, int l1) override {
+    cp_in(div, f);
+    if (l1) return include_ghost ? ::L1_norm<true>(fs.dx, fs.dy, div) : ::L1_norm<false>(fs.dx, fs.dy, div);
+    return include_ghost ? ::integrate<true>(fs.dx, fs.dy, div) : ::integrate<false>(fs.dx, fs.dy, div);
+  }
+  void grad_centered(const double* f, double* dfdx, double* dfdy) override {
+    auto gx = std::make_unique<Field2D<Float, NX, NY, G>>();
+    auto gy = std::make_unique<Field2D<Float, NX, NY, G>>();
+    cp_in(div, f);
+    ::calc_grad_of_centered_points(div, fs.dx, fs.dy, *gx, *gy);
+    cp_out(*gx, dfdx);
+    cp_out(*gy, dfdy);
+  }
   void diagnostics(double* umax, double* vmax, double* divmax) override {
     ::calc_divergence(fs.curr.U, fs.curr.V, fs.dx, fs.dy, div);
     *umax = abs_max(fs.curr.U); *vmax = abs_max(fs.curr.V); *divmax = abs_max(div);
@@ -471,6 +487,10 @@ void fsref_calc_pressure_jump(void* s, const double* vf, const double* curv, con
 void fsref_interpolate_uv(void* s, double* ui, double* vi) { S->interpolate_uv(ui, vi); }
 void fsref_conserved(void* s, double* mass, double* mx, double* my) { S->conserved(mass, mx, my); }
 int fsref_to_npy(void* s, const char* dir) { return S->to_npy(dir); }
+double fsref_integrate_cell(void* s, const double* f, int include_ghost, int l1) {
+  return S->integrate_cell(f, include_ghost, l1);
+}
+void fsref_grad_centered(void* s, const double* f, double* dfdx, double* dfdy) { S->grad_centered(f, dfdx, dfdy); }
 int fsref_write_vtk(void* s, const char* dir, double t) { return S->write_vtk(dir, t); }
 double fsref_flow_control(void* s, int mode, double total_flow, double* io) {
   return S->flow_control(mode, total_flow, io);

@@ -229,6 +229,21 @@ def channel_study(name="channel_study", ns=(3, 4, 5)):
     np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
 
 
+def operators_misc(name="operators_random48x20"):
+    """integrate / L1_norm (src/Operators.hpp:51-76) with and without ghosts, and calc_grad_of_centered_points
+    (:164-201) applied twice as src/Curvature.hpp:337-339 does, on a seeded cell field"""
+    st = random_state(48, 20, seed=11)
+    f = np.random.default_rng(12).uniform(-1, 1, (st.nx + 2, st.ny + 2)) + 0.2
+    r = Ref(st.nx, st.ny)
+    r.load(st)
+    out = {"sums": np.array([r.integrate(f, g, l1) for g in (False, True) for l1 in (False, True)])}
+    out["gx"], out["gy"] = r.grad_centered(f)
+    out["gxx"], out["gxy"] = r.grad_centered(out["gx"])
+    out["gyx"], out["gyy"] = r.grad_centered(out["gy"])
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
+    print(name, out["sums"])
+
+
 def solve_psd(name="solve_psd128"):
     """one PCG+PFMG solve per PSDirichlet side (src/LinearSystem.hpp:10,32-155; the two-phase drivers use
     PSDirichlet::RIGHT with all-Neumann velocity BCs, test/StationaryDrop.cpp:67-72,223-224) on the
@@ -255,6 +270,9 @@ if __name__ == "__main__":
     if "channel215" in sys.argv:
         for nm in CHANNEL215:
             run_channel215(nm)
+        sys.exit(0)
+    if "operators" in sys.argv:
+        operators_misc()
         sys.exit(0)
     if "study" in sys.argv:
         channel_study()
@@ -285,3 +303,4 @@ if __name__ == "__main__":
         run_channel215(nm)
     io_files()
     channel_study()
+    operators_misc()

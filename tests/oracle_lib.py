@@ -157,6 +157,9 @@ class Oracle:
         L.fso_flow_control.restype = C.c_double
         L.fso_flow_control.argtypes = [C.POINTER(CFs), C.c_int, C.c_double, DP]
         L.fso_abs_max.restype = C.c_double
+        L.fso_integrate.restype = C.c_double
+        L.fso_integrate.argtypes = [DP, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_int, C.c_int]
+        L.fso_grad_centered.argtypes = [DP, C.c_int64, C.c_int64, C.c_double, C.c_double, DP, DP]
         L.fso_abs_max.argtypes = [DP, C.c_int64, C.c_int64, C.c_int]
         L.fso_calc_mid_time.argtypes = [DP, DP, C.c_int64]
         L.fso_update_velocity.argtypes = [C.POINTER(CFs), DP, DP, C.c_double]
@@ -278,6 +281,18 @@ class Oracle:
     def calc_rho_visc_vof(self, st, vf):
         self.lib.fso_calc_rho_visc_vof(C.byref(st.cstruct()), _ptr(vf))
 
+    def integrate(self, a, dx, dy, include_ghost=False, l1=False):
+        """integrate<INCLUDE_GHOST> / L1_norm<INCLUDE_GHOST>(dx, dy, field), src/Operators.hpp:51-76"""
+        a = np.ascontiguousarray(a)
+        return self.lib.fso_integrate(_ptr(a), a.shape[0] - 2, a.shape[1] - 2, dx, dy, int(include_ghost), int(l1))
+
+    def grad_centered(self, f, dx, dy):
+        """calc_grad_of_centered_points, src/Operators.hpp:164-201 -> (dfdx, dfdy)"""
+        f = np.ascontiguousarray(f)
+        gx, gy = np.zeros_like(f), np.zeros_like(f)
+        self.lib.fso_grad_centered(_ptr(f), f.shape[0] - 2, f.shape[1] - 2, dx, dy, _ptr(gx), _ptr(gy))
+        return gx, gy
+
     def apply_neumann_bconds(self, f):
         self.lib.fso_apply_neumann_bconds(_ptr(f), f.shape[0] - 2, f.shape[1] - 2)
 
@@ -375,6 +390,9 @@ class Ref:
             L.fsref_conserved.argtypes = [C.c_void_p, DP, DP, DP]
             L.fsref_flow_control.argtypes = [C.c_void_p, C.c_int, C.c_double, DP]
             L.fsref_to_npy.argtypes = [C.c_void_p, C.c_char_p]
+            L.fsref_integrate_cell.argtypes = [C.c_void_p, DP, C.c_int, C.c_int]
+            L.fsref_integrate_cell.restype = C.c_double
+            L.fsref_grad_centered.argtypes = [C.c_void_p, DP, DP, DP]
             L.fsref_write_vtk.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
             L.fsref_flow_control.restype = C.c_double
             L.fsref_ib_implicit_euler.argtypes = [C.c_void_p, DP, DP, C.c_double]
@@ -486,6 +504,16 @@ class Ref:
 
     def ib_semi_analytical(self, dU, dV, dt, ibu, ibv):
         self.lib().fsref_ib_semi_analytical(self.h, _ptr(dU), _ptr(dV), dt, _ptr(ibu), _ptr(ibv))
+
+    def integrate(self, a, include_ghost=False, l1=False):
+        a = np.ascontiguousarray(a)
+        return self.lib().fsref_integrate_cell(self.h, _ptr(a), int(include_ghost), int(l1))
+
+    def grad_centered(self, f):
+        f = np.ascontiguousarray(f)
+        gx, gy = np.zeros_like(f), np.zeros_like(f)
+        self.lib().fsref_grad_centered(self.h, _ptr(f), _ptr(gx), _ptr(gy))
+        return gx, gy
 
     def to_npy(self, directory):
         """to_npy(directory, fs), src/IO.hpp:231-269 -- REMOVES and re-creates `directory`"""

@@ -66,6 +66,10 @@ int main(int argc, char**) {
   Float mass = 0, mx = 0, my = 0;
   calc_conserved_quantities(fs, mass, mx, my);
   const Float m = abs_max(fs.curr.U) + abs_max<true>(div) + mass + mx + my;
+  Field2D<Float, NX, NY, NGHOST> dvfdx{}, dvfdy{};
+  calc_grad_of_centered_points(vf, fs.dx, fs.dy, dvfdx, dvfdy);
+  const Float vol = integrate<true>(fs.dx, fs.dy, vf) + L1_norm(fs.dx, fs.dy, div);
+  if (!(vol == vol)) return 3;
   DataWriter<Float, NX, NY, NGHOST> data_writer("/tmp/fsgpu_shim_check", &fs.x, &fs.y);
   data_writer.add_scalar("pressure", &fs.p);
   data_writer.add_scalar("divergence", &div);

@@ -322,3 +322,72 @@ def test_channel_convergence_study(F, oracle):
         ps.close()
         fs.close()
     assert ue[0] / ue[1] > 3.0 and ue[1] / ue[2] > 3.0
+
+
+# ---- integrate / L1_norm / calc_grad_of_centered_points (src/Operators.hpp:51-76,164-201) ----------
+def test_integrate_l1_grad_vs_reference_golden(F, oracle):
+    from cases import random_state, rel_inf
+    g = np.load(os.path.join(GOLD, "operators_random48x20.npz"))
+    st = random_state(48, 20, seed=11)
+    f = np.random.default_rng(12).uniform(-1, 1, (st.nx + 2, st.ny + 2)) + 0.2
+    fs = to_gpu(F, st)
+    fs.upload("VF", f)
+    sums = [fn("VF", gh) for gh in (False, True) for fn in (fs.integrate, fs.l1_norm)]
+    assert np.allclose(sums, g["sums"], rtol=1e-12, atol=0)
+    # a U-like and a V-like field: interior = the faces the reference's for_each_i visits
+    for name, a in (("U", st.U), ("V", st.V)):
+        assert fs.integrate(name) == pytest.approx(oracle.integrate(a, st.dx, st.dy), rel=1e-12, abs=1e-13)
+        assert fs.l1_norm(name, True) == pytest.approx(oracle.integrate(a, st.dx, st.dy, True, True), rel=1e-12)
+    fs.calc_grad_of_centered_points("VF", "GRAD_X", "GRAD_Y")
+    fs.calc_grad_of_centered_points("GRAD_X", "GRAD_XX", "CURV")   # dfdxx, dfdxy
+    fs.calc_grad_of_centered_points("GRAD_Y", "RHOI", "GRAD_YY")   # dfdyx, dfdyy
+    for name, k in (("GRAD_X", "gx"), ("GRAD_Y", "gy"), ("GRAD_XX", "gxx"), ("CURV", "gxy"), ("RHOI", "gyx"),
+                    ("GRAD_YY", "gyy")):
+        assert rel_inf(fs.download(name), g[k]) <= 1e-12, k
+    with pytest.raises(F.FsgpuError):
+        fs.calc_grad_of_centered_points("VF", "VF", "GRAD_Y")
+    with pytest.raises(F.FsgpuError):
+        fs.calc_grad_of_centered_points("U", "GRAD_X", "GRAD_Y")
+    fs.close()
+
+
+def test_gradient_centered_points_known_answer(F):
+    """the reference's own test/Operators.cpp:86-215 on the GPU (quadratic f, derivatives exact within 2e-10)"""
+    nx, ny, dx, dy = 200, 300, 2.0 / 200, 4.0 / 300
+    x = 2.0 + (np.arange(-1, nx + 1) + 0.5) * dx - 0.5
+    y = -1.0 + (np.arange(-1, ny + 1) + 0.5) * dy - 0.5
+    X, Y = np.meshgrid(x, y, indexing="ij")
+    fs = F.FS(nx, ny, dx, dy)
+    fs.upload("VF", X * X + X * Y + Y * Y)
+    fs.calc_grad_of_centered_points("VF", "GRAD_X", "GRAD_Y")
+    fs.calc_grad_of_centered_points("GRAD_X", "GRAD_XX", "CURV")
+    fs.calc_grad_of_centered_points("GRAD_Y", "RHOI", "GRAD_YY")
+    eps = 2e-10
+    assert np.abs(fs.download("GRAD_X") - (2 * X + Y)).max() <= eps
+    assert np.abs(fs.download("GRAD_Y") - (X + 2 * Y)).max() <= eps
+    for name, want in (("GRAD_XX", 2.0), ("GRAD_YY", 2.0), ("CURV", 1.0), ("RHOI", 1.0)):
+        assert np.abs(fs.download(name) - want).max() <= eps, name
+    fs.close()
+
+
+def test_integrate_grad_slabs(F, oracle):
+    """the same operators on 3 slab contexts: sums combined over the ranks, gradient rows next to a slab
+    boundary read the neighbour's rows"""
+    from test_gpu_slab import compare, run_ranks, run_single
+    from cases import cavity_bc, random_state
+    st = random_state(50, 23, seed=7)
+    st.vf = np.random.default_rng(3).uniform(0, 1, (st.nx + 2, st.ny + 2))
+
+    def body(fs, r):
+        out = [fs.integrate("VF"), fs.integrate("VF", True), fs.l1_norm("U"), fs.l1_norm("V", True)]
+        fs.calc_grad_of_centered_points("VF", "GRAD_X", "GRAD_Y")
+        fs.calc_grad_of_centered_points("GRAD_X", "GRAD_XX", "CURV")
+        return out
+
+    names = ("GRAD_X", "GRAD_Y", "GRAD_XX", "CURV")
+    a, ra = run_ranks(F, st, cavity_bc(), 3, body, fields=names)
+    b, rb = run_single(F, st, cavity_bc(), body, fields=names)
+    assert all(x == ra[0] for x in ra)
+    assert ra[0] == pytest.approx(rb, rel=1e-12)
+    assert rb[1] == pytest.approx(oracle.integrate(st.vf, st.dx, st.dy, True), rel=1e-12)
+    compare(a, b, names, tol=1e-13)
