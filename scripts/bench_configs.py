@@ -1,0 +1,98 @@
+"""Timestep throughput of the BASELINE.json configurations bench.py does not time (bench.py times
+configs[2], the 8192^2 cavity): configs[1] channel 4096 x 1024 (outflow correction, 5 sub-iterations),
+configs[3] variable-density drop 4096^2 (operator rebuilt every sub-iteration, 3 sub-iterations) and
+the same drop with consistent mass transport + capillary block switched on.  One JSON line each:
+ms/step over `steps` timed steps after `warmup` (CUDA events on the library's stream), MCell-updates/s,
+PCG iterations per solve.
+
+usage: python scripts/bench_configs.py [steps] [warmup] [scale]    (scale 2 halves every grid dimension)
+"""
+import json
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import fluidsolver_b200 as F  # noqa: E402
+import torch  # noqa: E402
+
+steps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+warmup = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+scale = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+
+
+def ellipse_vf(nx, ny, dx, dy, sharp=1.5):
+    """smoothed indicator of the ellipse (2(x-1/2))^2 + (y-1/2)^2 <= 0.25^2 (test/StationaryDrop.cpp:46-52)"""
+    x = (np.arange(-1, nx + 1) + 0.5) * dx
+    y = (np.arange(-1, ny + 1) + 0.5) * dy
+    X, Y = np.meshgrid(x, y, indexing="ij")
+    d = np.sqrt((2 * (X - 0.5)) ** 2 + (Y - 0.5) ** 2) - 0.25
+    return np.clip(0.5 - d / (sharp * dx), 0.0, 1.0)
+
+
+def timed(name, fs, ps, nsub, flags, cfl=0.9, dt_max=0.1):
+    for _ in range(warmup):
+        fs.step(ps, fs.adjust_dt(cfl, dt_max), nsub, flags)
+    st = torch.cuda.ExternalStream(fs.stream())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    fs.sync()
+    e0.record(st)
+    its, res = 0, 0.0
+    for _ in range(steps):
+        res, it = fs.step(ps, fs.adjust_dt(cfl, dt_max), nsub, flags)
+        its += it
+    e1.record(st)
+    fs.sync()
+    ms = e0.elapsed_time(e1) / steps
+    um, vm, dm = fs.monitor()
+    print(json.dumps({"config": name, "nx": fs.nx, "ny": fs.ny, "steps": steps, "warmup": warmup,
+                      "ms_per_step": round(ms, 3), "mcell_updates_per_s": round(fs.nx * fs.ny / ms / 1e3, 1),
+                      "pcg_iters_per_solve": round(its / (steps * nsub), 2), "last_residual": res,
+                      "levels": ps.num_levels, "max_U": um, "max_V": vm, "max_div": dm}), flush=True)
+
+
+def channel():
+    nx, ny = 4096 // scale, 1024 // scale
+    fs = F.FS(nx, ny, 100.0 / nx, 1.0 / ny, 0.5, 0.5, 1e-3, 1e-3)
+    fs.calc_rho_visc_const()
+    fs.fill("U", 1.0)
+    fs.set_bconds(F.LEFT, F.DIRICHLET, 1.0, 0.0)
+    fs.set_bconds(F.RIGHT, F.NEUMANN)
+    fs.set_bconds(F.BOTTOM, F.DIRICHLET, 0.0, 0.0)
+    fs.set_bconds(F.TOP, F.DIRICHLET, 0.0, 0.0)
+    fs.apply_velocity_bconds()
+    ps = F.LinearSolver(fs, tol=1e-6, max_iter=50, max_levels=40)
+    ps.set_pressure_operator()
+    timed("channel", fs, ps, 5, F.STEP_OUTFLOW_FIX)
+    ps.close()
+    fs.close()
+
+
+def drop(twophase):
+    n = 4096 // scale
+    fs = F.FS(n, n, 1.0 / n, 1.0 / n, 1.0, 1000.0, 1e-3, 1e-3, sigma=0.05 if twophase else 0.0)
+    vf = ellipse_vf(n, n, 1.0 / n, 1.0 / n)
+    fs.upload("VF", vf)
+    fs.calc_rho_visc_vof()
+    fs.save_old_density()
+    for s, u in enumerate((0.0, 0.0, 0.0, 1.0)):
+        fs.set_bconds(s, F.DIRICHLET, u, 0.0)
+    fs.apply_velocity_bconds()
+    flags = F.STEP_REBUILD_OPERATOR
+    if twophase:  # curvature 1 / R of a circle of the drop's height, interface cells flagged
+        band = ((vf > 1e-8) & (vf < 1 - 1e-8)).astype(np.float64)
+        fs.upload("CURV", band / 0.25)
+        fs.upload("INTERFACE_LENGTH", band)
+        flags |= F.STEP_DENSITY | F.STEP_CAPILLARY
+    ps = F.LinearSolver(fs, tol=1e-6, max_iter=50, max_levels=40)
+    ps.set_pressure_operator()
+    timed("drop_twophase" if twophase else "drop", fs, ps, 3, flags)
+    ps.close()
+    fs.close()
+
+
+if __name__ == "__main__":
+    channel()
+    drop(False)
+    drop(True)
