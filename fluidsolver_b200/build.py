@@ -67,7 +67,7 @@ def build_examples() -> list:
     """the C++ host layer (include/shim) + example drivers, plain g++ against libfsgpu.so"""
     root = os.path.dirname(HERE)
     outs = []
-    for name in ("lid_driven_cavity", "two_phase_drop"):
+    for name in ("lid_driven_cavity", "two_phase_drop", "periodic_channel"):
         src = os.path.join(root, "examples", name + ".cpp")
         out = os.path.join(root, "examples", name)
         deps = [src, LIB, os.path.join(root, "include", "fsgpu.h"),

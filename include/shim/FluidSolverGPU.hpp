@@ -453,6 +453,23 @@ void calc_conserved_quantities(const FS<Float, NX, NY, NGHOST>& fs, Float& mass,
   FSGPU_CHECK(fsgpu_calc_conserved_quantities(fs.ctx, &mass, &momentum_x, &momentum_y));
 }
 
+// The channel drivers' corrections of the two ghost columns U(-1, .) and U(NX+1, .) after
+// apply_velocity_bconds.  The reference drivers inline them as host loops (calc_inflow_outflow + for_each_a over
+// fs.ym); with the state in HBM they are these two calls.  inflow / outflow are the fluxes BEFORE the correction.
+//   correct_outflow(fs, false, ...)  test/LaminarChannel.cpp:55-66,201-205
+//   correct_outflow(fs, true, ...)   test/CustomDirichletChannel.cpp:61-72,197-202, scaling/Channel.cpp:208-213
+//   force_total_flow(fs, Q, ...)     test/PeriodicChannel.cpp:56-67,193-203, scaling/Channel.cpp:196-206
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void correct_outflow(FS<Float, NX, NY, NGHOST>& fs, bool dy_weighted, Float& inflow, Float& outflow, Float& mass_error) {
+  FSGPU_CHECK(fsgpu_flow_control(fs.ctx, dy_weighted ? FSGPU_FLOW_OUTFLOW_FIX_DY : FSGPU_FLOW_OUTFLOW_FIX, 0.0,
+                                 &inflow, &outflow));
+  mass_error = outflow - inflow;
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void force_total_flow(FS<Float, NX, NY, NGHOST>& fs, Float total_flow, Float& inflow, Float& outflow) {
+  FSGPU_CHECK(fsgpu_flow_control(fs.ctx, FSGPU_FLOW_FORCE_TOTAL, total_flow, &inflow, &outflow));
+}
+
 // integrate / L1_norm (src/Operators.hpp:51-76) and calc_grad_of_centered_points (:164-201) on device-bound
 // fields; the gradient's outputs are bound to FSGPU_GRAD_X / FSGPU_GRAD_Y unless already bound elsewhere
 template <bool INCLUDE_GHOST = false, typename Float, Index M, Index N, Index NGHOST>
