@@ -138,6 +138,7 @@ struct LocalGroup {
 //   byte 0   : flag[0]  last epoch whose rows from rank - 1 are complete       (own 128-byte line)
 //   byte 128 : flag[1]  ... from rank + 1
 //   byte 192 : arrive counter of the local exchange kernel
+//   byte 200 : device copy of the error flag (the kernels test this one: no PCIe read per exchange)
 //   byte 256 : 4 slots of `cap` doubles: (side 0 | side 1) x (epoch parity 0 | 1)
 // One exchange = ONE kernel per rank on the context's stream: (A) store my boundary rows straight
 // into the neighbours' slots over NVLink, fence, the last CTA to arrive raises the neighbours' flags
@@ -165,7 +166,7 @@ constexpr int P2P_CTAS = 8, P2P_THREADS = 512;
 
 __global__ void __launch_bounds__(P2P_THREADS)
 k_halo_p2p(const HaloP2PArgs a) {
-  if (*(volatile int*)a.err) return;  // an earlier exchange timed out: fail fast, the host reports it
+  if (*reinterpret_cast<volatile int*>(a.mine + 200)) return;  // an earlier exchange timed out: fail fast, the host reports it
   const size_t cnt2 = (size_t)a.h * (size_t)a.pitch / 2;  // double2 per array and direction
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (size_t)gridDim.x * blockDim.x;
   const int par = (int)(a.e & 1ull);
@@ -199,7 +200,10 @@ k_halo_p2p(const HaloP2PArgs a) {
     while (ok && ((a.up && *p2p_flag(a.mine, 0) < a.e) || (a.dn && *p2p_flag(a.mine, 1) < a.e))) {
       if (clock64() - t0 > 4000000000ll) ok = false;  // ~2 s
     }
-    if (!ok) *a.err = 1;
+    if (!ok) {
+      *a.err = 1;  // mapped pinned memory: the host sees it at its next scalar read
+      *reinterpret_cast<volatile int*>(a.mine + 200) = 1;
+    }
     __threadfence_system();
   }
   __syncthreads();
@@ -241,9 +245,9 @@ __device__ __forceinline__ double* red_vals(char* base, size_t off, int par, int
 }
 __global__ void __launch_bounds__(P2P_MAX_RANKS * P2P_RED_MAX)
 k_allreduce_p2p(const RedP2PArgs a) {
-  if (*(volatile int*)a.err) return;
   const int t = threadIdx.x, par = (int)(a.e & 1ull);
   char* mine = a.peer[a.rank];
+  if (*reinterpret_cast<volatile int*>(mine + 200)) return;
   if (t < a.nranks * a.n) {
     const int pr = t / a.n, q = t - pr * a.n;
     red_vals(a.peer[pr], a.red_off, par, a.rank)[q] = a.dev[q];
@@ -257,7 +261,10 @@ k_allreduce_p2p(const RedP2PArgs a) {
     bool ok = true;
     while (ok && *red_flag(mine, a.red_off, t) < a.e)
       if (clock64() - t0 > 4000000000ll) ok = false;  // ~2 s
-    if (!ok) *a.err = 1;
+    if (!ok) {
+      *a.err = 1;
+      *reinterpret_cast<volatile int*>(mine + 200) = 1;
+    }
     __threadfence_system();
   }
   __syncthreads();
