@@ -38,6 +38,17 @@
 #ifndef FS_PF_ROWS
 #define FS_PF_ROWS 0
 #endif
+// k_up_march: operand rows fetched FS_UP_ASYNC rows ahead with cp.async (LDGSTS) into a thread-private
+// shared-memory ring instead of into registers (0 = off).  Every thread copies and later reads only
+// its own words, so no barrier is needed -- cp.async.wait_group alone orders the ring; the depth
+// is bought with shared memory (7 KB per row ahead and CTA) instead of registers.  A/B variant for
+// scripts/build_variants.py (-DFS_UP_ASYNC=4), NOT yet run on hardware.
+#ifndef FS_UP_ASYNC
+#define FS_UP_ASYNC 0
+#endif
+#if FS_UP_ASYNC > 0 && (FS_UP_MODE != 1 || FS_UP_PREFETCH != 0 || FS_UP_ASYNC > 6)
+#error "FS_UP_ASYNC needs FS_UP_MODE == 1, FS_UP_PREFETCH == 0 and a depth of at most 6 rows (48 KB static shared memory)"
+#endif
 
 namespace {
 
@@ -269,6 +280,14 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
   const int strips = (n1 + MOUT * MWARPS - 1) / (MOUT * MWARPS);
   const int total  = strips * ((f_hi - f_lo + mr - 1) / mr);
   double acc[1] = {0.0};
+#if FS_UP_ASYNC > 0
+  // [row slot][operand][thread]: a warp's lanes touch 32 consecutive words of a bank row
+  __shared__ double ring[FS_UP_ASYNC][7][32 * MWARPS];
+  auto cpa = [](double* dst, const double* src) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(src) : "memory");
+  };
+#endif
   for (int t = blockIdx.x; t < total; t += gridDim.x) {
     const int ch = t / strips, sp = t - ch * strips;
     int lj = sp * (MOUT * MWARPS) + warp * MOUT - 1 + lane;  // lane 0 sits one column left
@@ -317,6 +336,47 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
 #if FS_UP_PREFETCH
     Row nx = load_row(li, o);
 #endif
+#if FS_UP_ASYNC > 0
+    // the seven operand words of row li_ (the same addresses load_row reads) into ring slot sl
+    auto issue_row = [&](int li_, int o_, int sl) {
+      const int tx = threadIdx.x;
+      cpa(&ring[sl][0][tx], f.cx + o_ + P);
+      cpa(&ring[sl][1][tx], fb + o_);
+      cpa(&ring[sl][2][tx], f.cy + o_);
+      cpa(&ring[sl][3][tx], f.cy + o_ + 1);
+      cpa(&ring[sl][4][tx], f.d + o_);
+      if (CDIR == 0) {
+        const int pos = li_ - foff, par = pos & 1;
+        const int oc  = (((pos - par) >> 1) + FS_RO) * Pc + lj + FS_CO;
+        cpa(&ring[sl][5][tx], xc + oc);
+        if (par) cpa(&ring[sl][6][tx], xc + oc + Pc);
+      } else {
+        const int pos = lj - foff, par = pos & 1;
+        const int oc  = (li_ + FS_RO) * Pc + ((pos - par) >> 1) + FS_CO;
+        cpa(&ring[sl][5][tx], xc + oc);
+        cpa(&ring[sl][6][tx], xc + oc + 1);
+      }
+    };
+    auto read_row = [&](int li_, int sl) {
+      const int tx = threadIdx.x;
+      Row q;
+      q.cxnn = ring[sl][0][tx];
+      q.b    = ring[sl][1][tx];
+      q.cy   = ring[sl][2][tx];
+      q.cy1  = ring[sl][3][tx];
+      q.d    = ring[sl][4][tx];
+      q.di = 0.0;  q.pc = 0.0;
+      q.xm = ring[sl][5][tx];
+      q.xp = (CDIR == 0 && (((li_ - foff) & 1) == 0)) ? 0.0 : ring[sl][6][tx];
+      return q;
+    };
+#pragma unroll
+    for (int dd = 0; dd < FS_UP_ASYNC; ++dd) {  // one group per row, empty past the chunk's last row
+      if (li + dd <= r1) issue_row(li + dd, o + dd * P, dd);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    int slot = 0;
+#endif
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
 #if FS_PF_ROWS > 0
@@ -325,7 +385,11 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
         pf_l2(fb + op, lane); pf_l2(f.d + op, lane); pf_l2(f.cy + op, lane); pf_l2(f.cx + op + P, lane);
       }
 #endif
-#if FS_UP_PREFETCH
+#if FS_UP_ASYNC > 0
+      // all but the newest FS_UP_ASYNC - 1 groups have landed: row li is in its slot
+      asm volatile("cp.async.wait_group %0;" ::"n"(FS_UP_ASYNC - 1) : "memory");
+      const Row q = read_row(li, slot);
+#elif FS_UP_PREFETCH
       const Row q = nx;
       if (li < r1) nx = load_row(li + 1, o + P);
 #else
@@ -379,6 +443,12 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
         }
       }
       x0p = x0c; x0c = x0n; bc = bn; dic = din; dc = dn; cyc = cyn; cy1c = cy1n; cxc = cxn; cxn = cxnn;
+#if FS_UP_ASYNC > 0
+      // refill the slot just consumed (its words are in registers; the clobber keeps the reads above)
+      if (li + FS_UP_ASYNC <= r1) issue_row(li + FS_UP_ASYNC, o + FS_UP_ASYNC * P, slot);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      slot = slot + 1 == FS_UP_ASYNC ? 0 : slot + 1;
+#endif
     }
   }
   if (DOT) {
