@@ -46,6 +46,13 @@
 #ifndef FS_UP_ASYNC
 #define FS_UP_ASYNC 0
 #endif
+// the same ring for the five operand words per row of k_down_march0 / k_down_march1 on ACTIVE levels
+#ifndef FS_DOWN_ASYNC
+#define FS_DOWN_ASYNC 0
+#endif
+#if FS_DOWN_ASYNC > 6
+#error "FS_DOWN_ASYNC: at most 6 rows ahead"
+#endif
 #if FS_UP_ASYNC > 0 && (FS_UP_MODE != 1 || FS_UP_PREFETCH != 0 || FS_UP_ASYNC > 6)
 #error "FS_UP_ASYNC needs FS_UP_MODE == 1, FS_UP_PREFETCH == 0 and a depth of at most 6 rows (48 KB static shared memory)"
 #endif
@@ -62,6 +69,15 @@ __device__ __forceinline__ void pf_l2(const double* p, int lane) {
   (void)p; (void)lane;
 #endif
 }
+
+// 8-byte asynchronous global -> shared copy (LDGSTS) and the two group operations of the variants above
+__device__ __forceinline__ void cp_async8(double* dst, const double* src) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // 1 / v with the convention of the stored dinv / pc arrays (0 where v == 0: pads, halo-less walls,
 // a singular coarsest point).  The active-level kernels recompute dinv = 1/d and the interpolation
@@ -103,6 +119,25 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
     double pc1 = 0.0, pc2 = 0.0, pc3 = 0.0;  // ACTIVE: pc of rows li - 1, li - 2, li - 3
     int li = f0 - 2;
     int o  = (li + FS_RO) * P + lj + FS_CO;
+#if FS_DOWN_ASYNC > 0
+    __shared__ double ring[FS_DOWN_ASYNC][5][128];
+    const int tx = threadIdx.x;
+    auto issue_row = [&](int o_, int sl) {
+      cp_async8(&ring[sl][0][tx], fb + o_);
+      cp_async8(&ring[sl][1][tx], f.cx + o_);
+      cp_async8(&ring[sl][2][tx], f.d + o_);
+      cp_async8(&ring[sl][3][tx], f.cy + o_);
+      cp_async8(&ring[sl][4][tx], f.cy + o_ + 1);
+    };
+    int slot = 0;
+    if (ACTIVE) {
+#pragma unroll
+      for (int dd = 0; dd < FS_DOWN_ASYNC; ++dd) {
+        if (li + dd <= fL + 2) issue_row(o + dd * P, dd);
+        cp_async_commit();
+      }
+    }
+#endif
 #pragma unroll 2
     for (; li <= fL + 2; ++li, o += P) {
 #if FS_PF_ROWS > 0
@@ -112,6 +147,22 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
         if (ACTIVE) { pf_l2(f.d + op, lane); pf_l2(f.cy + op, lane); }
       }
 #endif
+#if FS_DOWN_ASYNC > 0
+      double b0, cx0, X0 = 0.0, cy0 = 0.0, cy0p = 0.0, pc0 = 0.0;
+      if (ACTIVE) {
+        cp_async_wait<FS_DOWN_ASYNC - 1>();  // row li has landed in its slot
+        b0   = ring[slot][0][tx];
+        cx0  = ring[slot][1][tx];
+        const double d0 = ring[slot][2][tx];
+        cy0  = ring[slot][3][tx];
+        cy0p = ring[slot][4][tx];
+        X0   = w * b0 * rcp0(d0);
+        pc0  = rcp0(d0 + cy0 + cy0p);
+      } else {
+        b0  = __ldg(fb + o);
+        cx0 = __ldg(f.cx + o);
+      }
+#else
       const double b0 = __ldg(fb + o), cx0 = __ldg(f.cx + o);
       double X0 = 0.0, cy0 = 0.0, cy0p = 0.0, pc0 = 0.0;
       if (ACTIVE) {
@@ -121,6 +172,7 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
         X0   = w * b0 * rcp0(d0);
         pc0  = rcp0(d0 + cy0 + cy0p);
       }
+#endif
       // residual of row li - 1
       double Rn;
       if (ACTIVE) {
@@ -145,6 +197,13 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
       }
       X2 = X1; X1 = X0; b1 = b0; cx2 = cx1; cx1 = cx0; cy1 = cy0; cy1p = cy0p; Ra = Rb; Rb = Rn;
       pc3 = pc2; pc2 = pc1; pc1 = pc0;
+#if FS_DOWN_ASYNC > 0
+      if (ACTIVE) {  // refill the slot just consumed
+        if (li + FS_DOWN_ASYNC <= fL + 2) issue_row(o + FS_DOWN_ASYNC * P, slot);
+        cp_async_commit();
+        slot = slot + 1 == FS_DOWN_ASYNC ? 0 : slot + 1;
+      }
+#endif
     }
   }
 }
@@ -172,6 +231,25 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
     double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0, d1 = 0.0;
     int li = r0 - 1;
     int o  = (li + FS_RO) * P + lj + FS_CO;
+#if FS_DOWN_ASYNC > 0
+    __shared__ double ring[FS_DOWN_ASYNC][5][128];
+    const int tx = threadIdx.x;
+    auto issue_row = [&](int o_, int sl) {
+      cp_async8(&ring[sl][0][tx], fb + o_);
+      cp_async8(&ring[sl][1][tx], f.cy + o_);
+      cp_async8(&ring[sl][2][tx], f.cy + o_ + 1);
+      cp_async8(&ring[sl][3][tx], f.d + o_);
+      cp_async8(&ring[sl][4][tx], f.cx + o_);
+    };
+    int slot = 0;
+    if (ACTIVE) {
+#pragma unroll
+      for (int dd = 0; dd < FS_DOWN_ASYNC; ++dd) {
+        if (li + dd <= r1) issue_row(o + dd * P, dd);
+        cp_async_commit();
+      }
+    }
+#endif
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
 #if FS_PF_ROWS > 0
@@ -181,6 +259,22 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
         if (ACTIVE) { pf_l2(f.d + op, lane); pf_l2(f.cx + op, lane); }
       }
 #endif
+#if FS_DOWN_ASYNC > 0
+      double b0, cy0, cy0p, X0 = 0.0, cx0 = 0.0, d0 = 0.0;
+      if (ACTIVE) {
+        cp_async_wait<FS_DOWN_ASYNC - 1>();  // row li has landed in its slot
+        b0   = ring[slot][0][tx];
+        cy0  = ring[slot][1][tx];
+        cy0p = ring[slot][2][tx];
+        d0   = ring[slot][3][tx];
+        cx0  = ring[slot][4][tx];
+        X0   = w * b0 * rcp0(d0);
+      } else {
+        b0   = __ldg(fb + o);
+        cy0  = __ldg(f.cy + o);
+        cy0p = __ldg(f.cy + o + 1);
+      }
+#else
       const double b0 = __ldg(fb + o);
       const double cy0 = __ldg(f.cy + o), cy0p = __ldg(f.cy + o + 1);
       double X0 = 0.0, cx0 = 0.0, d0 = 0.0;
@@ -189,6 +283,7 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
         X0  = w * b0 * rcp0(d0);
         cx0 = __ldg(f.cx + o);
       }
+#endif
       if (li > r0) {  // row li - 1
         double Rn;
         if (ACTIVE) {
@@ -211,6 +306,13 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
         if (store_lane) cb[(li - 1 + FS_RO) * Pc + oc_col] = v;
       }
       X2 = X1; X1 = X0; b1 = b0; cx1 = cx0; cy1 = cy0; cy1p = cy0p; d1 = d0;
+#if FS_DOWN_ASYNC > 0
+      if (ACTIVE) {  // refill the slot just consumed
+        if (li + FS_DOWN_ASYNC <= r1) issue_row(o + FS_DOWN_ASYNC * P, slot);
+        cp_async_commit();
+        slot = slot + 1 == FS_DOWN_ASYNC ? 0 : slot + 1;
+      }
+#endif
     }
   }
 }
