@@ -22,7 +22,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <array>
+#include <cmath>
+#include <filesystem>
+#include <source_location>
 #include <string>
+#include <string_view>
 #include <variant>
 #include <vector>
 
@@ -563,6 +567,108 @@ class VTKWriter {
 };
 template <typename Float, Index NX, Index NY, Index NGHOST>
 using DataWriter = VTKWriter<Float, NX, NY, NGHOST>;
+
+// ---- host-side driver utilities: Monitor (src/Monitor.hpp), should_save / get_output_directory /
+// ---- init_output_directory (src/IO.hpp:97-175).  Plain host code, same observable behaviour: the
+// ---- monitor log is byte-identical to the reference's (tests/test_output_cpu.py).
+template <typename Float>
+class Monitor {
+  struct Column {
+    std::string name;
+    const Float* f;
+    const Index* i;
+    size_t width;  // max(len(name), 13): 13 characters hold a `.6e` number
+  };
+  std::FILE* m_file = nullptr;
+  std::vector<Column> m_cols;
+  bool m_header_done = false;
+
+  // text centred in `width` characters; an odd remainder goes to the right (as std::format's '^')
+  static std::string centred(const std::string& text, size_t width) {
+    if (text.size() >= width) return text;
+    const size_t pad = width - text.size(), left = pad / 2;
+    return std::string(left, ' ') + text + std::string(pad - left, ' ');
+  }
+
+ public:
+  explicit Monitor(const std::string& filename) : m_file(std::fopen(filename.c_str(), "w")) {
+    if (!m_file) {
+      std::fprintf(stderr, "Could not open monitor file `%s`\n", filename.c_str());
+      std::exit(1);
+    }
+  }
+  Monitor(const Monitor&)            = delete;
+  Monitor& operator=(const Monitor&) = delete;
+  ~Monitor() { if (m_file) std::fclose(m_file); }
+
+  void add_variable(const Float* variable, std::string name) {
+    const size_t w = name.size() > 13 ? name.size() : 13;
+    m_cols.push_back(Column{std::move(name), variable, nullptr, w});
+  }
+  void add_variable(const Index* variable, std::string name) {
+    const size_t w = name.size() > 13 ? name.size() : 13;
+    m_cols.push_back(Column{std::move(name), nullptr, variable, w});
+  }
+  void write() {
+    if (m_cols.empty()) return;
+    std::string line;
+    if (!m_header_done) {
+      line = "| ";
+      for (const Column& c : m_cols) line += centred(c.name, c.width) + " | ";
+      line += "\n|";
+      for (const Column& c : m_cols) line += std::string(c.width + 2, '-') + "|";
+      line += "\n";
+      m_header_done = true;
+    }
+    line += "| ";
+    char num[64];
+    for (const Column& c : m_cols) {
+      if (c.f) std::snprintf(num, sizeof num, "%.6e", static_cast<double>(*c.f));
+      else std::snprintf(num, sizeof num, "%lld", static_cast<long long>(*c.i));
+      line += centred(num, c.width) + " | ";
+    }
+    line += "\n";
+    std::fwrite(line.data(), 1, line.size(), m_file);
+    std::fflush(m_file);
+  }
+};
+
+// should_save(t, dt, dt_write, t_end), src/IO.hpp:97-108: true when a multiple of dt_write falls into the step
+// that just ended, and once at t_end (the last save time is remembered across calls, as in the reference)
+template <typename Float>
+[[nodiscard]] bool should_save(Float t, Float dt, Float dt_write, Float t_end) {
+  constexpr Float SAFE = 1e-6;
+  static Float last    = -1.0;
+  const bool at_end    = std::abs(t - t_end) < SAFE;
+  const bool crossed   = std::fmod(t + SAFE * dt, dt_write) < dt * (1.0 - SAFE);
+  if (!(crossed || at_end)) return false;
+  if (at_end && std::abs(t - last) < SAFE) return false;
+  last = t;
+  return true;
+}
+
+#ifndef FS_BASE_DIR
+#define FS_BASE_DIR "."
+#endif
+// "<base_dir>/<subdir>/<source file name without directory and extension>/", src/IO.hpp:114-155
+[[nodiscard]] inline std::string get_output_directory(std::string_view subdir = "output", std::string_view base_dir = FS_BASE_DIR,
+                                                      std::source_location loc = std::source_location::current()) {
+  const std::string_view file = loc.file_name();
+  const size_t slash = file.rfind('/');
+  std::string_view stem = slash == std::string_view::npos ? file : file.substr(slash + 1);
+  const size_t dot = stem.rfind('.');
+  // the reference drops one character more than the extension when there is no '.', keep real names intact
+  if (dot != std::string_view::npos) stem = stem.substr(0, dot);
+  return std::string(base_dir) + "/" + std::string(subdir) + "/" + std::string(stem) + "/";
+}
+// init_output_directory, src/IO.hpp:158-175: the directory is REMOVED with everything in it and created anew
+[[nodiscard]] inline bool init_output_directory(std::string_view directory_name) {
+  std::error_code ec;
+  std::filesystem::remove_all(directory_name, ec);
+  if (ec) return false;
+  std::filesystem::create_directories(directory_name, ec);
+  return !ec;
+}
 
 // ---- LinearSolver_StructHypre (src/LinearSolver_StructHypre.hpp:28-192) ----------------------------
 enum class HypreSolver { GMRES, PCG, BiCGSTAB };   // only PCG + PFMG (the reference's defaults) exist here

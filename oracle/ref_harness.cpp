@@ -22,6 +22,7 @@
 #include "IB.hpp"
 #include "IO.hpp"
 #include "LinearSolver_StructHypre.hpp"
+#include "Monitor.hpp"
 #include "Operators.hpp"
 #include "Utility.hpp"
 
@@ -487,6 +488,27 @@ void fsref_calc_pressure_jump(void* s, const double* vf, const double* curv, con
 void fsref_interpolate_uv(void* s, double* ui, double* vi) { S->interpolate_uv(ui, vi); }
 void fsref_conserved(void* s, double* mass, double* mx, double* my) { S->conserved(mass, mx, my); }
 int fsref_to_npy(void* s, const char* dir) { return S->to_npy(dir); }
+// Monitor (src/Monitor.hpp) driven with nrows x (nf Float + ni Index) values: the log file as the drivers write it
+int fsref_monitor_log(const char* filename, int nf, const char* const* fnames, int ni, const char* const* inames,
+                      int nrows, const double* fvals, const int64_t* ivals) {
+  std::vector<Float> fv(static_cast<size_t>(nf));
+  std::vector<Index> iv(static_cast<size_t>(ni));
+  Monitor<Float> monitor(filename);
+  // the drivers interleave Float and Index columns; here: all Float columns but the last, the Index columns, the last Float
+  for (int k = 0; k + 1 < nf; ++k) monitor.add_variable(&fv[static_cast<size_t>(k)], fnames[k]);
+  for (int k = 0; k < ni; ++k) monitor.add_variable(&iv[static_cast<size_t>(k)], inames[k]);
+  if (nf > 0) monitor.add_variable(&fv[static_cast<size_t>(nf - 1)], fnames[nf - 1]);
+  for (int r = 0; r < nrows; ++r) {
+    for (int k = 0; k < nf; ++k) fv[static_cast<size_t>(k)] = fvals[r * nf + k];
+    for (int k = 0; k < ni; ++k) iv[static_cast<size_t>(k)] = ivals[r * ni + k];
+    monitor.write();
+  }
+  return 0;
+}
+// should_save(t, dt, dt_write, t_end), src/IO.hpp:97-108 (keeps a function-static last save time)
+int fsref_should_save(double t, double dt, double dt_write, double t_end) {
+  return ::should_save(t, dt, dt_write, t_end) ? 1 : 0;
+}
 double fsref_integrate_cell(void* s, const double* f, int include_ghost, int l1) {
   return S->integrate_cell(f, include_ghost, l1);
 }

@@ -244,6 +244,16 @@ def operators_misc(name="operators_random48x20"):
     print(name, out["sums"])
 
 
+def monitor_log(name="monitor_log.txt"):
+    """src/Monitor.hpp and should_save (src/IO.hpp:97-108) of the unmodified reference on the rows / step sequence of
+    tests/test_output_cpu.py"""
+    from test_output_cpu import _reference_monitor_and_saves
+    log, seq = _reference_monitor_and_saves(os.path.join(HERE, name))
+    with open(os.path.join(HERE, name), "ab") as f:
+        f.write(b"#saves " + " ".join(map(str, seq)).encode() + b"\n")
+    print(log.decode(), seq)
+
+
 def solve_psd(name="solve_psd128"):
     """one PCG+PFMG solve per PSDirichlet side (src/LinearSystem.hpp:10,32-155; the two-phase drivers use
     PSDirichlet::RIGHT with all-Neumann velocity BCs, test/StationaryDrop.cpp:67-72,223-224) on the
@@ -270,6 +280,9 @@ if __name__ == "__main__":
     if "channel215" in sys.argv:
         for nm in CHANNEL215:
             run_channel215(nm)
+        sys.exit(0)
+    if "monitor" in sys.argv:
+        monitor_log()
         sys.exit(0)
     if "operators" in sys.argv:
         operators_misc()
@@ -304,3 +317,4 @@ if __name__ == "__main__":
     io_files()
     channel_study()
     operators_misc()
+    monitor_log()

@@ -390,6 +390,9 @@ class Ref:
             L.fsref_conserved.argtypes = [C.c_void_p, DP, DP, DP]
             L.fsref_flow_control.argtypes = [C.c_void_p, C.c_int, C.c_double, DP]
             L.fsref_to_npy.argtypes = [C.c_void_p, C.c_char_p]
+            L.fsref_monitor_log.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_char_p),
+                                            C.c_int, DP, C.POINTER(C.c_int64)]
+            L.fsref_should_save.argtypes = [C.c_double] * 4
             L.fsref_integrate_cell.argtypes = [C.c_void_p, DP, C.c_int, C.c_int]
             L.fsref_integrate_cell.restype = C.c_double
             L.fsref_grad_centered.argtypes = [C.c_void_p, DP, DP, DP]
@@ -400,6 +403,21 @@ class Ref:
             L.fsref_set_threads.argtypes = [C.c_int]
             cls._lib = L
         return cls._lib
+
+    @classmethod
+    def monitor_log(cls, filename, fnames, inames, frows, irows):
+        """the reference's Monitor (src/Monitor.hpp) writing len(frows) rows; column order: all Float columns but the
+        last, the Index columns, the last Float column"""
+        fr = np.ascontiguousarray(frows, dtype=np.float64)
+        ir = np.ascontiguousarray(irows, dtype=np.int64)
+        fn = (C.c_char_p * len(fnames))(*[n.encode() for n in fnames])
+        inn = (C.c_char_p * len(inames))(*[n.encode() for n in inames])
+        cls.lib().fsref_monitor_log(os.fsencode(filename), len(fnames), fn, len(inames), inn, fr.shape[0], _ptr(fr),
+                                    ir.ctypes.data_as(C.POINTER(C.c_int64)))
+
+    @classmethod
+    def should_save(cls, t, dt, dt_write, t_end):
+        return bool(cls.lib().fsref_should_save(t, dt, dt_write, t_end))
 
     def __init__(self, nx, ny):
         L = self.lib()
