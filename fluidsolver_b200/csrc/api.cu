@@ -416,6 +416,30 @@ int fsgpu_calc_grad_of_centered_points(fsgpu_ctx* c, int f, int dfdx, int dfdy) 
   if (c->g.nx < 2 || c->g.ny < 2) { fs_set_error("fsgpu_calc_grad_of_centered_points: grid too small"); return 1; }
   return fs_launch_grad_centered(c, f, dfdx, dfdy);
 }
+static int sample_impl(fsgpu_ctx* c, int mode, int fa, int fb, const double* x, const double* y, int64_t n,
+                       const double* px, const double* py, double* oa, double* ob) {
+  FS_CHECK_CTX(c);
+  FS_CHECK_FIELD(fa);
+  FS_CHECK_FIELD(fb);
+  int64_t m2, n2;
+  field_extent(c->g, fa, &m2, &n2);
+  if (m2 != c->g.nx + 2 || n2 != c->g.ny + 2) { fs_set_error("point sampling: field %d is not a cell field", fa); return 1; }
+  if (c->nranks > 1) { fs_set_error("point sampling works on a single context (points may lie in any slab)"); return 1; }
+  if (n < 0 || !x || !y || (n > 0 && (!px || !py || !oa || (mode == 0 && !ob)))) {
+    fs_set_error("point sampling: bad arguments");
+    return 1;
+  }
+  if (c->g.nx < 2 || c->g.ny < 2) { fs_set_error("point sampling: grid too small"); return 1; }
+  return fs_sample_points(c, mode, fa, fb, x, y, n, px, py, oa, ob);
+}
+int fsgpu_eval_flow_field_at(fsgpu_ctx* c, const double* x, const double* y, int64_t n, const double* px,
+                             const double* py, double* u, double* v) {
+  return sample_impl(c, 0, FSGPU_UI, FSGPU_VI, x, y, n, px, py, u, v);
+}
+int fsgpu_bilinear_interpolate(fsgpu_ctx* c, int field, const double* x, const double* y, int64_t n,
+                               const double* px, const double* py, double* out) {
+  return sample_impl(c, 1, field, field, x, y, n, px, py, out, nullptr);
+}
 int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out) { return abs_max_impl(c, field, false, out); }
 int fsgpu_abs_max_all(fsgpu_ctx* c, int field, double* out) { return abs_max_impl(c, field, true, out); }
 

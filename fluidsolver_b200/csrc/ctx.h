@@ -125,3 +125,5 @@ int fs_launch_interpolate(fsgpu_ctx* c);
 int fs_launch_conserved(fsgpu_ctx* c);  // -> red_out[4..6]
 int fs_launch_monitor(fsgpu_ctx* c);    // -> red_out[4..6]
 int fs_launch_grad_centered(fsgpu_ctx* c, int f, int dfdx, int dfdy);
+int fs_sample_points(fsgpu_ctx* c, int mode, int fa, int fb, const double* xm, const double* ym, int64_t npts,
+                     const double* px, const double* py, double* oa, double* ob);

@@ -16,6 +16,7 @@
 #include <math.h>
 
 #include <algorithm>
+#include <vector>
 
 namespace {
 
@@ -273,6 +274,49 @@ k_grad_centered(const double* __restrict__ f, double* __restrict__ gx, double* _
   gy[k] = y;
 }
 
+// bilinear sampling of cell fields at arbitrary points, src/Operators.hpp:85-161.  xm, ym: cell-centre
+// coordinates incl. their ghost entry (index + 1).  MODE 0 = eval_flow_field_at (index pairs clamped into
+// [0, N-1], two fields), MODE 1 = bilinear_interpolate (clamped by position only, one field).
+struct SampleArgs {
+  const double *fa, *fb, *xm, *ym, *px, *py;
+  double *oa, *ob;
+  int64_t npts;
+};
+template <int MODE>
+__device__ __forceinline__ void sample_indices(double pos, const double* __restrict__ grid, int64_t N, double delta,
+                                               int64_t& prev, int64_t& next) {
+  const int64_t p = (int64_t)floor((pos - grid[1]) / delta);
+  const int64_t q = (int64_t)floor((pos - grid[1]) / delta + 1.0);
+  if (pos <= grid[1] || (MODE == 0 && p < 0)) { prev = next = 0; return; }
+  if (pos >= grid[N] || (MODE == 0 && q >= N)) { prev = next = N - 1; return; }
+  prev = p;
+  next = q;
+}
+template <int MODE>
+__global__ void __launch_bounds__(256)
+k_sample(const SampleArgs s, const Geom g) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= s.npts) return;
+  const double dx = s.xm[2] - s.xm[1], dy = s.ym[2] - s.ym[1];
+  const double x = s.px[k], y = s.py[k];
+  int64_t ip, in, jp, jn;
+  sample_indices<MODE>(x, s.xm, g.nx, dx, ip, in);
+  sample_indices<MODE>(y, s.ym, g.ny, dy, jp, jn);
+  const int64_t k00 = g.idx(ip + 1, jp + 1), k10 = g.idx(in + 1, jp + 1), k01 = g.idx(ip + 1, jn + 1),
+                k11 = g.idx(in + 1, jn + 1);
+  const double tx = x - s.xm[ip + 1], ty = y - s.ym[jp + 1];
+  {
+    const double a = (s.fa[k10] - s.fa[k00]) / dx * tx + s.fa[k00];
+    const double b = (s.fa[k11] - s.fa[k01]) / dx * tx + s.fa[k01];
+    s.oa[k] = (b - a) / dy * ty + a;
+  }
+  if (MODE == 0) {
+    const double a = (s.fb[k10] - s.fb[k00]) / dx * tx + s.fb[k00];
+    const double b = (s.fb[k11] - s.fb[k01]) / dx * tx + s.fb[k01];
+    s.ob[k] = (b - a) / dy * ty + a;
+  }
+}
+
 }  // namespace
 
 static dim3 face_grid(const Geom& g) {
@@ -423,6 +467,37 @@ int fs_launch_grad_centered(fsgpu_ctx* c, int f, int dfdx, int dfdy) {
   FS_LAUNCHED();
   const int fl[2] = {dfdx, dfdy};
   return fs_exchange_fields(c, fl, 2, FS_RO);
+}
+
+// host arrays in, host arrays out: xm, ym are fs.xm / fs.ym incl. ghosts (NX + 2 and NY + 2 values)
+int fs_sample_points(fsgpu_ctx* c, int mode, int fa, int fb, const double* xm, const double* ym, int64_t npts,
+                     const double* px, const double* py, double* oa, double* ob) {
+  const int64_t nx = c->g.nx, ny = c->g.ny;
+  if (npts <= 0) return 0;
+  std::vector<double> h((size_t)(nx + ny + 4));
+  std::copy(xm, xm + nx + 2, h.begin());
+  std::copy(ym, ym + ny + 2, h.begin() + (nx + 2));
+  double* d = nullptr;
+  const size_t nc = (size_t)(nx + ny + 4), np = (size_t)npts;
+  FS_CUDA(cudaMalloc(&d, (nc + 4 * np) * sizeof(double)));
+  int rc = cudaMemcpyAsync(d, h.data(), nc * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+           cudaMemcpyAsync(d + nc, px, np * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess ||
+           cudaMemcpyAsync(d + nc + np, py, np * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess;
+  if (!rc) {
+    SampleArgs s{c->f[fa], mode == 0 ? c->f[fb] : nullptr, d, d + nx + 2, d + nc, d + nc + np, d + nc + 2 * np,
+                 d + nc + 3 * np, npts};
+    const unsigned nb = (unsigned)((npts + 255) / 256);
+    if (mode == 0) k_sample<0><<<nb, 256, 0, c->stream>>>(s, c->g);
+    else k_sample<1><<<nb, 256, 0, c->stream>>>(s, c->g);
+    ++g_launches;
+    rc = cudaPeekAtLastError() != cudaSuccess ||
+         cudaMemcpyAsync(oa, d + nc + 2 * np, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+         (mode == 0 && cudaMemcpyAsync(ob, d + nc + 3 * np, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess);
+  }
+  rc = rc || cudaStreamSynchronize(c->stream) != cudaSuccess;
+  cudaFree(d);
+  if (rc) fs_set_error("point sampling: %s", cudaGetErrorString(cudaGetLastError()));
+  return rc ? 1 : 0;
 }
 
 int fs_launch_monitor(fsgpu_ctx* c) {  // -> red_out[4..6]

@@ -46,6 +46,7 @@ SYMBOLS = (
     "fsgpu_calc_mid_time", "fsgpu_calc_dmomdt", "fsgpu_update_velocity", "fsgpu_momentum_update",
     "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_flow_control", "fsgpu_set_flow_control",
     "fsgpu_integrate", "fsgpu_l1_norm", "fsgpu_calc_grad_of_centered_points",
+    "fsgpu_eval_flow_field_at", "fsgpu_bilinear_interpolate",
     "fsgpu_to_npy", "fsgpu_to_npy_state", "fsgpu_npy_write_host", "fsgpu_write_vtk", "fsgpu_calc_divergence",
     "fsgpu_shift_pressure_to_zero", "fsgpu_correct_velocity", "fsgpu_abs_max", "fsgpu_abs_max_all",
     "fsgpu_calc_rho_visc_const", "fsgpu_calc_rho_visc_vof", "fsgpu_apply_neumann_bconds",
@@ -125,6 +126,8 @@ def load():
     L.fsgpu_integrate.argtypes = [vp, i32, i32, DP]
     L.fsgpu_l1_norm.argtypes = [vp, i32, i32, DP]
     L.fsgpu_calc_grad_of_centered_points.argtypes = [vp, i32, i32, i32]
+    L.fsgpu_eval_flow_field_at.argtypes = [vp, DP, DP, i64, DP, DP, DP, DP]
+    L.fsgpu_bilinear_interpolate.argtypes = [vp, i32, DP, DP, i64, DP, DP, DP]
     L.fsgpu_abs_max_all.argtypes = [vp, i32, DP]
     L.fsgpu_apply_neumann_bconds.argtypes = [vp, i32]
     L.fsgpu_ps_create.argtypes = [vp, C.POINTER(PsOpts), C.POINTER(vp)]
@@ -405,6 +408,32 @@ class FS:
     def calc_grad_of_centered_points(self, f, dfdx="GRAD_X", dfdy="GRAD_Y"):
         """src/Operators.hpp:164-201 on cell fields"""
         _chk(self.L.fsgpu_calc_grad_of_centered_points(self.h, FIELD_ID[f], FIELD_ID[dfdx], FIELD_ID[dfdy]))
+
+    def _centres(self, x, y):
+        x, y = self._coords(x, y)
+        assert x.size == self.nx + 3 and y.size == self.ny + 3
+        return np.ascontiguousarray((x[:-1] + x[1:]) / 2), np.ascontiguousarray((y[:-1] + y[1:]) / 2)  # init_grid, FS.hpp:71-72
+
+    def eval_flow_field_at(self, x, y, px, py):
+        """eval_flow_field_at(xm, ym, Ui, Vi, x, y), src/Operators.hpp:118-161, at the points (px, py) -> (u, v);
+        x, y: fs.x / fs.y incl. ghosts (grid_coords())"""
+        x, y = self._centres(x, y)
+        px, py = self._coords(px, py)
+        u, v = np.zeros_like(px), np.zeros_like(px)
+        _chk(self.L.fsgpu_eval_flow_field_at(self.h, x.ctypes.data_as(DP), y.ctypes.data_as(DP), px.size,
+                                             px.ctypes.data_as(DP), py.ctypes.data_as(DP), u.ctypes.data_as(DP),
+                                             v.ctypes.data_as(DP)))
+        return u, v
+
+    def bilinear_interpolate(self, name, x, y, px, py):
+        """bilinear_interpolate(xm, ym, field, x, y), src/Operators.hpp:85-115, on a cell field"""
+        x, y = self._centres(x, y)
+        px, py = self._coords(px, py)
+        out = np.zeros_like(px)
+        _chk(self.L.fsgpu_bilinear_interpolate(self.h, FIELD_ID[name], x.ctypes.data_as(DP), y.ctypes.data_as(DP),
+                                               px.size, px.ctypes.data_as(DP), py.ctypes.data_as(DP),
+                                               out.ctypes.data_as(DP)))
+        return out
 
     def calc_rho_visc_const(self):
         _chk(self.L.fsgpu_calc_rho_visc_const(self.h))

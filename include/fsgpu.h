@@ -205,6 +205,14 @@ int fsgpu_l1_norm(fsgpu_ctx* c, int field, int include_ghost, double* out);
 /* calc_grad_of_centered_points(f, dx, dy, dfdx, dfdy), src/Operators.hpp:164-201: three distinct cell
  * fields (e.g. FSGPU_VF -> FSGPU_GRAD_X, FSGPU_GRAD_Y); every cell incl. ghosts is written */
 int fsgpu_calc_grad_of_centered_points(fsgpu_ctx* c, int f, int dfdx, int dfdy);
+/* eval_flow_field_at(xm, ym, Ui, Vi, x, y), src/Operators.hpp:118-161, at n points (px[k], py[k]) on FSGPU_UI /
+ * FSGPU_VI as they are (fsgpu_interpolate_cell_centres fills them), and bilinear_interpolate(xm, ym, field, x, y),
+ * :85-115, on any cell field.  xm, ym: fs.xm / fs.ym incl. ghosts (NX + 2 and NY + 2 doubles, fs.xm.get_data());
+ * all arrays are host arrays; single context only. */
+int fsgpu_eval_flow_field_at(fsgpu_ctx* c, const double* xm, const double* ym, int64_t n, const double* px,
+                             const double* py, double* u, double* v);
+int fsgpu_bilinear_interpolate(fsgpu_ctx* c, int field, const double* xm, const double* ym, int64_t n,
+                               const double* px, const double* py, double* out);
 /* calc_rho(fs)/calc_visc(fs), src/FS.hpp:569-589 and calc_rho(vf,fs)/calc_visc(vf,fs),
  * src/FS.hpp:592-650 (uses FSGPU_VF) */
 int fsgpu_calc_rho_visc_const(fsgpu_ctx* c);

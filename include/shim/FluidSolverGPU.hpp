@@ -27,6 +27,7 @@
 #include <source_location>
 #include <string>
 #include <string_view>
+#include <utility>
 #include <variant>
 #include <vector>
 
@@ -455,6 +456,32 @@ template <typename Float, Index NX, Index NY, Index NGHOST>
 void calc_conserved_quantities(const FS<Float, NX, NY, NGHOST>& fs, Float& mass, Float& momentum_x,
                                Float& momentum_y) {
   FSGPU_CHECK(fsgpu_calc_conserved_quantities(fs.ctx, &mass, &momentum_x, &momentum_y));
+}
+
+// eval_flow_field_at / bilinear_interpolate, src/Operators.hpp:85-161, on device-bound cell fields: the reference's
+// one-point signatures (one kernel per call) and batched forms for callers that sample many points per step
+template <typename Float, Index NX, Index NY, Index NGHOST>
+void eval_flow_field_at(const Field1D<Float, NX, NGHOST>& xm, const Field1D<Float, NY, NGHOST>& ym,
+                        const Field2D<Float, NX, NY, NGHOST>& Ui, const Field2D<Float, NX, NY, NGHOST>& Vi, Index n,
+                        const Float* x, const Float* y, Float* u, Float* v) {
+  if (Ui.field_id() != FSGPU_UI || Vi.field_id() != FSGPU_VI) fsgpu_shim::check(1, "eval_flow_field_at expects the fields interpolate_U / interpolate_V filled");
+  FSGPU_CHECK(fsgpu_eval_flow_field_at(fsgpu_shim::ctx_of(Ui), xm.get_data(), ym.get_data(), n, x, y, u, v));
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+[[nodiscard]] std::pair<Float, Float> eval_flow_field_at(const Field1D<Float, NX, NGHOST>& xm, const Field1D<Float, NY, NGHOST>& ym,
+                                                         const Field2D<Float, NX, NY, NGHOST>& Ui,
+                                                         const Field2D<Float, NX, NY, NGHOST>& Vi, Float x, Float y) {
+  Float u = 0, v = 0;
+  eval_flow_field_at(xm, ym, Ui, Vi, Index{1}, &x, &y, &u, &v);
+  return {u, v};
+}
+template <typename Float, Index NX, Index NY, Index NGHOST>
+[[nodiscard]] Float bilinear_interpolate(const Field1D<Float, NX, NGHOST>& xm, const Field1D<Float, NY, NGHOST>& ym,
+                                         const Field2D<Float, NX, NY, NGHOST>& field, Float x, Float y) {
+  Float out = 0;
+  FSGPU_CHECK(fsgpu_bilinear_interpolate(fsgpu_shim::ctx_of(field), field.field_id(), xm.get_data(), ym.get_data(), 1, &x,
+                                         &y, &out));
+  return out;
 }
 
 // The channel drivers' corrections of the two ghost columns U(-1, .) and U(NX+1, .) after

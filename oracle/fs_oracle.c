@@ -524,6 +524,43 @@ void fso_grad_centered(const double* f, int64_t m, int64_t n, double dx, double 
 #undef GY
 }
 
+/* bilinear sampling of cell-centred fields, src/Operators.hpp:85-161.  xm, ym: the cell-centre coordinates incl.
+ * their ghost entries (m + 2 and n + 2 values).  mode 0 = eval_flow_field_at (:118-161, both index pairs clamped
+ * into [0, N-1]); mode 1 = bilinear_interpolate (:85-115, clamped by position only). */
+static void sample_indices(int mode, double pos, const double* grid /* grid[k + 1] = grid(k) */, int64_t N, double delta,
+                           int64_t* prev, int64_t* next) {
+  const int64_t p = (int64_t)floor((pos - grid[1]) / delta);
+  const int64_t q = (int64_t)floor((pos - grid[1]) / delta + 1.0);
+  if (mode == 0) {
+    if (pos <= grid[1] || p < 0) { *prev = *next = 0; return; }
+    if (pos >= grid[N] || q >= N) { *prev = *next = N - 1; return; }
+  } else {
+    if (pos <= grid[1]) { *prev = *next = 0; return; }
+    if (pos >= grid[N]) { *prev = *next = N - 1; return; }
+  }
+  *prev = p;
+  *next = q;
+}
+static double sample_one(const double* f, int64_t n, const double* xm, const double* ym, double dx, double dy,
+                         int64_t ip, int64_t in, int64_t jp, int64_t jn, double x, double y) {
+#define F(i, j) f[(j) + 1 + ((i) + 1) * (n + 2)]
+  const double a = (F(in, jp) - F(ip, jp)) / dx * (x - xm[ip + 1]) + F(ip, jp);
+  const double b = (F(in, jn) - F(ip, jn)) / dx * (x - xm[ip + 1]) + F(ip, jn);
+#undef F
+  return (b - a) / dy * (y - ym[jp + 1]) + a;
+}
+void fso_sample(int mode, const double* fa, const double* fb, int64_t m, int64_t n, const double* xm, const double* ym,
+                int64_t npts, const double* px, const double* py, double* oa, double* ob) {
+  const double dx = xm[2] - xm[1], dy = ym[2] - ym[1];  /* xm(1) - xm(0) */
+  for (int64_t k = 0; k < npts; ++k) {
+    int64_t ip, in, jp, jn;
+    sample_indices(mode, px[k], xm, m, dx, &ip, &in);
+    sample_indices(mode, py[k], ym, n, dy, &jp, &jn);
+    oa[k] = sample_one(fa, n, xm, ym, dx, dy, ip, in, jp, jn, px[k], py[k]);
+    if (fb && ob) ob[k] = sample_one(fb, n, xm, ym, dx, dy, ip, in, jp, jn, px[k], py[k]);
+  }
+}
+
 /* src/BoundaryConditions.hpp:227-252 for an (m+2) x (n+2) field */
 void fso_apply_neumann_bconds(double* f, int64_t m, int64_t n) {
 #define F(i, j) f[(j) + 1 + ((i) + 1) * (n + 2)]

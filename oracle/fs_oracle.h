@@ -80,6 +80,9 @@ void fso_correct(fso_fs* fs, const double* dp, double dt);
 double fso_abs_max(const double* a, int64_t m, int64_t n, int include_ghost);
 /* integrate / L1_norm, src/Operators.hpp:51-76; calc_grad_of_centered_points, :164-201 */
 double fso_integrate(const double* a, int64_t m, int64_t n, double dx, double dy, int include_ghost, int l1);
+/* eval_flow_field_at (mode 0, fa = Ui, fb = Vi) / bilinear_interpolate (mode 1, fb = ob = NULL), src/Operators.hpp:85-161 */
+void fso_sample(int mode, const double* fa, const double* fb, int64_t m, int64_t n, const double* xm, const double* ym,
+                int64_t npts, const double* px, const double* py, double* oa, double* ob);
 void fso_grad_centered(const double* f, int64_t m, int64_t n, double dx, double dy, double* dfdx, double* dfdy);
 /* src/FS.hpp:569-650 with src/BoundaryConditions.hpp:227-252 */
 void fso_calc_rho_visc_const(fso_fs* fs);

@@ -82,6 +82,7 @@ struct SessionBase {
   virtual void conserved(double* mass, double* mx, double* my)                 = 0;
   virtual double flow_control(int mode, double total_flow, double* io)         = 0;
   virtual int to_npy(const char* dir)                                          = 0;
+  virtual void sample(int mode, int n, const double* px, const double* py, double* a, double* b) = 0;
   virtual double integrate_cell(const double* f, int include_ghost, int l1)    = 0;
   virtual void grad_centered(const double* f, double* dfdx, double* dfdy)      = 0;
   virtual int write_vtk(const char* dir, double t)                             = 0;
@@ -402,6 +403,23 @@ struct Session final : SessionBase {
     if (res) *res = r;
     return iters;
   }
+  // mode 0: eval_flow_field_at(xm, ym, Ui, Vi, x, y) (src/Operators.hpp:118-161) with Ui, Vi from interpolate_U / _V;
+  // mode 1: bilinear_interpolate(xm, ym, p, x, y) (:85-115) -> a
+  void sample(int mode, int n, const double* px, const double* py, double* a, double* b) override {
+    auto ui = std::make_unique<Field2D<Float, NX, NY, G>>();
+    auto vi = std::make_unique<Field2D<Float, NX, NY, G>>();
+    ::interpolate_U(fs.curr.U, *ui);
+    ::interpolate_V(fs.curr.V, *vi);
+    for (int k = 0; k < n; ++k) {
+      if (mode == 0) {
+        const auto uv = ::eval_flow_field_at(fs.xm, fs.ym, *ui, *vi, px[k], py[k]);
+        a[k] = uv.first;
+        b[k] = uv.second;
+      } else {
+        a[k] = ::bilinear_interpolate(fs.xm, fs.ym, fs.p, px[k], py[k]);
+      }
+    }
+  }
   // integrate / L1_norm (src/Operators.hpp:51-76) and calc_grad_of_centered_points (:164-201) on a cell field
   double integrate_cell(const double* f, int include_ghost, int l1) override {
     cp_in(div, f);
@@ -488,6 +506,9 @@ void fsref_calc_pressure_jump(void* s, const double* vf, const double* curv, con
 void fsref_interpolate_uv(void* s, double* ui, double* vi) { S->interpolate_uv(ui, vi); }
 void fsref_conserved(void* s, double* mass, double* mx, double* my) { S->conserved(mass, mx, my); }
 int fsref_to_npy(void* s, const char* dir) { return S->to_npy(dir); }
+void fsref_sample(void* s, int mode, int n, const double* px, const double* py, double* a, double* b) {
+  S->sample(mode, n, px, py, a, b);
+}
 // Monitor (src/Monitor.hpp) driven with nrows x (nf Float + ni Index) values: the log file as the drivers write it
 int fsref_monitor_log(const char* filename, int nf, const char* const* fnames, int ni, const char* const* inames,
                       int nrows, const double* fvals, const int64_t* ivals) {

@@ -315,3 +315,17 @@ def run_channel_study(adjust_dt, step, t_end=20.0):
         t += dt
         n += 1
     return n
+
+
+def sample_points(st, n=400, seed=33):
+    """query points for eval_flow_field_at / bilinear_interpolate: uniform over a box 1.5 cells larger than the
+    domain (so every clamped branch is taken), plus points exactly on cell centres and on the first / last one"""
+    rng = np.random.default_rng(seed)
+    lx, ly = st.nx * st.dx, st.ny * st.dy
+    px = rng.uniform(-1.5 * st.dx, lx + 1.5 * st.dx, n)
+    py = rng.uniform(-1.5 * st.dy, ly + 1.5 * st.dy, n)
+    xm = (np.arange(st.nx) + 0.5) * st.dx
+    ym = (np.arange(st.ny) + 0.5) * st.dy
+    ex = np.array([xm[0], xm[-1], xm[3], xm[0], xm[-1], 0.5 * lx])
+    ey = np.array([ym[0], ym[-1], ym[5], ym[-1], ym[0], ym[2]])
+    return np.concatenate([px, ex]), np.concatenate([py, ey])

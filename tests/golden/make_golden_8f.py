@@ -15,7 +15,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
 
-from cases import (CHANNEL215_TOTAL_FLOW, channel_study_case, channel_study_errors, run_channel_study, cavity_bc, cavity_state, channel215_state, couette_bc,  # noqa: E402
+from cases import (sample_points, CHANNEL215_TOTAL_FLOW, channel_study_case, channel_study_errors, run_channel_study, cavity_bc, cavity_state, channel215_state, couette_bc,  # noqa: E402
                    couette_state, custom_channel_bc, ib_inputs, periodic_channel_bc, profile_bcs, random_state,
                    twophase_inputs)
 from oracle_lib import Oracle, Ref  # noqa: E402
@@ -244,6 +244,18 @@ def operators_misc(name="operators_random48x20"):
     print(name, out["sums"])
 
 
+def sampling(name="sampling_random48x20"):
+    """eval_flow_field_at on (Ui, Vi) and bilinear_interpolate on p (src/Operators.hpp:85-161) at seeded points, some of
+    them outside the cell-centre box (clamped branches) and some exactly on cell centres"""
+    st = random_state(48, 20, seed=21)
+    px, py = sample_points(st)
+    r = Ref(st.nx, st.ny)
+    r.load(st)
+    u, v = r.sample(0, px, py)
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), u=u, v=v, p=r.sample(1, px, py))
+    print(name, u[:3], v[:3])
+
+
 def monitor_log(name="monitor_log.txt"):
     """src/Monitor.hpp and should_save (src/IO.hpp:97-108) of the unmodified reference on the rows / step sequence of
     tests/test_output_cpu.py"""
@@ -280,6 +292,9 @@ if __name__ == "__main__":
     if "channel215" in sys.argv:
         for nm in CHANNEL215:
             run_channel215(nm)
+        sys.exit(0)
+    if "sampling" in sys.argv:
+        sampling()
         sys.exit(0)
     if "monitor" in sys.argv:
         monitor_log()
@@ -318,3 +333,4 @@ if __name__ == "__main__":
     channel_study()
     operators_misc()
     monitor_log()
+    sampling()

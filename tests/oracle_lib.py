@@ -159,6 +159,7 @@ class Oracle:
         L.fso_abs_max.restype = C.c_double
         L.fso_integrate.restype = C.c_double
         L.fso_integrate.argtypes = [DP, C.c_int64, C.c_int64, C.c_double, C.c_double, C.c_int, C.c_int]
+        L.fso_sample.argtypes = [C.c_int, DP, DP, C.c_int64, C.c_int64, DP, DP, C.c_int64, DP, DP, DP, DP]
         L.fso_grad_centered.argtypes = [DP, C.c_int64, C.c_int64, C.c_double, C.c_double, DP, DP]
         L.fso_abs_max.argtypes = [DP, C.c_int64, C.c_int64, C.c_int]
         L.fso_calc_mid_time.argtypes = [DP, DP, C.c_int64]
@@ -286,6 +287,19 @@ class Oracle:
         a = np.ascontiguousarray(a)
         return self.lib.fso_integrate(_ptr(a), a.shape[0] - 2, a.shape[1] - 2, dx, dy, int(include_ghost), int(l1))
 
+    def sample(self, mode, fa, fb, xm, ym, px, py):
+        """mode 0: eval_flow_field_at(xm, ym, fa = Ui, fb = Vi, x, y) -> (u, v); mode 1: bilinear_interpolate(xm, ym, fa, x, y)
+        -> values (src/Operators.hpp:85-161); xm, ym incl. ghost entries"""
+        fa = np.ascontiguousarray(fa)
+        px, py = np.ascontiguousarray(px, dtype=np.float64), np.ascontiguousarray(py, dtype=np.float64)
+        xm, ym = np.ascontiguousarray(xm, dtype=np.float64), np.ascontiguousarray(ym, dtype=np.float64)
+        oa, ob = np.zeros_like(px), np.zeros_like(px)
+        if fb is not None:
+            fb = np.ascontiguousarray(fb)
+        self.lib.fso_sample(mode, _ptr(fa), _ptr(fb) if fb is not None else None, fa.shape[0] - 2, fa.shape[1] - 2,
+                            _ptr(xm), _ptr(ym), px.size, _ptr(px), _ptr(py), _ptr(oa), _ptr(ob) if fb is not None else None)
+        return (oa, ob) if fb is not None else oa
+
     def grad_centered(self, f, dx, dy):
         """calc_grad_of_centered_points, src/Operators.hpp:164-201 -> (dfdx, dfdy)"""
         f = np.ascontiguousarray(f)
@@ -390,6 +404,7 @@ class Ref:
             L.fsref_conserved.argtypes = [C.c_void_p, DP, DP, DP]
             L.fsref_flow_control.argtypes = [C.c_void_p, C.c_int, C.c_double, DP]
             L.fsref_to_npy.argtypes = [C.c_void_p, C.c_char_p]
+            L.fsref_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, DP, DP, DP, DP]
             L.fsref_monitor_log.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_char_p),
                                             C.c_int, DP, C.POINTER(C.c_int64)]
             L.fsref_should_save.argtypes = [C.c_double] * 4
@@ -526,6 +541,13 @@ class Ref:
     def integrate(self, a, include_ghost=False, l1=False):
         a = np.ascontiguousarray(a)
         return self.lib().fsref_integrate_cell(self.h, _ptr(a), int(include_ghost), int(l1))
+
+    def sample(self, mode, px, py):
+        """mode 0: eval_flow_field_at on Ui, Vi of the loaded state -> (u, v); mode 1: bilinear_interpolate of fs.p"""
+        px, py = np.ascontiguousarray(px, dtype=np.float64), np.ascontiguousarray(py, dtype=np.float64)
+        a, b = np.zeros_like(px), np.zeros_like(px)
+        self.lib().fsref_sample(self.h, mode, px.size, _ptr(px), _ptr(py), _ptr(a), _ptr(b))
+        return (a, b) if mode == 0 else a
 
     def grad_centered(self, f):
         f = np.ascontiguousarray(f)

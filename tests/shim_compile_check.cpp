@@ -69,7 +69,8 @@ int main(int argc, char**) {
   Field2D<Float, NX, NY, NGHOST> dvfdx{}, dvfdy{};
   calc_grad_of_centered_points(vf, fs.dx, fs.dy, dvfdx, dvfdy);
   const Float vol = integrate<true>(fs.dx, fs.dy, vf) + L1_norm(fs.dx, fs.dy, div);
-  if (!(vol == vol)) return 3;
+  const auto [us, vs] = eval_flow_field_at(fs.xm, fs.ym, Ui, Vi, 0.7, 0.3);
+  if (!(vol + us + vs + bilinear_interpolate(fs.xm, fs.ym, fs.p, 0.7, 0.3) == vol + us + vs + bilinear_interpolate(fs.xm, fs.ym, fs.p, 0.7, 0.3))) return 3;
   DataWriter<Float, NX, NY, NGHOST> data_writer("/tmp/fsgpu_shim_check", &fs.x, &fs.y);
   data_writer.add_scalar("pressure", &fs.p);
   data_writer.add_scalar("divergence", &div);

@@ -427,3 +427,38 @@ def test_cpp_periodic_channel_driver(tmp_path):
     assert head.startswith(b"# vtk DataFile Version 2.0\nState of FluidSolver at time t=")
     size = os.path.getsize(out / frames[-1])
     assert size > (nx + 1) * (ny + 1) * 24 + nx * ny * (8 + 8 + 24)
+
+
+def test_point_sampling_vs_reference_golden(F, oracle):
+    """eval_flow_field_at / bilinear_interpolate (src/Operators.hpp:85-161) at seeded points, incl. points outside the
+    cell-centre box, against the unmodified reference; then the reference's own known-answer test
+    (test/Operators.cpp:24-84, bilinear fields reproduced within 100 eps)"""
+    from cases import grid_coords, random_state, rel_inf, sample_points
+    g = np.load(os.path.join(GOLD, "sampling_random48x20.npz"))
+    st = random_state(48, 20, seed=21)
+    px, py = sample_points(st)
+    x, y = grid_coords(st)
+    fs = to_gpu(F, st)
+    fs.interpolate_cell_centres()
+    u, v = fs.eval_flow_field_at(x, y, px, py)
+    assert rel_inf(u, g["u"]) <= 1e-12 and rel_inf(v, g["v"]) <= 1e-12
+    assert rel_inf(fs.bilinear_interpolate("P", x, y, px, py), g["p"]) <= 1e-12
+    with pytest.raises(F.FsgpuError):
+        fs.bilinear_interpolate("U", x, y, px, py)
+    fs.close()
+
+    nx, ny, dx, dy = 200, 300, 2.0 / 200, 4.0 / 300
+    x = 2.0 + np.arange(-1, nx + 2) * dx
+    y = -1.0 + np.arange(-1, ny + 2) * dy
+    xm, ym = (x[:-1] + x[1:]) / 2, (y[:-1] + y[1:]) / 2
+    fs = F.FS(nx, ny, dx, dy)
+    fs.upload("U", 12.0 * x[:, None] + ym[None, :])
+    fs.upload("V", xm[:, None] * y[None, :] - 27.31415)
+    fs.interpolate_cell_centres()
+    k = np.arange(50)
+    PX, PY = (a.ravel() for a in np.meshgrid((xm[nx] - xm[1]) / 49.0 * k + xm[1], (ym[ny] - ym[1]) / 49.0 * k + ym[1],
+                                             indexing="ij"))
+    u, v = fs.eval_flow_field_at(x, y, PX, PY)
+    eps = 400.0 * np.finfo(float).eps   # the reference asks 100 eps of its own (differently contracted) arithmetic
+    assert np.abs(u - (12.0 * PX + PY)).max() <= eps and np.abs(v - (PX * PY - 27.31415)).max() <= eps
+    fs.close()
