@@ -329,3 +329,24 @@ def sample_points(st, n=400, seed=33):
     ex = np.array([xm[0], xm[-1], xm[3], xm[0], xm[-1], 0.5 * lx])
     ey = np.array([ym[0], ym[-1], ym[5], ym[-1], ym[0], ym[2]])
     return np.concatenate([px, ex]), np.concatenate([py, ey])
+
+
+def conserved_known_answer():
+    """the reference's own test of calc_conserved_quantities (test/Operators.cpp:217-283): rho = 12 x + x y^2,
+    rho U = rho sin(x + y), rho V = rho cos(x + y) on [2, 4] x [-1, 3], 200 x 300 cells; -> (state, expected (mass,
+    momentum_x, momentum_y) by Gauss-Legendre quadrature, tolerance 10 min(dx, dy)^2)"""
+    nx, ny, dx, dy = 200, 300, 2.0 / 200, 4.0 / 300
+    st = State(nx, ny, dx, dy)
+    x = 2.0 + np.arange(-1, nx + 2) * dx
+    y = -1.0 + np.arange(-1, ny + 2) * dy
+    xm, ym = (x[:-1] + x[1:]) / 2, (y[:-1] + y[1:]) / 2
+    rho = lambda X, Y: 12.0 * X + X * Y * Y  # noqa: E731
+    XU, YU = np.meshgrid(x, ym, indexing="ij")
+    XV, YV = np.meshgrid(xm, y, indexing="ij")
+    st.a["rho_u"][:], st.a["U"][:] = rho(XU, YU), np.sin(XU + YU)
+    st.a["rho_v"][:], st.a["V"][:] = rho(XV, YV), np.cos(XV + YV)
+    gx, gw = np.polynomial.legendre.leggauss(96)
+    QX, QY = np.meshgrid(3.0 + gx, 1.0 + 2.0 * gx, indexing="ij")   # [2, 4] x [-1, 3]
+    W = np.outer(gw, gw) * 2.0
+    expected = tuple(float((W * f).sum()) for f in (rho(QX, QY), rho(QX, QY) * np.sin(QX + QY), rho(QX, QY) * np.cos(QX + QY)))
+    return st, expected, 10.0 * min(dx, dy) ** 2

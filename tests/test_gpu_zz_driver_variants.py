@@ -462,3 +462,13 @@ def test_point_sampling_vs_reference_golden(F, oracle):
     eps = 400.0 * np.finfo(float).eps   # the reference asks 100 eps of its own (differently contracted) arithmetic
     assert np.abs(u - (12.0 * PX + PY)).max() <= eps and np.abs(v - (PX * PY - 27.31415)).max() <= eps
     fs.close()
+
+
+def test_conserved_quantities_known_answer(F):
+    """the reference's own test of calc_conserved_quantities (test/Operators.cpp:217-283) on the GPU"""
+    from cases import conserved_known_answer
+    st, expected, tol = conserved_known_answer()
+    fs = to_gpu(F, st)
+    got = fs.calc_conserved_quantities()
+    assert np.abs(np.array(got) - np.array(expected)).max() <= tol
+    fs.close()
