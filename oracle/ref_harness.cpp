@@ -24,6 +24,7 @@
 #include "LinearSolver_StructHypre.hpp"
 #include "Monitor.hpp"
 #include "Operators.hpp"
+#include "Quadrature.hpp"
 #include "Utility.hpp"
 
 #include "fs_oracle.h"
@@ -82,6 +83,7 @@ struct SessionBase {
   virtual void conserved(double* mass, double* mx, double* my)                 = 0;
   virtual double flow_control(int mode, double total_flow, double* io)         = 0;
   virtual int to_npy(const char* dir)                                          = 0;
+  virtual void vf_drop(double* vf)                                             = 0;
   virtual void sample(int mode, int n, const double* px, const double* py, double* a, double* b) = 0;
   virtual double integrate_cell(const double* f, int include_ghost, int l1)    = 0;
   virtual void grad_centered(const double* f, double* dfdx, double* dfdy)      = 0;
@@ -420,6 +422,19 @@ struct Session final : SessionBase {
       }
     }
   }
+  // the initial volume fraction of test/StationaryDrop.cpp:47-52,209-212: 16-point Gauss quadrature
+  // (src/Quadrature.hpp:37-66) of the ellipse indicator over every cell incl. ghosts, then apply_neumann_bconds
+  void vf_drop(double* out) override {
+    constexpr Float CX = 0.5, CY = 0.5, R0 = 0.25;
+    constexpr auto vof0 = [](Float x, Float y) {
+      return static_cast<Float>(Igor::sqr(2.0 * (x - CX)) + Igor::sqr(y - CY) <= Igor::sqr(R0));
+    };
+    for_each_a<Exec::Parallel>(div, [&](Index i, Index j) {
+      div(i, j) = quadrature(vof0, fs.x(i), fs.x(i + 1), fs.y(j), fs.y(j + 1)) / (fs.dx * fs.dy);
+    });
+    ::apply_neumann_bconds(div);
+    cp_out(div, out);
+  }
   // integrate / L1_norm (src/Operators.hpp:51-76) and calc_grad_of_centered_points (:164-201) on a cell field
   double integrate_cell(const double* f, int include_ghost, int l1) override {
     cp_in(div, f);
@@ -506,6 +521,7 @@ void fsref_calc_pressure_jump(void* s, const double* vf, const double* curv, con
 void fsref_interpolate_uv(void* s, double* ui, double* vi) { S->interpolate_uv(ui, vi); }
 void fsref_conserved(void* s, double* mass, double* mx, double* my) { S->conserved(mass, mx, my); }
 int fsref_to_npy(void* s, const char* dir) { return S->to_npy(dir); }
+void fsref_vf_drop(void* s, double* vf) { S->vf_drop(vf); }
 void fsref_sample(void* s, int mode, int n, const double* px, const double* py, double* a, double* b) {
   S->sample(mode, n, px, py, a, b);
 }

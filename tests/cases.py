@@ -32,6 +32,23 @@ def ellipse_vf(nx, ny, dx, dy, sharp=1.5):
     return np.clip(0.5 - d / (sharp * dx), 0.0, 1.0)
 
 
+def drop_vf_quadrature(nx, ny, dx, dy, npt=16):
+    """the initial volume fraction of test/StationaryDrop.cpp:47-52,209-212: npt-point Gauss quadrature per
+    direction (src/Quadrature.hpp:37-66) of the indicator of the ellipse (2 (x - 1/2))^2 + (y - 1/2)^2 <= 1/16 over
+    every cell incl. ghosts, divided by the cell area, then apply_neumann_bconds; ghost inclusive"""
+    xi, w = np.polynomial.legendre.leggauss(npt)
+    x = np.arange(-1, nx + 2) * dx
+    y = np.arange(-1, ny + 2) * dy
+    X = (x[1:] - x[:-1])[:, None] / 2.0 * xi[None, :] + (x[1:] + x[:-1])[:, None] / 2.0   # (nx + 2, npt)
+    Y = (y[1:] - y[:-1])[:, None] / 2.0 * xi[None, :] + (y[1:] + y[:-1])[:, None] / 2.0
+    inside = ((2.0 * (X[:, None, :, None] - 0.5)) ** 2 + (Y[None, :, None, :] - 0.5) ** 2 <= 0.25 ** 2)
+    integral = np.einsum("ijab,a,b->ij", inside.astype(np.float64), w, w)
+    vf = ((x[1:] - x[:-1])[:, None] / 2.0 * (y[1:] - y[:-1])[None, :] / 2.0 * integral) / (dx * dy)
+    vf[0, :], vf[-1, :] = vf[1, :], vf[-2, :]
+    vf[:, 0], vf[:, -1] = vf[:, 1], vf[:, -2]
+    return vf
+
+
 def cavity_bc():
     """scaling/LidDrivenFlow.cpp:33-41: no-slip walls, lid U = 1 on top."""
     return BConds(kind=(DIRICHLET,) * 4, u_val=(0.0, 0.0, 0.0, 1.0), v_val=(0.0,) * 4)

@@ -256,6 +256,19 @@ def sampling(name="sampling_random48x20"):
     print(name, u[:3], v[:3])
 
 
+def vf_drop(name="vf_drop64"):
+    """the initial volume fraction of test/StationaryDrop.cpp:47-52,209-212 (Gauss quadrature of the ellipse indicator)
+    from the unmodified reference on 64 x 64 and 48 x 20 cells of the unit-cell-size grids the tests use"""
+    out = {}
+    for nx, ny in ((64, 64), (48, 20)):
+        st = random_state(nx, ny, seed=1)   # only the grid matters: dx = 1 / nx, dy = 1 / ny
+        r = Ref(nx, ny)
+        r.load(st)
+        out[f"vf{nx}x{ny}"] = r.vf_drop()
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
+    print(name, {k: float(v[1:-1, 1:-1].mean()) for k, v in out.items()})
+
+
 def monitor_log(name="monitor_log.txt"):
     """src/Monitor.hpp and should_save (src/IO.hpp:97-108) of the unmodified reference on the rows / step sequence of
     tests/test_output_cpu.py"""
@@ -292,6 +305,9 @@ if __name__ == "__main__":
     if "channel215" in sys.argv:
         for nm in CHANNEL215:
             run_channel215(nm)
+        sys.exit(0)
+    if "vf" in sys.argv:
+        vf_drop()
         sys.exit(0)
     if "sampling" in sys.argv:
         sampling()
@@ -334,3 +350,4 @@ if __name__ == "__main__":
     operators_misc()
     monitor_log()
     sampling()
+    vf_drop()

@@ -404,6 +404,7 @@ class Ref:
             L.fsref_conserved.argtypes = [C.c_void_p, DP, DP, DP]
             L.fsref_flow_control.argtypes = [C.c_void_p, C.c_int, C.c_double, DP]
             L.fsref_to_npy.argtypes = [C.c_void_p, C.c_char_p]
+            L.fsref_vf_drop.argtypes = [C.c_void_p, DP]
             L.fsref_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, DP, DP, DP, DP]
             L.fsref_monitor_log.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_char_p),
                                             C.c_int, DP, C.POINTER(C.c_int64)]
@@ -554,6 +555,12 @@ class Ref:
         gx, gy = np.zeros_like(f), np.zeros_like(f)
         self.lib().fsref_grad_centered(self.h, _ptr(f), _ptr(gx), _ptr(gy))
         return gx, gy
+
+    def vf_drop(self):
+        """the initial volume fraction of test/StationaryDrop.cpp:47-52,209-212 on this session's grid"""
+        vf = np.zeros((self.nx + 2, self.ny + 2))
+        self.lib().fsref_vf_drop(self.h, _ptr(vf))
+        return vf
 
     def to_npy(self, directory):
         """to_npy(directory, fs), src/IO.hpp:231-269 -- REMOVES and re-creates `directory`"""
