@@ -367,3 +367,21 @@ def conserved_known_answer():
     W = np.outer(gw, gw) * 2.0
     expected = tuple(float((W * f).sum()) for f in (rho(QX, QY), rho(QX, QY) * np.sin(QX + QY), rho(QX, QY) * np.cos(QX + QY)))
     return st, expected, 10.0 * min(dx, dy) ** 2
+
+
+def twophase_quadrature_case(oracle, n=128):
+    """BASELINE configs[3] with the reference's own inputs: volume fraction by Gauss quadrature of the ellipse
+    indicator (test/StationaryDrop.cpp:47-52,209-212), rho 1 : 1000 and mu from calc_rho / calc_visc(vf, fs),
+    sigma = 1/20, curvature 1 / R of the circle R = 0.25 and interface length dx on the interface cells;
+    lid-driven boundary conditions; -> (state, bconds, (vf, curv, interface_length))"""
+    st = cavity_state(oracle, n, n, drop=True, seed=1)
+    vf = drop_vf_quadrature(n, n, st.dx, st.dy)
+    st.vf = vf
+    oracle.calc_rho_visc_vof(st, vf)
+    for k in ("rho_u", "rho_v"):
+        st.a[k + "_old"][:] = st.a[k]
+    st.sigma = 0.05
+    bc = cavity_bc()
+    oracle.apply_velocity_bconds(st, bc)
+    band = ((vf > 1e-8) & (vf < 1.0 - 1e-8)).astype(np.float64)
+    return st, bc, (vf, band * 4.0, band * st.dx)

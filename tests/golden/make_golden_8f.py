@@ -269,6 +269,29 @@ def vf_drop(name="vf_drop64"):
     print(name, {k: float(v[1:-1, 1:-1].mean()) for k, v in out.items()})
 
 
+def run_twophase_quadrature(name="run_twophase_q128", nsub=3, nsteps=2):
+    """two timesteps of the two-phase sub-iteration on the drop initialised as the reference's drivers do (Gauss
+    quadrature of the ellipse indicator: a sharp 1 : 1000 density jump)"""
+    from cases import twophase_quadrature_case
+    st, bc, cap = twophase_quadrature_case(o)
+    r = Ref(st.nx, st.ny)
+    r.load(st)
+    r.set_bconds(bc)
+    r.solver_create(1e-13, 500)
+    r.solver_set_operator()
+    dts, its = [], []
+    for _ in range(nsteps):
+        dt = r.adjust_dt(0.9, 0.1)
+        it, res = r.step(dt, nsub, rebuild=1, density=1, capillary=cap)
+        dts.append(dt)
+        its.append(it)
+    s2 = st.copy()
+    r.store(s2)
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), dts=np.array(dts), its=np.array(its), U=s2.U, V=s2.V,
+                        p=s2.a["p"], rho_u=s2.rho_u, pj_u=s2.p_jump_u)
+    print("run", name, "its", its, "dt", dts)
+
+
 def monitor_log(name="monitor_log.txt"):
     """src/Monitor.hpp and should_save (src/IO.hpp:97-108) of the unmodified reference on the rows / step sequence of
     tests/test_output_cpu.py"""
@@ -305,6 +328,9 @@ if __name__ == "__main__":
     if "channel215" in sys.argv:
         for nm in CHANNEL215:
             run_channel215(nm)
+        sys.exit(0)
+    if "twophase_q" in sys.argv:
+        run_twophase_quadrature()
         sys.exit(0)
     if "vf" in sys.argv:
         vf_drop()
@@ -351,3 +377,4 @@ if __name__ == "__main__":
     monitor_log()
     sampling()
     vf_drop()
+    run_twophase_quadrature()

@@ -472,3 +472,34 @@ def test_conserved_quantities_known_answer(F):
     got = fs.calc_conserved_quantities()
     assert np.abs(np.array(got) - np.array(expected)).max() <= tol
     fs.close()
+
+
+def test_twophase_quadrature_timesteps(F, oracle):
+    """BASELINE configs[3] with the reference drivers' own initialisation (volume fraction by Gauss quadrature of
+    the ellipse indicator: a sharp 1 : 1000 density jump), density update + capillary block + operator rebuild
+    through fsgpu_step, against the committed output of the unmodified reference"""
+    from cases import rel_inf, twophase_quadrature_case
+    g = np.load(os.path.join(GOLD, "run_twophase_q128.npz"))
+    st, bc, cap = twophase_quadrature_case(oracle)
+    fs = to_gpu(F, st, bc)
+    for n, a in zip(("VF", "CURV", "INTERFACE_LENGTH"), cap):
+        fs.upload(n, a)
+    # calc_rho / calc_visc(vf, fs) on the device reproduce the uploaded (oracle-made) densities
+    rho_u, visc = fs.download("RHO_U"), fs.download("VISC")
+    fs.calc_rho_visc_vof()
+    assert rel_inf(fs.download("RHO_U"), rho_u) <= 1e-12 and rel_inf(fs.download("VISC"), visc) <= 1e-12
+    ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
+    ps.set_pressure_operator()
+    flags = F.STEP_REBUILD_OPERATOR | F.STEP_DENSITY | F.STEP_CAPILLARY
+    for k, dt_ref in enumerate(g["dts"]):
+        assert fs.adjust_dt(0.9, 0.1) == pytest.approx(float(dt_ref), rel=1e-9)
+        res, it = fs.step(ps, float(dt_ref), 3, flags)
+        assert res < 1e-12 and abs(it - int(g["its"][k])) <= max(3, 0.35 * int(g["its"][k]))
+    U, V, p = fs.download("U"), fs.download("V"), fs.download("P")
+    ev = vel_err(U, V, g["U"], g["V"])
+    ep = rel_l2(p - p.mean(), g["p"] - g["p"].mean())
+    print(f"\n[twophase_q128] velocity rel L2 {ev:.3e}, pressure rel L2 {ep:.3e}")
+    assert ev <= 1e-10 and ep <= 1e-8
+    assert rel_inf(fs.download("RHO_U"), g["rho_u"]) <= 1e-12 and rel_inf(fs.download("P_JUMP_U"), g["pj_u"]) <= 1e-12
+    ps.close()
+    fs.close()
