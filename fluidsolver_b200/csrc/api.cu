@@ -391,6 +391,14 @@ static int reduce_impl(fsgpu_ctx* c, int field, int include_ghost, int op, doubl
   *out = c->h_red[0];
   return 0;
 }
+int fsgpu_field_max(fsgpu_ctx* c, int field, int include_ghost, double* out) {
+  return reduce_impl(c, field, include_ghost, 3, out);
+}
+int fsgpu_field_min(fsgpu_ctx* c, int field, int include_ghost, double* out) {
+  if (reduce_impl(c, field, include_ghost, 4, out)) return 1;
+  *out = -*out;
+  return 0;
+}
 int fsgpu_integrate(fsgpu_ctx* c, int field, int include_ghost, double* out) {
   return reduce_impl(c, field, include_ghost, 1, out);
 }

@@ -138,22 +138,25 @@ k_cfl(const double* __restrict__ U, const double* __restrict__ V, const double* 
   }
 }
 
-// max |f| (OP 0), sum f (OP 1) or sum |f| (OP 2) over rows [r0, r1) x columns [b0, b0 + nb)
-// (ghost-inclusive indices): abs_max, integrate, L1_norm (src/Utility.hpp:80-88, src/Operators.hpp:51-76)
+// max |f| (OP 0), sum f (OP 1), sum |f| (OP 2), max f (OP 3) or max -f (OP 4) over rows [r0, r1) x columns
+// [b0, b0 + nb) (ghost-inclusive indices): abs_max, integrate, L1_norm, max, min (src/Utility.hpp:80-115,
+// src/Operators.hpp:51-76)
 template <int OP>
 __global__ void __launch_bounds__(BX* BY)
 k_reduce_field(const double* __restrict__ f, int64_t r0, int64_t r1, int64_t b0, int64_t nb, const Geom g,
                double scale, double* part, unsigned int* ticket, double* out) {
-  double v[1] = {0.0};
+  double v[1] = {OP >= 3 ? ReduceMax::id() : 0.0};
   for_each_point(r0, r1, nb, [&](int64_t a, int64_t j) {
     const double x = f[g.idx(a, b0 + j)];
     if (OP == 0) v[0] = fmax(v[0], fabs(x));
+    else if (OP == 3) v[0] = fmax(v[0], x);
+    else if (OP == 4) v[0] = fmax(v[0], -x);
     else v[0] += OP == 2 ? fabs(x) : x;
   });
   double tot[1];
-  if (OP == 0) {
+  if (OP == 0 || OP >= 3) {
     if (grid_reduce<ReduceMax, 1>(v, part, ticket, tot)) {
-      if (threadIdx.x == 0 && threadIdx.y == 0) out[0] = fmax(tot[0], 0.0);
+      if (threadIdx.x == 0 && threadIdx.y == 0) out[0] = OP == 0 ? fmax(tot[0], 0.0) : tot[0];
     }
   } else {
     if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
@@ -296,7 +299,8 @@ int fs_launch_cfl(fsgpu_ctx* c) {
 
 // abs_max<INCLUDE_GHOST>(field), src/Utility.hpp:44-88: the reference's default reduces over the
 // INTERIOR of the field (for_each_i), abs_max<true> over the whole ghost-inclusive extent
-// op 0: abs_max -> red_out[0] (max over ranks); op 1 / 2: integrate / L1_norm (* dx * dy, sum over ranks)
+// op 0: abs_max -> red_out[0] (max over ranks); op 1 / 2: integrate / L1_norm (* dx * dy, sum over ranks);
+// op 3: max; op 4: -min
 int fs_launch_reduce_field(fsgpu_ctx* c, int field, bool include_ghost, int op) {
   const Geom& g = c->g;
   int64_t m2, n2;
@@ -314,10 +318,14 @@ int fs_launch_reduce_field(fsgpu_ctx* c, int field, bool include_ghost, int op) 
     k_reduce_field<0><<<nbl, blk, 0, c->stream>>>(c->f[field], r0, r1, lo, nb, g, 1.0, c->part, c->ticket, c->red_out);
   else if (op == 1)
     k_reduce_field<1><<<nbl, blk, 0, c->stream>>>(c->f[field], r0, r1, lo, nb, g, sc, c->part, c->ticket, c->red_out);
-  else
+  else if (op == 2)
     k_reduce_field<2><<<nbl, blk, 0, c->stream>>>(c->f[field], r0, r1, lo, nb, g, sc, c->part, c->ticket, c->red_out);
+  else if (op == 3)
+    k_reduce_field<3><<<nbl, blk, 0, c->stream>>>(c->f[field], r0, r1, lo, nb, g, 1.0, c->part, c->ticket, c->red_out);
+  else  // the minimum travels as max(-f); the caller negates
+    k_reduce_field<4><<<nbl, blk, 0, c->stream>>>(c->f[field], r0, r1, lo, nb, g, 1.0, c->part, c->ticket, c->red_out);
   FS_LAUNCHED();
-  return comm_allreduce(c, c->red_out, 1, op == 0 ? COMM_MAX : COMM_SUM);
+  return comm_allreduce(c, c->red_out, 1, (op == 1 || op == 2) ? COMM_SUM : COMM_MAX);
 }
 int fs_launch_absmax(fsgpu_ctx* c, int field, bool include_ghost) {
   return fs_launch_reduce_field(c, field, include_ghost, 0);

@@ -45,7 +45,7 @@ SYMBOLS = (
     "fsgpu_save_old_state", "fsgpu_save_old_velocity", "fsgpu_save_old_density",
     "fsgpu_calc_mid_time", "fsgpu_calc_dmomdt", "fsgpu_update_velocity", "fsgpu_momentum_update",
     "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_flow_control", "fsgpu_set_flow_control",
-    "fsgpu_integrate", "fsgpu_l1_norm", "fsgpu_calc_grad_of_centered_points",
+    "fsgpu_field_max", "fsgpu_field_min", "fsgpu_integrate", "fsgpu_l1_norm", "fsgpu_calc_grad_of_centered_points",
     "fsgpu_eval_flow_field_at", "fsgpu_bilinear_interpolate",
     "fsgpu_to_npy", "fsgpu_to_npy_state", "fsgpu_npy_write_host", "fsgpu_write_vtk", "fsgpu_calc_divergence",
     "fsgpu_shift_pressure_to_zero", "fsgpu_correct_velocity", "fsgpu_abs_max", "fsgpu_abs_max_all",
@@ -124,6 +124,8 @@ def load():
                                   C.POINTER(i32), C.POINTER(C.c_char_p)]
     L.fsgpu_abs_max.argtypes = [vp, i32, DP]
     L.fsgpu_integrate.argtypes = [vp, i32, i32, DP]
+    L.fsgpu_field_max.argtypes = [vp, i32, i32, DP]
+    L.fsgpu_field_min.argtypes = [vp, i32, i32, DP]
     L.fsgpu_l1_norm.argtypes = [vp, i32, i32, DP]
     L.fsgpu_calc_grad_of_centered_points.argtypes = [vp, i32, i32, i32]
     L.fsgpu_eval_flow_field_at.argtypes = [vp, DP, DP, i64, DP, DP, DP, DP]
@@ -391,6 +393,18 @@ class FS:
         o = C.c_double()
         fn = self.L.fsgpu_abs_max_all if include_ghost else self.L.fsgpu_abs_max
         _chk(fn(self.h, FIELD_ID[name], C.byref(o)))
+        return o.value
+
+    def max(self, name, include_ghost=False):
+        """max<INCLUDE_GHOST>(field), src/Utility.hpp:91-101"""
+        o = C.c_double()
+        _chk(self.L.fsgpu_field_max(self.h, FIELD_ID[name], int(include_ghost), C.byref(o)))
+        return o.value
+
+    def min(self, name, include_ghost=False):
+        """min<INCLUDE_GHOST>(field), src/Utility.hpp:103-115"""
+        o = C.c_double()
+        _chk(self.L.fsgpu_field_min(self.h, FIELD_ID[name], int(include_ghost), C.byref(o)))
         return o.value
 
     def integrate(self, name, include_ghost=False):

@@ -198,6 +198,9 @@ int fsgpu_correct_velocity(fsgpu_ctx* c, double dt);
  * abs_max<true>(field), the whole ghost-inclusive extent */
 int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out);
 int fsgpu_abs_max_all(fsgpu_ctx* c, int field, double* out);
+/* max<INCLUDE_GHOST>(field) and min<INCLUDE_GHOST>(field), src/Utility.hpp:91-115 */
+int fsgpu_field_max(fsgpu_ctx* c, int field, int include_ghost, double* out);
+int fsgpu_field_min(fsgpu_ctx* c, int field, int include_ghost, double* out);
 /* integrate<INCLUDE_GHOST>(dx, dy, field) and L1_norm<INCLUDE_GHOST>(dx, dy, field), src/Operators.hpp:51-76:
  * (sum of the entries, or of their magnitudes) * dx * dy over the interior or the whole extent */
 int fsgpu_integrate(fsgpu_ctx* c, int field, int include_ghost, double* out);

@@ -503,3 +503,30 @@ def test_twophase_quadrature_timesteps(F, oracle):
     assert rel_inf(fs.download("RHO_U"), g["rho_u"]) <= 1e-12 and rel_inf(fs.download("P_JUMP_U"), g["pj_u"]) <= 1e-12
     ps.close()
     fs.close()
+
+
+def test_min_max_known_answer_and_slabs(F):
+    """min / max / abs_max with and without ghosts: the reference's own test (test/Utility.cpp:89-136: ghosts -100,
+    interior rows i even ? i : -i on 10 x 10, here with the path's single ghost layer), random fields against numpy,
+    and 3 slab contexts against one"""
+    from test_gpu_slab import run_ranks, run_single
+    from cases import cavity_bc, random_state
+    fs = F.FS(10, 10, 0.1, 0.1)
+    a = np.full((12, 12), -100.0)
+    a[1:-1, 1:-1] = np.array([i if i % 2 == 0 else -i for i in range(10)], dtype=np.float64)[:, None]
+    fs.upload("P", a)
+    assert (fs.min("P"), fs.min("P", True)) == (-9.0, -100.0)
+    assert (fs.max("P"), fs.max("P", True)) == (8.0, 8.0)
+    assert (fs.abs_max("P"), fs.abs_max("P", True)) == (9.0, 100.0)
+    fs.close()
+    st = random_state(50, 23, seed=9)
+
+    def body(fs, r):
+        return [f(n, gh) for n in ("U", "V", "P") for gh in (False, True) for f in (fs.min, fs.max)]
+
+    _, ra = run_ranks(F, st, cavity_bc(), 3, body, fields=("U",))
+    _, rb = run_single(F, st, cavity_bc(), body, fields=("U",))
+    assert all(x == ra[0] for x in ra) and ra[0] == rb
+    want = [f(arr if gh else arr[1:-1, 1:-1]) for arr in (st.U, st.V, st.a["p"]) for gh in (False, True)
+            for f in (np.min, np.max)]
+    assert rb == want
