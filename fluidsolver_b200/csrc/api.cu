@@ -391,6 +391,15 @@ static int reduce_impl(fsgpu_ctx* c, int field, int include_ghost, int op, doubl
   *out = c->h_red[0];
   return 0;
 }
+int fsgpu_count_nonfinite(fsgpu_ctx* c, int field, int64_t* n_nan, int64_t* n_inf) {
+  FS_CHECK_CTX(c);
+  FS_CHECK_FIELD(field);
+  if (fs_launch_count_nonfinite(c, field)) return 1;
+  if (read_red(c, 0, 2)) return 1;
+  if (n_nan) *n_nan = (int64_t)c->h_red[0];
+  if (n_inf) *n_inf = (int64_t)c->h_red[1];
+  return 0;
+}
 int fsgpu_field_max(fsgpu_ctx* c, int field, int include_ghost, double* out) {
   return reduce_impl(c, field, include_ghost, 3, out);
 }

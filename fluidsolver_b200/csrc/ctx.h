@@ -106,6 +106,7 @@ int fs_launch_shift_pressure(fsgpu_ctx* c);
 int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift);
 int fs_launch_cfl(fsgpu_ctx* c);               // 4 maxima -> red_out[0..3]
 int fs_launch_absmax(fsgpu_ctx* c, int field, bool include_ghost);  // -> red_out[0]
+int fs_launch_count_nonfinite(fsgpu_ctx* c, int field);  // -> red_out[0] NaNs, red_out[1] Infs
 int fs_launch_reduce_field(fsgpu_ctx* c, int field, bool include_ghost, int op);  // 0 max|f|, 1 sum, 2 sum|f| (* dx dy)
 int fs_launch_fill(fsgpu_ctx* c, int field, double v);
 int fs_launch_rho_visc_vof(fsgpu_ctx* c);

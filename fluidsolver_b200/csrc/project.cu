@@ -165,6 +165,22 @@ k_reduce_field(const double* __restrict__ f, int64_t r0, int64_t r1, int64_t b0,
   }
 }
 
+// has_nan / has_inf (src/Container.hpp:191-204) over the whole ghost-inclusive extent: counts of both in one pass
+__global__ void __launch_bounds__(BX* BY)
+k_count_nonfinite(const double* __restrict__ f, int64_t r0, int64_t r1, int64_t nb, const Geom g, double* part,
+                  unsigned int* ticket, double* out) {
+  double v[2] = {0.0, 0.0};
+  for_each_point(r0, r1, nb, [&](int64_t a, int64_t j) {
+    const double x = f[g.idx(a, j)];
+    if (isnan(x)) v[0] += 1.0;
+    else if (isinf(x)) v[1] += 1.0;
+  });
+  double tot[2];
+  if (grid_reduce<ReduceSum, 2>(v, part, ticket, tot)) {
+    if (threadIdx.x == 0 && threadIdx.y == 0) { out[0] = tot[0]; out[1] = tot[1]; }
+  }
+}
+
 // fill the (m+2) x (n+2) ghost-inclusive extent of a field
 // (rows [r0, r1): the owned rows and the halo rows inside the field's extent)
 __global__ void k_fill(double* __restrict__ f, int64_t r0, int64_t r1, int64_t n2, double v, const Geom g) {
@@ -326,6 +342,17 @@ int fs_launch_reduce_field(fsgpu_ctx* c, int field, bool include_ghost, int op) 
     k_reduce_field<4><<<nbl, blk, 0, c->stream>>>(c->f[field], r0, r1, lo, nb, g, 1.0, c->part, c->ticket, c->red_out);
   FS_LAUNCHED();
   return comm_allreduce(c, c->red_out, 1, (op == 1 || op == 2) ? COMM_SUM : COMM_MAX);
+}
+int fs_launch_count_nonfinite(fsgpu_ctx* c, int field) {  // -> red_out[0] NaN count, red_out[1] Inf count
+  const Geom& g = c->g;
+  int64_t m2, n2;
+  field_extent(g, field, &m2, &n2);
+  const int64_t r0 = g.a_lo, r1 = g.last() ? m2 : g.a_hi;
+  const unsigned nbl = persist_blocks(r1 - r0, n2);
+  if (fs_ensure_part(c, (size_t)nbl * 4)) return 1;
+  k_count_nonfinite<<<nbl, dim3(BX, BY), 0, c->stream>>>(c->f[field], r0, r1, n2, g, c->part, c->ticket, c->red_out);
+  FS_LAUNCHED();
+  return comm_allreduce(c, c->red_out, 2, COMM_SUM);
 }
 int fs_launch_absmax(fsgpu_ctx* c, int field, bool include_ghost) {
   return fs_launch_reduce_field(c, field, include_ghost, 0);

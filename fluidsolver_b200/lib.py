@@ -45,7 +45,7 @@ SYMBOLS = (
     "fsgpu_save_old_state", "fsgpu_save_old_velocity", "fsgpu_save_old_density",
     "fsgpu_calc_mid_time", "fsgpu_calc_dmomdt", "fsgpu_update_velocity", "fsgpu_momentum_update",
     "fsgpu_apply_velocity_bconds", "fsgpu_outflow_fix", "fsgpu_flow_control", "fsgpu_set_flow_control",
-    "fsgpu_field_max", "fsgpu_field_min", "fsgpu_integrate", "fsgpu_l1_norm", "fsgpu_calc_grad_of_centered_points",
+    "fsgpu_field_max", "fsgpu_field_min", "fsgpu_count_nonfinite", "fsgpu_integrate", "fsgpu_l1_norm", "fsgpu_calc_grad_of_centered_points",
     "fsgpu_eval_flow_field_at", "fsgpu_bilinear_interpolate",
     "fsgpu_to_npy", "fsgpu_to_npy_state", "fsgpu_npy_write_host", "fsgpu_write_vtk", "fsgpu_calc_divergence",
     "fsgpu_shift_pressure_to_zero", "fsgpu_correct_velocity", "fsgpu_abs_max", "fsgpu_abs_max_all",
@@ -125,6 +125,7 @@ def load():
     L.fsgpu_abs_max.argtypes = [vp, i32, DP]
     L.fsgpu_integrate.argtypes = [vp, i32, i32, DP]
     L.fsgpu_field_max.argtypes = [vp, i32, i32, DP]
+    L.fsgpu_count_nonfinite.argtypes = [vp, i32, C.POINTER(i64), C.POINTER(i64)]
     L.fsgpu_field_min.argtypes = [vp, i32, i32, DP]
     L.fsgpu_l1_norm.argtypes = [vp, i32, i32, DP]
     L.fsgpu_calc_grad_of_centered_points.argtypes = [vp, i32, i32, i32]
@@ -394,6 +395,12 @@ class FS:
         fn = self.L.fsgpu_abs_max_all if include_ghost else self.L.fsgpu_abs_max
         _chk(fn(self.h, FIELD_ID[name], C.byref(o)))
         return o.value
+
+    def count_nonfinite(self, name):
+        """(number of NaN, number of +-Inf) entries of the ghost-inclusive array: has_nan / has_inf, src/Container.hpp:191-204"""
+        a, b = C.c_int64(), C.c_int64()
+        _chk(self.L.fsgpu_count_nonfinite(self.h, FIELD_ID[name], C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def max(self, name, include_ghost=False):
         """max<INCLUDE_GHOST>(field), src/Utility.hpp:91-101"""

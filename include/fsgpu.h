@@ -198,6 +198,9 @@ int fsgpu_correct_velocity(fsgpu_ctx* c, double dt);
  * abs_max<true>(field), the whole ghost-inclusive extent */
 int fsgpu_abs_max(fsgpu_ctx* c, int field, double* out);
 int fsgpu_abs_max_all(fsgpu_ctx* c, int field, double* out);
+/* has_nan(field) / has_inf(field) / has_nan_or_inf(field), src/Container.hpp:191-204 (the NaN scans the drivers run
+ * on delta_p and the momentum increments): number of NaN and of +-Inf entries of the whole ghost-inclusive array */
+int fsgpu_count_nonfinite(fsgpu_ctx* c, int field, int64_t* n_nan, int64_t* n_inf);
 /* max<INCLUDE_GHOST>(field) and min<INCLUDE_GHOST>(field), src/Utility.hpp:91-115 */
 int fsgpu_field_max(fsgpu_ctx* c, int field, int include_ghost, double* out);
 int fsgpu_field_min(fsgpu_ctx* c, int field, int include_ghost, double* out);

@@ -80,6 +80,11 @@ class Field2D {
   const Float* get_data() const { return m_data.data(); }
   static constexpr Index extent(Index d) { return d == 0 ? M : N; }
   static constexpr Index size() { return (M + 2 * NGHOST) * (N + 2 * NGHOST); }
+  static constexpr Index n_ghost() { return NGHOST; }
+  static constexpr bool is_valid_interior_index(Index i, Index j) { return i >= 0 && i < M && j >= 0 && j < N; }
+  static constexpr bool is_valid_index(Index i, Index j) {
+    return i >= -NGHOST && i < M + NGHOST && j >= -NGHOST && j < N + NGHOST;
+  }
   // device binding
   void bind(fsgpu_ctx* ctx, int field) { m_ctx = ctx; m_field = field; }
   bool bound() const { return m_ctx != nullptr; }
@@ -499,6 +504,33 @@ void correct_outflow(FS<Float, NX, NY, NGHOST>& fs, bool dy_weighted, Float& inf
 template <typename Float, Index NX, Index NY, Index NGHOST>
 void force_total_flow(FS<Float, NX, NY, NGHOST>& fs, Float total_flow, Float& inflow, Float& outflow) {
   FSGPU_CHECK(fsgpu_flow_control(fs.ctx, FSGPU_FLOW_FORCE_TOTAL, total_flow, &inflow, &outflow));
+}
+
+// has_nan / has_inf / has_nan_or_inf, src/Container.hpp:191-204, on a device-bound field (one reduction pass,
+// no copy to the host)
+namespace fsgpu_shim {
+template <class F>
+void count_nonfinite(const F& f, std::int64_t& n_nan, std::int64_t& n_inf) {
+  FSGPU_CHECK(fsgpu_count_nonfinite(ctx_of(f), f.field_id(), &n_nan, &n_inf));
+}
+}  // namespace fsgpu_shim
+template <typename Float, Index M, Index N, Index NGHOST>
+bool has_nan(const Field2D<Float, M, N, NGHOST>& f) {
+  std::int64_t a = 0, b = 0;
+  fsgpu_shim::count_nonfinite(f, a, b);
+  return a > 0;
+}
+template <typename Float, Index M, Index N, Index NGHOST>
+bool has_inf(const Field2D<Float, M, N, NGHOST>& f) {
+  std::int64_t a = 0, b = 0;
+  fsgpu_shim::count_nonfinite(f, a, b);
+  return b > 0;
+}
+template <typename Float, Index M, Index N, Index NGHOST>
+bool has_nan_or_inf(const Field2D<Float, M, N, NGHOST>& f) {
+  std::int64_t a = 0, b = 0;
+  fsgpu_shim::count_nonfinite(f, a, b);
+  return a + b > 0;
 }
 
 // integrate / L1_norm (src/Operators.hpp:51-76) and calc_grad_of_centered_points (:164-201) on device-bound

@@ -77,7 +77,7 @@ int main(int argc, char**) {
   data_writer.add_vector("velocity", &Ui, &Vi);
   const bool wrote = to_npy("/tmp/fsgpu_shim_check", fs) && data_writer.write(0.0) &&
                      to_npy("/tmp/fsgpu_shim_check/ym.npy", fs.ym) && to_npy("/tmp/fsgpu_shim_check/div.npy", div);
-  if (!wrote) return 2;
+  if (!wrote || has_nan_or_inf(delta_p) || has_nan(fs.curr.U) || has_inf(div) || !div.is_valid_index(-1, NY)) return 2;
   fill(fs.p, 0.0);
   fs.to_host();
   return m == m ? 0 : 1;

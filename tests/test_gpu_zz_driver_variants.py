@@ -530,3 +530,21 @@ def test_min_max_known_answer_and_slabs(F):
     want = [f(arr if gh else arr[1:-1, 1:-1]) for arr in (st.U, st.V, st.a["p"]) for gh in (False, True)
             for f in (np.min, np.max)]
     assert rb == want
+
+
+def test_count_nonfinite(F):
+    """has_nan / has_inf / has_nan_or_inf (src/Container.hpp:191-204) as one device pass over the ghost-inclusive array"""
+    from cases import random_state
+    st = random_state(50, 23, seed=4)
+    fs = to_gpu(F, st)
+    assert fs.count_nonfinite("U") == (0, 0) and fs.count_nonfinite("DELTA_P") == (0, 0)
+    a = st.U.copy()
+    a[0, 0] = np.nan            # a ghost corner counts: the reference scans the whole array
+    a[17, 5] = np.nan
+    a[-1, -1] = np.inf
+    a[3, 3] = -np.inf
+    a[4, 4] = np.inf
+    fs.upload("U", a)
+    assert fs.count_nonfinite("U") == (2, 3)
+    assert fs.count_nonfinite("V") == (0, 0)
+    fs.close()
