@@ -385,3 +385,21 @@ def twophase_quadrature_case(oracle, n=128):
     oracle.apply_velocity_bconds(st, bc)
     band = ((vf > 1e-8) & (vf < 1.0 - 1e-8)).astype(np.float64)
     return st, bc, (vf, band * 4.0, band * st.dx)
+
+
+def channel215_measures(periodic, p, U, V, nx=215, ny=43, dx=5.0 / 215, visc=1e-3):
+    """the end-of-run measures of test/PeriodicChannel.cpp:264-337 (periodic) and test/CustomDirichletChannel.cpp:
+    252-331: (max deviation of p along y, max deviation of dp/dx from its reference, worst trapezoid L1 error of the
+    U profile over all stations x_i, max |V| on the interior faces)"""
+    P = p[1:, 1:]
+    ym = (np.arange(-1, ny + 1) + 0.5) / ny
+    dev_p = float(np.abs(P[:nx, :ny] - P[:nx, :1]).max())
+    dpdx = (P[1:nx, ny // 2] - P[0:nx - 1, ny // 2]) / dx
+    dpdx_ref = (P[nx // 2 + 1, ny // 2] - P[nx // 2, ny // 2]) / dx if periodic else -12.0 * visc
+    dev_dpdx = float(np.abs(dpdx - dpdx_ref).max())
+    l1 = 0.0
+    for i in range(nx + 1):
+        g = (p[i + 1, :] - p[i, :]) / dx if periodic else dpdx_ref
+        d = np.abs(U[i + 1, :] - g / (2 * visc) * (ym * ym - ym))
+        l1 = max(l1, float(np.sum((ym[1:] - ym[:-1]) * 0.5 * (d[1:] + d[:-1]))))
+    return dev_p, dev_dpdx, l1, float(np.abs(V[1:nx + 1, 1:ny + 2]).max())

@@ -548,3 +548,34 @@ def test_count_nonfinite(F):
     assert fs.count_nonfinite("U") == (2, 3)
     assert fs.count_nonfinite("V") == (0, 0)
     fs.close()
+
+
+def test_custom_dirichlet_channel_reference_criteria(F, oracle):
+    """the reference's own test/CustomDirichletChannel.cpp on the GPU at the driver's settings (tol 1e-6, 50
+    iterations, NUM_SUBITER 2, CFL 0.9, T_END = 60), judged by the driver's criteria (:240-331): outflow = inflow
+    within 1e-8 once t > 10, pressure constant along y and dp/dx = -12 mu within 1e-4, U profile within 2e-3 (L1) of
+    the Poiseuille profile at every station, |V| <= 3e-4"""
+    from cases import channel215_cases, channel215_measures, channel215_state, run_channel_study
+    bc, mode, total, _ = channel215_cases()["customdirichlet215x43"]
+    st = channel215_state(oracle)
+    oracle.apply_velocity_bconds(st, bc)
+    fs = to_gpu(F, st, bc)
+    fs.set_flow_control(mode, total)
+    ps = F.LinearSolver(fs, tol=1e-6, max_iter=50)
+    ps.set_pressure_operator()
+    t, worst = [0.0], [0.0]
+
+    def step(dt):
+        fs.step(ps, dt, 2, F.STEP_OUTFLOW_FIX)
+        t[0] += dt
+        if t[0] > 10.0:   # rho U dy summed over the two ghost columns (CustomDirichletChannel.cpp:61-72)
+            flux = 0.5 * fs.download("U")[[0, -1], :].sum(axis=1) * st.dy
+            worst[0] = max(worst[0], abs(flux[1] - flux[0]))
+
+    steps = run_channel_study(lambda: fs.adjust_dt(0.9, 0.1), step, t_end=60.0)
+    dev_p, dev_dpdx, l1, vmax = channel215_measures(False, fs.download("P"), fs.download("U"), fs.download("V"))
+    print(f"\n[customdirichlet215x43, {steps} steps] p dev {dev_p:.2e}, dpdx dev {dev_dpdx:.2e}, U L1 {l1:.3e}, "
+          f"max|V| {vmax:.3e}, worst flux mismatch {worst[0]:.2e}")
+    assert dev_p <= 1e-4 and dev_dpdx <= 1e-4 and l1 <= 2e-3 and vmax <= 3e-4 and worst[0] <= 1e-8
+    ps.close()
+    fs.close()
