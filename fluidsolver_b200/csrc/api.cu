@@ -441,7 +441,6 @@ static int sample_impl(fsgpu_ctx* c, int mode, int fa, int fb, const double* x, 
   int64_t m2, n2;
   field_extent(c->g, fa, &m2, &n2);
   if (m2 != c->g.nx + 2 || n2 != c->g.ny + 2) { fs_set_error("point sampling: field %d is not a cell field", fa); return 1; }
-  if (c->nranks > 1) { fs_set_error("point sampling works on a single context (points may lie in any slab)"); return 1; }
   if (n < 0 || !x || !y || (n > 0 && (!px || !py || !oa || (mode == 0 && !ob)))) {
     fs_set_error("point sampling: bad arguments");
     return 1;

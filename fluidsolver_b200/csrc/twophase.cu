@@ -302,6 +302,11 @@ k_sample(const SampleArgs s, const Geom g) {
   int64_t ip, in, jp, jn;
   sample_indices<MODE>(x, s.xm, g.nx, dx, ip, in);
   sample_indices<MODE>(y, s.ym, g.ny, dy, jp, jn);
+  if (ip + 1 < g.a_lo || ip + 1 >= g.a_hi) {  // another slab owns the point's row: it contributes, the sum combines
+    s.oa[k] = 0.0;
+    if (MODE == 0) s.ob[k] = 0.0;
+    return;
+  }
   const int64_t k00 = g.idx(ip + 1, jp + 1), k10 = g.idx(in + 1, jp + 1), k01 = g.idx(ip + 1, jn + 1),
                 k11 = g.idx(in + 1, jn + 1);
   const double tx = x - s.xm[ip + 1], ty = y - s.ym[jp + 1];
@@ -477,6 +482,10 @@ int fs_sample_points(fsgpu_ctx* c, int mode, int fa, int fb, const double* xm, c
   std::vector<double> h((size_t)(nx + ny + 4));
   std::copy(xm, xm + nx + 2, h.begin());
   std::copy(ym, ym + ny + 2, h.begin() + (nx + 2));
+  {  // row ip + 2 may be the first halo row of this slab
+    const int fl[2] = {fa, fb};
+    if (fs_exchange_fields(c, fl, mode == 0 ? 2 : 1, 1)) return 1;
+  }
   double* d = nullptr;
   const size_t nc = (size_t)(nx + ny + 4), np = (size_t)npts;
   FS_CUDA(cudaMalloc(&d, (nc + 4 * np) * sizeof(double)));
@@ -491,6 +500,7 @@ int fs_sample_points(fsgpu_ctx* c, int mode, int fa, int fb, const double* xm, c
     else k_sample<1><<<nb, 256, 0, c->stream>>>(s, c->g);
     ++g_launches;
     rc = cudaPeekAtLastError() != cudaSuccess ||
+         comm_allreduce(c, d + nc + 2 * np, (int64_t)(mode == 0 ? 2 * np : np), COMM_SUM) != 0 ||
          cudaMemcpyAsync(oa, d + nc + 2 * np, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
          (mode == 0 && cudaMemcpyAsync(ob, d + nc + 3 * np, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess);
   }

@@ -214,7 +214,8 @@ int fsgpu_calc_grad_of_centered_points(fsgpu_ctx* c, int f, int dfdx, int dfdy);
 /* eval_flow_field_at(xm, ym, Ui, Vi, x, y), src/Operators.hpp:118-161, at n points (px[k], py[k]) on FSGPU_UI /
  * FSGPU_VI as they are (fsgpu_interpolate_cell_centres fills them), and bilinear_interpolate(xm, ym, field, x, y),
  * :85-115, on any cell field.  xm, ym: fs.xm / fs.ym incl. ghosts (NX + 2 and NY + 2 doubles, fs.xm.get_data());
- * all arrays are host arrays; single context only. */
+ * all arrays are host arrays.  With slab contexts the call is collective with the same points on every rank: the
+ * slab owning a point's row evaluates it and the results are summed over the ranks. */
 int fsgpu_eval_flow_field_at(fsgpu_ctx* c, const double* xm, const double* ym, int64_t n, const double* px,
                              const double* py, double* u, double* v);
 int fsgpu_bilinear_interpolate(fsgpu_ctx* c, int field, const double* xm, const double* ym, int64_t n,

@@ -579,3 +579,24 @@ def test_custom_dirichlet_channel_reference_criteria(F, oracle):
     assert dev_p <= 1e-4 and dev_dpdx <= 1e-4 and l1 <= 2e-3 and vmax <= 3e-4 and worst[0] <= 1e-8
     ps.close()
     fs.close()
+
+
+def test_point_sampling_slabs(F, oracle):
+    """eval_flow_field_at / bilinear_interpolate on 3 slab contexts: the slab owning a point's row evaluates it,
+    the results are summed over the ranks; identical to one context"""
+    from test_gpu_slab import run_ranks, run_single
+    from cases import cavity_bc, grid_coords, random_state, sample_points
+    st = random_state(50, 23, seed=5)
+    px, py = sample_points(st)
+    x, y = grid_coords(st)
+
+    def body(fs, r):
+        fs.interpolate_cell_centres()
+        u, v = fs.eval_flow_field_at(x, y, px, py)
+        return [u, v, fs.bilinear_interpolate("P", x, y, px, py)]
+
+    _, ra = run_ranks(F, st, cavity_bc(), 3, body, fields=("U",))
+    _, rb = run_single(F, st, cavity_bc(), body, fields=("U",))
+    for q in range(3):
+        assert all(np.array_equal(r[q], ra[0][q]) for r in ra)
+        assert np.array_equal(ra[0][q], rb[q])
