@@ -1,13 +1,17 @@
-"""Further reference drivers as parity configs.  Added after the round's
-GPU budget was spent, so this file sorts last: a surprise here cannot hide the other GPU tests
-behind `pytest -x`.
+"""GPU parity of everything added after round 1's GPU budget was spent (SURVEY.md section 8f rows 2 and 3 and the
+reference's own unit / integration tests).  The file sorts last on purpose: a surprise here cannot hide the
+hardware-verified GPU tests behind `pytest -x`.
 
-* test/Couette.cpp: 210 x 21, Neumann left / right, lid on top, T = 10 -> U(y) within 1e-5 (trapezoid
-  L1 at three stations, :226-255) of the linear profile, inflow = outflow.  The flow stays
-  x-independent, so every pressure rhs is exactly zero and each of the 2 x 2178 solves takes HYPRE's
-  zero-rhs exit (pcg.c:473-488) -- on the GPU the PCG_ZERO_RHS path without a single iteration.
-* the same boundary conditions on a seeded velocity field: three timesteps against the oracle and
-  against the committed output of the unmodified reference (tests/golden/run_couette210x21.npz).
+* test/Couette.cpp: analytic criterion at T = 10 (every pressure rhs exactly zero -> HYPRE's zero-rhs exit,
+  pcg.c:473-488; here the PCG_ZERO_RHS path) and seeded timesteps against the reference golden
+* function-pointer Dirichlet sides, PSDirichlet solves, the misc golden (sigma CFL, monitor maxima, shift, rho / mu)
+* test/PeriodicChannel.cpp, test/CustomDirichletChannel.cpp, scaling/Channel.cpp: flux corrections, timesteps against
+  reference goldens, slab variants, the convergence study, the drivers' own pass criteria at T = 60 (Python and the
+  C++ shim example)
+* file output from the device buffers: .npy / VTK bytes against files written by the reference, other sizes, slabs
+* integrate / L1_norm / min / max / NaN scan / gradients / point sampling: reference goldens, the reference's
+  known-answer tests (test/Operators.cpp, test/Utility.cpp), slab variants
+* two-phase timesteps on the drop initialised by quadrature as the reference's drivers do
 """
 import os
 
