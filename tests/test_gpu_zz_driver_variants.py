@@ -155,73 +155,6 @@ def _channel215(oracle, name):
     return st, bc, mode, total
 
 
-@pytest.mark.parametrize("name", CHANNEL215)
-def test_channel215_drivers_vs_reference_golden(F, oracle, name):
-    """test/PeriodicChannel.cpp (total-flow forcing of both ghost columns), test/CustomDirichletChannel.cpp
-    (function inlet, dy-weighted outflow correction) and scaling/Channel.cpp (clipped Neumann outlet with
-    backflow): fsgpu_flow_control alone, then timesteps through fsgpu_step with
-    fsgpu_set_flow_control, against the committed output of the unmodified reference"""
-    from cases import rel_inf
-    g = np.load(os.path.join(GOLD, f"run_{name}.npz"))
-    st, bc, mode, total = _channel215(oracle, name)
-    fs = to_gpu(F, st, bc)
-    io = fs.flow_control(mode, total)
-    assert np.allclose(io, g["flow_io"], rtol=1e-13, atol=0)
-    assert rel_inf(fs.download("U"), g["flow_U"]) <= 1e-12
-    if mode == F.FLOW_FORCE_TOTAL:
-        assert np.allclose(fs.flow_control(mode, total), total, rtol=1e-12)
-    fs.upload("U", st.U)
-    fs.set_flow_control(mode, total)
-    ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
-    ps.set_pressure_operator()
-    worst = 0.0
-    for k, dt_ref in enumerate(g["dts"]):
-        assert fs.adjust_dt(0.9, 0.1) == pytest.approx(float(dt_ref), rel=1e-9)
-        res, it = fs.step(ps, float(dt_ref), 2, F.STEP_OUTFLOW_FIX)
-        worst = max(worst, res)
-        assert res < 1e-6
-        if res < 1e-12:
-            assert abs(it - int(g["its"][k])) <= max(3, 0.35 * int(g["its"][k]))
-    U, V, p = fs.download("U"), fs.download("V"), fs.download("P")
-    ev = vel_err(U, V, g["U"], g["V"])
-    ep = rel_l2(p - p.mean(), g["p"] - g["p"].mean())
-    print(f"\n[{name}] velocity rel L2 {ev:.3e}, pressure rel L2 {ep:.3e}, worst residual {worst:.2e}")
-    # the reference reaches 1e-13 in every solve of these runs; should the PCG here leave one at its
-    # breakdown floor instead (as HYPRE itself does on the TGV / channel systems, tests/test_gpu_solver.py),
-    # the fields agree to that floor
-    floor = worst >= 1e-12
-    assert ev <= (1e-7 if floor else 1e-10) and ep <= (1e-5 if floor else 1e-8)
-    ps.close()
-    fs.close()
-
-
-@pytest.mark.parametrize("name", CHANNEL215[:2])
-def test_channel215_drivers_slabs(F, oracle, name):
-    """the same drivers on 3 slab contexts (in-process transport) vs one context: the inlet sum lives
-    on the first slab, the outlet sum on the last, the periodic wrap-around between the two"""
-    from test_gpu_slab import run_ranks, run_single
-    st, bc, mode, total = _channel215(oracle, name)
-
-    def body(fs, r):
-        fs.set_flow_control(mode, total)
-        ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
-        ps.set_pressure_operator()
-        hist = [fs.flow_control(mode, total)]
-        for _ in range(2):
-            dt = fs.adjust_dt(0.9, 0.1)
-            fs.step(ps, dt, 2, F.STEP_OUTFLOW_FIX)
-            hist.append(dt)
-        ps.close()
-        return hist
-
-    a, ra = run_ranks(F, st, bc, 3, body, fields=("U", "V", "P"))
-    b, rb = run_single(F, st, bc, body, fields=("U", "V", "P"))
-    assert all(x == ra[0] for x in ra)
-    assert np.allclose(ra[0][0], rb[0], rtol=1e-13) and ra[0][1:] == pytest.approx(rb[1:], rel=1e-9)
-    # channel systems: same bound as tests/test_gpu_slab.py::test_slab_timesteps (PCG breakdown floor)
-    assert vel_err(a["U"], a["V"], b["U"], b["V"]) <= 1e-7
-
-
 # ---- file output from the device buffers (SURVEY.md section 8f row 3) ------------------------------
 def _io_case():
     from cases import grid_coords, random_state
@@ -309,36 +242,6 @@ def test_output_files_from_slabs(F, oracle, tmp_path):
         assert (tmp_path / "slabs" / f).read_bytes() == (tmp_path / "one" / f).read_bytes(), f
 
 
-def test_channel_convergence_study(F, oracle):
-    """scaling/Channel.cpp (non-periodic) on the GPU at the driver's own settings, T_END = 20, n = 3, 4, 5:
-    the error measures of :253-300 against the unmodified reference's (tests/golden/channel_study.npz) and
-    the second-order trend of the profile error.  The reference solves to tol 1e-6, so two implementations
-    agree to about that in the fields."""
-    from cases import channel_study_case, channel_study_errors, run_channel_study
-    g = np.load(os.path.join(GOLD, "channel_study.npz"))
-    ue = []
-    for k, n in enumerate(g["n"]):
-        st, bc = channel_study_case(oracle, int(n))
-        fs = to_gpu(F, st, bc)
-        fs.set_flow_control(F.FLOW_OUTFLOW_FIX_DY)
-        ps = F.LinearSolver(fs, tol=1e-6, max_iter=50)
-        ps.set_pressure_operator()
-        steps = run_channel_study(lambda: fs.adjust_dt(0.9, 0.1), lambda dt: fs.step(ps, dt, 2, F.STEP_OUTFLOW_FIX))
-        e = np.array(channel_study_errors(fs.download("P"), fs.download("U"), fs.download("V"), st.nx, st.ny, st.dx))
-        print(f"\n[channel study n={n}] steps {steps} (reference {int(g['errors'][k][4])}), errors {e}, "
-              f"reference {g['errors'][k][:4]}")
-        assert abs(steps - int(g["errors"][k][4])) <= 1
-        # the profile error is a discretisation error (2 %); the pressure / dpdx / V measures are at the level the
-        # 1e-6 solves leave behind and move with the iteration at which a solve stops (20 %)
-        assert np.all(np.abs(e / g["errors"][k][:4] - 1.0) <= np.array([0.2, 0.2, 0.02, 0.2])), (n, e)
-        if k == 0:
-            assert np.abs(fs.download("U") - g["U_n3"]).max() <= 1e-5
-        ue.append(e[2])
-        ps.close()
-        fs.close()
-    assert ue[0] / ue[1] > 3.0 and ue[1] / ue[2] > 3.0
-
-
 # ---- integrate / L1_norm / calc_grad_of_centered_points (src/Operators.hpp:51-76,164-201) ----------
 def test_integrate_l1_grad_vs_reference_golden(F, oracle):
     from cases import random_state, rel_inf
@@ -406,31 +309,6 @@ def test_integrate_grad_slabs(F, oracle):
     assert ra[0] == pytest.approx(rb, rel=1e-12)
     assert rb[1] == pytest.approx(oracle.integrate(st.vf, st.dx, st.dy, True), rel=1e-12)
     compare(a, b, names, tol=1e-13)
-
-
-def test_cpp_periodic_channel_driver(tmp_path):
-    """examples/periodic_channel.cpp: the reference's test/PeriodicChannel.cpp on the C++ shim, run to its own
-    T_END = 60 with the reference's own pass criteria (:264-337) as the exit code; the VTK frames it writes
-    are legacy-VTK files of the expected size"""
-    import subprocess
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    exe = os.path.join(root, "examples", "periodic_channel")
-    if not os.path.exists(exe):
-        from fluidsolver_b200 import build
-        build.build_examples()
-    out = tmp_path / "vtk"
-    out.mkdir()
-    r = subprocess.run([exe, "60", str(out)], capture_output=True, text=True, timeout=900)
-    print("\n" + r.stdout[-600:])
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
-    assert "all tests of test/PeriodicChannel.cpp passed" in r.stdout
-    frames = sorted(os.listdir(out))
-    assert len(frames) >= 60 and frames[0] == "state_000000.vtk"
-    nx, ny = 215, 43
-    head = (out / frames[-1]).read_bytes()[:200]
-    assert head.startswith(b"# vtk DataFile Version 2.0\nState of FluidSolver at time t=")
-    size = os.path.getsize(out / frames[-1])
-    assert size > (nx + 1) * (ny + 1) * 24 + nx * ny * (8 + 8 + 24)
 
 
 def test_point_sampling_vs_reference_golden(F, oracle):
@@ -554,6 +432,125 @@ def test_count_nonfinite(F):
     fs.close()
 
 
+def test_point_sampling_slabs(F, oracle):
+    """eval_flow_field_at / bilinear_interpolate on 3 slab contexts: the slab owning a point's row evaluates it,
+    the results are summed over the ranks; identical to one context"""
+    from test_gpu_slab import run_ranks, run_single
+    from cases import cavity_bc, grid_coords, random_state, sample_points
+    st = random_state(50, 23, seed=5)
+    px, py = sample_points(st)
+    x, y = grid_coords(st)
+
+    def body(fs, r):
+        fs.interpolate_cell_centres()
+        u, v = fs.eval_flow_field_at(x, y, px, py)
+        return [u, v, fs.bilinear_interpolate("P", x, y, px, py)]
+
+    _, ra = run_ranks(F, st, cavity_bc(), 3, body, fields=("U",))
+    _, rb = run_single(F, st, cavity_bc(), body, fields=("U",))
+    for q in range(3):
+        assert all(np.array_equal(r[q], ra[0][q]) for r in ra)
+        assert np.array_equal(ra[0][q], rb[q])
+
+
+# ---- the long / tolerance-sensitive runs last (pytest -x stops at the first failure) ---------------------------
+@pytest.mark.parametrize("name", CHANNEL215)
+def test_channel215_drivers_vs_reference_golden(F, oracle, name):
+    """test/PeriodicChannel.cpp (total-flow forcing of both ghost columns), test/CustomDirichletChannel.cpp
+    (function inlet, dy-weighted outflow correction) and scaling/Channel.cpp (clipped Neumann outlet with
+    backflow): fsgpu_flow_control alone, then timesteps through fsgpu_step with
+    fsgpu_set_flow_control, against the committed output of the unmodified reference"""
+    from cases import rel_inf
+    g = np.load(os.path.join(GOLD, f"run_{name}.npz"))
+    st, bc, mode, total = _channel215(oracle, name)
+    fs = to_gpu(F, st, bc)
+    io = fs.flow_control(mode, total)
+    assert np.allclose(io, g["flow_io"], rtol=1e-13, atol=0)
+    assert rel_inf(fs.download("U"), g["flow_U"]) <= 1e-12
+    if mode == F.FLOW_FORCE_TOTAL:
+        assert np.allclose(fs.flow_control(mode, total), total, rtol=1e-12)
+    fs.upload("U", st.U)
+    fs.set_flow_control(mode, total)
+    ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
+    ps.set_pressure_operator()
+    worst = 0.0
+    for k, dt_ref in enumerate(g["dts"]):
+        assert fs.adjust_dt(0.9, 0.1) == pytest.approx(float(dt_ref), rel=1e-9)
+        res, it = fs.step(ps, float(dt_ref), 2, F.STEP_OUTFLOW_FIX)
+        worst = max(worst, res)
+        assert res < 1e-6
+        if res < 1e-12:
+            assert abs(it - int(g["its"][k])) <= max(3, 0.35 * int(g["its"][k]))
+    U, V, p = fs.download("U"), fs.download("V"), fs.download("P")
+    ev = vel_err(U, V, g["U"], g["V"])
+    ep = rel_l2(p - p.mean(), g["p"] - g["p"].mean())
+    print(f"\n[{name}] velocity rel L2 {ev:.3e}, pressure rel L2 {ep:.3e}, worst residual {worst:.2e}")
+    # the reference reaches 1e-13 in every solve of these runs; should the PCG here leave one at its
+    # breakdown floor instead (as HYPRE itself does on the TGV / channel systems, tests/test_gpu_solver.py),
+    # the fields agree to that floor
+    floor = worst >= 1e-12
+    assert ev <= (1e-7 if floor else 1e-10) and ep <= (1e-5 if floor else 1e-8)
+    ps.close()
+    fs.close()
+
+
+@pytest.mark.parametrize("name", CHANNEL215[:2])
+def test_channel215_drivers_slabs(F, oracle, name):
+    """the same drivers on 3 slab contexts (in-process transport) vs one context: the inlet sum lives
+    on the first slab, the outlet sum on the last, the periodic wrap-around between the two"""
+    from test_gpu_slab import run_ranks, run_single
+    st, bc, mode, total = _channel215(oracle, name)
+
+    def body(fs, r):
+        fs.set_flow_control(mode, total)
+        ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
+        ps.set_pressure_operator()
+        hist = [fs.flow_control(mode, total)]
+        for _ in range(2):
+            dt = fs.adjust_dt(0.9, 0.1)
+            fs.step(ps, dt, 2, F.STEP_OUTFLOW_FIX)
+            hist.append(dt)
+        ps.close()
+        return hist
+
+    a, ra = run_ranks(F, st, bc, 3, body, fields=("U", "V", "P"))
+    b, rb = run_single(F, st, bc, body, fields=("U", "V", "P"))
+    assert all(x == ra[0] for x in ra)
+    assert np.allclose(ra[0][0], rb[0], rtol=1e-13) and ra[0][1:] == pytest.approx(rb[1:], rel=1e-9)
+    # channel systems: same bound as tests/test_gpu_slab.py::test_slab_timesteps (PCG breakdown floor)
+    assert vel_err(a["U"], a["V"], b["U"], b["V"]) <= 1e-7
+
+
+def test_channel_convergence_study(F, oracle):
+    """scaling/Channel.cpp (non-periodic) on the GPU at the driver's own settings, T_END = 20, n = 3, 4, 5:
+    the error measures of :253-300 against the unmodified reference's (tests/golden/channel_study.npz) and
+    the second-order trend of the profile error.  The reference solves to tol 1e-6, so two implementations
+    agree to about that in the fields."""
+    from cases import channel_study_case, channel_study_errors, run_channel_study
+    g = np.load(os.path.join(GOLD, "channel_study.npz"))
+    ue = []
+    for k, n in enumerate(g["n"]):
+        st, bc = channel_study_case(oracle, int(n))
+        fs = to_gpu(F, st, bc)
+        fs.set_flow_control(F.FLOW_OUTFLOW_FIX_DY)
+        ps = F.LinearSolver(fs, tol=1e-6, max_iter=50)
+        ps.set_pressure_operator()
+        steps = run_channel_study(lambda: fs.adjust_dt(0.9, 0.1), lambda dt: fs.step(ps, dt, 2, F.STEP_OUTFLOW_FIX))
+        e = np.array(channel_study_errors(fs.download("P"), fs.download("U"), fs.download("V"), st.nx, st.ny, st.dx))
+        print(f"\n[channel study n={n}] steps {steps} (reference {int(g['errors'][k][4])}), errors {e}, "
+              f"reference {g['errors'][k][:4]}")
+        assert abs(steps - int(g["errors"][k][4])) <= 1
+        # the profile error is a discretisation error (2 %); the pressure / dpdx / V measures are at the level the
+        # 1e-6 solves leave behind and move with the iteration at which a solve stops (20 %)
+        assert np.all(np.abs(e / g["errors"][k][:4] - 1.0) <= np.array([0.2, 0.2, 0.02, 0.2])), (n, e)
+        if k == 0:
+            assert np.abs(fs.download("U") - g["U_n3"]).max() <= 1e-5
+        ue.append(e[2])
+        ps.close()
+        fs.close()
+    assert ue[0] / ue[1] > 3.0 and ue[1] / ue[2] > 3.0
+
+
 def test_custom_dirichlet_channel_reference_criteria(F, oracle):
     """the reference's own test/CustomDirichletChannel.cpp on the GPU at the driver's settings (tol 1e-6, 50
     iterations, NUM_SUBITER 2, CFL 0.9, T_END = 60), judged by the driver's criteria (:240-331): outflow = inflow
@@ -585,22 +582,26 @@ def test_custom_dirichlet_channel_reference_criteria(F, oracle):
     fs.close()
 
 
-def test_point_sampling_slabs(F, oracle):
-    """eval_flow_field_at / bilinear_interpolate on 3 slab contexts: the slab owning a point's row evaluates it,
-    the results are summed over the ranks; identical to one context"""
-    from test_gpu_slab import run_ranks, run_single
-    from cases import cavity_bc, grid_coords, random_state, sample_points
-    st = random_state(50, 23, seed=5)
-    px, py = sample_points(st)
-    x, y = grid_coords(st)
-
-    def body(fs, r):
-        fs.interpolate_cell_centres()
-        u, v = fs.eval_flow_field_at(x, y, px, py)
-        return [u, v, fs.bilinear_interpolate("P", x, y, px, py)]
-
-    _, ra = run_ranks(F, st, cavity_bc(), 3, body, fields=("U",))
-    _, rb = run_single(F, st, cavity_bc(), body, fields=("U",))
-    for q in range(3):
-        assert all(np.array_equal(r[q], ra[0][q]) for r in ra)
-        assert np.array_equal(ra[0][q], rb[q])
+def test_cpp_periodic_channel_driver(tmp_path):
+    """examples/periodic_channel.cpp: the reference's test/PeriodicChannel.cpp on the C++ shim, run to its own
+    T_END = 60 with the reference's own pass criteria (:264-337) as the exit code; the VTK frames it writes
+    are legacy-VTK files of the expected size"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = os.path.join(root, "examples", "periodic_channel")
+    if not os.path.exists(exe):
+        from fluidsolver_b200 import build
+        build.build_examples()
+    out = tmp_path / "vtk"
+    out.mkdir()
+    r = subprocess.run([exe, "60", str(out)], capture_output=True, text=True, timeout=900)
+    print("\n" + r.stdout[-600:])
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "all tests of test/PeriodicChannel.cpp passed" in r.stdout
+    frames = sorted(os.listdir(out))
+    assert len(frames) >= 60 and frames[0] == "state_000000.vtk"
+    nx, ny = 215, 43
+    head = (out / frames[-1]).read_bytes()[:200]
+    assert head.startswith(b"# vtk DataFile Version 2.0\nState of FluidSolver at time t=")
+    size = os.path.getsize(out / frames[-1])
+    assert size > (nx + 1) * (ny + 1) * 24 + nx * ny * (8 + 8 + 24)
