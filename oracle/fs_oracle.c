@@ -810,7 +810,12 @@ int fso_step(fso_fs* fs, const fso_bconds* bc, fso_solver* s, const fso_step_opt
       fso_apply_neumann_bconds(fs->rho_v, NX, NY + 1);
     }
     fso_calc_dmomdt(fs, dmomU, dmomV);
-    fso_update_velocity(fs, dmomU, dmomV, dt);
+    if (o->ib_mode == 2) {
+      fso_update_velocity_ib_semi_analytical(fs, dmomU, dmomV, dt, o->ib_u, o->ib_v);
+    } else {
+      fso_update_velocity(fs, dmomU, dmomV, dt);
+      if (o->ib_mode == 1) fso_correct_velocity_ib_implicit_euler(fs, o->ib_u, o->ib_v, dt);
+    }
     fso_apply_velocity_bconds(fs, bc);
     if (o->outflow_fix) fso_flow_control(fs, o->outflow_fix, o->total_flow, NULL);
     fso_calc_divergence(fs, div);

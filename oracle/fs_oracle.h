@@ -136,6 +136,9 @@ typedef struct {
   int capillary;      /* pressure-jump block, test/StationaryDrop.cpp:331-353 (needs vf, curv, ilen) */
   const double *vf, *curv, *ilen; /* cell fields (NX+2)x(NY+2); frozen during the step */
   double total_flow;  /* outflow_fix == 3: the flux both ghost columns are forced to */
+  int ib_mode;        /* immersed-boundary drivers, scaling/LuchiniIBChannel.cpp:212-221: 0 none; 1 update_velocity +
+                         correct_velocity_ib_implicit_euler; 2 update_velocity_ib_semi_analytical (src/IB.hpp:110-186) */
+  const double *ib_u, *ib_v; /* ib_corr_u_stag (U-like), ib_corr_v_stag (V-like); Inf marks solid points */
 } fso_step_opts;
 /* returns total PCG iterations of the step; *res = last residual */
 int fso_step(fso_fs* fs, const fso_bconds* bc, fso_solver* s, const fso_step_opts* o, double dt,

@@ -83,6 +83,7 @@ struct SessionBase {
   virtual void conserved(double* mass, double* mx, double* my)                 = 0;
   virtual double flow_control(int mode, double total_flow, double* io)         = 0;
   virtual int to_npy(const char* dir)                                          = 0;
+  virtual void ib_channel_correction(double y0, double y1, double* ibu, double* ibv) = 0;
   virtual void vf_drop(double* vf)                                             = 0;
   virtual void sample(int mode, int n, const double* px, const double* py, double* a, double* b) = 0;
   virtual double integrate_cell(const double* f, int include_ghost, int l1)    = 0;
@@ -224,6 +225,8 @@ struct Session final : SessionBase {
   }
   // cell-field scratch for the two-phase inputs (vf, curv, interface_length)
   std::unique_ptr<Field2D<Float, NX, NY, G>> c_vf{}, c_curv{}, c_ilen{};
+  std::unique_ptr<Field2D<Float, NX + 1, NY, G>> ib_u{};
+  std::unique_ptr<Field2D<Float, NX, NY + 1, G>> ib_v{};
   void load_cells(const double* vf, const double* curv, const double* ilen) {
     if (!c_vf) {
       c_vf   = std::make_unique<Field2D<Float, NX, NY, G>>();
@@ -351,14 +354,29 @@ struct Session final : SessionBase {
         ::apply_neumann_bconds(fs.curr.rho_v_stag);
       }
       ::calc_dmomdt(fs, dU, dV);
-      for_each_i<Exec::Parallel>(fs.curr.U, [&](Index i, Index j) {
-        fs.curr.U(i, j) =
-            (fs.old.rho_u_stag(i, j) * fs.old.U(i, j) + dt * dU(i, j)) / fs.curr.rho_u_stag(i, j);
-      });
-      for_each_i<Exec::Parallel>(fs.curr.V, [&](Index i, Index j) {
-        fs.curr.V(i, j) =
-            (fs.old.rho_v_stag(i, j) * fs.old.V(i, j) + dt * dV(i, j)) / fs.curr.rho_v_stag(i, j);
-      });
+      if (o->ib_mode) {  // the calls of scaling/LuchiniIBChannel.cpp:212-221
+        if (!ib_u) {
+          ib_u = std::make_unique<Field2D<Float, NX + 1, NY, G>>();
+          ib_v = std::make_unique<Field2D<Float, NX, NY + 1, G>>();
+        }
+        cp_in(*ib_u, o->ib_u);
+        cp_in(*ib_v, o->ib_v);
+        if (o->ib_mode == 1) {
+          ::update_velocity(dU, dV, dt, fs);
+          ::correct_velocity_ib_implicit_euler(*ib_u, *ib_v, dt, fs);
+        } else {
+          ::update_velocity_ib_semi_analytical(dU, dV, dt, *ib_u, *ib_v, fs);
+        }
+      } else {
+        for_each_i<Exec::Parallel>(fs.curr.U, [&](Index i, Index j) {
+          fs.curr.U(i, j) =
+              (fs.old.rho_u_stag(i, j) * fs.old.U(i, j) + dt * dU(i, j)) / fs.curr.rho_u_stag(i, j);
+        });
+        for_each_i<Exec::Parallel>(fs.curr.V, [&](Index i, Index j) {
+          fs.curr.V(i, j) =
+              (fs.old.rho_v_stag(i, j) * fs.old.V(i, j) + dt * dV(i, j)) / fs.curr.rho_v_stag(i, j);
+        });
+      }
       ::apply_velocity_bconds(fs, bconds, 0.0);
       if (o->outflow_fix) flow_control(o->outflow_fix, o->total_flow, nullptr);
       auto t1 = clk::now();
@@ -434,6 +452,23 @@ struct Session final : SessionBase {
     });
     ::apply_neumann_bconds(div);
     cp_out(div, out);
+  }
+  // calc_ib_correction_shape (src/IB.hpp:45-107) for the two walls of scaling/LuchiniIBChannel.cpp:36-47,203-209:
+  // solid below y0 and above y1
+  void ib_channel_correction(double y0, double y1, double* ibu, double* ibv) override {
+    const Float lx = fs.dx * static_cast<Float>(NX), ly = fs.dy * static_cast<Float>(NY);
+    const Rect<Float> wall_bottom{.x = -1.0, .y = 0.0, .w = lx + 1.0, .h = y0};
+    const Rect<Float> wall_top{.x = -1.0, .y = y1, .w = lx + 1.0, .h = ly - y1};
+    auto a = std::make_unique<Field2D<Float, NX + 1, NY, G>>();
+    auto b = std::make_unique<Field2D<Float, NX, NY + 1, G>>();
+    fill(*a, 0.0);
+    fill(*b, 0.0);
+    ::calc_ib_correction_shape(wall_bottom, fs.dx, fs.dy, fs.x, fs.ym, *a);
+    ::calc_ib_correction_shape(wall_bottom, fs.dx, fs.dy, fs.xm, fs.y, *b);
+    ::calc_ib_correction_shape(wall_top, fs.dx, fs.dy, fs.x, fs.ym, *a);
+    ::calc_ib_correction_shape(wall_top, fs.dx, fs.dy, fs.xm, fs.y, *b);
+    cp_out(*a, ibu);
+    cp_out(*b, ibv);
   }
   // integrate / L1_norm (src/Operators.hpp:51-76) and calc_grad_of_centered_points (:164-201) on a cell field
   double integrate_cell(const double* f, int include_ghost, int l1) override {
@@ -521,6 +556,9 @@ void fsref_calc_pressure_jump(void* s, const double* vf, const double* curv, con
 void fsref_interpolate_uv(void* s, double* ui, double* vi) { S->interpolate_uv(ui, vi); }
 void fsref_conserved(void* s, double* mass, double* mx, double* my) { S->conserved(mass, mx, my); }
 int fsref_to_npy(void* s, const char* dir) { return S->to_npy(dir); }
+void fsref_ib_channel_correction(void* s, double y0, double y1, double* ibu, double* ibv) {
+  S->ib_channel_correction(y0, y1, ibu, ibv);
+}
 void fsref_vf_drop(void* s, double* vf) { S->vf_drop(vf); }
 void fsref_sample(void* s, int mode, int n, const double* px, const double* py, double* a, double* b) {
   S->sample(mode, n, px, py, a, b);

@@ -403,3 +403,24 @@ def channel215_measures(periodic, p, U, V, nx=215, ny=43, dx=5.0 / 215, visc=1e-
         d = np.abs(U[i + 1, :] - g / (2 * visc) * (ym * ym - ym))
         l1 = max(l1, float(np.sum((ym[1:] - ym[:-1]) * 0.5 * (d[1:] + d[:-1]))))
     return dev_p, dev_dpdx, l1, float(np.abs(V[1:nx + 1, 1:ny + 2]).max())
+
+
+def ib_channel_case(oracle, n=64):
+    """scaling/LuchiniIBChannel.cpp:17-75 at n x n cells: 5 x 5 domain, channel of height 1 between immersed walls
+    (solid for y <= 2 and y >= 3), rho = 10, mu = 1e-2, Poiseuille inlet inside the channel, Neumann outlet;
+    -> (state, bconds); the wall correction fields come from the reference (tests/golden/run_ibchannel64.npz)"""
+    visc, rho, p0, length, height, off = 1e-2, 10.0, 0.2, 5.0, 1.0, 2.0
+    st = State(n, n, 5.0 / n, 5.0 / n, rho_gas=rho, rho_liquid=rho, visc_gas=visc, visc_liquid=visc)
+    oracle.calc_rho_visc_const(st)
+    ym = (np.arange(-1, n + 1) + 0.5) * st.dy
+    yo = ym - off
+    prof = np.where((ym <= off) | (ym >= off + height), 0.0, p0 * height / (visc * length) * yo * (1.0 - yo / height))
+    # half the developed profile plus a seeded perturbation: the pressure solves have a right-hand side well above
+    # rounding (on the developed x-independent flow the divergence vanishes and PCG would iterate on noise)
+    rng = np.random.default_rng(17)
+    st.a["U"][:] = 0.5 * prof[None, :] + 0.02 * rng.uniform(-1, 1, st.a["U"].shape)
+    st.a["V"][:] = 0.02 * rng.uniform(-1, 1, st.a["V"].shape)
+    bc = BConds(kind=(DIRICHLET, NEUMANN, DIRICHLET, DIRICHLET), u_val=(0.0,) * 4, v_val=(0.0,) * 4,
+                u_prof=(prof, None, None, None))
+    oracle.apply_velocity_bconds(st, bc)
+    return st, bc

@@ -292,6 +292,37 @@ def run_twophase_quadrature(name="run_twophase_q128", nsub=3, nsteps=2):
     print("run", name, "its", its, "dt", dts)
 
 
+def run_ibchannel(name="run_ibchannel64", nsub=5, nsteps=3):
+    """scaling/LuchiniIBChannel.cpp: the wall correction fields of calc_ib_correction_shape and three timesteps with
+    each of the two immersed-boundary velocity updates (:212-221), CFL 0.25.
+    NOT part of the committed goldens / test suites yet (python make_golden_8f.py ib writes it on request): on this
+    state the restatement's PCG takes one of its breakdown exits at iteration 7 (relative residual 5e-3) where HYPRE
+    continues to 6e-7 -- the two agree to 1e-15 on every other pinned system, so the cause is open."""
+    from cases import ib_channel_case
+    out = {}
+    for mode in (1, 2):
+        st, bc = ib_channel_case(o)
+        r = Ref(st.nx, st.ny)
+        r.load(st)
+        r.set_bconds(bc)
+        ibu, ibv = r.ib_channel_correction(2.0, 3.0)
+        out["ib_u"], out["ib_v"] = ibu, ibv
+        r.solver_create(1e-13, 500)
+        r.solver_set_operator()
+        dts, its = [], []
+        for _ in range(nsteps):
+            dt = r.adjust_dt(0.25, 0.1)
+            it, res = r.step(dt, nsub, outflow_fix=1, ib=(mode, ibu, ibv))
+            dts.append(dt)
+            its.append(it)
+        s2 = st.copy()
+        r.store(s2)
+        out.update({f"dts{mode}": np.array(dts), f"its{mode}": np.array(its), f"U{mode}": s2.U, f"V{mode}": s2.V,
+                    f"p{mode}": s2.a["p"]})
+        print("run", name, "mode", mode, "its", its, "dt", dts, "solid points", int(np.isinf(ibu).sum()))
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
+
+
 def monitor_log(name="monitor_log.txt"):
     """src/Monitor.hpp and should_save (src/IO.hpp:97-108) of the unmodified reference on the rows / step sequence of
     tests/test_output_cpu.py"""
@@ -331,6 +362,9 @@ if __name__ == "__main__":
         sys.exit(0)
     if "twophase_q" in sys.argv:
         run_twophase_quadrature()
+        sys.exit(0)
+    if "ib" in sys.argv:
+        run_ibchannel()
         sys.exit(0)
     if "vf" in sys.argv:
         vf_drop()

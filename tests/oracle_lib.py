@@ -48,14 +48,19 @@ class CSolverOpts(C.Structure):
 class CStepOpts(C.Structure):
     _fields_ = [("num_subiter", C.c_int), ("outflow_fix", C.c_int), ("psd", C.c_int),
                 ("rebuild_operator_each_subiter", C.c_int), ("density_update", C.c_int),
-                ("capillary", C.c_int), ("vf", DP), ("curv", DP), ("ilen", DP), ("total_flow", C.c_double)]
+                ("capillary", C.c_int), ("vf", DP), ("curv", DP), ("ilen", DP), ("total_flow", C.c_double),
+                ("ib_mode", C.c_int), ("ib_u", DP), ("ib_v", DP)]
 
 
-def _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary, total_flow=0.0):
+def _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary, total_flow=0.0, ib=None):
     """outflow_fix: 0 none, 1 LaminarChannel, 2 CustomDirichletChannel (dy-weighted), 3 PeriodicChannel
     (both ghost columns forced to total_flow)"""
     o = CStepOpts(num_subiter, outflow_fix, psd, rebuild, int(density), int(capillary is not None))
     o.total_flow = total_flow
+    if ib is not None:  # (mode, ib_corr_u_stag, ib_corr_v_stag): 1 implicit Euler, 2 semi-analytical
+        o._keep_ib = [np.ascontiguousarray(a, dtype=np.float64) for a in ib[1:]]
+        o.ib_mode = int(ib[0])
+        o.ib_u, o.ib_v = (a.ctypes.data_as(DP) for a in o._keep_ib)
     if capillary is not None:
         o._keep = [np.ascontiguousarray(a, dtype=np.float64) for a in capillary]
         o.vf, o.curv, o.ilen = (a.ctypes.data_as(DP) for a in o._keep)
@@ -314,10 +319,10 @@ class Oracle:
         return OracleSolver(self, nx, ny, CSolverOpts(tol, max_iter, max_levels, relax_type, skip_relax))
 
     def step(self, st, bc, solver, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0, density=0,
-             capillary=None, total_flow=0.0):
-        """capillary = (vf, curv, interface_length) cell arrays, or None"""
+             capillary=None, total_flow=0.0, ib=None):
+        """capillary = (vf, curv, interface_length) cell arrays, or None; ib = (mode, ib_corr_u, ib_corr_v) or None"""
         res = C.c_double(0)
-        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary, total_flow)
+        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary, total_flow, ib)
         it = self.lib.fso_step(C.byref(st.cstruct()), C.byref(bc.cstruct()), solver.h, C.byref(o), dt,
                                C.byref(res))
         return it, res.value
@@ -404,6 +409,7 @@ class Ref:
             L.fsref_conserved.argtypes = [C.c_void_p, DP, DP, DP]
             L.fsref_flow_control.argtypes = [C.c_void_p, C.c_int, C.c_double, DP]
             L.fsref_to_npy.argtypes = [C.c_void_p, C.c_char_p]
+            L.fsref_ib_channel_correction.argtypes = [C.c_void_p, C.c_double, C.c_double, DP, DP]
             L.fsref_vf_drop.argtypes = [C.c_void_p, DP]
             L.fsref_sample.argtypes = [C.c_void_p, C.c_int, C.c_int, DP, DP, DP, DP]
             L.fsref_monitor_log.argtypes = [C.c_char_p, C.c_int, C.POINTER(C.c_char_p), C.c_int, C.POINTER(C.c_char_p),
@@ -556,6 +562,12 @@ class Ref:
         self.lib().fsref_grad_centered(self.h, _ptr(f), _ptr(gx), _ptr(gy))
         return gx, gy
 
+    def ib_channel_correction(self, y0, y1):
+        """calc_ib_correction_shape (src/IB.hpp:45-107) for solid walls below y0 and above y1 -> (ib_corr_u, ib_corr_v)"""
+        ibu, ibv = np.zeros((self.nx + 3, self.ny + 2)), np.zeros((self.nx + 2, self.ny + 3))
+        self.lib().fsref_ib_channel_correction(self.h, y0, y1, _ptr(ibu), _ptr(ibv))
+        return ibu, ibv
+
     def vf_drop(self):
         """the initial volume fraction of test/StationaryDrop.cpp:47-52,209-212 on this session's grid"""
         vf = np.zeros((self.nx + 2, self.ny + 2))
@@ -576,9 +588,9 @@ class Ref:
         return io[0], io[1]
 
     def step(self, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0, phases=None, density=0,
-             capillary=None, total_flow=0.0):
+             capillary=None, total_flow=0.0, ib=None):
         res = C.c_double(0)
-        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary, total_flow)
+        o = _step_opts(num_subiter, outflow_fix, psd, rebuild, density, capillary, total_flow, ib)
         ph = _ptr(phases) if phases is not None else None
         it = self.lib().fsref_step(self.h, C.byref(o), dt, C.byref(res), ph)
         return it, res.value
