@@ -115,6 +115,9 @@ typedef struct {
   int max_levels;   /* 16 = reference (PS_PFMG_MAX_LEVELS) */
   int relax_type;   /* 1 = weighted Jacobi (reference default), 2 = symmetric red/black GS */
   int skip_relax;   /* 1 = reference default */
+  int snap_zero_diag; /* 0 = HYPRE's arithmetic as is. 1 = coarse diagonals that are pure cancellation noise become 0
+                         (what k_rap of the CUDA path does, see setup_rap in pfmg_oracle.c): for singular operators
+                         whose coefficients are not dyadic, where HYPRE's `== 0.0` test hinges on the last bit */
 } fso_solver_opts;
 fso_solver* fso_solver_create(int64_t nx, int64_t ny, const fso_solver_opts* o);
 void fso_solver_destroy(fso_solver* s);

@@ -138,7 +138,7 @@ static void setup_interp(level* l) {
 }
 
 /* struct_ls/pfmg_setup_rap5.c:339-379 */
-static void setup_rap(const level* f, level* c) {
+static void setup_rap(const level* f, level* c, int snap) {
   const int d = f->cdir;
   const int em = d == 0 ? 1 : 3, ep = d == 0 ? 2 : 4;
   const int tm = d == 0 ? 3 : 1, tp = d == 0 ? 4 : 2;
@@ -165,8 +165,19 @@ static void setup_rap(const level* f, level* c) {
       if (f->a[tp][k] == 0.0) east = 0.0;
       c->a[tm][kc] = west;
       c->a[tp][kc] = east;
-      c->a[0][kc]  = f->a[0][k] + f->a[tm][k] + f->a[tp][k] + f->a[em][k] * pp_m +
-                    f->a[ep][k] * pm_p - west - east;
+      double dc = f->a[0][k] + f->a[tm][k] + f->a[tp][k] + f->a[em][k] * pp_m +
+                  f->a[ep][k] * pm_p - west - east;
+      /* opts.snap_zero_diag; NOT in HYPRE (same guard as k_rap, fluidsolver_b200/csrc/solver_setup.cu): a singular all-Neumann operator
+       * has zero row sums on every level, so the one-point coarsest grid's diagonal is 0 in exact arithmetic and
+       * pure cancellation noise otherwise (3e-16 on the rho = 10, dx = 5/64 channel of scaling/LuchiniIBChannel.cpp).
+       * hypre_StructMatrixZeroDiagonal tests == 0.0; noise that fails that test is divided by in the coarsest
+       * relaxation and PCG breaks down (HYPRE itself: 10 iterations, residual 6e-8, at tol 1e-10 on that system).
+       * Off by default: where HYPRE's own solve stalls at the rounding floor (tgv32 at tol 1e-13) the guard changes
+       * the iteration count. */
+      const double scale = fabs(f->a[0][k]) + fabs(f->a[tm][k]) + fabs(f->a[tp][k]) + fabs(f->a[em][k] * pp_m) +
+                           fabs(f->a[ep][k] * pm_p) + fabs(west) + fabs(east);
+      if (snap && fabs(dc) <= 1e-13 * scale) dc = 0.0;
+      c->a[0][kc] = dc;
     }
 }
 
@@ -251,7 +262,7 @@ void fso_solver_set_operator(fso_solver* s, const double* op) {
   for (l = 0; l < s->nl - 1; ++l) {
     level_alloc(&L[l + 1]);
     setup_interp(&L[l]);
-    setup_rap(&L[l], &L[l + 1]);
+    setup_rap(&L[l], &L[l + 1], s->o.snap_zero_diag);
   }
   /* zero diagonal on the coarsest grid => no relaxation there, pfmg_setup.c:349-357 */
   level* c = &L[s->nl - 1];

@@ -42,7 +42,7 @@ class CBconds(C.Structure):
 
 class CSolverOpts(C.Structure):
     _fields_ = [("tol", C.c_double), ("max_iter", C.c_int), ("max_levels", C.c_int),
-                ("relax_type", C.c_int), ("skip_relax", C.c_int)]
+                ("relax_type", C.c_int), ("skip_relax", C.c_int), ("snap_zero_diag", C.c_int)]
 
 
 class CStepOpts(C.Structure):
@@ -315,8 +315,8 @@ class Oracle:
     def apply_neumann_bconds(self, f):
         self.lib.fso_apply_neumann_bconds(_ptr(f), f.shape[0] - 2, f.shape[1] - 2)
 
-    def solver(self, nx, ny, tol=1e-6, max_iter=50, max_levels=16, relax_type=1, skip_relax=1):
-        return OracleSolver(self, nx, ny, CSolverOpts(tol, max_iter, max_levels, relax_type, skip_relax))
+    def solver(self, nx, ny, tol=1e-6, max_iter=50, max_levels=16, relax_type=1, skip_relax=1, snap_zero_diag=0):
+        return OracleSolver(self, nx, ny, CSolverOpts(tol, max_iter, max_levels, relax_type, skip_relax, snap_zero_diag))
 
     def step(self, st, bc, solver, dt, num_subiter, outflow_fix=0, psd=PSD_NONE, rebuild=0, density=0,
              capillary=None, total_flow=0.0, ib=None):
