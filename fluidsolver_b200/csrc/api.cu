@@ -341,7 +341,8 @@ int fsgpu_momentum_update(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_
 int fsgpu_apply_velocity_bconds(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_bconds(c); }
 int fsgpu_calc_divergence(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_divergence(c); }
 int fsgpu_shift_pressure_to_zero(fsgpu_ctx* c) { FS_CHECK_CTX(c); return fs_launch_shift_pressure(c); }
-int fsgpu_correct_velocity(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_correct(c, dt, false); }
+int fsgpu_correct_velocity(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_correct(c, dt, false, false); }
+int fsgpu_project(fsgpu_ctx* c, double dt) { FS_CHECK_CTX(c); return fs_launch_correct(c, dt, true, false); }
 
 static bool flow_mode_ok(int mode) {
   if (mode >= FSGPU_FLOW_OUTFLOW_FIX && mode <= FSGPU_FLOW_FORCE_TOTAL) return true;
@@ -571,6 +572,12 @@ int fsgpu_ps_set_rhs(fsgpu_ps* s, double dt) {
   return fs_launch_rhs(s->c, dt, s->o.psd, false);
 }
 
+int fsgpu_ps_set_rhs_from_velocity(fsgpu_ps* s, double dt) {
+  if (!s) { fs_set_error("null solver"); return 1; }
+  FS_CHECK_CTX(s->c);
+  return fs_launch_rhs(s->c, dt, s->o.psd, true);
+}
+
 int fsgpu_ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   if (!s) { fs_set_error("null solver"); return 1; }
   FS_CHECK_CTX(s->c);
@@ -618,7 +625,7 @@ int fsgpu_substep(fsgpu_ctx* c, fsgpu_ps* s, double dt, int flags, double* resid
   if (ps_solve(s, residual, iters)) return 1;
   {
     ProfScope ps_(PROF_CORRECT, c->stream);
-    if (fs_launch_correct(c, dt, true)) return 1;  // shift + p += dp + velocity correction
+    if (fs_launch_correct(c, dt, true, true)) return 1;  // shift + p += dp + velocity correction, one pass
   }
   return 0;
 }

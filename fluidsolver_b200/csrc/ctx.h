@@ -103,7 +103,7 @@ int fs_launch_divergence(fsgpu_ctx* c);
 // subtracted (two passes).  div_from_uv: compute div on the fly from U,V and store it too.
 int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv);
 int fs_launch_shift_pressure(fsgpu_ctx* c);
-int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift);
+int fs_launch_correct(fsgpu_ctx* c, double dt, bool shift, bool sum_ready);
 int fs_launch_cfl(fsgpu_ctx* c);               // 4 maxima -> red_out[0..3]
 int fs_launch_absmax(fsgpu_ctx* c, int field, bool include_ghost);  // -> red_out[0]
 int fs_launch_count_nonfinite(fsgpu_ctx* c, int field);  // -> red_out[0] NaNs, red_out[1] Infs

@@ -3,7 +3,7 @@
 //   k_divergence   calc_divergence               src/Operators.hpp:32-41 (all cells incl. ghosts)
 //   k_rhs          fill_pressure_rhs             src/LinearSystem.hpp:125-155
 //   k_sum          integrate<true>               src/Operators.hpp:52-62
-//   k_correct      shift_pressure_to_zero + p += dp + velocity correction
+//   k_project      shift_pressure_to_zero + p += dp + velocity correction
 //                                                src/Operators.hpp:78-82, scaling/LidDrivenFlow.cpp:153-160,
 //                                                test/LaminarChannel.cpp:222-233
 //   k_cfl          adjust_dt                     src/FS.hpp:100-128
@@ -39,22 +39,20 @@ k_divergence(const double* __restrict__ U, const double* __restrict__ V, double*
 template <bool FROM_UV>
 __global__ void __launch_bounds__(BX* BY)
 k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __restrict__ div,
-      double* __restrict__ rhs, const Geom g, double dt, double rdx, double rdy, double mvol_dt, int psd,
-      double* part, unsigned int* ticket, double* out) {
+      double* __restrict__ rhs, const Geom g, double dt, int psd, double* part, unsigned int* ticket,
+      double* out) {
   double v[1] = {0.0};
+  const double vol = g.dx * g.dy;
   for_each_point(g.a_lo, g.a_hi, g.ny + 2, [&](int64_t a, int64_t b) {
     const int64_t k = g.idx(a, b);
     double d;
-    double r;
-    if (FROM_UV) {  // fused fast path: multiplies by 1/dx, 1/dy, -vol/dt (<= 1 ulp per quotient, tolerance 1e-12)
-      d      = (__ldg(U + k + g.pitch) - __ldg(U + k)) * rdx + (__ldg(V + k + 1) - __ldg(V + k)) * rdy;
+    if (FROM_UV) {  // the reference's operation order (Operators.hpp:36-39): true divisions by dx, dy
+      d      = div_at(U, V, k, g.pitch, g.dx, g.dy);
       div[k] = d;
-      r      = mvol_dt * d;
     } else {
       d = div[k];
-      const double vol = g.dx * g.dy;
-      r                = -vol * d / dt;
     }
+    double r = -vol * d / dt;  // LinearSystem.hpp:134
     if ((psd == FSGPU_PSD_LEFT && a == 0) || (psd == FSGPU_PSD_RIGHT && a == g.nx + 1) ||
         (psd == FSGPU_PSD_BOTTOM && b == 0) || (psd == FSGPU_PSD_TOP && b == g.ny + 1))
       r = 0.0;
@@ -67,13 +65,15 @@ k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __rest
   }
 }
 
-// f -= (*sum) * scale on all cells
+// f -= (*sum) * s0 * s1 on all cells (the association of integrate(), src/Operators.hpp:61: integral * dx * dy;
+// the rhs mean passes s0 = 1 / size, s1 = 1)
 __global__ void __launch_bounds__(BX* BY)
-k_sub_scaled(double* __restrict__ f, const double* __restrict__ sum, double scale, const Geom g) {
+k_sub_scaled(double* __restrict__ f, const double* __restrict__ sum, double s0, double s1, bool divide, const Geom g) {
   const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
   const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
   if (a >= g.a_hi || b > g.ny + 1) return;
-  f[g.idx(a, b)] -= __ldg(sum) * scale;
+  const double c = divide ? __ldg(sum) / s0 : __ldg(sum) * s0 * s1;
+  f[g.idx(a, b)] -= c;
 }
 
 __global__ void __launch_bounds__(BX* BY)
@@ -86,36 +86,38 @@ k_sum(const double* __restrict__ f, const Geom g, double* part, unsigned int* ti
   }
 }
 
-// SHIFT: dp is used as (dp - c), c = (*sum) * dx * dy (shift_pressure_to_zero), and stored so.
+// The projection of one sub-iteration in ONE pass: shift_pressure_to_zero (src/Operators.hpp:78-82) + p += delta_p +
+// the velocity correction (scaling/LidDrivenFlow.cpp:153-160, test/LaminarChannel.cpp:222-233), with the
+// reference's operation order ((delta / dx) * dt) / rho.
+// SHIFT: delta_p is used as dpi - c with c = (*sum) * dx * dy, *sum = the sum of ALL entries of dpi, and the
+// shifted field is stored to dpo, a DIFFERENT buffer (a neighbour's un-shifted value is still needed by the threads
+// next to it, so the shift cannot be stored in place inside the same pass); the caller swaps the two buffers.
 template <bool SHIFT>
 __global__ void __launch_bounds__(BX* BY)
-k_correct(double* __restrict__ dp, double* __restrict__ p, double* __restrict__ U,
+k_project(const double* __restrict__ dpi, double* __restrict__ dpo, double* __restrict__ p, double* __restrict__ U,
           double* __restrict__ V, const double* __restrict__ ru, const double* __restrict__ rv,
-          const double* __restrict__ sum, const Geom g, double dt_dx, double dt_dy) {
+          const double* __restrict__ sum, const Geom g, double dt) {
   const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
   const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
   if (a >= g.a_hi || b > g.ny + 1) return;
   const int64_t k = g.idx(a, b), P = g.pitch;
   const double c  = SHIFT ? __ldg(sum) * g.dx * g.dy : 0.0;
-  // neighbours are read un-shifted from global memory and shifted locally: no ordering hazard
-  // with the in-place store below because every thread only stores its own dp[k].
-  const double d0 = dp[k] - c;
+  const double d0 = SHIFT ? __ldg(dpi + k) - c : __ldg(dpi + k);
   // U(i,j) for i in [0,NX], j in [0,NY): a in [1,NX+1], b in [1,NY]
   if (a >= 1 && b >= 1 && b <= g.ny) {
-    const double dm = __ldcg(dp + k - P) - c;
-    U[k] -= (d0 - dm) * dt_dx / __ldg(ru + k);  // (delta / dx * dt) / rho with dt/dx formed once (<= 1 ulp)
+    const double dm = SHIFT ? __ldg(dpi + k - P) - c : __ldg(dpi + k - P);
+    U[k] -= (d0 - dm) / g.dx * dt / __ldg(ru + k);
   }
   // V(i,j) for i in [0,NX), j in [0,NY]: a in [1,NX], b in [1,NY+1]
   if (a >= 1 && a <= g.nx && b >= 1) {
-    const double dm = __ldcg(dp + k - 1) - c;
-    V[k] -= (d0 - dm) * dt_dy / __ldg(rv + k);
+    const double dm = SHIFT ? __ldg(dpi + k - 1) - c : __ldg(dpi + k - 1);
+    V[k] -= (d0 - dm) / g.dy * dt / __ldg(rv + k);
   }
   p[k] += d0;
-  (void)d0;
+  if (SHIFT) dpo[k] = d0;
 }
 
-// in-place shift as its own pass (public fsgpu_shift_pressure_to_zero)
-// -> k_sub_scaled with scale dx*dy.
+// in-place shift as its own pass (public fsgpu_shift_pressure_to_zero): k_sum -> k_sub_scaled.
 
 __global__ void __launch_bounds__(BX* BY)
 k_cfl(const double* __restrict__ U, const double* __restrict__ V, const double* __restrict__ ru,
@@ -251,23 +253,23 @@ int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
   if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
   if (div_from_uv)
     k_rhs<true><<<pg, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
-                                                    c->f[FSGPU_RHS], c->g, dt, 1.0 / c->g.dx, 1.0 / c->g.dy,
-                                                    -(c->g.dx * c->g.dy) / dt, psd, c->part, c->ticket,
+                                                    c->f[FSGPU_RHS], c->g, dt, psd, c->part, c->ticket,
                                                     c->red_out);
   else
     k_rhs<false><<<pg, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
-                                                     c->f[FSGPU_RHS], c->g, dt, 0.0, 0.0, 0.0, psd, c->part,
-                                                     c->ticket, c->red_out);
+                                                     c->f[FSGPU_RHS], c->g, dt, psd, c->part, c->ticket,
+                                                     c->red_out);
   FS_LAUNCHED();
-  if (psd == FSGPU_PSD_NONE) {  // subtract the arithmetic mean over all (NX+2)(NY+2) entries
+  if (psd == FSGPU_PSD_NONE) {  // subtract the arithmetic mean over all (NX+2)(NY+2) entries: sum / size (LinearSystem.hpp:150-152)
     if (comm_allreduce(c, c->red_out, 1, COMM_SUM)) return 1;
-    const double inv_n = 1.0 / (double)((c->g.nx + 2) * (c->g.ny + 2));
-    k_sub_scaled<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_RHS], c->red_out, inv_n, c->g);
+    k_sub_scaled<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_RHS], c->red_out,
+                                                     (double)((c->g.nx + 2) * (c->g.ny + 2)), 1.0, true, c->g);
     FS_LAUNCHED();
   }
   return 0;
 }
 
+// sum of all entries of delta_p -> red_out[1] (all ranks)
 static int launch_sum_dp(fsgpu_ctx* c) {
   const unsigned gr = persist_blocks(c->g.a_hi - c->g.a_lo, c->g.ny + 2);
   if (fs_ensure_part(c, (size_t)gr * 4)) return 1;
@@ -279,25 +281,32 @@ static int launch_sum_dp(fsgpu_ctx* c) {
 
 int fs_launch_shift_pressure(fsgpu_ctx* c) {
   if (launch_sum_dp(c)) return 1;
-  k_sub_scaled<<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_DELTA_P], c->red_out + 1,
-                                                                c->g.dx * c->g.dy, c->g);
+  k_sub_scaled<<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_DELTA_P], c->red_out + 1, c->g.dx,
+                                                                c->g.dy, false, c->g);
   FS_LAUNCHED();
   return 0;
 }
 
-int fs_launch_correct(fsgpu_ctx* c, double dt, bool fuse_shift) {
-  if (fuse_shift) {
-    // a shifted dp is needed by every thread's neighbours too, so the shift cannot be stored
-    // in place inside the same pass: shift first (in place), then correct.
-    if (fs_launch_shift_pressure(c)) return 1;
-  }
+// shift: shift_pressure_to_zero, p += delta_p and the velocity correction in one pass (k_project<true>);
+// sum_ready: red_out[1] already holds the sum of all entries of delta_p on every rank (the solver leaves it
+// there, solver_pcg.cu), otherwise k_sum runs first.  The shifted delta_p lands in the buffer of FSGPU_RHS
+// (dead after the solve) and the two field pointers are swapped.
+int fs_launch_correct(fsgpu_ctx* c, double dt, bool shift, bool sum_ready) {
+  if (shift && !sum_ready && launch_sum_dp(c)) return 1;
   {  // the correction of face a reads delta_p of row a - 1
     const int fl[1] = {FSGPU_DELTA_P};
     if (fs_exchange_fields(c, fl, 1, 1)) return 1;
   }
-  k_correct<false><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
-      c->f[FSGPU_DELTA_P], c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
-      c->f[FSGPU_RHO_V], c->red_out + 1, c->g, dt / c->g.dx, dt / c->g.dy);
+  if (shift) {
+    k_project<true><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
+        c->f[FSGPU_DELTA_P], c->f[FSGPU_RHS], c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
+        c->f[FSGPU_RHO_V], c->red_out + 1, c->g, dt);
+    std::swap(c->f[FSGPU_DELTA_P], c->f[FSGPU_RHS]);
+  } else {
+    k_project<false><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
+        c->f[FSGPU_DELTA_P], nullptr, c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
+        c->f[FSGPU_RHO_V], c->red_out + 1, c->g, dt);
+  }
   FS_LAUNCHED();
   const int fl[3] = {FSGPU_U, FSGPU_V, FSGPU_P};
   return fs_exchange_fields(c, fl, 3, 1);

@@ -48,16 +48,27 @@ k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict_
 
 // x += alpha p; r -= alpha s.  Persistent grid (as the reduction kernels): the copy of this kernel
 // that is enqueued past convergence then costs ~3 us instead of the 140 us a 264k-CTA empty grid takes.
+// The sum of all entries of the new x rides along (-> *sum_out, this rank's rows): after the last iteration
+// it is the integral shift_pressure_to_zero needs (src/Operators.hpp:78-82), so the projection needs no
+// separate summation pass over delta_p.
 __global__ void __launch_bounds__(BX* BY)
 k_xr_update(const LevelDev L, double* __restrict__ x, double* __restrict__ r,
-            const double* __restrict__ p, const double* __restrict__ s, const PcgScal* scal) {
+            const double* __restrict__ p, const double* __restrict__ s, const PcgScal* scal, double* part,
+            unsigned int* ticket, double* sum_out) {
   if (scal->done) return;
   const double alpha = scal->alpha;
+  double v[1] = {0.0};
   for_each_point(L.i0, L.i1, L.n1, [&](int64_t li, int64_t lj) {
     const int64_t k = L.idx(li, lj);
-    x[k] += alpha * p[k];
+    const double xn = x[k] + alpha * p[k];
+    x[k] = xn;
+    v[0] += xn;
     r[k] -= alpha * s[k];
   });
+  double tot[1];
+  if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
+    if (threadIdx.x == 0 && threadIdx.y == 0) sum_out[0] = tot[0];
+  }
 }
 
 // gamma' = <r, z>.  INIT: this is bi = <C b, b>; otherwise the convergence test + beta.
@@ -100,7 +111,8 @@ __global__ void k_after_rz(PcgScal* scal) {
   if (!scal->done) pcg_after_rz<INIT>(scal, scal->red[0]);
 }
 
-__global__ void k_scal_init(PcgScal* scal, double eps, int nranks) {
+__global__ void k_scal_init(PcgScal* scal, double eps, int nranks, double* sum_x) {
+  sum_x[0] = 0.0;  // x = 0
   scal->nranks = nranks;
   scal->gamma = scal->sdotp = scal->alpha = scal->beta = scal->bi = scal->iprod = 0.0;
   scal->eps   = eps;
@@ -143,7 +155,7 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   double* r = c->f[FSGPU_RHS];  // r = b - A 0 = b: the rhs buffer becomes the residual
   const size_t prof0 = fs_prof_mark();
   g_prof_tag = 0;
-  k_scal_init<<<1, 1, 0, st>>>(s->scal, s->o.tol * s->o.tol, c->nranks);
+  k_scal_init<<<1, 1, 0, st>>>(s->scal, s->o.tol * s->o.tol, c->nranks, c->red_out + 1);
   FS_LAUNCHED();
   FS_CUDA(cudaMemsetAsync(alloc_base(c->g, x), 0, (size_t)c->g.count() * sizeof(double), st));
   // slab decomposition, per iteration: r needs FS_RO halo rows before the V-cycle (restriction
@@ -166,7 +178,7 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
     }
     {
       ProfScope ps_(PROF_XR, st);
-      k_xr_update<<<pg, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal);
+      k_xr_update<<<pg, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1);
       FS_LAUNCHED();
       if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
     }
@@ -188,6 +200,8 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
     }
   }
   (void)launched;
+  // the sum of all entries of the solution, on every rank (fs_launch_correct's sum_ready)
+  if (comm_allreduce(c, c->red_out + 1, 1, COMM_SUM)) return 1;
   FS_CUDA(cudaMemcpyAsync(&s->h_scal[0], s->scal, sizeof(PcgScal), cudaMemcpyDeviceToHost, st));
   FS_CUDA(cudaStreamSynchronize(st));
   const PcgScal& h = s->h_scal[0];

@@ -58,6 +58,7 @@ SYMBOLS = (
     "fsgpu_capillary_divergence", "fsgpu_correct_velocity_ib_implicit_euler",
     "fsgpu_update_velocity_ib_semi_analytical", "fsgpu_interpolate_cell_centres",
     "fsgpu_calc_conserved_quantities", "fsgpu_monitor",
+    "fsgpu_project", "fsgpu_ps_set_rhs_from_velocity",
 )
 TRANSPORT_NCCL, TRANSPORT_LOCAL = 0, 1
 COMM_ID_BYTES = 128
@@ -65,7 +66,7 @@ COMM_ID_BYTES = 128
 
 class PsOpts(C.Structure):
     _fields_ = [("tol", C.c_double), ("max_iter", C.c_int), ("psd", C.c_int), ("relax", C.c_int),
-                ("max_levels", C.c_int), ("skip_relax", C.c_int)]
+                ("max_levels", C.c_int), ("skip_relax", C.c_int), ("no_diag_snap", C.c_int)]
 
 
 class FsgpuError(RuntimeError):
@@ -108,7 +109,7 @@ def load():
               "shift_pressure_to_zero", "calc_rho_visc_const", "calc_rho_visc_vof", "calc_drhodt",
               "calc_pressure_jump", "interpolate_cell_centres"):
         getattr(L, "fsgpu_" + n).argtypes = [vp]
-    for n in ("update_velocity", "momentum_update", "correct_velocity", "update_density", "density_step",
+    for n in ("update_velocity", "momentum_update", "correct_velocity", "project", "update_density", "density_step",
               "capillary_divergence", "correct_velocity_ib_implicit_euler",
               "update_velocity_ib_semi_analytical"):
         getattr(L, "fsgpu_" + n).argtypes = [vp, dbl]
@@ -137,6 +138,7 @@ def load():
     L.fsgpu_ps_destroy.argtypes = [vp]
     L.fsgpu_ps_set_operator.argtypes = [vp]
     L.fsgpu_ps_set_rhs.argtypes = [vp, dbl]
+    L.fsgpu_ps_set_rhs_from_velocity.argtypes = [vp, dbl]
     L.fsgpu_ps_solve.argtypes = [vp, DP, C.POINTER(i32)]
     L.fsgpu_ps_num_levels.argtypes = [vp, C.POINTER(i32)]
     L.fsgpu_substep.argtypes = [vp, vp, dbl, i32, DP, C.POINTER(i32)]
@@ -389,6 +391,10 @@ class FS:
     def correct_velocity(self, dt):
         _chk(self.L.fsgpu_correct_velocity(self.h, dt))
 
+    def project(self, dt):
+        """shift_pressure_to_zero + p += delta_p + velocity correction in one pass (the kernel fsgpu_substep runs)"""
+        _chk(self.L.fsgpu_project(self.h, dt))
+
     def abs_max(self, name, include_ghost=False):
         """abs_max<INCLUDE_GHOST = false>(field), src/Utility.hpp:44-88: interior entries unless include_ghost"""
         o = C.c_double()
@@ -555,10 +561,10 @@ class LinearSolver:
     """``LinearSolver_StructHypre<Float,NX,NY,1>`` (src/LinearSolver_StructHypre.hpp:28-192)."""
 
     def __init__(self, fs: FS, tol=1e-6, max_iter=50, psd=PSD_NONE, relax=0, max_levels=0,
-                 skip_relax=-1):
+                 skip_relax=-1, no_diag_snap=0):
         self.fs, self.L = fs, fs.L
         self.h = C.c_void_p()
-        o = PsOpts(tol, max_iter, psd, relax, max_levels, skip_relax)
+        o = PsOpts(tol, max_iter, psd, relax, max_levels, skip_relax, no_diag_snap)
         _chk(self.L.fsgpu_ps_create(fs.h, C.byref(o), C.byref(self.h)))
         fs._solvers.append(weakref.ref(self))
 
@@ -578,6 +584,10 @@ class LinearSolver:
 
     def set_pressure_rhs(self, dt):
         _chk(self.L.fsgpu_ps_set_rhs(self.h, dt))
+
+    def set_pressure_rhs_from_velocity(self, dt):
+        """calc_divergence + set_pressure_rhs in one pass (the kernel fsgpu_substep runs)"""
+        _chk(self.L.fsgpu_ps_set_rhs_from_velocity(self.h, dt))
 
     def solve(self):
         """-> (residual, num_iter); the solution is field DELTA_P"""

@@ -193,6 +193,9 @@ int fsgpu_shift_pressure_to_zero(fsgpu_ctx* c);
 /* the driver-inlined projection, scaling/LidDrivenFlow.cpp:153-160 and, for variable density,
  * test/LaminarChannel.cpp:222-233: p += delta_p; U,V -= grad(delta_p)*dt/rho on interior faces */
 int fsgpu_correct_velocity(fsgpu_ctx* c, double dt);
+/* the three driver lines shift_pressure_to_zero + p += delta_p + velocity correction in one pass (what
+ * fsgpu_substep runs); FSGPU_DELTA_P holds the shifted field afterwards, FSGPU_RHS is scratch */
+int fsgpu_project(fsgpu_ctx* c, double dt);
 /* abs_max(field) = abs_max<INCLUDE_GHOST = false>, src/Utility.hpp:44-88: the maximum over the
  * field's INTERIOR entries (what every driver's monitor row uses); fsgpu_abs_max_all is
  * abs_max<true>(field), the whole ghost-inclusive extent */
@@ -268,6 +271,13 @@ typedef struct {
   int relax;      /* FSGPU_RELAX_*; 0 = default (Jacobi, the reference's configuration) */
   int max_levels; /* 0 = default 16 = PS_PFMG_MAX_LEVELS (src/LinearSolver_StructHypre.hpp:221) */
   int skip_relax; /* -1 = default (1, HYPRE's pfmg.c:38); 0/1 */
+  int no_diag_snap; /* 0 = default: a coarse-grid diagonal that is pure cancellation noise (|d| <= 1e-13 * sum of the
+                       magnitudes of its terms) is stored as exactly 0, so that the zero-diagonal test of
+                       pfmg_setup.c:349-361 fires on the one-point coarsest grid of a singular (all-Neumann)
+                       operator whatever the rounding.  A DELIBERATE deviation from HYPRE, which tests the rounded
+                       value: with non-dyadic coefficients HYPRE divides by ~1e-16 there and stalls or breaks down
+                       (the oracle has the same switch, oracle/fs_oracle.h snap_zero_diag).
+                       1 = HYPRE's arithmetic as is. */
 } fsgpu_ps_opts;
 int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out);
 int fsgpu_ps_destroy(fsgpu_ps* s);
@@ -277,6 +287,9 @@ int fsgpu_ps_set_operator(fsgpu_ps* s);
 /* set_pressure_rhs(fs, div, dt), src/LinearSolver_StructHypre.hpp:109-116 (+ LinearSystem.hpp:125-155);
  * reads FSGPU_DIV, writes FSGPU_RHS */
 int fsgpu_ps_set_rhs(fsgpu_ps* s, double dt);
+/* calc_divergence + set_pressure_rhs in one pass over curr.U, curr.V (what fsgpu_substep runs): writes
+ * FSGPU_DIV and FSGPU_RHS; same arithmetic as the two separate calls */
+int fsgpu_ps_set_rhs_from_velocity(fsgpu_ps* s, double dt);
 /* solve(delta_p, &residual, &num_iter), src/LinearSolver_StructHypre.hpp:119-192 -> FSGPU_DELTA_P.
  * Non-convergence is not an error (the reference only warns, :177-183): returns 0 with
  * *iters == max_iter and *residual >= tol. */

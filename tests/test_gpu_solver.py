@@ -6,6 +6,12 @@ counts and solutions to ~1e-14.  The GPU solver runs the same algorithm, so here
   * iteration count equal to the oracle's, reported residual < tol (same norm, pcg.c:1016),
   * solution (mean removed, pressure is defined up to a constant) within 1e-10 relative L2,
   * U, V, p - mean after N timesteps within 1e-10 relative L2 (north_star's tolerance).
+
+Coarse-diagonal guard: the product stores a coarse-grid diagonal that is pure cancellation noise as exactly 0
+(fsgpu_ps_opts.no_diag_snap = 0, the default; a deliberate deviation from HYPRE, include/fsgpu.h), so the oracle
+side of every comparison here runs with its identical switch, snap_zero_diag = 1.  test_diag_snap_option pins both
+settings; tests/test_oracle.py pins the oracle WITH the guard against the unmodified reference at solver tolerance
+(test_ib_channel_steps_vs_golden) and WITHOUT it iteration for iteration.
 """
 import numpy as np
 import pytest
@@ -48,7 +54,7 @@ def test_solve_matches_oracle(F, oracle, name, kw, drop, tol):
     bc = cavity_bc()
     dt = 1e-2
     fs, op, rhs = _setup(oracle, F, st, bc, dt)
-    so = oracle.solver(st.nx, st.ny, tol=tol, max_iter=200)
+    so = oracle.solver(st.nx, st.ny, tol=tol, max_iter=200, snap_zero_diag=1)
     so.set_operator(op)
     sol, res_o, it_o = so.solve(rhs)
     ps = F.LinearSolver(fs, tol=tol, max_iter=200)
@@ -77,7 +83,7 @@ def test_truncated_hierarchy(F, oracle, max_levels):
     reference rebuilt with -DPS_PFMG_MAX_LEVELS (tests/test_oracle.py)."""
     st = cavity_state(oracle, seed=2, nx=96, ny=72)
     fs, op, rhs = _setup(oracle, F, st, cavity_bc(), 1e-2)
-    so = oracle.solver(st.nx, st.ny, tol=1e-10, max_iter=300, max_levels=max_levels)
+    so = oracle.solver(st.nx, st.ny, tol=1e-10, max_iter=300, max_levels=max_levels, snap_zero_diag=1)
     so.set_operator(op)
     sol, res_o, it_o = so.solve(rhs)
     ps = F.LinearSolver(fs, tol=1e-10, max_iter=300, max_levels=max_levels)
@@ -87,6 +93,47 @@ def test_truncated_hierarchy(F, oracle, max_levels):
     res_g, it_g = ps.solve()
     dp = fs.download("DELTA_P")
     assert it_g == it_o and res_g == pytest.approx(res_o, rel=1e-3), (it_g, it_o, res_g, res_o)
+    assert rel_l2(dp - dp.mean(), sol - sol.mean()) <= TOL_FIELD
+    ps.close()
+    fs.close()
+
+
+def test_diag_snap_option(F, oracle):
+    """both settings of the coarse-diagonal guard against the oracle's identical switch.  Dyadic coefficients
+    (cavity 64^2: the one-point coarsest diagonal is an exact 0 in HYPRE's arithmetic) -> the guard changes
+    nothing; TGV 32^2 (dx = 2 pi / 32): HYPRE's arithmetic leaves ~1e-16 there, divides by it and stalls near 1e-8,
+    with the guard the same solve converges"""
+    st = cavity_state(oracle, seed=4, nx=64, ny=64)
+    fs, op, rhs = _setup(oracle, F, st, cavity_bc(), 1e-2)
+    out = []
+    for snap in (1, 0):
+        so = oracle.solver(64, 64, tol=1e-10, max_iter=200, snap_zero_diag=snap)
+        so.set_operator(op)
+        sol, res_o, it_o = so.solve(rhs)
+        ps = F.LinearSolver(fs, tol=1e-10, max_iter=200, no_diag_snap=1 - snap)
+        ps.set_pressure_operator()
+        ps.set_pressure_rhs(1e-2)
+        res_g, it_g = ps.solve()
+        dp = fs.download("DELTA_P")
+        assert it_g == it_o and res_g < 1e-10
+        assert rel_l2(dp - dp.mean(), sol - sol.mean()) <= TOL_FIELD
+        out.append((it_g, dp))
+        ps.close()
+    assert out[0][0] == out[1][0] and np.array_equal(out[0][1], out[1][1])
+    fs.close()
+    st = tgv_state(oracle, 32)
+    rng = np.random.default_rng(8)
+    st.a["U"][:] += 0.05 * rng.uniform(-1, 1, st.a["U"].shape)
+    fs, op, rhs = _setup(oracle, F, st, periodic_bc(), 1e-2)
+    so = oracle.solver(32, 32, tol=1e-12, max_iter=200, snap_zero_diag=1)
+    so.set_operator(op)
+    sol, res_o, it_o = so.solve(rhs)
+    ps = F.LinearSolver(fs, tol=1e-12, max_iter=200)
+    ps.set_pressure_operator()
+    ps.set_pressure_rhs(1e-2)
+    res_g, it_g = ps.solve()
+    dp = fs.download("DELTA_P")
+    assert res_o < 1e-12 and res_g < 1e-12 and abs(it_g - it_o) <= 1, (res_o, res_g, it_o, it_g)
     assert rel_l2(dp - dp.mean(), sol - sol.mean()) <= TOL_FIELD
     ps.close()
     fs.close()
@@ -155,7 +202,7 @@ def test_dirichlet_side(F, oracle):
     bc = BConds(kind=(NEUMANN,) * 4)
     dt, tol = 1e-2, 1e-12
     fs, op, rhs = _setup(oracle, F, st, bc, dt, PSD_RIGHT)
-    so = oracle.solver(st.nx, st.ny, tol=tol, max_iter=300)
+    so = oracle.solver(st.nx, st.ny, tol=tol, max_iter=300, snap_zero_diag=1)
     so.set_operator(op)
     sol, res_o, it_o = so.solve(rhs)
     ps = F.LinearSolver(fs, tol=tol, max_iter=300, psd=PSD_RIGHT)
@@ -181,7 +228,9 @@ STEP_CASES = [
 @pytest.mark.parametrize("name,kind,n,nsub,flags", STEP_CASES, ids=[c[0] for c in STEP_CASES])
 def test_timesteps_match_oracle(F, oracle, name, kind, n, nsub, flags):
     """N whole timesteps (adjust_dt, save_old_state, NUM_SUBITER projection sub-iterations) with
-    both sides solving to 1e-13: fields within 1e-10 relative L2."""
+    both sides solving to 1e-13: fields within 1e-10 relative L2.  The projection inside
+    fsgpu_step takes the integral of delta_p from the solver's last x update (no summation pass): the MEAN of p,
+    which the mean-removed comparison cannot see, is asserted on its own."""
     tol, max_iter, nsteps = 1e-13, 500, 4
     if kind == "tgv":
         st, bc, cfl, dtmax = tgv_state(oracle, n), periodic_bc(), 0.5, 1e-2
@@ -195,7 +244,7 @@ def test_timesteps_match_oracle(F, oracle, name, kind, n, nsub, flags):
         st, bc, cfl, dtmax = cavity_state(oracle, n, n, drop=True, seed=1), cavity_bc(), 0.9, 0.1
     oracle.apply_velocity_bconds(st, bc)
     fs = to_gpu(F, st, bc)
-    so = oracle.solver(st.nx, st.ny, tol=tol, max_iter=max_iter)
+    so = oracle.solver(st.nx, st.ny, tol=tol, max_iter=max_iter, snap_zero_diag=1)
     so.set_operator(oracle.fill_pressure_operator(st))
     ps = F.LinearSolver(fs, tol=tol, max_iter=max_iter)
     ps.set_pressure_operator()
@@ -205,19 +254,22 @@ def test_timesteps_match_oracle(F, oracle, name, kind, n, nsub, flags):
         assert dt_g == pytest.approx(dt_o, rel=1e-9)
         it_o, res_o = oracle.step(st, bc, so, dt_o, nsub, outflow_fix=flags & 1, rebuild=(flags >> 1) & 1)
         res_g, it_g = fs.step(ps, dt_o, nsub, flags)
-        # cavity / drop converge to the requested 1e-13.  On the TGV and channel systems the
-        # REFERENCE's PCG+PFMG itself stalls at a relative residual of ~1e-8 (rounding floor of
-        # those all-Neumann systems; HYPRE exits on its breakdown test) and so does the same
-        # algorithm here: the residual must be no worse than the oracle's floor.
+        # tgv / cavity / drop converge to the requested 1e-13 (tgv only with the coarse-diagonal guard both sides
+        # run with: HYPRE's own arithmetic stalls near 1e-8 there).  On the channel system the rhs itself is at
+        # rounding level (uniform flow, div ~ 1e-16) and the REFERENCE's PCG+PFMG exits on its breakdown test at
+        # a relative residual of ~1e-8; so does the same algorithm here: no worse than the oracle's floor.
         assert res_g < max(1e-12, 20 * res_o), (res_g, res_o)
-        if kind in ("cavity", "drop"):  # at the floor the exit iteration is decided by rounding
+        if kind != "channel":  # at the floor the exit iteration is decided by rounding
             assert abs(it_g - it_o) <= max(nsub, 0.35 * it_o), (it_g, it_o)
-    floor = kind in ("tgv", "channel")
     ev = vel_err(fs.download("U"), fs.download("V"), st.U, st.V)
     p_g, p_o = fs.download("P"), st.a["p"]
     ep = rel_l2(p_g - p_g.mean(), p_o - p_o.mean())
-    print(f"\n[{name}] velocity rel L2 {ev:.3e}, pressure (mean removed) rel L2 {ep:.3e}, last residual {res_g:.2e}")
-    assert ev <= (1e-7 if kind == "tgv" else TOL_FIELD)
-    assert ep <= (1e-5 if kind == "tgv" else 1e-8)
+    em = abs(p_g.mean() - p_o.mean()) / max(np.abs(p_o).max(), 1e-300)
+    print(f"\n[{name}] velocity rel L2 {ev:.3e}, pressure (mean removed) rel L2 {ep:.3e}, mean of p {em:.3e} of max|p|, "
+          f"last residual {res_g:.2e} (oracle {res_o:.2e}), iterations {it_g} (oracle {it_o})")
+    assert ev <= TOL_FIELD
+    assert ep <= 1e-8
+    if kind != "channel":
+        assert em <= 1e-8
     ps.close()
     fs.close()

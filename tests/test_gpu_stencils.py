@@ -128,6 +128,90 @@ def test_divergence_rhs(F, oracle, nx, ny, psd):
     fs.close()
 
 
+@pytest.mark.parametrize("nx,ny", SIZES)
+@pytest.mark.parametrize("psd", [PSD_NONE, PSD_LEFT, PSD_RIGHT, PSD_BOTTOM, PSD_TOP])
+def test_fused_divergence_rhs(F, oracle, nx, ny, psd):
+    """k_rhs<true> (fsgpu_ps_set_rhs_from_velocity): calc_divergence + fill_pressure_rhs in ONE pass over U, V --
+    the kernel fsgpu_substep and bench.py run -- against the two reference calls (src/Operators.hpp:32-41,
+    src/LinearSystem.hpp:125-155), all five PSDirichlet sides"""
+    st = random_state(nx, ny, seed=15)
+    fs = to_gpu(F, st)
+    dt = 7e-3
+    div = oracle.calc_divergence(st)
+    rhs = oracle.fill_pressure_rhs(st, div, dt, psd)
+    ps = F.LinearSolver(fs, psd=psd)
+    ps.set_pressure_rhs_from_velocity(dt)
+    assert rel_inf(fs.download("DIV"), div) <= TOL
+    assert rel_inf(fs.download("RHS"), rhs.T) <= TOL
+    ps.close()
+    fs.close()
+
+
+@pytest.mark.parametrize("nx,ny", SIZES)
+@pytest.mark.parametrize("ratio", [1.0, 1000.0])
+def test_fused_projection(F, oracle, nx, ny, ratio):
+    """k_project<true> (fsgpu_project): shift_pressure_to_zero + p += delta_p + the velocity correction in ONE pass
+    -- the kernel fsgpu_substep and bench.py run -- against the three driver lines (src/Operators.hpp:78-82,
+    test/LaminarChannel.cpp:222-233) on a delta_p with a large mean"""
+    st = random_state(nx, ny, seed=19 + nx, rho_ratio=ratio)
+    rng = np.random.default_rng(nx + ny)
+    dp = rng.uniform(-1, 1, (nx + 2, ny + 2)) + 3.0
+    fs = to_gpu(F, st)
+    fs.upload("DELTA_P", dp)
+    dt = 5e-3
+    oracle.shift_pressure_to_zero(st, dp)
+    oracle.correct(st, dp, dt)
+    fs.project(dt)
+    assert rel_inf(fs.download("DELTA_P"), dp) <= TOL
+    for n in ("U", "V", "P"):
+        assert rel_inf(fs.download(n), st.a[n.lower() if n == "P" else n]) <= TOL, n
+    # twice in a row: the delta_p / rhs buffer swap must leave a usable pair behind
+    dp2 = rng.uniform(-1, 1, (nx + 2, ny + 2))
+    fs.upload("DELTA_P", dp2)
+    oracle.shift_pressure_to_zero(st, dp2)
+    oracle.correct(st, dp2, dt)
+    fs.project(dt)
+    assert rel_inf(fs.download("DELTA_P"), dp2) <= TOL
+    for n in ("U", "V", "P"):
+        assert rel_inf(fs.download(n), st.a[n.lower() if n == "P" else n]) <= TOL, n
+    fs.close()
+
+
+@pytest.mark.parametrize("ratio", [1.0, 1000.0])
+@pytest.mark.parametrize("psd", [PSD_NONE, PSD_LEFT, PSD_RIGHT, PSD_BOTTOM, PSD_TOP])
+def test_substep_kernel_chain(F, oracle, ratio, psd):
+    """every output of the kernel chain fsgpu_substep launches (and bench.py times), in its order, on the random
+    density-jump state: k_momentum<1> -> BCs -> k_rhs<true> -> [solve] -> k_project<true>"""
+    nx, ny = 66, 50
+    st = random_state(nx, ny, seed=23, rho_ratio=ratio)
+    bc = BConds(kind=(DIRICHLET, NEUMANN, DIRICHLET, SYMMETRY), u_val=(1.0, 0, 0, 0.5), v_val=(0.1, 0, 0, 0))
+    oracle.apply_velocity_bconds(st, bc)
+    fs = to_gpu(F, st, bc)
+    dt = 2e-3
+    oracle.calc_mid_time(st)
+    dU, dV = oracle.calc_dmomdt(st)
+    oracle.update_velocity(st, dU, dV, dt)
+    oracle.apply_velocity_bconds(st, bc)
+    fs.momentum_update(dt)
+    fs.apply_velocity_bconds()
+    assert rel_inf(fs.download("U"), st.U) <= TOL and rel_inf(fs.download("V"), st.V) <= TOL
+    div = oracle.calc_divergence(st)
+    rhs = oracle.fill_pressure_rhs(st, div, dt, psd)
+    ps = F.LinearSolver(fs, psd=psd)
+    ps.set_pressure_rhs_from_velocity(dt)
+    assert rel_inf(fs.download("DIV"), div) <= TOL
+    assert rel_inf(fs.download("RHS"), rhs.T) <= TOL
+    dp = np.random.default_rng(3).uniform(-1, 1, (nx + 2, ny + 2))
+    fs.upload("DELTA_P", dp)
+    oracle.shift_pressure_to_zero(st, dp)
+    oracle.correct(st, dp, dt)
+    fs.project(dt)
+    for n in ("U", "V", "P"):
+        assert rel_inf(fs.download(n), st.a[n.lower() if n == "P" else n]) <= TOL, n
+    ps.close()
+    fs.close()
+
+
 def test_shift_and_correct(F, oracle):
     nx, ny = 50, 34
     st = random_state(nx, ny, seed=9)

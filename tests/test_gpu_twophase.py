@@ -138,7 +138,7 @@ def test_twophase_timesteps(F, oracle):
     st, bc, cap = _twophase_case(oracle)
     fs = _twophase_gpu(F, st, bc, cap)
     flags = F.STEP_REBUILD_OPERATOR | F.STEP_DENSITY | F.STEP_CAPILLARY
-    so = oracle.solver(st.nx, st.ny, tol=1e-13, max_iter=500)
+    so = oracle.solver(st.nx, st.ny, tol=1e-13, max_iter=500, snap_zero_diag=1)
     so.set_operator(oracle.fill_pressure_operator(st))
     ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
     ps.set_pressure_operator()
