@@ -66,7 +66,7 @@ COMM_ID_BYTES = 128
 
 class PsOpts(C.Structure):
     _fields_ = [("tol", C.c_double), ("max_iter", C.c_int), ("psd", C.c_int), ("relax", C.c_int),
-                ("max_levels", C.c_int), ("skip_relax", C.c_int), ("no_diag_snap", C.c_int)]
+                ("max_levels", C.c_int), ("skip_relax", C.c_int)]
 
 
 class FsgpuError(RuntimeError):
@@ -561,10 +561,10 @@ class LinearSolver:
     """``LinearSolver_StructHypre<Float,NX,NY,1>`` (src/LinearSolver_StructHypre.hpp:28-192)."""
 
     def __init__(self, fs: FS, tol=1e-6, max_iter=50, psd=PSD_NONE, relax=0, max_levels=0,
-                 skip_relax=-1, no_diag_snap=0):
+                 skip_relax=-1):
         self.fs, self.L = fs, fs.L
         self.h = C.c_void_p()
-        o = PsOpts(tol, max_iter, psd, relax, max_levels, skip_relax, no_diag_snap)
+        o = PsOpts(tol, max_iter, psd, relax, max_levels, skip_relax)
         _chk(self.L.fsgpu_ps_create(fs.h, C.byref(o), C.byref(self.h)))
         fs._solvers.append(weakref.ref(self))
 

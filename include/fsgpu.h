@@ -263,7 +263,15 @@ int fsgpu_monitor(fsgpu_ctx* c, double* u_max, double* v_max, double* div_max);
 /* ---- pressure solver = `LinearSolver_StructHypre<Float,NX,NY,1>` -------------------------------
  * constructor (src/LinearSolver_StructHypre.hpp:43-62): tol, max_iter, PSDirichlet.  The solver
  * is always PCG preconditioned by one PFMG-style V-cycle (the reference's default
- * HypreSolver::PCG + HyprePrecond::PFMG, :31-32). */
+ * HypreSolver::PCG + HyprePrecond::PFMG, :31-32).
+ * One DELIBERATE deviation from HYPRE's arithmetic: a coarse-grid diagonal that is pure cancellation noise
+ * (|d| <= 1e-13 * sum of the magnitudes of its terms) is stored as exactly 0, so that the zero-diagonal test of
+ * pfmg_setup.c:349-361 fires on the one-point coarsest grid of a singular (all-Neumann) operator whatever the
+ * rounding.  HYPRE tests the rounded value: exact with dyadic coefficients, ~1e-16 otherwise, which it then
+ * divides by (TGV: PCG stalls near 1e-8; IB channel: breakdown).  The setup here (symmetric 3-array storage,
+ * reciprocal interpolation weights) is not bit-identical to HYPRE's, so it cannot inherit HYPRE's exact zeros
+ * either.  The oracle has the same guard as a switch (oracle/fs_oracle.h snap_zero_diag), pinned against the
+ * unmodified reference with and without it. */
 typedef struct {
   double tol;
   int max_iter;
@@ -271,13 +279,6 @@ typedef struct {
   int relax;      /* FSGPU_RELAX_*; 0 = default (Jacobi, the reference's configuration) */
   int max_levels; /* 0 = default 16 = PS_PFMG_MAX_LEVELS (src/LinearSolver_StructHypre.hpp:221) */
   int skip_relax; /* -1 = default (1, HYPRE's pfmg.c:38); 0/1 */
-  int no_diag_snap; /* 0 = default: a coarse-grid diagonal that is pure cancellation noise (|d| <= 1e-13 * sum of the
-                       magnitudes of its terms) is stored as exactly 0, so that the zero-diagonal test of
-                       pfmg_setup.c:349-361 fires on the one-point coarsest grid of a singular (all-Neumann)
-                       operator whatever the rounding.  A DELIBERATE deviation from HYPRE, which tests the rounded
-                       value: with non-dyadic coefficients HYPRE divides by ~1e-16 there and stalls or breaks down
-                       (the oracle has the same switch, oracle/fs_oracle.h snap_zero_diag).
-                       1 = HYPRE's arithmetic as is. */
 } fsgpu_ps_opts;
 int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out);
 int fsgpu_ps_destroy(fsgpu_ps* s);

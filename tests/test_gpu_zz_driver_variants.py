@@ -95,8 +95,10 @@ def test_dirichlet_profiles_vs_reference_golden(F):
 @pytest.mark.parametrize("psd", [1, 2, 3, 4])
 def test_solve_with_dirichlet_side_vs_reference_golden(F, oracle, psd):
     """PSDirichlet LEFT / RIGHT / BOTTOM / TOP (src/LinearSystem.hpp:10,32-155) on the rho-ratio-1000
-    drop with all-Neumann velocity BCs (test/StationaryDrop.cpp:67-72,223-224): same iteration count and
-    solution as HYPRE"""
+    drop with all-Neumann velocity BCs (test/StationaryDrop.cpp:67-72,223-224): the solution HYPRE finds.  The
+    reference keeps the coupling of the neighbouring row TO the identity row (a non-symmetric matrix, which PCG is not
+    built for); the product eliminates that column as well (same solution, symmetric operator, csrc/solver_setup.cu
+    k_build_l0) and must not need more iterations than HYPRE: measured 21 against 25 / 23 / 21 / 21"""
     from cases import cavity_state
     from oracle_lib import BConds, NEUMANN
     g = np.load(os.path.join(GOLD, "solve_psd128.npz"))
@@ -112,7 +114,7 @@ def test_solve_with_dirichlet_side_vs_reference_golden(F, oracle, psd):
     dp = fs.download("DELTA_P")
     print(f"\n[PSDirichlet {psd}] its gpu {it} reference {int(g[f'it{psd}'])}, residual {res:.2e}, "
           f"rel L2 {rel_l2(dp, g[f'dp{psd}']):.2e}")
-    assert res < 1e-10 and abs(it - int(g[f"it{psd}"])) <= 1
+    assert res < 1e-10 and 0.7 * int(g[f"it{psd}"]) <= it <= int(g[f"it{psd}"]) + 1
     assert rel_l2(dp, g[f"dp{psd}"]) <= 1e-8
     ps.close()
     fs.close()
