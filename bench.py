@@ -33,7 +33,12 @@ os.environ.setdefault("OMP_PROC_BIND", "close")
 os.environ.setdefault("OMP_PLACES", "cores")
 
 NSUB, TOL, MAX_ITER, CFL, DT_MAX = 5, 1e-6, 50, 0.9, 0.1
-CPU_SAMPLE_N = int(os.environ.get("FSBENCH_CPU_N", "2048"))  # grid of the bounded CPU sample (reference instantiation in ref_harness_sizes.inc)
+# The CPU legs run the SAME configuration as the GPU arm: the 8192^2 cavity (the reference
+# harness instantiates it, oracle/ref_harness_sizes.inc).  Bounded in the number of timesteps, not in the grid:
+# CPU_WARMUP warm-up + CPU_STEPS timed timesteps (a timestep takes the host tens of seconds).  FSBENCH_CPU_N
+# overrides the grid for quick local runs only.
+CPU_SAMPLE_N = int(os.environ.get("FSBENCH_CPU_N", "8192"))
+CPU_STEPS, CPU_WARMUP = int(os.environ.get("FSBENCH_CPU_STEPS", "2")), 1
 
 
 def parse():
@@ -49,6 +54,7 @@ def parse():
     ap.add_argument("--no-ref-depth", action="store_true", help="skip the secondary 16-level measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-anchor", action="store_true", help="N > 1: skip the 1-GPU timing of the same grid")
     ap.add_argument("--halo", default="", choices=["", "nccl", "p2p"],
                     help="N > 1: p2p = halo rows and scalar reductions through peer-mapped mailboxes (sets FSGPU_HALO)")
     ap.add_argument("--prof", default="", help="kernel class to time for the roofline (default: auto)")
@@ -97,7 +103,7 @@ class ClockSampler:
 # ---- the CPU leg: the UNMODIFIED reference (oracle/_ref/libfsref.so), else the C oracle --------
 def cpu_leg(steps, warmup, n=CPU_SAMPLE_N):
     """Times the reference's own OpenMP + HYPRE path on this box's host cores for the same
-    workload at n^2 (a bounded sample: the 8192^2 step takes the CPU about a minute)."""
+    workload and grid as the GPU arm (bounded in the number of timesteps)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import numpy as np  # noqa: F401
     from cases import cavity_bc, cavity_state
@@ -142,6 +148,39 @@ def cpu_leg(steps, warmup, n=CPU_SAMPLE_N):
             "ms_per_step": el / steps * 1e3}
 
 
+def single_gpu_anchor(F, torch, n, dev, max_levels, steps=3):
+    """The whole n^2 cavity on ONE GPU with the settings of the timed run: the 1-GPU point of the strong-scaling
+    curve on the same problem (16384^2 needs ~66 GB of the 180 GB)."""
+    try:
+        fs = F.FS(n, n, 1.0 / n, 1.0 / n, 1.0, 1.0, 1e-3, 1e-3, device=dev)
+        fs.calc_rho_visc_const()
+        for s, u in enumerate((0.0, 0.0, 0.0, 1.0)):
+            fs.set_bconds(s, F.DIRICHLET, u, 0.0)
+        fs.apply_velocity_bconds()
+        ps = F.LinearSolver(fs, tol=TOL, max_iter=MAX_ITER, max_levels=max_levels)
+        ps.set_pressure_operator()
+        stream = torch.cuda.ExternalStream(fs.stream(), device=torch.device("cuda", dev))
+        fs.step(ps, fs.adjust_dt(CFL, DT_MAX), NSUB)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        fs.sync()
+        e0.record(stream)
+        its = 0
+        for _ in range(steps):
+            its += fs.step(ps, fs.adjust_dt(CFL, DT_MAX), NSUB)[1]
+        e1.record(stream)
+        fs.sync()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        umax = fs.abs_max("U")
+        ps.close()
+        fs.close()
+        return {"n_gpus": 1, "grid": n, "value": n * n * steps / (ms * 1e-3) / 1e6, "unit": "MCell-updates/s",
+                "ms_per_step": ms / steps, "steps": steps, "warmup": 1,
+                "pcg_iters_per_solve": its / (steps * NSUB), "max_abs_U_after_4_steps": umax}
+    except Exception as e:  # e.g. a grid that does not fit one GPU
+        return {"n_gpus": 1, "grid": n, "unavailable": str(e)[:200]}
+
+
 # ---- algorithmic bytes per cell of each kernel class (DESIGN.md "Kernels and rooflines") -------
 # doubles moved once per launch by the algorithm as implemented (8 B each), per fine-level cell
 ALGO_BYTES = {
@@ -165,13 +204,18 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return 0
-        cb = cpu_leg(max(a.steps, 1), min(a.warmup, 1))
+        # same grid and constants as the GPU arm; the timed steps are capped (each costs the host tens of
+        # seconds) and the counts actually run are the ones reported
+        ks, kw = max(1, min(a.steps, CPU_STEPS)), min(a.warmup, CPU_WARMUP)
+        cb = cpu_leg(ks, kw)
         line = {"impl": "reference", "metric": "timestep MCell-updates/s (FP64, incl. Poisson solve)",
-                "value": cb["value"], "unit": "MCell-updates/s", "n_gpus": n_gpus, "steps": a.steps,
-                "warmup": min(a.warmup, 1), "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+                "value": cb["value"], "unit": "MCell-updates/s", "n_gpus": n_gpus, "steps": ks,
+                "warmup": kw, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"lid-driven cavity (scaling/LidDrivenFlow.cpp constants), bounded sample "
-                                       f"{CPU_SAMPLE_N}^2 of the 8192^2 workload, NUM_SUBITER {NSUB}, PCG+PFMG tol {TOL}"},
+                "config": {"workload": f"lid-driven cavity {CPU_SAMPLE_N}^2 (scaling/LidDrivenFlow.cpp:16-42), NUM_SUBITER {NSUB}, "
+                                       f"PCG tol {TOL} max_iter {MAX_ITER}, CFL {CFL}",
+                           "solver": "the reference's own: HYPRE Struct PCG + PFMG, PS_PFMG_MAX_LEVELS 16",
+                           "steps_requested": a.steps, "warmup_requested": a.warmup},
                 "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": cb["value"], "unit": "MCell-updates/s", "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": 0},
@@ -201,6 +245,14 @@ def main():
     # N > 1: configs[4], the 16384^2 strong-scaling case, slab-decomposed over the N GPUs
     n = a.n or (8192 if world == 1 else 16384)
 
+    # N > 1: the same-problem anchor of the scaling curve -- rank 0 alone runs the WHOLE n^2 grid on its one GPU
+    # (same solver settings, 1 warm-up + 3 timed steps) before the slabs are created; the others wait.
+    anchor = None
+    if world > 1 and not a.no_anchor:
+        if rank == 0:
+            anchor = single_gpu_anchor(F, torch, n, local, max(a.max_levels, 0))
+        dist.barrier()
+
     fs = F.FS(n, n, 1.0 / n, 1.0 / n, 1.0, 1.0, 1e-3, 1e-3, device=local, rank=rank, nranks=world,
               comm_id=comm_id)
     fs.calc_rho_visc_const()
@@ -227,7 +279,8 @@ def main():
     F.prof_enable((prof_cls,))
     F.prof_read()
     clocks = ClockSampler(local)
-    clocks.start()
+    if rank == 0:  # one poller per job: N pollers contend for the driver lock beside the kernels they time
+        clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     fs.sync()
     torch.cuda.synchronize()
@@ -366,7 +419,7 @@ def main():
 
     cpu = None
     if rank == 0 and n_gpus == 1 and not a.no_cpu:
-        cpu = cpu_leg(2, 1)
+        cpu = cpu_leg(CPU_STEPS, CPU_WARMUP)
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
 
     line = {"metric": "timestep MCell-updates/s (FP64, incl. Poisson solve)", "value": value,
@@ -377,7 +430,7 @@ def main():
                                    f"PCG tol {TOL} max_iter {MAX_ITER}, CFL {CFL}",
                        "pcg_iters_per_solve": k_bar, "mg_levels": levels[0],
                        "mg_depth": "uncapped (coarsest grid = 1 point)" if a.max_levels >= 40 else f"capped at {a.max_levels}",
-                       "reference_depth_16": ref_depth,
+                       "reference_depth_16": ref_depth, "same_problem_1gpu": anchor,
                        "decomposition": None if world == 1 else
                        f"{world} slabs of i-rows, " + ("mailbox (peer-mapped, one kernel per exchange) halo exchange + scalar "
                                                      "all-reduce, NCCL for large reductions" if direct else

@@ -145,6 +145,9 @@ int fsgpu_create_slab(int64_t nx, int64_t ny, double dx, double dy, int device, 
   for (int f = 0; f < FSGPU_NUM_CORE_FIELDS; ++f) c->f[f] = c->slab + n * f - c->g.voff();
   c->U_alt = c->slab + n * FSGPU_NUM_CORE_FIELDS - c->g.voff();
   c->V_alt = c->slab + n * (FSGPU_NUM_CORE_FIELDS + 1) - c->g.voff();
+  // block partials of every grid-wide reduction: the persistent grids are <= 148 x 8 CTAs x 4 values, so
+  // the hot path never allocates (fs_ensure_part only grows it for a larger request)
+  if (fs_ensure_part(c, (size_t)FS_NUM_SMS * 8 * 4 * 2)) { fsgpu_destroy(c); return 1; }
   FS_CUDA(cudaMalloc(&c->ticket, sizeof(unsigned int)));
   FS_CUDA(cudaMemsetAsync(c->ticket, 0, sizeof(unsigned int), c->stream));
   FS_CUDA(cudaMalloc(&c->red_out, 16 * sizeof(double)));
@@ -532,6 +535,7 @@ int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out) {
     std::lock_guard<std::mutex> lk(g_live_mu);
     g_live_solvers.insert(s);
   }
+  if (comm_alloc_fence(c)) return 1;
   *out = s;
   return 0;
 }

@@ -18,6 +18,7 @@
 //                          (partitioning, halo widths, replicated coarse levels, reductions) can be
 //                          tested bit for bit on a single-GPU box.
 #include "ctx.h"
+#include "p2p.cuh"
 
 #include <dlfcn.h>
 #include <stdio.h>
@@ -133,20 +134,16 @@ struct LocalGroup {
   }
 };
 // ---- direct halo exchange through peer-mapped mailboxes (FSGPU_HALO=p2p) ---------------------------
-// Every rank owns one device allocation, its MAILBOX, that its two neighbours map (cudaIpc between
-// processes, plain pointers inside one process):
-//   byte 0   : flag[0]  last epoch whose rows from rank - 1 are complete       (own 128-byte line)
-//   byte 128 : flag[1]  ... from rank + 1
-//   byte 192 : arrive counter of the local exchange kernel
-//   byte 200 : device copy of the error flag (the kernels test this one: no PCIe read per exchange)
-//   byte 256 : 4 slots of `cap` doubles: (side 0 | side 1) x (epoch parity 0 | 1)
+// Every rank owns one device allocation, its MAILBOX, that the other ranks map (layout: p2p.cuh).
 // One exchange = ONE kernel per rank on the context's stream: (A) store my boundary rows straight
 // into the neighbours' slots over NVLink, fence, the last CTA to arrive raises the neighbours' flags
 // to the epoch number; (B) wait for my own flags to reach the epoch, copy my slots into my halo rows.
 // No host round trip, no NCCL launch.  Two slots per side are enough: a rank can only start epoch
 // e + 2 after finishing e + 1, which needed the neighbour's flag e + 1, which the neighbour raises
 // after its epoch-e kernel (including the unpacking of slot e & 1) has completed in stream order.
-// The waits are bounded (a peer that never arrives sets *err instead of hanging the GPU).
+// The waits are bounded (a peer that never arrives sets *err instead of hanging the GPU): FSGPU_P2P_TIMEOUT_S
+// seconds, default 20 -- long enough for any host-side skew between the ranks of one job (file output, a slower
+// setup), short enough that a dead peer surfaces as an error at the next call that returns a scalar.
 struct HaloP2PArgs {
   double* ptr[4];
   int n, h;
@@ -155,6 +152,7 @@ struct HaloP2PArgs {
   size_t cap;            // doubles per slot
   unsigned long long e;  // epoch, counts exchanges from 1
   int* err;
+  long long timeout;     // clock64 ticks
 };
 __device__ __forceinline__ double* p2p_slot(char* base, int side, int par, size_t cap) {
   return reinterpret_cast<double*>(base + 256) + (size_t)(side * 2 + par) * cap;
@@ -198,10 +196,15 @@ k_halo_p2p(const HaloP2PArgs a) {
     const long long t0 = clock64();
     bool ok = true;
     while (ok && ((a.up && *p2p_flag(a.mine, 0) < a.e) || (a.dn && *p2p_flag(a.mine, 1) < a.e))) {
-      if (clock64() - t0 > 4000000000ll) ok = false;  // ~2 s
+      if (clock64() - t0 > a.timeout) ok = false;
     }
     if (!ok) {
-      *a.err = 1;  // mapped pinned memory: the host sees it at its next scalar read
+      if (blockIdx.x == 0) {  // mapped pinned memory: the host sees it at its next scalar read
+        a.err[1] = (int)a.e;
+        a.err[2] = a.up ? (int)*p2p_flag(a.mine, 0) : -1;
+        a.err[3] = a.dn ? (int)*p2p_flag(a.mine, 1) : -1;
+      }
+      *a.err = 1;
       *reinterpret_cast<volatile int*>(a.mine + 200) = 1;
     }
     __threadfence_system();
@@ -225,53 +228,47 @@ k_halo_p2p(const HaloP2PArgs a) {
 // values into slot [parity][its rank] of EVERY rank's reduce area and raises that rank's flag for it;
 // then it waits for all flags of this epoch and folds the slots in rank order -- the same order on
 // every rank, so the result is bitwise identical everywhere (what the PCG control flow relies on).
-// Area layout at mailbox offset red_off: flag[P2P_MAX_RANKS] (u64), then
-// values[2][P2P_MAX_RANKS][P2P_RED_MAX].
-constexpr int P2P_MAX_RANKS = 16, P2P_RED_MAX = 16;
+// The epoch lives in the mailbox (p2p.cuh): the PCG dot products run the same protocol from inside
+// their reduction kernels (p2p_allreduce_sum1) and advance the same counter.
 struct RedP2PArgs {
-  char* peer[P2P_MAX_RANKS];
+  P2PRedDev d;
   double* dev;
-  int n, rank, nranks, op;
-  size_t red_off;
-  unsigned long long e;
-  int* err;
+  int n, op;
 };
-__device__ __forceinline__ volatile unsigned long long* red_flag(char* base, size_t off, int src) {
-  return reinterpret_cast<volatile unsigned long long*>(base + off) + src;
-}
-__device__ __forceinline__ double* red_vals(char* base, size_t off, int par, int src) {
-  return reinterpret_cast<double*>(base + off + P2P_MAX_RANKS * sizeof(unsigned long long)) +
-         ((size_t)par * P2P_MAX_RANKS + src) * P2P_RED_MAX;
-}
 __global__ void __launch_bounds__(P2P_MAX_RANKS * P2P_RED_MAX)
 k_allreduce_p2p(const RedP2PArgs a) {
-  const int t = threadIdx.x, par = (int)(a.e & 1ull);
-  char* mine = a.peer[a.rank];
-  if (*reinterpret_cast<volatile int*>(mine + 200)) return;
-  if (t < a.nranks * a.n) {
+  const int t = threadIdx.x;
+  char* mine = a.d.peer[a.d.rank];
+  if (*p2p_dev_err(mine)) return;
+  __shared__ unsigned long long se;
+  if (t == 0) se = ++*p2p_red_epoch(mine);
+  __syncthreads();
+  const unsigned long long e = se;
+  const int par = (int)(e & 1ull);
+  if (t < a.d.nranks * a.n) {
     const int pr = t / a.n, q = t - pr * a.n;
-    red_vals(a.peer[pr], a.red_off, par, a.rank)[q] = a.dev[q];
+    p2p_red_vals(a.d.peer[pr], a.d.red_off, par, a.d.rank)[q] = a.dev[q];
   }
   __threadfence_system();
   __syncthreads();
-  if (t < a.nranks) {
+  if (t < a.d.nranks) {
     __threadfence_system();
-    *red_flag(a.peer[t], a.red_off, a.rank) = a.e;
+    *p2p_red_flag(a.d.peer[t], a.d.red_off, a.d.rank) = e;
     const long long t0 = clock64();
     bool ok = true;
-    while (ok && *red_flag(mine, a.red_off, t) < a.e)
-      if (clock64() - t0 > 4000000000ll) ok = false;  // ~2 s
+    while (ok && *p2p_red_flag(mine, a.d.red_off, t) < e)
+      if (clock64() - t0 > a.d.timeout) ok = false;
     if (!ok) {
-      *a.err = 1;
-      *reinterpret_cast<volatile int*>(mine + 200) = 1;
+      *a.d.err = 1;
+      *p2p_dev_err(mine) = 1;
     }
     __threadfence_system();
   }
   __syncthreads();
   if (t < a.n) {
-    double acc = __ldcg(red_vals(mine, a.red_off, par, 0) + t);
-    for (int r = 1; r < a.nranks; ++r) {
-      const double v = __ldcg(red_vals(mine, a.red_off, par, r) + t);
+    double acc = __ldcg(p2p_red_vals(mine, a.d.red_off, par, 0) + t);
+    for (int r = 1; r < a.d.nranks; ++r) {
+      const double v = __ldcg(p2p_red_vals(mine, a.d.red_off, par, r) + t);
       acc = a.op == COMM_MAX ? (acc > v ? acc : v) : acc + v;
     }
     a.dev[t] = acc;
@@ -287,8 +284,16 @@ struct P2PBox {
   std::vector<char*> peer;            // every rank's mailbox (peer[rank] == base)
   std::vector<char> ipc;              // mapped with cudaIpcOpenMemHandle (to be closed)
   size_t red_off = 0;                 // byte offset of the scalar all-reduce area
-  unsigned long long red_epoch = 0;
   int *h_err = nullptr, *d_err = nullptr;  // mapped pinned flag the kernel raises on a timeout
+  long long timeout = 0;              // clock64 ticks a device-side wait may last
+  P2PRedDev red{};                    // what the reduction kernels need (host copy)
+  P2PRedDev* d_red = nullptr;         // ... and its device copy (PcgScal::p2p)
+  // overlap: exchanges enqueued with comm_halo_async run on their own stream, fenced by two events
+  cudaStream_t xstream = nullptr;
+  cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
+  bool pending = false;
+  bool overlap = true;                // FSGPU_NO_OVERLAP unset (read when the context is created)
+  int64_t overlap_min_points = 262144;  // FSGPU_OVERLAP_MIN_POINTS: smaller slabs of a level exchange in stream order
 };
 std::map<std::string, std::shared_ptr<LocalGroup>> g_groups;
 std::mutex g_groups_mu;
@@ -326,9 +331,9 @@ static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
   b.ipc.assign((size_t)c->nranks, 0);
   if (cudaMalloc(&b.base, bytes) != cudaSuccess) { b.base = nullptr; ok = 0; }
   if (ok && cudaMemsetAsync(b.base, 0, bytes, c->stream) != cudaSuccess) ok = 0;
-  if (ok && cudaHostAlloc(&b.h_err, sizeof(int), cudaHostAllocMapped) != cudaSuccess) { b.h_err = nullptr; ok = 0; }
+  if (ok && cudaHostAlloc(&b.h_err, 4 * sizeof(int), cudaHostAllocMapped) != cudaSuccess) { b.h_err = nullptr; ok = 0; }
   if (ok) {
-    *b.h_err = 0;
+    for (int q = 0; q < 4; ++q) b.h_err[q] = 0;
     if (cudaHostGetDevicePointer(&b.d_err, b.h_err, 0) != cudaSuccess) ok = 0;
   }
   const int peer[2] = {c->rank - 1, c->rank + 1 < c->nranks ? c->rank + 1 : -1};
@@ -375,6 +380,23 @@ static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
       if (peer[sd] >= 0) b.nb[sd] = g.box[(size_t)peer[sd]];
     LOCAL_BARRIER(cm);
   }
+  if (ok) {
+    double secs = 20.0;
+    if (const char* e = getenv("FSGPU_P2P_TIMEOUT_S")) secs = atof(e) > 0.0 ? atof(e) : secs;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, c->device);
+    b.timeout = (long long)(secs * 1e3 * (khz > 0 ? khz : 2000000));
+    for (int r = 0; r < P2P_MAX_RANKS; ++r) b.red.peer[r] = r < c->nranks ? b.peer[(size_t)r] : nullptr;
+    b.red.rank = c->rank; b.red.nranks = c->nranks; b.red.red_off = b.red_off;
+    b.red.err = b.d_err; b.red.timeout = b.timeout;
+    FS_CUDA(cudaMalloc(&b.d_red, sizeof(P2PRedDev)));
+    FS_CUDA(cudaMemcpy(b.d_red, &b.red, sizeof(P2PRedDev), cudaMemcpyHostToDevice));
+    b.overlap = getenv("FSGPU_NO_OVERLAP") == nullptr;
+    if (const char* e = getenv("FSGPU_OVERLAP_MIN_POINTS")) b.overlap_min_points = atoll(e);
+    FS_CUDA(cudaStreamCreateWithFlags(&b.xstream, cudaStreamNonBlocking));
+    FS_CUDA(cudaEventCreateWithFlags(&b.ev_ready, cudaEventDisableTiming));
+    FS_CUDA(cudaEventCreateWithFlags(&b.ev_done, cudaEventDisableTiming));
+  }
   b.on = ok != 0;
   if (!b.on && c->rank == 0)
     fprintf(stderr, "[fsgpu] FSGPU_HALO=p2p: peer mailboxes unavailable, halo exchange stays on the default transport\n");
@@ -385,6 +407,10 @@ static void p2p_teardown(Comm* cm) {
   P2PBox& b = cm->p2p;
   for (size_t r = 0; r < b.peer.size(); ++r)
     if (b.ipc[r] && b.peer[r]) cudaIpcCloseMemHandle(b.peer[r]);
+  if (b.xstream) { cudaStreamSynchronize(b.xstream); cudaStreamDestroy(b.xstream); }
+  if (b.ev_ready) cudaEventDestroy(b.ev_ready);
+  if (b.ev_done) cudaEventDestroy(b.ev_done);
+  if (b.d_red) cudaFree(b.d_red);
   if (b.base) cudaFree(b.base);
   if (b.h_err) cudaFreeHost(b.h_err);
   b = P2PBox();
@@ -447,7 +473,12 @@ int comm_is_direct(fsgpu_ctx* c) { return c->comm && c->comm->p2p.on ? 1 : 0; }
 int comm_failed(fsgpu_ctx* c) {
   Comm* cm = c->comm;
   if (!cm || !cm->p2p.on || !*(volatile int*)cm->p2p.h_err) return 0;
-  fs_set_error("direct halo exchange: rank %d timed out waiting for a neighbour's rows", c->rank);
+  const volatile int* e = cm->p2p.h_err;
+  if (e[1])
+    fs_set_error("mailbox transport: rank %d timed out in halo exchange %d (flags seen: from rank-1 %d, from rank+1 %d)",
+                 c->rank, e[1], e[2], e[3]);
+  else
+    fs_set_error("mailbox transport: rank %d timed out waiting for a peer in a scalar all-reduce", c->rank);
   return 1;
 }
 
@@ -471,6 +502,79 @@ void comm_destroy(fsgpu_ctx* c) {
   c->comm = nullptr;
 }
 
+// true when this exchange fits the mailbox slots (the same decision on every rank)
+static bool halo_fits_mailbox(const Comm* cm, int n, int64_t pitch, int h) {
+  return cm->p2p.on && n <= 4 && (size_t)n * (size_t)h * (size_t)pitch <= cm->p2p.cap;
+}
+static int halo_mailbox_launch(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i0, int64_t i1,
+                               int h, cudaStream_t st) {
+  Comm* cm = c->comm;
+  HaloP2PArgs a;
+  for (int k = 0; k < 4; ++k) a.ptr[k] = k < n ? ptrs[k] : nullptr;
+  a.n = n; a.h = h; a.pitch = pitch; a.i0 = i0; a.i1 = i1;
+  a.mine = cm->p2p.base;
+  a.up = c->rank > 0 ? cm->p2p.nb[0] : nullptr;
+  a.dn = c->rank + 1 < c->nranks ? cm->p2p.nb[1] : nullptr;
+  a.cap = cm->p2p.cap;
+  a.e = ++cm->p2p.epoch;
+  a.err = cm->p2p.d_err;
+  a.timeout = cm->p2p.timeout;
+  k_halo_p2p<<<P2P_CTAS, P2P_THREADS, 0, st>>>(a);
+  FS_LAUNCHED();
+  return 0;
+}
+
+// Overlap: the caller has just enqueued the kernel(s) that wrote the h boundary rows
+// at both ends of [i0, i1) and will enqueue the interior part next.  The exchange then runs on the
+// transport's own stream, behind an event on the compute stream, while the interior kernel computes;
+// comm_halo_wait makes the compute stream wait for it before the first consumer of the halo rows.
+// Returns 0 with *async_out = false when the exchange is not one the mailbox can carry: the caller then
+// uses the blocking comm_halo after its interior kernel.
+int comm_halo_async(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i0, int64_t i1, int h,
+                    bool* async_out) {
+  Comm* cm = c->comm;
+  *async_out = false;
+  if (!cm || c->nranks <= 1 || n <= 0) return 0;
+  if (!halo_fits_mailbox(cm, n, pitch, h) || i1 - i0 < 2 * h) return 0;
+  if (comm_halo_wait(c)) return 1;  // one exchange in flight at a time: the slot protocol is per epoch
+  P2PBox& b = cm->p2p;
+  FS_CUDA(cudaEventRecord(b.ev_ready, c->stream));
+  FS_CUDA(cudaStreamWaitEvent(b.xstream, b.ev_ready, 0));
+  if (halo_mailbox_launch(c, ptrs, n, pitch, i0, i1, h, b.xstream)) return 1;
+  FS_CUDA(cudaEventRecord(b.ev_done, b.xstream));
+  b.pending = true;
+  *async_out = true;
+  return 0;
+}
+int comm_halo_wait(fsgpu_ctx* c) {
+  Comm* cm = c->comm;
+  if (!cm || !cm->p2p.pending) return 0;
+  FS_CUDA(cudaStreamWaitEvent(c->stream, cm->p2p.ev_done, 0));
+  cm->p2p.pending = false;
+  return 0;
+}
+// In-process ranks on ONE device (the LOCAL test transport) with the mailboxes on: a call that synchronises
+// the device implicitly (cudaFree, cudaMalloc, pinned allocations) on one host thread would wait for a peer
+// rank's exchange kernel that is itself waiting for a kernel this thread has not enqueued yet.  Every
+// allocation site reachable after comm_create therefore ends in this fence: drain my stream, meet the
+// other ranks.  Nothing of the kind exists with one process per GPU (a device only waits for its own
+// work, and that work only for kernels the peers have already enqueued), where this is a no-op.
+int comm_alloc_fence(fsgpu_ctx* c) {
+  Comm* cm = c->comm;
+  if (!cm || cm->transport != FSGPU_TRANSPORT_LOCAL || !cm->p2p.on) return 0;
+  FS_CUDA(cudaStreamSynchronize(c->stream));
+  LOCAL_BARRIER(cm);
+  return 0;
+}
+
+// > 0: slabs of a level with at least that many points split their producer kernels (boundary rows first)
+// and exchange on the transport's stream; 0: no overlap (no mailbox, or FSGPU_NO_OVERLAP)
+int64_t comm_overlap_min_points(fsgpu_ctx* c) {
+  if (!c->comm || !c->comm->p2p.on || !c->comm->p2p.overlap) return 0;
+  return c->comm->p2p.overlap_min_points > 0 ? c->comm->p2p.overlap_min_points : 1;
+}
+const P2PRedDev* comm_red_dev(fsgpu_ctx* c) { return c->comm && c->comm->p2p.on ? c->comm->p2p.d_red : nullptr; }
+
 int comm_halo(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i0, int64_t i1, int h) {
   Comm* cm = c->comm;
   if (!cm || c->nranks <= 1 || n <= 0) return 0;
@@ -479,23 +583,11 @@ int comm_halo(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i
                  (long long)(i1 - i0), h);
     return 1;
   }
+  if (comm_halo_wait(c)) return 1;
   const size_t cnt = (size_t)h * (size_t)pitch;
   auto row = [&](double* p, int64_t i) { return p + (i + FS_RO) * pitch; };
   const bool up = c->rank > 0, dn = c->rank + 1 < c->nranks;
-  if (cm->p2p.on && n <= 4 && (size_t)n * cnt <= cm->p2p.cap) {  // same decision on every rank
-    HaloP2PArgs a;
-    for (int k = 0; k < 4; ++k) a.ptr[k] = k < n ? ptrs[k] : nullptr;
-    a.n = n; a.h = h; a.pitch = pitch; a.i0 = i0; a.i1 = i1;
-    a.mine = cm->p2p.base;
-    a.up = up ? cm->p2p.nb[0] : nullptr;
-    a.dn = dn ? cm->p2p.nb[1] : nullptr;
-    a.cap = cm->p2p.cap;
-    a.e = ++cm->p2p.epoch;
-    a.err = cm->p2p.d_err;
-    k_halo_p2p<<<P2P_CTAS, P2P_THREADS, 0, c->stream>>>(a);
-    FS_LAUNCHED();
-    return 0;
-  }
+  if (halo_fits_mailbox(cm, n, pitch, h)) return halo_mailbox_launch(c, ptrs, n, pitch, i0, i1, h, c->stream);
   if (cm->transport == FSGPU_TRANSPORT_NCCL) {
     FS_NCCL(g_nccl.GroupStart());
     for (int k = 0; k < n; ++k) {
@@ -536,13 +628,11 @@ int comm_halo(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i
 int comm_allreduce(fsgpu_ctx* c, double* dev, int64_t n, int op) {
   Comm* cm = c->comm;
   if (!cm || c->nranks <= 1 || n <= 0) return 0;
+  if (comm_halo_wait(c)) return 1;
   if (cm->p2p.on && n <= P2P_RED_MAX) {  // scalars: one kernel, rank-ordered fold
     RedP2PArgs a;
-    for (int r = 0; r < P2P_MAX_RANKS; ++r) a.peer[r] = r < c->nranks ? cm->p2p.peer[(size_t)r] : nullptr;
-    a.dev = dev; a.n = (int)n; a.rank = c->rank; a.nranks = c->nranks; a.op = op;
-    a.red_off = cm->p2p.red_off;
-    a.e = ++cm->p2p.red_epoch;
-    a.err = cm->p2p.d_err;
+    a.d = cm->p2p.red;
+    a.dev = dev; a.n = (int)n; a.op = op;
     k_allreduce_p2p<<<1, P2P_MAX_RANKS * P2P_RED_MAX, 0, c->stream>>>(a);
     FS_LAUNCHED();
     return 0;

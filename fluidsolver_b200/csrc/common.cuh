@@ -139,6 +139,14 @@ __device__ __forceinline__ void for_each_point(int64_t r0, int64_t r1, int64_t n
     }
   }
 }
+// two row ranges [a0, a1) and [b0, b1) (either may be empty): the boundary rows at both ends of a slab,
+// swept by ONE launch ahead of the interior so that their halo exchange overlaps the interior launch
+struct RowSplit { int64_t a0, a1, b0, b1; };
+template <class F>
+__device__ __forceinline__ void for_each_point2(const RowSplit& R, int64_t n1, F&& f) {
+  if (R.a1 > R.a0) for_each_point(R.a0, R.a1, n1, f);
+  if (R.b1 > R.b0) for_each_point(R.b0, R.b1, n1, f);
+}
 #define FS_NUM_SMS 148
 static inline unsigned persist_blocks(int64_t n0, int64_t n1, int per_sm = 8) {
   const int64_t nt = ((n1 + 63) / 64) * ((n0 + 15) / 16);

@@ -82,6 +82,16 @@ int comm_failed(fsgpu_ctx* c);  // a direct (FSGPU_HALO=p2p) halo exchange timed
 // arrays given by VIRTUAL base pointers sharing `pitch`; this rank owns rows [i0, i1) (global
 // indices).  Fills the h rows above and below from the neighbour ranks' owned rows.
 int comm_halo(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i0, int64_t i1, int h);
+// the same exchange on the transport's own stream, ordered after what the compute stream holds NOW; the
+// compute stream goes on (interior rows) and meets it again at comm_halo_wait.  *async_out = false: not
+// available for this exchange (no mailbox, too large, too few rows) -- use comm_halo instead.
+int comm_halo_async(fsgpu_ctx* c, double* const* ptrs, int n, int64_t pitch, int64_t i0, int64_t i1, int h,
+                    bool* async_out);
+int comm_halo_wait(fsgpu_ctx* c);
+int comm_alloc_fence(fsgpu_ctx* c);  // after an allocation made once the ranks talk (in-process ranks only; see comm.cu)
+int64_t comm_overlap_min_points(fsgpu_ctx* c);  // 0: no overlap; else the smallest slab (points) worth splitting
+struct P2PRedDev;
+const P2PRedDev* comm_red_dev(fsgpu_ctx* c);  // device struct of the in-kernel scalar all-reduce (null: none)
 int comm_allreduce(fsgpu_ctx* c, double* dev, int64_t n, int op);
 // n doubles to / from one peer rank (the x-periodic wrap-around); peer < 0: not a participant
 int comm_sendrecv(fsgpu_ctx* c, int peer, const double* const* send, double* const* recv, int narr, int64_t n);

@@ -230,7 +230,7 @@ int fs_ensure_part(fsgpu_ctx* c, size_t doubles) {
   c->part = nullptr;
   FS_CUDA(cudaMalloc(&c->part, doubles * sizeof(double)));
   c->part_cap = doubles;
-  return 0;
+  return comm_alloc_fence(c);
 }
 
 static dim3 cell_grid(const Geom& g) {  // the owned cell rows

@@ -14,6 +14,7 @@
 #pragma once
 
 #include "ctx.h"
+#include "p2p.cuh"
 
 #define FS_MAX_LEVELS 40
 
@@ -51,8 +52,12 @@ struct PcgScal {
   int iter, done, first, coarse_zero_diag;
   // slab decomposition: nranks > 1 makes the reduction kernels park their LOCAL sum in red[]
   // instead of finishing the recurrence; after the all-reduce k_pcg_after_* finishes it.
+  // With the mailbox transport (p2p != null) the thread holding the local sum all-reduces it over
+  // peer memory on the spot (p2p_allreduce_sum1) and finishes the recurrence itself: a dot product
+  // of the distributed PCG is then ONE kernel, as on a single GPU.
   int nranks;
   double red[4];
+  const P2PRedDev* p2p;
 };
 // done codes
 enum { PCG_RUNNING = 0, PCG_CONVERGED = 1, PCG_BREAKDOWN = 2, PCG_ZERO_RHS = 3 };
@@ -98,12 +103,20 @@ __device__ __forceinline__ void pcg_after_sp(PcgScal* scal, double sp) {
 // called by the last block of a reduction kernel with this rank's sum
 template <bool INIT>
 __device__ __forceinline__ void pcg_local_rz(PcgScal* scal, double g) {
-  if (scal->nranks > 1) scal->red[0] = g;
-  else pcg_after_rz<INIT>(scal, g);
+  if (scal->nranks > 1) {
+    if (scal->p2p) pcg_after_rz<INIT>(scal, p2p_allreduce_sum1(*scal->p2p, g));
+    else scal->red[0] = g;
+  } else {
+    pcg_after_rz<INIT>(scal, g);
+  }
 }
 __device__ __forceinline__ void pcg_local_sp(PcgScal* scal, double sp) {
-  if (scal->nranks > 1) scal->red[0] = sp;
-  else pcg_after_sp(scal, sp);
+  if (scal->nranks > 1) {
+    if (scal->p2p) pcg_after_sp(scal, p2p_allreduce_sum1(*scal->p2p, sp));
+    else scal->red[0] = sp;
+  } else {
+    pcg_after_sp(scal, sp);
+  }
 }
 #endif
 
@@ -139,3 +152,6 @@ int ps_finish_sp(fsgpu_ps* s);
 // halo rows of level-l arrays given by virtual base pointers
 int ps_halo(fsgpu_ps* s, int l, double* const* ptrs, int n, int h);
 int ps_solve(fsgpu_ps* s, double* residual, int* iters);
+// boundary-first split of level l's owned rows for an exchange of h halo rows (overlap)
+struct SlabSplit { RowSplit bnd, in; bool on; };
+SlabSplit ps_split(fsgpu_ps* s, int l, int h);

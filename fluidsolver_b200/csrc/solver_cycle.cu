@@ -857,14 +857,21 @@ static unsigned march_blocks(int64_t rows, int64_t strips, int mr) {
   return (unsigned)(total < cap ? (total > 0 ? total : 1) : cap);
 }
 
-static int launch_down(fsgpu_ps* s, int l, const double* fb) {
+// [r0, r1): the COARSE rows to produce (r0 < 0: all rows this rank owns / the whole replicated level).  A
+// j-coarsened level keeps its rows, so there the range is the fine rows swept as well.
+static int launch_down(fsgpu_ps* s, int l, const double* fb, int64_t r0 = -1, int64_t r1 = -1) {
   cudaStream_t st = s->c->stream;
   Level* L        = s->L;
-  const LevelDev& f = L[l].v;
+  LevelDev f = L[l].v;
   LevelDev c = L[l + 1].v;
   if (!L[l].replicated) {  // a distributed level writes the coarse rows this rank owns
     c.i0 = L[l + 1].own0;
     c.i1 = L[l + 1].own1;
+  }
+  if (r0 >= 0) {
+    if (r1 <= r0) return 0;
+    if (L[l].cdir == 0) { c.i0 = r0; c.i1 = r1; }
+    else { f.i0 = r0; f.i1 = r1; }
   }
   if (L[l].cdir == 0) {
     const int64_t strips = cdiv(f.n1, 120);
@@ -883,21 +890,28 @@ static int launch_down(fsgpu_ps* s, int l, const double* fb) {
   return 0;
 }
 
+// [r0, r1): the rows of level l to produce (r0 < 0: all rows this rank sweeps)
 template <int CDIR>
-static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_mode) {
+static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_mode, int64_t r0 = -1,
+                     int64_t r1 = -1) {
   cudaStream_t st = s->c->stream;
   Level* L        = s->L;
   fsgpu_ctx* c    = s->c;
+  LevelDev f      = L[l].v;
+  if (r0 >= 0) {
+    if (r1 <= r0) return 0;
+    f.i0 = r0; f.i1 = r1;
+  }
   if (!L[l].active) {
-    k_up_interp<CDIR><<<persist_blocks(L[l].v.i1 - L[l].v.i0, L[l].v.n1), dim3(BX, BY), 0, st>>>(L[l].v, fx, L[l + 1].v, L[l + 1].v.x, s->scal);
+    k_up_interp<CDIR><<<persist_blocks(f.i1 - f.i0, f.n1), dim3(BX, BY), 0, st>>>(f, fx, L[l + 1].v, L[l + 1].v.x, s->scal);
     FS_LAUNCHED();
     return 0;
   }
-  const int64_t strips = cdiv(L[l].v.n1, MOUT * MWARPS);
-  const int mr      = pick_rows(L[l].v.i1 - L[l].v.i0, strips);
-  const unsigned nb = march_blocks(L[l].v.i1 - L[l].v.i0, strips, mr);
+  const int64_t strips = cdiv(f.n1, MOUT * MWARPS);
+  const int mr      = pick_rows(f.i1 - f.i0, strips);
+  const unsigned nb = march_blocks(f.i1 - f.i0, strips, mr);
   const int bl = 32 * MWARPS;
-#define UP_ARGS L[l].v, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket
+#define UP_ARGS f, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket
   if (dot_mode == 1) k_up_march<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
   else if (dot_mode == 2) k_up_march<CDIR, 2><<<nb, bl, 0, st>>>(UP_ARGS);
   else k_up_march<CDIR, 0><<<nb, bl, 0, st>>>(UP_ARGS);
@@ -972,12 +986,25 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
     const size_t cn = (size_t)(L[l + 1].v.n0 * L[l + 1].v.pitch);
     double* crow0 = L[l + 1].v.b + FS_RO * L[l + 1].v.pitch;  // row 0 of the replicated level
     if (gather) FS_CUDA(cudaMemsetAsync(crow0, 0, cn * sizeof(double), st));
-    if (launch_down(s, l, fb)) return 1;
-    if (gather) {
-      if (comm_allreduce(s->c, crow0, (int64_t)cn, COMM_SUM)) return 1;
-    } else if (dist && l + 1 < s->ld) {
-      if (ps_halo(s, l + 1, &L[l + 1].v.b, 1, FS_RO)) return 1;
+    if (dist && l + 1 < s->ld) {
+      // the coarse rhs needs FS_RO halo rows: boundary rows first, their exchange on the transport's
+      // stream while the interior rows are restricted
+      const SlabSplit sp = ps_split(s, l + 1, FS_RO);
+      bool async = false;
+      if (sp.on) {
+        if (launch_down(s, l, fb, sp.bnd.a0, sp.bnd.a1) || launch_down(s, l, fb, sp.bnd.b0, sp.bnd.b1)) return 1;
+        if (comm_halo_async(s->c, &L[l + 1].v.b, 1, L[l + 1].v.pitch, L[l + 1].own0, L[l + 1].own1, FS_RO, &async))
+          return 1;
+        if (launch_down(s, l, fb, sp.in.a0, sp.in.a1)) return 1;
+      } else if (launch_down(s, l, fb)) {
+        return 1;
+      }
+      if (async) { if (comm_halo_wait(s->c)) return 1; }
+      else if (ps_halo(s, l + 1, &L[l + 1].v.b, 1, FS_RO)) return 1;
+      continue;
     }
+    if (launch_down(s, l, fb)) return 1;
+    if (gather && comm_allreduce(s->c, crow0, (int64_t)cn, COMM_SUM)) return 1;
   }
   {
     ProfScope ps_(PROF_COARSE, st);
@@ -991,9 +1018,24 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
     double* fx       = l == 0 ? z : L[l].v.x;
     ProfScope ps_(l == 0 ? PROF_UP0 : PROF_UP, st);
     const int dm = l == 0 ? dot_mode : 0;
-    if (L[l].cdir == 0) { if (launch_up<0>(s, l, fb, fx, dm)) return 1; }
-    else { if (launch_up<1>(s, l, fb, fx, dm)) return 1; }
-    if (dist && l >= 1 && l < s->ld && ps_halo(s, l, &fx, 1, 1)) return 1;
+    auto up = [&](int64_t r0, int64_t r1) {
+      return L[l].cdir == 0 ? launch_up<0>(s, l, fb, fx, dm, r0, r1) : launch_up<1>(s, l, fb, fx, dm, r0, r1);
+    };
+    if (dist && l >= 1 && l < s->ld) {  // x of a distributed level: one halo row for the next finer level
+      const SlabSplit sp = ps_split(s, l, 1);
+      bool async = false;
+      if (sp.on) {
+        if (up(sp.bnd.a0, sp.bnd.a1) || up(sp.bnd.b0, sp.bnd.b1)) return 1;
+        if (comm_halo_async(s->c, &fx, 1, L[l].v.pitch, L[l].own0, L[l].own1, 1, &async)) return 1;
+        if (up(sp.in.a0, sp.in.a1)) return 1;
+      } else if (up(-1, -1)) {
+        return 1;
+      }
+      if (async) { if (comm_halo_wait(s->c)) return 1; }
+      else if (ps_halo(s, l, &fx, 1, 1)) return 1;
+    } else if (up(-1, -1)) {
+      return 1;
+    }
   }
   if (dot_mode && ps_finish_rz(s, dot_mode == 2)) return 1;
   return 0;

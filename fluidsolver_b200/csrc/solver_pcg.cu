@@ -15,6 +15,7 @@
 #include "solver.h"
 
 #include <math.h>
+#include <stdlib.h>
 
 #define FS_LAG 1
 
@@ -51,14 +52,17 @@ k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict_
 // The sum of all entries of the new x rides along (-> *sum_out, this rank's rows): after the last iteration
 // it is the integral shift_pressure_to_zero needs (src/Operators.hpp:78-82), so the projection needs no
 // separate summation pass over delta_p.
+// Slab overlap: the launch is split in two (boundary rows first, RowSplit; ACC adds the second launch's sum to the
+// first's), so that the exchange of r's halo rows runs beside the interior launch.
+template <bool ACC>
 __global__ void __launch_bounds__(BX* BY)
-k_xr_update(const LevelDev L, double* __restrict__ x, double* __restrict__ r,
+k_xr_update(const LevelDev L, const RowSplit rr, double* __restrict__ x, double* __restrict__ r,
             const double* __restrict__ p, const double* __restrict__ s, const PcgScal* scal, double* part,
             unsigned int* ticket, double* sum_out) {
   if (scal->done) return;
   const double alpha = scal->alpha;
   double v[1] = {0.0};
-  for_each_point(L.i0, L.i1, L.n1, [&](int64_t li, int64_t lj) {
+  for_each_point2(rr, L.n1, [&](int64_t li, int64_t lj) {
     const int64_t k = L.idx(li, lj);
     const double xn = x[k] + alpha * p[k];
     x[k] = xn;
@@ -67,7 +71,7 @@ k_xr_update(const LevelDev L, double* __restrict__ x, double* __restrict__ r,
   });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
-    if (threadIdx.x == 0 && threadIdx.y == 0) sum_out[0] = tot[0];
+    if (threadIdx.x == 0 && threadIdx.y == 0) sum_out[0] = ACC ? sum_out[0] + tot[0] : tot[0];
   }
 }
 
@@ -91,11 +95,11 @@ k_dot_rz(const LevelDev L, const double* __restrict__ r, const double* __restric
 // p = z + beta p   (FIRST: p = z); persistent grid for the same reason
 template <bool FIRST>
 __global__ void __launch_bounds__(BX* BY)
-k_p_update(const LevelDev L, double* __restrict__ p, const double* __restrict__ z,
+k_p_update(const LevelDev L, const RowSplit rr, double* __restrict__ p, const double* __restrict__ z,
            const PcgScal* scal) {
   if (scal->done) return;
   const double beta = FIRST ? 0.0 : scal->beta;
-  for_each_point(L.i0, L.i1, L.n1, [&](int64_t li, int64_t lj) {
+  for_each_point2(rr, L.n1, [&](int64_t li, int64_t lj) {
     const int64_t k = L.idx(li, lj);
     if (FIRST) p[k] = z[k];
     else p[k] = z[k] + beta * p[k];
@@ -111,9 +115,10 @@ __global__ void k_after_rz(PcgScal* scal) {
   if (!scal->done) pcg_after_rz<INIT>(scal, scal->red[0]);
 }
 
-__global__ void k_scal_init(PcgScal* scal, double eps, int nranks, double* sum_x) {
+__global__ void k_scal_init(PcgScal* scal, double eps, int nranks, const P2PRedDev* p2p, double* sum_x) {
   sum_x[0] = 0.0;  // x = 0
   scal->nranks = nranks;
+  scal->p2p = p2p;
   scal->gamma = scal->sdotp = scal->alpha = scal->beta = scal->bi = scal->iprod = 0.0;
   scal->eps   = eps;
   scal->iter  = 0;
@@ -124,14 +129,14 @@ __global__ void k_scal_init(PcgScal* scal, double eps, int nranks, double* sum_x
 }  // namespace
 
 int ps_finish_sp(fsgpu_ps* s) {
-  if (s->c->nranks <= 1) return 0;
+  if (s->c->nranks <= 1 || comm_red_dev(s->c)) return 0;  // mailbox transport: done inside the reduction kernel
   if (comm_allreduce(s->c, s->scal->red, 1, COMM_SUM)) return 1;
   k_after_sp<<<1, 1, 0, s->c->stream>>>(s->scal);
   FS_LAUNCHED();
   return 0;
 }
 int ps_finish_rz(fsgpu_ps* s, bool init) {
-  if (s->c->nranks <= 1) return 0;
+  if (s->c->nranks <= 1 || comm_red_dev(s->c)) return 0;
   if (comm_allreduce(s->c, s->scal->red, 1, COMM_SUM)) return 1;
   if (init) k_after_rz<true><<<1, 1, 0, s->c->stream>>>(s->scal);
   else k_after_rz<false><<<1, 1, 0, s->c->stream>>>(s->scal);
@@ -142,6 +147,22 @@ int ps_halo(fsgpu_ps* s, int l, double* const* ptrs, int n, int h) {
   if (s->c->nranks <= 1) return 0;
   const Level& L = s->L[l];
   return comm_halo(s->c, ptrs, n, L.v.pitch, L.own0, L.own1, h);
+}
+
+// Boundary-first split of a level's owned rows [i0, i1) for an exchange of h halo rows: `bnd` = the h rows
+// next to each neighbouring slab, `in` = the rest.  on == false: too small to be worth it (or no mailbox).
+SlabSplit ps_split(fsgpu_ps* s, int l, int h) {
+  fsgpu_ctx* c = s->c;
+  const int64_t min_pts = comm_overlap_min_points(c);
+  const Level& L = s->L[l];
+  const int64_t i0 = L.own0, i1 = L.own1;
+  SlabSplit sp;
+  const bool up = c->rank > 0, dn = c->rank + 1 < c->nranks;
+  const int64_t lo = i0 + (up ? h : 0), hi = i1 - (dn ? h : 0);
+  sp.on  = min_pts > 0 && !L.replicated && i1 - i0 >= 4 * h && (i1 - i0) * L.v.n1 >= min_pts;
+  sp.bnd = RowSplit{i0, lo, hi, i1};
+  sp.in  = RowSplit{lo, hi, 0, 0};
+  return sp;
 }
 
 int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
@@ -155,14 +176,17 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   double* r = c->f[FSGPU_RHS];  // r = b - A 0 = b: the rhs buffer becomes the residual
   const size_t prof0 = fs_prof_mark();
   g_prof_tag = 0;
-  k_scal_init<<<1, 1, 0, st>>>(s->scal, s->o.tol * s->o.tol, c->nranks, c->red_out + 1);
+  k_scal_init<<<1, 1, 0, st>>>(s->scal, s->o.tol * s->o.tol, c->nranks, comm_red_dev(c), c->red_out + 1);
   FS_LAUNCHED();
   FS_CUDA(cudaMemsetAsync(alloc_base(c->g, x), 0, (size_t)c->g.count() * sizeof(double), st));
   // slab decomposition, per iteration: r needs FS_RO halo rows before the V-cycle (restriction
   // reaches two rows out), p one halo row before the matvec
   if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
   if (ps_vcycle(s, r, s->z, 2)) return 1;  // z = C b and bi = <z, b>
-  k_p_update<true><<<pg, bl, 0, st>>>(L0, s->p, s->z, s->scal);
+  const RowSplit all{L0.i0, L0.i1, 0, 0};
+  const SlabSplit sp1 = ps_split(s, 0, 1), sp2 = ps_split(s, 0, FS_RO);  // p: one halo row, r: FS_RO
+  const unsigned pg1 = persist_blocks(2, L0.n1), pg2 = persist_blocks(2 * FS_RO, L0.n1);
+  k_p_update<true><<<pg, bl, 0, st>>>(L0, all, s->p, s->z, s->scal);
   FS_LAUNCHED();
   if (ps_halo(s, 0, &s->p, 1, 1)) return 1;
   const int nslot = FS_LAG + 1;
@@ -178,16 +202,36 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
     }
     {
       ProfScope ps_(PROF_XR, st);
-      k_xr_update<<<pg, bl, 0, st>>>(L0, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1);
-      FS_LAUNCHED();
-      if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
+      bool async = false;
+      if (sp2.on) {  // boundary rows, their exchange on the transport's stream, interior rows beside it
+        k_xr_update<false><<<pg2, bl, 0, st>>>(L0, sp2.bnd, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1);
+        FS_LAUNCHED();
+        if (comm_halo_async(c, &r, 1, L0.pitch, s->L[0].own0, s->L[0].own1, FS_RO, &async)) return 1;
+        k_xr_update<true><<<pg, bl, 0, st>>>(L0, sp2.in, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1);
+        FS_LAUNCHED();
+      } else {
+        k_xr_update<false><<<pg, bl, 0, st>>>(L0, all, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1);
+        FS_LAUNCHED();
+      }
+      if (async) { if (comm_halo_wait(c)) return 1; }
+      else if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
     }
     if (ps_vcycle(s, r, s->z, 1)) return 1;  // z = C r and gamma' = <r, z>
     {
       ProfScope ps_(PROF_PUPD, st);
-      k_p_update<false><<<pg, bl, 0, st>>>(L0, s->p, s->z, s->scal);
-      FS_LAUNCHED();
-      if (ps_halo(s, 0, &s->p, 1, 1)) return 1;
+      bool async = false;
+      if (sp1.on) {
+        k_p_update<false><<<pg1, bl, 0, st>>>(L0, sp1.bnd, s->p, s->z, s->scal);
+        FS_LAUNCHED();
+        if (comm_halo_async(c, &s->p, 1, L0.pitch, s->L[0].own0, s->L[0].own1, 1, &async)) return 1;
+        k_p_update<false><<<pg, bl, 0, st>>>(L0, sp1.in, s->p, s->z, s->scal);
+        FS_LAUNCHED();
+      } else {
+        k_p_update<false><<<pg, bl, 0, st>>>(L0, all, s->p, s->z, s->scal);
+        FS_LAUNCHED();
+      }
+      if (async) { if (comm_halo_wait(c)) return 1; }
+      else if (ps_halo(s, 0, &s->p, 1, 1)) return 1;
     }
     const int slot = it % nslot;
     FS_CUDA(cudaMemcpyAsync(&s->h_scal[slot], s->scal, sizeof(PcgScal), cudaMemcpyDeviceToHost, st));

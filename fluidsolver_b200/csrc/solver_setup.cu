@@ -321,7 +321,7 @@ static int alloc_levels(fsgpu_ps* s) {
   }
   cur = s->nl - 1;
   s->ctmp = take((size_t)(c.rows * c.v.pitch));
-  return 0;
+  return comm_alloc_fence(s->c);
 }
 
 static dim3 lvl_grid(const LevelDev& v) {

@@ -340,7 +340,7 @@ int fs_ensure_field(fsgpu_ctx* c, int field) {
   FS_CUDA(cudaMemsetAsync(base, 0, n * sizeof(double), c->stream));
   c->ext_alloc[field] = base;
   c->f[field] = base - c->g.voff();
-  return 0;
+  return comm_alloc_fence(c);
 }
 static int ensure_fields(fsgpu_ctx* c, std::initializer_list<int> fl) {
   for (int f : fl)

@@ -191,16 +191,18 @@ def test_slab_timesteps(F, oracle, name, kind, n, nsub, flags, R):
     assert ep <= (1e-5 if floor else 1e-8)
 
 
-@pytest.mark.skipif(os.environ.get("FSGPU_TEST_P2P") != "1",
-                    reason="direct (mailbox) halo exchange is opt-in until it has run on a GPU box: FSGPU_TEST_P2P=1")
-@pytest.mark.parametrize("R", [2, 3])
-def test_slab_timesteps_p2p_halo(F, oracle, R, monkeypatch):
-    """FSGPU_HALO=p2p: halo rows travel through peer-mapped mailboxes (one kernel per exchange) instead
-    of the staged copies; results must equal the default transport bit for bit"""
+@pytest.mark.parametrize("R,overlap", [(2, False), (3, False), (2, True), (3, True)])
+def test_slab_timesteps_p2p_halo(F, oracle, R, overlap, monkeypatch):
+    """FSGPU_HALO=p2p: halo rows travel through peer-mapped mailboxes (one kernel per exchange) and the PCG dot
+    products are all-reduced inside their reduction kernels, instead of the staged copies.  Without overlap the
+    results equal the default transport's bit for bit; with it (boundary rows first, exchange on the transport's
+    stream beside the interior launch) only the association of the sum of delta_p changes."""
     st, bc = cavity_state(oracle, 96, 96), cavity_bc()
     oracle.apply_velocity_bconds(st, bc)
+    direct = []
 
     def body(fs, r):
+        direct.append(fs.halo_is_direct())
         ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
         ps.set_pressure_operator()
         hist = []
@@ -211,8 +213,19 @@ def test_slab_timesteps_p2p_halo(F, oracle, R, monkeypatch):
         return hist
 
     b, rb = run_ranks(F, st, bc, R, body, fields=("U", "V", "P"))
+    assert not any(direct)
+    del direct[:]
     monkeypatch.setenv("FSGPU_HALO", "p2p")
+    monkeypatch.setenv("FSGPU_P2P_TIMEOUT_S", "5")
+    if overlap:
+        monkeypatch.setenv("FSGPU_OVERLAP_MIN_POINTS", "1")
+    else:
+        monkeypatch.setenv("FSGPU_NO_OVERLAP", "1")
     a, ra = run_ranks(F, st, bc, R, body, fields=("U", "V", "P"))
+    assert all(direct) and len(direct) == R
     assert ra == rb
     for n in ("U", "V", "P"):
-        assert np.array_equal(a[n], b[n]), n
+        if overlap:
+            assert np.abs(a[n] - b[n]).max() <= 1e-13 * np.abs(b[n]).max(), n
+        else:
+            assert np.array_equal(a[n], b[n]), n
