@@ -26,11 +26,13 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# CPU-baseline protocol: all host cores, threads pinned.  Must be in the
-# environment before any OpenMP runtime is loaded (without binding, 8 spinning threads on this
-# container's 8 vCPUs ran the reference 4x slower).
-os.environ.setdefault("OMP_PROC_BIND", "close")
-os.environ.setdefault("OMP_PLACES", "cores")
+# CPU-baseline protocol: all host cores, threads pinned (OMP_PROC_BIND=close,
+# OMP_PLACES=cores; without binding, 8 spinning threads on the build container's 8 vCPUs ran the reference 4x
+# slower).  The binding must be in the environment before any OpenMP runtime is loaded AND it also pins the
+# process's initial thread to the first core -- under torchrun that put the launch threads of all N ranks on
+# core 0 (round 1's 8-GPU collapse).  So the CPU legs run in a child process of their own with that
+# environment (cpu_leg -> _cpu_leg_child), and the GPU ranks never see it.
+CPU_CHILD_ENV = {"OMP_PROC_BIND": "close", "OMP_PLACES": "cores"}
 
 NSUB, TOL, MAX_ITER, CFL, DT_MAX = 5, 1e-6, 50, 0.9, 0.1
 # The CPU legs run the SAME configuration as the GPU arm: the 8192^2 cavity (the reference
@@ -102,6 +104,18 @@ class ClockSampler:
 
 # ---- the CPU leg: the UNMODIFIED reference (oracle/_ref/libfsref.so), else the C oracle --------
 def cpu_leg(steps, warmup, n=CPU_SAMPLE_N):
+    """The CPU leg in a child process (its OpenMP binding must not leak into the GPU ranks)."""
+    env = dict(os.environ)
+    for k, v in CPU_CHILD_ENV.items():
+        env.setdefault(k, v)
+    for k in ("OMP_NUM_THREADS", "RANK", "WORLD_SIZE", "LOCAL_RANK"):  # torchrun sets OMP_NUM_THREADS=1
+        env.pop(k, None)
+    r = subprocess.run([sys.executable, os.path.abspath(__file__), "--cpu-child", str(steps), str(warmup), str(n)],
+                       env=env, stdout=subprocess.PIPE, text=True, check=True)
+    return json.loads(r.stdout.strip().splitlines()[-1])
+
+
+def _cpu_leg_child(steps, warmup, n):
     """Times the reference's own OpenMP + HYPRE path on this box's host cores for the same
     workload and grid as the GPU arm (bounded in the number of timesteps)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -443,4 +457,7 @@ def main():
 
 
 if __name__ == "__main__":
+    if len(sys.argv) >= 5 and sys.argv[1] == "--cpu-child":
+        print(json.dumps(_cpu_leg_child(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]))), flush=True)
+        sys.exit(0)
     sys.exit(main())

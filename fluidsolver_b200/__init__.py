@@ -7,4 +7,4 @@ from .lib import (FS, LinearSolver, FsgpuError, load, npy_write_host, launch_cou
                   PSD_NONE, PSD_LEFT, PSD_RIGHT, PSD_BOTTOM, PSD_TOP, RELAX_JACOBI, RELAX_RBGS,
                   FLOW_FORCE_TOTAL, FLOW_OUTFLOW_FIX, FLOW_OUTFLOW_FIX_DY, STEP_OUTFLOW_FIX,
                   STEP_REBUILD_OPERATOR, STEP_DENSITY, STEP_CAPILLARY, TRANSPORT_NCCL, TRANSPORT_LOCAL,
-                  COMM_ID_BYTES, comm_id, slab_range, slab_coarse_range, slab_rows)
+                  COMM_ID_BYTES, comm_id, slab_range, slab_coarse_range, slab_rows, selftest_division)

@@ -1,9 +1,11 @@
 // fluidsolver_b200/csrc/api.cu -- the C ABI of include/fsgpu.h.
 #include "solver.h"
 
+#include <cuda_profiler_api.h>
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -13,6 +15,11 @@
 
 int64_t g_launches = 0;
 unsigned int g_prof_mask = 0;
+unsigned int g_ncu_mask = getenv("FSGPU_NCU_CLASSES") ? (unsigned int)strtoul(getenv("FSGPU_NCU_CLASSES"), nullptr, 0) : 0u;
+void fs_ncu_range(bool begin) {
+  if (begin) cudaProfilerStart();
+  else cudaProfilerStop();
+}
 int g_prof_tag = 0;
 
 namespace {
@@ -64,9 +71,41 @@ void fs_set_error(const char* fmt, ...) {
 }
 
 
+// DivBy (common.cuh) against the hardware-exact division on n pseudo-random numerators
+__global__ void k_selftest_division(const DivBy q, int64_t n, unsigned long long seed, unsigned long long* bad) {
+  unsigned long long local = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    unsigned long long z = seed + 0x9e3779b97f4a7c15ull * (unsigned long long)(i + 1);  // splitmix64
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    z ^= z >> 31;
+    // random sign and significand, exponent in [2^-200, 2^200) (every 64th sample exactly 0)
+    const unsigned long long ex = 1023 - 200 + ((z >> 52) % 400);
+    double x = __longlong_as_double((long long)((z & 0x800fffffffffffffull) | (ex << 52)));
+    if ((i & 63) == 0) x = 0.0;
+    const double a = q(x), b = x / q.y;
+    if (__double_as_longlong(a) != __double_as_longlong(b) && fabs(b) >= 2.3e-308) ++local;
+  }
+  if (local) atomicAdd(bad, local);
+}
+
 extern "C" {
 
 const char* fsgpu_last_error(void) { return g_err; }
+
+int fsgpu_selftest_division(double y, int64_t n, uint64_t seed, int* fast, int64_t* mismatches) {
+  const DivBy q = make_div_by(y);
+  unsigned long long* d = nullptr;
+  FS_CUDA(cudaMalloc(&d, sizeof(*d)));
+  FS_CUDA(cudaMemset(d, 0, sizeof(*d)));
+  k_selftest_division<<<148 * 8, 256>>>(q, n, (unsigned long long)seed, d);
+  unsigned long long h = 0;
+  FS_CUDA(cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost));
+  cudaFree(d);
+  if (fast) *fast = q.fast;
+  if (mismatches) *mismatches = (int64_t)h;
+  return 0;
+}
 int64_t fsgpu_launch_count(void) { return g_launches; }
 
 int fsgpu_prof_enable(unsigned int class_mask) {
@@ -140,8 +179,9 @@ int fsgpu_create_slab(int64_t nx, int64_t ny, double dx, double dy, int device, 
   const size_t n = (size_t)c->g.count();
   const int nf = FSGPU_NUM_CORE_FIELDS + 2;
   FS_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  FS_CUDA(cudaMalloc(&c->slab, n * nf * sizeof(double)));
-  FS_CUDA(cudaMemsetAsync(c->slab, 0, n * nf * sizeof(double), c->stream));
+  // + slack: bulk-copy row segments (solver_cycle.cu) of the last strip may run past the last row's pitch
+  FS_CUDA(cudaMalloc(&c->slab, (n * nf + 512) * sizeof(double)));
+  FS_CUDA(cudaMemsetAsync(c->slab, 0, (n * nf + 512) * sizeof(double), c->stream));
   for (int f = 0; f < FSGPU_NUM_CORE_FIELDS; ++f) c->f[f] = c->slab + n * f - c->g.voff();
   c->U_alt = c->slab + n * FSGPU_NUM_CORE_FIELDS - c->g.voff();
   c->V_alt = c->slab + n * (FSGPU_NUM_CORE_FIELDS + 1) - c->g.voff();
@@ -527,6 +567,8 @@ int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out) {
   s->c = c;
   s->o = *o;
   if (s->o.relax == 0) s->o.relax = FSGPU_RELAX_JACOBI;
+  if (const char* e = getenv("FSGPU_RING_MIN_POINTS")) s->ring_min_points = atoll(e) > 0 ? atoll(e) : 1;
+  if (const char* e = getenv("FSGPU_RING")) { if (atoi(e) == 0) s->ring_min_points = 0; }
   FS_CUDA(cudaMalloc(&s->scal, sizeof(PcgScal)));
   FS_CUDA(cudaMemset(s->scal, 0, sizeof(PcgScal)));
   FS_CUDA(cudaMallocHost(&s->h_scal, 4 * sizeof(PcgScal)));

@@ -46,6 +46,39 @@ struct Geom {
   __host__ __device__ inline int64_t u_hi() const { return a_hi + (last() ? 1 : 0); }
 };
 
+// ---- x / y for a launch-uniform divisor, correctly rounded ---------------------------------------
+// The reference divides by dx, dy, dt (src/Operators.hpp:36-39, src/LinearSystem.hpp:134,
+// scaling/LidDrivenFlow.cpp:155-159) and the kernels must round as it does.  The compiler's FP64 division
+// costs ~35 instructions per quotient and drops to a subroutine for zero / tiny numerators -- on the
+// cavity's mostly quiescent field that made k_rhs instruction bound (ncu: 340 instructions per point,
+// 25 % DRAM).  With r = RN(1 / y) formed once on the host,
+//     q = RN(x r);   q' = RN(q + RN(x - q y) r)          (the inner remainder is exact under FMA)
+// is the correctly rounded quotient (Markstein 1990) unless the significand of y is all ones, which
+// make_div_by tests for (fast = 0 -> the ordinary division); huge / non-finite q takes it as well.
+// Results in the denormal range may differ from the division's in their last (denormal) bit.
+struct DivBy {
+  double y, r;
+  int fast;
+#ifdef __CUDACC__
+  __device__ __forceinline__ double operator()(double x) const {
+    const double q = __dmul_rn(x, r);
+    if (!fast || !(fabs(q) < 1e300)) return x / y;
+    return fma(fma(-q, y, x), r, q);
+  }
+#endif
+};
+static inline DivBy make_div_by(double y) {
+  DivBy d;
+  d.y = y;
+  d.r = 1.0 / y;
+  unsigned long long bits;
+  __builtin_memcpy(&bits, &y, sizeof(bits));
+  const unsigned long long man = bits & 0xfffffffffffffull, ex = (bits >> 52) & 0x7ff;
+  const double ar = d.r < 0 ? -d.r : d.r;
+  d.fast = (man != 0xfffffffffffffull && ex != 0 && ex != 0x7ff && ar > 1e-290 && ar < 1e290) ? 1 : 0;
+  return d;
+}
+
 // ---- deterministic grid-wide reductions -----------------------------------------------------
 // Each block reduces with warp shuffles + one shared-memory stage and stores its partial at
 // part[blockIdx]; the LAST block to finish (threadfence + atomic ticket) folds all partials in a
@@ -125,16 +158,18 @@ __device__ inline bool grid_reduce(const double (&v)[NV], double* part, unsigned
 // rows [r0, r1) x columns [0, n1)
 template <class F>
 __device__ __forceinline__ void for_each_point(int64_t r0, int64_t r1, int64_t n1, F&& f) {
-  const int64_t n0 = r1 - r0;
-  const int64_t tiles_j = (n1 + 63) / 64, nt = tiles_j * ((n0 + 15) / 16);
-  for (int64_t t = blockIdx.x; t < nt; t += gridDim.x) {
-    const int64_t ti = t / tiles_j, tj = t - ti * tiles_j;
-    const int64_t lj = tj * 64 + threadIdx.x;
-    if (lj < n1) {
+  // tile arithmetic in 32 bits (a 64-bit division per tile and thread was a quarter of the instructions of
+  // the element-wise kernels); only the element index the callback forms is 64-bit
+  const int n0 = (int)(r1 - r0);
+  const unsigned tiles_j = (unsigned)((n1 + 63) / 64), nt = tiles_j * (unsigned)((n0 + 15) / 16);
+  for (unsigned t = blockIdx.x; t < nt; t += gridDim.x) {
+    const unsigned ti = t / tiles_j, tj = t - ti * tiles_j;
+    const int lj = (int)(tj * 64 + threadIdx.x);
+    if (lj < (int)n1) {
 #pragma unroll
       for (int m = 0; m < 4; ++m) {
-        const int64_t li = r0 + ti * 16 + threadIdx.y + 4 * m;
-        if (li < r1) f(li, lj);
+        const int i = (int)(ti * 16 + threadIdx.y) + 4 * m;
+        if (i < n0) f(r0 + i, (int64_t)lj);
       }
     }
   }
@@ -191,14 +226,21 @@ size_t fs_prof_mark(void);
 void fs_prof_drop_after(size_t from, int last_real_tag, int cls_empty_at_last);
 void fs_prof_begin(int cls, cudaStream_t st);
 void fs_prof_end(int cls, cudaStream_t st);
+// FSGPU_NCU_CLASSES=<bit mask of PROF_*> (read once): launches inside scopes of those classes are bracketed by
+// cudaProfilerStart / Stop, so `ncu --profile-from-start off` captures exactly them (e.g. only the
+// level-0 kernels of the V-cycle) instead of the thousands of small coarse-level launches of a step
+extern unsigned int g_ncu_mask;
+void fs_ncu_range(bool begin);
 struct ProfScope {
   int cls;
   cudaStream_t st;
-  bool on;
-  ProfScope(int c, cudaStream_t s) : cls(c), st(s), on((g_prof_mask >> c) & 1u) {
+  bool on, ncu;
+  ProfScope(int c, cudaStream_t s) : cls(c), st(s), on((g_prof_mask >> c) & 1u), ncu((g_ncu_mask >> c) & 1u) {
     if (on) fs_prof_begin(cls, st);
+    if (ncu) fs_ncu_range(true);
   }
   ~ProfScope() {
+    if (ncu) fs_ncu_range(false);
     if (on) fs_prof_end(cls, st);
   }
 };

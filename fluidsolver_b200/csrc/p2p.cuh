@@ -46,7 +46,9 @@ __device__ __forceinline__ volatile int* p2p_dev_err(char* mine) {
 // per (destination, source), then a fold in rank order -- the same order on every rank, so the result
 // is bitwise identical everywhere (the PCG control flow relies on that).  Two value slots per source
 // (epoch parity) suffice: a rank can only be one reduction ahead of a peer.
-__device__ inline double p2p_allreduce_sum1(const P2PRedDev& a, double v) {
+// (not inlined: it runs once per launch in one thread, and inlined it costs the hot kernels registers -- k_matvec_dot
+// went from 32 to 40 and lost two resident CTAs per SM)
+static __device__ __noinline__ double p2p_allreduce_sum1(const P2PRedDev& a, double v) {
   char* mine = a.peer[a.rank];
   if (*p2p_dev_err(mine)) return v;  // an earlier wait timed out: fail fast, the host reports it
   const unsigned long long e = ++*p2p_red_epoch(mine);

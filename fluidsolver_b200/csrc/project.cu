@@ -19,19 +19,22 @@ namespace {
 
 constexpr int BX = 64, BY = 4;
 
+// uniform divisors of a launch (DivBy: the reference's divisions, correctly rounded, without the division)
+struct Divs { DivBy dx, dy, dt; };
+
 __device__ __forceinline__ double div_at(const double* __restrict__ U, const double* __restrict__ V,
-                                         int64_t k, int64_t P, double dx, double dy) {
-  return (__ldg(U + k + P) - __ldg(U + k)) / dx + (__ldg(V + k + 1) - __ldg(V + k)) / dy;
+                                         int64_t k, int64_t P, const Divs& q) {
+  return q.dx(__ldg(U + k + P) - __ldg(U + k)) + q.dy(__ldg(V + k + 1) - __ldg(V + k));
 }
 
 __global__ void __launch_bounds__(BX* BY)
 k_divergence(const double* __restrict__ U, const double* __restrict__ V, double* __restrict__ div,
-             const Geom g) {
+             const Geom g, const Divs q) {
   const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
   const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
   if (a >= g.a_hi || b > g.ny + 1) return;
   const int64_t k = g.idx(a, b);
-  div[k] = div_at(U, V, k, g.pitch, g.dx, g.dy);
+  div[k] = div_at(U, V, k, g.pitch, q);
 }
 
 // rhs = -vol * div / dt on all cells; zero on the Dirichlet side; block partial sums of rhs.
@@ -39,7 +42,7 @@ k_divergence(const double* __restrict__ U, const double* __restrict__ V, double*
 template <bool FROM_UV>
 __global__ void __launch_bounds__(BX* BY)
 k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __restrict__ div,
-      double* __restrict__ rhs, const Geom g, double dt, int psd, double* part, unsigned int* ticket,
+      double* __restrict__ rhs, const Geom g, const Divs q, int psd, double* part, unsigned int* ticket,
       double* out) {
   double v[1] = {0.0};
   const double vol = g.dx * g.dy;
@@ -47,12 +50,12 @@ k_rhs(const double* __restrict__ U, const double* __restrict__ V, double* __rest
     const int64_t k = g.idx(a, b);
     double d;
     if (FROM_UV) {  // the reference's operation order (Operators.hpp:36-39): true divisions by dx, dy
-      d      = div_at(U, V, k, g.pitch, g.dx, g.dy);
+      d      = div_at(U, V, k, g.pitch, q);
       div[k] = d;
     } else {
       d = div[k];
     }
-    double r = -vol * d / dt;  // LinearSystem.hpp:134
+    double r = q.dt(__dmul_rn(-vol, d));  // -vol * div / dt, LinearSystem.hpp:134
     if ((psd == FSGPU_PSD_LEFT && a == 0) || (psd == FSGPU_PSD_RIGHT && a == g.nx + 1) ||
         (psd == FSGPU_PSD_BOTTOM && b == 0) || (psd == FSGPU_PSD_TOP && b == g.ny + 1))
       r = 0.0;
@@ -96,7 +99,7 @@ template <bool SHIFT>
 __global__ void __launch_bounds__(BX* BY)
 k_project(const double* __restrict__ dpi, double* __restrict__ dpo, double* __restrict__ p, double* __restrict__ U,
           double* __restrict__ V, const double* __restrict__ ru, const double* __restrict__ rv,
-          const double* __restrict__ sum, const Geom g, double dt) {
+          const double* __restrict__ sum, const Geom g, const Divs q, double dt) {
   const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
   const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
   if (a >= g.a_hi || b > g.ny + 1) return;
@@ -106,12 +109,12 @@ k_project(const double* __restrict__ dpi, double* __restrict__ dpo, double* __re
   // U(i,j) for i in [0,NX], j in [0,NY): a in [1,NX+1], b in [1,NY]
   if (a >= 1 && b >= 1 && b <= g.ny) {
     const double dm = SHIFT ? __ldg(dpi + k - P) - c : __ldg(dpi + k - P);
-    U[k] -= (d0 - dm) / g.dx * dt / __ldg(ru + k);
+    U[k] -= __dmul_rn(q.dx(d0 - dm), dt) / __ldg(ru + k);
   }
   // V(i,j) for i in [0,NX), j in [0,NY]: a in [1,NX], b in [1,NY+1]
   if (a >= 1 && a <= g.nx && b >= 1) {
     const double dm = SHIFT ? __ldg(dpi + k - 1) - c : __ldg(dpi + k - 1);
-    V[k] -= (d0 - dm) / g.dy * dt / __ldg(rv + k);
+    V[k] -= __dmul_rn(q.dy(d0 - dm), dt) / __ldg(rv + k);
   }
   p[k] += d0;
   if (SHIFT) dpo[k] = d0;
@@ -233,6 +236,7 @@ int fs_ensure_part(fsgpu_ctx* c, size_t doubles) {
   return comm_alloc_fence(c);
 }
 
+static Divs make_divs(const Geom& g, double dt) { return Divs{make_div_by(g.dx), make_div_by(g.dy), make_div_by(dt)}; }
 static dim3 cell_grid(const Geom& g) {  // the owned cell rows
   return dim3((unsigned)cdiv(g.ny + 2, BX), (unsigned)cdiv(g.a_hi - g.a_lo, BY));
 }
@@ -242,7 +246,7 @@ static dim3 ext_grid(int64_t m2, int64_t n2) {
 
 int fs_launch_divergence(fsgpu_ctx* c) {
   k_divergence<<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V],
-                                                                c->f[FSGPU_DIV], c->g);
+                                                                c->f[FSGPU_DIV], c->g, make_divs(c->g, 1.0));
   FS_LAUNCHED();
   return 0;
 }
@@ -253,11 +257,11 @@ int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
   if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
   if (div_from_uv)
     k_rhs<true><<<pg, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
-                                                    c->f[FSGPU_RHS], c->g, dt, psd, c->part, c->ticket,
+                                                    c->f[FSGPU_RHS], c->g, make_divs(c->g, dt), psd, c->part, c->ticket,
                                                     c->red_out);
   else
     k_rhs<false><<<pg, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_DIV],
-                                                     c->f[FSGPU_RHS], c->g, dt, psd, c->part, c->ticket,
+                                                     c->f[FSGPU_RHS], c->g, make_divs(c->g, dt), psd, c->part, c->ticket,
                                                      c->red_out);
   FS_LAUNCHED();
   if (psd == FSGPU_PSD_NONE) {  // subtract the arithmetic mean over all (NX+2)(NY+2) entries: sum / size (LinearSystem.hpp:150-152)
@@ -300,12 +304,12 @@ int fs_launch_correct(fsgpu_ctx* c, double dt, bool shift, bool sum_ready) {
   if (shift) {
     k_project<true><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
         c->f[FSGPU_DELTA_P], c->f[FSGPU_RHS], c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
-        c->f[FSGPU_RHO_V], c->red_out + 1, c->g, dt);
+        c->f[FSGPU_RHO_V], c->red_out + 1, c->g, make_divs(c->g, dt), dt);
     std::swap(c->f[FSGPU_DELTA_P], c->f[FSGPU_RHS]);
   } else {
     k_project<false><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
         c->f[FSGPU_DELTA_P], nullptr, c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
-        c->f[FSGPU_RHO_V], c->red_out + 1, c->g, dt);
+        c->f[FSGPU_RHO_V], c->red_out + 1, c->g, make_divs(c->g, dt), dt);
   }
   FS_LAUNCHED();
   const int fl[3] = {FSGPU_U, FSGPU_V, FSGPU_P};

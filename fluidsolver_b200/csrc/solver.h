@@ -134,6 +134,9 @@ struct fsgpu_ps {
   PcgScal* scal = nullptr;   // device
   PcgScal* h_scal = nullptr; // pinned, FS_LAG + 1 slots
   cudaEvent_t ev[4] = {};
+  // launches sweeping at least this many points use the TMA-fed marching kernels (0: never).  Environment, read
+  // by fsgpu_ps_create: FSGPU_RING=0 turns them off, FSGPU_RING_MIN_POINTS moves the threshold.
+  int64_t ring_min_points = 1 << 20;
   bool is_setup = false;
   bool levels_allocated = false;
   double last_dt = 0.0;

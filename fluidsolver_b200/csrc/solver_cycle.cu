@@ -23,61 +23,10 @@
 #ifndef FS_MARCH_MINB
 #define FS_MARCH_MINB 8
 #endif
-// k_up_march operand policy: 0 load dinv and pc; 1 recompute both (two divisions per point);
-// 2 load dinv, recompute pc (half a division per point on an i-coarsened level)
-#ifndef FS_UP_MODE
-#define FS_UP_MODE 1
-#endif
-#ifndef FS_UP_PREFETCH
-#define FS_UP_PREFETCH 0
-#endif
-// marching kernels: rows ahead whose operands are pulled into L2 with prefetch.global.L2 (0 = off).
-// The kernels are latency bound (ncu: long-scoreboard stalls, DRAM 61 % busy, 30 warps/SM at 64
-// registers); an L2 prefetch adds memory-level parallelism without costing a register.  A/B variant
-// for scripts/build_variants.py (-DFS_PF_ROWS=4), not yet timed.
-#ifndef FS_PF_ROWS
-#define FS_PF_ROWS 0
-#endif
-// k_up_march: operand rows fetched FS_UP_ASYNC rows ahead with cp.async (LDGSTS) into a thread-private
-// shared-memory ring instead of into registers (0 = off).  Every thread copies and later reads only
-// its own words, so no barrier is needed -- cp.async.wait_group alone orders the ring; the depth
-// is bought with shared memory (7 KB per row ahead and CTA) instead of registers.  A/B variant for
-// scripts/build_variants.py (-DFS_UP_ASYNC=4), NOT yet run on hardware.
-#ifndef FS_UP_ASYNC
-#define FS_UP_ASYNC 0
-#endif
-// the same ring for the five operand words per row of k_down_march0 / k_down_march1 on ACTIVE levels
-#ifndef FS_DOWN_ASYNC
-#define FS_DOWN_ASYNC 0
-#endif
-#if FS_DOWN_ASYNC > 6
-#error "FS_DOWN_ASYNC: at most 6 rows ahead"
-#endif
-#if FS_UP_ASYNC > 0 && (FS_UP_MODE != 1 || FS_UP_PREFETCH != 0 || FS_UP_ASYNC > 6)
-#error "FS_UP_ASYNC needs FS_UP_MODE == 1, FS_UP_PREFETCH == 0 and a depth of at most 6 rows (48 KB static shared memory)"
-#endif
 
 namespace {
 
 constexpr int BX = 64, BY = 4;
-
-// one lane in eight touches the line (a warp row is 256 B = 2-3 lines of 128 B)
-__device__ __forceinline__ void pf_l2(const double* p, int lane) {
-#if FS_PF_ROWS > 0
-  if ((lane & 7) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-#else
-  (void)p; (void)lane;
-#endif
-}
-
-// 8-byte asynchronous global -> shared copy (LDGSTS) and the two group operations of the variants above
-__device__ __forceinline__ void cp_async8(double* dst, const double* src) {
-  const unsigned sa = (unsigned)__cvta_generic_to_shared(dst);
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // 1 / v with the convention of the stored dinv / pc arrays (0 where v == 0: pads, halo-less walls,
 // a singular coarsest point).  The active-level kernels recompute dinv = 1/d and the interpolation
@@ -85,6 +34,46 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // per point buy 16 B/point less HBM traffic, and the values are bit-identical to the stored ones
 // (same operands, same association as k_interp / k_rap, correctly rounded division).
 __device__ __forceinline__ double rcp0(double v) { return v != 0.0 ? 1.0 / v : 0.0; }
+
+// The per-point arithmetic of the marching kernels, with the multiply-add contraction written out:
+// a sum of two products can be fused either way round, and the register-pipelined and the TMA-fed
+// version of a kernel must round alike to stay bit-identical (tests/test_gpu_solver.py).
+// residual of the zero-guess Jacobi iterate X = w b / d:  b - (w b + sum of the four couplings * X)
+__device__ __forceinline__ double mg_resid(double w, double b, double ca, double Xa, double cb, double Xb,
+                                           double cl, double Xl, double cr, double Xr) {
+  double v = __dmul_rn(w, b);
+  v = fma(ca, Xa, v);
+  v = fma(cb, Xb, v);
+  v = fma(cl, Xl, v);
+  v = fma(cr, Xr, v);
+  return b - v;
+}
+// restriction  R + (-cm pm) Rm + (-cp pp) Rp
+__device__ __forceinline__ double mg_restrict(double R, double cm, double pm, double Rm, double cp, double pp,
+                                              double Rp) {
+  double v = fma(__dmul_rn(-cm, pm), Rm, R);
+  return fma(__dmul_rn(-cp, pp), Rp, v);
+}
+// interpolation at an F point  (-cm pc) xm + (-cp pc) xp
+__device__ __forceinline__ double mg_interp(double cm, double cp, double pc, double xm, double xp) {
+  const double v = __dmul_rn(__dmul_rn(-cm, pc), xm);
+  return fma(__dmul_rn(-cp, pc), xp, v);
+}
+// pre-relaxed iterate + interpolated correction  w b / d + xi
+__device__ __forceinline__ double mg_x0(double w, double b, double dinv, double xi) {
+  return fma(__dmul_rn(w, b), dinv, xi);
+}
+// post-relaxation  x0 + w (b - A x0) / d
+__device__ __forceinline__ double mg_post(double w, double b, double d, double dinv, double x0, double ca,
+                                          double xa, double cb, double xb, double cl, double xl, double cr,
+                                          double xr) {
+  double v = __dmul_rn(d, x0);
+  v = fma(ca, xa, v);
+  v = fma(cb, xb, v);
+  v = fma(cl, xl, v);
+  v = fma(cr, xr, v);
+  return fma(__dmul_rn(w, b - v), dinv, x0);
+}
 
 template <int CDIR>
 struct Coef {
@@ -94,95 +83,68 @@ struct Coef {
   __device__ __forceinline__ double ap(int64_t q) const { return CDIR == 0 ? __ldg(cx + q + P) : __ldg(cy + q + 1); }
 };
 
-// ---- marching restriction kernels (same strip / chunk scheme as k_up_march below) -------------
+// ---- work partition of the marching kernels --------------------------------------------------------
+// A level is cut into tasks of `mr` rows x one column strip, numbered block-row by block-row, and dealt
+// round-robin to the resident CTAs: the CTAs that run together then sweep neighbouring strips of the same
+// few row blocks (a compact set of DRAM pages / TLB entries; handing every CTA one long private run of
+// rows instead measured 8-30 % SLOWER at 8192^2).  Balance comes from the host's choice of mr
+// (pick_rows): the task count lands just under a multiple of the grid size, so no round of the deal is
+// left partly filled (a fixed mr = 64 gave 8832 tasks on 1184 resident CTAs: 7.46 rounds paid as 8).
+struct MarchCursor {
+  int t, total, strips, mr, lo, hi;
+  __device__ MarchCursor(int strips_, int lo_, int hi_, int mr_)
+      : t(blockIdx.x), strips(strips_), mr(mr_), lo(lo_), hi(hi_) {
+    total = strips * ((hi - lo + mr - 1) / mr);
+  }
+  __device__ bool next(int& sp, int& r0, int& r1) {
+    if (t >= total) return false;
+    const int ch = t / strips;
+    sp = t - ch * strips;
+    r0 = lo + ch * mr;
+    r1 = min(r0 + mr, hi);
+    t += gridDim.x;
+    return true;
+  }
+};
+
+// ---- marching restriction kernels (same strip / task scheme as k_up_march below) --------------
 // k_down_march0: coarsening along i.  Per fine row the warp forms X = w b / d, then the residual
 // R of the row above from three rows of X held in registers (left/right by shuffle), and on every
 // second row the coarse rhs  b_c = R + pp(row-1) R(row-1) + pm(row+1) R(row+1).
 template <bool ACTIVE>
 __global__ void __launch_bounds__(128, FS_MARCH_MINB)
 k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
-              double* __restrict__ cb, double w, int mrc, const PcgScal* scal) {
+              double* __restrict__ cb, double w, int mr, const PcgScal* scal) {
   if (scal->done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int n1 = (int)f.n1, c_lo = (int)c.i0, c_hi = (int)c.i1, P = (int)f.pitch, Pc = (int)c.pitch,
-            foff = (int)c.foff;
-  const int strips = (n1 + 119) / 120;
-  const int total  = strips * ((c_hi - c_lo + mrc - 1) / mrc);
-  for (int t = blockIdx.x; t < total; t += gridDim.x) {
-    const int ch = t / strips, sp = t - ch * strips;
+  const int n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  MarchCursor cur((n1 + 119) / 120, (int)c.i0, (int)c.i1, mr);  // rows of a task: coarse rows
+  int sp, c0, c1;
+  while (cur.next(sp, c0, c1)) {
     int lj = sp * 120 + warp * 30 - 1 + lane;
     const bool store_lane = lane >= 1 && lane <= 30 && lj < n1;
     if (lj > n1) lj = n1;
-    const int c0 = c_lo + ch * mrc, c1 = min(c0 + mrc, c_hi);
     const int f0 = 2 * c0 + foff, fL = 2 * (c1 - 1) + foff;
     double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx2 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0, Ra = 0.0, Rb = 0.0;
     double pc1 = 0.0, pc2 = 0.0, pc3 = 0.0;  // ACTIVE: pc of rows li - 1, li - 2, li - 3
     int li = f0 - 2;
     int o  = (li + FS_RO) * P + lj + FS_CO;
-#if FS_DOWN_ASYNC > 0
-    __shared__ double ring[FS_DOWN_ASYNC][5][128];
-    const int tx = threadIdx.x;
-    auto issue_row = [&](int o_, int sl) {
-      cp_async8(&ring[sl][0][tx], fb + o_);
-      cp_async8(&ring[sl][1][tx], f.cx + o_);
-      cp_async8(&ring[sl][2][tx], f.d + o_);
-      cp_async8(&ring[sl][3][tx], f.cy + o_);
-      cp_async8(&ring[sl][4][tx], f.cy + o_ + 1);
-    };
-    int slot = 0;
-    if (ACTIVE) {
-#pragma unroll
-      for (int dd = 0; dd < FS_DOWN_ASYNC; ++dd) {
-        if (li + dd <= fL + 2) issue_row(o + dd * P, dd);
-        cp_async_commit();
-      }
-    }
-#endif
 #pragma unroll 2
     for (; li <= fL + 2; ++li, o += P) {
-#if FS_PF_ROWS > 0
-      if (li + FS_PF_ROWS <= fL + 2) {
-        const int op = o + FS_PF_ROWS * P;
-        pf_l2(fb + op, lane); pf_l2(f.cx + op, lane);
-        if (ACTIVE) { pf_l2(f.d + op, lane); pf_l2(f.cy + op, lane); }
-      }
-#endif
-#if FS_DOWN_ASYNC > 0
-      double b0, cx0, X0 = 0.0, cy0 = 0.0, cy0p = 0.0, pc0 = 0.0;
-      if (ACTIVE) {
-        cp_async_wait<FS_DOWN_ASYNC - 1>();  // row li has landed in its slot
-        b0   = ring[slot][0][tx];
-        cx0  = ring[slot][1][tx];
-        const double d0 = ring[slot][2][tx];
-        cy0  = ring[slot][3][tx];
-        cy0p = ring[slot][4][tx];
-        X0   = w * b0 * rcp0(d0);
-        pc0  = rcp0(d0 + cy0 + cy0p);
-      } else {
-        b0  = __ldg(fb + o);
-        cx0 = __ldg(f.cx + o);
-      }
-#else
       const double b0 = __ldg(fb + o), cx0 = __ldg(f.cx + o);
       double X0 = 0.0, cy0 = 0.0, cy0p = 0.0, pc0 = 0.0;
       if (ACTIVE) {
         const double d0 = __ldg(f.d + o);
         cy0  = __ldg(f.cy + o);
         cy0p = __ldg(f.cy + o + 1);
-        X0   = w * b0 * rcp0(d0);
+        X0   = __dmul_rn(__dmul_rn(w, b0), rcp0(d0));
         pc0  = rcp0(d0 + cy0 + cy0p);
       }
-#endif
       // residual of row li - 1
       double Rn;
       if (ACTIVE) {
         const double xl = __shfl_up_sync(0xffffffffu, X1, 1), xr = __shfl_down_sync(0xffffffffu, X1, 1);
-        double v = w * b1;
-        v += cx1 * X2;
-        v += cx0 * X0;
-        v += cy1 * xl;
-        v += cy1p * xr;
-        Rn = b1 - v;
+        Rn = mg_resid(w, b1, cx1, X2, cx0, X0, cy1, xl, cy1p, xr);
       } else {
         Rn = b1;
       }
@@ -190,20 +152,11 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
       if (li >= f0 + 2 && ((li - f0) & 1) == 0) {
         const double pcm = ACTIVE ? pc3 : __ldg(f.pc + o - 3 * P);
         const double pcp = ACTIVE ? pc1 : __ldg(f.pc + o - P);
-        double v = Rb;
-        v += (-cx2 * pcm) * Ra;
-        v += (-cx1 * pcp) * Rn;
+        const double v = mg_restrict(Rb, cx2, pcm, Ra, cx1, pcp, Rn);
         if (store_lane) cb[(((li - 2 - foff) >> 1) + FS_RO) * Pc + lj + FS_CO] = v;
       }
       X2 = X1; X1 = X0; b1 = b0; cx2 = cx1; cx1 = cx0; cy1 = cy0; cy1p = cy0p; Ra = Rb; Rb = Rn;
       pc3 = pc2; pc2 = pc1; pc1 = pc0;
-#if FS_DOWN_ASYNC > 0
-      if (ACTIVE) {  // refill the slot just consumed
-        if (li + FS_DOWN_ASYNC <= fL + 2) issue_row(o + FS_DOWN_ASYNC * P, slot);
-        cp_async_commit();
-        slot = slot + 1 == FS_DOWN_ASYNC ? 0 : slot + 1;
-      }
-#endif
     }
   }
 }
@@ -216,103 +169,43 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
               double* __restrict__ cb, double w, int mr, const PcgScal* scal) {
   if (scal->done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int f_lo = (int)f.i0, f_hi = (int)f.i1, n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch,
-            foff = (int)c.foff;
-  const int strips = (n1 + 111) / 112;
-  const int total  = strips * ((f_hi - f_lo + mr - 1) / mr);
-  for (int t = blockIdx.x; t < total; t += gridDim.x) {
-    const int ch = t / strips, sp = t - ch * strips;
+  const int n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  MarchCursor cur((n1 + 111) / 112, (int)f.i0, (int)f.i1, mr);
+  int sp, r0, r1;
+  while (cur.next(sp, r0, r1)) {
     int lj = sp * 112 + warp * 28 - 2 + lane;
     const int pos = lj - foff;
     const bool store_lane = lane >= 2 && lane <= 29 && lj < n1 && (pos & 1) == 0;
     const int oc_col = (pos >> 1) + FS_CO;
     if (lj > n1) lj = n1;
-    const int r0 = f_lo + ch * mr, r1 = min(r0 + mr, f_hi);
     double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0, d1 = 0.0;
     int li = r0 - 1;
     int o  = (li + FS_RO) * P + lj + FS_CO;
-#if FS_DOWN_ASYNC > 0
-    __shared__ double ring[FS_DOWN_ASYNC][5][128];
-    const int tx = threadIdx.x;
-    auto issue_row = [&](int o_, int sl) {
-      cp_async8(&ring[sl][0][tx], fb + o_);
-      cp_async8(&ring[sl][1][tx], f.cy + o_);
-      cp_async8(&ring[sl][2][tx], f.cy + o_ + 1);
-      cp_async8(&ring[sl][3][tx], f.d + o_);
-      cp_async8(&ring[sl][4][tx], f.cx + o_);
-    };
-    int slot = 0;
-    if (ACTIVE) {
-#pragma unroll
-      for (int dd = 0; dd < FS_DOWN_ASYNC; ++dd) {
-        if (li + dd <= r1) issue_row(o + dd * P, dd);
-        cp_async_commit();
-      }
-    }
-#endif
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
-#if FS_PF_ROWS > 0
-      if (li + FS_PF_ROWS <= r1) {
-        const int op = o + FS_PF_ROWS * P;
-        pf_l2(fb + op, lane); pf_l2(f.cy + op, lane);
-        if (ACTIVE) { pf_l2(f.d + op, lane); pf_l2(f.cx + op, lane); }
-      }
-#endif
-#if FS_DOWN_ASYNC > 0
-      double b0, cy0, cy0p, X0 = 0.0, cx0 = 0.0, d0 = 0.0;
-      if (ACTIVE) {
-        cp_async_wait<FS_DOWN_ASYNC - 1>();  // row li has landed in its slot
-        b0   = ring[slot][0][tx];
-        cy0  = ring[slot][1][tx];
-        cy0p = ring[slot][2][tx];
-        d0   = ring[slot][3][tx];
-        cx0  = ring[slot][4][tx];
-        X0   = w * b0 * rcp0(d0);
-      } else {
-        b0   = __ldg(fb + o);
-        cy0  = __ldg(f.cy + o);
-        cy0p = __ldg(f.cy + o + 1);
-      }
-#else
       const double b0 = __ldg(fb + o);
       const double cy0 = __ldg(f.cy + o), cy0p = __ldg(f.cy + o + 1);
       double X0 = 0.0, cx0 = 0.0, d0 = 0.0;
       if (ACTIVE) {
         d0  = __ldg(f.d + o);
-        X0  = w * b0 * rcp0(d0);
+        X0  = __dmul_rn(__dmul_rn(w, b0), rcp0(d0));
         cx0 = __ldg(f.cx + o);
       }
-#endif
       if (li > r0) {  // row li - 1
         double Rn;
         if (ACTIVE) {
           const double xl = __shfl_up_sync(0xffffffffu, X1, 1), xr = __shfl_down_sync(0xffffffffu, X1, 1);
-          double v = w * b1;
-          v += cx1 * X2;
-          v += cx0 * X0;
-          v += cy1 * xl;
-          v += cy1p * xr;
-          Rn = b1 - v;
+          Rn = mg_resid(w, b1, cx1, X2, cx0, X0, cy1, xl, cy1p, xr);
         } else {
           Rn = b1;
         }
         const double pcv = ACTIVE ? rcp0(d1 + cx1 + cx0) : __ldg(f.pc + o - P);
         const double pcl = __shfl_up_sync(0xffffffffu, pcv, 1), pcr = __shfl_down_sync(0xffffffffu, pcv, 1);
         const double Rl = __shfl_up_sync(0xffffffffu, Rn, 1), Rr = __shfl_down_sync(0xffffffffu, Rn, 1);
-        double v = Rn;
-        v += (-cy1 * pcl) * Rl;
-        v += (-cy1p * pcr) * Rr;
+        const double v = mg_restrict(Rn, cy1, pcl, Rl, cy1p, pcr, Rr);
         if (store_lane) cb[(li - 1 + FS_RO) * Pc + oc_col] = v;
       }
       X2 = X1; X1 = X0; b1 = b0; cx1 = cx0; cy1 = cy0; cy1p = cy0p; d1 = d0;
-#if FS_DOWN_ASYNC > 0
-      if (ACTIVE) {  // refill the slot just consumed
-        if (li + FS_DOWN_ASYNC <= r1) issue_row(o + FS_DOWN_ASYNC * P, slot);
-        cp_async_commit();
-        slot = slot + 1 == FS_DOWN_ASYNC ? 0 : slot + 1;
-      }
-#endif
     }
   }
 }
@@ -360,197 +253,255 @@ k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
 // registers, takes the left/right neighbours by warp shuffle, and emits
 // x = x0 + w (b - A x0) / d  for the row above.  No shared memory, no block barrier, 32-bit
 // offsets advanced by one pitch per row; every array is read once (plus the 2/32 column and
-// 2/MR row overlap).  CTAs loop over (strip, chunk) tasks, so the optional dot product <b, x>
-// (= <r, z> of PCG on level 0) ends in ~1e3 partials.
+// 2/MR row overlap).  dinv and pc are recomputed from d, cx, cy (rcp0 above).  CTAs loop over
+// (strip, chunk) tasks, so the optional dot product <b, x> (= <r, z> of PCG on level 0) ends in
+// ~1e3 partials.
 // DOT: 0 none, 1 PCG iteration (convergence test + beta), 2 first V-cycle (bi).
-// FS_MWARPS: warps (= adjacent 30-column strips) per CTA of k_up_march; A/B variant (-DFS_MWARPS=8 keeps the
-// resident warps per SM: the CTA count per SM scales down with it)
-#ifndef FS_MWARPS
-#define FS_MWARPS 4
-#endif
-constexpr int MOUT = 30, MWARPS = FS_MWARPS;
+constexpr int MOUT = 30, MWARPS = 4;
 
 template <int CDIR, int DOT>
-__global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB * 4 / MWARPS)
+__global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB)
 k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
-           const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part,
-           unsigned int* ticket) {
+           const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket) {
   if (scal->done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int f_lo = (int)f.i0, f_hi = (int)f.i1, n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch,
-            foff = (int)c.foff;
-  const int strips = (n1 + MOUT * MWARPS - 1) / (MOUT * MWARPS);
-  const int total  = strips * ((f_hi - f_lo + mr - 1) / mr);
+  const int n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  MarchCursor cur((n1 + MOUT * MWARPS - 1) / (MOUT * MWARPS), (int)f.i0, (int)f.i1, mr);
   double acc[1] = {0.0};
-#if FS_UP_ASYNC > 0
-  // [row slot][operand][thread]: a warp's lanes touch 32 consecutive words of a bank row
-  __shared__ double ring[FS_UP_ASYNC][7][32 * MWARPS];
-  auto cpa = [](double* dst, const double* src) {
-    const unsigned sa = (unsigned)__cvta_generic_to_shared(dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(src) : "memory");
-  };
-#endif
-  for (int t = blockIdx.x; t < total; t += gridDim.x) {
-    const int ch = t / strips, sp = t - ch * strips;
+  int sp, r0, r1;
+  while (cur.next(sp, r0, r1)) {
     int lj = sp * (MOUT * MWARPS) + warp * MOUT - 1 + lane;  // lane 0 sits one column left
     const bool store_lane = lane >= 1 && lane <= MOUT && lj < n1;
     if (lj > n1) lj = n1;  // the zero pad column right of the grid
-    const int r0 = f_lo + ch * mr, r1 = min(r0 + mr, f_hi);
     double x0p = 0.0, x0c = 0.0, bc = 0.0, dic = 0.0, dc = 0.0, cyc = 0.0, cy1c = 0.0, cxc = 0.0;
     int li = r0 - 1;
     int o  = (li + FS_RO) * P + lj + FS_CO;
     double cxn = __ldg(f.cx + o);
-    // operands of one row, loaded one row AHEAD of their use (software pipelining: the loads of
-    // row li + 1 are in flight while row li is computed, independent of what the compiler hoists)
-    struct Row { double b, d, di, cy, cy1, cxnn, xm, xp, pc; };
+    // operands of one row
+    struct Row { double b, d, cy, cy1, cxnn, xm, xp; };
     auto load_row = [&](int li_, int o_) {
       Row q;
       q.cxnn = __ldg(f.cx + o_ + P);
       q.b    = __ldg(fb + o_);
       q.cy   = __ldg(f.cy + o_);
       q.cy1  = __ldg(f.cy + o_ + 1);
-#if FS_UP_MODE == 1
-      q.d = __ldg(f.d + o_);  q.di = 0.0;  q.pc = 0.0;
-#elif FS_UP_MODE == 2
-      q.d = __ldg(f.d + o_);  q.di = __ldg(f.dinv + o_);  q.pc = 0.0;
-#else
-      q.d = __ldg(f.d + o_);  q.di = __ldg(f.dinv + o_);  q.pc = 0.0;
-#endif
+      q.d    = __ldg(f.d + o_);
       if (CDIR == 0) {
         const int pos = li_ - foff, par = pos & 1;
         const int oc  = (((pos - par) >> 1) + FS_RO) * Pc + lj + FS_CO;
         q.xm = __ldg(xc + oc);
         q.xp = par ? __ldg(xc + oc + Pc) : 0.0;
-#if FS_UP_MODE == 0
-        if (par) q.pc = __ldg(f.pc + o_);
-#endif
       } else {
         const int pos = lj - foff, par = pos & 1;
         const int oc  = (li_ + FS_RO) * Pc + ((pos - par) >> 1) + FS_CO;
         q.xm = __ldg(xc + oc);
         q.xp = __ldg(xc + oc + 1);
-#if FS_UP_MODE == 0
-        q.pc = __ldg(f.pc + o_);
-#endif
       }
       return q;
     };
-#if FS_UP_PREFETCH
-    Row nx = load_row(li, o);
-#endif
-#if FS_UP_ASYNC > 0
-    // the seven operand words of row li_ (the same addresses load_row reads) into ring slot sl
-    auto issue_row = [&](int li_, int o_, int sl) {
-      const int tx = threadIdx.x;
-      cpa(&ring[sl][0][tx], f.cx + o_ + P);
-      cpa(&ring[sl][1][tx], fb + o_);
-      cpa(&ring[sl][2][tx], f.cy + o_);
-      cpa(&ring[sl][3][tx], f.cy + o_ + 1);
-      cpa(&ring[sl][4][tx], f.d + o_);
-      if (CDIR == 0) {
-        const int pos = li_ - foff, par = pos & 1;
-        const int oc  = (((pos - par) >> 1) + FS_RO) * Pc + lj + FS_CO;
-        cpa(&ring[sl][5][tx], xc + oc);
-        if (par) cpa(&ring[sl][6][tx], xc + oc + Pc);
-      } else {
-        const int pos = lj - foff, par = pos & 1;
-        const int oc  = (li_ + FS_RO) * Pc + ((pos - par) >> 1) + FS_CO;
-        cpa(&ring[sl][5][tx], xc + oc);
-        cpa(&ring[sl][6][tx], xc + oc + 1);
-      }
-    };
-    auto read_row = [&](int li_, int sl) {
-      const int tx = threadIdx.x;
-      Row q;
-      q.cxnn = ring[sl][0][tx];
-      q.b    = ring[sl][1][tx];
-      q.cy   = ring[sl][2][tx];
-      q.cy1  = ring[sl][3][tx];
-      q.d    = ring[sl][4][tx];
-      q.di = 0.0;  q.pc = 0.0;
-      q.xm = ring[sl][5][tx];
-      q.xp = (CDIR == 0 && (((li_ - foff) & 1) == 0)) ? 0.0 : ring[sl][6][tx];
-      return q;
-    };
-#pragma unroll
-    for (int dd = 0; dd < FS_UP_ASYNC; ++dd) {  // one group per row, empty past the chunk's last row
-      if (li + dd <= r1) issue_row(li + dd, o + dd * P, dd);
-      asm volatile("cp.async.commit_group;" ::: "memory");
-    }
-    int slot = 0;
-#endif
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
-#if FS_PF_ROWS > 0
-      if (li + FS_PF_ROWS <= r1) {  // cx is read one row further down than the others
-        const int op = o + FS_PF_ROWS * P;
-        pf_l2(fb + op, lane); pf_l2(f.d + op, lane); pf_l2(f.cy + op, lane); pf_l2(f.cx + op + P, lane);
-      }
-#endif
-#if FS_UP_ASYNC > 0
-      // all but the newest FS_UP_ASYNC - 1 groups have landed: row li is in its slot
-      asm volatile("cp.async.wait_group %0;" ::"n"(FS_UP_ASYNC - 1) : "memory");
-      const Row q = read_row(li, slot);
-#elif FS_UP_PREFETCH
-      const Row q = nx;
-      if (li < r1) nx = load_row(li + 1, o + P);
-#else
       const Row q = load_row(li, o);
-#endif
       const double cxnn = q.cxnn, bn = q.b, dn = q.d, cyn = q.cy, cy1n = q.cy1;
-#if FS_UP_MODE == 1
       const double din = rcp0(dn);
-#else
-      const double din = q.di;
-#endif
       double xi;
       if (CDIR == 0) {
         const int par = (li - foff) & 1;
         if (par == 0) {  // C row (warp uniform)
           xi = q.xm;
         } else {
-#if FS_UP_MODE == 0
-          const double pcv = q.pc;
-#else
-          const double pcv = rcp0(dn + cyn + cy1n);
-#endif
-          double v = (-cxn * pcv) * q.xm;
-          v += (-cxnn * pcv) * q.xp;
-          xi = v;
+          xi = mg_interp(cxn, cxnn, rcp0(dn + cyn + cy1n), q.xm, q.xp);
         }
       } else {
         const int par = (lj - foff) & 1;
-#if FS_UP_MODE == 0
-        const double pcv = q.pc;
-#else
-        const double pcv = rcp0(dn + cxn + cxnn);
-#endif
-        double v = (-cyn * pcv) * q.xm;
-        v += (-cy1n * pcv) * q.xp;
+        const double v = mg_interp(cyn, cy1n, rcp0(dn + cxn + cxnn), q.xm, q.xp);
         xi = par ? v : q.xm;
       }
-      const double x0n = w * bn * din + xi;
+      const double x0n = mg_x0(w, bn, din, xi);
       if (li > r0) {  // emit row li - 1
-        const double dd = dc;
         const double xl = __shfl_up_sync(0xffffffffu, x0c, 1), xr = __shfl_down_sync(0xffffffffu, x0c, 1);
-        double v = dd * x0c;
-        v += cxc * x0p;
-        v += cxn * x0n;
-        v += cyc * xl;
-        v += cy1c * xr;
-        const double xo = x0c + w * (bc - v) * dic;
+        const double xo = mg_post(w, bc, dc, dic, x0c, cxc, x0p, cxn, x0n, cyc, xl, cy1c, xr);
         if (store_lane) {
           fx[o - P] = xo;
           if (DOT) acc[0] += bc * xo;
         }
       }
       x0p = x0c; x0c = x0n; bc = bn; dic = din; dc = dn; cyc = cyn; cy1c = cy1n; cxc = cxn; cxn = cxnn;
-#if FS_UP_ASYNC > 0
-      // refill the slot just consumed (its words are in registers; the clobber keeps the reads above)
-      if (li + FS_UP_ASYNC <= r1) issue_row(li + FS_UP_ASYNC, o + FS_UP_ASYNC * P, slot);
-      asm volatile("cp.async.commit_group;" ::: "memory");
-      slot = slot + 1 == FS_UP_ASYNC ? 0 : slot + 1;
+    }
+  }
+  if (DOT) {
+    double tot[1];
+    if (grid_reduce<ReduceSum, 1>(acc, part, ticket, tot)) {
+      if (threadIdx.x == 0) pcg_local_rz<DOT == 2>(scal, tot[0]);
+    }
+  }
+}
+
+// ---- the same kernel fed by the TMA engine ---------------------------------------------------------
+// k_up_march keeps its loads in registers, so the bytes a warp has in flight are bounded by its
+// register budget (ncu: long-scoreboard stalls, DRAM 61 % busy at 30 resident warps per SM).  Here the
+// operand rows of a CTA's 120-column strip are streamed into a shared-memory ring by bulk asynchronous
+// copies (cp.async.bulk -> UBLKCP: one instruction per 1 KB row segment, issued by ONE thread, no
+// register staging), FS_RING_STAGES rows deep, behind one full / one empty mbarrier per stage.  The four
+// warps consume a row as soon as its bytes have landed and keep the x0 window in registers exactly
+// as above (same arithmetic, same association: results are bit-identical).  Segments start at an even
+// physical column (16-byte aligned source) two columns left of the strip's first output column.
+constexpr int RING_SEG = 128, RING_SLOTS = 6;
+#ifndef FS_RING_STAGES
+#define FS_RING_STAGES 4
 #endif
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* b, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* b, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* b) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* b, unsigned parity) {
+  unsigned ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(double* dst, const double* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// the barriers of the ring (one instance per CTA): `full` is armed by the issuing thread with the bytes of
+// the row, `empty` collects one arrival per consumer warp.
+// Measured alternatives (8192^2, level 0, profiles/r02_ring_variants.txt): 3, 4 and 6 stages run alike;
+// sharing the copies out over the four warps (lane 0 of each announcing and issuing its own segment) was
+// 16 % slower than one issuing thread; b and d by LDG beside a four-array ring 48 % slower; the restriction
+// kernels gained nothing from the ring (507 vs 495 us) and keep their register pipeline.
+template <int NS>
+struct RingBars {
+  unsigned long long full[NS], empty[NS];
+  __device__ void init() {
+    if (threadIdx.x == 0) {
+      for (int q = 0; q < NS; ++q) { mbar_init(&full[q], 1); mbar_init(&empty[q], MWARPS); }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+  }
+};
+
+template <int CDIR, int DOT>
+__global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB)
+k_up_ring(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
+          const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket) {
+  if (scal->done) return;
+  constexpr int S = FS_RING_STAGES;
+  __shared__ __align__(128) double ring[S][RING_SLOTS][RING_SEG];
+  __shared__ __align__(8) RingBars<S> bar;
+  unsigned long long* const full = bar.full;
+  unsigned long long* const empty = bar.empty;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n1 = (int)f.n1, foff = (int)c.foff;
+  const int64_t P = f.pitch, Pc = c.pitch;
+  const int strips = (n1 + MOUT * MWARPS - 1) / (MOUT * MWARPS);
+  bar.init();
+  // producer (thread 0): the CTA's rows form one sequence across its tasks.  Segments of a row:
+  // 0 cx (of the row below), 1 b, 2 cy, 3 d, 4 / 5 coarse x (5: odd rows of CDIR 0 only)
+  MarchCursor pcur(strips, (int)f.i0, (int)f.i1, mr);
+  int psp = 0, pr0 = 0, pr1 = 0, pq = 0;
+  bool pmore = pcur.next(psp, pr0, pr1);
+  unsigned pn = 0;
+  auto issue = [&]() {
+    if (!pmore) return;
+    const int li = pr0 - 1 + pq;
+    const int st = (int)(pn % S);
+    mbar_wait(&empty[st], ((pn / S) & 1u) ^ 1u);  // the consumers are done with the previous tenant
+    const int col0 = psp * (MOUT * MWARPS) + 2;   // physical column (even): logical column of lane 0 minus 1
+    const int64_t o = (int64_t)(li + FS_RO) * P + col0;
+    constexpr unsigned SB = RING_SEG * sizeof(double);
+    if (CDIR == 0) {
+      const int pos = li - foff, par = pos & 1;
+      const int64_t oc = (int64_t)(((pos - par) >> 1) + FS_RO) * Pc + col0;
+      mbar_expect_tx(&full[st], (par ? 6u : 5u) * SB);
+      bulk_g2s(ring[st][4], xc + oc, SB, &full[st]);
+      if (par) bulk_g2s(ring[st][5], xc + oc + Pc, SB, &full[st]);
+    } else {
+      constexpr unsigned CB = 72 * sizeof(double);
+      const int cj0 = ((psp * (MOUT * MWARPS) - 2 - foff) >> 1) & ~1;  // even, <= the leftmost coarse column used
+      mbar_expect_tx(&full[st], 4u * SB + CB);
+      bulk_g2s(ring[st][4], xc + (int64_t)(li + FS_RO) * Pc + cj0 + FS_CO, CB, &full[st]);
+    }
+    bulk_g2s(ring[st][0], f.cx + o + P, SB, &full[st]);
+    bulk_g2s(ring[st][1], fb + o, SB, &full[st]);
+    bulk_g2s(ring[st][2], f.cy + o, SB, &full[st]);
+    bulk_g2s(ring[st][3], f.d + o, SB, &full[st]);
+    ++pn;
+    if (++pq == pr1 - pr0 + 2) { pq = 0; pmore = pcur.next(psp, pr0, pr1); }
+  };
+  if (threadIdx.x == 0)
+    for (int q = 0; q < S - 1; ++q) issue();
+  unsigned cn = 0;
+  double acc[1] = {0.0};
+  MarchCursor cur(strips, (int)f.i0, (int)f.i1, mr);
+  int sp, r0, r1;
+  while (cur.next(sp, r0, r1)) {
+    const int ljr = sp * (MOUT * MWARPS) + warp * MOUT - 1 + lane;  // lane 0 sits one column left
+    const bool store_lane = lane >= 1 && lane <= MOUT && ljr < n1;
+    const bool colok = ljr <= n1;       // lanes right of the zero pad column compute with zeros
+    const int lj = colok ? ljr : n1;
+    const int ti = warp * MOUT + lane + 1;  // my column inside the segments
+    double x0p = 0.0, x0c = 0.0, bc = 0.0, dic = 0.0, dc = 0.0, cyc = 0.0, cy1c = 0.0, cxc = 0.0;
+    int li = r0 - 1;
+    int64_t o = (int64_t)(li + FS_RO) * P + lj + FS_CO;
+    double cxn = __ldg(f.cx + o);
+    int tc = 0;
+    if (CDIR == 1) {
+      const int cj0 = ((sp * (MOUT * MWARPS) - 2 - foff) >> 1) & ~1;
+      const int pos = ljr - foff;
+      tc = ((pos - (pos & 1)) >> 1) - cj0;
+    }
+    for (; li <= r1; ++li, o += P) {
+      if (threadIdx.x == 0) issue();
+      const int st = (int)(cn % S);
+      mbar_wait(&full[st], (cn / S) & 1u);
+      double cxnn = ring[st][0][ti], bn = ring[st][1][ti], cyn = ring[st][2][ti], cy1n = ring[st][2][ti + 1],
+             dn = ring[st][3][ti], xm, xp = 0.0;
+      const int par = CDIR == 0 ? ((li - foff) & 1) : ((ljr - foff) & 1);
+      if (CDIR == 0) {
+        xm = ring[st][4][ti];
+        if (par) xp = ring[st][5][ti];
+      } else {
+        xm = ring[st][4][tc];
+        xp = ring[st][4][tc + 1];
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[st]);
+      ++cn;
+      if (!colok) { cxnn = 0.0; bn = 0.0; cyn = 0.0; cy1n = 0.0; dn = 0.0; xm = 0.0; xp = 0.0; }
+      const double din = rcp0(dn);
+      double xi;
+      if (CDIR == 0) {
+        if (par == 0) {  // C row (warp uniform)
+          xi = xm;
+        } else {
+          xi = mg_interp(cxn, cxnn, rcp0(dn + cyn + cy1n), xm, xp);
+        }
+      } else {
+        const double v = mg_interp(cyn, cy1n, rcp0(dn + cxn + cxnn), xm, xp);
+        xi = par ? v : xm;
+      }
+      const double x0n = mg_x0(w, bn, din, xi);
+      if (li > r0) {  // emit row li - 1
+        const double xl = __shfl_up_sync(0xffffffffu, x0c, 1), xr = __shfl_down_sync(0xffffffffu, x0c, 1);
+        const double xo = mg_post(w, bc, dc, dic, x0c, cxc, x0p, cxn, x0n, cyc, xl, cy1c, xr);
+        if (store_lane) {
+          fx[o - P] = xo;
+          if (DOT) acc[0] += bc * xo;
+        }
+      }
+      x0p = x0c; x0c = x0n; bc = bn; dic = din; dc = dn; cyc = cyn; cy1c = cy1n; cxc = cxn; cxn = cxnn;
     }
   }
   if (DOT) {
@@ -841,20 +792,42 @@ static int coarse_solve(fsgpu_ps* s, int l, const double* b, double* x) {
   return 0;
 }
 
-// rows per marching task: 64 when that still gives every SM several tasks, else smaller chunks
-// (more halo-row overlap, but small levels are latency bound, not bandwidth bound)
+// Rows per marching task.  Bandwidth-bound levels: the height in [40, 96] whose task count fills the
+// rounds of the round-robin deal best (tasks / (rounds x grid)), discounted by the two rows a task re-reads
+// around its range.  Levels with fewer tasks than a few rounds: smaller tasks (they are latency bound; a
+// task's rows are a serial chain of loads), down to one row while the level still fits one wave.
 static int pick_rows(int64_t rows, int64_t strips) {
+  const int64_t G = (int64_t)FS_NUM_SMS * FS_MARCH_MINB;
+  if (strips * cdiv(rows, 64) >= 2 * G) {
+    int best = 64;
+    double best_score = 0.0;
+    for (int mr = 96; mr >= 40; --mr) {
+      const int64_t total = strips * cdiv(rows, mr);
+      const double score = (double)total / (double)(cdiv(total, G) * G) * mr / (mr + 2.0);
+      if (score > best_score + 1e-9) { best_score = score; best = mr; }
+    }
+    return best;
+  }
   int mr = 64;
   while (mr > 4 && strips * cdiv(rows, mr) < (int64_t)FS_NUM_SMS * 16) mr >>= 1;
-  // tiny levels are pure latency: a task's rows are a serial chain of dependent loads, so hand
-  // every warp as few rows as possible while the whole level still fits one wave of CTAs
   while (mr > 1 && strips * cdiv(rows, mr) < (int64_t)FS_NUM_SMS * 2) mr >>= 1;
   return mr;
 }
 static unsigned march_blocks(int64_t rows, int64_t strips, int mr) {
   const int64_t total = strips * cdiv(rows, mr);
-  const int64_t cap = (int64_t)FS_NUM_SMS * 8;
+  const int64_t cap = (int64_t)FS_NUM_SMS * FS_MARCH_MINB;
   return (unsigned)(total < cap ? (total > 0 ? total : 1) : cap);
+}
+
+// levels large enough to be bandwidth bound take the TMA-fed kernels (fsgpu_ps::ring_min_points, read from
+// FSGPU_RING / FSGPU_RING_MIN_POINTS when the solver is created: threshold on the points a launch sweeps)
+static bool ring_level(const fsgpu_ps* s, int64_t rows, int64_t n1) {
+  return s->ring_min_points > 0 && rows * n1 >= s->ring_min_points;
+}
+// FS_MARCH_MINB CTAs with a 16-24 KB ring each only fit with the shared-memory carve-out at its maximum
+static bool ring_carveout(const void* kernel) {
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  return true;
 }
 
 // [r0, r1): the COARSE rows to produce (r0 < 0: all rows this rank owns / the whole replicated level).  A
@@ -912,7 +885,15 @@ static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_m
   const unsigned nb = march_blocks(f.i1 - f.i0, strips, mr);
   const int bl = 32 * MWARPS;
 #define UP_ARGS f, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket
-  if (dot_mode == 1) k_up_march<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
+  if (ring_level(s, f.i1 - f.i0, f.n1)) {  // bandwidth-bound levels: operands through the TMA ring
+    static const bool carve = ring_carveout((const void*)k_up_ring<CDIR, 0>) &&
+                              ring_carveout((const void*)k_up_ring<CDIR, 1>) &&
+                              ring_carveout((const void*)k_up_ring<CDIR, 2>);
+    (void)carve;
+    if (dot_mode == 1) k_up_ring<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
+    else if (dot_mode == 2) k_up_ring<CDIR, 2><<<nb, bl, 0, st>>>(UP_ARGS);
+    else k_up_ring<CDIR, 0><<<nb, bl, 0, st>>>(UP_ARGS);
+  } else if (dot_mode == 1) k_up_march<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
   else if (dot_mode == 2) k_up_march<CDIR, 2><<<nb, bl, 0, st>>>(UP_ARGS);
   else k_up_march<CDIR, 0><<<nb, bl, 0, st>>>(UP_ARGS);
 #undef UP_ARGS

@@ -24,7 +24,7 @@ namespace {
 constexpr int BX = 64, BY = 4;
 
 // s = A p and <s, p>;  last block: alpha = gamma / <s,p> with HYPRE's breakdown exits
-__global__ void __launch_bounds__(BX* BY)
+__global__ void __launch_bounds__(BX* BY, 8)
 k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict__ s, PcgScal* scal,
              double* part, unsigned int* ticket) {
   if (scal->done) return;

@@ -298,6 +298,7 @@ static int alloc_levels(fsgpu_ps* s) {
   }
   const Level& c = L[s->nl - 1];
   total += (size_t)(c.rows * c.v.pitch);  // coarsest ping-pong
+  total += 512;  // slack: the 1 KB bulk-copy segments of a level's last strip may run past the last row
   if (total > s->slab_doubles) {
     if (s->slab) cudaFree(s->slab);
     s->slab = nullptr;

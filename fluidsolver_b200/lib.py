@@ -58,7 +58,7 @@ SYMBOLS = (
     "fsgpu_capillary_divergence", "fsgpu_correct_velocity_ib_implicit_euler",
     "fsgpu_update_velocity_ib_semi_analytical", "fsgpu_interpolate_cell_centres",
     "fsgpu_calc_conserved_quantities", "fsgpu_monitor",
-    "fsgpu_project", "fsgpu_ps_set_rhs_from_velocity",
+    "fsgpu_project", "fsgpu_ps_set_rhs_from_velocity", "fsgpu_selftest_division",
 )
 TRANSPORT_NCCL, TRANSPORT_LOCAL = 0, 1
 COMM_ID_BYTES = 128
@@ -179,6 +179,15 @@ def prof_read():
     L.fsgpu_prof_read.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int]
     _chk(L.fsgpu_prof_read(ms, cnt, n))
     return {PROF_CLASSES[i]: (ms[i], cnt[i]) for i in range(n) if cnt[i]}
+
+
+def selftest_division(y, n=1 << 24, seed=1):
+    """-> (fast, mismatches): the kernels' division-free quotient x / y against the FP64 division on n random x"""
+    L = load()
+    fast, bad = C.c_int(), C.c_int64()
+    L.fsgpu_selftest_division.argtypes = [C.c_double, C.c_int64, C.c_uint64, C.POINTER(C.c_int), C.POINTER(C.c_int64)]
+    _chk(L.fsgpu_selftest_division(y, n, seed, C.byref(fast), C.byref(bad)))
+    return fast.value, bad.value
 
 
 def device_count() -> int:

@@ -301,6 +301,15 @@ int fsgpu_ps_num_levels(fsgpu_ps* s, int* n);
  * of levels for a single rank. */
 int fsgpu_ps_num_distributed_levels(fsgpu_ps* s, int* n);
 
+/* ---- self-test --------------------------------------------------------------------------------
+ * The kernels that divide by dx, dy, dt (calc_divergence, fill_pressure_rhs, the projection) form the
+ * quotient from a host-made reciprocal with one FMA correction instead of an FP64 division
+ * (csrc/common.cuh: DivBy); it must equal the division bit for bit.  This compares the two on n
+ * pseudo-random numerators (random sign and significand, magnitudes 2^-200 ... 2^200, zeros) for the
+ * divisor y: *mismatches counts the differing quotients, *fast is 0 when y is one of the divisors the
+ * shortcut does not cover (significand all ones), for which the kernels divide. */
+int fsgpu_selftest_division(double y, int64_t n, uint64_t seed, int* fast, int64_t* mismatches);
+
 /* ---- file output from the device buffers --------------------------
  * Files are byte-identical to the reference's.  x and y are the reference's fs.x / fs.y arrays
  * including their ghost entries (NX + 3 and NY + 3 doubles, fs.x.get_data()).  With slab contexts

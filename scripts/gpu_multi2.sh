@@ -6,19 +6,23 @@ mkdir -p gpurun_out
 nvidia-smi -L | head -8
 export NCCL_DEBUG=WARN
 port=29541
-for V in ${@:-p2p p2p_noovl nccl}; do
-  unset FSGPU_NO_OVERLAP
+for VV in ${@:-p2p p2p_noovl nccl}; do
+  # a variant may carry environment settings: name:ENV=VAL,ENV=VAL
+  V=${VV%%:*}; ENVS=""; [ "$VV" != "$V" ] && ENVS=${VV#*:}
+  unset FSGPU_NO_OVERLAP FSGPU_REPL_POINTS FSGPU_OVERLAP_MIN_POINTS
+  for kv in ${ENVS//,/ }; do export "$kv"; done
   case $V in
     p2p) ARGS="--halo p2p" ;;
     p2p_noovl) ARGS="--halo p2p --no-anchor --no-e2e --no-ref-depth"; export FSGPU_NO_OVERLAP=1 ;;
+    p2p_lite) ARGS="--halo p2p --no-anchor --no-e2e --no-ref-depth" ;;
     nccl) ARGS="--halo nccl --no-anchor --no-e2e --no-ref-depth" ;;
     *) ARGS="$V" ;;
   esac
-  out=gpurun_out/${TAG}_n${N}_${V}
+  out=gpurun_out/${TAG}_n${N}_${VV//[:=,]/_}
   port=$((port+1))
   ( time timeout ${RUN_TIMEOUT:-240} python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 \
       --master-port $port bench.py --gpus $N --steps ${STEPS:-5} --warmup 3 $ARGS ) > $out.json 2> $out.err
-  echo "== N=$N $V exit $?"
+  echo "== N=$N $VV exit $?"
   python - <<PY
 import json
 try:

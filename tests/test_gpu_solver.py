@@ -75,6 +75,39 @@ def test_solve_matches_oracle(F, oracle, name, kw, drop, tol):
     fs.close()
 
 
+RING_CASES = [("cavity200x72", dict(nx=200, ny=72), 40), ("wide150x520", dict(nx=150, ny=520), 40),
+              ("channel256x64", dict(nx=256, ny=64, lx=100.0, ly=1.0, rho=0.5), 16),
+              ("drop300x250", dict(nx=300, ny=250, drop=True), 40)]
+
+
+@pytest.mark.parametrize("name,kw,ml", RING_CASES, ids=[c[0] for c in RING_CASES])
+def test_tma_ring_kernels_bit_identical(F, oracle, name, kw, ml, monkeypatch):
+    """The marching V-cycle kernels fed by the TMA ring (cp.async.bulk + mbarrier; taken by launches of >= 2^20
+    points in production) against the register-pipelined ones: same arithmetic and association, so the whole
+    solve -- every iterate, the iteration count, the residual -- is bit-identical.  Grids with one and several
+    120-column strips, both coarsening directions, a ragged last strip."""
+    st = cavity_state(oracle, seed=4, **kw)
+    dt = 1e-2
+    out = []
+    for env in ({"FSGPU_RING": "0"}, {"FSGPU_RING_MIN_POINTS": "1"}):
+        for k in ("FSGPU_RING", "FSGPU_RING_MIN_POINTS"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        fs, op, rhs = _setup(oracle, F, st, cavity_bc(), dt)
+        ps = F.LinearSolver(fs, tol=1e-12, max_iter=200, max_levels=ml)
+        ps.set_pressure_operator()
+        ps.set_pressure_rhs(dt)
+        res, it = ps.solve()
+        out.append((res, it, fs.download("DELTA_P")))
+        ps.close()
+        fs.close()
+    (r0, i0, d0), (r1, i1, d1) = out
+    assert i0 == i1 and r0 == r1, (i0, i1, r0, r1)
+    assert np.array_equal(d0, d1)
+    assert r1 < 1e-12
+
+
 @pytest.mark.parametrize("max_levels", [2, 3, 4, 7, 10])
 def test_truncated_hierarchy(F, oracle, max_levels):
     """PS_PFMG_MAX_LEVELS truncation (src/LinearSolver_StructHypre.hpp:221-229; 16 in production,

@@ -268,3 +268,16 @@ def test_upload_download_roundtrip_and_pads(F):
             fs.upload(n, a)
             assert np.array_equal(fs.download(n), a), (n, nx, ny)
         fs.close()
+
+
+@pytest.mark.parametrize("y", [1.0 / 8192, 1.0 / 96, 1.0 / 3, 100.0 / 215, 0.1, 1e-3, 7.123456789e-5, 3.0, 2.0 - 2.0 ** -52])
+def test_division_by_uniform_divisor_is_exact(F, y):
+    """calc_divergence / fill_pressure_rhs / the projection divide by dx, dy, dt as the reference does
+    (src/Operators.hpp:36-39, src/LinearSystem.hpp:134, scaling/LidDrivenFlow.cpp:155-159); the kernels form
+    those quotients from a reciprocal with one FMA correction (csrc/common.cuh DivBy), which must be the
+    correctly rounded quotient: compared bit for bit with the FP64 division on 2^24 random numerators.
+    The last divisor has an all-ones significand -- the one case the shortcut does not cover, where the
+    kernels fall back to the division itself."""
+    fast, bad = F.selftest_division(y, 1 << 24, seed=12345)
+    assert bad == 0
+    assert fast == (0 if y == 2.0 - 2.0 ** -52 else 1)
