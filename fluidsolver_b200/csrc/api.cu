@@ -8,25 +8,27 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 #include <new>
 #include <set>
 #include <vector>
 
-int64_t g_launches = 0;
+std::atomic<int64_t> g_launches{0};
 unsigned int g_prof_mask = 0;
 unsigned int g_ncu_mask = getenv("FSGPU_NCU_CLASSES") ? (unsigned int)strtoul(getenv("FSGPU_NCU_CLASSES"), nullptr, 0) : 0u;
 void fs_ncu_range(bool begin) {
   if (begin) cudaProfilerStart();
   else cudaProfilerStop();
 }
-int g_prof_tag = 0;
+thread_local int g_prof_tag = 0;
 
 namespace {
 struct ProfRec { int cls; cudaEvent_t a, b; int tag; };
-std::vector<ProfRec> g_prof_recs;
-std::vector<cudaEvent_t> g_prof_pool;
-cudaEvent_t g_prof_open[PROF_NCLASS];
+// per host thread: the in-process transport drives one context per thread, and a thread reads back its own records
+thread_local std::vector<ProfRec> g_prof_recs;
+thread_local std::vector<cudaEvent_t> g_prof_pool;
+thread_local cudaEvent_t g_prof_open[PROF_NCLASS];
 cudaEvent_t prof_event() {
   cudaEvent_t e;
   if (!g_prof_pool.empty()) { e = g_prof_pool.back(); g_prof_pool.pop_back(); }
@@ -106,7 +108,7 @@ int fsgpu_selftest_division(double y, int64_t n, uint64_t seed, int* fast, int64
   if (mismatches) *mismatches = (int64_t)h;
   return 0;
 }
-int64_t fsgpu_launch_count(void) { return g_launches; }
+int64_t fsgpu_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 int fsgpu_prof_enable(unsigned int class_mask) {
   g_prof_mask = class_mask;
@@ -569,15 +571,21 @@ int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out) {
   if (s->o.relax == 0) s->o.relax = FSGPU_RELAX_JACOBI;
   if (const char* e = getenv("FSGPU_RING_MIN_POINTS")) s->ring_min_points = atoll(e) > 0 ? atoll(e) : 1;
   if (const char* e = getenv("FSGPU_RING")) { if (atoi(e) == 0) s->ring_min_points = 0; }
-  FS_CUDA(cudaMalloc(&s->scal, sizeof(PcgScal)));
-  FS_CUDA(cudaMemset(s->scal, 0, sizeof(PcgScal)));
-  FS_CUDA(cudaMallocHost(&s->h_scal, 4 * sizeof(PcgScal)));
-  for (int i = 0; i < 4; ++i) FS_CUDA(cudaEventCreateWithFlags(&s->ev[i], cudaEventDisableTiming));
-  {
+  {  // registered first: every failure below is undone by the one teardown routine
     std::lock_guard<std::mutex> lk(g_live_mu);
     g_live_solvers.insert(s);
   }
-  if (comm_alloc_fence(c)) return 1;
+  auto alloc = [&]() {
+    FS_CUDA(cudaMalloc(&s->scal, sizeof(PcgScal)));
+    FS_CUDA(cudaMemset(s->scal, 0, sizeof(PcgScal)));
+    FS_CUDA(cudaMallocHost(&s->h_scal, 4 * sizeof(PcgScal)));
+    for (int i = 0; i < 4; ++i) FS_CUDA(cudaEventCreateWithFlags(&s->ev[i], cudaEventDisableTiming));
+    return comm_alloc_fence(c);
+  };
+  if (alloc()) {
+    ps_destroy_impl(s);
+    return 1;
+  }
   *out = s;
   return 0;
 }
@@ -600,8 +608,9 @@ static int ps_destroy_impl(fsgpu_ps* s) {
   cudaStreamSynchronize(s->c->stream);
   cudaFree(s->slab);
   cudaFree(s->scal);
-  cudaFreeHost(s->h_scal);
-  for (int i = 0; i < 4; ++i) cudaEventDestroy(s->ev[i]);
+  if (s->h_scal) cudaFreeHost(s->h_scal);
+  for (int i = 0; i < 4; ++i)
+    if (s->ev[i]) cudaEventDestroy(s->ev[i]);
   delete s;
   return 0;
 }
@@ -666,7 +675,10 @@ int fsgpu_substep(fsgpu_ctx* c, fsgpu_ps* s, double dt, int flags, double* resid
   }
   {
     ProfScope ps_(PROF_RHS, c->stream);  // divergence + rhs (+ mean removal)
-    if (fs_launch_rhs(c, dt, s->o.psd, !(flags & FSGPU_STEP_CAPILLARY))) return 1;
+    bool deferred = false;
+    // (a one-level hierarchy has no marching kernels to absorb the mean: subtract it here)
+    if (fs_launch_rhs(c, dt, s->o.psd, !(flags & FSGPU_STEP_CAPILLARY), s->nl > 1, &deferred)) return 1;
+    s->rhs_mean_pending = deferred;
   }
   if (ps_solve(s, residual, iters)) return 1;
   {

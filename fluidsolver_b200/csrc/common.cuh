@@ -191,7 +191,8 @@ static inline unsigned persist_blocks(int64_t n0, int64_t n1, int per_sm = 8) {
 
 // ---- error handling / launch accounting (api.cu) ---------------------------------------------
 void fs_set_error(const char* fmt, ...);
-extern int64_t g_launches;
+#include <atomic>
+extern std::atomic<int64_t> g_launches;  // contexts may be driven by different host threads
 #define FS_CUDA(x)                                                                       \
   do {                                                                                   \
     cudaError_t e_ = (x);                                                                \
@@ -202,7 +203,7 @@ extern int64_t g_launches;
   } while (0)
 #define FS_LAUNCHED()                                                                    \
   do {                                                                                   \
-    ++g_launches;                                                                        \
+    g_launches.fetch_add(1, std::memory_order_relaxed);                                                                     \
     cudaError_t e_ = cudaPeekAtLastError();                                              \
     if (e_ != cudaSuccess) {                                                             \
       fs_set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
@@ -220,7 +221,7 @@ enum {
   PROF_DOWN0, PROF_UP0, PROF_DOWN, PROF_UP, PROF_COARSE, PROF_SETUP, PROF_OTHER, PROF_NCLASS
 };
 extern unsigned int g_prof_mask;
-extern int g_prof_tag;  // stamped on every record (PCG: the iteration number)
+extern thread_local int g_prof_tag;  // stamped on every record (PCG: the iteration number)
 size_t fs_prof_mark(void);
 // drop records [from, end) with tag > last_real_tag, and those of class cls_empty_at_last with tag == last_real_tag
 void fs_prof_drop_after(size_t from, int last_real_tag, int cls_empty_at_last);

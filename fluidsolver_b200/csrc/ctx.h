@@ -111,7 +111,7 @@ int fs_launch_flow_control(fsgpu_ctx* c, int mode, double total_flow, double* d_
 int fs_launch_divergence(fsgpu_ctx* c);
 // rhs = -vol*div/dt (+ Dirichlet row zeroing); if psd == NONE the mean over all cells is
 // subtracted (two passes).  div_from_uv: compute div on the fly from U,V and store it too.
-int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv);
+int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv, bool defer_mean = false, bool* deferred = nullptr);
 int fs_launch_shift_pressure(fsgpu_ctx* c);
 int fs_launch_correct(fsgpu_ctx* c, double dt, bool shift, bool sum_ready);
 int fs_launch_cfl(fsgpu_ctx* c);               // 4 maxima -> red_out[0..3]

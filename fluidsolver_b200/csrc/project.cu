@@ -95,29 +95,33 @@ k_sum(const double* __restrict__ f, const Geom g, double* part, unsigned int* ti
 // SHIFT: delta_p is used as dpi - c with c = (*sum) * dx * dy, *sum = the sum of ALL entries of dpi, and the
 // shifted field is stored to dpo, a DIFFERENT buffer (a neighbour's un-shifted value is still needed by the threads
 // next to it, so the shift cannot be stored in place inside the same pass); the caller swaps the two buffers.
+#ifndef FS_PROJECT_MINB
+#define FS_PROJECT_MINB 8
+#endif
 template <bool SHIFT>
-__global__ void __launch_bounds__(BX* BY)
+__global__ void __launch_bounds__(BX* BY, FS_PROJECT_MINB)
 k_project(const double* __restrict__ dpi, double* __restrict__ dpo, double* __restrict__ p, double* __restrict__ U,
           double* __restrict__ V, const double* __restrict__ ru, const double* __restrict__ rv,
           const double* __restrict__ sum, const Geom g, const Divs q, double dt) {
-  const int64_t b = (int64_t)blockIdx.x * BX + threadIdx.x;
-  const int64_t a = g.a_lo + (int64_t)blockIdx.y * BY + threadIdx.y;
-  if (a >= g.a_hi || b > g.ny + 1) return;
-  const int64_t k = g.idx(a, b), P = g.pitch;
-  const double c  = SHIFT ? __ldg(sum) * g.dx * g.dy : 0.0;
-  const double d0 = SHIFT ? __ldg(dpi + k) - c : __ldg(dpi + k);
-  // U(i,j) for i in [0,NX], j in [0,NY): a in [1,NX+1], b in [1,NY]
-  if (a >= 1 && b >= 1 && b <= g.ny) {
-    const double dm = SHIFT ? __ldg(dpi + k - P) - c : __ldg(dpi + k - P);
-    U[k] -= __dmul_rn(q.dx(d0 - dm), dt) / __ldg(ru + k);
-  }
-  // V(i,j) for i in [0,NX), j in [0,NY]: a in [1,NX], b in [1,NY+1]
-  if (a >= 1 && a <= g.nx && b >= 1) {
-    const double dm = SHIFT ? __ldg(dpi + k - 1) - c : __ldg(dpi + k - 1);
-    V[k] -= __dmul_rn(q.dy(d0 - dm), dt) / __ldg(rv + k);
-  }
-  p[k] += d0;
-  if (SHIFT) dpo[k] = d0;
+  const double c = SHIFT ? __ldg(sum) * g.dx * g.dy : 0.0;
+  const int64_t P = g.pitch;
+  // persistent tile loop (as the reduction kernels): four rows per thread in flight, 8 CTAs per SM
+  for_each_point(g.a_lo, g.a_hi, g.ny + 2, [&](int64_t a, int64_t b) {
+    const int64_t k = g.idx(a, b);
+    const double d0 = SHIFT ? __ldg(dpi + k) - c : __ldg(dpi + k);
+    // U(i,j) for i in [0,NX], j in [0,NY): a in [1,NX+1], b in [1,NY]
+    if (a >= 1 && b >= 1 && b <= g.ny) {
+      const double dm = SHIFT ? __ldg(dpi + k - P) - c : __ldg(dpi + k - P);
+      U[k] -= __dmul_rn(q.dx(d0 - dm), dt) / __ldg(ru + k);
+    }
+    // V(i,j) for i in [0,NX), j in [0,NY]: a in [1,NX], b in [1,NY+1]
+    if (a >= 1 && a <= g.nx && b >= 1) {
+      const double dm = SHIFT ? __ldg(dpi + k - 1) - c : __ldg(dpi + k - 1);
+      V[k] -= __dmul_rn(q.dy(d0 - dm), dt) / __ldg(rv + k);
+    }
+    p[k] += d0;
+    if (SHIFT) dpo[k] = d0;
+  });
 }
 
 // in-place shift as its own pass (public fsgpu_shift_pressure_to_zero): k_sum -> k_sub_scaled.
@@ -251,7 +255,10 @@ int fs_launch_divergence(fsgpu_ctx* c) {
   return 0;
 }
 
-int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
+// defer_mean: leave the mean in (its sum, all-reduced, stays in red_out[0]); the solver's first readers of the
+// rhs subtract it (fsgpu_substep; solver_cycle.cu BShift).  *deferred tells the caller whether that applies.
+int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv, bool defer_mean, bool* deferred) {
+  if (deferred) *deferred = false;
   const dim3 gr = cell_grid(c->g);
   const unsigned pg = persist_blocks(c->g.a_hi - c->g.a_lo, c->g.ny + 2);
   if (fs_ensure_part(c, (size_t)pg * 4)) return 1;
@@ -266,6 +273,10 @@ int fs_launch_rhs(fsgpu_ctx* c, double dt, int psd, bool div_from_uv) {
   FS_LAUNCHED();
   if (psd == FSGPU_PSD_NONE) {  // subtract the arithmetic mean over all (NX+2)(NY+2) entries: sum / size (LinearSystem.hpp:150-152)
     if (comm_allreduce(c, c->red_out, 1, COMM_SUM)) return 1;
+    if (defer_mean) {
+      if (deferred) *deferred = true;
+      return 0;
+    }
     k_sub_scaled<<<gr, dim3(BX, BY), 0, c->stream>>>(c->f[FSGPU_RHS], c->red_out,
                                                      (double)((c->g.nx + 2) * (c->g.ny + 2)), 1.0, true, c->g);
     FS_LAUNCHED();
@@ -302,12 +313,12 @@ int fs_launch_correct(fsgpu_ctx* c, double dt, bool shift, bool sum_ready) {
     if (fs_exchange_fields(c, fl, 1, 1)) return 1;
   }
   if (shift) {
-    k_project<true><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
+    k_project<true><<<persist_blocks(c->g.a_hi - c->g.a_lo, c->g.ny + 2), dim3(BX, BY), 0, c->stream>>>(
         c->f[FSGPU_DELTA_P], c->f[FSGPU_RHS], c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
         c->f[FSGPU_RHO_V], c->red_out + 1, c->g, make_divs(c->g, dt), dt);
     std::swap(c->f[FSGPU_DELTA_P], c->f[FSGPU_RHS]);
   } else {
-    k_project<false><<<cell_grid(c->g), dim3(BX, BY), 0, c->stream>>>(
+    k_project<false><<<persist_blocks(c->g.a_hi - c->g.a_lo, c->g.ny + 2), dim3(BX, BY), 0, c->stream>>>(
         c->f[FSGPU_DELTA_P], nullptr, c->f[FSGPU_P], c->f[FSGPU_U], c->f[FSGPU_V], c->f[FSGPU_RHO_U],
         c->f[FSGPU_RHO_V], c->red_out + 1, c->g, make_divs(c->g, dt), dt);
   }

@@ -137,6 +137,11 @@ struct fsgpu_ps {
   // launches sweeping at least this many points use the TMA-fed marching kernels (0: never).  Environment, read
   // by fsgpu_ps_create: FSGPU_RING=0 turns them off, FSGPU_RING_MIN_POINTS moves the threshold.
   int64_t ring_min_points = 1 << 20;
+  // fsgpu_substep: the rhs still carries its mean; b_shift (device: the sum of all its entries, on every rank)
+  // is non-null from the start of the solve until the first x / r update has absorbed it (solver_cycle.cu BShift)
+  bool rhs_mean_pending = false;
+  const double* b_shift = nullptr;
+  double b_shift_size = 1.0;
   bool is_setup = false;
   bool levels_allocated = false;
   double last_dt = 0.0;

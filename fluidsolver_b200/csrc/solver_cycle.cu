@@ -75,6 +75,16 @@ __device__ __forceinline__ double mg_post(double w, double b, double d, double d
   return fma(__dmul_rn(w, b - v), dinv, x0);
 }
 
+// The rhs of the pressure system with its mean still in it (fill_pressure_rhs subtracts the mean over all
+// (NX+2)(NY+2) entries, src/LinearSystem.hpp:150-152): fsgpu_substep leaves the subtraction to the first
+// readers of the rhs -- the level-0 kernels of the first V-cycle here and the first x / r update -- instead of
+// a pass of its own over the array.  sum == null: nothing to subtract.  Pads stay zero: callers mask.
+struct BShift {
+  const double* sum;  // device: the sum of all entries (on every rank)
+  double size;        // number of entries
+  __device__ __forceinline__ double mean() const { return sum ? __ldg(sum) / size : 0.0; }
+};
+
 template <int CDIR>
 struct Coef {
   const double *cx, *cy;
@@ -111,18 +121,20 @@ struct MarchCursor {
 // k_down_march0: coarsening along i.  Per fine row the warp forms X = w b / d, then the residual
 // R of the row above from three rows of X held in registers (left/right by shuffle), and on every
 // second row the coarse rhs  b_c = R + pp(row-1) R(row-1) + pm(row+1) R(row+1).
-template <bool ACTIVE>
+template <bool ACTIVE, bool SHIFT>
 __global__ void __launch_bounds__(128, FS_MARCH_MINB)
 k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
-              double* __restrict__ cb, double w, int mr, const PcgScal* scal) {
+              double* __restrict__ cb, double w, int mr, const PcgScal* scal, const BShift bs) {
   if (scal->done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  const double bm = SHIFT ? bs.mean() : 0.0;
   MarchCursor cur((n1 + 119) / 120, (int)c.i0, (int)c.i1, mr);  // rows of a task: coarse rows
   int sp, c0, c1;
   while (cur.next(sp, c0, c1)) {
     int lj = sp * 120 + warp * 30 - 1 + lane;
     const bool store_lane = lane >= 1 && lane <= 30 && lj < n1;
+    const bool colin = lj >= 0 && lj < n1;
     if (lj > n1) lj = n1;
     const int f0 = 2 * c0 + foff, fL = 2 * (c1 - 1) + foff;
     double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx2 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0, Ra = 0.0, Rb = 0.0;
@@ -131,7 +143,9 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
     int o  = (li + FS_RO) * P + lj + FS_CO;
 #pragma unroll 2
     for (; li <= fL + 2; ++li, o += P) {
-      const double b0 = __ldg(fb + o), cx0 = __ldg(f.cx + o);
+      double b0 = __ldg(fb + o);
+      const double cx0 = __ldg(f.cx + o);
+      if (SHIFT && colin && li >= 0 && li < (int)f.n0) b0 -= bm;
       double X0 = 0.0, cy0 = 0.0, cy0p = 0.0, pc0 = 0.0;
       if (ACTIVE) {
         const double d0 = __ldg(f.d + o);
@@ -163,19 +177,21 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
 
 // k_down_march1: coarsening along j.  Lanes 1..30 hold a valid residual (X of the neighbours by
 // shuffle), lanes 2..29 that sit on a C column emit  b_c = R + pp(j-1) R(j-1) + pm(j+1) R(j+1).
-template <bool ACTIVE>
+template <bool ACTIVE, bool SHIFT>
 __global__ void __launch_bounds__(128, FS_MARCH_MINB)
 k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
-              double* __restrict__ cb, double w, int mr, const PcgScal* scal) {
+              double* __restrict__ cb, double w, int mr, const PcgScal* scal, const BShift bs) {
   if (scal->done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  const double bm = SHIFT ? bs.mean() : 0.0;
   MarchCursor cur((n1 + 111) / 112, (int)f.i0, (int)f.i1, mr);
   int sp, r0, r1;
   while (cur.next(sp, r0, r1)) {
     int lj = sp * 112 + warp * 28 - 2 + lane;
     const int pos = lj - foff;
     const bool store_lane = lane >= 2 && lane <= 29 && lj < n1 && (pos & 1) == 0;
+    const bool colin = lj >= 0 && lj < n1;
     const int oc_col = (pos >> 1) + FS_CO;
     if (lj > n1) lj = n1;
     double X2 = 0.0, X1 = 0.0, b1 = 0.0, cx1 = 0.0, cy1 = 0.0, cy1p = 0.0, d1 = 0.0;
@@ -183,7 +199,8 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
     int o  = (li + FS_RO) * P + lj + FS_CO;
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
-      const double b0 = __ldg(fb + o);
+      double b0 = __ldg(fb + o);
+      if (SHIFT && colin && li >= 0 && li < (int)f.n0) b0 -= bm;
       const double cy0 = __ldg(f.cy + o), cy0p = __ldg(f.cy + o + 1);
       double X0 = 0.0, cx0 = 0.0, d0 = 0.0;
       if (ACTIVE) {
@@ -262,16 +279,20 @@ constexpr int MOUT = 30, MWARPS = 4;
 template <int CDIR, int DOT>
 __global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB)
 k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
-           const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket) {
+           const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket,
+           const BShift bs) {
   if (scal->done) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
+  const bool shift = DOT == 2 && bs.sum != nullptr;  // only the first V-cycle of a solve can see an unshifted rhs
+  const double bm  = shift ? bs.mean() : 0.0;
   MarchCursor cur((n1 + MOUT * MWARPS - 1) / (MOUT * MWARPS), (int)f.i0, (int)f.i1, mr);
   double acc[1] = {0.0};
   int sp, r0, r1;
   while (cur.next(sp, r0, r1)) {
     int lj = sp * (MOUT * MWARPS) + warp * MOUT - 1 + lane;  // lane 0 sits one column left
     const bool store_lane = lane >= 1 && lane <= MOUT && lj < n1;
+    const bool colin = lj >= 0 && lj < n1;
     if (lj > n1) lj = n1;  // the zero pad column right of the grid
     double x0p = 0.0, x0c = 0.0, bc = 0.0, dic = 0.0, dc = 0.0, cyc = 0.0, cy1c = 0.0, cxc = 0.0;
     int li = r0 - 1;
@@ -302,7 +323,8 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
 #pragma unroll 2
     for (; li <= r1; ++li, o += P) {
       const Row q = load_row(li, o);
-      const double cxnn = q.cxnn, bn = q.b, dn = q.d, cyn = q.cy, cy1n = q.cy1;
+      const double cxnn = q.cxnn, dn = q.d, cyn = q.cy, cy1n = q.cy1;
+      const double bn = (DOT == 2 && shift && colin && li >= 0 && li < (int)f.n0) ? q.b - bm : q.b;
       const double din = rcp0(dn);
       double xi;
       if (CDIR == 0) {
@@ -395,9 +417,12 @@ struct RingBars {
 template <int CDIR, int DOT>
 __global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB)
 k_up_ring(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
-          const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket) {
+          const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket,
+          const BShift bs) {
   if (scal->done) return;
   constexpr int S = FS_RING_STAGES;
+  const bool shift = DOT == 2 && bs.sum != nullptr;
+  const double bm  = shift ? bs.mean() : 0.0;
   __shared__ __align__(128) double ring[S][RING_SLOTS][RING_SEG];
   __shared__ __align__(8) RingBars<S> bar;
   unsigned long long* const full = bar.full;
@@ -480,6 +505,7 @@ k_up_ring(const LevelDev f, const double* __restrict__ fb, double* __restrict__ 
       if (lane == 0) mbar_arrive(&empty[st]);
       ++cn;
       if (!colok) { cxnn = 0.0; bn = 0.0; cyn = 0.0; cy1n = 0.0; dn = 0.0; xm = 0.0; xp = 0.0; }
+      if (DOT == 2 && shift && ljr >= 0 && ljr < n1 && li >= 0 && li < (int)f.n0) bn -= bm;
       const double din = rcp0(dn);
       double xi;
       if (CDIR == 0) {
@@ -846,18 +872,23 @@ static int launch_down(fsgpu_ps* s, int l, const double* fb, int64_t r0 = -1, in
     if (L[l].cdir == 0) { c.i0 = r0; c.i1 = r1; }
     else { f.i0 = r0; f.i1 = r1; }
   }
+  const BShift bs{l == 0 ? s->b_shift : nullptr, s->b_shift_size};  // only level 0 reads the rhs itself
   if (L[l].cdir == 0) {
     const int64_t strips = cdiv(f.n1, 120);
     const int mrc = pick_rows(c.i1 - c.i0, strips);
     const unsigned nb = march_blocks(c.i1 - c.i0, strips, mrc);
-    if (L[l].active) k_down_march0<true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal);
-    else k_down_march0<false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal);
+    if (bs.sum && L[l].active) k_down_march0<true, true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal, bs);
+    else if (bs.sum) k_down_march0<false, true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal, bs);
+    else if (L[l].active) k_down_march0<true, false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal, bs);
+    else k_down_march0<false, false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal, bs);
   } else {
     const int64_t strips = cdiv(f.n1, 112);
     const int mr = pick_rows(f.i1 - f.i0, strips);
     const unsigned nb = march_blocks(f.i1 - f.i0, strips, mr);
-    if (L[l].active) k_down_march1<true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal);
-    else k_down_march1<false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal);
+    if (bs.sum && L[l].active) k_down_march1<true, true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal, bs);
+    else if (bs.sum) k_down_march1<false, true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal, bs);
+    else if (L[l].active) k_down_march1<true, false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal, bs);
+    else k_down_march1<false, false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal, bs);
   }
   FS_LAUNCHED();
   return 0;
@@ -884,7 +915,8 @@ static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_m
   const int mr      = pick_rows(f.i1 - f.i0, strips);
   const unsigned nb = march_blocks(f.i1 - f.i0, strips, mr);
   const int bl = 32 * MWARPS;
-#define UP_ARGS f, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket
+  const BShift bs{l == 0 ? s->b_shift : nullptr, s->b_shift_size};
+#define UP_ARGS f, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket, bs
   if (ring_level(s, f.i1 - f.i0, f.n1)) {  // bandwidth-bound levels: operands through the TMA ring
     static const bool carve = ring_carveout((const void*)k_up_ring<CDIR, 0>) &&
                               ring_carveout((const void*)k_up_ring<CDIR, 1>) &&

@@ -54,20 +54,23 @@ k_matvec_dot(const LevelDev L, const double* __restrict__ p, double* __restrict_
 // separate summation pass over delta_p.
 // Slab overlap: the launch is split in two (boundary rows first, RowSplit; ACC adds the second launch's sum to the
 // first's), so that the exchange of r's halo rows runs beside the interior launch.
+// bsum != null (first iteration after fsgpu_substep): r still is the rhs with its mean in it, which goes here.
 template <bool ACC>
 __global__ void __launch_bounds__(BX* BY)
 k_xr_update(const LevelDev L, const RowSplit rr, double* __restrict__ x, double* __restrict__ r,
             const double* __restrict__ p, const double* __restrict__ s, const PcgScal* scal, double* part,
-            unsigned int* ticket, double* sum_out) {
+            unsigned int* ticket, double* sum_out, const double* bsum, double bsize) {
   if (scal->done) return;
   const double alpha = scal->alpha;
+  const double bm = bsum ? __ldg(bsum) / bsize : 0.0;
   double v[1] = {0.0};
   for_each_point2(rr, L.n1, [&](int64_t li, int64_t lj) {
     const int64_t k = L.idx(li, lj);
     const double xn = x[k] + alpha * p[k];
     x[k] = xn;
     v[0] += xn;
-    r[k] -= alpha * s[k];
+    const double rk = bsum ? r[k] - bm : r[k];
+    r[k] = rk - alpha * s[k];
   });
   double tot[1];
   if (grid_reduce<ReduceSum, 1>(v, part, ticket, tot)) {
@@ -182,6 +185,13 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
   // slab decomposition, per iteration: r needs FS_RO halo rows before the V-cycle (restriction
   // reaches two rows out), p one halo row before the matvec
   if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
+  // red_out[12]: a copy of the rhs sum that later reductions of the solve leave alone
+  if (s->rhs_mean_pending) {
+    FS_CUDA(cudaMemcpyAsync(c->red_out + 12, c->red_out, sizeof(double), cudaMemcpyDeviceToDevice, st));
+    s->b_shift      = c->red_out + 12;
+    s->b_shift_size = (double)((c->g.nx + 2) * (c->g.ny + 2));
+  }
+  s->rhs_mean_pending = false;
   if (ps_vcycle(s, r, s->z, 2)) return 1;  // z = C b and bi = <z, b>
   const RowSplit all{L0.i0, L0.i1, 0, 0};
   const SlabSplit sp1 = ps_split(s, 0, 1), sp2 = ps_split(s, 0, FS_RO);  // p: one halo row, r: FS_RO
@@ -204,15 +214,19 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
       ProfScope ps_(PROF_XR, st);
       bool async = false;
       if (sp2.on) {  // boundary rows, their exchange on the transport's stream, interior rows beside it
-        k_xr_update<false><<<pg2, bl, 0, st>>>(L0, sp2.bnd, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1);
+        k_xr_update<false><<<pg2, bl, 0, st>>>(L0, sp2.bnd, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1,
+                                               s->b_shift, s->b_shift_size);
         FS_LAUNCHED();
         if (comm_halo_async(c, &r, 1, L0.pitch, s->L[0].own0, s->L[0].own1, FS_RO, &async)) return 1;
-        k_xr_update<true><<<pg, bl, 0, st>>>(L0, sp2.in, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1);
+        k_xr_update<true><<<pg, bl, 0, st>>>(L0, sp2.in, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1,
+                                             s->b_shift, s->b_shift_size);
         FS_LAUNCHED();
       } else {
-        k_xr_update<false><<<pg, bl, 0, st>>>(L0, all, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1);
+        k_xr_update<false><<<pg, bl, 0, st>>>(L0, all, x, r, s->p, s->s, s->scal, c->part, c->ticket, c->red_out + 1,
+                                              s->b_shift, s->b_shift_size);
         FS_LAUNCHED();
       }
+      s->b_shift = nullptr;  // r is the residual from here on
       if (async) { if (comm_halo_wait(c)) return 1; }
       else if (ps_halo(s, 0, &r, 1, FS_RO)) return 1;
     }
@@ -244,6 +258,7 @@ int ps_solve(fsgpu_ps* s, double* residual, int* iters) {
     }
   }
   (void)launched;
+  s->b_shift = nullptr;
   // the sum of all entries of the solution, on every rank (fs_launch_correct's sum_ready)
   if (comm_allreduce(c, c->red_out + 1, 1, COMM_SUM)) return 1;
   FS_CUDA(cudaMemcpyAsync(&s->h_scal[0], s->scal, sizeof(PcgScal), cudaMemcpyDeviceToHost, st));

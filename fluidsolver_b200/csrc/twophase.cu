@@ -498,7 +498,7 @@ int fs_sample_points(fsgpu_ctx* c, int mode, int fa, int fb, const double* xm, c
     const unsigned nb = (unsigned)((npts + 255) / 256);
     if (mode == 0) k_sample<0><<<nb, 256, 0, c->stream>>>(s, c->g);
     else k_sample<1><<<nb, 256, 0, c->stream>>>(s, c->g);
-    ++g_launches;
+    g_launches.fetch_add(1, std::memory_order_relaxed);
     rc = cudaPeekAtLastError() != cudaSuccess ||
          comm_allreduce(c, d + nc + 2 * np, (int64_t)(mode == 0 ? 2 * np : np), COMM_SUM) != 0 ||
          cudaMemcpyAsync(oa, d + nc + 2 * np, np * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||

@@ -30,7 +30,7 @@ V_LIKE = {"P_JUMP_V", "RHO_V_OLD", "V_OLD", "RHO_V", "V", "DMOM_V", "DRHO_V", "P
 DIRICHLET, NEUMANN, PERIODIC, SYMMETRY = 0, 1, 2, 3
 LEFT, RIGHT, BOTTOM, TOP = 0, 1, 2, 3
 PSD_NONE, PSD_LEFT, PSD_RIGHT, PSD_BOTTOM, PSD_TOP = 0, 1, 2, 3, 4
-RELAX_JACOBI, RELAX_RBGS = 1, 2
+RELAX_JACOBI = 1
 STEP_OUTFLOW_FIX, STEP_REBUILD_OPERATOR, STEP_DENSITY, STEP_CAPILLARY = 1, 2, 4, 8
 FLOW_OUTFLOW_FIX, FLOW_OUTFLOW_FIX_DY, FLOW_FORCE_TOTAL = 1, 2, 3
 

@@ -79,12 +79,10 @@ enum { FSGPU_BC_DIRICHLET = 0, FSGPU_BC_NEUMANN = 1, FSGPU_BC_PERIODIC = 2, FSGP
 enum { FSGPU_LEFT = 0, FSGPU_RIGHT = 1, FSGPU_BOTTOM = 2, FSGPU_TOP = 3 };
 /* PSDirichlet, src/LinearSystem.hpp:10 */
 enum { FSGPU_PSD_NONE = 0, FSGPU_PSD_LEFT = 1, FSGPU_PSD_RIGHT = 2, FSGPU_PSD_BOTTOM = 3, FSGPU_PSD_TOP = 4 };
-/* smoother of the multigrid preconditioner */
-enum {
-  FSGPU_RELAX_JACOBI = 1, /* weighted Jacobi: what the reference gets from HYPRE's defaults
-                             (Submodules/hypre/src/struct_ls/pfmg.c:32) */
-  FSGPU_RELAX_RBGS = 2    /* symmetric red/black Gauss-Seidel (struct_ls/red_black_gs.c) */
-};
+/* smoother of the multigrid preconditioner: weighted Jacobi, what the reference gets from HYPRE's defaults
+ * (Submodules/hypre/src/struct_ls/pfmg.c:32; src/LinearSolver_StructHypre.hpp never calls SetRelaxType).
+ * It is the only smoother: iterate-level parity with the reference depends on it. */
+enum { FSGPU_RELAX_JACOBI = 1 };
 
 const char* fsgpu_last_error(void);
 /* number of CUDA kernels launched by this library since load (bench.py's gpu_launches) */

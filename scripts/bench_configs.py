@@ -6,20 +6,28 @@ ms/step over `steps` timed steps after `warmup` (CUDA events on the library's st
 PCG iterations per solve.
 
 usage: python scripts/bench_configs.py [steps] [warmup] [scale]    (scale 2 halves every grid dimension)
+       python scripts/bench_configs.py --cpu [scale]   the UNMODIFIED reference (oracle/_ref/libfsref.so, OpenMP + HYPRE,
+                                                       all host cores) on the channel and the drop at the same sizes:
+                                                       1 warm-up + 2 timed timesteps each, one JSON line each
 """
 import json
 import os
+import subprocess
 import sys
+import time
 
 import numpy as np
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import fluidsolver_b200 as F  # noqa: E402
-import torch  # noqa: E402
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+CPU = len(sys.argv) > 1 and sys.argv[1] in ("--cpu", "--cpu-child")
+if not CPU:
+    import fluidsolver_b200 as F  # noqa: E402
+    import torch  # noqa: E402
 
-steps = int(sys.argv[1]) if len(sys.argv) > 1 else 20
-warmup = int(sys.argv[2]) if len(sys.argv) > 2 else 5
-scale = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+steps = int(sys.argv[1]) if len(sys.argv) > 1 and not CPU else 20
+warmup = int(sys.argv[2]) if len(sys.argv) > 2 and not CPU else 5
+scale = int(sys.argv[2]) if CPU and len(sys.argv) > 2 else (int(sys.argv[3]) if len(sys.argv) > 3 and not CPU else 1)
 
 
 def ellipse_vf(nx, ny, dx, dy, npt=16, rows=64):
@@ -110,7 +118,56 @@ def drop(twophase):
     fs.close()
 
 
+def cpu_child():
+    """the reference's own path on the host cores (the protocol of bench.py's CPU legs: threads bound, all cores)"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from cases import cavity_bc, cavity_state, channel_bc
+    from oracle_lib import Oracle, Ref
+    o = Oracle()
+    cores = os.cpu_count() or 1
+    Ref.lib().fsref_set_threads(cores)
+    for name in ("channel", "drop"):
+        if name == "channel":
+            nx, ny, nsub, kw = 4096 // scale, 1024 // scale, 5, dict(outflow_fix=1)
+            st, bc = cavity_state(o, nx, ny, lx=100.0, ly=1.0, rho=0.5), channel_bc()
+            st.a["U"][:] = 1.0
+        else:
+            nx = ny = 4096 // scale
+            nsub, kw = 3, dict(rebuild=1)
+            st, bc = cavity_state(o, nx, ny), cavity_bc()
+            st.rho_liquid = 1000.0
+            vf = ellipse_vf(nx, ny, st.dx, st.dy)
+            o.calc_rho_visc_vof(st, vf)
+            st.a["rho_u_old"][:] = st.a["rho_u"]
+            st.a["rho_v_old"][:] = st.a["rho_v"]
+        o.apply_velocity_bconds(st, bc)
+        r = Ref(nx, ny)
+        r.load(st)
+        r.set_bconds(bc)
+        r.solver_create(1e-6, 50)
+        r.solver_set_operator()
+        r.step(r.adjust_dt(0.9, 0.1), nsub, **kw)
+        t0 = time.perf_counter()
+        its, k = 0, 2
+        for _ in range(k):
+            it, res = r.step(r.adjust_dt(0.9, 0.1), nsub, **kw)
+            its += it
+        ms = (time.perf_counter() - t0) / k * 1e3
+        print(json.dumps({"config": name, "impl": "reference", "nx": nx, "ny": ny, "steps": k, "warmup": 1,
+                          "ms_per_step": round(ms, 1), "mcell_updates_per_s": round(nx * ny / ms / 1e3, 3),
+                          "pcg_iters_per_solve": round(its / (k * nsub), 2), "last_residual": res,
+                          "cores": cores, "solver": "HYPRE Struct PCG + PFMG, PS_PFMG_MAX_LEVELS 16"}), flush=True)
+        del r
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "--cpu":
+        env = dict(os.environ, OMP_PROC_BIND="close", OMP_PLACES="cores")
+        env.pop("OMP_NUM_THREADS", None)
+        sys.exit(subprocess.call([sys.executable, os.path.abspath(__file__), "--cpu-child", str(scale)], env=env))
+    if len(sys.argv) > 1 and sys.argv[1] == "--cpu-child":
+        cpu_child()
+        sys.exit(0)
     channel()
     drop(False)
     drop(True)

@@ -268,3 +268,47 @@ def test_drop_4096_variable_density(F):
     assert mass0 == pytest.approx(1.0 + 999.0 * np.pi * 0.125 * 0.25, rel=2e-3)
     ps.close()
     fs.close()
+
+
+def test_capped_hierarchy_vs_unmodified_reference_2048(F, oracle):
+    """GPU against the UNMODIFIED reference (oracle/_ref/libfsref.so: its headers + vendored HYPRE) at a size where
+    the reference's 16-level cap is active (src/LinearSolver_StructHypre.hpp:221-229: from 2048^2 upwards the
+    hierarchy stops at a 32 x 32 coarsest grid with 64 sweeps).  Lid-driven cavity 2048^2 with the constants of
+    scaling/LidDrivenFlow.cpp:16-42, developed for two timesteps, then one more step on both sides from the same
+    state: max_levels = 16, PCG tol 1e-6.  Both sides stop at a 1e-6 residual, so the fields agree to the solver
+    tolerance (not to rounding), the iteration counts per timestep are equal and so is dt."""
+    from cases import cavity_bc, cavity_state, rel_l2, to_gpu, vel_err
+    from oracle_lib import Ref, have_ref
+    if not have_ref():
+        pytest.skip("oracle/_ref/libfsref.so not built (it is built where /root/reference exists and travels with the repo)")
+    n, nsub, tol = 2048, 5, 1e-6
+    st, bc = cavity_state(oracle, n, n), cavity_bc()
+    oracle.apply_velocity_bconds(st, bc)
+    r = Ref(n, n)
+    r.load(st)
+    r.set_bconds(bc)
+    r.solver_create(tol, 50)
+    r.solver_set_operator()
+    for _ in range(2):  # develop the flow on the reference, then hand the SAME state to both sides
+        r.step(r.adjust_dt(0.9, 0.1), nsub)
+    r.store(st)
+    fs = to_gpu(F, st, bc)
+    ps = F.LinearSolver(fs, tol=tol, max_iter=50, max_levels=16)
+    ps.set_pressure_operator()
+    assert ps.num_levels == 16
+    dt_r = r.adjust_dt(0.9, 0.1)
+    dt_g = fs.adjust_dt(0.9, 0.1)
+    assert dt_g == pytest.approx(dt_r, rel=1e-12)
+    it_r, res_r = r.step(dt_r, nsub)
+    res_g, it_g = fs.step(ps, dt_g, nsub)
+    r.store(st)
+    U, V, P = fs.download("U"), fs.download("V"), fs.download("P")
+    ev = vel_err(U, V, st.U, st.V)
+    ep = rel_l2(P - P.mean(), st.p - st.p.mean())
+    print(f"\n[2048^2 vs libfsref] PCG iterations gpu {it_g} reference {it_r}, residuals {res_g:.2e} {res_r:.2e}, "
+          f"velocity rel L2 {ev:.2e}, pressure rel L2 {ep:.2e}")
+    assert res_g < tol and res_r < tol
+    assert it_g == it_r
+    assert ev <= 1e-6 and ep <= 1e-4
+    ps.close()
+    fs.close()
