@@ -13,7 +13,7 @@ from oracle_lib import (ALL_FIELDS, BConds, DIRICHLET, NEUMANN, PERIODIC, SYMMET
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-12
-SIZES = [(64, 64), (48, 20), (20, 48), (130, 67)]
+SIZES = [(64, 64), (48, 20), (20, 48), (130, 67), (37, 301)]
 
 
 def _down(fs, names):
