@@ -292,7 +292,7 @@ struct P2PBox {
   cudaStream_t xstream = nullptr;
   cudaEvent_t ev_ready = nullptr, ev_done = nullptr;
   bool pending = false;
-  bool overlap = true;                // FSGPU_NO_OVERLAP unset (read when the context is created)
+  bool overlap = false;               // FSGPU_OVERLAP=1 (read when the context is created)
   int64_t overlap_min_points = 262144;  // FSGPU_OVERLAP_MIN_POINTS: smaller slabs of a level exchange in stream order
 };
 std::map<std::string, std::shared_ptr<LocalGroup>> g_groups;
@@ -391,7 +391,10 @@ static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
     b.red.err = b.d_err; b.red.timeout = b.timeout;
     FS_CUDA(cudaMalloc(&b.d_red, sizeof(P2PRedDev)));
     FS_CUDA(cudaMemcpy(b.d_red, &b.red, sizeof(P2PRedDev), cudaMemcpyHostToDevice));
-    b.overlap = getenv("FSGPU_NO_OVERLAP") == nullptr;
+    // boundary-first overlap is opt-in (FSGPU_OVERLAP=1): at 16384^2 on 8 GPUs the two extra launches and the
+    // cross-stream events per exchange cost more than the ~10 us they hide (115.0 vs 111.6 ms per step,
+    // profiles/r02_multigpu.txt)
+    b.overlap = getenv("FSGPU_OVERLAP") != nullptr && atoi(getenv("FSGPU_OVERLAP")) != 0;
     if (const char* e = getenv("FSGPU_OVERLAP_MIN_POINTS")) b.overlap_min_points = atoll(e);
     FS_CUDA(cudaStreamCreateWithFlags(&b.xstream, cudaStreamNonBlocking));
     FS_CUDA(cudaEventCreateWithFlags(&b.ev_ready, cudaEventDisableTiming));
@@ -519,7 +522,10 @@ static int halo_mailbox_launch(fsgpu_ctx* c, double* const* ptrs, int n, int64_t
   a.e = ++cm->p2p.epoch;
   a.err = cm->p2p.d_err;
   a.timeout = cm->p2p.timeout;
-  k_halo_p2p<<<P2P_CTAS, P2P_THREADS, 0, st>>>(a);
+  // one CTA per 32 KB sent to a neighbour (coarse levels: a single CTA, whose arrival counter is trivially complete)
+  const size_t bytes = (size_t)n * (size_t)h * (size_t)pitch * sizeof(double);
+  const unsigned ctas = (unsigned)(bytes / 32768 < 1 ? 1 : bytes / 32768 > P2P_CTAS ? P2P_CTAS : bytes / 32768);
+  k_halo_p2p<<<ctas, P2P_THREADS, 0, st>>>(a);
   FS_LAUNCHED();
   return 0;
 }
@@ -568,7 +574,7 @@ int comm_alloc_fence(fsgpu_ctx* c) {
 }
 
 // > 0: slabs of a level with at least that many points split their producer kernels (boundary rows first)
-// and exchange on the transport's stream; 0: no overlap (no mailbox, or FSGPU_NO_OVERLAP)
+// and exchange on the transport's stream; 0: no overlap (no mailbox, or FSGPU_OVERLAP not set)
 int64_t comm_overlap_min_points(fsgpu_ctx* c) {
   if (!c->comm || !c->comm->p2p.on || !c->comm->p2p.overlap) return 0;
   return c->comm->p2p.overlap_min_points > 0 ? c->comm->p2p.overlap_min_points : 1;

@@ -1,6 +1,6 @@
 #!/bin/bash
 # multi-GPU comparison of the transports at 16384^2. usage: bash scripts/gpu_multi2.sh TAG N "variant variant ..."
-# variants: p2p (mailbox + overlap), p2p_noovl, nccl
+# variants: p2p (mailbox, full bench line), p2p_lite (no anchor / e2e), p2p_ovl (boundary-first overlap), nccl, nccl_full
 TAG=$1; N=$2; shift 2
 mkdir -p gpurun_out
 nvidia-smi -L | head -8
@@ -9,12 +9,13 @@ port=29541
 for VV in ${@:-p2p p2p_noovl nccl}; do
   # a variant may carry environment settings: name:ENV=VAL,ENV=VAL
   V=${VV%%:*}; ENVS=""; [ "$VV" != "$V" ] && ENVS=${VV#*:}
-  unset FSGPU_NO_OVERLAP FSGPU_REPL_POINTS FSGPU_OVERLAP_MIN_POINTS
+  unset FSGPU_OVERLAP FSGPU_REPL_POINTS FSGPU_OVERLAP_MIN_POINTS
   for kv in ${ENVS//,/ }; do export "$kv"; done
   case $V in
     p2p) ARGS="--halo p2p" ;;
-    p2p_noovl) ARGS="--halo p2p --no-anchor --no-e2e --no-ref-depth"; export FSGPU_NO_OVERLAP=1 ;;
+    p2p_ovl) ARGS="--halo p2p --no-anchor --no-e2e --no-ref-depth"; export FSGPU_OVERLAP=1 ;;
     p2p_lite) ARGS="--halo p2p --no-anchor --no-e2e --no-ref-depth" ;;
+    nccl_full) ARGS="--halo nccl" ;;
     nccl) ARGS="--halo nccl --no-anchor --no-e2e --no-ref-depth" ;;
     *) ARGS="$V" ;;
   esac

@@ -218,9 +218,8 @@ def test_slab_timesteps_p2p_halo(F, oracle, R, overlap, monkeypatch):
     monkeypatch.setenv("FSGPU_HALO", "p2p")
     monkeypatch.setenv("FSGPU_P2P_TIMEOUT_S", "5")
     if overlap:
+        monkeypatch.setenv("FSGPU_OVERLAP", "1")
         monkeypatch.setenv("FSGPU_OVERLAP_MIN_POINTS", "1")
-    else:
-        monkeypatch.setenv("FSGPU_NO_OVERLAP", "1")
     a, ra = run_ranks(F, st, bc, R, body, fields=("U", "V", "P"))
     assert all(direct) and len(direct) == R
     assert ra == rb
