@@ -254,7 +254,8 @@ static int partition(fsgpu_ps* s) {
     s->ld = s->nl;
     return 0;
   }
-  int64_t repl_points = 1 << 16;
+  // 2^18: at 16384^2 on 8 GPUs 103.6 -> 101.8 ms per step against 2^16, 2^20 no better (profiles/r02_multigpu.txt)
+  int64_t repl_points = 1 << 18;
   if (const char* e = getenv("FSGPU_REPL_POINTS")) repl_points = atoll(e);
   std::vector<int64_t> lo(R), hi(R);
   for (int r = 0; r < R; ++r)
