@@ -302,9 +302,9 @@ def main():
         dist.barrier()
     l0 = F.launch_count()
     e0.record(stream)
-    its = 0
+    its, last_res = 0, 0.0
     for _ in range(a.steps):
-        _, it = one_step()
+        last_res, it = one_step()
         its += it
     e1.record(stream)
     fs.sync()
@@ -320,6 +320,8 @@ def main():
     clk = clocks.stop()
     prof = F.prof_read()
     F.prof_enable(())
+    if not last_res < TOL:  # a step whose solves stop short of the tolerance is not the workload
+        raise SystemExit(f"bench.py: the last pressure solve did not converge (residual {last_res} >= {TOL})")
     value = n * n * a.steps / (ms * 1e-3) / 1e6
     k_bar = its / (a.steps * NSUB)
 
@@ -442,8 +444,8 @@ def main():
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"lid-driven cavity {n}^2 (scaling/LidDrivenFlow.cpp:16-42), NUM_SUBITER {NSUB}, "
                                    f"PCG tol {TOL} max_iter {MAX_ITER}, CFL {CFL}",
-                       "pcg_iters_per_solve": k_bar, "mg_levels": levels[0],
-                       "mg_depth": "uncapped (coarsest grid = 1 point)" if a.max_levels >= 40 else f"capped at {a.max_levels}",
+                       "pcg_iters_per_solve": k_bar, "pcg_last_residual": last_res, "mg_levels": levels[0],
+                       "mg_depth": "uncapped (coarsest grid = 2 points)" if a.max_levels >= 40 else f"capped at {a.max_levels}",
                        "reference_depth_16": ref_depth, "same_problem_1gpu": anchor,
                        "decomposition": None if world == 1 else
                        f"{world} slabs of i-rows, " + ("mailbox (peer-mapped, one kernel per exchange) halo exchange + scalar "

@@ -243,6 +243,16 @@ void fso_solver_set_operator(fso_solver* s, const double* op) {
         L[l].weight = 2.0 / (3.0 - beta / alpha);
       }
       if (l == max_levels - 1) cdir = -1;
+      /* Hierarchies deeper than the reference's cap of 16 (src/LinearSolver_StructHypre.hpp:221) stop at a
+       * two-point coarsest grid instead of a single point.  The one-point level of an all-Neumann system is
+       * the zero operator; on the anisotropic channel grid (4096 x 1024 on 100 x 1) carrying it made the
+       * V-cycle indefinite and PCG broke down after ~4 iterations at a 1e-2 residual, while one level
+       * fewer converges like the capped hierarchy (and the cavity's iteration counts do not change). */
+      if (cdir != -1 && s->o.max_levels > 16) {
+        int64_t nc[2] = {hi[0] - lo[0] + 1, hi[1] - lo[1] + 1};
+        nc[cdir] = floor_div2(hi[cdir]) - ceil_div2(lo[cdir]) + 1;
+        if (nc[0] * nc[1] <= 1) cdir = -1;
+      }
     }
     if (cdir == -1) { L[l].active = 1; L[l].cdir = -1; break; }
     L[l].cdir = cdir;

@@ -72,6 +72,7 @@ def timed(name, fs, ps, nsub, flags, cfl=0.9, dt_max=0.1):
     fs.sync()
     ms = e0.elapsed_time(e1) / steps
     um, vm, dm = fs.monitor()
+    assert res < 1e-6, f"{name}: the last solve did not converge (residual {res})"
     print(json.dumps({"config": name, "nx": fs.nx, "ny": fs.ny, "steps": steps, "warmup": warmup,
                       "ms_per_step": round(ms, 3), "mcell_updates_per_s": round(fs.nx * fs.ny / ms / 1e3, 1),
                       "pcg_iters_per_solve": round(its / (steps * nsub), 2), "last_residual": res,
