@@ -274,10 +274,14 @@ k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
 // (strip, chunk) tasks, so the optional dot product <b, x> (= <r, z> of PCG on level 0) ends in
 // ~1e3 partials.
 // DOT: 0 none, 1 PCG iteration (convergence test + beta), 2 first V-cycle (bi).
-constexpr int MOUT = 30, MWARPS = 4;
+// FS_UP_WARPS warps (= adjacent 30-column strips) per CTA; the CTAs per SM scale down with it (32 warps per SM)
+#ifndef FS_UP_WARPS
+#define FS_UP_WARPS 8
+#endif
+constexpr int MOUT = 30, MWARPS = FS_UP_WARPS, UP_MINB = 32 / FS_UP_WARPS;
 
 template <int CDIR, int DOT>
-__global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB)
+__global__ void __launch_bounds__(32 * MWARPS, UP_MINB)
 k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
            const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket,
            const BShift bs) {
@@ -368,10 +372,12 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
 // warps consume a row as soon as its bytes have landed and keep the x0 window in registers exactly
 // as above (same arithmetic, same association: results are bit-identical).  Segments start at an even
 // physical column (16-byte aligned source) two columns left of the strip's first output column.
-constexpr int RING_SEG = 128, RING_SLOTS = 6;
 #ifndef FS_RING_STAGES
-#define FS_RING_STAGES 4
+#define FS_RING_STAGES (FS_UP_WARPS >= 8 ? 3 : 4)
 #endif
+// doubles per operand row segment (the strip + its halo columns, a multiple of 16 bytes) and per coarse
+// segment of a j-coarsened level (half the strip + slack); segments per stage
+constexpr int RING_SEG = 32 * MWARPS, RING_CSEG = RING_SEG / 2 + 8, RING_SLOTS = 6;
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long* b, unsigned count) {
@@ -415,7 +421,7 @@ struct RingBars {
 };
 
 template <int CDIR, int DOT>
-__global__ void __launch_bounds__(32 * MWARPS, FS_MARCH_MINB)
+__global__ void __launch_bounds__(32 * MWARPS, UP_MINB)
 k_up_ring(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
           const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket,
           const BShift bs) {
@@ -453,7 +459,7 @@ k_up_ring(const LevelDev f, const double* __restrict__ fb, double* __restrict__ 
       bulk_g2s(ring[st][4], xc + oc, SB, &full[st]);
       if (par) bulk_g2s(ring[st][5], xc + oc + Pc, SB, &full[st]);
     } else {
-      constexpr unsigned CB = 72 * sizeof(double);
+      constexpr unsigned CB = RING_CSEG * sizeof(double);
       const int cj0 = ((psp * (MOUT * MWARPS) - 2 - foff) >> 1) & ~1;  // even, <= the leftmost coarse column used
       mbar_expect_tx(&full[st], 4u * SB + CB);
       bulk_g2s(ring[st][4], xc + (int64_t)(li + FS_RO) * Pc + cj0 + FS_CO, CB, &full[st]);
@@ -822,8 +828,8 @@ static int coarse_solve(fsgpu_ps* s, int l, const double* b, double* x) {
 // rounds of the round-robin deal best (tasks / (rounds x grid)), discounted by the two rows a task re-reads
 // around its range.  Levels with fewer tasks than a few rounds: smaller tasks (they are latency bound; a
 // task's rows are a serial chain of loads), down to one row while the level still fits one wave.
-static int pick_rows(int64_t rows, int64_t strips) {
-  const int64_t G = (int64_t)FS_NUM_SMS * FS_MARCH_MINB;
+static int pick_rows(int64_t rows, int64_t strips, int minb = FS_MARCH_MINB) {
+  const int64_t G = (int64_t)FS_NUM_SMS * minb;
   if (strips * cdiv(rows, 64) >= 2 * G) {
     int best = 64;
     double best_score = 0.0;
@@ -835,13 +841,13 @@ static int pick_rows(int64_t rows, int64_t strips) {
     return best;
   }
   int mr = 64;
-  while (mr > 4 && strips * cdiv(rows, mr) < (int64_t)FS_NUM_SMS * 16) mr >>= 1;
-  while (mr > 1 && strips * cdiv(rows, mr) < (int64_t)FS_NUM_SMS * 2) mr >>= 1;
+  while (mr > 4 && strips * cdiv(rows, mr) < 2 * G) mr >>= 1;
+  while (mr > 1 && strips * cdiv(rows, mr) < G / 4) mr >>= 1;
   return mr;
 }
-static unsigned march_blocks(int64_t rows, int64_t strips, int mr) {
+static unsigned march_blocks(int64_t rows, int64_t strips, int mr, int minb = FS_MARCH_MINB) {
   const int64_t total = strips * cdiv(rows, mr);
-  const int64_t cap = (int64_t)FS_NUM_SMS * FS_MARCH_MINB;
+  const int64_t cap = (int64_t)FS_NUM_SMS * minb;
   return (unsigned)(total < cap ? (total > 0 ? total : 1) : cap);
 }
 
@@ -912,8 +918,8 @@ static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_m
     return 0;
   }
   const int64_t strips = cdiv(f.n1, MOUT * MWARPS);
-  const int mr      = pick_rows(f.i1 - f.i0, strips);
-  const unsigned nb = march_blocks(f.i1 - f.i0, strips, mr);
+  const int mr      = pick_rows(f.i1 - f.i0, strips, UP_MINB);
+  const unsigned nb = march_blocks(f.i1 - f.i0, strips, mr, UP_MINB);
   const int bl = 32 * MWARPS;
   const BShift bs{l == 0 ? s->b_shift : nullptr, s->b_shift_size};
 #define UP_ARGS f, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket, bs
