@@ -606,6 +606,7 @@ static int ps_destroy_impl(fsgpu_ps* s) {
   }
   cudaSetDevice(s->c->device);
   cudaStreamSynchronize(s->c->stream);
+  if (s->nb_token) comm_unmap_neighbours(s->c, s->nb_token);
   cudaFree(s->slab);
   cudaFree(s->scal);
   if (s->h_scal) cudaFreeHost(s->h_scal);

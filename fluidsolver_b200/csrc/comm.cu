@@ -284,6 +284,10 @@ struct P2PBox {
   std::vector<char*> peer;            // every rank's mailbox (peer[rank] == base)
   std::vector<char> ipc;              // mapped with cudaIpcOpenMemHandle (to be closed)
   size_t red_off = 0;                 // byte offset of the scalar all-reduce area
+  size_t push_off = 0;                // byte offset of the fused-push flags: [level][kind b | x][side] u64
+  unsigned int* push_ticket = nullptr;  // arrival counter of the producer kernels
+  bool push = false;                  // fused push allowed (FSGPU_PUSH, read when the context is created)
+  unsigned long long push_epoch = 0;  // one per V-cycle of any solver of this context
   int *h_err = nullptr, *d_err = nullptr;  // mapped pinned flag the kernel raises on a timeout
   long long timeout = 0;              // clock64 ticks a device-side wait may last
   P2PRedDev red{};                    // what the reduction kernels need (host copy)
@@ -324,8 +328,9 @@ static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
   if (!env || strcmp(env, "p2p") != 0) return 0;
   b.cap = (size_t)((8 * c->g.pitch + 15) / 16 * 16);  // the widest exchange: 4 arrays x FS_RO rows
   b.red_off = 256 + 4 * b.cap * sizeof(double);
-  const size_t bytes = b.red_off + P2P_MAX_RANKS * sizeof(unsigned long long) +
-                       2 * (size_t)P2P_MAX_RANKS * P2P_RED_MAX * sizeof(double);
+  b.push_off = b.red_off + P2P_MAX_RANKS * sizeof(unsigned long long) +
+               2 * (size_t)P2P_MAX_RANKS * P2P_RED_MAX * sizeof(double);
+  const size_t bytes = b.push_off + (size_t)P2P_PUSH_LEVELS * 4 * sizeof(unsigned long long);
   int ok = c->nranks <= P2P_MAX_RANKS ? 1 : 0;
   b.peer.assign((size_t)c->nranks, nullptr);
   b.ipc.assign((size_t)c->nranks, 0);
@@ -395,6 +400,15 @@ static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
     // cross-stream events per exchange cost more than the ~10 us they hide (115.0 vs 111.6 ms per step,
     // profiles/r02_multigpu.txt)
     b.overlap = getenv("FSGPU_OVERLAP") != nullptr && atoi(getenv("FSGPU_OVERLAP")) != 0;
+    // One process per GPU: on unless FSGPU_PUSH=0.  In-process ranks share ONE device: a consumer kernel whose
+    // CTAs fill the GPU while they wait would keep the neighbour rank's producer from ever being scheduled, so
+    // there it is opt-in (FSGPU_PUSH=1; the tests' grids are a handful of CTAs).
+    {
+      const char* e = getenv("FSGPU_PUSH");
+      b.push = cm->transport == FSGPU_TRANSPORT_NCCL ? !(e && atoi(e) == 0) : (e && atoi(e) != 0);
+    }
+    FS_CUDA(cudaMalloc(&b.push_ticket, sizeof(unsigned int)));
+    FS_CUDA(cudaMemset(b.push_ticket, 0, sizeof(unsigned int)));
     if (const char* e = getenv("FSGPU_OVERLAP_MIN_POINTS")) b.overlap_min_points = atoll(e);
     FS_CUDA(cudaStreamCreateWithFlags(&b.xstream, cudaStreamNonBlocking));
     FS_CUDA(cudaEventCreateWithFlags(&b.ev_ready, cudaEventDisableTiming));
@@ -414,6 +428,7 @@ static void p2p_teardown(Comm* cm) {
   if (b.ev_ready) cudaEventDestroy(b.ev_ready);
   if (b.ev_done) cudaEventDestroy(b.ev_done);
   if (b.d_red) cudaFree(b.d_red);
+  if (b.push_ticket) cudaFree(b.push_ticket);
   if (b.base) cudaFree(b.base);
   if (b.h_err) cudaFreeHost(b.h_err);
   b = P2PBox();
@@ -503,6 +518,121 @@ void comm_destroy(fsgpu_ctx* c) {
   }
   delete cm;
   c->comm = nullptr;
+}
+
+// ---- fused push: neighbours' arrays mapped here ---------------------------------------------------
+// collective: every rank contributes `bytes` bytes of host memory and receives all ranks' contributions
+int comm_allgather_host(fsgpu_ctx* c, const void* mine, size_t bytes, void* all) {
+  Comm* cm = c->comm;
+  if (!cm || c->nranks <= 1) { memcpy(all, mine, bytes); return 0; }
+  if (cm->transport == FSGPU_TRANSPORT_NCCL) {
+    char* d = nullptr;
+    FS_CUDA(cudaMalloc(&d, bytes * (size_t)c->nranks));
+    FS_CUDA(cudaMemcpyAsync(d + bytes * c->rank, mine, bytes, cudaMemcpyHostToDevice, c->stream));
+    FS_NCCL(g_nccl.AllGather(d + bytes * c->rank, d, bytes, ncclChar, cm->nccl, c->stream));
+    FS_CUDA(cudaMemcpyAsync(all, d, bytes * (size_t)c->nranks, cudaMemcpyDeviceToHost, c->stream));
+    FS_CUDA(cudaStreamSynchronize(c->stream));
+    cudaFree(d);
+    return 0;
+  }
+  LocalGroup& g = *cm->grp;
+  g.host[c->rank].assign((bytes + 7) / 8, 0.0);
+  memcpy(g.host[c->rank].data(), mine, bytes);
+  FS_CUDA(cudaStreamSynchronize(c->stream));
+  LOCAL_BARRIER(cm);
+  for (int r = 0; r < c->nranks; ++r) memcpy((char*)all + bytes * r, g.host[r].data(), bytes);
+  LOCAL_BARRIER(cm);
+  return 0;
+}
+
+// collective: `base` is this rank's instance of an allocation every rank has (the solver's slab).  Returns the
+// neighbours' instances as mapped in THIS rank's address space (cudaIpc between processes, the plain pointers
+// inside one process; null at the ends of the chain).  *token: what comm_unmap_neighbours needs.
+struct NeighbourMap { void* ptr[2]; bool ipc[2]; };
+int comm_map_neighbours(fsgpu_ctx* c, void* base, void** up, void** dn, void** token) {
+  *up = *dn = nullptr;
+  *token = nullptr;
+  Comm* cm = c->comm;
+  if (!cm || c->nranks <= 1 || !cm->p2p.on) return 0;
+  NeighbourMap* m = new NeighbourMap();
+  m->ptr[0] = m->ptr[1] = nullptr;
+  m->ipc[0] = m->ipc[1] = false;
+  const int peer[2] = {c->rank - 1, c->rank + 1 < c->nranks ? c->rank + 1 : -1};
+  if (cm->transport == FSGPU_TRANSPORT_NCCL) {
+    cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof(mine));
+    int ok = cudaIpcGetMemHandle(&mine, base) == cudaSuccess ? 1 : 0;
+    std::vector<char> all((size_t)c->nranks * (sizeof(mine) + sizeof(int)));
+    char rec[sizeof(mine) + sizeof(int)];
+    memcpy(rec, &mine, sizeof(mine));
+    memcpy(rec + sizeof(mine), &ok, sizeof(int));
+    if (comm_allgather_host(c, rec, sizeof(rec), all.data())) { delete m; return 1; }
+    for (int r = 0; r < c->nranks; ++r) {
+      int okr;
+      memcpy(&okr, all.data() + (size_t)r * sizeof(rec) + sizeof(mine), sizeof(int));
+      ok = ok && okr;
+    }
+    for (int sd = 0; sd < 2 && ok; ++sd) {
+      if (peer[sd] < 0) continue;
+      cudaIpcMemHandle_t h;
+      memcpy(&h, all.data() + (size_t)peer[sd] * sizeof(rec), sizeof(h));
+      void* q = nullptr;
+      if (cudaIpcOpenMemHandle(&q, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) ok = 0;
+      else { m->ptr[sd] = q; m->ipc[sd] = true; }
+    }
+    cudaGetLastError();
+    // all ranks or none (a rank that cannot map must not be pushed to either)
+    int allok = ok;
+    std::vector<int> oks((size_t)c->nranks);
+    if (comm_allgather_host(c, &ok, sizeof(int), oks.data())) { delete m; return 1; }
+    for (int r = 0; r < c->nranks; ++r) allok = allok && oks[(size_t)r];
+    if (!allok) {
+      for (int sd = 0; sd < 2; ++sd)
+        if (m->ipc[sd] && m->ptr[sd]) cudaIpcCloseMemHandle(m->ptr[sd]);
+      delete m;
+      return 0;
+    }
+  } else {
+    std::vector<void*> all((size_t)c->nranks);
+    if (comm_allgather_host(c, &base, sizeof(void*), all.data())) { delete m; return 1; }
+    for (int sd = 0; sd < 2; ++sd)
+      if (peer[sd] >= 0) m->ptr[sd] = all[(size_t)peer[sd]];
+  }
+  *up = m->ptr[0];
+  *dn = m->ptr[1];
+  *token = m;
+  return 0;
+}
+void comm_unmap_neighbours(fsgpu_ctx* c, void* token) {
+  (void)c;
+  NeighbourMap* m = static_cast<NeighbourMap*>(token);
+  if (!m) return;
+  for (int sd = 0; sd < 2; ++sd)
+    if (m->ipc[sd] && m->ptr[sd]) cudaIpcCloseMemHandle(m->ptr[sd]);
+  delete m;
+}
+// 1: producer kernels may push halo rows into mapped neighbour arrays (mailbox transport on, FSGPU_PUSH)
+int comm_push_enabled(fsgpu_ctx* c) { return c->comm && c->comm->p2p.on && c->comm->p2p.push ? 1 : 0; }
+unsigned long long comm_push_next_epoch(fsgpu_ctx* c) { return ++c->comm->p2p.push_epoch; }
+// flags of the exchange (level, kind): what a producer raises in its neighbours' mailboxes, what a consumer waits for
+void comm_push_flags(fsgpu_ctx* c, int level, int kind, HaloPush* p, HaloWait* w) {
+  P2PBox& b = c->comm->p2p;
+  auto flag = [&](char* base, int side) {
+    return reinterpret_cast<unsigned long long*>(base + b.push_off) + ((size_t)level * 2 + kind) * 2 + side;
+  };
+  // rows I send up land in rank - 1's LOWER halo: its flag for side 1; rows I send down: rank + 1's side 0
+  if (p) {
+    p->raise[0] = b.nb[0] ? flag(b.nb[0], 1) : nullptr;
+    p->raise[1] = b.nb[1] ? flag(b.nb[1], 0) : nullptr;
+    p->ticket   = b.push_ticket;
+  }
+  if (w) {
+    w->flag[0] = b.nb[0] ? flag(b.base, 0) : nullptr;
+    w->flag[1] = b.nb[1] ? flag(b.base, 1) : nullptr;
+    w->err = b.d_err;
+    w->mine = b.base;
+    w->timeout = b.timeout;
+  }
 }
 
 // true when this exchange fits the mailbox slots (the same decision on every rank)

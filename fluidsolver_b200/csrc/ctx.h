@@ -93,6 +93,15 @@ int64_t comm_overlap_min_points(fsgpu_ctx* c);  // 0: no overlap; else the small
 struct P2PRedDev;
 const P2PRedDev* comm_red_dev(fsgpu_ctx* c);  // device struct of the in-kernel scalar all-reduce (null: none)
 int comm_allreduce(fsgpu_ctx* c, double* dev, int64_t n, int op);
+// fused push (p2p.cuh): collectives used when the solver (re)allocates its levels
+struct HaloPush;
+struct HaloWait;
+int comm_allgather_host(fsgpu_ctx* c, const void* mine, size_t bytes, void* all);
+int comm_map_neighbours(fsgpu_ctx* c, void* base, void** up, void** dn, void** token);
+void comm_unmap_neighbours(fsgpu_ctx* c, void* token);
+int comm_push_enabled(fsgpu_ctx* c);
+unsigned long long comm_push_next_epoch(fsgpu_ctx* c);  // epochs are per context: its mailbox flags outlive a solver
+void comm_push_flags(fsgpu_ctx* c, int level, int kind, HaloPush* p, HaloWait* w);
 // n doubles to / from one peer rank (the x-periodic wrap-around); peer < 0: not a participant
 int comm_sendrecv(fsgpu_ctx* c, int peer, const double* const* send, double* const* recv, int narr, int64_t n);
 // halo rows of flow fields (ids), h rows each

@@ -26,7 +26,75 @@ struct P2PRedDev {
   long long timeout;          // clock64 ticks a wait may last before it gives up
 };
 
+// ---- halo rows pushed by the kernel that produces them ("fused push", comm.cu / solver_cycle.cu) ----------
+// A producer kernel of a distributed multigrid level stores every point of its h boundary rows twice: into its
+// own array and, over NVLink, into the halo rows of the neighbouring rank's array (the same global row
+// indices there).  Each CTA fences its remote stores and takes a ticket; the last one raises the epoch flag in
+// the neighbours' mailboxes.  The kernels that read those halo rows wait for their own flags in their prologue.
+// No exchange kernel, no unpacking: what is left of an exchange is the flag's flight time.
+// Safe without double buffering: between two writes of the same halo rows lies a PCG all-reduce, which the
+// writer can only pass after the reader's V-cycle -- every kernel that read the old rows -- has finished.
+#define P2P_PUSH_LEVELS 40
+struct HaloPush {
+  int on, h;                      // on == 0: plain kernel
+  long long i0, i1;               // rows this rank owns of the produced array (global indices)
+  double* dst[2];                 // the array's virtual base in rank - 1's / rank + 1's address space (null: none)
+  unsigned long long* raise[2];   // that neighbour's flag for rows arriving from me
+  unsigned long long epoch;
+  unsigned int* ticket;           // arrival counter (this rank's memory; wraps to 0)
+};
+struct HaloWait {
+  int on;
+  const unsigned long long* flag[2];  // my flags: rows from rank - 1 / rank + 1 (null: no such neighbour)
+  unsigned long long epoch;
+  int* err;                       // mapped pinned error flag
+  char* mine;                     // my mailbox (device copy of the error flag)
+  long long timeout;
+};
+
 #ifdef __CUDACC__
+// consumer prologue (all threads of every CTA): the halo rows of this epoch have landed
+__device__ __forceinline__ void halo_wait(const HaloWait& w) {
+  if (!w.on) return;
+  if (threadIdx.x == 0 && threadIdx.y == 0) {
+    const long long t0 = clock64();
+    for (int sd = 0; sd < 2; ++sd) {
+      if (!w.flag[sd]) continue;
+      while (*reinterpret_cast<const volatile unsigned long long*>(w.flag[sd]) < w.epoch) {
+        if (clock64() - t0 > w.timeout || *reinterpret_cast<volatile int*>(w.mine + 200)) {
+          w.err[1] = -(int)w.epoch;
+          *w.err   = 1;
+          *reinterpret_cast<volatile int*>(w.mine + 200) = 1;
+          break;
+        }
+      }
+    }
+    __threadfence_system();
+  }
+  __syncthreads();
+}
+// producer epilogue (all threads of every CTA, after their last store)
+__device__ __forceinline__ void halo_push_done(const HaloPush& p) {
+  if (!p.on) return;
+  __threadfence_system();  // my remote stores are visible before my ticket is
+  __syncthreads();
+  if (threadIdx.x == 0 && threadIdx.y == 0) {
+    const unsigned nb = gridDim.x * gridDim.y;
+    if (atomicInc(p.ticket, nb - 1) == nb - 1) {
+      __threadfence_system();
+      if (p.dst[0]) *reinterpret_cast<volatile unsigned long long*>(p.raise[0]) = p.epoch;
+      if (p.dst[1]) *reinterpret_cast<volatile unsigned long long*>(p.raise[1]) = p.epoch;
+    }
+  }
+}
+// the neighbour's copy of row `row`, or null when the row is not one of the h rows next to that neighbour
+__device__ __forceinline__ double* halo_push_row(const HaloPush& p, long long row) {
+  if (!p.on) return nullptr;
+  if (p.dst[0] && row < p.i0 + p.h) return p.dst[0];
+  if (p.dst[1] && row >= p.i1 - p.h) return p.dst[1];
+  return nullptr;
+}
+
 __device__ __forceinline__ volatile unsigned long long* p2p_red_flag(char* base, size_t off, int src) {
   return reinterpret_cast<volatile unsigned long long*>(base + off) + src;
 }

@@ -142,6 +142,13 @@ struct fsgpu_ps {
   bool rhs_mean_pending = false;
   const double* b_shift = nullptr;
   double b_shift_size = 1.0;
+  // fused push (p2p.cuh): the neighbours' level arrays as mapped here (virtual bases of b and x of every
+  // distributed level, [level][0: rank - 1, 1: rank + 1]), set up by alloc_levels when the mailbox transport is on
+  bool push_ready = false;
+  void* nb_token = nullptr;
+  double* nb_b[FS_MAX_LEVELS][2] = {};
+  double* nb_x[FS_MAX_LEVELS][2] = {};
+  unsigned long long push_epoch = 0;
   bool is_setup = false;
   bool levels_allocated = false;
   double last_dt = 0.0;

@@ -121,11 +121,13 @@ struct MarchCursor {
 // k_down_march0: coarsening along i.  Per fine row the warp forms X = w b / d, then the residual
 // R of the row above from three rows of X held in registers (left/right by shuffle), and on every
 // second row the coarse rhs  b_c = R + pp(row-1) R(row-1) + pm(row+1) R(row+1).
-template <bool ACTIVE, bool SHIFT>
+template <bool ACTIVE, bool SHIFT, bool PUSH>
 __global__ void __launch_bounds__(128, FS_MARCH_MINB)
 k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
-              double* __restrict__ cb, double w, int mr, const PcgScal* scal, const BShift bs) {
+              double* __restrict__ cb, double w, int mr, const PcgScal* scal, const BShift bs, const HaloWait wt,
+              const HaloPush ps) {
   if (scal->done) return;
+  halo_wait(wt);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
   const double bm = SHIFT ? bs.mean() : 0.0;
@@ -167,21 +169,29 @@ k_down_march0(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
         const double pcm = ACTIVE ? pc3 : __ldg(f.pc + o - 3 * P);
         const double pcp = ACTIVE ? pc1 : __ldg(f.pc + o - P);
         const double v = mg_restrict(Rb, cx2, pcm, Ra, cx1, pcp, Rn);
-        if (store_lane) cb[(((li - 2 - foff) >> 1) + FS_RO) * Pc + lj + FS_CO] = v;
+        const int crow = (li - 2 - foff) >> 1;
+        if (store_lane) cb[(crow + FS_RO) * Pc + lj + FS_CO] = v;
+        if (PUSH) {  // a boundary row of the slab: also into the neighbour's halo
+          double* pr = halo_push_row(ps, crow);
+          if (pr && store_lane) pr[(int64_t)(crow + FS_RO) * Pc + lj + FS_CO] = v;
+        }
       }
       X2 = X1; X1 = X0; b1 = b0; cx2 = cx1; cx1 = cx0; cy1 = cy0; cy1p = cy0p; Ra = Rb; Rb = Rn;
       pc3 = pc2; pc2 = pc1; pc1 = pc0;
     }
   }
+  if (PUSH) halo_push_done(ps);
 }
 
 // k_down_march1: coarsening along j.  Lanes 1..30 hold a valid residual (X of the neighbours by
 // shuffle), lanes 2..29 that sit on a C column emit  b_c = R + pp(j-1) R(j-1) + pm(j+1) R(j+1).
-template <bool ACTIVE, bool SHIFT>
+template <bool ACTIVE, bool SHIFT, bool PUSH>
 __global__ void __launch_bounds__(128, FS_MARCH_MINB)
 k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
-              double* __restrict__ cb, double w, int mr, const PcgScal* scal, const BShift bs) {
+              double* __restrict__ cb, double w, int mr, const PcgScal* scal, const BShift bs, const HaloWait wt,
+              const HaloPush ps) {
   if (scal->done) return;
+  halo_wait(wt);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
   const double bm = SHIFT ? bs.mean() : 0.0;
@@ -221,10 +231,15 @@ k_down_march1(const LevelDev f, const double* __restrict__ fb, const LevelDev c,
         const double Rl = __shfl_up_sync(0xffffffffu, Rn, 1), Rr = __shfl_down_sync(0xffffffffu, Rn, 1);
         const double v = mg_restrict(Rn, cy1, pcl, Rl, cy1p, pcr, Rr);
         if (store_lane) cb[(li - 1 + FS_RO) * Pc + oc_col] = v;
+        if (PUSH) {
+          double* pr = halo_push_row(ps, li - 1);
+          if (pr && store_lane) pr[(int64_t)(li - 1 + FS_RO) * Pc + oc_col] = v;
+        }
       }
       X2 = X1; X1 = X0; b1 = b0; cx1 = cx0; cy1 = cy0; cy1p = cy0p; d1 = d0;
     }
   }
+  if (PUSH) halo_push_done(ps);
 }
 
 // value at fine point (li, lj) after [zero-guess relaxation] + interpolation of the coarse x
@@ -256,12 +271,17 @@ __device__ __forceinline__ double x_interp(const LevelDev& f, double bq, const L
 template <int CDIR>
 __global__ void __launch_bounds__(BX* BY)
 k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
-            const double* __restrict__ cxv, const PcgScal* scal) {
+            const double* __restrict__ cxv, const PcgScal* scal, const HaloWait wt, const HaloPush ps) {
   if (scal->done) return;
+  halo_wait(wt);
   for_each_point(f.i0, f.i1, f.n1, [&](int64_t li, int64_t lj) {
     const int64_t k = f.idx(li, lj);
-    fx[k] = x_interp<CDIR, false>(f, 0.0, c, cxv, li, lj, k, 0.0);
+    const double v = x_interp<CDIR, false>(f, 0.0, c, cxv, li, lj, k, 0.0);
+    fx[k] = v;
+    double* pr = halo_push_row(ps, li);
+    if (pr) pr[k] = v;
   });
+  halo_push_done(ps);
 }
 
 // active level, "marching" formulation.  A warp owns a strip of 32 consecutive columns (30 of
@@ -280,12 +300,13 @@ k_up_interp(const LevelDev f, double* __restrict__ fx, const LevelDev c,
 #endif
 constexpr int MOUT = 30, MWARPS = FS_UP_WARPS, UP_MINB = 32 / FS_UP_WARPS;
 
-template <int CDIR, int DOT>
+template <int CDIR, int DOT, bool PUSH>
 __global__ void __launch_bounds__(32 * MWARPS, UP_MINB)
 k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
            const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket,
-           const BShift bs) {
+           const BShift bs, const HaloWait wt, const HaloPush ps) {
   if (scal->done) return;
+  halo_wait(wt);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int n1 = (int)f.n1, P = (int)f.pitch, Pc = (int)c.pitch, foff = (int)c.foff;
   const bool shift = DOT == 2 && bs.sum != nullptr;  // only the first V-cycle of a solve can see an unshifted rhs
@@ -351,10 +372,15 @@ k_up_march(const LevelDev f, const double* __restrict__ fb, double* __restrict__
           fx[o - P] = xo;
           if (DOT) acc[0] += bc * xo;
         }
+        if (PUSH) {
+          double* pr = halo_push_row(ps, li - 1);
+          if (pr && store_lane) pr[o - P] = xo;
+        }
       }
       x0p = x0c; x0c = x0n; bc = bn; dic = din; dc = dn; cyc = cyn; cy1c = cy1n; cxc = cxn; cxn = cxnn;
     }
   }
+  if (PUSH) halo_push_done(ps);
   if (DOT) {
     double tot[1];
     if (grid_reduce<ReduceSum, 1>(acc, part, ticket, tot)) {
@@ -420,12 +446,13 @@ struct RingBars {
   }
 };
 
-template <int CDIR, int DOT>
+template <int CDIR, int DOT, bool PUSH>
 __global__ void __launch_bounds__(32 * MWARPS, UP_MINB)
 k_up_ring(const LevelDev f, const double* __restrict__ fb, double* __restrict__ fx, const LevelDev c,
           const double* __restrict__ xc, double w, int mr, PcgScal* scal, double* part, unsigned int* ticket,
-          const BShift bs) {
+          const BShift bs, const HaloWait wt, const HaloPush ps) {
   if (scal->done) return;
+  halo_wait(wt);
   constexpr int S = FS_RING_STAGES;
   const bool shift = DOT == 2 && bs.sum != nullptr;
   const double bm  = shift ? bs.mean() : 0.0;
@@ -532,10 +559,15 @@ k_up_ring(const LevelDev f, const double* __restrict__ fb, double* __restrict__ 
           fx[o - P] = xo;
           if (DOT) acc[0] += bc * xo;
         }
+        if (PUSH) {
+          double* pr = halo_push_row(ps, li - 1);
+          if (pr && store_lane) pr[o - P] = xo;
+        }
       }
       x0p = x0c; x0c = x0n; bc = bn; dic = din; dc = dn; cyc = cyn; cy1c = cy1n; cxc = cxn; cxn = cxnn;
     }
   }
+  if (PUSH) halo_push_done(ps);
   if (DOT) {
     double tot[1];
     if (grid_reduce<ReduceSum, 1>(acc, part, ticket, tot)) {
@@ -879,23 +911,47 @@ static int launch_down(fsgpu_ps* s, int l, const double* fb, int64_t r0 = -1, in
     else { f.i0 = r0; f.i1 = r1; }
   }
   const BShift bs{l == 0 ? s->b_shift : nullptr, s->b_shift_size};  // only level 0 reads the rhs itself
+  // fused push (p2p.cuh): this kernel reads the halo rows of b_l (pushed by the neighbours' previous down kernel)
+  // and stores the boundary rows of b_{l+1} into the neighbours' halos as well
+  HaloWait wt{};
+  HaloPush ps{};
+  if (s->push_ready && r0 < 0) {
+    if (l >= 1 && l < s->ld) {
+      wt.on = 1; wt.epoch = s->push_epoch;
+      comm_push_flags(s->c, l, 0, nullptr, &wt);
+    }
+    if (l + 1 < s->ld) {
+      ps.on = 1; ps.h = FS_RO; ps.i0 = L[l + 1].own0; ps.i1 = L[l + 1].own1; ps.epoch = s->push_epoch;
+      ps.dst[0] = s->nb_b[l + 1][0]; ps.dst[1] = s->nb_b[l + 1][1];
+      comm_push_flags(s->c, l + 1, 0, &ps, nullptr);
+    }
+  }
+#define DOWN_ARGS(MR) f, fb, c, c.b, L[l].weight, MR, s->scal, bs, wt, ps
+#define DOWN_LAUNCH(K, MR)                                                                              \
+  do {                                                                                                  \
+    const bool a_ = L[l].active != 0, h_ = bs.sum != nullptr, p_ = ps.on != 0;                          \
+    if (a_ && h_ && p_) K<true, true, true><<<nb, 128, 0, st>>>(DOWN_ARGS(MR));                         \
+    else if (a_ && h_) K<true, true, false><<<nb, 128, 0, st>>>(DOWN_ARGS(MR));                         \
+    else if (a_ && p_) K<true, false, true><<<nb, 128, 0, st>>>(DOWN_ARGS(MR));                         \
+    else if (a_) K<true, false, false><<<nb, 128, 0, st>>>(DOWN_ARGS(MR));                              \
+    else if (h_ && p_) K<false, true, true><<<nb, 128, 0, st>>>(DOWN_ARGS(MR));                         \
+    else if (h_) K<false, true, false><<<nb, 128, 0, st>>>(DOWN_ARGS(MR));                              \
+    else if (p_) K<false, false, true><<<nb, 128, 0, st>>>(DOWN_ARGS(MR));                              \
+    else K<false, false, false><<<nb, 128, 0, st>>>(DOWN_ARGS(MR));                                     \
+  } while (0)
   if (L[l].cdir == 0) {
     const int64_t strips = cdiv(f.n1, 120);
     const int mrc = pick_rows(c.i1 - c.i0, strips);
     const unsigned nb = march_blocks(c.i1 - c.i0, strips, mrc);
-    if (bs.sum && L[l].active) k_down_march0<true, true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal, bs);
-    else if (bs.sum) k_down_march0<false, true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal, bs);
-    else if (L[l].active) k_down_march0<true, false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal, bs);
-    else k_down_march0<false, false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mrc, s->scal, bs);
+    DOWN_LAUNCH(k_down_march0, mrc);
   } else {
     const int64_t strips = cdiv(f.n1, 112);
     const int mr = pick_rows(f.i1 - f.i0, strips);
     const unsigned nb = march_blocks(f.i1 - f.i0, strips, mr);
-    if (bs.sum && L[l].active) k_down_march1<true, true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal, bs);
-    else if (bs.sum) k_down_march1<false, true><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal, bs);
-    else if (L[l].active) k_down_march1<true, false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal, bs);
-    else k_down_march1<false, false><<<nb, 128, 0, st>>>(f, fb, c, c.b, L[l].weight, mr, s->scal, bs);
+    DOWN_LAUNCH(k_down_march1, mr);
   }
+#undef DOWN_LAUNCH
+#undef DOWN_ARGS
   FS_LAUNCHED();
   return 0;
 }
@@ -912,8 +968,23 @@ static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_m
     if (r1 <= r0) return 0;
     f.i0 = r0; f.i1 = r1;
   }
+  // fused push: this kernel reads the halo row of x_{l+1} (pushed by the neighbours' previous up kernel) and
+  // stores the boundary rows of x_l into the neighbours' halos as well (levels >= 1: level 0's z needs no halo)
+  HaloWait wt{};
+  HaloPush ps{};
+  if (s->push_ready && r0 < 0) {
+    if (l + 1 < s->ld) {
+      wt.on = 1; wt.epoch = s->push_epoch;
+      comm_push_flags(c, l + 1, 1, nullptr, &wt);
+    }
+    if (l >= 1 && l < s->ld) {
+      ps.on = 1; ps.h = 1; ps.i0 = L[l].own0; ps.i1 = L[l].own1; ps.epoch = s->push_epoch;
+      ps.dst[0] = s->nb_x[l][0]; ps.dst[1] = s->nb_x[l][1];
+      comm_push_flags(c, l, 1, &ps, nullptr);
+    }
+  }
   if (!L[l].active) {
-    k_up_interp<CDIR><<<persist_blocks(f.i1 - f.i0, f.n1), dim3(BX, BY), 0, st>>>(f, fx, L[l + 1].v, L[l + 1].v.x, s->scal);
+    k_up_interp<CDIR><<<persist_blocks(f.i1 - f.i0, f.n1), dim3(BX, BY), 0, st>>>(f, fx, L[l + 1].v, L[l + 1].v.x, s->scal, wt, ps);
     FS_LAUNCHED();
     return 0;
   }
@@ -922,18 +993,21 @@ static int launch_up(fsgpu_ps* s, int l, const double* fb, double* fx, int dot_m
   const unsigned nb = march_blocks(f.i1 - f.i0, strips, mr, UP_MINB);
   const int bl = 32 * MWARPS;
   const BShift bs{l == 0 ? s->b_shift : nullptr, s->b_shift_size};
-#define UP_ARGS f, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket, bs
+#define UP_ARGS f, fb, fx, L[l + 1].v, L[l + 1].v.x, L[l].weight, mr, s->scal, c->part, c->ticket, bs, wt, ps
   if (ring_level(s, f.i1 - f.i0, f.n1)) {  // bandwidth-bound levels: operands through the TMA ring
-    static const bool carve = ring_carveout((const void*)k_up_ring<CDIR, 0>) &&
-                              ring_carveout((const void*)k_up_ring<CDIR, 1>) &&
-                              ring_carveout((const void*)k_up_ring<CDIR, 2>);
+    static const bool carve = ring_carveout((const void*)k_up_ring<CDIR, 0, false>) &&
+                              ring_carveout((const void*)k_up_ring<CDIR, 0, true>) &&
+                              ring_carveout((const void*)k_up_ring<CDIR, 1, false>) &&
+                              ring_carveout((const void*)k_up_ring<CDIR, 2, false>);
     (void)carve;
-    if (dot_mode == 1) k_up_ring<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
-    else if (dot_mode == 2) k_up_ring<CDIR, 2><<<nb, bl, 0, st>>>(UP_ARGS);
-    else k_up_ring<CDIR, 0><<<nb, bl, 0, st>>>(UP_ARGS);
-  } else if (dot_mode == 1) k_up_march<CDIR, 1><<<nb, bl, 0, st>>>(UP_ARGS);
-  else if (dot_mode == 2) k_up_march<CDIR, 2><<<nb, bl, 0, st>>>(UP_ARGS);
-  else k_up_march<CDIR, 0><<<nb, bl, 0, st>>>(UP_ARGS);
+    if (dot_mode == 1) k_up_ring<CDIR, 1, false><<<nb, bl, 0, st>>>(UP_ARGS);
+    else if (dot_mode == 2) k_up_ring<CDIR, 2, false><<<nb, bl, 0, st>>>(UP_ARGS);
+    else if (ps.on) k_up_ring<CDIR, 0, true><<<nb, bl, 0, st>>>(UP_ARGS);
+    else k_up_ring<CDIR, 0, false><<<nb, bl, 0, st>>>(UP_ARGS);
+  } else if (dot_mode == 1) k_up_march<CDIR, 1, false><<<nb, bl, 0, st>>>(UP_ARGS);
+  else if (dot_mode == 2) k_up_march<CDIR, 2, false><<<nb, bl, 0, st>>>(UP_ARGS);
+  else if (ps.on) k_up_march<CDIR, 0, true><<<nb, bl, 0, st>>>(UP_ARGS);
+  else k_up_march<CDIR, 0, false><<<nb, bl, 0, st>>>(UP_ARGS);
 #undef UP_ARGS
   FS_LAUNCHED();
   return 0;
@@ -998,6 +1072,7 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
   // (every rank writes its rows into a zeroed full array, then a sum all-reduce).
   const int lt = tail_start(s);  // levels [lt, nl) run inside k_tail_vcycle (lt == nl: none)
   const int lbot = lt < nl ? lt : nl - 1;
+  if (s->push_ready) s->push_epoch = comm_push_next_epoch(s->c);  // one per V-cycle, the same count on every rank
   for (int l = 0; l <= lbot - 1; ++l) {
     const double* fb = l == 0 ? r : L[l].v.b;
     ProfScope ps_(l == 0 ? PROF_DOWN0 : PROF_DOWN, st);
@@ -1005,6 +1080,10 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
     const size_t cn = (size_t)(L[l + 1].v.n0 * L[l + 1].v.pitch);
     double* crow0 = L[l + 1].v.b + FS_RO * L[l + 1].v.pitch;  // row 0 of the replicated level
     if (gather) FS_CUDA(cudaMemsetAsync(crow0, 0, cn * sizeof(double), st));
+    if (dist && l + 1 < s->ld && s->push_ready) {  // the kernel pushes its boundary rows itself (p2p.cuh)
+      if (launch_down(s, l, fb)) return 1;
+      continue;
+    }
     if (dist && l + 1 < s->ld) {
       // the coarse rhs needs FS_RO halo rows: boundary rows first, their exchange on the transport's
       // stream while the interior rows are restricted
@@ -1040,7 +1119,9 @@ int ps_vcycle(fsgpu_ps* s, const double* r, double* z, int dot_mode) {
     auto up = [&](int64_t r0, int64_t r1) {
       return L[l].cdir == 0 ? launch_up<0>(s, l, fb, fx, dm, r0, r1) : launch_up<1>(s, l, fb, fx, dm, r0, r1);
     };
-    if (dist && l >= 1 && l < s->ld) {  // x of a distributed level: one halo row for the next finer level
+    if (dist && l >= 1 && l < s->ld && s->push_ready) {
+      if (up(-1, -1)) return 1;
+    } else if (dist && l >= 1 && l < s->ld) {  // x of a distributed level: one halo row for the next finer level
       const SlabSplit sp = ps_split(s, l, 1);
       bool async = false;
       if (sp.on) {

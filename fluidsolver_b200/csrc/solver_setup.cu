@@ -293,6 +293,39 @@ static int partition(fsgpu_ps* s) {
   return 0;
 }
 
+// Fused push (p2p.cuh): map the neighbours' slabs and learn where their b and x arrays of every distributed
+// level live, so that the marching kernels can store boundary rows straight into the neighbours' halo rows.
+// Collective; every (re)allocation of the levels repeats it.  Leaves push_ready false when the mailbox
+// transport is off or a rank cannot map a neighbour (the exchanges then run as separate kernels).
+static int map_neighbour_levels(fsgpu_ps* s) {
+  fsgpu_ctx* c = s->c;
+  s->push_ready = false;
+  if (s->nb_token) { comm_unmap_neighbours(c, s->nb_token); s->nb_token = nullptr; }
+  if (c->nranks <= 1 || !comm_push_enabled(c) || s->ld > P2P_PUSH_LEVELS) return 0;
+  void *up = nullptr, *dn = nullptr;
+  if (comm_map_neighbours(c, s->slab, &up, &dn, &s->nb_token)) return 1;
+  if (!s->nb_token) return 0;
+  // offsets (in doubles, signed) of the virtual bases of b and x relative to each rank's slab
+  struct Rec { long long off_b[FS_MAX_LEVELS], off_x[FS_MAX_LEVELS]; };
+  Rec mine{};
+  for (int l = 1; l < s->ld; ++l) {
+    mine.off_b[l] = (long long)(s->L[l].v.b - s->slab);
+    mine.off_x[l] = (long long)(s->L[l].v.x - s->slab);
+  }
+  std::vector<Rec> all((size_t)c->nranks);
+  if (comm_allgather_host(c, &mine, sizeof(Rec), all.data())) return 1;
+  void* nbp[2] = {up, dn};
+  const int peer[2] = {c->rank - 1, c->rank + 1 < c->nranks ? c->rank + 1 : -1};
+  for (int l = 0; l < FS_MAX_LEVELS; ++l)
+    for (int sd = 0; sd < 2; ++sd) {
+      const bool on = l >= 1 && l < s->ld && peer[sd] >= 0 && nbp[sd];
+      s->nb_b[l][sd] = on ? static_cast<double*>(nbp[sd]) + all[(size_t)peer[sd]].off_b[l] : nullptr;
+      s->nb_x[l][sd] = on ? static_cast<double*>(nbp[sd]) + all[(size_t)peer[sd]].off_x[l] : nullptr;
+    }
+  s->push_ready = true;
+  return 0;
+}
+
 // (re)allocate the level arrays for the current schedule; returns 0 on success
 static int alloc_levels(fsgpu_ps* s) {
   const Geom& g = s->c->g;
@@ -333,7 +366,8 @@ static int alloc_levels(fsgpu_ps* s) {
   }
   cur = s->nl - 1;
   s->ctmp = take((size_t)(c.rows * c.v.pitch));
-  return comm_alloc_fence(s->c);
+  if (comm_alloc_fence(s->c)) return 1;
+  return map_neighbour_levels(s);
 }
 
 static dim3 lvl_grid(const LevelDev& v) {

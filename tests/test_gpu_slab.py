@@ -111,9 +111,15 @@ def test_slab_stencil_ops(F, oracle, R, nx, ny):
         assert ra[r] == ra[0]
 
 
-@pytest.mark.parametrize("R,name", [(2, "cavity"), (3, "cavity"), (2, "drop"), (4, "aniso")])
-def test_slab_solve(F, oracle, R, name):
-    """set_pressure_operator + rhs + solve: same iteration count and solution as one context"""
+@pytest.mark.parametrize("R,name", [(2, "cavity"), (3, "cavity"), (2, "drop"), (4, "aniso"), (2, "cavity-deep"),
+                                    (3, "drop-deep")])
+def test_slab_solve(F, oracle, R, name, monkeypatch):
+    """set_pressure_operator + rhs + solve: same iteration count and solution as one context
+    ("-deep": multigrid levels stay distributed down to ~100 points instead of 2^18, so that the exchanges of
+    the coarse levels, which the production threshold only reaches on multi-GPU grids, run here too)"""
+    if name.endswith("-deep"):
+        monkeypatch.setenv("FSGPU_REPL_POINTS", "100")
+        name = name[:-5]
     if name == "cavity":
         st = cavity_state(oracle, 96, 80, seed=5)
     elif name == "drop":
@@ -138,6 +144,8 @@ def test_slab_solve(F, oracle, R, name):
     b, rb = run_single(F, st, bc, body)
     nl, ld = got[(R, 0)]
     assert nl == got[(1, 0)][0] and 1 <= ld < nl, (nl, ld)
+    if "FSGPU_REPL_POINTS" in os.environ:
+        assert ld >= 4, (nl, ld)
     assert all(x == ra[0] for x in ra)
     assert ra[0][0] < 1e-12 and abs(ra[0][1] - rb[1]) <= 1
     dpa, dpb = a["DELTA_P"], b["DELTA_P"]
@@ -191,20 +199,25 @@ def test_slab_timesteps(F, oracle, name, kind, n, nsub, flags, R):
     assert ep <= (1e-5 if floor else 1e-8)
 
 
-@pytest.mark.parametrize("R,overlap", [(2, False), (3, False), (2, True), (3, True)])
+@pytest.mark.parametrize("R,overlap", [(2, False), (3, False), (2, True), (3, True), (2, "push"), (3, "push")])
 def test_slab_timesteps_p2p_halo(F, oracle, R, overlap, monkeypatch):
     """FSGPU_HALO=p2p: halo rows travel through peer-mapped mailboxes (one kernel per exchange) and the PCG dot
     products are all-reduced inside their reduction kernels, instead of the staged copies.  Without overlap the
     results equal the default transport's bit for bit; with it (boundary rows first, exchange on the transport's
-    stream beside the interior launch) only the association of the sum of delta_p changes."""
+    stream beside the interior launch) only the association of the sum of delta_p changes.  "push": the fused
+    form -- producer kernels of the distributed multigrid levels store boundary rows straight into the mapped
+    neighbour arrays and raise a flag, consumers wait in their prologue -- again bit for bit."""
     st, bc = cavity_state(oracle, 96, 96), cavity_bc()
     oracle.apply_velocity_bconds(st, bc)
-    direct = []
+    direct, dlev = [], []
+    # keep levels distributed down to ~100 points, so that the exchanges of the coarse levels run too
+    monkeypatch.setenv("FSGPU_REPL_POINTS", "100")
 
     def body(fs, r):
         direct.append(fs.halo_is_direct())
         ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
         ps.set_pressure_operator()
+        dlev.append(ps.num_distributed_levels)
         hist = []
         for _ in range(2):
             dt = fs.adjust_dt(0.9, 0.1)
@@ -217,11 +230,15 @@ def test_slab_timesteps_p2p_halo(F, oracle, R, overlap, monkeypatch):
     del direct[:]
     monkeypatch.setenv("FSGPU_HALO", "p2p")
     monkeypatch.setenv("FSGPU_P2P_TIMEOUT_S", "5")
-    if overlap:
+    if overlap == "push":  # the marching kernels store their boundary rows into the neighbours' halos themselves
+        monkeypatch.setenv("FSGPU_PUSH", "1")
+        overlap = False
+    elif overlap:
         monkeypatch.setenv("FSGPU_OVERLAP", "1")
         monkeypatch.setenv("FSGPU_OVERLAP_MIN_POINTS", "1")
     a, ra = run_ranks(F, st, bc, R, body, fields=("U", "V", "P"))
     assert all(direct) and len(direct) == R
+    assert min(dlev) >= 4, dlev
     assert ra == rb
     for n in ("U", "V", "P"):
         if overlap:
