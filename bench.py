@@ -58,7 +58,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-anchor", action="store_true", help="N > 1: skip the 1-GPU timing of the same grid")
     ap.add_argument("--halo", default="", choices=["", "nccl", "p2p"],
-                    help="N > 1: p2p = halo rows and scalar reductions through peer-mapped mailboxes (sets FSGPU_HALO)")
+                    help="N > 1: sets FSGPU_HALO (default: the library's, i.e. peer-mapped mailboxes + fused push; nccl = NCCL send/recv)")
     ap.add_argument("--prof", default="", help="kernel class to time for the roofline (default: auto)")
     return ap.parse_args()
 
@@ -448,8 +448,9 @@ def main():
                        "mg_depth": "uncapped (coarsest grid = 2 points)" if a.max_levels >= 40 else f"capped at {a.max_levels}",
                        "reference_depth_16": ref_depth, "same_problem_1gpu": anchor,
                        "decomposition": None if world == 1 else
-                       f"{world} slabs of i-rows, " + ("mailbox (peer-mapped, one kernel per exchange) halo exchange + scalar "
-                                                     "all-reduce, NCCL for large reductions" if direct else
+                       f"{world} slabs of i-rows, " + ("peer-mapped transport (boundary rows pushed by the producing kernels on "
+                                                     "the multigrid levels, mailbox kernels elsewhere, in-kernel scalar "
+                                                     "all-reduce), NCCL for large reductions" if direct else
                                                      "NCCL halo exchange + all-reduce") + ", multigrid levels "
                        f"0..{levels[1] - 1} distributed, {levels[1]}..{levels[0] - 1} replicated", "l2": "inputs larger than L2 "
                        f"(each field {cells * 8 / 1e6:.0f} MB vs 126 MB L2)", "max_abs_U": umax},

@@ -324,8 +324,12 @@ struct Comm {
 // off on EVERY rank: the decision is all-reduced) -- the NCCL / staged exchange keeps working.
 static int p2p_setup(fsgpu_ctx* c, Comm* cm) {
   P2PBox& b = cm->p2p;
+  // One process per GPU: the mailboxes (with the fused push) are the default transport -- 99.2 ms per 16384^2 step on
+  // 8 GPUs against 102.6 with NCCL send/recv (profiles/r02_multigpu.txt); FSGPU_HALO=nccl keeps everything on NCCL.
+  // The in-process test transport takes them only on request (FSGPU_HALO=p2p).
   const char* env = getenv("FSGPU_HALO");
-  if (!env || strcmp(env, "p2p") != 0) return 0;
+  const bool want = env ? strcmp(env, "p2p") == 0 : cm->transport == FSGPU_TRANSPORT_NCCL;
+  if (!want) return 0;
   b.cap = (size_t)((8 * c->g.pitch + 15) / 16 * 16);  // the widest exchange: 4 arrays x FS_RO rows
   b.red_off = 256 + 4 * b.cap * sizeof(double);
   b.push_off = b.red_off + P2P_MAX_RANKS * sizeof(unsigned long long) +

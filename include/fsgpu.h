@@ -119,9 +119,13 @@ enum { FSGPU_TRANSPORT_NCCL = 0, FSGPU_TRANSPORT_LOCAL = 1 };
 int fsgpu_comm_id(void* id128); /* ncclGetUniqueId */
 int fsgpu_create_slab(int64_t nx, int64_t ny, double dx, double dy, int device, int rank, int nranks,
                       const void* id128, int transport, fsgpu_ctx** out);
-/* Environment FSGPU_HALO=p2p (read by fsgpu_create_slab): halo rows and scalar all-reduces bypass NCCL
- * and travel through peer-mapped mailboxes (cudaIpc between the processes), one kernel per exchange;
- * falls back to the transport above on every rank if any rank cannot map a peer.  *on = 1 if active. */
+/* With FSGPU_TRANSPORT_NCCL (one process per GPU) halo rows and scalar all-reduces travel through peer-mapped
+ * memory by default (cudaIpc between the processes): mailboxes with one kernel per exchange, the PCG dot
+ * products all-reduced inside their reduction kernels, and the multigrid kernels of the distributed levels
+ * storing their boundary rows straight into the neighbours' halo rows (FSGPU_PUSH=0: exchange kernels
+ * there too).  Every rank falls back to NCCL send/recv + all-reduce if any rank cannot map a peer, or
+ * with FSGPU_HALO=nccl.  The in-process transport uses the mailboxes with FSGPU_HALO=p2p only.
+ * *on = 1 if the peer-mapped path is active. */
 int fsgpu_halo_is_direct(fsgpu_ctx* c, int* on);
 /* host-only partition rule (no device needed): rows [*a_lo, *a_hi) of rank `rank` */
 int fsgpu_slab_range(int64_t nx, int rank, int nranks, int64_t* a_lo, int64_t* a_hi);
