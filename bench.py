@@ -204,8 +204,8 @@ ALGO_BYTES = {
     "vcycle_down_l0": 36.0,    # read r, d, cx, cy; write b_coarse (0.5)   (dinv, pc recomputed in registers)
     "vcycle_up_l0": 44.0,      # read r, d, cx, cy, x_coarse (0.5); write z (dinv, pc recomputed in registers)
     "momentum": 112.0,         # 12 fields read, U and V written
-    "div_rhs": 48.0,           # read U, V; write div, rhs; second pass rhs -= mean (read + write)
-    "shift_correct": 104.0,    # sum dp (1), dp -= c (2), read dp, p, U, V, rho_u, rho_v; write p, U, V (10)
+    "div_rhs": 32.0,           # read U, V; write div, rhs (the mean is subtracted by the solver's first readers)
+    "shift_correct": 80.0,     # read dp, p, U, V, rho_u, rho_v; write dp', p, U, V (one pass; the sum of dp rides on PCG)
 }
 
 

@@ -4,11 +4,8 @@
 // cites what it replaces):
 //   k_momentum<...>      calc_mid_time + calc_dmomdt + update_velocity   Operators.hpp:44-49,
 //                        FS.hpp:158-315, FS.hpp:423-436 (fusion pattern: bench/update-velo-fuse.cpp)
-//   k_bc_lr / k_bc_bt    apply_velocity_bconds                           BoundaryConditions.hpp:14-224
-//   k_outflow_fix        channel outflow mass fix                        test/LaminarChannel.cpp:55-66,201-205
-//   k_divergence, k_rhs  calc_divergence, fill_pressure_rhs              Operators.hpp:32-41, LinearSystem.hpp:125-155
-//   k_sum / k_correct    shift_pressure_to_zero + projection             Operators.hpp:52-62,78-82, LidDrivenFlow.cpp:153-160
-//   k_cfl, k_absmax      adjust_dt, abs_max                              FS.hpp:100-128, Utility.hpp:80-88
+// (boundary conditions and the channel flow corrections: bconds.cu; divergence, rhs, projection and the
+// reductions: project.cu)
 #include "ctx.h"
 
 #include <math.h>
