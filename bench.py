@@ -26,6 +26,9 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# every kernel is loaded when the library is, not at its first launch (a first launch under lazy loading waits for
+# the device to drain, which a rank whose kernel is waiting for a neighbour's flag does not do quickly)
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
 # CPU-baseline protocol: all host cores, threads pinned (OMP_PROC_BIND=close,
 # OMP_PLACES=cores; without binding, 8 spinning threads on the build container's 8 vCPUs ran the reference 4x
 # slower).  The binding must be in the environment before any OpenMP runtime is loaded AND it also pins the

@@ -10,6 +10,8 @@ Round 1 measured 710 ms per 16384^2 step on 8 GPUs with 1.7 % of it inside the d
 (profiles/bench_r01h_n8_16384.json): ~20 ms per PCG iteration for ~31 stream-ordered NCCL calls."""
 import os
 import sys
+
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")  # see bench.py
 import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

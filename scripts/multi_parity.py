@@ -11,6 +11,8 @@ pinned to the oracle / the unmodified reference by tests/; this ties the N-GPU p
 import os
 import sys
 
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")  # see bench.py
+
 import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

@@ -5,6 +5,8 @@ exchanges / all-reduces enqueued inside its scope; ranks 0 and 1 print their tab
 import os
 import sys
 
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")  # see bench.py
+
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import fluidsolver_b200 as F  # noqa: E402
 

@@ -1,7 +1,14 @@
 import os
 import sys
 
-import pytest
+# In-process ranks on ONE GPU (tests/test_gpu_slab.py, test_gpu_zzz_inprocess_mailbox.py): the mailbox kernels of one
+# rank wait on the device for a kernel of another rank.  With CUDA's default LAZY module loading the first launch
+# of a kernel loads its code, which waits for the device to drain -- i.e. for the very kernel that is waiting for it:
+# measured 1-2 device-side timeouts per run of the mailbox file with LAZY, none in 6 runs with EAGER
+# (scripts/gpu_flaky.sh).  Must be in the environment before CUDA starts.
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")
+
+import pytest  # noqa: E402
 
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

@@ -197,51 +197,3 @@ def test_slab_timesteps(F, oracle, name, kind, n, nsub, flags, R):
     floor = kind in ("tgv", "channel")
     assert ev <= (1e-7 if floor else 1e-10)
     assert ep <= (1e-5 if floor else 1e-8)
-
-
-@pytest.mark.parametrize("R,overlap", [(2, False), (3, False), (2, True), (3, True), (2, "push"), (3, "push")])
-def test_slab_timesteps_p2p_halo(F, oracle, R, overlap, monkeypatch):
-    """FSGPU_HALO=p2p: halo rows travel through peer-mapped mailboxes (one kernel per exchange) and the PCG dot
-    products are all-reduced inside their reduction kernels, instead of the staged copies.  Without overlap the
-    results equal the default transport's bit for bit; with it (boundary rows first, exchange on the transport's
-    stream beside the interior launch) only the association of the sum of delta_p changes.  "push": the fused
-    form -- producer kernels of the distributed multigrid levels store boundary rows straight into the mapped
-    neighbour arrays and raise a flag, consumers wait in their prologue -- again bit for bit."""
-    st, bc = cavity_state(oracle, 96, 96), cavity_bc()
-    oracle.apply_velocity_bconds(st, bc)
-    direct, dlev = [], []
-    # keep levels distributed down to ~100 points, so that the exchanges of the coarse levels run too
-    monkeypatch.setenv("FSGPU_REPL_POINTS", "100")
-
-    def body(fs, r):
-        direct.append(fs.halo_is_direct())
-        ps = F.LinearSolver(fs, tol=1e-13, max_iter=500)
-        ps.set_pressure_operator()
-        dlev.append(ps.num_distributed_levels)
-        hist = []
-        for _ in range(2):
-            dt = fs.adjust_dt(0.9, 0.1)
-            hist.append((dt, fs.step(ps, dt, 5)[1]))
-        ps.close()
-        return hist
-
-    b, rb = run_ranks(F, st, bc, R, body, fields=("U", "V", "P"))
-    assert not any(direct)
-    del direct[:]
-    monkeypatch.setenv("FSGPU_HALO", "p2p")
-    monkeypatch.setenv("FSGPU_P2P_TIMEOUT_S", "5")
-    if overlap == "push":  # the marching kernels store their boundary rows into the neighbours' halos themselves
-        monkeypatch.setenv("FSGPU_PUSH", "1")
-        overlap = False
-    elif overlap:
-        monkeypatch.setenv("FSGPU_OVERLAP", "1")
-        monkeypatch.setenv("FSGPU_OVERLAP_MIN_POINTS", "1")
-    a, ra = run_ranks(F, st, bc, R, body, fields=("U", "V", "P"))
-    assert all(direct) and len(direct) == R
-    assert min(dlev) >= 4, dlev
-    assert ra == rb
-    for n in ("U", "V", "P"):
-        if overlap:
-            assert np.abs(a[n] - b[n]).max() <= 1e-13 * np.abs(b[n]).max(), n
-        else:
-            assert np.array_equal(a[n], b[n]), n
