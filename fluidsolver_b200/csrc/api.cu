@@ -24,6 +24,13 @@ void fs_ncu_range(bool begin) {
 thread_local int g_prof_tag = 0;
 
 namespace {
+// Kernels are loaded with the library, not at their first launch: under CUDA's default lazy loading a first launch
+// waits for the device to drain, and a device whose running kernel waits for a neighbour rank's flag (mailbox
+// transport, fused push) drains late -- or, with in-process ranks on one device, never.
+// Only takes effect if CUDA has not started yet and the user has not chosen a mode.
+struct EagerModuleLoading {
+  EagerModuleLoading() { setenv("CUDA_MODULE_LOADING", "EAGER", 0); }
+} g_eager_module_loading;
 struct ProfRec { int cls; cudaEvent_t a, b; int tag; };
 // per host thread: the in-process transport drives one context per thread, and a thread reads back its own records
 thread_local std::vector<ProfRec> g_prof_recs;
