@@ -279,7 +279,8 @@ typedef struct {
   int max_iter;
   int psd;        /* FSGPU_PSD_* */
   int relax;      /* FSGPU_RELAX_*; 0 = default (Jacobi, the reference's configuration) */
-  int max_levels; /* 0 = default 16 = PS_PFMG_MAX_LEVELS (src/LinearSolver_StructHypre.hpp:221) */
+  int max_levels; /* 0 = default 16 = PS_PFMG_MAX_LEVELS (src/LinearSolver_StructHypre.hpp:221); values above 16
+                   * coarsen further but stop at a two-point coarsest grid */
   int skip_relax; /* -1 = default (1, HYPRE's pfmg.c:38); 0/1 */
 } fsgpu_ps_opts;
 int fsgpu_ps_create(fsgpu_ctx* c, const fsgpu_ps_opts* o, fsgpu_ps** out);
